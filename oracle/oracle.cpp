@@ -1,0 +1,544 @@
+/*
+ * oracle.cpp — CPU oracle for the RenderEngine raster hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+ * load this.  The product (renderengine_b200/) never links, imports or calls it.
+ *
+ * PARITY STATUS: "parity unpinned" at the rasteriser boundary — the reference has no tests,
+ * goldens or CPU rasteriser and its Vulkan path cannot run here.  The
+ * fixed-function rules below instantiate the Vulkan state the reference sets
+ * (Source/VkRHI/RHI/GraphicsPipelineCache.cpp:257-365) per SURVEY.md Appendix B.  The shading
+ * arithmetic restates Assets/Shaders/phong.glsl:39-81 and shadow.glsl:24-56 in glm's operation
+ * order and IS pinned: tests/test_oracle_golden.py checks it bit-for-bit against vectors produced
+ * by the reference's own GLSL compiled as C++ (oracle/ref_shim.cpp -> oracle/_ref/libref.so).
+ *
+ * Build: g++ -O2 -ffp-contract=off -fno-fast-math -shared -fPIC (oracle/Makefile).  Every fp32
+ * operation on the depth / coverage / shadow-lookup path is written as an un-fused binary op in a
+ * fixed order; the CUDA path must reproduce that order exactly.
+ */
+#include "oracle.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+namespace {
+
+constexpr uint32_t LIGHT_TYPE_DIRECTIONAL = 1;   // phong.glsl:16
+constexpr uint32_t LIGHT_TYPE_SPOT = 3;          // phong.glsl:18
+constexpr float GUARD_PX = 1048576.0f;           // |x_f|,|y_f| <= 2^20 px keeps 24.8 fixed point in int32
+constexpr uint32_t TRI_NONE = 0xFFFFFFFFu;
+
+struct V3 { float x, y, z; };
+struct V4 { float x, y, z, w; };
+
+// glm::mat4 * glm::vec4 — ThirdParty/glm/glm/detail/type_mat4x4.inl:562-573:
+// (m0*v0 + m1*v1) + (m2*v2 + m3*v3), column-major m[c*4+r].
+inline V4 mat4_mul(const float* m, V4 v) {
+    float o[4];
+    for (int r = 0; r < 4; ++r) {
+        float mul0 = m[0 + r] * v.x;
+        float mul1 = m[4 + r] * v.y;
+        float add0 = mul0 + mul1;
+        float mul2 = m[8 + r] * v.z;
+        float mul3 = m[12 + r] * v.w;
+        float add1 = mul2 + mul3;
+        o[r] = add0 + add1;
+    }
+    return {o[0], o[1], o[2], o[3]};
+}
+
+// glm::mat4 * glm::mat4, non-aligned path — type_mat4x4.inl:679-694: ((A0*b.x + A1*b.y) + A2*b.z) + A3*b.w.
+inline void mat4_mul_mat4(const float* a, const float* b, float* out) {
+    float tmp[16];
+    for (int c = 0; c < 4; ++c)
+        for (int r = 0; r < 4; ++r) {
+            float t = a[0 + r] * b[c * 4 + 0];
+            t = t + a[4 + r] * b[c * 4 + 1];
+            t = t + a[8 + r] * b[c * 4 + 2];
+            t = t + a[12 + r] * b[c * 4 + 3];
+            tmp[c * 4 + r] = t;
+        }
+    std::memcpy(out, tmp, sizeof tmp);
+}
+
+inline float dot3(V3 a, V3 b) {   // glm compute_dot<vec3>: func_geometric.inl:48-55
+    float tx = a.x * b.x, ty = a.y * b.y, tz = a.z * b.z;
+    return (tx + ty) + tz;
+}
+inline V3 sub3(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 add3(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V3 neg3(V3 a) { return {-a.x, -a.y, -a.z}; }
+inline V3 normalize3(V3 v) {      // v * (1/sqrt(dot(v,v))) — func_geometric.inl:104, func_exponential.inl:138
+    float inv = 1.0f / std::sqrt(dot3(v, v));
+    return {v.x * inv, v.y * inv, v.z * inv};
+}
+inline float glm_max(float x, float y) { return (x < y) ? y : x; }   // func_common.inl
+inline float glm_min(float x, float y) { return (y < x) ? y : x; }
+
+// transpose(inverse(mat3(T))) — primitive.vert:55; glm inv3x3<false> func_matrix.inl:353-376.
+// out9 is column-major N[c*3+r].
+void normal_matrix(const float* T, float* N) {
+    auto m = [&](int c, int r) { return T[c * 4 + r]; };
+    float det = +m(0, 0) * (m(1, 1) * m(2, 2) - m(2, 1) * m(1, 2))
+                - m(1, 0) * (m(0, 1) * m(2, 2) - m(2, 1) * m(0, 2))
+                + m(2, 0) * (m(0, 1) * m(1, 2) - m(1, 1) * m(0, 2));
+    float ood = 1.0f / det;
+    float inv[3][3];   // inv[c][r]
+    inv[0][0] = +(m(1, 1) * m(2, 2) - m(2, 1) * m(1, 2));
+    inv[1][0] = -(m(1, 0) * m(2, 2) - m(2, 0) * m(1, 2));
+    inv[2][0] = +(m(1, 0) * m(2, 1) - m(2, 0) * m(1, 1));
+    inv[0][1] = -(m(0, 1) * m(2, 2) - m(2, 1) * m(0, 2));
+    inv[1][1] = +(m(0, 0) * m(2, 2) - m(2, 0) * m(0, 2));
+    inv[2][1] = -(m(0, 0) * m(2, 1) - m(2, 0) * m(0, 1));
+    inv[0][2] = +(m(0, 1) * m(1, 2) - m(1, 1) * m(0, 2));
+    inv[1][2] = -(m(0, 0) * m(1, 2) - m(1, 0) * m(0, 2));
+    inv[2][2] = +(m(0, 0) * m(1, 1) - m(1, 0) * m(0, 1));
+    for (int c = 0; c < 3; ++c)
+        for (int r = 0; r < 3; ++r) inv[c][r] = inv[c][r] * ood;
+    for (int c = 0; c < 3; ++c)
+        for (int r = 0; r < 3; ++r) N[c * 3 + r] = inv[r][c];   // transpose
+}
+inline V3 mat3_mul(const float* N, V3 v) {   // type_mat3x3.inl:472-473: (m0*x + m1*y) + m2*z
+    V3 o;
+    o.x = (N[0] * v.x + N[3] * v.y) + N[6] * v.z;
+    o.y = (N[1] * v.x + N[4] * v.y) + N[7] * v.z;
+    o.z = (N[2] * v.x + N[5] * v.y) + N[8] * v.z;
+    return o;
+}
+
+struct Light {          // std430 layout of phong.glsl:20-37
+    int32_t type; V3 position; V3 direction; V4 ambient, diffuse, specular;
+    float innerCutoff, outerCutoff; uint32_t shadowIndex;
+};
+Light load_light(const uint8_t* p) {
+    Light l;
+    std::memcpy(&l.type, p + 0, 4);
+    std::memcpy(&l.position, p + 16, 12);
+    std::memcpy(&l.direction, p + 32, 12);
+    std::memcpy(&l.ambient, p + 48, 16);
+    std::memcpy(&l.diffuse, p + 64, 16);
+    std::memcpy(&l.specular, p + 80, 16);
+    std::memcpy(&l.innerCutoff, p + 96, 4);
+    std::memcpy(&l.outerCutoff, p + 100, 4);
+    std::memcpy(&l.shadowIndex, p + 104, 4);
+    return l;
+}
+struct PhongProps { V4 diffuse, specular; float shininess; };
+
+// phong.glsl:39-81, statement for statement.
+V4 phong_lighting(const Light& light, const PhongProps& props, V3 normal, V3 fragPos, V3 viewPos, float shadow) {
+    V3 viewDir = normalize3(sub3(viewPos, fragPos));
+    V3 lightDir = (uint32_t)light.type == LIGHT_TYPE_DIRECTIONAL ? neg3(light.direction) : sub3(light.position, fragPos);
+    float lightDistance = std::sqrt(dot3(lightDir, lightDir));
+    lightDir = {lightDir.x / lightDistance, lightDir.y / lightDistance, lightDir.z / lightDistance};
+
+    V4 ambient = {light.ambient.x * props.diffuse.x, light.ambient.y * props.diffuse.y,
+                  light.ambient.z * props.diffuse.z, light.ambient.w * props.diffuse.w};
+
+    float k_d = glm_max(dot3(lightDir, normal), 0.0f);
+    V4 diffuse = {(k_d * light.diffuse.x) * props.diffuse.x, (k_d * light.diffuse.y) * props.diffuse.y,
+                  (k_d * light.diffuse.z) * props.diffuse.z, (k_d * light.diffuse.w) * props.diffuse.w};
+
+    V3 h = normalize3(add3(lightDir, viewDir));
+    float k_s = std::pow(glm_max(dot3(normal, h), 0.0f), props.shininess);
+    V4 specular = {(k_s * light.specular.x) * props.specular.x, (k_s * light.specular.y) * props.specular.y,
+                   (k_s * light.specular.z) * props.specular.z, (k_s * light.specular.w) * props.specular.w};
+
+    float attenuation = 1.0f;
+    if ((uint32_t)light.type != LIGHT_TYPE_DIRECTIONAL) attenuation = 1.0f / lightDistance;
+
+    if ((uint32_t)light.type == LIGHT_TYPE_SPOT) {
+        float cos_theta = dot3(neg3(lightDir), normalize3(light.direction));
+        float epsilon = light.innerCutoff - light.outerCutoff;
+        float intensity = glm_min(glm_max((cos_theta - light.outerCutoff) / epsilon, 0.0f), 1.0f);
+        diffuse = {diffuse.x * intensity, diffuse.y * intensity, diffuse.z * intensity, diffuse.w * intensity};
+        specular = {specular.x * intensity, specular.y * intensity, specular.z * intensity, specular.w * intensity};
+    }
+    float k = 1.0f - shadow;
+    V4 r;
+    r.x = (ambient.x + k * (diffuse.x + specular.x)) * attenuation;
+    r.y = (ambient.y + k * (diffuse.y + specular.y)) * attenuation;
+    r.z = (ambient.z + k * (diffuse.z + specular.z)) * attenuation;
+    r.w = (ambient.w + k * (diffuse.w + specular.w)) * attenuation;
+    return r;
+}
+
+// Nearest, clamp-to-edge fetch of the S x S f32 shadow map (ShadowSystem.cpp:18-35; Appendix B.13).
+inline float shadow_fetch(const float* map, uint32_t S, float u, float v) {
+    float fs = (float)S;
+    float fu = std::floor(u * fs), fv = std::floor(v * fs);
+    float hi = (float)(S - 1);
+    // clamp in float first so NaN / huge values are well defined (NaN -> 0)
+    int i = (fu >= 0.0f) ? ((fu <= hi) ? (int)fu : (int)(S - 1)) : 0;
+    int j = (fv >= 0.0f) ? ((fv <= hi) ? (int)fv : (int)(S - 1)) : 0;
+    return map[(size_t)j * S + i];
+}
+
+// shadow.glsl:24-56, statement for statement.
+float compute_shadow(const Light& light, V3 fragPos, V3 normal, const float* transform, const float* map, uint32_t S) {
+    if ((uint32_t)light.type != LIGHT_TYPE_DIRECTIONAL) return 0.0f;
+    V4 flp = mat4_mul(transform, {fragPos.x, fragPos.y, fragPos.z, 1.0f});
+    V3 lightDir = normalize3(sub3(light.position, fragPos));
+    float currentDepth = flp.z / flp.w;
+    if (currentDepth > 1.0f) return 0.0f;
+    float mu = 0.5f * (flp.x / flp.w) + 0.5f;
+    float mv = 0.5f * (flp.y / flp.w) + 0.5f;
+    float bias = glm_max(0.05f * (1.0f - dot3(normal, lightDir)), 0.005f);
+    float shadow = 0.0f;
+    float texel = 1.0f / (float)S;
+    for (int x = -1; x <= 1; ++x)
+        for (int y = -1; y <= 1; ++y) {
+            float depth = shadow_fetch(map, S, mu + (float)x * texel, mv + (float)y * texel);
+            shadow += (currentDepth - bias > depth) ? 1.0f : 0.0f;
+        }
+    shadow /= 9.0f;
+    return shadow;
+}
+
+// Exact sRGB OETF + 8-bit quantisation of the R8G8B8A8_SRGB target (Swapchain.cpp:10-21; Appendix B.12).
+inline uint8_t quant8(float x) {
+    if (!(x > 0.0f)) return 0;
+    if (x >= 1.0f) return 255;
+    return (uint8_t)(int)std::floor(x * 255.0f + 0.5f);
+}
+inline float srgb_oetf(float x) {
+    if (!(x > 0.0f)) return 0.0f;
+    if (x >= 1.0f) return 1.0f;
+    return (x <= 0.0031308f) ? 12.92f * x : 1.055f * std::pow(x, 1.0f / 2.4f) - 0.055f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Geometry front end (Appendix B.1-6)
+// ---------------------------------------------------------------------------------------------
+struct Setup {
+    int32_t X[3], Y[3];
+    float z[3];
+    float w[3];
+    int64_t A2;      // < 0 for kept triangles
+    uint32_t triId;
+    int32_t x0, x1, y0, y1;   // inclusive pixel bbox (already clamped to the target)
+};
+
+enum SetupResult { KEEP = 0, REJECT = 1, NEEDS_CLIP = 2, CULLED = 3, NO_SAMPLE = 4 };
+
+struct PassParams {
+    const float* PV;     // proj*view (formed once with mat4_mul_mat4)
+    bool divideWorldByW; // primitive.vert:51 (forward) vs shadow_map.vert:49 (shadow)
+    uint32_t W, H;
+};
+
+inline V4 vertex_stage(const PassParams& pp, const float* T, const float* pos, V3* worldOut) {
+    V4 wH = mat4_mul(T, {pos[0], pos[1], pos[2], 1.0f});
+    V3 world;
+    if (pp.divideWorldByW) world = {wH.x / wH.w, wH.y / wH.w, wH.z / wH.w};
+    else world = {wH.x, wH.y, wH.z};
+    if (worldOut) *worldOut = world;
+    return mat4_mul(pp.PV, {world.x, world.y, world.z, 1.0f});
+}
+
+inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t triId, Setup& s) {
+    // B.2 trivial reject: all three outside one clip plane
+    bool allL = true, allR = true, allT = true, allB = true, allN = true, allF = true;
+    for (int k = 0; k < 3; ++k) {
+        allL = allL && (c[k].x < -c[k].w); allR = allR && (c[k].x > c[k].w);
+        allT = allT && (c[k].y < -c[k].w); allB = allB && (c[k].y > c[k].w);
+        allN = allN && (c[k].z < 0.0f);    allF = allF && (c[k].z > c[k].w);
+    }
+    if (allL || allR || allT || allB || allN || allF) return REJECT;
+    // B.3: a vertex at or behind the eye plane needs true clipping (not part of the bit-exact domain)
+    for (int k = 0; k < 3; ++k) if (!(c[k].w > 0.0f)) return NEEDS_CLIP;
+    float hw = 0.5f * (float)pp.W, hh = 0.5f * (float)pp.H;
+    for (int k = 0; k < 3; ++k) {
+        float nx = c[k].x / c[k].w, ny = c[k].y / c[k].w, nz = c[k].z / c[k].w;   // B.4
+        float xf = hw * nx + hw;
+        float yf = hh * ny + hh;
+        if (!(std::fabs(xf) <= GUARD_PX) || !(std::fabs(yf) <= GUARD_PX)) return NEEDS_CLIP;
+        s.X[k] = (int32_t)std::lrintf(xf * 256.0f);   // B.5 round-half-even, 8 sub-pixel bits
+        s.Y[k] = (int32_t)std::lrintf(yf * 256.0f);
+        s.z[k] = nz;
+        s.w[k] = c[k].w;
+    }
+    // B.6 facing: front = CCW = A2 < 0; cull back (A2 > 0) and degenerate (A2 == 0)
+    s.A2 = (int64_t)(s.X[1] - s.X[0]) * (int64_t)(s.Y[2] - s.Y[0]) - (int64_t)(s.X[2] - s.X[0]) * (int64_t)(s.Y[1] - s.Y[0]);
+    if (s.A2 >= 0) return CULLED;
+    int32_t minX = std::min(s.X[0], std::min(s.X[1], s.X[2])), maxX = std::max(s.X[0], std::max(s.X[1], s.X[2]));
+    int32_t minY = std::min(s.Y[0], std::min(s.Y[1], s.Y[2])), maxY = std::max(s.Y[0], std::max(s.Y[1], s.Y[2]));
+    // pixel centres 256*i+128 inside [min,max]
+    s.x0 = std::max((minX + 127) >> 8, 0);
+    s.x1 = std::min((maxX - 128) >> 8, (int32_t)pp.W - 1);
+    s.y0 = std::max((minY + 127) >> 8, 0);
+    s.y1 = std::min((maxY - 128) >> 8, (int32_t)pp.H - 1);
+    if (s.x0 > s.x1 || s.y0 > s.y1) return NO_SAMPLE;
+    s.triId = triId;
+    return KEEP;
+}
+
+// B.7 edge functions with interior positive (for A2 < 0) and the top-left bias folded in.
+struct Edges {
+    int64_t A[3], B[3], C[3];   // F_k(P) = A*Px + B*Py + C  (unbiased)
+    int64_t bias[3];            // 0 for top/left edges, 1 otherwise: covered iff F_k - bias_k >= 0
+};
+inline Edges make_edges(const Setup& s) {
+    Edges e;
+    for (int k = 0; k < 3; ++k) {
+        int a = (k + 1) % 3, b = (k + 2) % 3;   // edge a->b opposes vertex k
+        int64_t A = (int64_t)s.Y[b] - (int64_t)s.Y[a];
+        int64_t B = -((int64_t)s.X[b] - (int64_t)s.X[a]);
+        e.A[k] = A; e.B[k] = B;
+        e.C[k] = -(A * (int64_t)s.X[a]) - B * (int64_t)s.Y[a];
+        bool topLeft = (A > 0) || (A == 0 && B > 0);
+        e.bias[k] = topLeft ? 0 : 1;
+    }
+    return e;
+}
+
+// B.8 depth at a covered sample; F1, F2 are the unbiased edge values of vertices 1 and 2.
+inline float depth_at(const Setup& s, int64_t F1, int64_t F2) {
+    float area = (float)(-s.A2);
+    float b1 = (float)F1 / area;
+    float b2 = (float)F2 / area;
+    float z = (s.z[0] + b1 * (s.z[1] - s.z[0])) + b2 * (s.z[2] - s.z[0]);
+    if (z == 0.0f) z = 0.0f;   // canonicalise -0
+    return z;
+}
+
+struct DrawRec { uint32_t indexOffset, nbIndices, materialRaw, sceneNode; };
+
+struct Frontend {
+    std::vector<Setup> setups;       // submission order
+    std::vector<uint64_t> triPrefix; // per draw: first triId
+    uint64_t needsClip = 0;
+};
+
+unsigned thread_count(const orc_scene* s) {
+    unsigned n = s->nThreads ? s->nThreads : std::thread::hardware_concurrency();
+    return n ? n : 1;
+}
+
+template <class F> void parallel_for(unsigned nThreads, F f) {
+    if (nThreads <= 1) { f(0u); return; }
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nThreads; ++t) th.emplace_back(f, t);
+    for (auto& x : th) x.join();
+}
+
+void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe) {
+    const DrawRec* draws = reinterpret_cast<const DrawRec*>(sc->draws);
+    fe.triPrefix.resize(sc->nDraws + 1);
+    uint64_t total = 0;
+    for (uint32_t d = 0; d < sc->nDraws; ++d) { fe.triPrefix[d] = total; total += draws[d].nbIndices / 3; }
+    fe.triPrefix[sc->nDraws] = total;
+    unsigned nT = thread_count(sc);
+    std::vector<std::vector<Setup>> parts(nT);
+    std::vector<uint64_t> clip(nT, 0);
+    parallel_for(nT, [&](unsigned t) {
+        uint64_t lo = total * t / nT, hi = total * (t + 1) / nT;
+        uint32_t d = 0;
+        for (uint64_t tri = lo; tri < hi; ++tri) {
+            while (fe.triPrefix[d + 1] <= tri) ++d;
+            const DrawRec& dr = draws[d];
+            uint64_t local = tri - fe.triPrefix[d];
+            const uint32_t* ix = sc->indices + dr.indexOffset + 3 * local;
+            const float* T = sc->transforms + 16 * (size_t)dr.sceneNode;
+            V4 c[3];
+            for (int k = 0; k < 3; ++k) c[k] = vertex_stage(pp, T, sc->verts + 8 * (size_t)ix[k], nullptr);
+            Setup s;
+            SetupResult r = setup_triangle(pp, c, (uint32_t)tri, s);
+            if (r == KEEP) parts[t].push_back(s);
+            else if (r == NEEDS_CLIP) ++clip[t];
+        }
+    });
+    size_t n = 0;
+    for (auto& p : parts) n += p.size();
+    fe.setups.reserve(n);
+    for (auto& p : parts) fe.setups.insert(fe.setups.end(), p.begin(), p.end());
+    for (auto c : clip) fe.needsClip += c;
+}
+
+inline bool row_owned(const orc_scene* sc, int y) {
+    if (sc->nRanks <= 1) return true;
+    return ((uint32_t)y / sc->bandH) % sc->nRanks == sc->rank;
+}
+
+// In-order depth test "z <= stored" (LessOrEqual, GraphicsPipelineCache.cpp:330-340): processing
+// primitives in submission order makes the later primitive win ties, which is what the CUDA path's
+// (depthBits<<32 | ~triId) minimum key encodes (Appendix B.9).
+void rasterize(const orc_scene* sc, const PassParams& pp, const Frontend& fe, float* depth, uint32_t* triId,
+               bool honourRanks, uint64_t* fragCount) {
+    unsigned nT = thread_count(sc);
+    std::vector<uint64_t> frags(nT, 0);
+    const int H = (int)pp.H, W = (int)pp.W;
+    parallel_for(nT, [&](unsigned t) {
+        int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);   // rows [r0,r1)
+        for (int y = r0; y < r1; ++y)
+            for (int x = 0; x < W; ++x) { depth[(size_t)y * W + x] = 1.0f; if (triId) triId[(size_t)y * W + x] = TRI_NONE; }
+        for (const Setup& s : fe.setups) {
+            int ya = std::max(s.y0, r0), yb = std::min(s.y1, r1 - 1);
+            if (ya > yb) continue;
+            Edges e = make_edges(s);
+            for (int y = ya; y <= yb; ++y) {
+                if (honourRanks && !row_owned(sc, y)) continue;
+                int64_t Py = 256 * (int64_t)y + 128;
+                for (int x = s.x0; x <= s.x1; ++x) {
+                    int64_t Px = 256 * (int64_t)x + 128;
+                    int64_t F0 = e.A[0] * Px + e.B[0] * Py + e.C[0];
+                    int64_t F1 = e.A[1] * Px + e.B[1] * Py + e.C[1];
+                    int64_t F2 = e.A[2] * Px + e.B[2] * Py + e.C[2];
+                    if (F0 - e.bias[0] < 0 || F1 - e.bias[1] < 0 || F2 - e.bias[2] < 0) continue;
+                    float z = depth_at(s, F1, F2);
+                    if (!(z >= 0.0f && z <= 1.0f)) continue;   // B.8 depth clip
+                    ++frags[t];
+                    size_t p = (size_t)y * W + x;
+                    if (z <= depth[p]) { depth[p] = z; if (triId) triId[p] = s.triId; }
+                }
+            }
+        }
+    });
+    if (fragCount) for (auto f : frags) *fragCount += f;
+}
+
+}  // namespace
+
+extern "C" {
+
+void orc_mat4_mul(const float* a, const float* b, float* out) { mat4_mul_mat4(a, b, out); }
+void orc_mat4_mul_vec4(const float* m, const float* v, float* out) {
+    V4 r = mat4_mul(m, {v[0], v[1], v[2], v[3]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+void orc_normal_matrix(const float* mat4, float* out9) { normal_matrix(mat4, out9); }
+
+void orc_phong_lighting(const uint8_t* light112, const float* p, const float* normal, const float* fragPos,
+                        const float* viewPos, float shadow, float* out4) {
+    Light l = load_light(light112);
+    PhongProps props{{p[0], p[1], p[2], p[3]}, {p[4], p[5], p[6], p[7]}, p[8]};
+    V4 r = phong_lighting(l, props, {normal[0], normal[1], normal[2]}, {fragPos[0], fragPos[1], fragPos[2]},
+                          {viewPos[0], viewPos[1], viewPos[2]}, shadow);
+    out4[0] = r.x; out4[1] = r.y; out4[2] = r.z; out4[3] = r.w;
+}
+
+float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal, const float* transform16,
+                         const float* shadowMap, uint32_t S) {
+    Light l = load_light(light112);
+    return compute_shadow(l, {fragPos[0], fragPos[1], fragPos[2]}, {normal[0], normal[1], normal[2]}, transform16, shadowMap, S);
+}
+
+void orc_srgb8(const float* rgba, uint8_t* out4) {
+    out4[0] = quant8(srgb_oetf(rgba[0]));
+    out4[1] = quant8(srgb_oetf(rgba[1]));
+    out4[2] = quant8(srgb_oetf(rgba[2]));
+    out4[3] = quant8(rgba[3]);
+}
+
+// Shadow depth pass: ShadowSystem::Render (ShadowSystem.cpp:319-376) + shadow_map.vert:48-52 with the
+// pipeline state of ShadowSystem.cpp:37-53 (1 sample, cull back / CCW front per F5, LessOrEqual, clear 1.0).
+int orc_render_shadow(const orc_scene* sc, float* shadowMap, uint64_t* counters) {
+    if (!sc || !shadowMap || sc->shadowSize == 0) return -1;
+    float SPV[16];
+    mat4_mul_mat4(sc->shadowProj, sc->shadowView, SPV);   // shadow.proj * shadow.view (shadow_map.vert:51)
+    PassParams pp{SPV, false, sc->shadowSize, sc->shadowSize};
+    Frontend fe;
+    run_frontend(sc, pp, fe);
+    uint64_t frags = 0;
+    rasterize(sc, pp, fe, shadowMap, nullptr, false, &frags);
+    if (counters) { counters[0] = fe.needsClip; counters[1] = fe.setups.size(); counters[2] = frags; counters[3] = 0; }
+    return 0;
+}
+
+// Forward pass: MaterialSystem::Draw (MaterialSystem.cpp:88-101) + primitive.vert:49-57 + the
+// builder-defined Phong main() of Appendix B.11 over phong.glsl / shadow.glsl.
+int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth, uint32_t* triId, float* colorF32,
+                       uint8_t* colorSRGB8, uint64_t* counters) {
+    if (!sc || !depth || !triId) return -1;
+    const float* view = reinterpret_cast<const float*>(sc->view);
+    const float* proj = view + 16;
+    V3 viewPos = {view[32], view[33], view[34]};
+    float PV[16], STR[16];
+    mat4_mul_mat4(proj, view, PV);   // GetView().proj * GetView().view (primitive.vert:53)
+    const bool haveShadow = sc->shadowSize > 0 && shadowMap != nullptr;
+    if (haveShadow) mat4_mul_mat4(sc->shadowProj, sc->shadowView, STR);   // ShadowSystem.cpp:303
+    PassParams pp{PV, true, sc->width, sc->height};
+    Frontend fe;
+    run_frontend(sc, pp, fe);
+    uint64_t frags = 0;
+    rasterize(sc, pp, fe, depth, triId, true, &frags);
+    if (counters) { counters[0] = fe.needsClip; counters[1] = fe.setups.size(); counters[2] = frags; counters[3] = 0; }
+    if (!colorF32 && !colorSRGB8) return 0;
+
+    const DrawRec* draws = reinterpret_cast<const DrawRec*>(sc->draws);
+    std::vector<float> nmat((size_t)sc->nNodes * 9);
+    for (uint32_t n = 0; n < sc->nNodes; ++n) normal_matrix(sc->transforms + 16 * (size_t)n, &nmat[9 * (size_t)n]);
+    std::vector<Light> lights(sc->nLights);
+    for (uint32_t l = 0; l < sc->nLights; ++l) lights[l] = load_light(sc->lights + (size_t)l * sc->lightStride);
+
+    unsigned nT = thread_count(sc);
+    const int W = (int)sc->width, H = (int)sc->height;
+    parallel_for(nT, [&](unsigned t) {
+        int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
+        for (int y = r0; y < r1; ++y)
+            for (int x = 0; x < W; ++x) {
+                size_t p = (size_t)y * W + x;
+                V4 out = {0.0f, 0.0f, 0.0f, 1.0f};   // clear colour (RenderScene.cpp:217-220)
+                uint32_t tri = triId[p];
+                if (tri != TRI_NONE) {
+                    uint32_t d = (uint32_t)(std::upper_bound(fe.triPrefix.begin(), fe.triPrefix.end(), (uint64_t)tri) - fe.triPrefix.begin()) - 1;
+                    const DrawRec& dr = draws[d];
+                    const uint32_t* ix = sc->indices + dr.indexOffset + 3 * ((uint64_t)tri - fe.triPrefix[d]);
+                    const float* T = sc->transforms + 16 * (size_t)dr.sceneNode;
+                    const float* N = &nmat[9 * (size_t)dr.sceneNode];
+                    V4 c[3]; V3 world[3], nrm[3]; float uv[3][2];
+                    for (int k = 0; k < 3; ++k) {
+                        const float* v = sc->verts + 8 * (size_t)ix[k];
+                        c[k] = vertex_stage(pp, T, v, &world[k]);
+                        nrm[k] = normalize3(mat3_mul(N, {v[3], v[4], v[5]}));   // primitive.vert:55
+                        uv[k][0] = v[6]; uv[k][1] = v[7];
+                    }
+                    Setup s;
+                    setup_triangle(pp, c, tri, s);
+                    Edges e = make_edges(s);
+                    int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
+                    float area = (float)(-s.A2);
+                    float b[3], q[3];
+                    for (int k = 0; k < 3; ++k) {
+                        int64_t F = e.A[k] * Px + e.B[k] * Py + e.C[k];
+                        b[k] = (float)F / area;
+                        q[k] = b[k] * (1.0f / s.w[k]);   // B.10 perspective-correct weights
+                    }
+                    float den = (q[0] + q[1]) + q[2];
+                    auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) / den; };
+                    V3 fragPos = {interp(world[0].x, world[1].x, world[2].x), interp(world[0].y, world[1].y, world[2].y),
+                                  interp(world[0].z, world[1].z, world[2].z)};
+                    V3 normal = {interp(nrm[0].x, nrm[1].x, nrm[2].x), interp(nrm[0].y, nrm[1].y, nrm[2].y),
+                                 interp(nrm[0].z, nrm[1].z, nrm[2].z)};
+                    float tu = interp(uv[0][0], uv[1][0], uv[2][0]), tv = interp(uv[0][1], uv[1][1], uv[2][1]);
+                    (void)tu; (void)tv;
+
+                    uint32_t matIndex = dr.materialRaw >> 4;   // MaterialHandle::GetIndex (MaterialDefines.h:88-96)
+                    const uint8_t* mr = sc->materials + (size_t)matIndex * sc->materialStride;
+                    PhongProps props;
+                    std::memcpy(&props.diffuse, mr + 0, 16);
+                    std::memcpy(&props.specular, mr + 16, 16);
+                    std::memcpy(&props.shininess, mr + 32, 4);
+
+                    V4 acc = {0.0f, 0.0f, 0.0f, 0.0f};
+                    for (uint32_t l = 0; l < sc->nLights; ++l) {
+                        const Light& L = lights[l];
+                        float shadow = 0.0f;
+                        if (haveShadow && (uint32_t)L.type == LIGHT_TYPE_DIRECTIONAL && L.shadowIndex == 0)
+                            shadow = compute_shadow(L, fragPos, normal, STR, shadowMap, sc->shadowSize);
+                        V4 cl = phong_lighting(L, props, normal, fragPos, viewPos, shadow);
+                        acc = {acc.x + cl.x, acc.y + cl.y, acc.z + cl.z, acc.w + cl.w};
+                    }
+                    out = {acc.x, acc.y, acc.z, props.diffuse.w};
+                }
+                if (colorF32) { colorF32[4 * p + 0] = out.x; colorF32[4 * p + 1] = out.y; colorF32[4 * p + 2] = out.z; colorF32[4 * p + 3] = out.w; }
+                if (colorSRGB8) orc_srgb8(&out.x, colorSRGB8 + 4 * p);
+            }
+    });
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,77 @@
+/*
+ * oracle.h — C interface of the CPU oracle (TEST INFRASTRUCTURE, NOT PRODUCT).
+ *
+ * This is a plain C++ restatement of the reference's raster hot path (shadow depth pass +
+ * Phong/PCF forward pass) used ONLY as the checker by tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py.  Nothing under renderengine_b200/ may call it.
+ *
+ * PARITY STATUS: "parity unpinned" at the rasteriser boundary.  The reference holds no tests,
+ * golden vectors or CPU rasteriser for this path and a Vulkan
+ * implementation cannot run on this box.  What IS pinned: the shading arithmetic
+ * (phong.glsl / shadow.glsl) and the camera / bounding-box code are checked against the
+ * reference's own sources compiled in oracle/_ref (see oracle/Makefile, tests/golden/).
+ */
+#ifndef ORACLE_H
+#define ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orc_texture {
+    const uint16_t* texels;   /* mip 0, RGBA16 UNORM, row-major */
+    uint32_t width, height;
+    uint32_t srgb;            /* decode with the sRGB EOTF after filtering (pbr.glsl:20-26,104-105) */
+    uint32_t pad;
+} orc_texture;
+
+typedef struct orc_scene {
+    const float*    verts;        /* 32-B AoS: pos@0 normal@12 uv@24 (MeshAllocator.h:14-24) */
+    uint64_t        nVerts;
+    const uint32_t* indices;      /* absolute u32 (MeshAllocator.cpp:42) */
+    uint64_t        nIndices;
+    const float*    transforms;   /* column-major mat4 per node (SceneTree.h:69) */
+    uint32_t        nNodes;
+    uint32_t        nDraws;
+    const uint32_t* draws;        /* 4 x u32: indexOffset, nbIndices, materialRaw, sceneNode (MeshAllocator.h:26-39) */
+    const uint8_t*  materials;    /* 48-B Phong records: diffuse@0 specular@16 shininess@32 diffuseTex@36 specularTex@40 */
+    uint32_t        materialStride;
+    uint32_t        nMaterials;
+    const uint8_t*  lights;       /* 112-B std430 Phong Light (phong.glsl:20-37) */
+    uint32_t        lightStride;
+    uint32_t        nLights;
+    const uint8_t*  view;         /* 160-B ViewProperties (ViewProperties.h:27-35) */
+    uint32_t        width, height;
+    uint32_t        shadowSize;   /* S; 0 = no shadow map */
+    uint32_t        maxDescriptors;
+    const float*    shadowView;   /* mat4 */
+    const float*    shadowProj;   /* mat4 (already kClip * ortho) */
+    const orc_texture* textures;
+    uint32_t        nTextures;
+    uint32_t        nThreads;     /* 0 = hardware_concurrency */
+    /* sort-first tile split: only pixels with ((y / bandH) % nRanks) == rank are owned.
+       nRanks <= 1 disables. */
+    uint32_t        rank, nRanks, bandH, pad0;
+} orc_scene;
+
+/* counters[0] = triangles dropped because they need true clipping (w<=0 or guard band),
+   counters[1] = front-facing triangles rasterised, counters[2] = fragments passing coverage */
+int orc_render_shadow(const orc_scene* s, float* shadowMap /* S*S */, uint64_t* counters /* 4 or NULL */);
+int orc_render_forward(const orc_scene* s, const float* shadowMap /* S*S or NULL */,
+                       float* depth, uint32_t* triId, float* colorF32 /* RGBA or NULL */,
+                       uint8_t* colorSRGB8 /* RGBA or NULL */, uint64_t* counters);
+
+/* unit-level entry points used to pin the restatement against oracle/_ref */
+void orc_mat4_mul(const float* a, const float* b, float* out);
+void orc_mat4_mul_vec4(const float* m, const float* v, float* out);
+void orc_normal_matrix(const float* mat4, float* out9);
+void orc_phong_lighting(const uint8_t* light112, const float* props9 /* diffuse4 specular4 shininess */,
+                        const float* normal, const float* fragPos, const float* viewPos, float shadow, float* out4);
+float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal,
+                         const float* transform16, const float* shadowMap, uint32_t S);
+void orc_srgb8(const float* rgba, uint8_t* out4);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,310 @@
+"""Procedural scenes and host-side record packing for the raster hot path.
+
+Everything here is host logic in numpy float32: icosphere grids, the reference's GPU-visible record
+layouts and the camera / shadow-transform matrices that are INPUTS to the
+hot path.  No device code and no oracle code is used here.
+
+Reference conventions followed:
+  Vertex 32-B AoS                      Source/Runtime/Renderer/MeshAllocator.h:14-24
+  MeshDrawInfo / draw sort             MeshAllocator.h:26-39, RenderScene.cpp:105-125
+  MaterialHandle bit packing           Source/Runtime/Renderer/MaterialDefines.h:88-96
+  ViewProperties (160 B)               Source/Runtime/Renderer/ViewProperties.h:27-35
+  Camera look-at / kClip*perspective   Source/Runtime/Renderer/Camera.h:93-117, glm_includes.h:18-23
+  ComputeShadowTransform               Source/Runtime/Renderer/ShadowSystem.cpp:129-204 (F8: up = cross(dir, right))
+  Phong Light (std430, 112 B)          Assets/Shaders/phong.glsl:20-37
+"""
+import numpy as np
+
+f32 = np.float32
+
+LIGHT_DIRECTIONAL, LIGHT_POINT, LIGHT_SPOT = 1, 2, 3
+INVALID_HANDLE = 0xFFFFFFFF
+MATERIAL_STRIDE = 48
+LIGHT_STRIDE = 112
+VIEW_BYTES = 160
+
+K_CLIP = np.array([[1, 0, 0, 0], [0, -1, 0, 0], [0, 0, 0.5, 0.5], [0, 0, 0, 1]], f32)   # row-major view of glm_vk::kClip
+
+
+# ---------------------------------------------------------------------------------------------
+# small float32 linear algebra in glm conventions (matrices stored column-major as flat[16])
+# ---------------------------------------------------------------------------------------------
+def _norm(v):
+    v = np.asarray(v, f32)
+    return (v * (f32(1) / np.sqrt(np.dot(v, v), dtype=f32))).astype(f32)
+
+
+def to_flat(m_rowmajor):
+    """4x4 numpy (row, col) -> column-major flat[16] as glm stores it."""
+    return np.ascontiguousarray(np.asarray(m_rowmajor, f32).T).reshape(16)
+
+
+def from_flat(flat):
+    return np.asarray(flat, f32).reshape(4, 4).T.copy()
+
+
+def look_at(eye, center, up):
+    """glm::lookAtRH (ThirdParty/glm/glm/ext/matrix_transform.inl:153-174)."""
+    eye, center, up = (np.asarray(a, f32) for a in (eye, center, up))
+    f = _norm(center - eye)
+    s = _norm(np.cross(f, up).astype(f32))
+    u = np.cross(s, f).astype(f32)
+    m = np.eye(4, dtype=f32)
+    m[0, :3] = s; m[1, :3] = u; m[2, :3] = -f
+    m[0, 3] = -np.dot(s, eye); m[1, 3] = -np.dot(u, eye); m[2, 3] = np.dot(f, eye)
+    return m
+
+
+def perspective_clip(fov_deg, aspect, near, far):
+    """kClip * glm::perspectiveRH_ZO (Camera.h:110-117; matrix_clip_space.inl:233-246)."""
+    t = np.tan(np.radians(f32(fov_deg), dtype=f32) / f32(2), dtype=f32)
+    m = np.zeros((4, 4), f32)
+    m[0, 0] = f32(1) / (f32(aspect) * t)
+    m[1, 1] = f32(1) / t
+    m[2, 2] = f32(far) / (f32(near) - f32(far))
+    m[3, 2] = -1
+    m[2, 3] = -(f32(far) * f32(near)) / (f32(far) - f32(near))
+    return (K_CLIP @ m).astype(f32)
+
+
+def ortho_clip(l, r, b, t, n, f):
+    """kClip * glm::orthoRH_ZO (ShadowSystem.cpp:192-203; matrix_clip_space.inl:42-52)."""
+    l, r, b, t, n, f = (f32(a) for a in (l, r, b, t, n, f))
+    m = np.eye(4, dtype=f32)
+    m[0, 0] = f32(2) / (r - l); m[1, 1] = f32(2) / (t - b); m[2, 2] = -f32(1) / (f - n)
+    m[0, 3] = -(r + l) / (r - l); m[1, 3] = -(t + b) / (t - b); m[2, 3] = -n / (f - n)
+    return (K_CLIP @ m).astype(f32)
+
+
+def camera_view(eye, look, up):
+    """Camera::UpdateViewMatrix (Camera.h:93-108): re-orthogonalised up, then lookAt."""
+    eye, look, up = (np.asarray(a, f32) for a in (eye, look, up))
+    d = _norm(eye - look)
+    r = _norm(np.cross(up, d).astype(f32))
+    u = np.cross(d, r).astype(f32)
+    return look_at(eye, look, u)
+
+
+def bbox_corners(mn, mx):
+    return np.array([[x, y, z] for x in (mn[0], mx[0]) for y in (mn[1], mx[1]) for z in (mn[2], mx[2])], f32)
+
+
+def bbox_transform(mn, mx, m):
+    """BoundingBox::Transform (BoundingBox.h:47-60): 8 corners, divide by w, min/max."""
+    c = bbox_corners(mn, mx)
+    p = (np.c_[c, np.ones(8, f32)] @ m.T).astype(f32)
+    p = p[:, :3] / p[:, 3:4]
+    return p.min(0).astype(f32), p.max(0).astype(f32)
+
+
+def frustum_corners(view, proj):
+    """Camera::ComputeFrustrumCorners (Camera.cpp:3-25)."""
+    t = (np.linalg.inv(view.astype(np.float64)) @ np.linalg.inv(proj.astype(np.float64))).astype(f32)
+    pts = np.array([[x, y, z, 1] for x in (-1, 1) for y in (-1, 1) for z in (-1, 1)], f32)
+    w = (pts @ t.T).astype(f32)
+    return (w[:, :3] / w[:, 3:4]).astype(f32)
+
+
+def light_view_matrix(direction):
+    """ComputeDirectionalLightViewMatrix (ShadowSystem.cpp:129-147) with up = cross(dir, right) (F8)."""
+    d = np.asarray(direction, f32)
+    right = np.array([0, 0, 1], f32)
+    if abs(float(np.dot(d, right))) > 0.9999:
+        right = np.array([1, 0, 0], f32)
+    up = np.cross(d, right).astype(f32)
+    return look_at(np.zeros(3, f32), d, up)
+
+
+def compute_shadow_transform(light_dir, cam_view, cam_proj, scene_box, boxes, transforms):
+    """ComputeShadowTransform (ShadowSystem.cpp:148-204). Returns (view, proj) row/col numpy 4x4."""
+    cam_pts = frustum_corners(cam_view, cam_proj)
+    cam_min, cam_max = cam_pts.min(0), cam_pts.max(0)
+    sview = light_view_matrix(light_dir)
+    cv_min, cv_max = bbox_transform(cam_min, cam_max, sview)
+    sv_min, sv_max = bbox_transform(scene_box[0], scene_box[1], sview)
+    cv_max[2] = sv_max[2]
+    sinv = np.linalg.inv(sview.astype(np.float64)).astype(f32)
+    cw_min, cw_max = bbox_transform(cv_min, cv_max, sinv)
+    lb_min = np.full(3, np.finfo(f32).max, f32); lb_max = -lb_min
+    for (bmn, bmx), t in zip(boxes, transforms):
+        wmn, wmx = bbox_transform(bmn, bmx, from_flat(t))
+        if np.all(wmn <= cw_max) and np.all(wmx >= cw_min):
+            lb_min = np.minimum(lb_min, wmn); lb_max = np.maximum(lb_max, wmx)
+    lv_min, lv_max = bbox_transform(lb_min, lb_max, sview)
+    sproj = ortho_clip(lv_min[0], lv_max[0], lv_min[1], lv_max[1], lv_min[2], lv_max[2])
+    return sview, sproj
+
+
+# ---------------------------------------------------------------------------------------------
+# record packing
+# ---------------------------------------------------------------------------------------------
+def material_handle(index, domain=0, model=1):
+    """MaterialHandle raw bits: domain[0:2] model[2:4] index[4:32]; (Surface, Lit, 5) = 0x54."""
+    return (domain & 3) | ((model & 3) << 2) | (index << 4)
+
+
+def pack_view(view, proj, pos, exposure=1.0):
+    rec = np.zeros(VIEW_BYTES, np.uint8)
+    f = rec.view(f32)
+    f[0:16] = to_flat(view); f[16:32] = to_flat(proj); f[32:35] = np.asarray(pos, f32); f[35] = exposure
+    return rec
+
+
+def pack_light(ltype, position, direction, ambient, diffuse, specular, inner=1.0, outer=0.0, shadow_index=0):
+    rec = np.zeros(LIGHT_STRIDE, np.uint8)
+    f = rec.view(f32)
+    rec.view(np.int32)[0] = ltype
+    f[4:7] = position; f[8:11] = direction
+    f[12:16] = ambient; f[16:20] = diffuse; f[20:24] = specular
+    f[24] = inner; f[25] = outer
+    rec.view(np.uint32)[26] = shadow_index
+    return rec
+
+
+def pack_material(diffuse, specular, shininess, diffuse_tex=INVALID_HANDLE, specular_tex=INVALID_HANDLE):
+    """48-B Phong record (builder-defined from phong.glsl:2-12)."""
+    rec = np.zeros(MATERIAL_STRIDE, np.uint8)
+    f = rec.view(f32); u = rec.view(np.uint32)
+    f[0:4] = diffuse; f[4:8] = specular; f[8] = shininess
+    u[9] = diffuse_tex; u[10] = specular_tex
+    return rec
+
+
+# ---------------------------------------------------------------------------------------------
+# geometry
+# ---------------------------------------------------------------------------------------------
+_ICO_CACHE = {}
+
+
+def icosphere(level):
+    """Unit icosphere: 10*4^L + 2 shared vertices, 20*4^L CCW-outward triangles."""
+    if level in _ICO_CACHE:
+        return _ICO_CACHE[level]
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    v = np.array([[-1, t, 0], [1, t, 0], [-1, -t, 0], [1, -t, 0], [0, -1, t], [0, 1, t], [0, -1, -t], [0, 1, -t],
+                  [t, 0, -1], [t, 0, 1], [-t, 0, -1], [-t, 0, 1]], np.float64)
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    tri = np.array([[0, 11, 5], [0, 5, 1], [0, 1, 7], [0, 7, 10], [0, 10, 11], [1, 5, 9], [5, 11, 4], [11, 10, 2], [10, 7, 6],
+                    [7, 1, 8], [3, 9, 4], [3, 4, 2], [3, 2, 6], [3, 6, 8], [3, 8, 9], [4, 9, 5], [2, 4, 11], [6, 2, 10],
+                    [8, 6, 7], [9, 8, 1]], np.int64)
+    for _ in range(level):
+        e = np.concatenate([tri[:, [0, 1]], tri[:, [1, 2]], tri[:, [2, 0]]])
+        es = np.sort(e, axis=1)
+        key = es[:, 0] * (len(v) + 1) + es[:, 1]
+        uniq, inv = np.unique(key, return_inverse=True)
+        first = np.zeros(len(uniq), np.int64); first[inv[::-1]] = np.arange(len(key))[::-1]
+        mid = v[es[first, 0]] + v[es[first, 1]]
+        mid /= np.linalg.norm(mid, axis=1, keepdims=True)
+        base = len(v)
+        v = np.concatenate([v, mid])
+        n = len(tri)
+        m01, m12, m20 = base + inv[:n], base + inv[n:2 * n], base + inv[2 * n:]
+        a, b, c = tri[:, 0], tri[:, 1], tri[:, 2]
+        tri = np.concatenate([np.stack([a, m01, m20], 1), np.stack([b, m12, m01], 1), np.stack([c, m20, m12], 1),
+                              np.stack([m01, m12, m20], 1)])
+    pos = v.astype(f32)
+    uv = np.stack([np.arctan2(v[:, 2], v[:, 0]) / (2 * np.pi) + 0.5, np.arcsin(np.clip(v[:, 1], -1, 1)) / np.pi + 0.5], 1).astype(f32)
+    verts = np.concatenate([pos, pos, uv], axis=1).astype(f32)   # normal = position on the unit sphere
+    _ICO_CACHE[level] = (verts, tri.astype(np.uint32))
+    return _ICO_CACHE[level]
+
+
+CONFIGS = {
+    # name: grid (nx, nz), level, target, shadow size, materials   
+    "C1": dict(grid=(10, 5), level=3, width=1280, height=720, shadow_size=0, n_materials=4),
+    "C2": dict(grid=(7, 7), level=5, width=1920, height=1080, shadow_size=2048, n_materials=8),
+    "C3": dict(grid=(16, 8), level=6, width=3840, height=2160, shadow_size=2048, n_materials=1024),
+    "C4": dict(grid=(16, 8), level=6, width=7680, height=4320, shadow_size=2048, n_materials=1024),
+    "C5": dict(grid=(14, 7), level=5, width=1920, height=1080, shadow_size=2048, n_materials=8),
+    "tiny": dict(grid=(3, 2), level=2, width=160, height=96, shadow_size=128, n_materials=3),
+    "small": dict(grid=(4, 3), level=3, width=640, height=360, shadow_size=512, n_materials=5),
+}
+
+
+def camera_for(extent_x, extent_z, width, height, azimuth=0.0, fov=45.0, near=0.01, far=100.0):
+    """Eye on the (1,1,1) diagonal (rotated by `azimuth` rad about +Y) at a distance framing the grid."""
+    radius = float(np.hypot(extent_x, extent_z))
+    aspect = width / float(height)
+    half_v = np.radians(fov) / 2
+    half_h = np.arctan(np.tan(half_v) * aspect)
+    dist = min(0.85 * radius / np.sin(min(half_v, half_h)), far - radius - 1.0)
+    d = np.array([1.0, 1.0, 1.0]) / np.sqrt(3.0)
+    ca, sa = np.cos(azimuth), np.sin(azimuth)
+    d = np.array([ca * d[0] + sa * d[2], d[1], -sa * d[0] + ca * d[2]])
+    eye = (d * dist).astype(f32)
+    view = camera_view(eye, np.zeros(3, f32), np.array([0, 1, 0], f32))
+    proj = perspective_clip(fov, f32(width) / f32(height), near, far)
+    return eye, view, proj
+
+
+def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
+    """Build a scene dict for a named config. All arrays are host numpy."""
+    cfg = dict(CONFIGS[config]) if isinstance(config, str) else dict(config)
+    cfg.update(overrides)
+    nx, nz = cfg["grid"]; level = cfg["level"]
+    W, H, S, M = cfg["width"], cfg["height"], cfg["shadow_size"], cfg["n_materials"]
+    rng = np.random.default_rng(seed)
+    sv, st = icosphere(level)
+    n_s = nx * nz
+    nv, nt = len(sv), len(st)
+    spacing = 2.5
+    verts = np.tile(sv, (n_s, 1))
+    indices = (st.reshape(1, -1).astype(np.uint64) + (np.arange(n_s, dtype=np.uint64) * nv).reshape(-1, 1)).astype(np.uint32)
+    transforms = np.tile(np.eye(4, dtype=f32).reshape(1, 16), (n_s, 1))
+    gx = (np.arange(nx) - (nx - 1) / 2.0) * spacing
+    gz = (np.arange(nz) - (nz - 1) / 2.0) * spacing
+    cx, cz = np.meshgrid(gx, gz, indexing="ij")
+    transforms[:, 12] = cx.reshape(-1); transforms[:, 14] = cz.reshape(-1)
+    boxes = [(np.full(3, -1, f32), np.full(3, 1, f32))] * n_s
+    draws = [(k * nt * 3, nt * 3, material_handle(k % M), k) for k in range(n_s)]
+    ex, ez = abs(gx[0]) + 1.0, abs(gz[0]) + 1.0
+    n_mat = M
+    if ground:
+        gy = f32(-1.05)
+        hx, hz = f32(ex + 1.5), f32(ez + 1.5)
+        q = np.array([[-hx, gy, -hz, 0, 1, 0, 0, 0], [-hx, gy, hz, 0, 1, 0, 0, 1], [hx, gy, hz, 0, 1, 0, 1, 1], [hx, gy, -hz, 0, 1, 0, 1, 0]], f32)
+        base = len(verts)
+        verts = np.concatenate([verts, q])
+        qi = np.array([0, 1, 2, 0, 2, 3], np.uint32) + np.uint32(base)
+        draws.append((indices.size, 6, material_handle(M), n_s))
+        indices = np.concatenate([indices.reshape(-1), qi])
+        transforms = np.concatenate([transforms, np.eye(4, dtype=f32).reshape(1, 16)])
+        boxes = boxes + [(np.array([-hx, gy, -hz], f32), np.array([hx, gy, hz], f32))]
+        n_mat = M + 1
+    indices = indices.reshape(-1)
+    # RenderScene::SortOpaqueMeshes: by (materialHandle raw, sceneNodeID)
+    draws = np.array(sorted(draws, key=lambda d: (d[2], d[3])), np.uint32)
+    shin = np.array([8, 16, 32, 64], f32)
+    materials = np.stack([pack_material(np.r_[rng.uniform(0.2, 1.0, 3), 1.0].astype(f32), np.array([0.5, 0.5, 0.5, 1], f32),
+                                        shin[k % 4]) for k in range(n_mat)])
+    if ground:
+        materials[M] = pack_material(np.array([0.8, 0.8, 0.8, 1], f32), np.array([0.2, 0.2, 0.2, 1], f32), 16.0)
+    ldir = _norm([-0.3, -1.0, -0.2])
+    lights = np.stack([pack_light(LIGHT_DIRECTIONAL, (-ldir * f32(50)).astype(f32), ldir, [0.1] * 4, [1.0] * 4, [1.0] * 4)])
+    eye, view, proj = camera_for(ex, ez, W, H, azimuth)
+    scene = dict(config=config if isinstance(config, str) else "custom", verts=verts, indices=indices, transforms=transforms,
+                 draws=draws, materials=materials, lights=lights, view=pack_view(view, proj, eye), width=W, height=H,
+                 shadow_size=S, max_descriptors=8192, n_triangles=int(indices.size // 3), n_vertices=int(len(verts)),
+                 eye=eye, view_mat=view, proj_mat=proj, boxes=boxes, extent=(ex, ez), textures=[])
+    if S:
+        all_min = np.array([-ex - 1.5, -1.05, -ez - 1.5], f32) if ground else np.array([-ex, -1, -ez], f32)
+        all_max = np.array([ex + 1.5, 1, ez + 1.5], f32) if ground else np.array([ex, 1, ez], f32)
+        sview, sproj = compute_shadow_transform(ldir, view, proj, (all_min, all_max), boxes, transforms)
+        scene["shadow_view"] = to_flat(sview); scene["shadow_proj"] = to_flat(sproj)
+    return scene
+
+
+def view_for_azimuth(scene, azimuth):
+    """A new 160-B ViewProperties record orbiting the same scene (view-parallel batches, C5)."""
+    ex, ez = scene["extent"]
+    eye, view, proj = camera_for(ex, ez, scene["width"], scene["height"], azimuth)
+    return pack_view(view, proj, eye)
+
+
+def algorithmic_bytes(scene, hdr=False):
+    """Compulsory HBM traffic per frame: returns (B_shadow, B_forward)."""
+    V, T = scene["n_vertices"], scene["n_triangles"]
+    W, H, S = scene["width"], scene["height"], scene["shadow_size"]
+    b_shadow = 12 * V + 12 * T + 4 * S * S if S else 0
+    b_forward = 32 * V + 12 * T + (min(36 * W * H, 4 * S * S) if S else 0) + 12 * W * H + (16 * W * H if hdr else 0)
+    return b_shadow, b_forward
