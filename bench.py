@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the raster hot path (BASELINE.json metric: Mtri/s and frames/s,
+Phong + 3x3-PCF shadow, 1080p; achieved HBM GB/s as a fraction of the measured B200 peak).
+
+A "step" is one full frame of config C2 (1,003,522 triangles, 1920x1080, 2048^2 shadow
+map): shadow depth pass + forward pass, every step.  N > 1 (torchrun): view-parallel batch — rank 0 renders
+the shadow map once per step and NCCL-broadcasts it, every rank renders its own camera view (weak
+scaling); `--mode tiles` runs the sort-first row-band split of one frame instead (strong scaling).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config C2] [--mode views|tiles]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from renderengine_b200 import scene as sc  # noqa: E402
+
+METRIC, UNIT = "Mtri/s", "Mtri/s"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx = float(f[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_frames(scene, n_frames, warm=1):
+    """Times the CPU oracle (the port of the reference path) on all host cores: full frames of the same workload."""
+    from oracle import orc
+    o = orc.Oracle(scene)
+    cores = os.cpu_count() or 1
+    times = []
+    for i in range(warm + n_frames):
+        t0 = time.perf_counter()
+        sm = o.render_shadow() if scene["shadow_size"] else None
+        o.render_forward(sm)
+        if i >= warm:
+            times.append(time.perf_counter() - t0)
+    return times, cores
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    scene = sc.make_scene(args.config)
+    budget_s = 150.0
+    probe, cores = cpu_reference_frames(scene, 1, warm=1)
+    steps = max(1, min(args.steps, int(budget_s / max(probe[0], 1e-3))))
+    warm = min(args.warmup, 2)
+    times, cores = cpu_reference_frames(scene, steps, warm=warm)
+    ms = 1e3 * float(np.mean(times))
+    val = scene["n_triangles"] / (ms * 1e3)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "frames_per_s": 1e3 / ms,
+        "config": {"workload": f"{args.config}: {scene['n_triangles']} tris, {scene['width']}x{scene['height']}, shadow {scene['shadow_size']}^2 3x3 PCF, full frame (shadow + forward) per step"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{steps} full frames of the same workload on the CPU oracle (reference Vulkan/lavapipe path unavailable on this box)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+class _DevArray:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"data": (ptr, False), "shape": shape, "typestr": typestr, "version": 2}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2")
+    ap.add_argument("--mode", default="views", choices=["views", "tiles"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from renderengine_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    scene = sc.make_scene(args.config)
+    T, W, H, S = scene["n_triangles"], scene["width"], scene["height"], scene["shadow_size"]
+    tiles = args.mode == "tiles" and world > 1
+    st = torch.cuda.Stream()
+    outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32
+    ctx = capi.Context(W, H, device=local_rank, stream=st.cuda_stream, outputs=outputs,
+                       rank=rank if tiles else 0, n_ranks=world if tiles else 1, band_h=64)
+    ctx.upload_scene(scene)
+    if not tiles and world > 1:
+        ctx.set_view(sc.view_for_azimuth(scene, 2 * np.pi * rank / world))   # one camera view per rank
+    draws = scene["draws"]
+    shadow_t = None
+    if S and world > 1:
+        ptr, _ = ctx.output_ptr(capi.REB_SHADOW_F32)
+        shadow_t = torch.as_tensor(_DevArray(ptr, (S, S), "<f4"), device=f"cuda:{local_rank}")
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def step():
+        if S:
+            if world == 1:
+                ctx.render_shadow(draws)
+            else:
+                if rank == 0:
+                    ctx.render_shadow(draws)
+                dist.broadcast(shadow_t, src=0)          # NCCL over NVLink; ordered on the current stream
+                if rank != 0:
+                    ctx.shadow_mark_valid()
+        ctx.render_forward(draws)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(st):
+        for _ in range(args.warmup):
+            flush.add_(1); step()
+        ctx.sync()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        l0 = ctx.launch_count()
+        for a, b in ev:
+            flush.add_(1)                                 # L2 flush between timed iterations (outside the event pair)
+            a.record(st); step(); b.record(st)
+        ctx.sync()
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        launches = ctx.launch_count() - l0
+        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+        tt = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item()) / args.steps
+        frames_per_step = 1 if tiles else world
+        value = frames_per_step * T / (ms * 1e3)
+
+        # ---- per-kernel timing + roofline of the dominant kernel (separate, instrumented frames) ----------
+        ctx.set_profiling(True)
+        acc = [dict(), dict()]
+        n_prof = 20
+        for _ in range(n_prof):
+            flush.add_(1)
+            if S and (world == 1 or rank == 0):
+                ctx.render_shadow(draws)
+            ctx.render_forward(draws)
+            ctx.sync()
+            for k in (0, 1):
+                if k == 0 and not (S and (world == 1 or rank == 0)):
+                    continue
+                for name, v in ctx.kernel_times_ms(k).items():
+                    acc[k][name] = acc[k].get(name, 0.0) + v / n_prof
+        ctx.set_profiling(False)
+        counters = ctx.counters()
+
+        # ---- end to end through the C ABI with host buffers (wall clock, includes D2H of the frame) -------
+        pinned = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+        view_host = np.array(scene["view"] if world == 1 or tiles else sc.view_for_azimuth(scene, 2 * np.pi * rank / world))
+        n_e2e = max(10, min(args.steps, 50))
+        for _ in range(3):
+            step(); ctx.readback_into(capi.REB_COLOR_SRGB8, pinned.data_ptr())
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            ctx.set_view(view_host)
+            if S:
+                ctx.shadow_set_transform(scene["shadow_view"], scene["shadow_proj"])
+            step()
+            ctx.readback_into(capi.REB_COLOR_SRGB8, pinned.data_ptr())
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / n_e2e
+        te = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_ms = float(te.item())
+    e2e_val = frames_per_step * T / (e2e_ms * 1e3)
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        b_shadow, b_forward = sc.algorithmic_bytes(scene)
+        V = scene["n_vertices"]
+        # algorithmic bytes owned by each kernel; their sum is B_shadow + B_forward of SURVEY.md §8d
+        alg = {
+            (0, "clear"): 0, (0, "setup_raster"): 12 * V + 12 * T, (0, "tile_stage"): 4 * S * S,
+            (1, "setup_raster"): 12 * V + 12 * T,
+            (1, "tile_stage"): 20 * V + (min(36 * W * H, 4 * S * S) if S else 0) + 12 * W * H,
+        }
+        kt = {f"{'shadow' if k == 0 else 'forward'}.{n}": v for k in (0, 1) for n, v in acc[k].items()}
+        dom = max(((k, n) for k in (0, 1) for n in acc[k]), key=lambda kn: acc[kn[0]][kn[1]])
+        dom_ms = acc[dom[0]][dom[1]]
+        dom_bytes = alg.get(dom, 0)
+        achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+        frame_bytes = (b_shadow + b_forward) * frames_per_step
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
+            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step",
+                       "parallelism": ("sort-first row bands x%d" % world) if tiles else ("view-parallel x%d, shadow map NCCL-broadcast" % world if world > 1 else "1 GPU"),
+                       "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
+            "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
+                          "frac_of_peak": frame_bytes / (ms * 1e-3) / 1e9 / peak / world, "peak_gbs": peak, "peak_source": peak_src},
+            "roofline": {"bound": "hbm", "kernel": f"{'shadow' if dom[0] == 0 else 'forward'}.{dom[1]}", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "algorithmic_bytes_per_launch": dom_bytes,
+                         "kernel_ms": dom_ms, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs, burst copy)"},
+            "kernel_ms": kt,
+            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 160 + 128 + 2 * 16 * len(draws),
+                    "d2h_bytes_per_step": W * H * 4, "note": "wall clock through reb_set_view/reb_render_*/reb_readback with host buffers; geometry is static and resident as in the reference frame loop"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "counters": {"needs_clip": int(counters[0]), "binned_triangles": int(counters[1]), "tile_list_entries": int(counters[2]), "regrows": int(counters[3])},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            times, cores = cpu_reference_frames(scene, 5, warm=1)
+            cms = 1e3 * float(np.mean(times))
+            line["cpu_baseline"] = {"value": T / (cms * 1e3), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_frame": cms,
+                                    "sample": "5 full frames (shadow + forward) of the same workload on the CPU oracle, all host cores"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

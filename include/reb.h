@@ -1,0 +1,122 @@
+/*
+ * reb.h — C ABI of the B200-native raster hot path (shadow depth pass + Phong/PCF forward pass).
+ *
+ * The reference (hugbed/RenderEngine) has no plugin / FFI layer: the boundary is a set of C++
+ * member calls inside one process.  Each entry point below replaces the reference
+ * call cited beside it; the C++ facade in renderengine_b200/host keeps the reference's class and
+ * method names and forwards here.  All functions return 0 on success or a negative reb_status;
+ * reb_last_error() gives the text (the reference throws std::runtime_error instead —
+ * Source/VkRHI/RHI/RenderLoop.cpp:144, Source/Runtime/Renderer/TextureCache.cpp:68-70).
+ *
+ * Threading: a context is NOT thread-safe (reference: single-threaded frame loop,
+ * RenderLoop.cpp:52-67; Device.h:12-13).  One context per GPU.  All work is asynchronous on the
+ * context's CUDA stream; host input buffers are consumed (copied) before the call returns.
+ * There is no CPU fallback: without a CUDA device reb_create fails.
+ */
+#ifndef REB_H
+#define REB_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define REB_ABI_VERSION 1
+
+typedef struct reb_ctx reb_ctx;
+
+typedef enum reb_status {
+    REB_OK = 0,
+    REB_E_INVALID = -1,     /* bad argument / call order (std::invalid_argument in the reference) */
+    REB_E_CUDA = -2,        /* CUDA runtime error */
+    REB_E_NO_DEVICE = -3,   /* no usable sm_100 device */
+    REB_E_OVERFLOW = -4,    /* an internal queue overflowed and could not be grown */
+    REB_E_UNSUPPORTED = -5
+} reb_status;
+
+/* which buffers the forward pass writes (reb_params.outputs) */
+#define REB_OUT_COLOR_SRGB8 1u   /* R8G8B8A8_SRGB target, Source/VkRHI/RHI/Swapchain.cpp:10-21 */
+#define REB_OUT_COLOR_F32   2u   /* linear RGBA f32 before encode (HDR parity buffer) */
+#define REB_OUT_DEPTH_F32   4u
+#define REB_OUT_TRIID_U32   8u
+
+typedef enum reb_output_kind {
+    REB_COLOR_SRGB8 = 0, REB_COLOR_F32 = 1, REB_DEPTH_F32 = 2, REB_TRIID_U32 = 3, REB_SHADOW_F32 = 4
+} reb_output_kind;
+
+/* Renderer ctor (Source/Runtime/Renderer/Renderer.cpp:38-51): runtime parameters that the
+ * reference hard-codes (image extent Swapchain.cpp:200-237, Bindless.h:76 descriptor limit). */
+typedef struct reb_params {
+    uint32_t struct_size;      /* sizeof(reb_params) */
+    int32_t  device;           /* CUDA ordinal */
+    uint32_t width, height;    /* forward target extent */
+    uint32_t max_descriptors;  /* 0 -> 8192; texture handle valid iff handle < max_descriptors (bindless.glsl:14) */
+    uint32_t outputs;          /* REB_OUT_* mask; 0 -> all */
+    uint32_t rank, n_ranks;    /* sort-first split: this context owns row bands b with b % n_ranks == rank */
+    uint32_t band_h;           /* band height in pixels (multiple of 8); 0 -> 64 */
+    uint32_t reserved;
+    void*    stream;           /* cudaStream_t to run on, or NULL for a private stream */
+} reb_params;
+
+/* MeshDrawInfo (Source/Runtime/Renderer/MeshAllocator.h:26-39): one vkCmdDrawIndexed of the reference's
+ * draw loops (MaterialSystem.cpp:94-100, ShadowSystem.cpp:358-370). materialRaw = MaterialHandle bits. */
+typedef struct reb_draw { uint32_t indexOffset, nbIndices, materialRaw, sceneNode; } reb_draw;
+
+/* TextureCache::LoadTexture (TextureCache.cpp:44-106): R16G16B16A16_UNORM, full mip chain, repeat, trilinear */
+typedef struct reb_texture_desc { uint32_t width, height, format /* 0 = RGBA16_UNORM */, srgb; } reb_texture_desc;
+
+int         reb_abi_version(void);
+/* Renderer::Renderer / ~Renderer — Renderer.cpp:38-51 */
+int         reb_create(const reb_params* params, reb_ctx** out);
+int         reb_destroy(reb_ctx* ctx);
+const char* reb_last_error(reb_ctx* ctx /* may be NULL: error of the last failed reb_create */);
+
+/* MeshAllocator::AddVertex/AddIndex/UploadToGPU — MeshAllocator.h:45-61, MeshAllocator.cpp:5-35.
+ * verts: 32-B AoS (pos@0 normal@12 uv@24); idx: absolute u32. Split into SoA streams on the device. */
+int reb_upload_geometry(reb_ctx* ctx, const void* verts, uint64_t nVerts, const uint32_t* idx, uint64_t nIdx);
+/* SceneTree::CreateNode/UploadToGPU — SceneTree.h:32, SceneTree.cpp:6-31 (column-major mat4 per node) */
+int reb_upload_transforms(reb_ctx* ctx, const float* mat4ColMajor, uint32_t nNodes);
+/* MaterialSystem::CreateMaterialInstance/UploadToGPU — MaterialSystem.cpp:49-59,68-86 (48-B Phong records) */
+int reb_upload_materials(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n);
+/* LightSystem::AddLight/UploadToGPU — LightSystem.h:47-55, LightSystem.cpp:17-34 (112-B std430 Phong Light) */
+int reb_upload_lights(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n);
+/* BindlessDescriptors::StoreTexture — Bindless.cpp:221-241: handle = running index */
+int reb_register_texture(reb_ctx* ctx, const reb_texture_desc* desc, const void* texelsMip0, uint32_t* outHandle);
+/* ShadowSystem::CreateShadowMap — ShadowSystem.cpp:229-238 */
+int reb_shadow_create(reb_ctx* ctx, uint32_t size, uint32_t* outShadowId);
+/* ShadowSystem::Update result (ShadowSystem.cpp:277-317): light view and proj (= kClip * ortho) */
+int reb_shadow_set_transform(reb_ctx* ctx, uint32_t shadowId, const float* view16, const float* proj16);
+/* CameraViewSystem::Update — CameraViewSystem.cpp:61-72: the 160-B ViewProperties block */
+int reb_set_view(reb_ctx* ctx, const void* viewProperties160);
+
+/* ShadowSystem::Render(drawCommands) — ShadowSystem.cpp:319-376 */
+int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, uint32_t n);
+/* RenderScene::RenderBasePass -> MaterialSystem::Draw — RenderScene.cpp:210-242, MaterialSystem.cpp:88-101 */
+int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n);
+
+/* swapchain resolve / present (Swapchain.cpp:200-237, RenderLoop.cpp:124-132) become headless buffers */
+int reb_get_output(reb_ctx* ctx, reb_output_kind kind, void** devPtr, uint64_t* bytes);
+int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host);
+int reb_sync(reb_ctx* ctx);
+
+/* multi-GPU helpers */
+int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH);
+/* marks the shadow map as valid after its storage (reb_get_output REB_SHADOW_F32) was filled externally,
+ * e.g. by an NCCL broadcast from the rank that rendered it */
+int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);
+
+/* diagnostics: counters[0] triangles needing true clipping (dropped; outside the bit-exact domain),
+ * [1] triangles sent to the binned tile path in the last pass, [2] tile-list entries, [3] queue regrow count */
+int reb_get_counters(reb_ctx* ctx, uint64_t* counters4);
+/* number of kernels this library has launched on the context since creation */
+int reb_get_launch_count(reb_ctx* ctx, uint64_t* out);
+
+/* per-kernel device timing of the last enqueued pass (0 = shadow, 1 = forward), CUDA events on the
+ * context stream: ms6 = { clear, setup+small raster, bin count, tile scan, bin scatter, tile stage } */
+int reb_set_profiling(reb_ctx* ctx, int on);
+int reb_get_kernel_times(reb_ctx* ctx, int pass, float* ms6);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REB_H */

@@ -1,0 +1,215 @@
+"""ctypes mirror of include/reb.h.  Loads the in-tree libreb.so and fails loudly if it is missing —
+there is no Python or CPU fallback for any render call."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libreb.so")
+
+REB_OUT_COLOR_SRGB8, REB_OUT_COLOR_F32, REB_OUT_DEPTH_F32, REB_OUT_TRIID_U32 = 1, 2, 4, 8
+REB_COLOR_SRGB8, REB_COLOR_F32, REB_DEPTH_F32, REB_TRIID_U32, REB_SHADOW_F32 = 0, 1, 2, 3, 4
+
+SYMBOLS = [
+    "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
+    "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync",
+    "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
+    "reb_get_kernel_times",
+]
+
+
+class RebParams(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("width", C.c_uint32), ("height", C.c_uint32),
+                ("max_descriptors", C.c_uint32), ("outputs", C.c_uint32), ("rank", C.c_uint32), ("n_ranks", C.c_uint32),
+                ("band_h", C.c_uint32), ("reserved", C.c_uint32), ("stream", C.c_void_p)]
+
+
+class RebTextureDesc(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("format", C.c_uint32), ("srgb", C.c_uint32)]
+
+
+class RebError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """dlopen libreb.so (building nothing here: run `python -m renderengine_b200.build` or __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RebError(f"{LIB_PATH} is missing: build it with `python -m renderengine_b200.build` (no CPU fallback exists)")
+    lib = C.CDLL(LIB_PATH)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    lib.reb_abi_version.restype = C.c_int
+    lib.reb_last_error.restype = C.c_char_p
+    lib.reb_last_error.argtypes = [vp]
+    lib.reb_create.argtypes = [C.POINTER(RebParams), C.POINTER(vp)]
+    lib.reb_destroy.argtypes = [vp]
+    lib.reb_upload_geometry.argtypes = [vp, vp, u64, vp, u64]
+    lib.reb_upload_transforms.argtypes = [vp, vp, u32]
+    lib.reb_upload_materials.argtypes = [vp, vp, u32, u32]
+    lib.reb_upload_lights.argtypes = [vp, vp, u32, u32]
+    lib.reb_register_texture.argtypes = [vp, C.POINTER(RebTextureDesc), vp, C.POINTER(u32)]
+    lib.reb_shadow_create.argtypes = [vp, u32, C.POINTER(u32)]
+    lib.reb_shadow_set_transform.argtypes = [vp, u32, vp, vp]
+    lib.reb_set_view.argtypes = [vp, vp]
+    lib.reb_render_shadow.argtypes = [vp, u32, vp, u32]
+    lib.reb_render_forward.argtypes = [vp, vp, u32]
+    lib.reb_get_output.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(u64)]
+    lib.reb_readback.argtypes = [vp, C.c_int, vp]
+    lib.reb_sync.argtypes = [vp]
+    lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
+    lib.reb_shadow_mark_valid.argtypes = [vp, u32]
+    lib.reb_get_counters.argtypes = [vp, vp]
+    lib.reb_get_launch_count.argtypes = [vp, C.POINTER(u64)]
+    lib.reb_set_profiling.argtypes = [vp, C.c_int]
+    lib.reb_get_kernel_times.argtypes = [vp, C.c_int, vp]
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+_KIND_INFO = {REB_COLOR_SRGB8: (np.uint8, 4), REB_COLOR_F32: (np.float32, 4), REB_DEPTH_F32: (np.float32, 1),
+              REB_TRIID_U32: (np.uint32, 1)}
+
+
+class Context:
+    """One raster context per GPU (the reference's Renderer + RenderScene systems, headless)."""
+
+    def __init__(self, width, height, device=0, outputs=0, rank=0, n_ranks=1, band_h=64, stream=None, max_descriptors=0):
+        self.lib = load()
+        self.width, self.height = int(width), int(height)
+        p = RebParams(C.sizeof(RebParams), device, width, height, max_descriptors, outputs, rank, n_ranks, band_h, 0, stream)
+        h = C.c_void_p()
+        rc = self.lib.reb_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise RebError(f"reb_create failed ({rc}): {self.lib.reb_last_error(None).decode()}")
+        self.h = h
+        self.shadow_size = 0
+        self.shadow_id = None
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RebError(f"libreb error {rc}: {self.lib.reb_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.reb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- uploads (RenderScene::UploadToGPU, RenderScene.cpp:80-92) ----------------------------
+    def upload_geometry(self, verts, indices):
+        v = np.ascontiguousarray(verts, np.float32); i = np.ascontiguousarray(indices, np.uint32)
+        assert v.ndim == 2 and v.shape[1] == 8
+        self._ck(self.lib.reb_upload_geometry(self.h, _ptr(v), v.shape[0], _ptr(i), i.size))
+
+    def upload_transforms(self, transforms):
+        t = np.ascontiguousarray(transforms, np.float32).reshape(-1, 16)
+        self._ck(self.lib.reb_upload_transforms(self.h, _ptr(t), t.shape[0]))
+
+    def upload_materials(self, records):
+        m = np.ascontiguousarray(records, np.uint8)
+        self._ck(self.lib.reb_upload_materials(self.h, _ptr(m), m.shape[1], m.shape[0]))
+
+    def upload_lights(self, records):
+        l = np.ascontiguousarray(records, np.uint8)
+        self._ck(self.lib.reb_upload_lights(self.h, _ptr(l), l.shape[1], l.shape[0]))
+
+    def shadow_create(self, size):
+        sid = C.c_uint32()
+        self._ck(self.lib.reb_shadow_create(self.h, size, C.byref(sid)))
+        self.shadow_size, self.shadow_id = size, sid.value
+        return sid.value
+
+    def shadow_set_transform(self, view16, proj16):
+        v = np.ascontiguousarray(view16, np.float32); p = np.ascontiguousarray(proj16, np.float32)
+        self._ck(self.lib.reb_shadow_set_transform(self.h, self.shadow_id, _ptr(v), _ptr(p)))
+
+    def set_view(self, view160):
+        v = np.ascontiguousarray(view160, np.uint8)
+        assert v.size == 160
+        self._ck(self.lib.reb_set_view(self.h, _ptr(v)))
+
+    def upload_scene(self, scene):
+        self.upload_geometry(scene["verts"], scene["indices"])
+        self.upload_transforms(scene["transforms"])
+        self.upload_materials(scene["materials"])
+        self.upload_lights(scene["lights"])
+        if scene.get("shadow_size", 0):
+            self.shadow_create(scene["shadow_size"])
+            self.shadow_set_transform(scene["shadow_view"], scene["shadow_proj"])
+        self.set_view(scene["view"])
+
+    # --- the hot path ---------------------------------------------------------------------------
+    def render_shadow(self, draws):
+        d = np.ascontiguousarray(draws, np.uint32).reshape(-1, 4)
+        self._ck(self.lib.reb_render_shadow(self.h, self.shadow_id, _ptr(d), d.shape[0]))
+
+    def render_forward(self, draws):
+        d = np.ascontiguousarray(draws, np.uint32).reshape(-1, 4)
+        self._ck(self.lib.reb_render_forward(self.h, _ptr(d), d.shape[0]))
+
+    def sync(self):
+        self._ck(self.lib.reb_sync(self.h))
+
+    # --- outputs ----------------------------------------------------------------------------------
+    def output_ptr(self, kind):
+        p = C.c_void_p(); b = C.c_uint64()
+        self._ck(self.lib.reb_get_output(self.h, kind, C.byref(p), C.byref(b)))
+        return p.value, b.value
+
+    def readback(self, kind, out=None):
+        if kind == REB_SHADOW_F32:
+            shape, dt = (self.shadow_size, self.shadow_size), np.float32
+        else:
+            dt, ch = _KIND_INFO[kind]
+            shape = (self.height, self.width, ch) if ch > 1 else (self.height, self.width)
+        if out is None:
+            out = np.empty(shape, dt)
+        self._ck(self.lib.reb_readback(self.h, kind, _ptr(out)))
+        return out
+
+    def readback_into(self, kind, host_ptr):
+        """D2H into a caller-owned (e.g. pinned) buffer given as an integer address."""
+        self._ck(self.lib.reb_readback(self.h, kind, C.c_void_p(host_ptr)))
+
+    def set_partition(self, rank, n_ranks, band_h=64):
+        self._ck(self.lib.reb_set_partition(self.h, rank, n_ranks, band_h))
+
+    def shadow_mark_valid(self):
+        self._ck(self.lib.reb_shadow_mark_valid(self.h, self.shadow_id))
+
+    def counters(self):
+        c = np.zeros(4, np.uint64)
+        self._ck(self.lib.reb_get_counters(self.h, _ptr(c)))
+        return c
+
+    KERNEL_SLOTS = ("clear", "setup_raster", "bin_count", "tile_scan", "bin_scatter", "tile_stage")
+
+    def set_profiling(self, on):
+        self._ck(self.lib.reb_set_profiling(self.h, int(on)))
+
+    def kernel_times_ms(self, pass_kind):
+        t = np.zeros(6, np.float32)
+        self._ck(self.lib.reb_get_kernel_times(self.h, pass_kind, _ptr(t)))
+        return dict(zip(self.KERNEL_SLOTS, (float(x) for x in t)))
+
+    def launch_count(self):
+        n = C.c_uint64()
+        self._ck(self.lib.reb_get_launch_count(self.h, C.byref(n)))
+        return n.value

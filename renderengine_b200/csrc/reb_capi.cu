@@ -1,0 +1,268 @@
+// reb_capi.cu — the C ABI (include/reb.h) over the raster kernels.  Host code only: owns device
+// memory, orders the kernels on one CUDA stream, converts the reference's host records into kernel
+// parameters.  There is no CPU rendering path here: every render call launches the sm_100a kernels.
+#include "../../include/reb.h"
+#include "reb_kernels.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace reb;
+
+namespace {
+
+std::string g_createError;
+
+struct PassState {               // per pass kind: 0 = shadow, 1 = forward
+    std::vector<reb_draw> draws; // last submitted list (host copy, for change detection and replay)
+    DrawDev* dDraws = nullptr; uint32_t drawCap = 0;
+    uint32_t nDraws = 0, nTris = 0;
+    bool pending = false;        // enqueued since the last overflow check
+};
+
+}  // namespace
+
+struct reb_ctx {
+    int device = 0; int numSMs = 148;
+    cudaStream_t stream = nullptr; bool ownStream = false;
+    std::string err;
+    uint32_t W = 0, H = 0, outputs = 0, maxDesc = 8192;
+    uint32_t rank = 0, nRanks = 1, bandH = 64;
+    // geometry (SoA streams)
+    float4* pos4 = nullptr; float4* nrm4 = nullptr; uint32_t* indices = nullptr; uint64_t nVerts = 0, nIdx = 0;
+    float* transforms = nullptr; float* nmats = nullptr; uint32_t nNodes = 0;
+    uint8_t* materials = nullptr; uint32_t materialStride = 0, nMaterials = 0;
+    uint8_t* lights = nullptr; uint32_t lightStride = 0, nLights = 0;
+    // view
+    float view[16], proj[16], PV[16], viewPos[3]; bool haveView = false;
+    // shadow (one directional shadow map, F10)
+    uint32_t S = 0; float* shadowMap = nullptr; float sview[16], sproj[16], SPV[16]; bool haveShadowXf = false, shadowValid = false;
+    // outputs + visibility buffer
+    uint8_t* outSRGB8 = nullptr; float* outF32 = nullptr; float* outDepth = nullptr; uint32_t* outTriId = nullptr;
+    unsigned long long* vis = nullptr;
+    // queues
+    LargeRec* large = nullptr; uint32_t largeCap = 0;
+    LargeRec* huge = nullptr;        // 2 x HUGE_CAP
+    uint32_t* tileCount = nullptr; uint32_t* tileStart = nullptr; uint32_t tileCap = 0;
+    uint32_t* tileList = nullptr; uint32_t listCap = 0;
+    uint32_t* dStatus = nullptr;     // 2 x 8 words
+    uint32_t* hStatus = nullptr;     // pinned mirror
+    PassState pass[2];
+    uint64_t launches = 0, regrows = 0;
+    bool profiling = false; cudaEvent_t ev[2][7] = {}; float kernelMs[2][6] = {};   // per-kernel timing slots (diagnostics)
+    uint64_t counters[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+int fail(reb_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg; else g_createError = msg;
+    return code;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(ctx, REB_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
+    } while (0)
+
+// glm mat4*mat4, non-aligned path (type_mat4x4.inl:679-694): ((A0*b.x + A1*b.y) + A2*b.z) + A3*b.w
+void mat4_mul(const float* a, const float* b, float* out) {
+    float tmp[16];
+    for (int c = 0; c < 4; ++c)
+        for (int r = 0; r < 4; ++r) {
+            float t = a[r] * b[c * 4];
+            t = t + a[4 + r] * b[c * 4 + 1];
+            t = t + a[8 + r] * b[c * 4 + 2];
+            t = t + a[12 + r] * b[c * 4 + 3];
+            tmp[c * 4 + r] = t;
+        }
+    std::memcpy(out, tmp, sizeof tmp);
+}
+
+// transpose(inverse(mat3(T))) hoisted per node (primitive.vert:55; glm func_matrix.inl:353-376)
+void normal_matrix12(const float* T, float* out12) {
+    const float a00 = T[0], a01 = T[1], a02 = T[2];     // column 0
+    const float a10 = T[4], a11 = T[5], a12 = T[6];     // column 1
+    const float a20 = T[8], a21 = T[9], a22 = T[10];    // column 2
+    const float det = +a00 * (a11 * a22 - a21 * a12) - a10 * (a01 * a22 - a21 * a02) + a20 * (a01 * a12 - a11 * a02);
+    const float ood = 1.0f / det;
+    float inv[3][3];
+    inv[0][0] = +(a11 * a22 - a21 * a12); inv[1][0] = -(a10 * a22 - a20 * a12); inv[2][0] = +(a10 * a21 - a20 * a11);
+    inv[0][1] = -(a01 * a22 - a21 * a02); inv[1][1] = +(a00 * a22 - a20 * a02); inv[2][1] = -(a00 * a21 - a20 * a01);
+    inv[0][2] = +(a01 * a12 - a11 * a02); inv[1][2] = -(a00 * a12 - a10 * a02); inv[2][2] = +(a00 * a11 - a10 * a01);
+    for (int c = 0; c < 3; ++c)
+        for (int r = 0; r < 3; ++r) out12[c * 3 + r] = inv[r][c] * ood;   // scaled, then transposed
+    out12[9] = out12[10] = out12[11] = 0.0f;
+}
+
+template <class T> int dev_alloc(reb_ctx* ctx, T** p, size_t count) {
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    if (count == 0) return REB_OK;
+    CU(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
+    return REB_OK;
+}
+
+int alloc_targets(reb_ctx* ctx) {
+    const size_t px = (size_t)ctx->W * ctx->H;
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->vis, px))) return rc;
+    launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->vis), 0xFFFFFFFFu, px * 2, ctx->numSMs, ctx->stream); ctx->launches++;
+    if (ctx->outputs & REB_OUT_COLOR_SRGB8) {
+        if ((rc = dev_alloc(ctx, &ctx->outSRGB8, px * 4))) return rc;
+        launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->outSRGB8), 0xFF000000u, px, ctx->numSMs, ctx->stream); ctx->launches++;
+    }
+    if (ctx->outputs & REB_OUT_COLOR_F32) {
+        if ((rc = dev_alloc(ctx, &ctx->outF32, px * 4))) return rc;
+        launch_fill_u32x4(ctx->outF32, 0u, 0u, 0u, 0x3F800000u, px, ctx->numSMs, ctx->stream); ctx->launches++;   // (0,0,0,1)
+    }
+    if (ctx->outputs & REB_OUT_DEPTH_F32) {
+        if ((rc = dev_alloc(ctx, &ctx->outDepth, px))) return rc;
+        launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->outDepth), 0x3F800000u, px, ctx->numSMs, ctx->stream); ctx->launches++;
+    }
+    if (ctx->outputs & REB_OUT_TRIID_U32) {
+        if ((rc = dev_alloc(ctx, &ctx->outTriId, px))) return rc;
+        launch_fill_u32(ctx->outTriId, 0xFFFFFFFFu, px, ctx->numSMs, ctx->stream); ctx->launches++;
+    }
+    return REB_OK;
+}
+
+int ensure_tiles(reb_ctx* ctx, uint32_t nTiles) {
+    if (nTiles + 1 <= ctx->tileCap) return REB_OK;
+    int rc;
+    CU(cudaStreamSynchronize(ctx->stream));
+    if ((rc = dev_alloc(ctx, &ctx->tileCount, (size_t)nTiles + 1))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->tileStart, (size_t)nTiles + 1))) return rc;
+    CU(cudaMemsetAsync(ctx->tileCount, 0, ((size_t)nTiles + 1) * 4, ctx->stream));   // the tile stage re-arms them after each pass
+    ctx->tileCap = nTiles + 1;
+    return REB_OK;
+}
+
+int ensure_large(reb_ctx* ctx, uint32_t nTris) {
+    if (nTris <= ctx->largeCap) return REB_OK;
+    CU(cudaStreamSynchronize(ctx->stream));
+    int rc = dev_alloc(ctx, &ctx->large, (size_t)nTris);
+    if (rc) return rc;
+    ctx->largeCap = nTris;
+    return REB_OK;
+}
+
+int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
+    PassState& ps = ctx->pass[kind];
+    if (ps.draws.size() == n && (n == 0 || std::memcmp(ps.draws.data(), draws, n * sizeof(reb_draw)) == 0) && ps.dDraws) return REB_OK;
+    std::vector<DrawDev> dd(n);
+    uint64_t tri = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        if ((uint64_t)draws[i].indexOffset + draws[i].nbIndices > ctx->nIdx) return fail(ctx, REB_E_INVALID, "draw index range exceeds the index buffer");
+        if (draws[i].sceneNode >= ctx->nNodes) return fail(ctx, REB_E_INVALID, "draw references an unknown scene node");
+        dd[i] = {draws[i].indexOffset, (uint32_t)tri, draws[i].materialRaw, draws[i].sceneNode};
+        tri += draws[i].nbIndices / 3;
+    }
+    if (tri >= 0xFFFFFFFFull) return fail(ctx, REB_E_INVALID, "more than 2^32-2 primitives in one pass");
+    if (n > ps.drawCap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        int rc = dev_alloc(ctx, &ps.dDraws, (size_t)std::max(n, 64u));
+        if (rc) return rc;
+        ps.drawCap = std::max(n, 64u);
+    }
+    if (n) CU(cudaMemcpyAsync(ps.dDraws, dd.data(), n * sizeof(DrawDev), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));   // dd is a stack-lifetime staging buffer
+    ps.draws.assign(draws, draws + n);
+    ps.nDraws = n; ps.nTris = (uint32_t)tri;
+    return REB_OK;
+}
+
+void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
+    const PassState& ps = ctx->pass[kind];
+    std::memset(&pc, 0, sizeof pc);
+    std::memcpy(pc.PV, kind == 0 ? ctx->SPV : ctx->PV, 64);
+    pc.W = kind == 0 ? ctx->S : ctx->W; pc.H = kind == 0 ? ctx->S : ctx->H;
+    pc.nTris = ps.nTris; pc.nDraws = ps.nDraws;
+    pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.transforms = ctx->transforms; pc.draws = ps.dDraws;
+    pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
+    pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
+    pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
+    pc.status = ctx->dStatus + 8 * kind;
+    if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
+    else { pc.rank = 0; pc.nRanks = 1; pc.bandH = 64; }
+}
+
+int enqueue_pass(reb_ctx* ctx, int kind) {
+    PassState& ps = ctx->pass[kind];
+    PassConst pc;
+    int rc;
+    if ((rc = ensure_large(ctx, ps.nTris))) return rc;
+    fill_pass(ctx, kind, pc);
+    const uint32_t nTiles = pc.tilesX * pc.tilesY;
+    if ((rc = ensure_tiles(ctx, nTiles))) return rc;
+    fill_pass(ctx, kind, pc);
+    CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
+    // slots: 0 fill, 1 setup+small raster, 2 bin count, 3 scan, 4 bin scatter, 5 tile stage
+    auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
+    mark(0);
+    if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
+    mark(1);
+    if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->stream); ctx->launches++; }
+    mark(2);
+    launch_bin_count(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
+    mark(3);
+    launch_scan_tiles(pc, ctx->tileCount, ctx->tileStart, ctx->listCap, ctx->stream); ctx->launches++;
+    mark(4);
+    launch_bin_scatter(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
+    mark(5);
+    if (kind == 0) {
+        launch_tile_shadow(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
+    } else {
+        ShadeConst sh;
+        std::memset(&sh, 0, sizeof sh);
+        std::memcpy(sh.STR, ctx->SPV, 64);
+        std::memcpy(sh.viewPos, ctx->viewPos, 12);
+        sh.nLights = ctx->nLights; sh.nrm4 = ctx->nrm4; sh.nmats = ctx->nmats;
+        sh.materials = ctx->materials; sh.materialStride = ctx->materialStride; sh.nMaterials = ctx->nMaterials;
+        sh.lights = ctx->lights; sh.lightStride = ctx->lightStride;
+        const bool useShadow = ctx->shadowMap && ctx->shadowValid && ctx->haveShadowXf;
+        sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
+        sh.maxDescriptors = ctx->maxDesc;
+        sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
+        launch_tile_forward(pc, sh, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->stream); ctx->launches++;
+    }
+    mark(6);
+    CU(cudaMemcpyAsync(ctx->hStatus + 8 * kind, pc.status, 32, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaGetLastError());
+    ps.pending = true;
+    if (kind == 0) ctx->shadowValid = true;
+    return REB_OK;
+}
+
+// After a stream sync: look at the status words of the passes enqueued since the last check; grow the
+// tile-list queue and replay the frame if it overflowed (failure detection / recovery).
+int check_and_recover(reb_ctx* ctx) {
+    for (int iter = 0; iter < 8; ++iter) {
+        bool overflow = false;
+        uint32_t need = ctx->listCap;
+        for (int k = 0; k < 2; ++k) {
+            if (!ctx->pass[k].pending) continue;
+            const uint32_t* st = ctx->hStatus + 8 * k;
+            ctx->counters[0] = (k == 0 ? 0 : ctx->counters[0]) + st[1];
+            ctx->counters[1] = st[0]; ctx->counters[2] = st[3];
+            if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
+        }
+        if (!overflow) { ctx->pass[0].pending = ctx->pass[1].pending = false; return REB_OK; }
+        int rc = dev_alloc(ctx, &ctx->tileList, (size_t)need);
+        if (rc) return rc;
+        ctx->listCap = need; ctx->regrows++; ctx->counters[3] = ctx->regrows;
+        const bool p0 = ctx->pass[0].pending, p1 = ctx->pass[1].pending;
+        if (p0 && (rc = enqueue_pass(ctx, 0))) return rc;
+        if (p1 && (rc = enqueue_pass(ctx, 1))) return rc;
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return fail(ctx, REB_E_OVERFLOW, "tile-list queue kept overflowing after 8 regrow attempts");
+}
+
+}  // namespace
+
+#include "reb_capi_entry.inl"

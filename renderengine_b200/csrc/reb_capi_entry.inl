@@ -1,0 +1,302 @@
+// reb_capi_entry.inl — extern "C" entry points (included by reb_capi.cu).
+
+#define CHECK_CTX() do { if (!ctx) return REB_E_INVALID; } while (0)
+
+extern "C" {
+
+int reb_abi_version(void) { return REB_ABI_VERSION; }
+
+const char* reb_last_error(reb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+int reb_create(const reb_params* params, reb_ctx** out) {
+    reb_ctx* ctx = nullptr;
+    if (!params || !out || params->struct_size != sizeof(reb_params)) return fail(nullptr, REB_E_INVALID, "reb_create: bad params / struct_size");
+    if (params->width == 0 || params->height == 0) return fail(nullptr, REB_E_INVALID, "reb_create: zero extent");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail(nullptr, REB_E_NO_DEVICE, "reb_create: no CUDA device (there is no CPU fallback)");
+    if (params->device < 0 || params->device >= count) return fail(nullptr, REB_E_INVALID, "reb_create: device ordinal out of range");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, params->device) != cudaSuccess) return fail(nullptr, REB_E_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major != 10) return fail(nullptr, REB_E_NO_DEVICE, "reb_create: kernels are built for sm_100a only; device is not compute capability 10.x");
+    ctx = new reb_ctx();
+    *out = nullptr;
+    auto bail = [&](int rc) { g_createError = ctx->err; reb_destroy(ctx); return rc; };
+    ctx->device = params->device; ctx->numSMs = prop.multiProcessorCount;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "cudaSetDevice failed"));
+    if (params->stream) ctx->stream = reinterpret_cast<cudaStream_t>(params->stream);
+    else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "cudaStreamCreate failed"));
+        ctx->ownStream = true;
+    }
+    ctx->W = params->width; ctx->H = params->height;
+    ctx->maxDesc = params->max_descriptors ? params->max_descriptors : 8192u;
+    ctx->outputs = params->outputs ? params->outputs : (REB_OUT_COLOR_SRGB8 | REB_OUT_COLOR_F32 | REB_OUT_DEPTH_F32 | REB_OUT_TRIID_U32);
+    ctx->nRanks = params->n_ranks ? params->n_ranks : 1u; ctx->rank = params->rank;
+    ctx->bandH = params->band_h ? params->band_h : 64u;
+    if (ctx->rank >= ctx->nRanks || ctx->bandH % TILE_H) return bail(fail(ctx, REB_E_INVALID, "reb_create: bad partition (rank < n_ranks, band_h multiple of 8)"));
+    int rc;
+    if ((rc = alloc_targets(ctx))) return bail(rc);
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 64) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 64) != cudaSuccess ||
+        cudaMalloc(reinterpret_cast<void**>(&ctx->huge), 2 * HUGE_CAP * sizeof(LargeRec)) != cudaSuccess ||
+        cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocDefault) != cudaSuccess)
+        return bail(fail(ctx, REB_E_CUDA, "status buffers allocation failed"));
+    std::memset(ctx->hStatus, 0, 64);
+    ctx->listCap = 4u << 20;
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->tileList), (size_t)ctx->listCap * 4) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "tile list allocation failed"));
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "stream sync failed in reb_create"));
+    *out = ctx;
+    return REB_OK;
+}
+
+int reb_destroy(reb_ctx* ctx) {
+    CHECK_CTX();
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
+                    ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount, ctx->tileStart,
+                    ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
+    if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return REB_OK;
+}
+
+int reb_upload_geometry(reb_ctx* ctx, const void* verts, uint64_t nVerts, const uint32_t* idx, uint64_t nIdx) {
+    CHECK_CTX();
+    if ((!verts && nVerts) || (!idx && nIdx)) return fail(ctx, REB_E_INVALID, "reb_upload_geometry: null buffer");
+    if (nVerts >= 0xFFFFFFFFull || nIdx >= 0xFFFFFFFFull) return fail(ctx, REB_E_INVALID, "reb_upload_geometry: counts must fit u32");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->pos4, nVerts))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->nrm4, nVerts))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->indices, nIdx))) return rc;
+    ctx->nVerts = nVerts; ctx->nIdx = nIdx;
+    ctx->pass[0].draws.clear(); ctx->pass[1].draws.clear();
+    if (nVerts) {
+        float4* aos = nullptr;
+        CU(cudaMalloc(reinterpret_cast<void**>(&aos), nVerts * 32));
+        CU(cudaMemcpyAsync(aos, verts, nVerts * 32, cudaMemcpyHostToDevice, ctx->stream));
+        launch_split_vertices(aos, ctx->pos4, ctx->nrm4, nVerts, ctx->stream); ctx->launches++;
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaFree(aos));
+    }
+    if (nIdx) {
+        CU(cudaMemcpyAsync(ctx->indices, idx, nIdx * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return REB_OK;
+}
+
+int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
+    CHECK_CTX();
+    if (!m && nNodes) return fail(ctx, REB_E_INVALID, "reb_upload_transforms: null buffer");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->nmats, (size_t)nNodes * 12))) return rc;
+    ctx->nNodes = nNodes;
+    if (!nNodes) return REB_OK;
+    std::vector<float> nm((size_t)nNodes * 12);
+    for (uint32_t n = 0; n < nNodes; ++n) normal_matrix12(m + 16 * (size_t)n, &nm[12 * (size_t)n]);
+    CU(cudaMemcpyAsync(ctx->transforms, m, (size_t)nNodes * 64, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->nmats, nm.data(), nm.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return REB_OK;
+}
+
+static int upload_records(reb_ctx* ctx, uint8_t** dst, const void* records, uint32_t stride, uint32_t n, uint32_t minStride, const char* what) {
+    if ((!records && n) || stride < minStride || stride % 16) return fail(ctx, REB_E_INVALID, std::string(what) + ": bad records / stride (16-B multiple required)");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    int rc;
+    if ((rc = dev_alloc(ctx, dst, (size_t)stride * n))) return rc;
+    if (n) {
+        CU(cudaMemcpyAsync(*dst, records, (size_t)stride * n, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return REB_OK;
+}
+
+int reb_upload_materials(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n) {
+    CHECK_CTX();
+    int rc = upload_records(ctx, &ctx->materials, records, stride, n, 48, "reb_upload_materials");
+    if (rc == REB_OK) { ctx->materialStride = stride; ctx->nMaterials = n; }
+    return rc;
+}
+
+int reb_upload_lights(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n) {
+    CHECK_CTX();
+    int rc = upload_records(ctx, &ctx->lights, records, stride, n, 112, "reb_upload_lights");
+    if (rc == REB_OK) { ctx->lightStride = stride; ctx->nLights = n; }
+    return rc;
+}
+
+int reb_register_texture(reb_ctx* ctx, const reb_texture_desc* desc, const void* texels, uint32_t* outHandle) {
+    CHECK_CTX();
+    (void)desc; (void)texels; (void)outHandle;
+    return fail(ctx, REB_E_UNSUPPORTED, "reb_register_texture: textured materials are not implemented yet");
+}
+
+int reb_shadow_create(reb_ctx* ctx, uint32_t size, uint32_t* outShadowId) {
+    CHECK_CTX();
+    if (size == 0 || size > 16384) return fail(ctx, REB_E_INVALID, "reb_shadow_create: size must be in 1..16384");
+    if (ctx->shadowMap) return fail(ctx, REB_E_UNSUPPORTED, "reb_shadow_create: exactly one directional shadow map is supported (SURVEY F10)");
+    CU(cudaSetDevice(ctx->device));
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->shadowMap, (size_t)size * size))) return rc;
+    ctx->S = size; ctx->shadowValid = false;
+    launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->shadowMap), 0x3F800000u, (size_t)size * size, ctx->numSMs, ctx->stream); ctx->launches++;
+    if (outShadowId) *outShadowId = 0;
+    return REB_OK;
+}
+
+int reb_shadow_set_transform(reb_ctx* ctx, uint32_t shadowId, const float* view16, const float* proj16) {
+    CHECK_CTX();
+    if (shadowId != 0 || !ctx->shadowMap || !view16 || !proj16) return fail(ctx, REB_E_INVALID, "reb_shadow_set_transform: unknown shadow id or null matrix");
+    std::memcpy(ctx->sview, view16, 64); std::memcpy(ctx->sproj, proj16, 64);
+    mat4_mul(ctx->sproj, ctx->sview, ctx->SPV);   // ShadowSystem.cpp:303 / shadow_map.vert:51
+    ctx->haveShadowXf = true;
+    return REB_OK;
+}
+
+int reb_set_view(reb_ctx* ctx, const void* vp) {
+    CHECK_CTX();
+    if (!vp) return fail(ctx, REB_E_INVALID, "reb_set_view: null");
+    const float* f = static_cast<const float*>(vp);
+    std::memcpy(ctx->view, f, 64); std::memcpy(ctx->proj, f + 16, 64); std::memcpy(ctx->viewPos, f + 32, 12);
+    mat4_mul(ctx->proj, ctx->view, ctx->PV);      // primitive.vert:53
+    ctx->haveView = true;
+    return REB_OK;
+}
+
+static int ready_to_render(reb_ctx* ctx) {
+    if (!ctx->pos4 || !ctx->indices) return fail(ctx, REB_E_INVALID, "render before reb_upload_geometry");
+    if (!ctx->transforms) return fail(ctx, REB_E_INVALID, "render before reb_upload_transforms");
+    return REB_OK;
+}
+
+int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, uint32_t n) {
+    CHECK_CTX();
+    if (shadowId != 0 || !ctx->shadowMap) return fail(ctx, REB_E_INVALID, "reb_render_shadow: unknown shadow id");
+    if (!ctx->haveShadowXf) return fail(ctx, REB_E_INVALID, "reb_render_shadow before reb_shadow_set_transform");
+    if (!draws && n) return fail(ctx, REB_E_INVALID, "reb_render_shadow: null draws");
+    int rc;
+    if ((rc = ready_to_render(ctx))) return rc;
+    CU(cudaSetDevice(ctx->device));
+    if ((rc = set_draws(ctx, 0, draws, n))) return rc;
+    return enqueue_pass(ctx, 0);
+}
+
+int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
+    CHECK_CTX();
+    if (!ctx->haveView) return fail(ctx, REB_E_INVALID, "reb_render_forward before reb_set_view");
+    if (!draws && n) return fail(ctx, REB_E_INVALID, "reb_render_forward: null draws");
+    int rc;
+    if ((rc = ready_to_render(ctx))) return rc;
+    if (!ctx->materials || !ctx->nMaterials) return fail(ctx, REB_E_INVALID, "reb_render_forward before reb_upload_materials");
+    if (ctx->nLights && !ctx->lights) return fail(ctx, REB_E_INVALID, "reb_render_forward: lights missing");
+    CU(cudaSetDevice(ctx->device));
+    if ((rc = set_draws(ctx, 1, draws, n))) return rc;
+    return enqueue_pass(ctx, 1);
+}
+
+int reb_sync(reb_ctx* ctx) {
+    CHECK_CTX();
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return check_and_recover(ctx);
+}
+
+static int output_info(reb_ctx* ctx, reb_output_kind kind, void** p, uint64_t* bytes) {
+    const uint64_t px = (uint64_t)ctx->W * ctx->H;
+    switch (kind) {
+        case REB_COLOR_SRGB8: *p = ctx->outSRGB8; *bytes = px * 4; break;
+        case REB_COLOR_F32: *p = ctx->outF32; *bytes = px * 16; break;
+        case REB_DEPTH_F32: *p = ctx->outDepth; *bytes = px * 4; break;
+        case REB_TRIID_U32: *p = ctx->outTriId; *bytes = px * 4; break;
+        case REB_SHADOW_F32: *p = ctx->shadowMap; *bytes = (uint64_t)ctx->S * ctx->S * 4; break;
+        default: return fail(ctx, REB_E_INVALID, "unknown output kind");
+    }
+    if (!*p) return fail(ctx, REB_E_INVALID, "requested output is not enabled on this context");
+    return REB_OK;
+}
+
+int reb_get_output(reb_ctx* ctx, reb_output_kind kind, void** devPtr, uint64_t* bytes) {
+    CHECK_CTX();
+    void* p = nullptr; uint64_t b = 0;
+    int rc = output_info(ctx, kind, &p, &b);
+    if (rc) return rc;
+    if (devPtr) *devPtr = p;
+    if (bytes) *bytes = b;
+    return REB_OK;
+}
+
+int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host) {
+    CHECK_CTX();
+    if (!host) return fail(ctx, REB_E_INVALID, "reb_readback: null host buffer");
+    CU(cudaSetDevice(ctx->device));
+    int rc;
+    if (ctx->pass[0].pending || ctx->pass[1].pending) { if ((rc = reb_sync(ctx))) return rc; }
+    void* p = nullptr; uint64_t b = 0;
+    if ((rc = output_info(ctx, kind, &p, &b))) return rc;
+    CU(cudaMemcpyAsync(host, p, b, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return REB_OK;
+}
+
+int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH) {
+    CHECK_CTX();
+    if (nRanks == 0 || rank >= nRanks || bandH == 0 || bandH % TILE_H) return fail(ctx, REB_E_INVALID, "reb_set_partition: need rank < nRanks and bandH a multiple of 8");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->rank = rank; ctx->nRanks = nRanks; ctx->bandH = bandH;
+    return alloc_targets(ctx);   // re-clear: pixels outside this rank's bands keep the clear values
+}
+
+int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId) {
+    CHECK_CTX();
+    if (shadowId != 0 || !ctx->shadowMap) return fail(ctx, REB_E_INVALID, "reb_shadow_mark_valid: unknown shadow id");
+    ctx->shadowValid = true;
+    return REB_OK;
+}
+
+int reb_get_counters(reb_ctx* ctx, uint64_t* c) {
+    CHECK_CTX();
+    if (!c) return REB_E_INVALID;
+    for (int i = 0; i < 4; ++i) c[i] = ctx->counters[i];
+    return REB_OK;
+}
+
+int reb_set_profiling(reb_ctx* ctx, int on) {
+    CHECK_CTX();
+    CU(cudaSetDevice(ctx->device));
+    if (on && !ctx->ev[0][0])
+        for (int k = 0; k < 2; ++k) for (int i = 0; i < 7; ++i) CU(cudaEventCreate(&ctx->ev[k][i]));
+    ctx->profiling = on != 0;
+    return REB_OK;
+}
+
+int reb_get_kernel_times(reb_ctx* ctx, int pass, float* ms6) {
+    CHECK_CTX();
+    if (pass < 0 || pass > 1 || !ms6 || !ctx->ev[0][0]) return fail(ctx, REB_E_INVALID, "reb_get_kernel_times: profiling not enabled / bad args");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 6; ++i) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, ctx->ev[pass][i], ctx->ev[pass][i + 1]) != cudaSuccess) { ms = 0.0f; cudaGetLastError(); }
+        ms6[i] = ms;
+    }
+    return REB_OK;
+}
+
+int reb_get_launch_count(reb_ctx* ctx, uint64_t* out) {
+    CHECK_CTX();
+    if (!out) return REB_E_INVALID;
+    *out = ctx->launches;
+    return REB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,36 @@
+// reb_kernels.h — host-visible launch wrappers of the raster kernels (internal to libreb.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "reb_device.cuh"
+
+namespace reb {
+
+struct ShadeConst {
+    float STR[16];                 // shadowProj*shadowView (ShadowSystem.cpp:303)
+    float viewPos[3]; uint32_t nLights;
+    const float4* nrm4;            // (nx, ny, nz, v)
+    const float* nmats;            // 12 floats per node: transpose(inverse(mat3(T))), column-major 3x3 + pad
+    const uint8_t* materials; uint32_t materialStride; uint32_t nMaterials;
+    const uint8_t* lights; uint32_t lightStride;
+    const float* shadowMap; uint32_t shadowSize;   // NULL / 0: shadow = 0
+    uint32_t maxDescriptors; uint32_t nTextures;
+    const void* textures;
+    uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;
+};
+
+void launch_setup_raster(const PassConst& pc, bool shadow, cudaStream_t st);
+void launch_bin_count(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
+                      int numSMs, cudaStream_t st);
+void launch_scan_tiles(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t listCap, cudaStream_t st);
+void launch_bin_scatter(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
+                        int numSMs, cudaStream_t st);
+void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
+void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
+void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
+void launch_tile_shadow(const PassConst& pc, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList, uint32_t listCap,
+                        int numSMs, cudaStream_t st);
+void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList,
+                         uint32_t listCap, cudaStream_t st);
+
+}  // namespace reb
