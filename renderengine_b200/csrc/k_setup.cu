@@ -12,108 +12,176 @@
 namespace reb {
 
 // ---------------------------------------------------------------------------------------------
-// K1: one thread per triangle.
-//   * indices / float4 positions fetched through the read-only path (LDG.128 gathers),
-//   * both matrix stages, viewport, snap, cull (exact order of Appendix B),
-//   * triangles whose bbox covers <= SMALL_MAX x SMALL_MAX pixel centres are rasterised here with
-//     32-bit edge functions and resolved with one 64-bit atomicMin per covered sample
-//     (key = depthBits<<32 | ~triId; shadow pass: 32-bit atomicMin on the depth bits),
-//   * everything else is compacted (warp ballot + popc prefix, one atomicAdd per warp) into the
-//     LargeRec queue consumed by the tile path.
+// K1: triangle setup + small-triangle raster.  256 triangles per CTA, two phases.
+//
+// Phase 1, one thread per triangle: 3 indices + 3 VtxA gathers (16 B each) from the post-transform
+//   cache, clip-flag logic, facing (int64 shoelace), pixel-centre bbox, classification:
+//     small  (spans <= SMALL_MAX px)  -> compacted into shared memory as 32-bit edge equations,
+//     huge   (> HUGE_TILES tiles)     -> short broadcast list tested by every tile,
+//     large  (everything else)        -> warp-aggregated append to the LargeRec queue (binned path).
+//   Compaction = warp ballot + shuffle scan + one shared-memory pass over the 8 warp totals; the same
+//   scan carries the number of pixel rows of every small triangle.
+// Phase 2, one thread per (small triangle, pixel row) work item: back-face-culled and clipped lanes
+//   no longer idle through the raster loop, and lanes of a warp walk rows of near-equal width.
+//   Coverage = three incrementally updated 32-bit edge functions with the top-left bias folded in;
+//   covered samples resolve with one 64-bit atomicMin (key = depthBits<<32 | ~triId; shadow pass:
+//   32-bit atomicMin on the depth bits, which are the shadow map itself).
 // ---------------------------------------------------------------------------------------------
+constexpr int K1_THREADS = 256;
+constexpr int K1_MAX_ROWS = K1_THREADS * (SMALL_MAX + 1);
+
+struct K1Shared {
+    int32_t Ax[3][K1_THREADS];      // 256 * A_k  (step of the biased edge function per pixel in x)
+    int32_t By[3][K1_THREADS];      // 256 * B_k  (step per pixel in y)
+    int32_t C[3][K1_THREADS];       // biased edge value at the bbox origin's pixel centre
+    uint32_t xy[K1_THREADS];        // x0 | y0 << 16
+    uint32_t whb[K1_THREADS];       // w | h << 8 | bias1 << 16 | bias2 << 17
+    float z0[K1_THREADS], dz1[K1_THREADS], dz2[K1_THREADS], area[K1_THREADS];
+    uint32_t idKey[K1_THREADS];
+    uint32_t rowStart[K1_THREADS];
+    uint32_t warpTot[K1_THREADS / 32];
+    uint32_t drawBase;
+    uint8_t itemTri[K1_MAX_ROWS];
+};
+
 template <bool SHADOW>
-__global__ void __launch_bounds__(256) k_setup_raster(const __grid_constant__ PassConst pc) {
-    const uint32_t tri = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(K1_THREADS) k_setup_raster(const __grid_constant__ PassConst pc) {
+    __shared__ K1Shared sm;
+    const uint32_t firstTri = blockIdx.x * K1_THREADS;
+    const uint32_t tri = firstTri + threadIdx.x;
     const bool valid = tri < pc.nTris;
-    Snapped s;
-    SetupResult res = SR_REJECT;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+
+    const uint32_t d = find_draw_cta<false>(pc.draws, pc.nDraws, firstTri, valid ? tri : firstTri, &sm.drawBase);
+    bool keep = false, needsClip = false;
+    VtxA a0, a1, a2;
+    long long A2 = 0;
+    int32_t x0 = 0, x1 = -1, y0 = 0, y1 = -1, spanX = 0, spanY = 0;
     if (valid) {
-        const uint32_t d = find_draw(pc.draws, pc.nDraws, tri);
-        const uint4 dr = __ldg(reinterpret_cast<const uint4*>(pc.draws) + d);   // indexOffset, firstTri, material, node
+        const uint4 dr = __ldg(reinterpret_cast<const uint4*>(pc.draws + d));        // indexOffset, firstTri, material, node
+        const int32_t cacheOffset = __ldg(&pc.draws[d].cacheOffset);
         const uint32_t* ix = pc.indices + dr.x + 3u * (tri - dr.y);
         const uint32_t i0 = __ldg(ix), i1 = __ldg(ix + 1), i2 = __ldg(ix + 2);
-        const float4 p0 = __ldg(pc.pos4 + i0), p1 = __ldg(pc.pos4 + i1), p2 = __ldg(pc.pos4 + i2);
-        const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * dr.w;
-        float T[16];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { float4 q = __ldg(Tq + k); T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
-        float4 c[3];
-        c[0] = vertex_stage<!SHADOW>(pc.PV, T, p0.x, p0.y, p0.z, nullptr);
-        c[1] = vertex_stage<!SHADOW>(pc.PV, T, p1.x, p1.y, p1.z, nullptr);
-        c[2] = vertex_stage<!SHADOW>(pc.PV, T, p2.x, p2.y, p2.z, nullptr);
-        res = setup_triangle(c, pc.W, pc.H, s);
+        const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
+        const uint4 q0 = __ldg(va + cache_slot(pc, cacheOffset, tri, 0, i0));
+        const uint4 q1 = __ldg(va + cache_slot(pc, cacheOffset, tri, 1, i1));
+        const uint4 q2 = __ldg(va + cache_slot(pc, cacheOffset, tri, 2, i2));
+        a0 = {(int32_t)q0.x, (int32_t)q0.y, __uint_as_float(q0.z), q0.w};
+        a1 = {(int32_t)q1.x, (int32_t)q1.y, __uint_as_float(q1.z), q1.w};
+        a2 = {(int32_t)q2.x, (int32_t)q2.y, __uint_as_float(q2.z), q2.w};
+        const bool reject = (a0.flags & a1.flags & a2.flags & VF_PLANES) != 0u;             // Appendix B.2
+        needsClip = !reject && ((a0.flags | a1.flags | a2.flags) & VF_NEEDS_CLIP) != 0u;    // Appendix B.3
+        if (!reject && !needsClip) {
+            A2 = (long long)(a1.X - a0.X) * (long long)(a2.Y - a0.Y) - (long long)(a2.X - a0.X) * (long long)(a1.Y - a0.Y);
+            if (A2 < 0) {                                                                   // Appendix B.6: front = CCW = A2 < 0
+                const int32_t minX = min(a0.X, min(a1.X, a2.X)), maxX = max(a0.X, max(a1.X, a2.X));
+                const int32_t minY = min(a0.Y, min(a1.Y, a2.Y)), maxY = max(a0.Y, max(a1.Y, a2.Y));
+                spanX = maxX - minX; spanY = maxY - minY;
+                x0 = max((minX + 127) >> 8, 0); x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+                y0 = max((minY + 127) >> 8, 0); y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+                keep = x0 <= x1 && y0 <= y1;
+            }
+        }
     }
-    if (res == SR_NEEDS_CLIP) atomicAdd(&pc.status[1], 1u);
+    if (needsClip) atomicAdd(&pc.status[1], 1u);
 
-    const bool keep = (res == SR_KEEP);
-    const bool isSmall = keep && (s.spanX <= SMALL_MAX * 256) && (s.spanY <= SMALL_MAX * 256);   // unclamped: keeps 32-bit edge math exact
+    const bool isSmall = keep && spanX <= SMALL_MAX * 256 && spanY <= SMALL_MAX * 256;   // unclamped spans keep the 32-bit edge math exact
     bool isLarge = keep && !isSmall;
     if (isLarge) {
         // screen-filling triangles go to a short broadcast list that every tile tests (no per-tile atomics)
-        const int ntiles = (s.x1 / TILE_W - s.x0 / TILE_W + 1) * (s.y1 / TILE_H - s.y0 / TILE_H + 1);
+        const int ntiles = (x1 / TILE_W - x0 / TILE_W + 1) * (y1 / TILE_H - y0 / TILE_H + 1);
         if (ntiles > HUGE_TILES) {
             const uint32_t slot = atomicAdd(&pc.status[4], 1u);
             if (slot < (uint32_t)HUGE_CAP) {
                 LargeRec r;
-                r.X0 = s.X[0]; r.Y0 = s.Y[0]; r.X1 = s.X[1]; r.Y1 = s.Y[1];
-                r.X2 = s.X[2]; r.Y2 = s.Y[2]; r.z0 = s.z[0]; r.z1 = s.z[1];
-                r.z2 = s.z[2]; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
+                r.X0 = a0.X; r.Y0 = a0.Y; r.X1 = a1.X; r.Y1 = a1.Y;
+                r.X2 = a2.X; r.Y2 = a2.Y; r.z0 = a0.z; r.z1 = a1.z;
+                r.z2 = a2.z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
                 pc.huge[slot] = r;
                 isLarge = false;
             }
         }
     }
 
-    if (isSmall) {
-        // 32-bit edge functions relative to the edge's first vertex; all magnitudes < 2^26 here.
-        int32_t A[3], B[3], Xa[3], Ya[3], bias[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int a = (k + 1) % 3, b = (k + 2) % 3;
-            A[k] = s.Y[b] - s.Y[a];
-            B[k] = -(s.X[b] - s.X[a]);
-            Xa[k] = s.X[a]; Ya[k] = s.Y[a];
-            bias[k] = ((A[k] > 0) || (A[k] == 0 && B[k] > 0)) ? 0 : 1;   // top-left rule
-        }
-        const float area = (float)(-s.A2);
-        const uint32_t idKey = ~tri;
-        for (int y = s.y0; y <= s.y1; ++y) {
-            if (!SHADOW && !row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) continue;
-            const int32_t Py = 256 * y + 128;
-            for (int x = s.x0; x <= s.x1; ++x) {
-                const int32_t Px = 256 * x + 128;
-                const int32_t F0 = A[0] * (Px - Xa[0]) + B[0] * (Py - Ya[0]);
-                const int32_t F1 = A[1] * (Px - Xa[1]) + B[1] * (Py - Ya[1]);
-                const int32_t F2 = A[2] * (Px - Xa[2]) + B[2] * (Py - Ya[2]);
-                if (((F0 - bias[0]) | (F1 - bias[1]) | (F2 - bias[2])) < 0) continue;
-                const float z = depth_from((float)F1, (float)F2, area, s.z[0], s.z[1], s.z[2]);
-                if (!(z >= 0.0f && z <= 1.0f)) continue;
-                const size_t p = (size_t)y * pc.W + x;
-                if (SHADOW) atomicMin(pc.depthBits + p, __float_as_uint(z));
-                else atomicMin(pc.vis + p, ((unsigned long long)__float_as_uint(z) << 32) | idKey);
-            }
-        }
-    }
-
-    // warp-aggregated compaction of large triangles
-    const unsigned mask = __ballot_sync(0xFFFFFFFFu, isLarge);
-    if (mask) {
-        const unsigned lane = threadIdx.x & 31u;
-        const int leader = __ffs(mask) - 1;
+    // warp-aggregated append of large triangles to the global queue
+    const unsigned lmask = __ballot_sync(0xFFFFFFFFu, isLarge);
+    if (lmask) {
+        const int leader = __ffs(lmask) - 1;
         uint32_t base = 0;
-        if ((int)lane == leader) base = atomicAdd(&pc.status[0], (uint32_t)__popc(mask));
+        if ((int)lane == leader) base = atomicAdd(&pc.status[0], (uint32_t)__popc(lmask));
         base = __shfl_sync(0xFFFFFFFFu, base, leader);
         if (isLarge) {
-            const uint32_t slot = base + __popc(mask & ((1u << lane) - 1u));
+            const uint32_t slot = base + __popc(lmask & ((1u << lane) - 1u));
             if (slot < pc.largeCap) {
                 LargeRec r;
-                r.X0 = s.X[0]; r.Y0 = s.Y[0]; r.X1 = s.X[1]; r.Y1 = s.Y[1];
-                r.X2 = s.X[2]; r.Y2 = s.Y[2]; r.z0 = s.z[0]; r.z1 = s.z[1];
-                r.z2 = s.z[2]; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
+                r.X0 = a0.X; r.Y0 = a0.Y; r.X1 = a1.X; r.Y1 = a1.Y;
+                r.X2 = a2.X; r.Y2 = a2.Y; r.z0 = a0.z; r.z1 = a1.z;
+                r.z2 = a2.z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
                 pc.large[slot] = r;
             } else {
                 atomicOr(&pc.status[2], OVF_LARGE);
             }
+        }
+    }
+
+    // CTA compaction of small triangles: packed scan of (count, rows) = 1 | h << 16
+    const uint32_t h = isSmall ? (uint32_t)(y1 - y0 + 1) : 0u;
+    const uint32_t mine = isSmall ? (1u | (h << 16)) : 0u;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= (unsigned)o) incl += n; }
+    if (lane == 31) sm.warpTot[warp] = incl;
+    __syncthreads();
+    uint32_t base = 0, total = 0;
+#pragma unroll
+    for (int wgt = 0; wgt < K1_THREADS / 32; ++wgt) { const uint32_t t = sm.warpTot[wgt]; if (wgt < (int)warp) base += t; total += t; }
+    const uint32_t nRows = total >> 16;
+    if (nRows == 0) return;   // CTA-uniform
+    if (isSmall) {
+        const uint32_t excl = base + incl - mine;
+        const uint32_t slot = excl & 0xFFFFu, row0 = excl >> 16;
+        const int32_t X[3] = {a0.X, a1.X, a2.X}, Y[3] = {a0.Y, a1.Y, a2.Y};
+        const int32_t Px = 256 * x0 + 128, Py = 256 * y0 + 128;
+        uint32_t biasBits = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int a = (k + 1) % 3, b = (k + 2) % 3;     // edge a->b opposes vertex k
+            const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
+            const int32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
+            sm.Ax[k][slot] = 256 * A;
+            sm.By[k][slot] = 256 * B;
+            sm.C[k][slot] = A * (Px - X[a]) + B * (Py - Y[a]) - bias;
+            if (k > 0) biasBits |= (uint32_t)bias << (15 + k);
+        }
+        sm.xy[slot] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+        sm.whb[slot] = (uint32_t)(x1 - x0 + 1) | (h << 8) | biasBits;
+        sm.z0[slot] = a0.z; sm.dz1[slot] = a1.z - a0.z; sm.dz2[slot] = a2.z - a0.z;
+        sm.area[slot] = (float)(-A2);
+        sm.idKey[slot] = ~tri;
+        sm.rowStart[slot] = row0;
+        for (uint32_t j = 0; j < h; ++j) sm.itemTri[row0 + j] = (uint8_t)slot;
+    }
+    __syncthreads();
+
+    for (uint32_t item = threadIdx.x; item < nRows; item += K1_THREADS) {
+        const uint32_t t = sm.itemTri[item];
+        const uint32_t j = item - sm.rowStart[t];
+        const uint32_t xy = sm.xy[t], whb = sm.whb[t];
+        const uint32_t y = (xy >> 16) + j;
+        if (!SHADOW && !row_owned(y, pc.rank, pc.nRanks, pc.bandH)) continue;
+        const int32_t s0 = sm.Ax[0][t], s1 = sm.Ax[1][t], s2 = sm.Ax[2][t];
+        int32_t F0 = sm.C[0][t] + (int32_t)j * sm.By[0][t];
+        int32_t F1 = sm.C[1][t] + (int32_t)j * sm.By[1][t];
+        int32_t F2 = sm.C[2][t] + (int32_t)j * sm.By[2][t];
+        const uint32_t w = whb & 0xFFu;
+        const size_t rowBase = (size_t)y * pc.W + (xy & 0xFFFFu);
+        for (uint32_t i = 0; i < w; ++i, F0 += s0, F1 += s1, F2 += s2) {
+            if ((F0 | F1 | F2) < 0) continue;
+            const float z = depth_from((float)(F1 + (int32_t)((whb >> 16) & 1u)), (float)(F2 + (int32_t)((whb >> 17) & 1u)),
+                                       sm.area[t], sm.z0[t], sm.dz1[t], sm.dz2[t]);
+            if (!(z >= 0.0f && z <= 1.0f)) continue;
+            if (SHADOW) atomicMin(pc.depthBits + rowBase + i, __float_as_uint(z));
+            else atomicMin(pc.vis + rowBase + i, ((unsigned long long)__float_as_uint(z) << 32) | sm.idKey[t]);
         }
     }
 }

@@ -1,0 +1,97 @@
+// k_vertex.cu — K0: the vertex stage, run once per referenced vertex into a post-transform cache.
+//
+// Replaces the vertex shaders the reference runs through vkCmdDrawIndexed: shadow_map.vert:48-52
+// (SHADOW) and primitive.vert:49-57 (forward), followed by the fixed-function viewport transform of
+// GraphicsPipelineCache.cpp:280-285.  The hardware's post-transform vertex cache becomes an explicit
+// SoA stream in HBM/L2: VtxA (snapped position + depth + clip flags, all that triangle setup needs)
+// and, for the forward pass, VtxBC (world position, 1/w, normalised normal — what shading interpolates).
+//
+// One thread per cache slot.  Indexed mode: every draw owns the contiguous slot range that covers the
+// vertex range its indices reference (host-side prefix over per-draw ranges), so slot -> (draw, vertex)
+// is a CTA-level search plus an add, loads are 16-B coalesced (float4 SoA) and stores are 16/32-B
+// coalesced.  De-indexed mode (draws referencing sparse / shared vertex ranges): slot = 3*tri + corner.
+#include "reb_device.cuh"
+#include "reb_kernels.h"
+
+namespace reb {
+
+template <bool SHADOW>
+__global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
+    __shared__ uint32_t sBase;
+    const uint32_t first = blockIdx.x * 256u;
+    const uint32_t slot = first + threadIdx.x;
+    const bool valid = slot < pc.cacheSize;
+    uint32_t d, v = 0;
+    if (pc.deindexed) {
+        const uint32_t tri = slot / 3u, k = slot - 3u * tri;
+        d = find_draw_cta<false>(pc.draws, pc.nDraws, first / 3u, valid ? tri : first / 3u, &sBase);
+        if (valid) v = __ldg(pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri)) + k);
+    } else {
+        d = find_draw_cta<true>(pc.draws, pc.nDraws, first, valid ? slot : first, &sBase);
+        if (valid) v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
+    }
+    if (!valid) return;
+    const uint32_t node = __ldg(&pc.draws[d].node);
+    const float4 p = __ldg(pc.pos4 + v);
+    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * node;
+    float T[16];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float4 q = __ldg(Tq + k); T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
+    V3 world;
+    const float4 c = vertex_stage<!SHADOW>(pc.PV, T, p.x, p.y, p.z, &world);
+    pc.vtxA[slot] = viewport_snap(c, pc.W, pc.H);
+    if (!SHADOW) {
+        const float4 n = __ldg(pc.nrm4 + v);
+        const float4* Nq = reinterpret_cast<const float4*>(pc.nmats) + 3u * node;
+        const float4 n0 = __ldg(Nq), n1 = __ldg(Nq + 1), n2 = __ldg(Nq + 2);
+        V3 tn;   // glm mat3 * vec3: (m0*x + m1*y) + m2*z   (primitive.vert:55)
+        tn.x = (n0.x * n.x + n0.w * n.y) + n1.z * n.z;
+        tn.y = (n0.y * n.x + n1.x * n.y) + n1.w * n.z;
+        tn.z = (n0.z * n.x + n1.y * n.y) + n2.x * n.z;
+        tn = normalize3(tn);
+        VtxBC bc;
+        bc.wx = world.x; bc.wy = world.y; bc.wz = world.z;
+        bc.invw = 1.0f / c.w;                       // Appendix B.10: q_k = b_k * (1 / w_k)
+        bc.nx = tn.x; bc.ny = tn.y; bc.nz = tn.z; bc.pad = 0.0f;
+        float4* o = reinterpret_cast<float4*>(pc.vtxBC + slot);
+        o[0] = make_float4(bc.wx, bc.wy, bc.wz, bc.invw);
+        o[1] = make_float4(bc.nx, bc.ny, bc.nz, bc.pad);
+    }
+}
+
+// Per-draw referenced vertex range (min, max index), computed when a draw list changes (not per frame).
+// ranges[2*d] = min, ranges[2*d+1] = max; initialised to (0xFFFFFFFF, 0) by the caller.
+__global__ void __launch_bounds__(256) k_draw_ranges(const uint32_t* __restrict__ indices, const DrawDev* __restrict__ draws, uint32_t nDraws,
+                                                     uint32_t* __restrict__ ranges) {
+    const uint32_t d = blockIdx.y;
+    if (d >= nDraws) return;
+    const uint32_t off = draws[d].indexOffset, n = 3u * (draws[d + 1].firstTri - draws[d].firstTri);
+    uint32_t lo = 0xFFFFFFFFu, hi = 0u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t v = __ldg(indices + off + i);
+        lo = min(lo, v); hi = max(hi, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xFFFFFFFFu, lo, o));
+        hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, o));
+    }
+    if ((threadIdx.x & 31u) == 0 && lo <= hi) { atomicMin(&ranges[2 * d], lo); atomicMax(&ranges[2 * d + 1], hi); }
+}
+
+void launch_vertex(const PassConst& pc, bool shadow, cudaStream_t st) {
+    if (pc.cacheSize == 0) return;
+    const uint32_t grid = (pc.cacheSize + 255u) / 256u;
+    if (shadow) k_vertex<true><<<grid, 256, 0, st>>>(pc);
+    else k_vertex<false><<<grid, 256, 0, st>>>(pc);
+}
+
+void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st) {
+    if (nDraws == 0) return;
+    for (uint32_t d0 = 0; d0 < nDraws; d0 += 65535u) {
+        const uint32_t n = nDraws - d0 < 65535u ? nDraws - d0 : 65535u;
+        k_draw_ranges<<<dim3(32, n), 256, 0, st>>>(indices, draws + d0, n, ranges + 2 * (size_t)d0);
+    }
+}
+
+}  // namespace reb

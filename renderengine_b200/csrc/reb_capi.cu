@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -18,8 +19,12 @@ std::string g_createError;
 
 struct PassState {               // per pass kind: 0 = shadow, 1 = forward
     std::vector<reb_draw> draws; // last submitted list (host copy, for change detection and replay)
-    DrawDev* dDraws = nullptr; uint32_t drawCap = 0;
+    DrawDev* dDraws = nullptr; uint32_t drawCap = 0;   // nDraws + 1 records (sentinel last)
     uint32_t nDraws = 0, nTris = 0;
+    // post-transform vertex cache of this pass (K0 output)
+    VtxA* vtxA = nullptr; VtxBC* vtxBC = nullptr; size_t cacheCap = 0;
+    uint32_t cacheSize = 0, deindexed = 0;
+    bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
     bool pending = false;        // enqueued since the last overflow check
 };
 
@@ -151,28 +156,72 @@ int ensure_large(reb_ctx* ctx, uint32_t nTris) {
     return REB_OK;
 }
 
+// Draw-list preprocessing (runs when a list changes, not per frame — the reference does the analogous work in
+// RenderScene::Init: PopulateMeshDrawCalls / SortOpaqueMeshes, RenderScene.cpp:94-125): running primitive counters,
+// the vertex range every draw references (device reduction) and from it the layout of the post-transform cache.
 int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
     PassState& ps = ctx->pass[kind];
-    if (ps.draws.size() == n && (n == 0 || std::memcmp(ps.draws.data(), draws, n * sizeof(reb_draw)) == 0) && ps.dDraws) return REB_OK;
-    std::vector<DrawDev> dd(n);
+    if (ps.valid && ps.draws.size() == n && (n == 0 || std::memcmp(ps.draws.data(), draws, n * sizeof(reb_draw)) == 0)) return REB_OK;
+    ps.valid = false;
+    std::vector<DrawDev> dd((size_t)n + 1);
     uint64_t tri = 0;
     for (uint32_t i = 0; i < n; ++i) {
         if ((uint64_t)draws[i].indexOffset + draws[i].nbIndices > ctx->nIdx) return fail(ctx, REB_E_INVALID, "draw index range exceeds the index buffer");
         if (draws[i].sceneNode >= ctx->nNodes) return fail(ctx, REB_E_INVALID, "draw references an unknown scene node");
-        dd[i] = {draws[i].indexOffset, (uint32_t)tri, draws[i].materialRaw, draws[i].sceneNode};
+        dd[i] = {draws[i].indexOffset, (uint32_t)tri, draws[i].materialRaw, draws[i].sceneNode, 0, 0u, 0u, 0u};
         tri += draws[i].nbIndices / 3;
     }
-    if (tri >= 0xFFFFFFFFull) return fail(ctx, REB_E_INVALID, "more than 2^32-2 primitives in one pass");
-    if (n > ps.drawCap) {
-        CU(cudaStreamSynchronize(ctx->stream));
-        int rc = dev_alloc(ctx, &ps.dDraws, (size_t)std::max(n, 64u));
+    if (tri >= 0x55555555ull) return fail(ctx, REB_E_INVALID, "more than 2^32/3 primitives in one pass");
+    dd[n] = {0u, (uint32_t)tri, 0u, 0u, 0, 0u, 0u, 0u};
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (n + 1 > ps.drawCap) {
+        int rc = dev_alloc(ctx, &ps.dDraws, (size_t)std::max(n + 1, 64u));
         if (rc) return rc;
-        ps.drawCap = std::max(n, 64u);
+        ps.drawCap = std::max(n + 1, 64u);
     }
-    if (n) CU(cudaMemcpyAsync(ps.dDraws, dd.data(), n * sizeof(DrawDev), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ps.dDraws, dd.data(), dd.size() * sizeof(DrawDev), cudaMemcpyHostToDevice, ctx->stream));
+    // per-draw referenced vertex range
+    std::vector<uint32_t> ranges((size_t)n * 2);
+    if (n) {
+        for (uint32_t i = 0; i < n; ++i) { ranges[2 * i] = 0xFFFFFFFFu; ranges[2 * i + 1] = 0u; }
+        uint32_t* dRanges = nullptr;
+        CU(cudaMalloc(reinterpret_cast<void**>(&dRanges), ranges.size() * 4));
+        cudaError_t e = cudaMemcpyAsync(dRanges, ranges.data(), ranges.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) { launch_draw_ranges(ctx->indices, ps.dDraws, n, dRanges, ctx->stream); ctx->launches++; }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(ranges.data(), dRanges, ranges.size() * 4, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(dRanges);
+        if (e != cudaSuccess) return fail(ctx, REB_E_CUDA, std::string("draw range reduction: ") + cudaGetErrorString(e));
+    }
+    uint64_t cache = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t lo = ranges[2 * i], hi = ranges[2 * i + 1];
+        if (lo > hi) { dd[i].cacheBase = (uint32_t)std::min<uint64_t>(cache, 0xFFFFFFFFull); continue; }   // draw without primitives
+        if (hi >= ctx->nVerts) return fail(ctx, REB_E_INVALID, "an index of draw " + std::to_string(i) + " exceeds the vertex buffer");
+        dd[i].cacheBase = (uint32_t)std::min<uint64_t>(cache, 0xFFFFFFFFull);
+        dd[i].nCache = hi - lo + 1;
+        dd[i].cacheOffset = (int32_t)((int64_t)cache - (int64_t)lo);
+        cache += dd[i].nCache;
+    }
+    // Indexed cache when the draws' vertex ranges are (nearly) disjoint, as the reference's loader produces them
+    // (AssimpSceneLoader.cpp:198-261 appends a fresh vertex block per mesh); otherwise one slot per triangle corner.
+    const bool forceDeindexed = std::getenv("REB_FORCE_DEINDEXED") != nullptr;
+    ps.deindexed = (forceDeindexed || cache > 2 * ctx->nVerts + 65536ull || cache > 3 * tri || cache >= 0x7FFFFFFFull) ? 1u : 0u;
+    const uint64_t slots = ps.deindexed ? 3 * tri : cache;
+    if (ps.deindexed) for (uint32_t i = 0; i <= n; ++i) { dd[i].cacheBase = 3u * dd[i].firstTri; dd[i].cacheOffset = 0; }
+    else dd[n].cacheBase = (uint32_t)cache;
+    CU(cudaMemcpyAsync(ps.dDraws, dd.data(), dd.size() * sizeof(DrawDev), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));   // dd is a stack-lifetime staging buffer
+    if (slots > ps.cacheCap) {
+        int rc;
+        if ((rc = dev_alloc(ctx, &ps.vtxA, (size_t)slots))) return rc;
+        if (kind == 1 && (rc = dev_alloc(ctx, &ps.vtxBC, (size_t)slots))) return rc;
+        ps.cacheCap = (size_t)slots;
+    }
+    ps.cacheSize = (uint32_t)slots;
     ps.draws.assign(draws, draws + n);
     ps.nDraws = n; ps.nTris = (uint32_t)tri;
+    ps.valid = true;
     return REB_OK;
 }
 
@@ -182,7 +231,9 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     std::memcpy(pc.PV, kind == 0 ? ctx->SPV : ctx->PV, 64);
     pc.W = kind == 0 ? ctx->S : ctx->W; pc.H = kind == 0 ? ctx->S : ctx->H;
     pc.nTris = ps.nTris; pc.nDraws = ps.nDraws;
-    pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.transforms = ctx->transforms; pc.draws = ps.dDraws;
+    pc.cacheSize = ps.cacheSize; pc.deindexed = ps.deindexed;
+    pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.nrm4 = ctx->nrm4; pc.transforms = ctx->transforms; pc.nmats = ctx->nmats;
+    pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC;
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
@@ -205,6 +256,7 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
     if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
+    if (ps.nTris) { launch_vertex(pc, kind == 0, ctx->stream); ctx->launches++; }
     mark(1);
     if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->stream); ctx->launches++; }
     mark(2);
@@ -221,7 +273,7 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         std::memset(&sh, 0, sizeof sh);
         std::memcpy(sh.STR, ctx->SPV, 64);
         std::memcpy(sh.viewPos, ctx->viewPos, 12);
-        sh.nLights = ctx->nLights; sh.nrm4 = ctx->nrm4; sh.nmats = ctx->nmats;
+        sh.nLights = ctx->nLights;
         sh.materials = ctx->materials; sh.materialStride = ctx->materialStride; sh.nMaterials = ctx->nMaterials;
         sh.lights = ctx->lights; sh.lightStride = ctx->lightStride;
         const bool useShadow = ctx->shadowMap && ctx->shadowValid && ctx->haveShadowXf;

@@ -54,7 +54,8 @@ int reb_destroy(reb_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
                     ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount, ctx->tileStart,
-                    ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws};
+                    ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
+                    ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -73,7 +74,7 @@ int reb_upload_geometry(reb_ctx* ctx, const void* verts, uint64_t nVerts, const 
     if ((rc = dev_alloc(ctx, &ctx->nrm4, nVerts))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->indices, nIdx))) return rc;
     ctx->nVerts = nVerts; ctx->nIdx = nIdx;
-    ctx->pass[0].draws.clear(); ctx->pass[1].draws.clear();
+    ctx->pass[0].valid = ctx->pass[1].valid = false;
     if (nVerts) {
         float4* aos = nullptr;
         CU(cudaMalloc(reinterpret_cast<void**>(&aos), nVerts * 32));
@@ -98,6 +99,7 @@ int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
     if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->nmats, (size_t)nNodes * 12))) return rc;
     ctx->nNodes = nNodes;
+    ctx->pass[0].valid = ctx->pass[1].valid = false;   // draws are validated against the node count
     if (!nNodes) return REB_OK;
     std::vector<float> nm((size_t)nNodes * 12);
     for (uint32_t n = 0; n < nNodes; ++n) normal_matrix12(m + 16 * (size_t)n, &nm[12 * (size_t)n]);

@@ -1,8 +1,8 @@
 // reb_device.cuh — device-side types and exact-arithmetic helpers shared by the raster kernels.
 //
 // Bit-exactness contract: every fp32 operation on the coverage / depth /
-// shadow-lookup path is an individually rounded IEEE op in a fixed order.  This translation unit is
-// compiled with --fmad=false (no contraction), default -prec-div/-prec-sqrt (IEEE / and sqrtf).
+// shadow-lookup path is an individually rounded IEEE op in a fixed order.  These translation units
+// are compiled with --fmad=false (no contraction), default -prec-div/-prec-sqrt (IEEE / and sqrtf).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -15,12 +15,27 @@ constexpr float GUARD_PX = 1048576.0f;                            // |x_f|,|y_f|
 constexpr int TILE_W = 32, TILE_H = 8;                            // one CTA (256 threads) per screen tile
 constexpr int HUGE_TILES = 256;                                   // bbox covering more tiles than this: broadcast list
 constexpr int HUGE_CAP = 64;                                      // capacity of the broadcast list (overflow -> binned path)
-constexpr int SMALL_MAX = 8;                                      // bbox <= 8x8 pixel centres: per-thread raster
+constexpr int SMALL_MAX = 8;                                      // bbox spans <= 8 px: rasterised inside the setup kernel
 constexpr uint32_t LIGHT_TYPE_DIRECTIONAL = 1, LIGHT_TYPE_SPOT = 3;   // phong.glsl:16-18
 
-// One vkCmdDrawIndexed of the reference's draw loops, with the running primitive counter
-// (Appendix B.9) precomputed on the host.
-struct DrawDev { uint32_t indexOffset, firstTri, material, node; };
+// Post-transform vertex flags (VtxA.flags): bits 0-5 = outside x<-w, x>w, y<-w, y>w, z<0, z>w (Appendix B.2);
+// bit 6 = !(w > 0); bit 7 = outside the guard band (Appendix B.3).
+constexpr uint32_t VF_PLANES = 0x3Fu, VF_NEEDS_CLIP = 0xC0u, VF_W = 0x40u, VF_GUARD = 0x80u;
+
+// One vkCmdDrawIndexed of the reference's draw loops (MeshDrawInfo, MeshAllocator.h:35-39) with the
+// running primitive counter (Appendix B.9) and its slice of the post-transform vertex cache
+// precomputed on the host.  The array holds nDraws + 1 records; the last one is a sentinel
+// (firstTri = nTris, cacheBase = cacheSize).
+struct __align__(16) DrawDev {
+    uint32_t indexOffset, firstTri, material, node;
+    int32_t cacheOffset;          // cache slot of vertex v of this draw = v + cacheOffset (indexed mode)
+    uint32_t cacheBase, nCache, pad;
+};
+
+// Post-transform vertex cache.  VtxA is all the setup kernel needs (one 16-B gather per corner);
+// VtxBC (one 32-B sector) carries what shading interpolates.
+struct __align__(16) VtxA { int32_t X, Y; float z; uint32_t flags; };      // snapped 24.8 position, ndc depth
+struct __align__(16) VtxBC { float wx, wy, wz, invw, nx, ny, nz, pad; };    // world position, 1/w_clip, normalised normal
 
 // A triangle that goes through the binned tile path: snapped vertices + depth + id (48 B, 3 x 16 B).
 struct __align__(16) LargeRec {
@@ -33,10 +48,16 @@ struct PassConst {
     float PV[16];                 // proj*view (forward) or shadowProj*shadowView (shadow), column-major
     uint32_t W, H;                // target extent of this pass
     uint32_t nTris, nDraws;
+    uint32_t cacheSize;           // number of post-transform cache slots
+    uint32_t deindexed;           // 1: cache slot = 3*tri + corner (fallback when draws share vertices sparsely)
     const uint32_t* indices;
     const float4* pos4;           // (x, y, z, u)
+    const float4* nrm4;           // (nx, ny, nz, v)
     const float* transforms;      // 16 floats per node
-    const DrawDev* draws;
+    const float* nmats;           // 12 floats per node: transpose(inverse(mat3(T))), column-major 3x3 + pad
+    const DrawDev* draws;         // nDraws + 1
+    VtxA* vtxA;
+    VtxBC* vtxBC;                 // forward only
     unsigned long long* vis;      // forward: W*H 64-bit keys
     uint32_t* depthBits;          // shadow: S*S depth bits (the shadow map itself)
     LargeRec* large; uint32_t largeCap;
@@ -83,76 +104,67 @@ __device__ __forceinline__ float4 vertex_stage(const float* __restrict__ PV, con
     return mat4_mul_point(PV, w.x, w.y, w.z);
 }
 
-enum SetupResult { SR_KEEP = 0, SR_REJECT = 1, SR_NEEDS_CLIP = 2, SR_CULLED = 3, SR_NO_SAMPLE = 4 };
-
-struct Snapped {
-    int32_t X[3], Y[3];
-    float z[3], w[3];
-    long long A2;
-    int32_t x0, x1, y0, y1;
-    int32_t spanX, spanY;   // unclamped sub-pixel extents
-};
-
-// Appendix B.2-B.6: trivial reject, viewport, snap (8 sub-pixel bits, round-half-even), facing, bbox.
-__device__ __forceinline__ SetupResult setup_triangle(const float4 c[3], uint32_t W, uint32_t H, Snapped& s) {
-    bool allL = true, allR = true, allT = true, allB = true, allN = true, allF = true;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        allL = allL && (c[k].x < -c[k].w); allR = allR && (c[k].x > c[k].w);
-        allT = allT && (c[k].y < -c[k].w); allB = allB && (c[k].y > c[k].w);
-        allN = allN && (c[k].z < 0.0f);    allF = allF && (c[k].z > c[k].w);
-    }
-    if (allL || allR || allT || allB || allN || allF) return SR_REJECT;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) if (!(c[k].w > 0.0f)) return SR_NEEDS_CLIP;
+// Appendix B.2-B.5 for one vertex: clip-plane outcodes, viewport transform, snap to 24.8 (round-half-even).
+__device__ __forceinline__ VtxA viewport_snap(float4 c, uint32_t W, uint32_t H) {
+    VtxA a;
+    uint32_t f = 0;
+    f |= (c.x < -c.w) ? 1u : 0u;  f |= (c.x > c.w) ? 2u : 0u;
+    f |= (c.y < -c.w) ? 4u : 0u;  f |= (c.y > c.w) ? 8u : 0u;
+    f |= (c.z < 0.0f) ? 16u : 0u; f |= (c.z > c.w) ? 32u : 0u;
+    if (!(c.w > 0.0f)) { a.X = 0; a.Y = 0; a.z = 0.0f; a.flags = f | VF_W; return a; }
     const float hw = 0.5f * (float)W, hh = 0.5f * (float)H;
-    bool guard = false;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        float nx = c[k].x / c[k].w, ny = c[k].y / c[k].w, nz = c[k].z / c[k].w;
-        float xf = hw * nx + hw;
-        float yf = hh * ny + hh;
-        guard = guard || !(fabsf(xf) <= GUARD_PX) || !(fabsf(yf) <= GUARD_PX);
-        s.X[k] = __float2int_rn(xf * 256.0f);
-        s.Y[k] = __float2int_rn(yf * 256.0f);
-        s.z[k] = nz;
-        s.w[k] = c[k].w;
-    }
-    if (guard) return SR_NEEDS_CLIP;
-    s.A2 = (long long)(s.X[1] - s.X[0]) * (long long)(s.Y[2] - s.Y[0]) - (long long)(s.X[2] - s.X[0]) * (long long)(s.Y[1] - s.Y[0]);
-    if (s.A2 >= 0) return SR_CULLED;
-    int32_t minX = min(s.X[0], min(s.X[1], s.X[2])), maxX = max(s.X[0], max(s.X[1], s.X[2]));
-    int32_t minY = min(s.Y[0], min(s.Y[1], s.Y[2])), maxY = max(s.Y[0], max(s.Y[1], s.Y[2]));
-    s.spanX = maxX - minX; s.spanY = maxY - minY;
-    s.x0 = max((minX + 127) >> 8, 0);
-    s.x1 = min((maxX - 128) >> 8, (int32_t)W - 1);
-    s.y0 = max((minY + 127) >> 8, 0);
-    s.y1 = min((maxY - 128) >> 8, (int32_t)H - 1);
-    if (s.x0 > s.x1 || s.y0 > s.y1) return SR_NO_SAMPLE;
-    return SR_KEEP;
+    const float nx = c.x / c.w, ny = c.y / c.w, nz = c.z / c.w;
+    const float xf = hw * nx + hw;
+    const float yf = hh * ny + hh;
+    if (!(fabsf(xf) <= GUARD_PX) || !(fabsf(yf) <= GUARD_PX)) { a.X = 0; a.Y = 0; a.z = nz; a.flags = f | VF_GUARD; return a; }
+    a.X = __float2int_rn(xf * 256.0f);
+    a.Y = __float2int_rn(yf * 256.0f);
+    a.z = nz;
+    a.flags = f;
+    return a;
 }
 
-// Appendix B.8: depth from the unbiased edge values of vertices 1 and 2 (exact integers as floats).
-__device__ __forceinline__ float depth_from(float fF1, float fF2, float area, float z0, float z1, float z2) {
+// Appendix B.8: depth from the unbiased edge values of vertices 1 and 2 (dz1 = z1 - z0, dz2 = z2 - z0).
+__device__ __forceinline__ float depth_from(float fF1, float fF2, float area, float z0, float dz1, float dz2) {
     float b1 = fF1 / area;
     float b2 = fF2 / area;
-    float z = (z0 + b1 * (z1 - z0)) + b2 * (z2 - z0);
+    float z = (z0 + b1 * dz1) + b2 * dz2;
     if (z == 0.0f) z = 0.0f;
     return z;
 }
 
-// binary search: last d with firstTri[d] <= tri
-__device__ __forceinline__ uint32_t find_draw(const DrawDev* __restrict__ draws, uint32_t nDraws, uint32_t tri) {
+// binary search: last d in [0, nDraws) with key(d) <= v, where key = firstTri (BY_CACHE = false) or cacheBase
+template <bool BY_CACHE>
+__device__ __forceinline__ uint32_t draw_key(const DrawDev* __restrict__ draws, uint32_t d) {
+    return BY_CACHE ? __ldg(&draws[d].cacheBase) : __ldg(&draws[d].firstTri);
+}
+template <bool BY_CACHE>
+__device__ __forceinline__ uint32_t find_draw(const DrawDev* __restrict__ draws, uint32_t nDraws, uint32_t v) {
     uint32_t lo = 0, hi = nDraws;
     while (hi - lo > 1) {
         uint32_t mid = (lo + hi) >> 1;
-        if (__ldg(&draws[mid].firstTri) <= tri) lo = mid; else hi = mid;
+        if (draw_key<BY_CACHE>(draws, mid) <= v) lo = mid; else hi = mid;
     }
     return lo;
+}
+// CTA-cooperative variant for 256 consecutive keys starting at `first`: one search per CTA, then a short walk.
+// Relies on the sentinel record draws[nDraws] whose key is the exclusive upper bound.  Contains a __syncthreads.
+template <bool BY_CACHE>
+__device__ __forceinline__ uint32_t find_draw_cta(const DrawDev* __restrict__ draws, uint32_t nDraws, uint32_t first, uint32_t v, uint32_t* sBase) {
+    if (threadIdx.x == 0) *sBase = find_draw<BY_CACHE>(draws, nDraws, first);
+    __syncthreads();
+    uint32_t d = *sBase;
+    while (d + 1 < nDraws && draw_key<BY_CACHE>(draws, d + 1) <= v) ++d;
+    return d;
 }
 
 __device__ __forceinline__ bool row_owned(uint32_t y, uint32_t rank, uint32_t nRanks, uint32_t bandH) {
     return nRanks <= 1 || ((y / bandH) % nRanks) == rank;
+}
+
+// cache slot of corner k of triangle `tri` whose vertex index is v
+__device__ __forceinline__ uint32_t cache_slot(const PassConst& pc, int32_t cacheOffset, uint32_t tri, uint32_t k, uint32_t v) {
+    return pc.deindexed ? 3u * tri + k : (uint32_t)((int32_t)v + cacheOffset);
 }
 
 }  // namespace reb

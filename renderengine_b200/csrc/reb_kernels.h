@@ -9,8 +9,6 @@ namespace reb {
 struct ShadeConst {
     float STR[16];                 // shadowProj*shadowView (ShadowSystem.cpp:303)
     float viewPos[3]; uint32_t nLights;
-    const float4* nrm4;            // (nx, ny, nz, v)
-    const float* nmats;            // 12 floats per node: transpose(inverse(mat3(T))), column-major 3x3 + pad
     const uint8_t* materials; uint32_t materialStride; uint32_t nMaterials;
     const uint8_t* lights; uint32_t lightStride;
     const float* shadowMap; uint32_t shadowSize;   // NULL / 0: shadow = 0
@@ -19,6 +17,8 @@ struct ShadeConst {
     uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;
 };
 
+void launch_vertex(const PassConst& pc, bool shadow, cudaStream_t st);
+void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, cudaStream_t st);
 void launch_bin_count(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
                       int numSMs, cudaStream_t st);
