@@ -253,9 +253,9 @@ def main():
         V = scene["n_vertices"]
         # algorithmic bytes owned by each kernel; their sum is B_shadow + B_forward of SURVEY.md §8d
         alg = {
-            (0, "clear"): 0, (0, "setup_raster"): 12 * V + 12 * T, (0, "tile_stage"): 4 * S * S,
-            (1, "setup_raster"): 12 * V + 12 * T,
-            (1, "tile_stage"): 20 * V + (min(36 * W * H, 4 * S * S) if S else 0) + 12 * W * H,
+            (0, "clear"): 0, (0, "vertex"): 12 * V, (0, "setup_raster"): 12 * T, (0, "bin_scatter"): 0, (0, "tile_stage"): 4 * S * S,
+            (1, "vertex"): 32 * V, (1, "setup_raster"): 12 * T, (1, "bin_scatter"): 0,
+            (1, "tile_stage"): (min(36 * W * H, 4 * S * S) if S else 0) + 12 * W * H,
         }
         kt = {f"{'shadow' if k == 0 else 'forward'}.{n}": v for k in (0, 1) for n, v in acc[k].items()}
         dom = max(((k, n) for k in (0, 1) for n in acc[k]), key=lambda kn: acc[kn[0]][kn[1]])

@@ -112,7 +112,7 @@ int reb_get_counters(reb_ctx* ctx, uint64_t* counters4);
 int reb_get_launch_count(reb_ctx* ctx, uint64_t* out);
 
 /* per-kernel device timing of the last enqueued pass (0 = shadow, 1 = forward), CUDA events on the
- * context stream: ms6 = { clear, setup+small raster, bin count, tile scan, bin scatter, tile stage } */
+ * context stream: ms6 = { clear, vertex stage, setup + small raster, bin scatter, tile stage, 0 } */
 int reb_set_profiling(reb_ctx* ctx, int on);
 int reb_get_kernel_times(reb_ctx* ctx, int pass, float* ms6);
 

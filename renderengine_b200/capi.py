@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libreb.so")
+LIB_PATH = os.environ.get("REB_LIB") or os.path.join(HERE, "libreb.so")   # REB_LIB: A/B-testing of kernel build variants
 
 REB_OUT_COLOR_SRGB8, REB_OUT_COLOR_F32, REB_OUT_DEPTH_F32, REB_OUT_TRIID_U32 = 1, 2, 4, 8
 REB_COLOR_SRGB8, REB_COLOR_F32, REB_DEPTH_F32, REB_TRIID_U32, REB_SHADOW_F32 = 0, 1, 2, 3, 4
@@ -199,7 +199,7 @@ class Context:
         self._ck(self.lib.reb_get_counters(self.h, _ptr(c)))
         return c
 
-    KERNEL_SLOTS = ("clear", "setup_raster", "bin_count", "tile_scan", "bin_scatter", "tile_stage")
+    KERNEL_SLOTS = ("clear", "vertex", "setup_raster", "bin_scatter", "tile_stage", "unused")
 
     def set_profiling(self, on):
         self._ck(self.lib.reb_set_profiling(self.h, int(on)))
@@ -207,7 +207,7 @@ class Context:
     def kernel_times_ms(self, pass_kind):
         t = np.zeros(6, np.float32)
         self._ck(self.lib.reb_get_kernel_times(self.h, pass_kind, _ptr(t)))
-        return dict(zip(self.KERNEL_SLOTS, (float(x) for x in t)))
+        return {k: float(x) for k, x in zip(self.KERNEL_SLOTS, t) if k != "unused"}
 
     def launch_count(self):
         n = C.c_uint64()

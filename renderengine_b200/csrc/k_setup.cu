@@ -1,10 +1,10 @@
-// k_setup.cu — K1: vertex transform + triangle setup + small-triangle raster; compaction of the
-// remaining ("large") triangles for the binned tile path; K2: tile binning (count / scan / scatter).
+// k_setup.cu — K1: triangle setup + small-triangle raster + large-triangle tile counting;
+// K2: scatter of the large triangles into per-tile lists; clears; AoS -> SoA split.
 //
-// Replaces, for the hot path, the vertex stage and fixed-function front end that the reference
-// reaches through vkCmdDrawIndexed (MaterialSystem.cpp:99, ShadowSystem.cpp:369) with the state of
-// GraphicsPipelineCache.cpp:257-365: shadow_map.vert:48-52 / primitive.vert:49-53, viewport, cull
-// back + CCW front (F5), 1 sample per pixel, LessOrEqual depth.
+// Replaces, for the hot path, the fixed-function front end that the reference reaches through
+// vkCmdDrawIndexed (MaterialSystem.cpp:99, ShadowSystem.cpp:369) with the state of
+// GraphicsPipelineCache.cpp:257-365: viewport, cull back + CCW front (F5), 1 sample per pixel,
+// LessOrEqual depth.  The vertex stage itself is k_vertex.cu.
 #include "reb_device.cuh"
 #include "reb_kernels.h"
 #include <algorithm>
@@ -12,263 +12,357 @@
 namespace reb {
 
 // ---------------------------------------------------------------------------------------------
-// K1: triangle setup + small-triangle raster.  256 triangles per CTA, two phases.
-//
-// Phase 1, one thread per triangle: 3 indices + 3 VtxA gathers (16 B each) from the post-transform
-//   cache, clip-flag logic, facing (int64 shoelace), pixel-centre bbox, classification:
-//     small  (spans <= SMALL_MAX px)  -> compacted into shared memory as 32-bit edge equations,
-//     huge   (> HUGE_TILES tiles)     -> short broadcast list tested by every tile,
-//     large  (everything else)        -> warp-aggregated append to the LargeRec queue (binned path).
-//   Compaction = warp ballot + shuffle scan + one shared-memory pass over the 8 warp totals; the same
-//   scan carries the number of pixel rows of every small triangle.
-// Phase 2, one thread per (small triangle, pixel row) work item: back-face-culled and clipped lanes
-//   no longer idle through the raster loop, and lanes of a warp walk rows of near-equal width.
-//   Coverage = three incrementally updated 32-bit edge functions with the top-left bias folded in;
-//   covered samples resolve with one 64-bit atomicMin (key = depthBits<<32 | ~triId; shadow pass:
-//   32-bit atomicMin on the depth bits, which are the shadow map itself).
+// Tile walk of one large triangle by one warp: lanes stride over the TILE_W x TILE_H tiles of its
+// bbox; a tile is skipped when it lies entirely outside one edge (edge function evaluated at the
+// tile's most-interior pixel centre for that edge).  SCATTER = false counts (inside K1),
+// SCATTER = true writes the triangle's queue slot into the per-tile lists (K2).
+// All arguments are warp-uniform.
 // ---------------------------------------------------------------------------------------------
-constexpr int K1_THREADS = 256;
-constexpr int K1_MAX_ROWS = K1_THREADS * (SMALL_MAX + 1);
-
-struct K1Shared {
-    int32_t Ax[3][K1_THREADS];      // 256 * A_k  (step of the biased edge function per pixel in x)
-    int32_t By[3][K1_THREADS];      // 256 * B_k  (step per pixel in y)
-    int32_t C[3][K1_THREADS];       // biased edge value at the bbox origin's pixel centre
-    uint32_t xy[K1_THREADS];        // x0 | y0 << 16
-    uint32_t whb[K1_THREADS];       // w | h << 8 | bias1 << 16 | bias2 << 17
-    float z0[K1_THREADS], dz1[K1_THREADS], dz2[K1_THREADS], area[K1_THREADS];
-    uint32_t idKey[K1_THREADS];
-    uint32_t rowStart[K1_THREADS];
-    uint32_t warpTot[K1_THREADS / 32];
-    uint32_t drawBase;
-    uint8_t itemTri[K1_MAX_ROWS];
-};
-
-template <bool SHADOW>
-__global__ void __launch_bounds__(K1_THREADS) k_setup_raster(const __grid_constant__ PassConst pc) {
-    __shared__ K1Shared sm;
-    const uint32_t firstTri = blockIdx.x * K1_THREADS;
-    const uint32_t tri = firstTri + threadIdx.x;
-    const bool valid = tri < pc.nTris;
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-
-    const uint32_t d = find_draw_cta<false>(pc.draws, pc.nDraws, firstTri, valid ? tri : firstTri, &sm.drawBase);
-    bool keep = false, needsClip = false;
-    VtxA a0, a1, a2;
-    long long A2 = 0;
-    int32_t x0 = 0, x1 = -1, y0 = 0, y1 = -1, spanX = 0, spanY = 0;
-    if (valid) {
-        const uint4 dr = __ldg(reinterpret_cast<const uint4*>(pc.draws + d));        // indexOffset, firstTri, material, node
-        const int32_t cacheOffset = __ldg(&pc.draws[d].cacheOffset);
-        const uint32_t* ix = pc.indices + dr.x + 3u * (tri - dr.y);
-        const uint32_t i0 = __ldg(ix), i1 = __ldg(ix + 1), i2 = __ldg(ix + 2);
-        const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
-        const uint4 q0 = __ldg(va + cache_slot(pc, cacheOffset, tri, 0, i0));
-        const uint4 q1 = __ldg(va + cache_slot(pc, cacheOffset, tri, 1, i1));
-        const uint4 q2 = __ldg(va + cache_slot(pc, cacheOffset, tri, 2, i2));
-        a0 = {(int32_t)q0.x, (int32_t)q0.y, __uint_as_float(q0.z), q0.w};
-        a1 = {(int32_t)q1.x, (int32_t)q1.y, __uint_as_float(q1.z), q1.w};
-        a2 = {(int32_t)q2.x, (int32_t)q2.y, __uint_as_float(q2.z), q2.w};
-        const bool reject = (a0.flags & a1.flags & a2.flags & VF_PLANES) != 0u;             // Appendix B.2
-        needsClip = !reject && ((a0.flags | a1.flags | a2.flags) & VF_NEEDS_CLIP) != 0u;    // Appendix B.3
-        if (!reject && !needsClip) {
-            A2 = (long long)(a1.X - a0.X) * (long long)(a2.Y - a0.Y) - (long long)(a2.X - a0.X) * (long long)(a1.Y - a0.Y);
-            if (A2 < 0) {                                                                   // Appendix B.6: front = CCW = A2 < 0
-                const int32_t minX = min(a0.X, min(a1.X, a2.X)), maxX = max(a0.X, max(a1.X, a2.X));
-                const int32_t minY = min(a0.Y, min(a1.Y, a2.Y)), maxY = max(a0.Y, max(a1.Y, a2.Y));
-                spanX = maxX - minX; spanY = maxY - minY;
-                x0 = max((minX + 127) >> 8, 0); x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
-                y0 = max((minY + 127) >> 8, 0); y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
-                keep = x0 <= x1 && y0 <= y1;
-            }
-        }
-    }
-    if (needsClip) atomicAdd(&pc.status[1], 1u);
-
-    const bool isSmall = keep && spanX <= SMALL_MAX * 256 && spanY <= SMALL_MAX * 256;   // unclamped spans keep the 32-bit edge math exact
-    bool isLarge = keep && !isSmall;
-    if (isLarge) {
-        // screen-filling triangles go to a short broadcast list that every tile tests (no per-tile atomics)
-        const int ntiles = (x1 / TILE_W - x0 / TILE_W + 1) * (y1 / TILE_H - y0 / TILE_H + 1);
-        if (ntiles > HUGE_TILES) {
-            const uint32_t slot = atomicAdd(&pc.status[4], 1u);
-            if (slot < (uint32_t)HUGE_CAP) {
-                LargeRec r;
-                r.X0 = a0.X; r.Y0 = a0.Y; r.X1 = a1.X; r.Y1 = a1.Y;
-                r.X2 = a2.X; r.Y2 = a2.Y; r.z0 = a0.z; r.z1 = a1.z;
-                r.z2 = a2.z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
-                pc.huge[slot] = r;
-                isLarge = false;
-            }
-        }
-    }
-
-    // warp-aggregated append of large triangles to the global queue
-    const unsigned lmask = __ballot_sync(0xFFFFFFFFu, isLarge);
-    if (lmask) {
-        const int leader = __ffs(lmask) - 1;
-        uint32_t base = 0;
-        if ((int)lane == leader) base = atomicAdd(&pc.status[0], (uint32_t)__popc(lmask));
-        base = __shfl_sync(0xFFFFFFFFu, base, leader);
-        if (isLarge) {
-            const uint32_t slot = base + __popc(lmask & ((1u << lane) - 1u));
-            if (slot < pc.largeCap) {
-                LargeRec r;
-                r.X0 = a0.X; r.Y0 = a0.Y; r.X1 = a1.X; r.Y1 = a1.Y;
-                r.X2 = a2.X; r.Y2 = a2.Y; r.z0 = a0.z; r.z1 = a1.z;
-                r.z2 = a2.z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
-                pc.large[slot] = r;
-            } else {
-                atomicOr(&pc.status[2], OVF_LARGE);
-            }
-        }
-    }
-
-    // CTA compaction of small triangles: packed scan of (count, rows) = 1 | h << 16
-    const uint32_t h = isSmall ? (uint32_t)(y1 - y0 + 1) : 0u;
-    const uint32_t mine = isSmall ? (1u | (h << 16)) : 0u;
-    uint32_t incl = mine;
+template <bool SCATTER>
+__device__ __noinline__ void tile_walk(const PassConst& pc, int32_t X0, int32_t Y0, int32_t X1, int32_t Y1, int32_t X2, int32_t Y2,
+                                          uint32_t queueSlot, unsigned lane) {
+    const int32_t X[3] = {X0, X1, X2}, Y[3] = {Y0, Y1, Y2};
+    const int32_t minX = min(X0, min(X1, X2)), maxX = max(X0, max(X1, X2));
+    const int32_t minY = min(Y0, min(Y1, Y2)), maxY = max(Y0, max(Y1, Y2));
+    const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int)pc.W - 1);
+    const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int)pc.H - 1);
+    const int tx0 = x0 / TILE_W, tx1 = x1 / TILE_W, ty0 = y0 / TILE_H, ty1 = y1 / TILE_H;
+    const int tw = tx1 - tx0 + 1, n = tw * (ty1 - ty0 + 1);
+    long long A[3], B[3], C[3];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= (unsigned)o) incl += n; }
-    if (lane == 31) sm.warpTot[warp] = incl;
-    __syncthreads();
-    uint32_t base = 0, total = 0;
-#pragma unroll
-    for (int wgt = 0; wgt < K1_THREADS / 32; ++wgt) { const uint32_t t = sm.warpTot[wgt]; if (wgt < (int)warp) base += t; total += t; }
-    const uint32_t nRows = total >> 16;
-    if (nRows == 0) return;   // CTA-uniform
-    if (isSmall) {
-        const uint32_t excl = base + incl - mine;
-        const uint32_t slot = excl & 0xFFFFu, row0 = excl >> 16;
-        const int32_t X[3] = {a0.X, a1.X, a2.X}, Y[3] = {a0.Y, a1.Y, a2.Y};
-        const int32_t Px = 256 * x0 + 128, Py = 256 * y0 + 128;
-        uint32_t biasBits = 0;
+    for (int k = 0; k < 3; ++k) {
+        const int a = (k + 1) % 3, b = (k + 2) % 3;
+        A[k] = (long long)Y[b] - Y[a];
+        B[k] = -((long long)X[b] - X[a]);
+        C[k] = -(A[k] * X[a]) - B[k] * Y[a];
+    }
+    for (int i = (int)lane; i < n; i += 32) {
+        const int tx = tx0 + i % tw, ty = ty0 + i / tw;
+        if (pc.nRanks > 1 && !row_owned((uint32_t)(ty * TILE_H), pc.rank, pc.nRanks, pc.bandH)) continue;
+        const long long cx0 = 256ll * (tx * TILE_W) + 128, cx1 = 256ll * (tx * TILE_W + TILE_W - 1) + 128;
+        const long long cy0 = 256ll * (ty * TILE_H) + 128, cy1 = 256ll * (ty * TILE_H + TILE_H - 1) + 128;
+        bool outside = false;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            const int a = (k + 1) % 3, b = (k + 2) % 3;     // edge a->b opposes vertex k
-            const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
-            const int32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
-            sm.Ax[k][slot] = 256 * A;
-            sm.By[k][slot] = 256 * B;
-            sm.C[k][slot] = A * (Px - X[a]) + B * (Py - Y[a]) - bias;
-            if (k > 0) biasBits |= (uint32_t)bias << (15 + k);
+            const long long Fmax = A[k] * (A[k] > 0 ? cx1 : cx0) + B[k] * (B[k] > 0 ? cy1 : cy0) + C[k];
+            outside = outside || (Fmax < 0);
         }
-        sm.xy[slot] = (uint32_t)x0 | ((uint32_t)y0 << 16);
-        sm.whb[slot] = (uint32_t)(x1 - x0 + 1) | (h << 8) | biasBits;
-        sm.z0[slot] = a0.z; sm.dz1[slot] = a1.z - a0.z; sm.dz2[slot] = a2.z - a0.z;
-        sm.area[slot] = (float)(-A2);
-        sm.idKey[slot] = ~tri;
-        sm.rowStart[slot] = row0;
-        for (uint32_t j = 0; j < h; ++j) sm.itemTri[row0 + j] = (uint8_t)slot;
-    }
-    __syncthreads();
-
-    for (uint32_t item = threadIdx.x; item < nRows; item += K1_THREADS) {
-        const uint32_t t = sm.itemTri[item];
-        const uint32_t j = item - sm.rowStart[t];
-        const uint32_t xy = sm.xy[t], whb = sm.whb[t];
-        const uint32_t y = (xy >> 16) + j;
-        if (!SHADOW && !row_owned(y, pc.rank, pc.nRanks, pc.bandH)) continue;
-        const int32_t s0 = sm.Ax[0][t], s1 = sm.Ax[1][t], s2 = sm.Ax[2][t];
-        int32_t F0 = sm.C[0][t] + (int32_t)j * sm.By[0][t];
-        int32_t F1 = sm.C[1][t] + (int32_t)j * sm.By[1][t];
-        int32_t F2 = sm.C[2][t] + (int32_t)j * sm.By[2][t];
-        const uint32_t w = whb & 0xFFu;
-        const size_t rowBase = (size_t)y * pc.W + (xy & 0xFFFFu);
-        for (uint32_t i = 0; i < w; ++i, F0 += s0, F1 += s1, F2 += s2) {
-            if ((F0 | F1 | F2) < 0) continue;
-            const float z = depth_from((float)(F1 + (int32_t)((whb >> 16) & 1u)), (float)(F2 + (int32_t)((whb >> 17) & 1u)),
-                                       sm.area[t], sm.z0[t], sm.dz1[t], sm.dz2[t]);
-            if (!(z >= 0.0f && z <= 1.0f)) continue;
-            if (SHADOW) atomicMin(pc.depthBits + rowBase + i, __float_as_uint(z));
-            else atomicMin(pc.vis + rowBase + i, ((unsigned long long)__float_as_uint(z) << 32) | sm.idKey[t]);
+        if (outside) continue;
+        const uint32_t tile = (uint32_t)ty * pc.tilesX + (uint32_t)tx;
+        if (!SCATTER) {
+            atomicAdd(&pc.tileCount[tile], 1u);
+        } else {
+            const uint32_t slot = pc.tileStart[tile] + atomicAdd(&pc.tileCount[tile], 1u);
+            if (slot < pc.listCap) pc.tileList[slot] = queueSlot;
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: bin the large triangles into TILE_W x TILE_H screen tiles.  One warp per triangle, lanes
-// stride over the tiles of its bbox; a tile is skipped when it lies entirely outside one edge
-// (evaluated at the tile's most-interior corner for that edge).  SCATTER=false counts,
-// SCATTER=true writes triangle slots into the per-tile lists laid out by the scan.
+// K1: persistent CTAs of 256 threads, one triangle per thread per block of 256 triangles.
+//
+// Phase 1, per triangle: 3 indices + 3 VtxA gathers (16 B each) from the post-transform cache,
+//   clip-flag logic, facing (int64 shoelace), pixel-centre bbox, classification:
+//     small  (spans <= SMALL_MAX px)  -> compacted into shared memory as 32-bit edge equations,
+//     huge   (> HUGE_TILES tiles)     -> short broadcast list tested by every tile,
+//     large  (everything else)        -> warp-aggregated append to the LargeRec queue; the warp then
+//                                        walks the triangle's tiles and bumps the per-tile counts.
+//   Compaction = warp shuffle scan of a packed (count, rows) word + one pass over the 8 warp totals.
+// Phase 2, one thread per (small triangle, pixel row) work item: back-face-culled and clipped lanes
+//   no longer idle through the raster loop.  Coverage of the row (three incrementally updated 32-bit
+//   edge functions, top-left bias folded in) is first collected into a bit mask with no divergent
+//   branch, then only the covered samples evaluate depth (two IEEE divides) and resolve with one
+//   atomicMin: 64-bit key depthBits<<32 | ~triId into the visibility buffer (forward), or the 32-bit
+//   depth bits into the shadow map itself (shadow).
+// Tail: the last CTA to finish lays out the per-tile lists (start = running cursor; no ordered scan is
+//   needed because list order inside a tile is irrelevant to the min-key resolve).
 // ---------------------------------------------------------------------------------------------
-template <bool SCATTER>
-__global__ void __launch_bounds__(256) k_bin_large(const __grid_constant__ PassConst pc, uint32_t* __restrict__ tileCount,
-                                                   const uint32_t* __restrict__ tileStart, uint32_t* __restrict__ tileList, uint32_t listCap) {
+constexpr int K1_THREADS = 256;
+constexpr int K1_TRIS = 256;
+constexpr int K1_WARPS = K1_THREADS / 32;
+constexpr int K1_MAX_ROWS = K1_TRIS * (SMALL_MAX + 1);
+constexpr int K1_WQ = 32 * (SMALL_MAX + 1);      // pixel-queue entries per warp: 32 rows x 9 samples
+
+struct K1Shared {
+    int32_t Ax[3][K1_TRIS];         // 256 * A_k  (step of the edge function per pixel in x)
+    int32_t By[3][K1_TRIS];         // 256 * B_k  (step per pixel in y)
+    int32_t C[3][K1_TRIS];          // unbiased edge value at the bbox origin's pixel centre
+    uint32_t xy[K1_TRIS];           // x0 | y0 << 16
+    uint32_t whb[K1_TRIS];          // w | h << 8 | top-left bias of edge k << (16 + k)
+    float z0[K1_TRIS], dz1[K1_TRIS], dz2[K1_TRIS], area[K1_TRIS];
+    uint32_t idKey[K1_TRIS];
+    uint16_t rowStart[K1_TRIS];
+    uint16_t itemTri[K1_MAX_ROWS];
+    uint16_t pixq[K1_WARPS][K1_WQ]; // per-warp queue of covered samples: slot | i << 8 | j << 12
+    uint32_t warpTot[K1_WARPS];
+    uint32_t nextBlk, cursor, isLast;
+};
+
+struct K1Tri {
+    VtxA a[3];
+    long long A2;
+    int32_t x0, x1, y0, y1;
+    bool isSmall, isLarge;
+};
+
+__device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, const uint4 q[3], K1Tri& t) {
+    t.isSmall = t.isLarge = false;
+    t.A2 = 0; t.x0 = t.y0 = 0; t.x1 = t.y1 = -1;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) t.a[k] = {(int32_t)q[k].x, (int32_t)q[k].y, __uint_as_float(q[k].z), q[k].w};
+    if (!valid) return;
+    const uint32_t f0 = t.a[0].flags, f1 = t.a[1].flags, f2 = t.a[2].flags;
+    if ((f0 & f1 & f2 & VF_PLANES) != 0u) return;                                   // Appendix B.2 trivial reject
+    if (((f0 | f1 | f2) & VF_NEEDS_CLIP) != 0u) { atomicAdd(&pc.status[1], 1u); return; }   // Appendix B.3 (counted, dropped)
+    const VtxA &a0 = t.a[0], &a1 = t.a[1], &a2 = t.a[2];
+    t.A2 = (long long)(a1.X - a0.X) * (long long)(a2.Y - a0.Y) - (long long)(a2.X - a0.X) * (long long)(a1.Y - a0.Y);
+    if (t.A2 >= 0) return;                                                          // Appendix B.6: front = CCW = A2 < 0
+    const int32_t minX = min(a0.X, min(a1.X, a2.X)), maxX = max(a0.X, max(a1.X, a2.X));
+    const int32_t minY = min(a0.Y, min(a1.Y, a2.Y)), maxY = max(a0.Y, max(a1.Y, a2.Y));
+    t.x0 = max((minX + 127) >> 8, 0); t.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+    t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+    if (t.x0 > t.x1 || t.y0 > t.y1) return;                                         // no pixel centre inside the bbox
+    // unclamped spans keep the 32-bit edge math of phase 2 exact
+    t.isSmall = (maxX - minX) <= SMALL_MAX * 256 && (maxY - minY) <= SMALL_MAX * 256;
+    t.isLarge = !t.isSmall;
+}
+
+__device__ __forceinline__ LargeRec k1_large_rec(const K1Tri& t, uint32_t tri) {
+    LargeRec r;
+    r.X0 = t.a[0].X; r.Y0 = t.a[0].Y; r.X1 = t.a[1].X; r.Y1 = t.a[1].Y;
+    r.X2 = t.a[2].X; r.Y2 = t.a[2].Y; r.z0 = t.a[0].z; r.z1 = t.a[1].z;
+    r.z2 = t.a[2].z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
+    return r;
+}
+
+// huge -> broadcast list; large -> queue + per-tile counts.  Called by all 32 lanes of the warp.
+__device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uint32_t tri, unsigned lane) {
+    if (t.isLarge) {
+        const int ntiles = (t.x1 / TILE_W - t.x0 / TILE_W + 1) * (t.y1 / TILE_H - t.y0 / TILE_H + 1);
+        if (ntiles > HUGE_TILES) {
+            const uint32_t slot = atomicAdd(&pc.status[4], 1u);
+            if (slot < (uint32_t)HUGE_CAP) { pc.huge[slot] = k1_large_rec(t, tri); t.isLarge = false; }
+        }
+    }
+    unsigned lmask = __ballot_sync(0xFFFFFFFFu, t.isLarge);
+    if (!lmask) return;
+    const int leader = __ffs(lmask) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(&pc.status[0], (uint32_t)__popc(lmask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    const uint32_t slot = base + __popc(lmask & ((1u << lane) - 1u));
+    if (t.isLarge) {
+        if (slot < pc.largeCap) pc.large[slot] = k1_large_rec(t, tri);
+        else atomicOr(&pc.status[2], OVF_LARGE);
+    }
+    while (lmask) {   // warp-cooperative tile counting, one large triangle at a time
+        const int src = __ffs(lmask) - 1;
+        lmask &= lmask - 1;
+        const int32_t X0 = __shfl_sync(0xFFFFFFFFu, t.a[0].X, src), Y0 = __shfl_sync(0xFFFFFFFFu, t.a[0].Y, src);
+        const int32_t X1 = __shfl_sync(0xFFFFFFFFu, t.a[1].X, src), Y1 = __shfl_sync(0xFFFFFFFFu, t.a[1].Y, src);
+        const int32_t X2 = __shfl_sync(0xFFFFFFFFu, t.a[2].X, src), Y2 = __shfl_sync(0xFFFFFFFFu, t.a[2].Y, src);
+        const uint32_t s = __shfl_sync(0xFFFFFFFFu, slot, src);
+        if (s < pc.largeCap) tile_walk<false>(pc, X0, Y0, X1, Y1, X2, Y2, s, lane);
+    }
+}
+
+__device__ __forceinline__ void k1_store_small(K1Shared& sm, const K1Tri& t, uint32_t tri, uint32_t slot, uint32_t row0) {
+    const int32_t X[3] = {t.a[0].X, t.a[1].X, t.a[2].X}, Y[3] = {t.a[0].Y, t.a[1].Y, t.a[2].Y};
+    const int32_t Px = 256 * t.x0 + 128, Py = 256 * t.y0 + 128;
+    const uint32_t h = (uint32_t)(t.y1 - t.y0 + 1);
+    uint32_t biasBits = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int a = (k + 1) % 3, b = (k + 2) % 3;     // edge a->b opposes vertex k
+        const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
+        const uint32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0u : 1u;   // top-left rule (Appendix B.7)
+        sm.Ax[k][slot] = 256 * A;
+        sm.By[k][slot] = 256 * B;
+        sm.C[k][slot] = A * (Px - X[a]) + B * (Py - Y[a]);
+        biasBits |= bias << (16 + k);
+    }
+    sm.xy[slot] = (uint32_t)t.x0 | ((uint32_t)t.y0 << 16);
+    sm.whb[slot] = (uint32_t)(t.x1 - t.x0 + 1) | (h << 8) | biasBits;
+    sm.z0[slot] = t.a[0].z; sm.dz1[slot] = t.a[1].z - t.a[0].z; sm.dz2[slot] = t.a[2].z - t.a[0].z;
+    sm.area[slot] = (float)(-t.A2);
+    sm.idKey[slot] = ~tri;
+    sm.rowStart[slot] = (uint16_t)row0;
+    for (uint32_t j = 0; j < h; ++j) sm.itemTri[row0 + j] = (uint16_t)slot;
+}
+
+// Cache slots of the three corners of triangle `tri` (flatSlots: the draw list's index stream re-based into
+// cache-slot space in submission order, built when the draw list changes; de-indexed mode needs no table).
+__device__ __forceinline__ uint3 k1_load_slots(const PassConst& pc, uint32_t tri) {
+    if (tri >= pc.nTris) return make_uint3(0u, 0u, 0u);
+    if (pc.deindexed) return make_uint3(3u * tri, 3u * tri + 1u, 3u * tri + 2u);
+    const uint32_t* f = pc.flatSlots + 3ull * tri;
+    return make_uint3(__ldg(f), __ldg(f + 1), __ldg(f + 2));
+}
+__device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uint3 s, uint4 q[3]) {
+    if (tri >= pc.nTris) { q[0] = q[1] = q[2] = make_uint4(0, 0, 0, 0); return; }
+    const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
+    q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
+}
+
+// Persistent CTAs pull blocks of K1_TRIS triangles from a global counter; the cache gathers of the next block
+// are issued before the current block is rasterised (register double buffering), so the
+// slot-table -> vertex load chain overlaps phase 2.
+#ifndef K1_MIN_BLOCKS
+#define K1_MIN_BLOCKS 4
+#endif
+template <bool SHADOW>
+__global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(const __grid_constant__ PassConst pc) {
+    __shared__ K1Shared sm;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t nBlocks = (pc.nTris + K1_TRIS - 1u) / K1_TRIS;
+    bool anyLarge = false;
+
+    uint32_t blk = blockIdx.x;                                   // grid <= nBlocks
+    uint32_t tri = blk * K1_TRIS + threadIdx.x;
+    uint4 q[3];
+    uint3 ns = k1_load_slots(pc, tri);
+    if (threadIdx.x == 0) sm.nextBlk = gridDim.x + atomicAdd(&pc.status[6], 1u);
+    __syncthreads();
+    uint32_t nblk = sm.nextBlk;
+    k1_gather(pc, tri, ns, q);
+    ns = k1_load_slots(pc, nblk * K1_TRIS + threadIdx.x);          // slots run two blocks ahead, gathers one
+    __syncthreads();                                               // (everyone has read nextBlk before thread 0 rewrites it)
+    while (blk < nBlocks) {
+        uint32_t nnblk = 0;
+        if (threadIdx.x == 0) nnblk = gridDim.x + atomicAdd(&pc.status[6], 1u);   // the block after next (dynamic schedule)
+
+        // ---- phase 1: classify, emit large, compact small ------------------------------------------------
+        K1Tri t;
+        k1_classify(pc, tri < pc.nTris, q, t);
+        anyLarge = anyLarge || t.isLarge;
+        k1_emit_large(pc, t, tri, lane);
+        const uint32_t mine = t.isSmall ? (1u | ((uint32_t)(t.y1 - t.y0 + 1) << 16)) : 0u;   // packed (count, rows)
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= (unsigned)o) incl += n; }
+        if (lane == 31) sm.warpTot[warp] = incl;
+        __syncthreads();
+        uint32_t base = 0, total = 0;
+#pragma unroll
+        for (int wgt = 0; wgt < K1_WARPS; ++wgt) { const uint32_t v = sm.warpTot[wgt]; if (wgt < (int)warp) base += v; total += v; }
+        const uint32_t nRows = total >> 16;
+        if (t.isSmall) { const uint32_t excl = base + incl - mine; k1_store_small(sm, t, tri, excl & 0xFFFFu, excl >> 16); }
+        const uint32_t ntri = nblk * K1_TRIS + threadIdx.x;
+        k1_gather(pc, ntri, ns, q);                                 // in flight during phase 2 (slots arrived an iteration ago)
+        if (threadIdx.x == 0) sm.nextBlk = nnblk;
+        __syncthreads();
+        ns = k1_load_slots(pc, sm.nextBlk * K1_TRIS + threadIdx.x);
+
+        // ---- phase 2, per warp: 32 (small triangle, pixel row) items -> coverage masks -> queue of covered
+        //      samples -> one lane per covered sample (depth + atomicMin) ------------------------------------
+        uint16_t* wq = sm.pixq[warp];
+        for (uint32_t ibase = warp * 32u; ibase < nRows; ibase += K1_THREADS) {     // warp-uniform trip count
+            const uint32_t item = ibase + lane;
+            bool active = item < nRows;
+            uint32_t tS = 0, j = 0, whb = 0;
+            if (active) {
+                tS = sm.itemTri[item];
+                j = item - sm.rowStart[tS];
+                whb = sm.whb[tS];
+                if (!SHADOW && !row_owned((sm.xy[tS] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
+            }
+            const uint32_t w = active ? (whb & 0xFFu) : 0u;
+            const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
+            uint32_t mask = 0;
+            {
+                const int32_t s0 = sm.Ax[0][tS], s1 = sm.Ax[1][tS], s2 = sm.Ax[2][tS];
+                int32_t F0 = sm.C[0][tS] + (int32_t)j * sm.By[0][tS] - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
+                int32_t F1 = sm.C[1][tS] + (int32_t)j * sm.By[1][tS] - (int32_t)((whb >> 17) & 1u);
+                int32_t F2 = sm.C[2][tS] + (int32_t)j * sm.By[2][tS] - (int32_t)((whb >> 18) & 1u);
+#pragma unroll 1
+                for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
+            }
+            mask &= (1u << w) - 1u;
+            const uint32_t cnt = __popc(mask);
+            uint32_t qi = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, qi, o); if (lane >= (unsigned)o) qi += n; }
+            const uint32_t nPix = __shfl_sync(0xFFFFFFFFu, qi, 31);
+            qi -= cnt;
+            const uint32_t tag = tS | (j << 12);
+            while (mask) {
+                const uint32_t i = (uint32_t)__ffs(mask) - 1u;
+                mask &= mask - 1u;
+                wq[qi++] = (uint16_t)(tag | (i << 8));
+            }
+            __syncwarp();
+            for (uint32_t pI = lane; pI < nPix; pI += 32u) {
+                const uint32_t e = wq[pI];
+                const uint32_t ts = e & 0xFFu;
+                const int32_t pi = (int32_t)((e >> 8) & 0xFu), pj = (int32_t)(e >> 12);
+                const int32_t u1 = sm.C[1][ts] + pj * sm.By[1][ts] + pi * sm.Ax[1][ts];   // unbiased edge values (Appendix B.8)
+                const int32_t u2 = sm.C[2][ts] + pj * sm.By[2][ts] + pi * sm.Ax[2][ts];
+                const float z = depth_from((float)u1, (float)u2, sm.area[ts], sm.z0[ts], sm.dz1[ts], sm.dz2[ts]);
+                if (!(z >= 0.0f && z <= 1.0f)) continue;
+                const uint32_t xy = sm.xy[ts];
+                const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
+                if (SHADOW) atomicMin(pc.depthBits + px, __float_as_uint(z));
+                else atomicMin(pc.vis + px, ((unsigned long long)__float_as_uint(z) << 32) | sm.idKey[ts]);
+            }
+            __syncwarp();
+        }
+        __syncthreads();   // shared arrays are reused by the next block
+        blk = nblk; tri = ntri; nblk = sm.nextBlk;
+    }
+
+    // ---- tail: the last CTA to get here lays out the per-tile lists of the large triangles ------------------
+    // (only the tile counts have to be visible, so CTAs that queued nothing skip the fence)
+    const int ctaLarge = __syncthreads_or(anyLarge ? 1 : 0);
+    if (ctaLarge) __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) { sm.isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; sm.cursor = 0u; }
+    __syncthreads();
+    if (!sm.isLast) return;
+    __threadfence();
+    const uint32_t nLarge = min(*reinterpret_cast<volatile uint32_t*>(&pc.status[0]), pc.largeCap);
+    if (nLarge == 0) return;
+    const uint32_t nTiles = pc.tilesX * pc.tilesY;
+    for (uint32_t i0 = 0; i0 < nTiles; i0 += K1_THREADS) {
+        const uint32_t i = i0 + threadIdx.x;
+        const uint32_t c = i < nTiles ? __ldcg(pc.tileCount + i) : 0u;
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= (unsigned)o) inc += n; }
+        uint32_t wbase = 0;
+        if (lane == 31 && inc) wbase = atomicAdd(&sm.cursor, inc);
+        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+        if (i < nTiles && c) { pc.tileStart[i] = wbase + inc - c; pc.tileCount[i] = 0u; }   // counts become the scatter cursors
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        pc.status[3] = sm.cursor;
+        if (sm.cursor > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
+    }
+}
+
+// Re-bases a draw list's index stream into cache-slot space, in submission order (runs when the list changes).
+__global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ PassConst pc, uint32_t* __restrict__ flat) {
+    const uint32_t tri = blockIdx.x * 256u + threadIdx.x;
+    if (tri >= pc.nTris) return;
+    const uint32_t d = find_draw<false>(pc.draws, pc.nDraws, tri);
+    const uint32_t* ix = pc.indices + pc.draws[d].indexOffset + 3u * (tri - pc.draws[d].firstTri);
+    const int32_t off = pc.draws[d].cacheOffset;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) flat[3ull * tri + k] = (uint32_t)((int32_t)ix[k] + off);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: scatter the queued large triangles into the per-tile lists laid out by K1's tail.
+// One warp per triangle (same tile walk as the count).  Does nothing when the queue is empty.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bin_scatter(const __grid_constant__ PassConst pc) {
     const uint32_t nLarge = min(pc.status[0], pc.largeCap);
     if (nLarge == 0) return;
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < nLarge; t += warpsPerGrid) {
         const LargeRec r = pc.large[t];
-        const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
-        const int32_t minX = min(X[0], min(X[1], X[2])), maxX = max(X[0], max(X[1], X[2]));
-        const int32_t minY = min(Y[0], min(Y[1], Y[2])), maxY = max(Y[0], max(Y[1], Y[2]));
-        const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int)pc.W - 1);
-        const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int)pc.H - 1);
-        const int tx0 = x0 / TILE_W, tx1 = x1 / TILE_W, ty0 = y0 / TILE_H, ty1 = y1 / TILE_H;
-        const int tw = tx1 - tx0 + 1, n = tw * (ty1 - ty0 + 1);
-        long long A[3], B[3], C[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int a = (k + 1) % 3, b = (k + 2) % 3;
-            A[k] = (long long)Y[b] - Y[a];
-            B[k] = -((long long)X[b] - X[a]);
-            C[k] = -(A[k] * X[a]) - B[k] * Y[a];
-        }
-        for (int i = lane; i < n; i += 32) {
-            const int tx = tx0 + i % tw, ty = ty0 + i / tw;
-            if (pc.nRanks > 1 && !row_owned((uint32_t)(ty * TILE_H), pc.rank, pc.nRanks, pc.bandH)) continue;
-            // pixel-centre extent of the tile in sub-pixel units
-            const long long cx0 = 256ll * (tx * TILE_W) + 128, cx1 = 256ll * (tx * TILE_W + TILE_W - 1) + 128;
-            const long long cy0 = 256ll * (ty * TILE_H) + 128, cy1 = 256ll * (ty * TILE_H + TILE_H - 1) + 128;
-            bool outside = false;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const long long Fmax = A[k] * (A[k] > 0 ? cx1 : cx0) + B[k] * (B[k] > 0 ? cy1 : cy0) + C[k];
-                outside = outside || (Fmax < 0);
-            }
-            if (outside) continue;
-            const uint32_t tile = (uint32_t)ty * pc.tilesX + (uint32_t)tx;
-            if (!SCATTER) {
-                atomicAdd(&tileCount[tile], 1u);
-            } else {
-                const uint32_t slot = tileStart[tile] + atomicAdd(&tileCount[tile], 1u);
-                if (slot < listCap) tileList[slot] = t;
-            }
-        }
-    }
-}
-
-// Exclusive scan of the per-tile counts (single CTA): every thread owns a contiguous chunk, one block scan of
-// the chunk sums.  Resets the counts so the scatter pass can reuse them as cursors; records the list total.
-__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart, uint32_t nTiles,
-                                                     uint32_t listCap, uint32_t* __restrict__ status) {
-    if (status[0] == 0) return;   // nothing was binned: the tile stage ignores the lists
-    __shared__ uint32_t warpSums[32];
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t chunk = (nTiles + 1023u) / 1024u;
-    const uint32_t lo = min(threadIdx.x * chunk, nTiles), hi = min(lo + chunk, nTiles);
-    uint32_t sum = 0;
-    for (uint32_t i = lo; i < hi; ++i) sum += tileCount[i];
-    uint32_t incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= (unsigned)o) incl += n; }
-    if (lane == 31) warpSums[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t ws = warpSums[lane], wi = ws;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xFFFFFFFFu, wi, o); if (lane >= (unsigned)o) wi += n; }
-        warpSums[lane] = wi - ws;
-    }
-    __syncthreads();
-    uint32_t run = warpSums[warp] + incl - sum;
-    for (uint32_t i = lo; i < hi; ++i) { const uint32_t c = tileCount[i]; tileStart[i] = run; tileCount[i] = 0; run += c; }
-    if (threadIdx.x == 1023) {
-        tileStart[nTiles] = run;
-        status[3] = run;
-        if (run > listCap) atomicOr(&status[2], OVF_LIST);
+        tile_walk<true>(pc, r.X0, r.Y0, r.X1, r.Y1, r.X2, r.Y2, t, lane);
     }
 }
 
@@ -299,23 +393,28 @@ __global__ void k_split_vertices(const float4* __restrict__ aos, float4* __restr
 // ---------------------------------------------------------------------------------------------
 // launch wrappers
 // ---------------------------------------------------------------------------------------------
-void launch_setup_raster(const PassConst& pc, bool shadow, cudaStream_t st) {
+void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
     if (pc.nTris == 0) return;
-    const uint32_t grid = (pc.nTris + 255u) / 256u;
-    if (shadow) k_setup_raster<true><<<grid, 256, 0, st>>>(pc);
-    else k_setup_raster<false><<<grid, 256, 0, st>>>(pc);
+    static int perSM[2] = {0, 0};
+    if (!perSM[shadow]) {
+        int n = 0;
+        if (shadow) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_setup_raster<true>, K1_THREADS, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_setup_raster<false>, K1_THREADS, 0);
+        perSM[shadow] = n > 0 ? n : 1;
+    }
+    const uint32_t nBlocks = (pc.nTris + K1_TRIS - 1u) / K1_TRIS;
+    const uint32_t grid = std::min<uint32_t>(nBlocks, (uint32_t)(numSMs * perSM[shadow]));
+    if (shadow) k_setup_raster<true><<<grid, K1_THREADS, 0, st>>>(pc);
+    else k_setup_raster<false><<<grid, K1_THREADS, 0, st>>>(pc);
 }
 
-void launch_bin_count(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
-                      int numSMs, cudaStream_t st) {
-    k_bin_large<false><<<numSMs * 4, 256, 0, st>>>(pc, tileCount, tileStart, tileList, listCap);
+void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) {
+    if (pc.nTris == 0) return;
+    k_flatten_slots<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, flat);
 }
-void launch_scan_tiles(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t listCap, cudaStream_t st) {
-    k_scan_tiles<<<1, 1024, 0, st>>>(tileCount, tileStart, pc.tilesX * pc.tilesY, listCap, pc.status);
-}
-void launch_bin_scatter(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
-                        int numSMs, cudaStream_t st) {
-    k_bin_large<true><<<numSMs * 4, 256, 0, st>>>(pc, tileCount, tileStart, tileList, listCap);
+
+void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st) {
+    k_bin_scatter<<<numSMs * 4, 256, 0, st>>>(pc);
 }
 
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st) {

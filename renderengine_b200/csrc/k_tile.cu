@@ -1,7 +1,9 @@
-// k_tile.cu — K3: the tile stage.  One CTA (256 threads) per TILE_W x TILE_H screen tile, one thread per
-// sample.  The tile's visibility keys live in registers (one per thread), the tile's large-triangle
-// list is staged through shared memory as precomputed edge equations, coverage uses the top-left
-// rule with 64-bit edge functions and an early-Z key compare, then (forward pass) every sample is
+// k_tile.cu — K3: the tile stage.  One CTA (256 threads) per TILE_W x TILE_H screen tile on a 2-D grid, one
+// thread per sample, each warp owning an 8 x 4 pixel block (compact footprint: neighbouring samples share
+// triangles, so the post-transform-cache gathers of a warp fall into few sectors).  The tile's visibility
+// keys live in registers (one per thread); the large triangles that touch the tile (broadcast list + binned
+// list) are staged through shared memory as edge equations relative to the tile origin; coverage uses the
+// top-left rule with 64-bit edge functions and an early-Z key compare; then (forward pass) every sample is
 // shaded in place: attribute reconstruction, bindless material fetch, Phong + 3x3 PCF.
 //
 // Reference: fixed-function raster/depth state GraphicsPipelineCache.cpp:280-340; fragment work
@@ -11,131 +13,152 @@
 
 namespace reb {
 
-constexpr int STAGE = 64;   // large-triangle records staged per round
+constexpr int STAGE = 64;   // large-triangle records staged per round (two warps' worth)
 
-struct EdgeRec {            // one staged large triangle: F_k(P) = A*Px + B*Py + C (interior positive)
+struct EdgeRec {            // one staged large triangle, relative to the tile's first pixel centre
+    long long E[3];         // biased edge value at the tile origin (covered iff E + A*dx + B*dy >= 0 for all three)
     int32_t A[3], B[3];
-    long long C[3];
-    int32_t bias[3];
     float area, z0, dz1, dz2;
-    uint32_t idKey;
+    uint32_t idKey, bias12; // bias12: bit 0 = bias of edge 1, bit 1 = bias of edge 2 (to recover the unbiased values)
 };
 
-__device__ __forceinline__ void stage_record(const LargeRec& r, EdgeRec& e) {
+struct TileShared {
+    EdgeRec stage[STAGE];
+    uint32_t liveMask[2];
+};
+
+// Build the staged record of triangle r for the tile whose first pixel is (tx0, ty0); returns false when the
+// triangle cannot touch any pixel centre of the tile (bbox + edge reject at the most-interior corner).
+__device__ __forceinline__ bool stage_record(const LargeRec& r, int tx0, int ty0, EdgeRec& e) {
     const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
+    const int32_t minX = min(r.X0, min(r.X1, r.X2)), maxX = max(r.X0, max(r.X1, r.X2));
+    const int32_t minY = min(r.Y0, min(r.Y1, r.Y2)), maxY = max(r.Y0, max(r.Y1, r.Y2));
+    const long long cx0 = 256ll * tx0 + 128, cy0 = 256ll * ty0 + 128;
+    const long long spanX = 256ll * (TILE_W - 1), spanY = 256ll * (TILE_H - 1);
+    bool live = !(maxX < cx0 || minX > cx0 + spanX || maxY < cy0 || minY > cy0 + spanY);
+    uint32_t bias12 = 0;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int a = (k + 1) % 3, b = (k + 2) % 3;
         const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
-        e.A[k] = A; e.B[k] = B;
-        e.C[k] = -((long long)A * X[a]) - (long long)B * Y[a];
-        e.bias[k] = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;
+        const int32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
+        const long long E = (long long)A * (cx0 - X[a]) + (long long)B * (cy0 - Y[a]) - bias;
+        e.A[k] = A; e.B[k] = B; e.E[k] = E;
+        const long long Emax = E + (A > 0 ? (long long)A * spanX : 0ll) + (B > 0 ? (long long)B * spanY : 0ll);
+        live = live && (Emax >= 0);
+        if (k > 0) bias12 |= (uint32_t)bias << (k - 1);
     }
     const long long A2 = (long long)(X[1] - X[0]) * (long long)(Y[2] - Y[0]) - (long long)(X[2] - X[0]) * (long long)(Y[1] - Y[0]);
     e.area = (float)(-A2);
     e.z0 = r.z0; e.dz1 = r.z1 - r.z0; e.dz2 = r.z2 - r.z0;
-    e.idKey = ~r.triId;
+    e.idKey = ~r.triId; e.bias12 = bias12;
+    return live;
 }
 
-// Does the triangle touch any pixel centre of the tile whose first pixel is (tx0, ty0)?  (bbox + edge reject)
-__device__ __forceinline__ bool tile_overlap(const LargeRec& r, const EdgeRec& e, int tx0, int ty0) {
-    const int32_t minX = min(r.X0, min(r.X1, r.X2)), maxX = max(r.X0, max(r.X1, r.X2));
-    const int32_t minY = min(r.Y0, min(r.Y1, r.Y2)), maxY = max(r.Y0, max(r.Y1, r.Y2));
-    const long long cx0 = 256ll * tx0 + 128, cx1 = 256ll * (tx0 + TILE_W - 1) + 128;
-    const long long cy0 = 256ll * ty0 + 128, cy1 = 256ll * (ty0 + TILE_H - 1) + 128;
-    if (maxX < cx0 || minX > cx1 || maxY < cy0 || minY > cy1) return false;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const long long Fmax = (long long)e.A[k] * (e.A[k] > 0 ? cx1 : cx0) + (long long)e.B[k] * (e.B[k] > 0 ? cy1 : cy0) + e.C[k];
-        if (Fmax < 0) return false;
-    }
-    return true;
-}
-
-// Merge a list of large triangles into this thread's key (depthBits<<32 | ~triId; minimum wins).
-// idx == nullptr: records src[begin..end) are used directly and culled against the tile (broadcast list);
-// otherwise src[idx[i]] for i in [begin, end) (binned list, already culled by the binner).
+// Merge a list of large triangles into this thread's key (depthBits<<32 | ~triId, or the bare depth bits for the
+// shadow pass; minimum wins).  idx == nullptr: records src[begin..end) directly (broadcast list); otherwise
+// src[idx[i]] for i in [begin, end) (binned list).  (lx, ly) = sample position inside the tile.
 template <bool SHADOW>
 __device__ __forceinline__ unsigned long long merge_large(const LargeRec* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t begin,
-                                                          uint32_t end, int tx0, int ty0, int x, int y, unsigned long long key,
-                                                          EdgeRec* stage, uint32_t* live) {
-    const long long Px = 256ll * x + 128, Py = 256ll * y + 128;
+                                                          uint32_t end, int tx0, int ty0, int lx, int ly, unsigned long long key, TileShared& sm) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const int32_t dx = 256 * lx, dy = 256 * ly;
     for (uint32_t base = begin; base < end; base += STAGE) {
         const uint32_t n = min((uint32_t)STAGE, end - base);
         __syncthreads();
-        if (threadIdx.x < n) {
-            const LargeRec r = src[idx ? __ldg(idx + base + threadIdx.x) : base + threadIdx.x];
-            stage_record(r, stage[threadIdx.x]);
-            live[threadIdx.x] = idx ? 1u : (tile_overlap(r, stage[threadIdx.x], tx0, ty0) ? 1u : 0u);
+        if (warp < 2) {
+            bool live = false;
+            if (threadIdx.x < n) {
+                const LargeRec r = src[idx ? __ldcg(idx + base + threadIdx.x) : base + threadIdx.x];
+                live = stage_record(r, tx0, ty0, sm.stage[threadIdx.x]);
+            }
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, live);
+            if (lane == 0) sm.liveMask[warp] = m;
         }
         __syncthreads();
-        for (uint32_t i = 0; i < n; ++i) {
-            if (!live[i]) continue;   // CTA-uniform
-            const EdgeRec& e = stage[i];
-            const long long F0 = (long long)e.A[0] * Px + (long long)e.B[0] * Py + e.C[0];
-            const long long F1 = (long long)e.A[1] * Px + (long long)e.B[1] * Py + e.C[1];
-            const long long F2 = (long long)e.A[2] * Px + (long long)e.B[2] * Py + e.C[2];
-            if (((F0 - e.bias[0]) | (F1 - e.bias[1]) | (F2 - e.bias[2])) < 0) continue;
-            const float b1 = (float)F1 / e.area, b2 = (float)F2 / e.area;
-            float z = (e.z0 + b1 * e.dz1) + b2 * e.dz2;
-            if (z == 0.0f) z = 0.0f;
-            if (!(z >= 0.0f && z <= 1.0f)) continue;
-            const unsigned long long k = SHADOW ? (unsigned long long)__float_as_uint(z)
-                                                : (((unsigned long long)__float_as_uint(z) << 32) | e.idKey);
-            if (k < key) key = k;   // early-Z + later-primitive-wins in one compare
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            unsigned m = sm.liveMask[h];   // CTA-uniform
+            while (m) {
+                const EdgeRec& e = sm.stage[32 * h + __ffs(m) - 1];
+                m &= m - 1;
+                const long long F0 = e.E[0] + (long long)e.A[0] * dx + (long long)e.B[0] * dy;
+                const long long F1 = e.E[1] + (long long)e.A[1] * dx + (long long)e.B[1] * dy;
+                const long long F2 = e.E[2] + (long long)e.A[2] * dx + (long long)e.B[2] * dy;
+                if ((F0 | F1 | F2) < 0) continue;
+                const float z = depth_from((float)(F1 + (long long)(e.bias12 & 1u)), (float)(F2 + (long long)(e.bias12 >> 1)), e.area, e.z0, e.dz1, e.dz2);
+                if (!(z >= 0.0f && z <= 1.0f)) continue;
+                const unsigned long long k = SHADOW ? (unsigned long long)__float_as_uint(z)
+                                                    : (((unsigned long long)__float_as_uint(z) << 32) | e.idKey);
+                if (k < key) key = k;   // early-Z + later-primitive-wins in one compare
+            }
         }
     }
     return key;
 }
 
-// Shadow pass tile stage (persistent CTAs striding over the tiles): only tiles touched by large triangles do work.
-__global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ PassConst pc, uint32_t* __restrict__ tileCount,
-                                                     const uint32_t* __restrict__ tileStart, const uint32_t* __restrict__ tileList, uint32_t listCap) {
-    __shared__ EdgeRec stage[STAGE];
-    __shared__ uint32_t live[STAGE];
+// sample position of this thread inside its tile: warp w owns the 8 x 4 block at (8 * (w & 3), 4 * (w >> 2))
+__device__ __forceinline__ void tile_sample(int& lx, int& ly) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    lx = (int)(8u * (warp & 3u) + (lane & 7u));
+    ly = (int)(4u * (warp >> 2) + (lane >> 3));
+}
+
+// Shadow pass tile stage: only tiles touched by large triangles do work (the small ones were resolved by K1's atomics).
+__global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ PassConst pc) {
+    __shared__ TileShared sm;
     const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    if (nLarge == 0 && nHuge == 0) return;
-    const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
-        uint32_t begin = 0, end = 0;
-        if (nLarge) { begin = min(tileStart[tile], listCap); end = min(tileStart[tile + 1], listCap); }
-        const int tx0 = (int)(tile % pc.tilesX) * TILE_W, ty0 = (int)(tile / pc.tilesX) * TILE_H;
-        const int x = tx0 + (int)(threadIdx.x & 31u), y = ty0 + (int)(threadIdx.x >> 5);
-        const bool inb = x < (int)pc.W && y < (int)pc.H;
-        const size_t p = (size_t)y * pc.W + x;
-        const unsigned long long cur = inb ? (unsigned long long)pc.depthBits[p] : 0ull;
-        unsigned long long key = cur;
-        if (nHuge) key = merge_large<true>(pc.huge, nullptr, 0, nHuge, tx0, ty0, x, y, key, stage, live);
-        if (begin != end) key = merge_large<true>(pc.large, tileList, begin, end, tx0, ty0, x, y, key, stage, live);
-        if (inb && key < cur) pc.depthBits[p] = (uint32_t)key;
-        if (nLarge && threadIdx.x == 0) tileCount[tile] = 0;   // re-arm the bin counters for the next pass
+    const uint32_t tile = blockIdx.y * pc.tilesX + blockIdx.x;
+    uint32_t begin = 0, end = 0;
+    if (nLarge) {
+        const uint32_t cnt = __ldcg(pc.tileCount + tile);
+        if (cnt) {
+            const uint32_t start = __ldcg(pc.tileStart + tile);
+            begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
+            if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm the bin counter for the next pass (only this CTA touches it here)
+        }
     }
+    if (nHuge == 0 && begin == end) return;   // CTA-uniform
+    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * TILE_H;
+    int lx, ly;
+    tile_sample(lx, ly);
+    const int x = tx0 + lx, y = ty0 + ly;
+    const bool inb = x < (int)pc.W && y < (int)pc.H;
+    const size_t p = (size_t)y * pc.W + x;
+    const unsigned long long cur = inb ? (unsigned long long)__ldcg(pc.depthBits + p) : 0ull;
+    unsigned long long key = cur;
+    if (nHuge) key = merge_large<true>(pc.huge, nullptr, 0, nHuge, tx0, ty0, lx, ly, key, sm);
+    if (begin != end) key = merge_large<true>(pc.large, pc.tileList, begin, end, tx0, ty0, lx, ly, key, sm);
+    if (inb && key < cur) pc.depthBits[p] = (uint32_t)key;
 }
 
 // Forward pass tile stage: consume (and reset) the visibility keys, merge large triangles, shade, write.
-__global__ void __launch_bounds__(256) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh,
-                                                      uint32_t* __restrict__ tileCount, const uint32_t* __restrict__ tileStart,
-                                                      const uint32_t* __restrict__ tileList, uint32_t listCap) {
-    __shared__ EdgeRec stage[STAGE];
-    __shared__ uint32_t live[STAGE];
-    const uint32_t tile = blockIdx.x;
-    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    if (nLarge && threadIdx.x == 0) tileCount[tile] = 0;
-    const int tx0 = (int)(tile % pc.tilesX) * TILE_W, ty0 = (int)(tile / pc.tilesX) * TILE_H;
-    if (!row_owned((uint32_t)ty0, pc.rank, pc.nRanks, pc.bandH)) return;
-    const int x = tx0 + (int)(threadIdx.x & 31u), y = ty0 + (int)(threadIdx.x >> 5);
+__global__ void __launch_bounds__(256, 3) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
+    __shared__ TileShared sm;
+    const uint32_t tile = blockIdx.y * pc.tilesX + blockIdx.x;
+    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * TILE_H;
+    int lx, ly;
+    tile_sample(lx, ly);
+    const int x = tx0 + lx, y = ty0 + ly;
     const bool inb = x < (int)pc.W && y < (int)pc.H;
     const size_t p = (size_t)y * pc.W + x;
+    const bool owned = row_owned((uint32_t)ty0, pc.rank, pc.nRanks, pc.bandH);
     unsigned long long key = VIS_CLEAR;
-    if (inb) {
-        key = pc.vis[p];
-        if (key != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
-    }
-    if (nHuge) key = merge_large<false>(pc.huge, nullptr, 0, nHuge, tx0, ty0, x, y, key, stage, live);
+    if (inb && owned) key = __ldcg(pc.vis + p);
+    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
+    uint32_t begin = 0, end = 0;
     if (nLarge) {
-        const uint32_t begin = min(tileStart[tile], listCap), end = min(tileStart[tile + 1], listCap);
-        if (begin != end) key = merge_large<false>(pc.large, tileList, begin, end, tx0, ty0, x, y, key, stage, live);
+        const uint32_t cnt = __ldcg(pc.tileCount + tile);
+        if (cnt) {
+            const uint32_t start = __ldcg(pc.tileStart + tile);
+            begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
+            if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm (only this CTA touches this counter here)
+        }
     }
+    if (!owned) return;
+    if (inb && key != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
+    if (nHuge) key = merge_large<false>(pc.huge, nullptr, 0, nHuge, tx0, ty0, lx, ly, key, sm);
+    if (begin != end) key = merge_large<false>(pc.large, pc.tileList, begin, end, tx0, ty0, lx, ly, key, sm);
     if (!inb) return;
 
     float depth = 1.0f;                    // depth clear 1.0 (RenderScene.cpp:219)
@@ -152,15 +175,12 @@ __global__ void __launch_bounds__(256) k_tile_forward(const __grid_constant__ Pa
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
 }
 
-void launch_tile_shadow(const PassConst& pc, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList, uint32_t listCap,
-                        int numSMs, cudaStream_t st) {
-    const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    k_tile_shadow<<<std::min<uint32_t>(nTiles, (uint32_t)numSMs * 8u), 256, 0, st>>>(pc, tileCount, tileStart, tileList, listCap);
+void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
+    k_tile_shadow<<<dim3(pc.tilesX, pc.tilesY), 256, 0, st>>>(pc);
 }
 
-void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList,
-                         uint32_t listCap, cudaStream_t st) {
-    k_tile_forward<<<pc.tilesX * pc.tilesY, 256, 0, st>>>(pc, sh, tileCount, tileStart, tileList, listCap);
+void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st) {
+    k_tile_forward<<<dim3(pc.tilesX, pc.tilesY), 256, 0, st>>>(pc, sh);
 }
 
 }  // namespace reb

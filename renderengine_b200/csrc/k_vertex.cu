@@ -17,20 +17,17 @@ namespace reb {
 
 template <bool SHADOW>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
-    __shared__ uint32_t sBase;
-    const uint32_t first = blockIdx.x * 256u;
-    const uint32_t slot = first + threadIdx.x;
-    const bool valid = slot < pc.cacheSize;
-    uint32_t d, v = 0;
+    const uint32_t slot = blockIdx.x * 256u + threadIdx.x;
+    if (slot >= pc.cacheSize) return;
+    // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
+    const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, slot);
+    uint32_t v;
     if (pc.deindexed) {
         const uint32_t tri = slot / 3u, k = slot - 3u * tri;
-        d = find_draw_cta<false>(pc.draws, pc.nDraws, first / 3u, valid ? tri : first / 3u, &sBase);
-        if (valid) v = __ldg(pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri)) + k);
+        v = __ldg(pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri)) + k);
     } else {
-        d = find_draw_cta<true>(pc.draws, pc.nDraws, first, valid ? slot : first, &sBase);
-        if (valid) v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
+        v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
     }
-    if (!valid) return;
     const uint32_t node = __ldg(&pc.draws[d].node);
     const float4 p = __ldg(pc.pos4 + v);
     const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * node;

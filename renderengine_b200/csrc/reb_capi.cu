@@ -23,6 +23,8 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward
     uint32_t nDraws = 0, nTris = 0;
     // post-transform vertex cache of this pass (K0 output)
     VtxA* vtxA = nullptr; VtxBC* vtxBC = nullptr; size_t cacheCap = 0;
+    uint32_t* blockDraw = nullptr; size_t blockDrawCap = 0; uint32_t triBlocks = 0;   // [triBlocks] by triangle, then by cache slot
+    uint32_t* flatSlots = nullptr; size_t flatCap = 0;   // 3 cache slots per triangle, submission order (indexed mode)
     uint32_t cacheSize = 0, deindexed = 0;
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
     bool pending = false;        // enqueued since the last overflow check
@@ -156,6 +158,8 @@ int ensure_large(reb_ctx* ctx, uint32_t nTris) {
     return REB_OK;
 }
 
+void fill_pass(reb_ctx* ctx, int kind, PassConst& pc);
+
 // Draw-list preprocessing (runs when a list changes, not per frame — the reference does the analogous work in
 // RenderScene::Init: PopulateMeshDrawCalls / SortOpaqueMeshes, RenderScene.cpp:94-125): running primitive counters,
 // the vertex range every draw references (device reduction) and from it the layout of the post-transform cache.
@@ -219,8 +223,37 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         ps.cacheCap = (size_t)slots;
     }
     ps.cacheSize = (uint32_t)slots;
-    ps.draws.assign(draws, draws + n);
+    {   // per-256-element block lookup tables: draw holding the first triangle / cache slot of the block
+        const uint32_t tb = (uint32_t)((tri + 255) / 256), sb = (uint32_t)((slots + 255) / 256);
+        std::vector<uint32_t> tbl((size_t)tb + sb);
+        uint32_t d = 0;
+        for (uint32_t b = 0; b < tb; ++b) { while (d + 1 < n && dd[d + 1].firstTri <= b * 256ull) ++d; tbl[b] = d; }
+        d = 0;
+        for (uint32_t b = 0; b < sb; ++b) { while (d + 1 < n && dd[d + 1].cacheBase <= b * 256ull) ++d; tbl[(size_t)tb + b] = d; }
+        if (tbl.size() > ps.blockDrawCap) {
+            int rc = dev_alloc(ctx, &ps.blockDraw, tbl.size());
+            if (rc) return rc;
+            ps.blockDrawCap = tbl.size();
+        }
+        if (!tbl.empty()) {
+            CU(cudaMemcpyAsync(ps.blockDraw, tbl.data(), tbl.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+        }
+        ps.triBlocks = tb;
+    }
     ps.nDraws = n; ps.nTris = (uint32_t)tri;
+    if (!ps.deindexed && tri) {   // index stream re-based into cache-slot space
+        if (3 * tri > ps.flatCap) {
+            int rc = dev_alloc(ctx, &ps.flatSlots, (size_t)(3 * tri));
+            if (rc) return rc;
+            ps.flatCap = (size_t)(3 * tri);
+        }
+        PassConst pc;
+        fill_pass(ctx, kind, pc);
+        launch_flatten_slots(pc, ps.flatSlots, ctx->stream); ctx->launches++;
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    ps.draws.assign(draws, draws + n);
     ps.valid = true;
     return REB_OK;
 }
@@ -237,6 +270,9 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
+    pc.tileCount = ctx->tileCount; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
+    pc.flatSlots = ps.flatSlots;
+    pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + 8 * kind;
     if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
     else { pc.rank = 0; pc.nRanks = 1; pc.bandH = 64; }
@@ -252,22 +288,19 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     if ((rc = ensure_tiles(ctx, nTiles))) return rc;
     fill_pass(ctx, kind, pc);
     CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
-    // slots: 0 fill, 1 setup+small raster, 2 bin count, 3 scan, 4 bin scatter, 5 tile stage
+    // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
     auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
     if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
-    if (ps.nTris) { launch_vertex(pc, kind == 0, ctx->stream); ctx->launches++; }
     mark(1);
-    if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->stream); ctx->launches++; }
+    if (ps.nTris) { launch_vertex(pc, kind == 0, ctx->stream); ctx->launches++; }
     mark(2);
-    launch_bin_count(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
+    if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(3);
-    launch_scan_tiles(pc, ctx->tileCount, ctx->tileStart, ctx->listCap, ctx->stream); ctx->launches++;
+    if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(4);
-    launch_bin_scatter(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
-    mark(5);
     if (kind == 0) {
-        launch_tile_shadow(pc, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->numSMs, ctx->stream); ctx->launches++;
+        launch_tile_shadow(pc, ctx->stream); ctx->launches++;
     } else {
         ShadeConst sh;
         std::memset(&sh, 0, sizeof sh);
@@ -280,9 +313,9 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
         sh.maxDescriptors = ctx->maxDesc;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
-        launch_tile_forward(pc, sh, ctx->tileCount, ctx->tileStart, ctx->tileList, ctx->listCap, ctx->stream); ctx->launches++;
+        launch_tile_forward(pc, sh, ctx->stream); ctx->launches++;
     }
-    mark(6);
+    mark(5);
     CU(cudaMemcpyAsync(ctx->hStatus + 8 * kind, pc.status, 32, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaGetLastError());
     ps.pending = true;

@@ -55,7 +55,8 @@ int reb_destroy(reb_ctx* ctx) {
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
                     ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount, ctx->tileStart,
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
-                    ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC};
+                    ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
+                    ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -276,7 +277,7 @@ int reb_set_profiling(reb_ctx* ctx, int on) {
     CHECK_CTX();
     CU(cudaSetDevice(ctx->device));
     if (on && !ctx->ev[0][0])
-        for (int k = 0; k < 2; ++k) for (int i = 0; i < 7; ++i) CU(cudaEventCreate(&ctx->ev[k][i]));
+        for (int k = 0; k < 2; ++k) for (int i = 0; i < 6; ++i) CU(cudaEventCreate(&ctx->ev[k][i]));
     ctx->profiling = on != 0;
     return REB_OK;
 }
@@ -286,7 +287,8 @@ int reb_get_kernel_times(reb_ctx* ctx, int pass, float* ms6) {
     if (pass < 0 || pass > 1 || !ms6 || !ctx->ev[0][0]) return fail(ctx, REB_E_INVALID, "reb_get_kernel_times: profiling not enabled / bad args");
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
-    for (int i = 0; i < 6; ++i) {
+    ms6[5] = 0.0f;
+    for (int i = 0; i < 5; ++i) {
         float ms = 0.0f;
         if (cudaEventElapsedTime(&ms, ctx->ev[pass][i], ctx->ev[pass][i + 1]) != cudaSuccess) { ms = 0.0f; cudaGetLastError(); }
         ms6[i] = ms;

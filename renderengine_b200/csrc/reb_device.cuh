@@ -63,7 +63,13 @@ struct PassConst {
     LargeRec* large; uint32_t largeCap;
     LargeRec* huge;               // HUGE_CAP records tested by every tile
     uint32_t tilesX, tilesY;
-    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount
+    uint32_t* tileCount;          // per tile: entries in its large-triangle list (zero outside a pass)
+    uint32_t* tileStart;          // per tile: first entry of its list inside tileList
+    uint32_t* tileList; uint32_t listCap;
+    const uint32_t* flatSlots;    // 3 cache slots per triangle in submission order (indexed mode)
+    const uint32_t* triBlockDraw; // draw containing the first triangle of every 256-triangle block
+    const uint32_t* slotBlockDraw;// draw containing the first cache slot of every 256-slot block
+    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket [6] block counter
     uint32_t rank, nRanks, bandH; // sort-first row bands (forward only)
 };
 
@@ -147,13 +153,11 @@ __device__ __forceinline__ uint32_t find_draw(const DrawDev* __restrict__ draws,
     }
     return lo;
 }
-// CTA-cooperative variant for 256 consecutive keys starting at `first`: one search per CTA, then a short walk.
-// Relies on the sentinel record draws[nDraws] whose key is the exclusive upper bound.  Contains a __syncthreads.
+// Table-assisted variant: blockDraw[v >> 8] is the draw holding key (v & ~255) (host-built when the draw list
+// changes), followed by a short forward walk.  Relies on the sentinel record draws[nDraws].
 template <bool BY_CACHE>
-__device__ __forceinline__ uint32_t find_draw_cta(const DrawDev* __restrict__ draws, uint32_t nDraws, uint32_t first, uint32_t v, uint32_t* sBase) {
-    if (threadIdx.x == 0) *sBase = find_draw<BY_CACHE>(draws, nDraws, first);
-    __syncthreads();
-    uint32_t d = *sBase;
+__device__ __forceinline__ uint32_t find_draw_block(const DrawDev* __restrict__ draws, uint32_t nDraws, const uint32_t* __restrict__ blockDraw, uint32_t v) {
+    uint32_t d = __ldg(blockDraw + (v >> 8));
     while (d + 1 < nDraws && draw_key<BY_CACHE>(draws, d + 1) <= v) ++d;
     return d;
 }

@@ -19,18 +19,13 @@ struct ShadeConst {
 
 void launch_vertex(const PassConst& pc, bool shadow, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
-void launch_setup_raster(const PassConst& pc, bool shadow, cudaStream_t st);
-void launch_bin_count(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
-                      int numSMs, cudaStream_t st);
-void launch_scan_tiles(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t listCap, cudaStream_t st);
-void launch_bin_scatter(const PassConst& pc, uint32_t* tileCount, uint32_t* tileStart, uint32_t* tileList, uint32_t listCap,
-                        int numSMs, cudaStream_t st);
+void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
+void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);
+void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
-void launch_tile_shadow(const PassConst& pc, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList, uint32_t listCap,
-                        int numSMs, cudaStream_t st);
-void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, uint32_t* tileCount, const uint32_t* tileStart, const uint32_t* tileList,
-                         uint32_t listCap, cudaStream_t st);
+void launch_tile_shadow(const PassConst& pc, cudaStream_t st);
+void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st);
 
 }  // namespace reb

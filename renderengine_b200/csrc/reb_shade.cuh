@@ -127,14 +127,12 @@ __device__ __forceinline__ uint32_t pack_srgb8(float4 c) {
 // vertices (exactly the integers triangle setup used), interpolate perspective-correct (Appendix B.10), then the
 // builder-defined Phong main() (Appendix B.11) over phong.glsl + shadow.glsl.
 __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
-    const uint32_t d = find_draw<false>(pc.draws, pc.nDraws, tri);
-    const uint4 dr = __ldg(reinterpret_cast<const uint4*>(pc.draws + d));   // indexOffset, firstTri, material, node
-    const int32_t cacheOffset = __ldg(&pc.draws[d].cacheOffset);
-    const uint32_t* ix = pc.indices + dr.x + 3u * (tri - dr.y);
+    const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
+    const uint32_t materialRaw = __ldg(&pc.draws[d].material);
     int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const uint32_t slot = cache_slot(pc, cacheOffset, tri, (uint32_t)k, __ldg(ix + k));
+        const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         const float4* bc = reinterpret_cast<const float4*>(pc.vtxBC + slot);
         const float4 b = __ldg(bc), c = __ldg(bc + 1);
@@ -164,7 +162,7 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
 #undef REB_INTERP
 
     // bindless material fetch: materials[materialIndex] (pbr.glsl:379 pattern; MaterialDefines.h:88-96)
-    uint32_t mi = dr.z >> 4;
+    uint32_t mi = materialRaw >> 4;
     if (mi >= sh.nMaterials) mi = sh.nMaterials - 1u;
     const float4* mq = reinterpret_cast<const float4*>(sh.materials + (size_t)mi * sh.materialStride);
     const float4 pDiffuse = __ldg(mq), pSpecular = __ldg(mq + 1);
