@@ -59,43 +59,49 @@ __device__ __noinline__ void tile_walk(const PassConst& pc, int32_t X0, int32_t 
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1: persistent CTAs of 256 threads, one triangle per thread per block of 256 triangles.
+// K1: triangle setup + small-triangle raster, WARP-AUTONOMOUS: every warp is an independent persistent
+// worker with private shared-memory queues, so there is no CTA barrier anywhere in the steady state and
+// the load latency of one warp is hidden by the raster arithmetic of the others.
 //
-// Phase 1, per triangle: 3 indices + 3 VtxA gathers (16 B each) from the post-transform cache,
-//   clip-flag logic, facing (int64 shoelace), pixel-centre bbox, classification:
-//     small  (spans <= SMALL_MAX px)  -> compacted into shared memory as 32-bit edge equations,
-//     huge   (> HUGE_TILES tiles)     -> short broadcast list tested by every tile,
-//     large  (everything else)        -> warp-aggregated append to the LargeRec queue; the warp then
-//                                        walks the triangle's tiles and bumps the per-tile counts.
-//   Compaction = warp shuffle scan of a packed (count, rows) word + one pass over the 8 warp totals.
-// Phase 2, one thread per (small triangle, pixel row) work item: back-face-culled and clipped lanes
-//   no longer idle through the raster loop.  Coverage of the row (three incrementally updated 32-bit
-//   edge functions, top-left bias folded in) is first collected into a bit mask with no divergent
-//   branch, then only the covered samples evaluate depth (two IEEE divides) and resolve with one
-//   atomicMin: 64-bit key depthBits<<32 | ~triId into the visibility buffer (forward), or the 32-bit
-//   depth bits into the shadow map itself (shadow).
-// Tail: the last CTA to finish lays out the per-tile lists (start = running cursor; no ordered scan is
-//   needed because list order inside a tile is irrelevant to the min-key resolve).
+// Per batch of 32 triangles (one per lane; batches are strided statically over all resident warps, the
+// cache gathers of batch n+1 are issued before batch n is rasterised):
+//   1. gather 3 VtxA (16 B each) through the flattened slot stream, clip-flag logic, facing (int64
+//      shoelace), pixel-centre bbox, classification:
+//        small (spans <= SMALL_MAX px) -> edge equations appended to the warp's 64-slot record ring, one
+//                                         entry per covered pixel ROW appended to the warp's row ring;
+//        huge  (> HUGE_TILES tiles)    -> short broadcast list tested by every tile;
+//        large (everything else)       -> warp-aggregated append to the LargeRec queue; the warp walks the
+//                                         triangle's tiles and bumps the per-tile counts.
+//   2. while >= 32 rows are pending: one lane per row computes the row's coverage mask (three 32-bit edge
+//      functions stepped incrementally, top-left bias folded in, warp-uniform trip count) and appends one
+//      entry per covered sample to the warp's pixel queue.  Rows of sparse batches accumulate across
+//      batches, so lanes stay busy even when most triangles are culled.
+//   3. one lane per covered sample: depth (two IEEE divides, Appendix B.8) and one atomicMin — 64-bit key
+//      depthBits<<32 | ~triId into the visibility buffer (forward) or the 32-bit depth bits into the
+//      shadow map itself (shadow).  Consecutive lanes hold consecutive samples of a row.
+// Tail (once per CTA): the last CTA to finish lays out the per-tile lists (start = running cursor; no
+// ordered scan is needed because list order inside a tile is irrelevant to the min-key resolve).
 // ---------------------------------------------------------------------------------------------
-constexpr int K1_THREADS = 256;
-constexpr int K1_TRIS = 256;
+constexpr int K1_THREADS = 128;                  // 4 autonomous warps per CTA (24.6 KB of queues)
 constexpr int K1_WARPS = K1_THREADS / 32;
-constexpr int K1_MAX_ROWS = K1_TRIS * (SMALL_MAX + 1);
-constexpr int K1_WQ = 32 * (SMALL_MAX + 1);      // pixel-queue entries per warp: 32 rows x 9 samples
+constexpr int K1_RING = 64;                      // triangle records per warp (32 being appended + <= 32 with pending rows)
+constexpr int K1_ROWQ = 512;                     // row ring: < 32 pending + 32 * (SMALL_MAX + 1) new
+constexpr int K1_PIXQ = 512;                     // pixel ring: < 32 pending + 32 * (SMALL_MAX + 1) new
 
+struct K1Warp {
+    int32_t Ax[3][K1_RING];         // 256 * A_k  (step of the edge function per pixel in x)
+    int32_t By[3][K1_RING];         // 256 * B_k  (step per pixel in y)
+    int32_t C[3][K1_RING];          // unbiased edge value at the bbox origin's pixel centre
+    uint32_t xy[K1_RING];           // x0 | y0 << 16
+    uint32_t whb[K1_RING];          // w | h << 8 | top-left bias of edge k << (16 + k)
+    float z0[K1_RING], dz1[K1_RING], dz2[K1_RING], area[K1_RING];
+    uint32_t idKey[K1_RING];
+    uint16_t rowq[K1_ROWQ];         // slot | j << 8
+    uint16_t pixq[K1_PIXQ];         // slot | i << 6 | j << 10
+};
 struct K1Shared {
-    int32_t Ax[3][K1_TRIS];         // 256 * A_k  (step of the edge function per pixel in x)
-    int32_t By[3][K1_TRIS];         // 256 * B_k  (step per pixel in y)
-    int32_t C[3][K1_TRIS];          // unbiased edge value at the bbox origin's pixel centre
-    uint32_t xy[K1_TRIS];           // x0 | y0 << 16
-    uint32_t whb[K1_TRIS];          // w | h << 8 | top-left bias of edge k << (16 + k)
-    float z0[K1_TRIS], dz1[K1_TRIS], dz2[K1_TRIS], area[K1_TRIS];
-    uint32_t idKey[K1_TRIS];
-    uint16_t rowStart[K1_TRIS];
-    uint16_t itemTri[K1_MAX_ROWS];
-    uint16_t pixq[K1_WARPS][K1_WQ]; // per-warp queue of covered samples: slot | i << 8 | j << 12
-    uint32_t warpTot[K1_WARPS];
-    uint32_t nextBlk, cursor, isLast;
+    K1Warp w[K1_WARPS];
+    uint32_t cursor, isLast;
 };
 
 struct K1Tri {
@@ -122,7 +128,7 @@ __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, con
     t.x0 = max((minX + 127) >> 8, 0); t.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
     t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
     if (t.x0 > t.x1 || t.y0 > t.y1) return;                                         // no pixel centre inside the bbox
-    // unclamped spans keep the 32-bit edge math of phase 2 exact
+    // unclamped spans keep the 32-bit edge math of the row stage exact
     t.isSmall = (maxX - minX) <= SMALL_MAX * 256 && (maxY - minY) <= SMALL_MAX * 256;
     t.isLarge = !t.isSmall;
 }
@@ -166,7 +172,13 @@ __device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uin
     }
 }
 
-__device__ __forceinline__ void k1_store_small(K1Shared& sm, const K1Tri& t, uint32_t tri, uint32_t slot, uint32_t row0) {
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, v, o); if (lane >= (unsigned)o) v += n; }
+    return v;
+}
+
+__device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint32_t tri, uint32_t slot, uint32_t rowPos) {
     const int32_t X[3] = {t.a[0].X, t.a[1].X, t.a[2].X}, Y[3] = {t.a[0].Y, t.a[1].Y, t.a[2].Y};
     const int32_t Px = 256 * t.x0 + 128, Py = 256 * t.y0 + 128;
     const uint32_t h = (uint32_t)(t.y1 - t.y0 + 1);
@@ -176,18 +188,17 @@ __device__ __forceinline__ void k1_store_small(K1Shared& sm, const K1Tri& t, uin
         const int a = (k + 1) % 3, b = (k + 2) % 3;     // edge a->b opposes vertex k
         const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
         const uint32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0u : 1u;   // top-left rule (Appendix B.7)
-        sm.Ax[k][slot] = 256 * A;
-        sm.By[k][slot] = 256 * B;
-        sm.C[k][slot] = A * (Px - X[a]) + B * (Py - Y[a]);
+        ws.Ax[k][slot] = 256 * A;
+        ws.By[k][slot] = 256 * B;
+        ws.C[k][slot] = A * (Px - X[a]) + B * (Py - Y[a]);
         biasBits |= bias << (16 + k);
     }
-    sm.xy[slot] = (uint32_t)t.x0 | ((uint32_t)t.y0 << 16);
-    sm.whb[slot] = (uint32_t)(t.x1 - t.x0 + 1) | (h << 8) | biasBits;
-    sm.z0[slot] = t.a[0].z; sm.dz1[slot] = t.a[1].z - t.a[0].z; sm.dz2[slot] = t.a[2].z - t.a[0].z;
-    sm.area[slot] = (float)(-t.A2);
-    sm.idKey[slot] = ~tri;
-    sm.rowStart[slot] = (uint16_t)row0;
-    for (uint32_t j = 0; j < h; ++j) sm.itemTri[row0 + j] = (uint16_t)slot;
+    ws.xy[slot] = (uint32_t)t.x0 | ((uint32_t)t.y0 << 16);
+    ws.whb[slot] = (uint32_t)(t.x1 - t.x0 + 1) | (h << 8) | biasBits;
+    ws.z0[slot] = t.a[0].z; ws.dz1[slot] = t.a[1].z - t.a[0].z; ws.dz2[slot] = t.a[2].z - t.a[0].z;
+    ws.area[slot] = (float)(-t.A2);
+    ws.idKey[slot] = ~tri;
+    for (uint32_t j = 0; j < h; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(slot | (j << 8));
 }
 
 // Cache slots of the three corners of triangle `tri` (flatSlots: the draw list's index stream re-based into
@@ -204,110 +215,114 @@ __device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uin
     q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
 }
 
-// Persistent CTAs pull blocks of K1_TRIS triangles from a global counter; the cache gathers of the next block
-// are issued before the current block is rasterised (register double buffering), so the
-// slot-table -> vertex load chain overlaps phase 2.
+// Row stage: `cnt` (<= 32) pending rows, one per lane -> coverage masks -> pixel queue entries.
+template <bool SHADOW>
+__device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_t rowHead, uint32_t cnt, uint32_t& pixTail, unsigned lane) {
+    bool active = lane < cnt;
+    uint32_t slot = 0, j = 0, whb = 0;
+    if (active) {
+        const uint32_t e = ws.rowq[(rowHead + lane) & (K1_ROWQ - 1)];
+        slot = e & 0xFFu; j = e >> 8;
+        whb = ws.whb[slot];
+        if (!SHADOW && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
+    }
+    const uint32_t w = active ? (whb & 0xFFu) : 0u;
+    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
+    uint32_t mask = 0;
+    {
+        const int32_t s0 = ws.Ax[0][slot], s1 = ws.Ax[1][slot], s2 = ws.Ax[2][slot];
+        int32_t F0 = ws.C[0][slot] + (int32_t)j * ws.By[0][slot] - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
+        int32_t F1 = ws.C[1][slot] + (int32_t)j * ws.By[1][slot] - (int32_t)((whb >> 17) & 1u);
+        int32_t F2 = ws.C[2][slot] + (int32_t)j * ws.By[2][slot] - (int32_t)((whb >> 18) & 1u);
+#pragma unroll 1
+        for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
+    }
+    mask &= (1u << w) - 1u;
+    const uint32_t n = __popc(mask);
+    const uint32_t incl = warp_incl_scan(n, lane);
+    uint32_t pos = pixTail + incl - n;
+    pixTail += __shfl_sync(0xFFFFFFFFu, incl, 31);
+    const uint32_t tag = slot | (j << 10);
+    while (mask) {
+        const uint32_t i = (uint32_t)__ffs(mask) - 1u;
+        mask &= mask - 1u;
+        ws.pixq[pos++ & (K1_PIXQ - 1)] = (uint16_t)(tag | (i << 6));
+    }
+    __syncwarp();
+}
+
+// Sample stage: `cnt` (<= 32) queued covered samples, one per lane: depth + resolve.
+template <bool SHADOW>
+__device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws, uint32_t pixHead, uint32_t cnt, unsigned lane) {
+    if (lane >= cnt) return;
+    const uint32_t e = ws.pixq[(pixHead + lane) & (K1_PIXQ - 1)];
+    const uint32_t slot = e & 0x3Fu;
+    const int32_t pi = (int32_t)((e >> 6) & 0xFu), pj = (int32_t)(e >> 10);
+    const int32_t u1 = ws.C[1][slot] + pj * ws.By[1][slot] + pi * ws.Ax[1][slot];   // unbiased edge values (Appendix B.8)
+    const int32_t u2 = ws.C[2][slot] + pj * ws.By[2][slot] + pi * ws.Ax[2][slot];
+    const float z = depth_from((float)u1, (float)u2, ws.area[slot], ws.z0[slot], ws.dz1[slot], ws.dz2[slot]);
+    if (!(z >= 0.0f && z <= 1.0f)) return;
+    const uint32_t xy = ws.xy[slot];
+    const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
+    if (SHADOW) atomicMin(pc.depthBits + px, __float_as_uint(z));
+    else atomicMin(pc.vis + px, ((unsigned long long)__float_as_uint(z) << 32) | ws.idKey[slot]);
+}
+
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 4
+#define K1_MIN_BLOCKS 6
 #endif
 template <bool SHADOW>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(const __grid_constant__ PassConst pc) {
     __shared__ K1Shared sm;
+    pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t nBlocks = (pc.nTris + K1_TRIS - 1u) / K1_TRIS;
+    K1Warp& ws = sm.w[warp];
+    const uint32_t nBatches = (pc.nTris + 31u) / 32u;
+    const uint32_t totalWarps = gridDim.x * K1_WARPS;
     bool anyLarge = false;
 
-    uint32_t blk = blockIdx.x;                                   // grid <= nBlocks
-    uint32_t tri = blk * K1_TRIS + threadIdx.x;
+    // static schedule: warp g takes batches g, g + totalWarps, ... (a shared work counter would serialise on one
+    // L2 atomic unit: ~10 cycles per same-address atomic-with-return chip-wide, measured as the top stall)
+    uint32_t batch = blockIdx.x * K1_WARPS + warp;
     uint4 q[3];
-    uint3 ns = k1_load_slots(pc, tri);
-    if (threadIdx.x == 0) sm.nextBlk = gridDim.x + atomicAdd(&pc.status[6], 1u);
-    __syncthreads();
-    uint32_t nblk = sm.nextBlk;
-    k1_gather(pc, tri, ns, q);
-    ns = k1_load_slots(pc, nblk * K1_TRIS + threadIdx.x);          // slots run two blocks ahead, gathers one
-    __syncthreads();                                               // (everyone has read nextBlk before thread 0 rewrites it)
-    while (blk < nBlocks) {
-        uint32_t nnblk = 0;
-        if (threadIdx.x == 0) nnblk = gridDim.x + atomicAdd(&pc.status[6], 1u);   // the block after next (dynamic schedule)
+    {
+        const uint32_t tri = batch * 32u + lane;
+        k1_gather(pc, tri, k1_load_slots(pc, tri), q);
+    }
+    uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
+    while (batch < nBatches) {
+        const uint32_t nbatch = batch + totalWarps;
+        const uint32_t tri = batch * 32u + lane, ntri = nbatch * 32u + lane;
+        const uint3 ns = k1_load_slots(pc, ntri);                  // in flight during classification
 
-        // ---- phase 1: classify, emit large, compact small ------------------------------------------------
+        // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
         k1_classify(pc, tri < pc.nTris, q, t);
         anyLarge = anyLarge || t.isLarge;
         k1_emit_large(pc, t, tri, lane);
-        const uint32_t mine = t.isSmall ? (1u | ((uint32_t)(t.y1 - t.y0 + 1) << 16)) : 0u;   // packed (count, rows)
-        uint32_t incl = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= (unsigned)o) incl += n; }
-        if (lane == 31) sm.warpTot[warp] = incl;
-        __syncthreads();
-        uint32_t base = 0, total = 0;
-#pragma unroll
-        for (int wgt = 0; wgt < K1_WARPS; ++wgt) { const uint32_t v = sm.warpTot[wgt]; if (wgt < (int)warp) base += v; total += v; }
-        const uint32_t nRows = total >> 16;
-        if (t.isSmall) { const uint32_t excl = base + incl - mine; k1_store_small(sm, t, tri, excl & 0xFFFFu, excl >> 16); }
-        const uint32_t ntri = nblk * K1_TRIS + threadIdx.x;
-        k1_gather(pc, ntri, ns, q);                                 // in flight during phase 2 (slots arrived an iteration ago)
-        if (threadIdx.x == 0) sm.nextBlk = nnblk;
-        __syncthreads();
-        ns = k1_load_slots(pc, sm.nextBlk * K1_TRIS + threadIdx.x);
+        const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
+        const uint32_t h = t.isSmall ? (uint32_t)(t.y1 - t.y0 + 1) : 0u;
+        const uint32_t hIncl = warp_incl_scan(h, lane);
+        if (t.isSmall) k1_store_small(ws, t, tri, (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1), rowTail + hIncl - h);
+        ringPos += __popc(smallMask);
+        rowTail += __shfl_sync(0xFFFFFFFFu, hIncl, 31);
+        k1_gather(pc, ntri, ns, q);                                 // in flight during the raster stages
+        __syncwarp();
 
-        // ---- phase 2, per warp: 32 (small triangle, pixel row) items -> coverage masks -> queue of covered
-        //      samples -> one lane per covered sample (depth + atomicMin) ------------------------------------
-        uint16_t* wq = sm.pixq[warp];
-        for (uint32_t ibase = warp * 32u; ibase < nRows; ibase += K1_THREADS) {     // warp-uniform trip count
-            const uint32_t item = ibase + lane;
-            bool active = item < nRows;
-            uint32_t tS = 0, j = 0, whb = 0;
-            if (active) {
-                tS = sm.itemTri[item];
-                j = item - sm.rowStart[tS];
-                whb = sm.whb[tS];
-                if (!SHADOW && !row_owned((sm.xy[tS] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
-            }
-            const uint32_t w = active ? (whb & 0xFFu) : 0u;
-            const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
-            uint32_t mask = 0;
-            {
-                const int32_t s0 = sm.Ax[0][tS], s1 = sm.Ax[1][tS], s2 = sm.Ax[2][tS];
-                int32_t F0 = sm.C[0][tS] + (int32_t)j * sm.By[0][tS] - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
-                int32_t F1 = sm.C[1][tS] + (int32_t)j * sm.By[1][tS] - (int32_t)((whb >> 17) & 1u);
-                int32_t F2 = sm.C[2][tS] + (int32_t)j * sm.By[2][tS] - (int32_t)((whb >> 18) & 1u);
-#pragma unroll 1
-                for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
-            }
-            mask &= (1u << w) - 1u;
-            const uint32_t cnt = __popc(mask);
-            uint32_t qi = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, qi, o); if (lane >= (unsigned)o) qi += n; }
-            const uint32_t nPix = __shfl_sync(0xFFFFFFFFu, qi, 31);
-            qi -= cnt;
-            const uint32_t tag = tS | (j << 12);
-            while (mask) {
-                const uint32_t i = (uint32_t)__ffs(mask) - 1u;
-                mask &= mask - 1u;
-                wq[qi++] = (uint16_t)(tag | (i << 8));
-            }
-            __syncwarp();
-            for (uint32_t pI = lane; pI < nPix; pI += 32u) {
-                const uint32_t e = wq[pI];
-                const uint32_t ts = e & 0xFFu;
-                const int32_t pi = (int32_t)((e >> 8) & 0xFu), pj = (int32_t)(e >> 12);
-                const int32_t u1 = sm.C[1][ts] + pj * sm.By[1][ts] + pi * sm.Ax[1][ts];   // unbiased edge values (Appendix B.8)
-                const int32_t u2 = sm.C[2][ts] + pj * sm.By[2][ts] + pi * sm.Ax[2][ts];
-                const float z = depth_from((float)u1, (float)u2, sm.area[ts], sm.z0[ts], sm.dz1[ts], sm.dz2[ts]);
-                if (!(z >= 0.0f && z <= 1.0f)) continue;
-                const uint32_t xy = sm.xy[ts];
-                const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
-                if (SHADOW) atomicMin(pc.depthBits + px, __float_as_uint(z));
-                else atomicMin(pc.vis + px, ((unsigned long long)__float_as_uint(z) << 32) | sm.idKey[ts]);
-            }
-            __syncwarp();
+        // ---- 2./3. rows -> samples -> resolve ----------------------------------------------------------------
+        while (rowTail - rowHead >= 32u) {
+            k1_rows<SHADOW>(pc, ws, rowHead, 32u, pixTail, lane);
+            rowHead += 32u;
+            while (pixTail - pixHead >= 32u) { k1_pixels<SHADOW>(pc, ws, pixHead, 32u, lane); pixHead += 32u; }
         }
-        __syncthreads();   // shared arrays are reused by the next block
-        blk = nblk; tri = ntri; nblk = sm.nextBlk;
+        // queued samples reference ring slots of this batch or the one before: drain them before the ring advances
+        if (pixTail != pixHead) { k1_pixels<SHADOW>(pc, ws, pixHead, pixTail - pixHead, lane); pixHead = pixTail; }
+        __syncwarp();
+        batch = nbatch;
+    }
+    if (rowTail != rowHead) {   // drain the rows left over from sparse batches
+        k1_rows<SHADOW>(pc, ws, rowHead, rowTail - rowHead, pixTail, lane);
+        while (pixTail != pixHead) { const uint32_t c = min(32u, pixTail - pixHead); k1_pixels<SHADOW>(pc, ws, pixHead, c, lane); pixHead += c; }
     }
 
     // ---- tail: the last CTA to get here lays out the per-tile lists of the large triangles ------------------
@@ -325,9 +340,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     for (uint32_t i0 = 0; i0 < nTiles; i0 += K1_THREADS) {
         const uint32_t i = i0 + threadIdx.x;
         const uint32_t c = i < nTiles ? __ldcg(pc.tileCount + i) : 0u;
-        uint32_t inc = c;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= (unsigned)o) inc += n; }
+        const uint32_t inc = warp_incl_scan(c, lane);
         uint32_t wbase = 0;
         if (lane == 31 && inc) wbase = atomicAdd(&sm.cursor, inc);
         wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
@@ -356,6 +369,7 @@ __global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ P
 // One warp per triangle (same tile walk as the count).  Does nothing when the queue is empty.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_bin_scatter(const __grid_constant__ PassConst pc) {
+    pdl_enter();
     const uint32_t nLarge = min(pc.status[0], pc.largeCap);
     if (nLarge == 0) return;
     const unsigned lane = threadIdx.x & 31u;
@@ -367,6 +381,7 @@ __global__ void __launch_bounds__(256) k_bin_scatter(const __grid_constant__ Pas
 }
 
 __global__ void k_fill_u32(uint32_t* __restrict__ p, uint32_t v, size_t n) {
+    pdl_enter();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     uint4* p4 = reinterpret_cast<uint4*>(p);
@@ -402,10 +417,10 @@ void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStrea
         else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_setup_raster<false>, K1_THREADS, 0);
         perSM[shadow] = n > 0 ? n : 1;
     }
-    const uint32_t nBlocks = (pc.nTris + K1_TRIS - 1u) / K1_TRIS;
-    const uint32_t grid = std::min<uint32_t>(nBlocks, (uint32_t)(numSMs * perSM[shadow]));
-    if (shadow) k_setup_raster<true><<<grid, K1_THREADS, 0, st>>>(pc);
-    else k_setup_raster<false><<<grid, K1_THREADS, 0, st>>>(pc);
+    const uint32_t nBatches = (pc.nTris + 31u) / 32u;
+    const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[shadow]));
+    if (shadow) launch_k(k_setup_raster<true>, dim3(grid), dim3(K1_THREADS), st, true, pc);
+    else launch_k(k_setup_raster<false>, dim3(grid), dim3(K1_THREADS), st, true, pc);
 }
 
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) {
@@ -414,7 +429,7 @@ void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) 
 }
 
 void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st) {
-    k_bin_scatter<<<numSMs * 4, 256, 0, st>>>(pc);
+    launch_k(k_bin_scatter, dim3(numSMs * 4), dim3(256), st, true, pc);
 }
 
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st) {

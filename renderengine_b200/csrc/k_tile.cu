@@ -29,12 +29,13 @@ struct TileShared {
 
 // Build the staged record of triangle r for the tile whose first pixel is (tx0, ty0); returns false when the
 // triangle cannot touch any pixel centre of the tile (bbox + edge reject at the most-interior corner).
+template <int ROWS>
 __device__ __forceinline__ bool stage_record(const LargeRec& r, int tx0, int ty0, EdgeRec& e) {
     const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
     const int32_t minX = min(r.X0, min(r.X1, r.X2)), maxX = max(r.X0, max(r.X1, r.X2));
     const int32_t minY = min(r.Y0, min(r.Y1, r.Y2)), maxY = max(r.Y0, max(r.Y1, r.Y2));
     const long long cx0 = 256ll * tx0 + 128, cy0 = 256ll * ty0 + 128;
-    const long long spanX = 256ll * (TILE_W - 1), spanY = 256ll * (TILE_H - 1);
+    const long long spanX = 256ll * (TILE_W - 1), spanY = 256ll * (ROWS - 1);
     bool live = !(maxX < cx0 || minX > cx0 + spanX || maxY < cy0 || minY > cy0 + spanY);
     uint32_t bias12 = 0;
 #pragma unroll
@@ -70,7 +71,7 @@ __device__ __forceinline__ unsigned long long merge_large(const LargeRec* __rest
             bool live = false;
             if (threadIdx.x < n) {
                 const LargeRec r = src[idx ? __ldcg(idx + base + threadIdx.x) : base + threadIdx.x];
-                live = stage_record(r, tx0, ty0, sm.stage[threadIdx.x]);
+                live = stage_record<TILE_H>(r, tx0, ty0, sm.stage[threadIdx.x]);
             }
             const unsigned m = __ballot_sync(0xFFFFFFFFu, live);
             if (lane == 0) sm.liveMask[warp] = m;
@@ -104,37 +105,101 @@ __device__ __forceinline__ void tile_sample(int& lx, int& ly) {
     ly = (int)(4u * (warp >> 2) + (lane >> 3));
 }
 
-// Shadow pass tile stage: only tiles touched by large triangles do work (the small ones were resolved by K1's atomics).
-__global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ PassConst pc) {
-    __shared__ TileShared sm;
-    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    const uint32_t tile = blockIdx.y * pc.tilesX + blockIdx.x;
-    uint32_t begin = 0, end = 0;
-    if (nLarge) {
-        const uint32_t cnt = __ldcg(pc.tileCount + tile);
-        if (cnt) {
-            const uint32_t start = __ldcg(pc.tileStart + tile);
-            begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
-            if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm the bin counter for the next pass (only this CTA touches it here)
+// Broadcast-list merge for a block of SUB vertically stacked tiles: every thread carries SUB samples (same
+// column, rows ly + TILE_H * r), so the staging cost and the load latency are amortised over SUB samples.
+template <int SUB>
+__device__ __forceinline__ void merge_huge_shadow(const LargeRec* __restrict__ src, uint32_t count, int tx0, int ty0, int lx, int ly,
+                                                  unsigned long long (&key)[SUB], TileShared& sm) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const int32_t dx = 256 * lx, dy = 256 * ly;
+    for (uint32_t base = 0; base < count; base += STAGE) {
+        const uint32_t n = min((uint32_t)STAGE, count - base);
+        __syncthreads();
+        if (warp < 2) {
+            bool live = false;
+            if (threadIdx.x < n) live = stage_record<SUB * TILE_H>(src[base + threadIdx.x], tx0, ty0, sm.stage[threadIdx.x]);
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, live);
+            if (lane == 0) sm.liveMask[warp] = m;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            unsigned m = sm.liveMask[h];   // CTA-uniform
+            while (m) {
+                const EdgeRec& e = sm.stage[32 * h + __ffs(m) - 1];
+                m &= m - 1;
+                long long F0 = e.E[0] + (long long)e.A[0] * dx + (long long)e.B[0] * dy;
+                long long F1 = e.E[1] + (long long)e.A[1] * dx + (long long)e.B[1] * dy;
+                long long F2 = e.E[2] + (long long)e.A[2] * dx + (long long)e.B[2] * dy;
+                const long long s0 = (long long)e.B[0] * (256 * TILE_H), s1 = (long long)e.B[1] * (256 * TILE_H), s2 = (long long)e.B[2] * (256 * TILE_H);
+#pragma unroll
+                for (int r = 0; r < SUB; ++r, F0 += s0, F1 += s1, F2 += s2) {
+                    if ((F0 | F1 | F2) < 0) continue;
+                    const float z = depth_from((float)(F1 + (long long)(e.bias12 & 1u)), (float)(F2 + (long long)(e.bias12 >> 1)), e.area, e.z0, e.dz1, e.dz2);
+                    if (!(z >= 0.0f && z <= 1.0f)) continue;
+                    const unsigned long long k = (unsigned long long)__float_as_uint(z);
+                    if (k < key[r]) key[r] = k;
+                }
+            }
         }
     }
-    if (nHuge == 0 && begin == end) return;   // CTA-uniform
-    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * TILE_H;
+}
+
+// Shadow pass tile stage: only tiles touched by large triangles do work (the small ones were resolved by K1's
+// atomics).  One CTA per column of SHADOW_SUB stacked tiles, SHADOW_SUB samples per thread, all loads up front.
+constexpr int SHADOW_SUB = 4;
+__global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ PassConst pc) {
+    __shared__ TileShared sm;
+    pdl_enter();
+    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
+    uint32_t begin[SHADOW_SUB], end[SHADOW_SUB];
+    bool anyList = false;
+#pragma unroll
+    for (int r = 0; r < SHADOW_SUB; ++r) {
+        begin[r] = end[r] = 0;
+        const uint32_t tyR = blockIdx.y * SHADOW_SUB + r;
+        if (nLarge && tyR < pc.tilesY) {
+            const uint32_t tile = tyR * pc.tilesX + blockIdx.x;
+            const uint32_t cnt = __ldcg(pc.tileCount + tile);
+            if (cnt) {
+                const uint32_t start = __ldcg(pc.tileStart + tile);
+                begin[r] = min(start, pc.listCap); end[r] = min(start + cnt, pc.listCap);
+                if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm the bin counter for the next pass (only this CTA touches it here)
+                anyList = anyList || begin[r] != end[r];
+            }
+        }
+    }
+    if (nHuge == 0 && !anyList) return;   // CTA-uniform
+    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * (TILE_H * SHADOW_SUB);
     int lx, ly;
     tile_sample(lx, ly);
-    const int x = tx0 + lx, y = ty0 + ly;
-    const bool inb = x < (int)pc.W && y < (int)pc.H;
-    const size_t p = (size_t)y * pc.W + x;
-    const unsigned long long cur = inb ? (unsigned long long)__ldcg(pc.depthBits + p) : 0ull;
-    unsigned long long key = cur;
-    if (nHuge) key = merge_large<true>(pc.huge, nullptr, 0, nHuge, tx0, ty0, lx, ly, key, sm);
-    if (begin != end) key = merge_large<true>(pc.large, pc.tileList, begin, end, tx0, ty0, lx, ly, key, sm);
-    if (inb && key < cur) pc.depthBits[p] = (uint32_t)key;
+    const int x = tx0 + lx;
+    unsigned long long cur[SHADOW_SUB], key[SHADOW_SUB];
+#pragma unroll
+    for (int r = 0; r < SHADOW_SUB; ++r) {
+        const int y = ty0 + TILE_H * r + ly;
+        const bool inb = x < (int)pc.W && y < (int)pc.H;
+        cur[r] = inb ? (unsigned long long)__ldcg(pc.depthBits + (size_t)y * pc.W + x) : 0ull;
+        key[r] = cur[r];
+    }
+    if (nHuge) merge_huge_shadow<SHADOW_SUB>(pc.huge, nHuge, tx0, ty0, lx, ly, key, sm);
+#pragma unroll
+    for (int r = 0; r < SHADOW_SUB; ++r)
+        if (begin[r] != end[r]) key[r] = merge_large<true>(pc.large, pc.tileList, begin[r], end[r], tx0, ty0 + TILE_H * r, lx, ly, key[r], sm);
+#pragma unroll
+    for (int r = 0; r < SHADOW_SUB; ++r) {
+        const int y = ty0 + TILE_H * r + ly;
+        if (key[r] < cur[r]) pc.depthBits[(size_t)y * pc.W + x] = (uint32_t)key[r];   // cur = 0 out of bounds, so never taken there
+    }
 }
 
 // Forward pass tile stage: consume (and reset) the visibility keys, merge large triangles, shade, write.
-__global__ void __launch_bounds__(256, 3) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
+#ifndef KT_MIN_BLOCKS
+#define KT_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(256, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ TileShared sm;
+    pdl_enter();
     const uint32_t tile = blockIdx.y * pc.tilesX + blockIdx.x;
     const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * TILE_H;
     int lx, ly;
@@ -176,11 +241,11 @@ __global__ void __launch_bounds__(256, 3) k_tile_forward(const __grid_constant__
 }
 
 void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
-    k_tile_shadow<<<dim3(pc.tilesX, pc.tilesY), 256, 0, st>>>(pc);
+    launch_k(k_tile_shadow, dim3(pc.tilesX, (pc.tilesY + SHADOW_SUB - 1) / SHADOW_SUB), dim3(256), st, true, pc);
 }
 
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st) {
-    k_tile_forward<<<dim3(pc.tilesX, pc.tilesY), 256, 0, st>>>(pc, sh);
+    launch_k(k_tile_forward, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
 }
 
 }  // namespace reb

@@ -15,10 +15,16 @@
 
 namespace reb {
 
+constexpr int K0_PER_THREAD = 4;   // cache slots per thread: four independent load chains in flight
+
+struct K0In { float4 p, n; uint32_t node; bool valid; };
+
 template <bool SHADOW>
-__global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
-    const uint32_t slot = blockIdx.x * 256u + threadIdx.x;
-    if (slot >= pc.cacheSize) return;
+__device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
+    K0In in;
+    in.valid = slot < pc.cacheSize;
+    in.node = 0; in.p = in.n = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!in.valid) return in;
     // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
     const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, slot);
     uint32_t v;
@@ -28,32 +34,57 @@ __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassCons
     } else {
         v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
     }
-    const uint32_t node = __ldg(&pc.draws[d].node);
-    const float4 p = __ldg(pc.pos4 + v);
-    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * node;
+    in.node = __ldg(&pc.draws[d].node);
+    in.p = __ldg(pc.pos4 + v);
+    if (!SHADOW) in.n = __ldg(pc.nrm4 + v);
+    return in;
+}
+
+template <bool SHADOW>
+__device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t slot, const K0In& in) {
+    if (!in.valid) return;
+    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * in.node;
     float T[16];
 #pragma unroll
     for (int k = 0; k < 4; ++k) { const float4 q = __ldg(Tq + k); T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
     V3 world;
-    const float4 c = vertex_stage<!SHADOW>(pc.PV, T, p.x, p.y, p.z, &world);
-    pc.vtxA[slot] = viewport_snap(c, pc.W, pc.H);
+    const float4 c = vertex_stage<!SHADOW>(pc.PV, T, in.p.x, in.p.y, in.p.z, &world);
+    const VtxA a = viewport_snap(c, pc.W, pc.H);
+    reinterpret_cast<uint4*>(pc.vtxA)[slot] = make_uint4((uint32_t)a.X, (uint32_t)a.Y, __float_as_uint(a.z), a.flags);
     if (!SHADOW) {
-        const float4 n = __ldg(pc.nrm4 + v);
-        const float4* Nq = reinterpret_cast<const float4*>(pc.nmats) + 3u * node;
+        const float4 n = in.n;
+        const float4* Nq = reinterpret_cast<const float4*>(pc.nmats) + 3u * in.node;
         const float4 n0 = __ldg(Nq), n1 = __ldg(Nq + 1), n2 = __ldg(Nq + 2);
         V3 tn;   // glm mat3 * vec3: (m0*x + m1*y) + m2*z   (primitive.vert:55)
         tn.x = (n0.x * n.x + n0.w * n.y) + n1.z * n.z;
         tn.y = (n0.y * n.x + n1.x * n.y) + n1.w * n.z;
         tn.z = (n0.z * n.x + n1.y * n.y) + n2.x * n.z;
         tn = normalize3(tn);
-        VtxBC bc;
-        bc.wx = world.x; bc.wy = world.y; bc.wz = world.z;
-        bc.invw = 1.0f / c.w;                       // Appendix B.10: q_k = b_k * (1 / w_k)
-        bc.nx = tn.x; bc.ny = tn.y; bc.nz = tn.z; bc.pad = 0.0f;
         float4* o = reinterpret_cast<float4*>(pc.vtxBC + slot);
-        o[0] = make_float4(bc.wx, bc.wy, bc.wz, bc.invw);
-        o[1] = make_float4(bc.nx, bc.ny, bc.nz, bc.pad);
+        o[0] = make_float4(world.x, world.y, world.z, 1.0f / c.w);   // Appendix B.10: q_k = b_k * (1 / w_k)
+        o[1] = make_float4(tn.x, tn.y, tn.z, 0.0f);
     }
+}
+
+template <bool SHADOW>
+__global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
+    pdl_enter();
+    const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
+    if (SHADOW) {
+        // fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice
+        const size_t nPix = (size_t)pc.W * pc.H, n4 = nPix / 4u;
+        if (blockIdx.x == 0 && threadIdx.x < (nPix & 3u)) pc.depthBits[4u * n4 + threadIdx.x] = 0x3F800000u;
+        const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
+        const size_t lo = per * blockIdx.x, hi = lo + per < n4 ? lo + per : n4;
+        uint4* dst = reinterpret_cast<uint4*>(pc.depthBits);
+        const uint4 one = make_uint4(0x3F800000u, 0x3F800000u, 0x3F800000u, 0x3F800000u);
+        for (size_t i = lo + threadIdx.x; i < hi; i += 256u) dst[i] = one;
+    }
+    K0In in[K0_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW>(pc, base + 256u * k);
+#pragma unroll
+    for (int k = 0; k < K0_PER_THREAD; ++k) k0_transform_store<SHADOW>(pc, base + 256u * k, in[k]);
 }
 
 // Per-draw referenced vertex range (min, max index), computed when a draw list changes (not per frame).
@@ -76,11 +107,11 @@ __global__ void __launch_bounds__(256) k_draw_ranges(const uint32_t* __restrict_
     if ((threadIdx.x & 31u) == 0 && lo <= hi) { atomicMin(&ranges[2 * d], lo); atomicMax(&ranges[2 * d + 1], hi); }
 }
 
-void launch_vertex(const PassConst& pc, bool shadow, cudaStream_t st) {
+void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) {
     if (pc.cacheSize == 0) return;
-    const uint32_t grid = (pc.cacheSize + 255u) / 256u;
-    if (shadow) k_vertex<true><<<grid, 256, 0, st>>>(pc);
-    else k_vertex<false><<<grid, 256, 0, st>>>(pc);
+    const uint32_t grid = (pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
+    if (shadow) launch_k(k_vertex<true>, dim3(grid), dim3(256), st, pdl, pc);
+    else launch_k(k_vertex<false>, dim3(grid), dim3(256), st, pdl, pc);
 }
 
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st) {

@@ -291,9 +291,10 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
     auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
-    if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
+    // the shadow-map clear is fused into the vertex kernel; an empty draw list still has to clear
+    if (kind == 0 && !ps.nTris) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(1);
-    if (ps.nTris) { launch_vertex(pc, kind == 0, ctx->stream); ctx->launches++; }
+    if (ps.nTris) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
     if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(3);

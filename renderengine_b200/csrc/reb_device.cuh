@@ -76,6 +76,14 @@ struct PassConst {
 // status[2] bits
 constexpr uint32_t OVF_LARGE = 1u, OVF_LIST = 2u;
 
+// Programmatic dependent launch (PDL): every kernel of a pass lets its successor's launch overlap its own last
+// wave (trigger at entry) and waits for its predecessor's completion + memory flush before touching global data.
+// Both are no-ops when the kernel was launched without the programmatic-serialization attribute.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 struct V3 { float x, y, z; };
 
 // glm::mat4 * glm::vec4: (m0*x + m1*y) + (m2*z + m3*w) — ThirdParty/glm/glm/detail/type_mat4x4.inl:562-573

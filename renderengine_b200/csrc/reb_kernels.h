@@ -17,11 +17,23 @@ struct ShadeConst {
     uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;
 };
 
-void launch_vertex(const PassConst& pc, bool shadow, cudaStream_t st);
+// <<<>>> with the programmatic-stream-serialization attribute (PDL) when `pdl` is set
+template <class... KArgs, class... Args>
+inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, bool pdl, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1u : 0u;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);
-void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);
+void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);   // PDL-chained after K1
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
