@@ -137,7 +137,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from renderengine_b200 import capi
+    from renderengine_b200 import capi, parallel
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
@@ -171,7 +171,7 @@ def main():
             else:
                 if rank == 0:
                     ctx.render_shadow(draws)
-                dist.broadcast(shadow_t, src=0)          # NCCL over NVLink; ordered on the current stream
+                parallel.broadcast_shadow(shadow_t, src=0)   # NCCL over NVLink; ordered on the current stream
                 if rank != 0:
                     ctx.shadow_mark_valid()
         ctx.render_forward(draws)

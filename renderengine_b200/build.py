@@ -60,6 +60,20 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def build_host(force=False):
+    """Compile the C++ host facade + demo (renderengine_b200/host) with g++ against libreb.so -> host/reb_host_demo."""
+    hdir = os.path.join(HERE, "host")
+    out = os.path.join(hdir, "reb_host_demo")
+    srcs = [os.path.join(hdir, f) for f in ("RenderEngine.cpp", "demo_main.cpp")]
+    deps = srcs + [os.path.join(hdir, f) for f in ("RenderEngine.h", "reb_math.h")] + [os.path.join(os.path.dirname(HERE), "include", "reb.h"), OUT]
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-o", out] + srcs + ["-L" + HERE, "-lreb", "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/.."]
+    subprocess.check_call(cmd)
+    return out
+
+
 if __name__ == "__main__":
     build(force=True, verbose=True)
     print("built", OUT)
+    print("built", build_host(force=True))
