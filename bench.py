@@ -27,6 +27,23 @@ from renderengine_b200 import scene as sc  # noqa: E402
 METRIC, UNIT = "Mtri/s", "Mtri/s"
 
 
+def profiled_traffic(kind, slot):
+    """dram__bytes_read+write per launch of the named kernel from the newest committed ncu capture (profiles/*_traffic.json)."""
+    import glob
+    name = {"tile_stage": "k_tile_forward" if kind == 1 else "k_tile_shadow",
+            "setup_raster": "k_setup_raster<%s>" % ("forward" if kind == 1 else "shadow"),
+            "vertex": "k_vertex<%s>" % ("forward" if kind == 1 else "shadow")}.get(slot)
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+        try:
+            with open(path) as f:
+                t = json.load(f)["dram_bytes_per_launch"]
+            if name in t:
+                return int(t[name]), os.path.basename(path)
+        except Exception:
+            pass
+    return None, None
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -262,6 +279,7 @@ def main():
         dom_ms = acc[dom[0]][dom[1]]
         dom_bytes = alg.get(dom, 0)
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+        traffic, traffic_src = profiled_traffic(dom[0], dom[1])
         frame_bytes = (b_shadow + b_forward) * frames_per_step
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -273,7 +291,7 @@ def main():
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
                           "frac_of_peak": frame_bytes / (ms * 1e-3) / 1e9 / peak / world, "peak_gbs": peak, "peak_source": peak_src},
             "roofline": {"bound": "hbm", "kernel": f"{'shadow' if dom[0] == 0 else 'forward'}.{dom[1]}", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "algorithmic_bytes_per_launch": dom_bytes,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "kernel_ms": dom_ms, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs, burst copy)"},
             "kernel_ms": kt,
             "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 160 + 128 + 2 * 16 * len(draws),
