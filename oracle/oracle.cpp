@@ -211,6 +211,89 @@ inline float srgb_oetf(float x) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Bindless 2-D textures.  Object semantics follow TextureCache.cpp:67-73,167-197 and
+// Texture.cpp:50-136: R16G16B16A16_UNORM, floor(log2(max(w,h)))+1 mips made by successive 2x linear blits
+// (= 2x2 box average for even extents, edge texels repeated for odd ones), sampler linear / linear /
+// mip-linear with repeat addressing and LOD in [0, mips-1].  The 16x anisotropy the reference requests is
+// implementation-defined in Vulkan; the oracle defines ISOTROPIC trilinear filtering with the LOD taken from
+// the longer screen-space derivative (builder decision).  Colour textures are decoded with
+// the exact sRGB EOTF after filtering, as pbr.glsl:20-26,100-108 does for the base colour; alpha stays linear.
+// ---------------------------------------------------------------------------------------------
+struct Texture {
+    std::vector<std::vector<uint16_t>> mips;   // RGBA16 per level
+    std::vector<uint32_t> w, h;
+    bool srgb = false;
+};
+
+Texture build_texture(const orc_texture& t) {
+    Texture x;
+    x.srgb = t.srgb != 0;
+    x.w.push_back(t.width); x.h.push_back(t.height);
+    x.mips.emplace_back(t.texels, t.texels + (size_t)t.width * t.height * 4);
+    while (x.w.back() > 1 || x.h.back() > 1) {
+        const uint32_t sw = x.w.back(), sh = x.h.back(), dw = std::max(1u, sw / 2), dh = std::max(1u, sh / 2);
+        const std::vector<uint16_t>& src = x.mips.back();
+        std::vector<uint16_t> dst((size_t)dw * dh * 4);
+        for (uint32_t j = 0; j < dh; ++j)
+            for (uint32_t i = 0; i < dw; ++i) {
+                const uint32_t i0 = std::min(2 * i, sw - 1), i1 = std::min(2 * i + 1, sw - 1), j0 = std::min(2 * j, sh - 1), j1 = std::min(2 * j + 1, sh - 1);
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t sum = (uint32_t)src[((size_t)j0 * sw + i0) * 4 + c] + src[((size_t)j0 * sw + i1) * 4 + c] +
+                                         src[((size_t)j1 * sw + i0) * 4 + c] + src[((size_t)j1 * sw + i1) * 4 + c];
+                    dst[((size_t)j * dw + i) * 4 + c] = (uint16_t)((sum + 2u) >> 2);
+                }
+            }
+        x.w.push_back(dw); x.h.push_back(dh);
+        x.mips.push_back(std::move(dst));
+    }
+    return x;
+}
+
+inline int wrap_repeat(int i, int n) { int m = i % n; return m < 0 ? m + n : m; }
+
+V4 sample_bilinear(const Texture& t, int level, float u, float v) {
+    const int w = (int)t.w[level], h = (int)t.h[level];
+    const float x = u * (float)w - 0.5f, y = v * (float)h - 0.5f;
+    const float fx0 = std::floor(x), fy0 = std::floor(y);
+    const float fx = x - fx0, fy = y - fy0;
+    // huge / non-finite coordinates are outside the bit-exact domain; keep the index arithmetic defined
+    const int ix = (std::fabs(fx0) < 1.0e9f) ? (int)fx0 : 0, iy = (std::fabs(fy0) < 1.0e9f) ? (int)fy0 : 0;
+    const int i0 = wrap_repeat(ix, w), i1 = wrap_repeat(ix + 1, w), j0 = wrap_repeat(iy, h), j1 = wrap_repeat(iy + 1, h);
+    const uint16_t* p = t.mips[level].data();
+    float o[4];
+    for (int c = 0; c < 4; ++c) {
+        const float t00 = (float)p[((size_t)j0 * w + i0) * 4 + c] * (1.0f / 65535.0f), t10 = (float)p[((size_t)j0 * w + i1) * 4 + c] * (1.0f / 65535.0f);
+        const float t01 = (float)p[((size_t)j1 * w + i0) * 4 + c] * (1.0f / 65535.0f), t11 = (float)p[((size_t)j1 * w + i1) * 4 + c] * (1.0f / 65535.0f);
+        const float a = t00 + fx * (t10 - t00), b = t01 + fx * (t11 - t01);
+        o[c] = a + fy * (b - a);
+    }
+    return {o[0], o[1], o[2], o[3]};
+}
+
+inline float srgb_eotf(float c) { return (c <= 0.04045f) ? c / 12.92f : std::pow((c + 0.055f) / 1.055f, 2.4f); }
+
+// texture(sampler2D, uv) with implicit derivatives (ddx, ddy = uv at the +x / +y neighbour pixel minus uv here)
+V4 sample_texture(const Texture& t, float u, float v, float dudx, float dvdx, float dudy, float dvdy) {
+    const float W = (float)t.w[0], H = (float)t.h[0];
+    const float rx = std::sqrt((dudx * W) * (dudx * W) + (dvdx * H) * (dvdx * H));
+    const float ry = std::sqrt((dudy * W) * (dudy * W) + (dvdy * H) * (dvdy * H));
+    const float rho = glm_max(rx, ry);
+    const int last = (int)t.mips.size() - 1;
+    float lod = (rho > 0.0f) ? std::log2(rho) : 0.0f;
+    if (!(lod > 0.0f)) lod = 0.0f;
+    if (lod > (float)last) lod = (float)last;
+    const int l0 = (int)std::floor(lod), l1 = std::min(l0 + 1, last);
+    const float f = lod - (float)l0;
+    V4 a = sample_bilinear(t, l0, u, v);
+    if (f > 0.0f && l1 != l0) {
+        const V4 b = sample_bilinear(t, l1, u, v);
+        a = {a.x + f * (b.x - a.x), a.y + f * (b.y - a.y), a.z + f * (b.z - a.z), a.w + f * (b.w - a.w)};
+    }
+    if (t.srgb) a = {srgb_eotf(a.x), srgb_eotf(a.y), srgb_eotf(a.z), a.w};
+    return a;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Geometry front end (Appendix B.1-6)
 // ---------------------------------------------------------------------------------------------
 struct Setup {
@@ -473,6 +556,8 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
     for (uint32_t n = 0; n < sc->nNodes; ++n) normal_matrix(sc->transforms + 16 * (size_t)n, &nmat[9 * (size_t)n]);
     std::vector<Light> lights(sc->nLights);
     for (uint32_t l = 0; l < sc->nLights; ++l) lights[l] = load_light(sc->lights + (size_t)l * sc->lightStride);
+    std::vector<Texture> textures;
+    for (uint32_t t = 0; t < sc->nTextures; ++t) textures.push_back(build_texture(sc->textures[t]));
 
     unsigned nT = thread_count(sc);
     const int W = (int)sc->width, H = (int)sc->height;
@@ -513,15 +598,43 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                                   interp(world[0].z, world[1].z, world[2].z)};
                     V3 normal = {interp(nrm[0].x, nrm[1].x, nrm[2].x), interp(nrm[0].y, nrm[1].y, nrm[2].y),
                                  interp(nrm[0].z, nrm[1].z, nrm[2].z)};
-                    float tu = interp(uv[0][0], uv[1][0], uv[2][0]), tv = interp(uv[0][1], uv[1][1], uv[2][1]);
-                    (void)tu; (void)tv;
-
                     uint32_t matIndex = dr.materialRaw >> 4;   // MaterialHandle::GetIndex (MaterialDefines.h:88-96)
                     const uint8_t* mr = sc->materials + (size_t)matIndex * sc->materialStride;
                     PhongProps props;
+                    uint32_t texHandle[2];
                     std::memcpy(&props.diffuse, mr + 0, 16);
                     std::memcpy(&props.specular, mr + 16, 16);
                     std::memcpy(&props.shininess, mr + 32, 4);
+                    std::memcpy(texHandle, mr + 36, 8);          // diffuseTex, specularTex (phong.glsl:8-12)
+
+                    // bindless texture lookup (pattern of pbr.glsl:100-108): a handle is live iff < MAX_DESCRIPTOR_COUNT
+                    const bool useTex[2] = {texHandle[0] < sc->maxDescriptors && texHandle[0] < textures.size(),
+                                            texHandle[1] < sc->maxDescriptors && texHandle[1] < textures.size()};
+                    if (useTex[0] || useTex[1]) {
+                        // uv here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
+                        float tuv[3][2];
+                        for (int n = 0; n < 3; ++n) {
+                            int64_t Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
+                            float qq[3];
+                            for (int k = 0; k < 3; ++k) {
+                                int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
+                                qq[k] = ((float)F / area) * (1.0f / s.w[k]);
+                            }
+                            float dd = (qq[0] + qq[1]) + qq[2];
+                            tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) / dd;
+                            tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) / dd;
+                        }
+                        const float dudx = tuv[1][0] - tuv[0][0], dvdx = tuv[1][1] - tuv[0][1];
+                        const float dudy = tuv[2][0] - tuv[0][0], dvdy = tuv[2][1] - tuv[0][1];
+                        if (useTex[0]) {
+                            V4 tcol = sample_texture(textures[texHandle[0]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
+                            props.diffuse = {props.diffuse.x * tcol.x, props.diffuse.y * tcol.y, props.diffuse.z * tcol.z, props.diffuse.w * tcol.w};
+                        }
+                        if (useTex[1]) {
+                            V4 tcol = sample_texture(textures[texHandle[1]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
+                            props.specular = {props.specular.x * tcol.x, props.specular.y * tcol.y, props.specular.z * tcol.z, props.specular.w * tcol.w};
+                        }
+                    }
 
                     V4 acc = {0.0f, 0.0f, 0.0f, 0.0f};
                     for (uint32_t l = 0; l < sc->nLights; ++l) {

@@ -145,11 +145,22 @@ class Context:
         assert v.size == 160
         self._ck(self.lib.reb_set_view(self.h, _ptr(v)))
 
+    def register_texture(self, texels, srgb=True):
+        """texels: [H, W, 4] uint16 (R16G16B16A16_UNORM mip 0). Returns the TextureHandle (running index)."""
+        t = np.ascontiguousarray(texels, np.uint16)
+        assert t.ndim == 3 and t.shape[2] == 4
+        desc = RebTextureDesc(t.shape[1], t.shape[0], 0, 1 if srgb else 0)
+        h = C.c_uint32()
+        self._ck(self.lib.reb_register_texture(self.h, C.byref(desc), _ptr(t), C.byref(h)))
+        return h.value
+
     def upload_scene(self, scene):
         self.upload_geometry(scene["verts"], scene["indices"])
         self.upload_transforms(scene["transforms"])
         self.upload_materials(scene["materials"])
         self.upload_lights(scene["lights"])
+        for k, tx in enumerate(scene.get("textures", [])):
+            assert self.register_texture(tx["texels"], tx.get("srgb", 1)) == k
         if scene.get("shadow_size", 0):
             self.shadow_create(scene["shadow_size"])
             self.shadow_set_transform(scene["shadow_view"], scene["shadow_proj"])

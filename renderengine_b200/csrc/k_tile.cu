@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ Pas
 #ifndef KT_MIN_BLOCKS
 #define KT_MIN_BLOCKS 3
 #endif
+template <bool TEXTURED>
 __global__ void __launch_bounds__(256, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ TileShared sm;
     pdl_enter();
@@ -232,7 +233,7 @@ __global__ void __launch_bounds__(256, KT_MIN_BLOCKS) k_tile_forward(const __gri
     if (key != VIS_CLEAR) {
         depth = __uint_as_float((uint32_t)(key >> 32));
         tri = ~(uint32_t)key;
-        if (sh.outSRGB8 || sh.outF32) col = shade_pixel(pc, sh, x, y, tri);
+        if (sh.outSRGB8 || sh.outF32) col = shade_pixel<TEXTURED>(pc, sh, x, y, tri);
     }
     if (sh.outDepth) sh.outDepth[p] = depth;
     if (sh.outTriId) sh.outTriId[p] = tri;
@@ -245,7 +246,9 @@ void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
 }
 
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st) {
-    launch_k(k_tile_forward, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
+    // the textured variant carries the uv derivatives + sampler state; untextured scenes keep the leaner kernel
+    if (sh.nTextures && pc.vtxUV) launch_k(k_tile_forward<true>, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
+    else launch_k(k_tile_forward<false>, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
 }
 
 }  // namespace reb

@@ -63,6 +63,7 @@ __device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t
         float4* o = reinterpret_cast<float4*>(pc.vtxBC + slot);
         o[0] = make_float4(world.x, world.y, world.z, 1.0f / c.w);   // Appendix B.10: q_k = b_k * (1 / w_k)
         o[1] = make_float4(tn.x, tn.y, tn.z, 0.0f);
+        if (pc.vtxUV) pc.vtxUV[slot] = make_float2(in.p.w, in.n.w);   // (u, v) ride in the w lanes of the two SoA streams
     }
 }
 
@@ -105,6 +106,24 @@ __global__ void __launch_bounds__(256) k_draw_ranges(const uint32_t* __restrict_
         hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, o));
     }
     if ((threadIdx.x & 31u) == 0 && lo <= hi) { atomicMin(&ranges[2 * d], lo); atomicMax(&ranges[2 * d + 1], hi); }
+}
+
+// One mip level from the previous one: 2x2 box average in UNORM16 with round-to-nearest (a 2x linear blit, Texture.cpp:50-136)
+__global__ void __launch_bounds__(256) k_mip_down(const ushort4* __restrict__ src, ushort4* __restrict__ dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i >= dw || j >= dh) return;
+    const uint32_t i0 = min(2u * i, sw - 1u), i1 = min(2u * i + 1u, sw - 1u), j0 = min(2u * j, sh - 1u), j1 = min(2u * j + 1u, sh - 1u);
+    const ushort4 a = src[(size_t)j0 * sw + i0], b = src[(size_t)j0 * sw + i1], c = src[(size_t)j1 * sw + i0], d = src[(size_t)j1 * sw + i1];
+    ushort4 o;
+    o.x = (unsigned short)(((uint32_t)a.x + b.x + c.x + d.x + 2u) >> 2);
+    o.y = (unsigned short)(((uint32_t)a.y + b.y + c.y + d.y + 2u) >> 2);
+    o.z = (unsigned short)(((uint32_t)a.z + b.z + c.z + d.z + 2u) >> 2);
+    o.w = (unsigned short)(((uint32_t)a.w + b.w + c.w + d.w + 2u) >> 2);
+    dst[(size_t)j * dw + i] = o;
+}
+
+void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st) {
+    k_mip_down<<<dim3((dw + 255u) / 256u, dh), 256, 0, st>>>(reinterpret_cast<const ushort4*>(src), reinterpret_cast<ushort4*>(dst), sw, sh, dw, dh);
 }
 
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) {

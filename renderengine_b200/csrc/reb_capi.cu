@@ -23,6 +23,7 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward
     uint32_t nDraws = 0, nTris = 0;
     // post-transform vertex cache of this pass (K0 output)
     VtxA* vtxA = nullptr; VtxBC* vtxBC = nullptr; size_t cacheCap = 0;
+    float2* vtxUV = nullptr; size_t uvCap = 0;          // forward pass, only once textures are registered
     uint32_t* blockDraw = nullptr; size_t blockDrawCap = 0; uint32_t triBlocks = 0;   // [triBlocks] by triangle, then by cache slot
     uint32_t* flatSlots = nullptr; size_t flatCap = 0;   // 3 cache slots per triangle, submission order (indexed mode)
     uint32_t cacheSize = 0, deindexed = 0;
@@ -43,6 +44,8 @@ struct reb_ctx {
     float* transforms = nullptr; float* nmats = nullptr; uint32_t nNodes = 0;
     uint8_t* materials = nullptr; uint32_t materialStride = 0, nMaterials = 0;
     uint8_t* lights = nullptr; uint32_t lightStride = 0, nLights = 0;
+    // bindless textures (TextureHandle = running index, Bindless.cpp:221-224)
+    std::vector<TexDev> texHost; std::vector<void*> texAllocs; TexDev* dTextures = nullptr; size_t texTableCap = 0; bool texDirty = false;
     // view
     float view[16], proj[16], PV[16], viewPos[3]; bool haveView = false;
     // shadow (one directional shadow map, F10)
@@ -266,7 +269,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.nTris = ps.nTris; pc.nDraws = ps.nDraws;
     pc.cacheSize = ps.cacheSize; pc.deindexed = ps.deindexed;
     pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.nrm4 = ctx->nrm4; pc.transforms = ctx->transforms; pc.nmats = ctx->nmats;
-    pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC;
+    pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC; pc.vtxUV = (kind == 1 && !ctx->texHost.empty()) ? ps.vtxUV : nullptr;
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
@@ -283,6 +286,23 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     PassConst pc;
     int rc;
     if ((rc = ensure_large(ctx, ps.nTris))) return rc;
+    if (kind == 1 && !ctx->texHost.empty()) {
+        if (ps.cacheSize > ps.uvCap) {
+            CU(cudaStreamSynchronize(ctx->stream));
+            if ((rc = dev_alloc(ctx, &ps.vtxUV, (size_t)ps.cacheSize))) return rc;
+            ps.uvCap = ps.cacheSize;
+        }
+        if (ctx->texDirty) {   // descriptor table: handle -> (pointer, extent, mips)
+            CU(cudaStreamSynchronize(ctx->stream));
+            if (ctx->texHost.size() > ctx->texTableCap) {
+                if ((rc = dev_alloc(ctx, &ctx->dTextures, ctx->texHost.size() * 2))) return rc;
+                ctx->texTableCap = ctx->texHost.size() * 2;
+            }
+            CU(cudaMemcpyAsync(ctx->dTextures, ctx->texHost.data(), ctx->texHost.size() * sizeof(TexDev), cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            ctx->texDirty = false;
+        }
+    }
     fill_pass(ctx, kind, pc);
     const uint32_t nTiles = pc.tilesX * pc.tilesY;
     if ((rc = ensure_tiles(ctx, nTiles))) return rc;
@@ -312,7 +332,7 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         sh.lights = ctx->lights; sh.lightStride = ctx->lightStride;
         const bool useShadow = ctx->shadowMap && ctx->shadowValid && ctx->haveShadowXf;
         sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
-        sh.maxDescriptors = ctx->maxDesc;
+        sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
         launch_tile_forward(pc, sh, ctx->stream); ctx->launches++;
     }

@@ -58,6 +58,9 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};
     for (void* p : ptrs) if (p) cudaFree(p);
+    for (void* p : ctx->texAllocs) cudaFree(p);
+    if (ctx->dTextures) cudaFree(ctx->dTextures);
+    if (ctx->pass[1].vtxUV) cudaFree(ctx->pass[1].vtxUV);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -139,8 +142,36 @@ int reb_upload_lights(reb_ctx* ctx, const void* records, uint32_t stride, uint32
 
 int reb_register_texture(reb_ctx* ctx, const reb_texture_desc* desc, const void* texels, uint32_t* outHandle) {
     CHECK_CTX();
-    (void)desc; (void)texels; (void)outHandle;
-    return fail(ctx, REB_E_UNSUPPORTED, "reb_register_texture: textured materials are not implemented yet");
+    if (!desc || !texels || !outHandle) return fail(ctx, REB_E_INVALID, "reb_register_texture: null argument");
+    if (desc->format != 0) return fail(ctx, REB_E_UNSUPPORTED, "reb_register_texture: only format 0 (R16G16B16A16_UNORM, TextureCache.h:59) is supported");
+    if (desc->width == 0 || desc->height == 0 || desc->width > 16384 || desc->height > 16384) return fail(ctx, REB_E_INVALID, "reb_register_texture: extent must be in 1..16384");
+    if (ctx->texHost.size() >= ctx->maxDesc) return fail(ctx, REB_E_OVERFLOW, "reb_register_texture: descriptor table full (max_descriptors, Bindless.h:76)");
+    CU(cudaSetDevice(ctx->device));
+    TexDev t;
+    std::memset(&t, 0, sizeof t);
+    t.w = desc->width; t.h = desc->height; t.srgb = desc->srgb ? 1u : 0u;
+    size_t total = 0;
+    uint32_t w = t.w, h = t.h, lw[16], lh[16];
+    for (;;) {   // floor(log2(max(w,h))) + 1 levels (TextureCache.cpp:67-73)
+        lw[t.mips] = w; lh[t.mips] = h; t.off[t.mips] = (uint32_t)total; total += (size_t)w * h; ++t.mips;
+        if ((w == 1 && h == 1) || t.mips == 16) break;
+        w = std::max(1u, w / 2); h = std::max(1u, h / 2);
+    }
+    uint16_t* base = nullptr;
+    CU(cudaMalloc(reinterpret_cast<void**>(&base), total * 8));
+    cudaError_t e = cudaMemcpyAsync(base, texels, (size_t)t.w * t.h * 8, cudaMemcpyHostToDevice, ctx->stream);
+    for (uint32_t l = 1; l < t.mips && e == cudaSuccess; ++l) {   // successive 2x linear blits (Texture.cpp:50-136)
+        launch_mip_down(base + (size_t)t.off[l - 1] * 4, base + (size_t)t.off[l] * 4, lw[l - 1], lh[l - 1], lw[l], lh[l], ctx->stream); ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // the host buffer is consumed before returning
+    if (e != cudaSuccess) { cudaFree(base); return fail(ctx, REB_E_CUDA, std::string("reb_register_texture: ") + cudaGetErrorString(e)); }
+    t.base = base;
+    ctx->texAllocs.push_back(base);
+    ctx->texHost.push_back(t);
+    ctx->texDirty = true;
+    *outHandle = (uint32_t)ctx->texHost.size() - 1;
+    return REB_OK;
 }
 
 int reb_shadow_create(reb_ctx* ctx, uint32_t size, uint32_t* outShadowId) {

@@ -37,6 +37,13 @@ struct __align__(16) DrawDev {
 struct __align__(16) VtxA { int32_t X, Y; float z; uint32_t flags; };      // snapped 24.8 position, ndc depth
 struct __align__(16) VtxBC { float wx, wy, wz, invw, nx, ny, nz, pad; };    // world position, 1/w_clip, normalised normal
 
+// Bindless 2-D texture (TextureCache.cpp:67-73,167-197): RGBA16 UNORM, full mip chain in one allocation.
+struct __align__(16) TexDev {
+    const uint16_t* base;         // level 0 first; level l starts at texel off[l]
+    uint32_t w, h, mips, srgb;
+    uint32_t off[16];
+};
+
 // A triangle that goes through the binned tile path: snapped vertices + depth + id (48 B, 3 x 16 B).
 struct __align__(16) LargeRec {
     int32_t X0, Y0, X1, Y1;
@@ -58,6 +65,7 @@ struct PassConst {
     const DrawDev* draws;         // nDraws + 1
     VtxA* vtxA;
     VtxBC* vtxBC;                 // forward only
+    float2* vtxUV;                // forward only, and only when textures are registered
     unsigned long long* vis;      // forward: W*H 64-bit keys
     uint32_t* depthBits;          // shadow: S*S depth bits (the shadow map itself)
     LargeRec* large; uint32_t largeCap;

@@ -13,7 +13,7 @@ struct ShadeConst {
     const uint8_t* lights; uint32_t lightStride;
     const float* shadowMap; uint32_t shadowSize;   // NULL / 0: shadow = 0
     uint32_t maxDescriptors; uint32_t nTextures;
-    const void* textures;
+    const TexDev* textures;
     uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;
 };
 
@@ -30,6 +30,7 @@ inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream
 }
 
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st);
+void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);

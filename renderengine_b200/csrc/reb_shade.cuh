@@ -109,6 +109,50 @@ __device__ __forceinline__ float compute_shadow(const LightDev& light, V3 fragPo
     return shadow;
 }
 
+// ---- bindless textures: isotropic trilinear, repeat, RGBA16 UNORM, optional sRGB decode after filtering.
+// Filtering is continuous in every input, so (like PhongLighting) it is held to the colour tolerance, not to bit-exactness.
+__device__ __forceinline__ int wrap_repeat(int i, int n) { int m = i % n; return m < 0 ? m + n : m; }
+__device__ __forceinline__ float4 unorm16x4(uint2 t) {
+    const float k = 1.0f / 65535.0f;
+    return make_float4((float)(t.x & 0xFFFFu) * k, (float)(t.x >> 16) * k, (float)(t.y & 0xFFFFu) * k, (float)(t.y >> 16) * k);
+}
+__device__ __forceinline__ float4 lerp4(float4 a, float4 b, float f) {
+    return make_float4(a.x + f * (b.x - a.x), a.y + f * (b.y - a.y), a.z + f * (b.z - a.z), a.w + f * (b.w - a.w));
+}
+__device__ __forceinline__ float4 sample_bilinear(const uint2* __restrict__ p, int w, int h, float u, float v) {
+    const float x = u * (float)w - 0.5f, y = v * (float)h - 0.5f;
+    const float fx0 = floorf(x), fy0 = floorf(y);
+    const float fx = x - fx0, fy = y - fy0;
+    const int ix = (fabsf(fx0) < 1.0e9f) ? (int)fx0 : 0, iy = (fabsf(fy0) < 1.0e9f) ? (int)fy0 : 0;
+    const int i0 = wrap_repeat(ix, w), i1 = wrap_repeat(ix + 1, w), j0 = wrap_repeat(iy, h), j1 = wrap_repeat(iy + 1, h);
+    const float4 t00 = unorm16x4(__ldg(p + (size_t)j0 * w + i0)), t10 = unorm16x4(__ldg(p + (size_t)j0 * w + i1));
+    const float4 t01 = unorm16x4(__ldg(p + (size_t)j1 * w + i0)), t11 = unorm16x4(__ldg(p + (size_t)j1 * w + i1));
+    return lerp4(lerp4(t00, t10, fx), lerp4(t01, t11, fx), fy);
+}
+__device__ __forceinline__ float srgb_eotf(float c) { return (c <= 0.04045f) ? c * (1.0f / 12.92f) : exp2f(2.4f * __log2f((c + 0.055f) * (1.0f / 1.055f))); }
+__device__ __forceinline__ float4 sample_texture(const TexDev* __restrict__ table, uint32_t handle, float u, float v, float dudx, float dvdx, float dudy, float dvdy) {
+    const uint4* q = reinterpret_cast<const uint4*>(table + handle);   // 96-B descriptor: {base, w, h} {mips, srgb, off[0..1]} ...
+    const uint4 d0 = __ldg(q), d1 = __ldg(q + 1);
+    const uint2* base = reinterpret_cast<const uint2*>(((unsigned long long)d0.y << 32) | d0.x);
+    const uint32_t tw = d0.z, th = d0.w, mips = d1.x, srgb = d1.y;
+    const uint32_t* offs = reinterpret_cast<const uint32_t*>(table + handle) + 6;   // off[] starts at byte 24
+    const float W = (float)tw, H = (float)th;
+    const float rx = sqrtf((dudx * W) * (dudx * W) + (dvdx * H) * (dvdx * H));
+    const float ry = sqrtf((dudy * W) * (dudy * W) + (dvdy * H) * (dvdy * H));
+    const float rho = fmaxf(rx, ry);
+    const int last = (int)mips - 1;
+    float lod = (rho > 0.0f) ? __log2f(rho) : 0.0f;
+    if (!(lod > 0.0f)) lod = 0.0f;
+    if (lod > (float)last) lod = (float)last;
+    const int l0 = (int)floorf(lod), l1 = min(l0 + 1, last);
+    const float f = lod - (float)l0;
+    float4 a = sample_bilinear(base + __ldg(offs + l0), max((int)(tw >> l0), 1), max((int)(th >> l0), 1), u, v);
+    if (f > 0.0f && l1 != l0)
+        a = lerp4(a, sample_bilinear(base + __ldg(offs + l1), max((int)(tw >> l1), 1), max((int)(th >> l1), 1), u, v), f);
+    if (srgb) a = make_float4(srgb_eotf(a.x), srgb_eotf(a.y), srgb_eotf(a.z), a.w);
+    return a;
+}
+
 __device__ __forceinline__ uint32_t quant8(float x) {
     if (!(x > 0.0f)) return 0u;
     if (x >= 1.0f) return 255u;
@@ -126,6 +170,7 @@ __device__ __forceinline__ uint32_t pack_srgb8(float4 c) {
 // Shade the sample at pixel (x, y) won by primitive `tri`: re-derive the barycentrics from the cached snapped
 // vertices (exactly the integers triangle setup used), interpolate perspective-correct (Appendix B.10), then the
 // builder-defined Phong main() (Appendix B.11) over phong.glsl + shadow.glsl.
+template <bool TEXTURED>
 __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
     const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
     const uint32_t materialRaw = __ldg(&pc.draws[d].material);
@@ -165,9 +210,46 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
     uint32_t mi = materialRaw >> 4;
     if (mi >= sh.nMaterials) mi = sh.nMaterials - 1u;
     const float4* mq = reinterpret_cast<const float4*>(sh.materials + (size_t)mi * sh.materialStride);
-    const float4 pDiffuse = __ldg(mq), pSpecular = __ldg(mq + 1);
+    float4 pDiffuse = __ldg(mq), pSpecular = __ldg(mq + 1);
     const float4 mExtra = __ldg(mq + 2);   // shininess, diffuseTex, specularTex, pad
     const float shininess = mExtra.x;
+    const uint32_t texD = __float_as_uint(mExtra.y), texS = __float_as_uint(mExtra.z);
+    const uint32_t texLimit = min(sh.maxDescriptors, sh.nTextures);   // live iff handle < MAX_DESCRIPTOR_COUNT (bindless.glsl:14) and registered
+    if (TEXTURED && (texD < texLimit || texS < texLimit) && pc.vtxUV != nullptr) {
+        // uv here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives, as the oracle)
+        float2 uvv[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+            uvv[k] = __ldg(pc.vtxUV + slot);
+        }
+        float tu[3], tv[3];
+#pragma unroll
+        for (int n = 0; n < 3; ++n) {
+            const long long Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
+            float qq[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int a = (k + 1) % 3, b = (k + 2) % 3;
+                const long long A = (long long)Y[b] - Y[a];
+                const long long B = -((long long)X[b] - X[a]);
+                const long long F = A * (Qx - X[a]) + B * (Qy - Y[a]);
+                qq[k] = ((float)F / area) * invw[k];
+            }
+            const float dd = (qq[0] + qq[1]) + qq[2];
+            tu[n] = ((qq[0] * uvv[0].x + qq[1] * uvv[1].x) + qq[2] * uvv[2].x) / dd;
+            tv[n] = ((qq[0] * uvv[0].y + qq[1] * uvv[1].y) + qq[2] * uvv[2].y) / dd;
+        }
+        const float dudx = tu[1] - tu[0], dvdx = tv[1] - tv[0], dudy = tu[2] - tu[0], dvdy = tv[2] - tv[0];
+        if (texD < texLimit) {
+            const float4 c = sample_texture(sh.textures, texD, tu[0], tv[0], dudx, dvdx, dudy, dvdy);
+            pDiffuse = make_float4(pDiffuse.x * c.x, pDiffuse.y * c.y, pDiffuse.z * c.z, pDiffuse.w * c.w);
+        }
+        if (texS < texLimit) {
+            const float4 c = sample_texture(sh.textures, texS, tu[0], tv[0], dudx, dvdx, dudy, dvdy);
+            pSpecular = make_float4(pSpecular.x * c.x, pSpecular.y * c.y, pSpecular.z * c.z, pSpecular.w * c.w);
+        }
+    }
 
     const V3 viewPos = {sh.viewPos[0], sh.viewPos[1], sh.viewPos[2]};
     float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);

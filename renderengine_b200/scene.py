@@ -213,12 +213,30 @@ CONFIGS = {
     # name: grid (nx, nz), level, target, shadow size, materials   
     "C1": dict(grid=(10, 5), level=3, width=1280, height=720, shadow_size=0, n_materials=4),
     "C2": dict(grid=(7, 7), level=5, width=1920, height=1080, shadow_size=2048, n_materials=8),
-    "C3": dict(grid=(16, 8), level=6, width=3840, height=2160, shadow_size=2048, n_materials=1024),
-    "C4": dict(grid=(16, 8), level=6, width=7680, height=4320, shadow_size=2048, n_materials=1024),
+    "C3": dict(grid=(16, 8), level=6, width=3840, height=2160, shadow_size=2048, n_materials=1024, n_textures=4096, tex_size=64),
+    "C4": dict(grid=(16, 8), level=6, width=7680, height=4320, shadow_size=2048, n_materials=1024, n_textures=4096, tex_size=64),
     "C5": dict(grid=(14, 7), level=5, width=1920, height=1080, shadow_size=2048, n_materials=8),
     "tiny": dict(grid=(3, 2), level=2, width=160, height=96, shadow_size=128, n_materials=3),
     "small": dict(grid=(4, 3), level=3, width=640, height=360, shadow_size=512, n_materials=5),
+    "small_tex": dict(grid=(4, 3), level=3, width=640, height=360, shadow_size=512, n_materials=5, n_textures=7, tex_size=32),
 }
+
+
+def make_textures(n, size, seed=1234):
+    """n procedural R16G16B16A16_UNORM textures (checker / noise, 64x64 by default): even handles are
+    sRGB-encoded colour maps, odd handles linear (specular) maps."""
+    rng = np.random.default_rng(seed + 77)
+    yy, xx = np.mgrid[0:size, 0:size]
+    out = []
+    for k in range(n):
+        cell = 2 << (k % 3)
+        checker = (((xx // cell) + (yy // cell)) & 1).astype(np.float64)
+        base = rng.uniform(0.25, 1.0, 3); alt = rng.uniform(0.05, 0.6, 3)
+        noise = rng.uniform(-0.08, 0.08, (size, size, 1))
+        rgb = np.clip(checker[..., None] * base + (1 - checker[..., None]) * alt + noise, 0.0, 1.0)
+        tex = np.concatenate([rgb, np.ones((size, size, 1))], axis=2)
+        out.append(dict(texels=np.round(tex * 65535.0).astype(np.uint16), srgb=1 if k % 2 == 0 else 0))
+    return out
 
 
 def camera_for(extent_x, extent_z, width, height, azimuth=0.0, fov=45.0, near=0.01, far=100.0):
@@ -243,6 +261,7 @@ def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
     cfg.update(overrides)
     nx, nz = cfg["grid"]; level = cfg["level"]
     W, H, S, M = cfg["width"], cfg["height"], cfg["shadow_size"], cfg["n_materials"]
+    n_tex, tex_size = cfg.get("n_textures", 0), cfg.get("tex_size", 64)
     rng = np.random.default_rng(seed)
     sv, st = icosphere(level)
     n_s = nx * nz
@@ -275,17 +294,21 @@ def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
     # RenderScene::SortOpaqueMeshes: by (materialHandle raw, sceneNodeID)
     draws = np.array(sorted(draws, key=lambda d: (d[2], d[3])), np.uint32)
     shin = np.array([8, 16, 32, 64], f32)
+    def tex_of(k, which):   # material k samples texture 2k (sRGB colour) and, every other material, 2k+1 (linear specular)
+        if not n_tex or (which == 1 and k % 2):
+            return INVALID_HANDLE
+        return (2 * k + which) % n_tex
     materials = np.stack([pack_material(np.r_[rng.uniform(0.2, 1.0, 3), 1.0].astype(f32), np.array([0.5, 0.5, 0.5, 1], f32),
-                                        shin[k % 4]) for k in range(n_mat)])
+                                        shin[k % 4], tex_of(k, 0), tex_of(k, 1)) for k in range(n_mat)])
     if ground:
-        materials[M] = pack_material(np.array([0.8, 0.8, 0.8, 1], f32), np.array([0.2, 0.2, 0.2, 1], f32), 16.0)
+        materials[M] = pack_material(np.array([0.8, 0.8, 0.8, 1], f32), np.array([0.2, 0.2, 0.2, 1], f32), 16.0, tex_of(M, 0))
     ldir = _norm([-0.3, -1.0, -0.2])
     lights = np.stack([pack_light(LIGHT_DIRECTIONAL, (-ldir * f32(50)).astype(f32), ldir, [0.1] * 4, [1.0] * 4, [1.0] * 4)])
     eye, view, proj = camera_for(ex, ez, W, H, azimuth)
     scene = dict(config=config if isinstance(config, str) else "custom", verts=verts, indices=indices, transforms=transforms,
                  draws=draws, materials=materials, lights=lights, view=pack_view(view, proj, eye), width=W, height=H,
                  shadow_size=S, max_descriptors=8192, n_triangles=int(indices.size // 3), n_vertices=int(len(verts)),
-                 eye=eye, view_mat=view, proj_mat=proj, boxes=boxes, extent=(ex, ez), textures=[])
+                 eye=eye, view_mat=view, proj_mat=proj, boxes=boxes, extent=(ex, ez), textures=make_textures(n_tex, tex_size, seed) if n_tex else [])
     if S:
         all_min = np.array([-ex - 1.5, -1.05, -ez - 1.5], f32) if ground else np.array([-ex, -1, -ez], f32)
         all_max = np.array([ex + 1.5, 1, ez + 1.5], f32) if ground else np.array([ex, 1, ez], f32)
