@@ -379,10 +379,12 @@ inline Edges make_edges(const Setup& s) {
 }
 
 // B.8 depth at a covered sample; F1, F2 are the unbiased edge values of vertices 1 and 2.
+// Revision r1b: the barycentrics are formed with ONE IEEE reciprocal per triangle, b = float(F) * (1 / |A2|),
+// the way a rasteriser's plane-equation setup does it (the first revision divided per sample).
 inline float depth_at(const Setup& s, int64_t F1, int64_t F2) {
-    float area = (float)(-s.A2);
-    float b1 = (float)F1 / area;
-    float b2 = (float)F2 / area;
+    float inv = 1.0f / (float)(-s.A2);
+    float b1 = (float)F1 * inv;
+    float b2 = (float)F2 * inv;
     float z = (s.z[0] + b1 * (s.z[1] - s.z[0])) + b2 * (s.z[2] - s.z[0]);
     if (z == 0.0f) z = 0.0f;   // canonicalise -0
     return z;
@@ -585,15 +587,16 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                     setup_triangle(pp, c, tri, s);
                     Edges e = make_edges(s);
                     int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
-                    float area = (float)(-s.A2);
+                    float inv = 1.0f / (float)(-s.A2);
                     float b[3], q[3];
                     for (int k = 0; k < 3; ++k) {
                         int64_t F = e.A[k] * Px + e.B[k] * Py + e.C[k];
-                        b[k] = (float)F / area;
+                        b[k] = (float)F * inv;
                         q[k] = b[k] * (1.0f / s.w[k]);   // B.10 perspective-correct weights
                     }
                     float den = (q[0] + q[1]) + q[2];
-                    auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) / den; };
+                    float rden = 1.0f / den;             // r1b: one reciprocal per fragment, then multiplies
+                    auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) * rden; };
                     V3 fragPos = {interp(world[0].x, world[1].x, world[2].x), interp(world[0].y, world[1].y, world[2].y),
                                   interp(world[0].z, world[1].z, world[2].z)};
                     V3 normal = {interp(nrm[0].x, nrm[1].x, nrm[2].x), interp(nrm[0].y, nrm[1].y, nrm[2].y),
@@ -618,11 +621,11 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                             float qq[3];
                             for (int k = 0; k < 3; ++k) {
                                 int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
-                                qq[k] = ((float)F / area) * (1.0f / s.w[k]);
+                                qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
                             }
-                            float dd = (qq[0] + qq[1]) + qq[2];
-                            tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) / dd;
-                            tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) / dd;
+                            float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
+                            tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) * rdd;
+                            tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) * rdd;
                         }
                         const float dudx = tuv[1][0] - tuv[0][0], dvdx = tuv[1][1] - tuv[0][1];
                         const float dudy = tuv[2][0] - tuv[0][0], dvdy = tuv[2][1] - tuv[0][1];

@@ -94,7 +94,7 @@ struct K1Warp {
     int32_t C[3][K1_RING];          // unbiased edge value at the bbox origin's pixel centre
     uint32_t xy[K1_RING];           // x0 | y0 << 16
     uint32_t whb[K1_RING];          // w | h << 8 | top-left bias of edge k << (16 + k)
-    float z0[K1_RING], dz1[K1_RING], dz2[K1_RING], area[K1_RING];
+    float z0[K1_RING], dz1[K1_RING], dz2[K1_RING], inv[K1_RING];   // inv = 1 / |A2|
     uint32_t idKey[K1_RING];
     uint16_t rowq[K1_ROWQ];         // slot | j << 8
     uint16_t pixq[K1_PIXQ];         // slot | i << 6 | j << 10
@@ -196,7 +196,7 @@ __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint3
     ws.xy[slot] = (uint32_t)t.x0 | ((uint32_t)t.y0 << 16);
     ws.whb[slot] = (uint32_t)(t.x1 - t.x0 + 1) | (h << 8) | biasBits;
     ws.z0[slot] = t.a[0].z; ws.dz1[slot] = t.a[1].z - t.a[0].z; ws.dz2[slot] = t.a[2].z - t.a[0].z;
-    ws.area[slot] = (float)(-t.A2);
+    ws.inv[slot] = 1.0f / (float)(-t.A2);
     ws.idKey[slot] = ~tri;
     for (uint32_t j = 0; j < h; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(slot | (j << 8));
 }
@@ -260,7 +260,7 @@ __device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws,
     const int32_t pi = (int32_t)((e >> 6) & 0xFu), pj = (int32_t)(e >> 10);
     const int32_t u1 = ws.C[1][slot] + pj * ws.By[1][slot] + pi * ws.Ax[1][slot];   // unbiased edge values (Appendix B.8)
     const int32_t u2 = ws.C[2][slot] + pj * ws.By[2][slot] + pi * ws.Ax[2][slot];
-    const float z = depth_from((float)u1, (float)u2, ws.area[slot], ws.z0[slot], ws.dz1[slot], ws.dz2[slot]);
+    const float z = depth_from((float)u1, (float)u2, ws.inv[slot], ws.z0[slot], ws.dz1[slot], ws.dz2[slot]);
     if (!(z >= 0.0f && z <= 1.0f)) return;
     const uint32_t xy = ws.xy[slot];
     const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;

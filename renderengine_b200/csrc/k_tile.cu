@@ -1,10 +1,15 @@
-// k_tile.cu — K3: the tile stage.  One CTA (256 threads) per TILE_W x TILE_H screen tile on a 2-D grid, one
-// thread per sample, each warp owning an 8 x 4 pixel block (compact footprint: neighbouring samples share
-// triangles, so the post-transform-cache gathers of a warp fall into few sectors).  The tile's visibility
-// keys live in registers (one per thread); the large triangles that touch the tile (broadcast list + binned
-// list) are staged through shared memory as edge equations relative to the tile origin; coverage uses the
-// top-left rule with 64-bit edge functions and an early-Z key compare; then (forward pass) every sample is
-// shaded in place: attribute reconstruction, bindless material fetch, Phong + 3x3 PCF.
+// k_tile.cu — K3: the tile stage.  Every WARP is an independent worker that owns an 8-px-wide block of samples
+// (compact footprint: neighbouring samples share triangles, so the post-transform-cache gathers of a warp fall
+// into few sectors).  The visibility keys of the block live in registers; the large triangles that touch it
+// (broadcast list + binned list of the enclosing 32 x 8 tile) are staged 32 at a time — one per lane — into the
+// warp's private slice of shared memory as edge equations relative to the block origin, then tested by every lane
+// with the top-left rule, 64-bit edge functions and a min-key compare (early-Z and later-primitive-wins in one).
+// There is no CTA barrier anywhere in this file.
+//   shadow pass : the surviving depth of every covered sample is merged into the map with one fire-and-forget
+//                 atomicMin (the small triangles were resolved the same way by K1), so the map is never read here.
+//   forward pass: persistent CTAs stride over the tiles; the visibility key of the NEXT tile is loaded before the
+//                 current one is shaded (software prefetch), then every sample is shaded in place: attribute
+//                 reconstruction, bindless material fetch, Phong + 3x3 PCF.
 //
 // Reference: fixed-function raster/depth state GraphicsPipelineCache.cpp:280-340; fragment work
 // phong.glsl:39-81 + shadow.glsl:24-56; clears RenderScene.cpp:217-220 / ShadowSystem.cpp:111-127.
@@ -13,29 +18,26 @@
 
 namespace reb {
 
-constexpr int STAGE = 64;   // large-triangle records staged per round (two warps' worth)
+constexpr int KT_THREADS = 256, KT_WARPS = KT_THREADS / 32;
+constexpr int BLK_W = 8, BLK_ROWS = 4;   // a warp's lanes: 8 columns x 4 rows; SUB stacked copies 4 rows apart
 
-struct EdgeRec {            // one staged large triangle, relative to the tile's first pixel centre
-    long long E[3];         // biased edge value at the tile origin (covered iff E + A*dx + B*dy >= 0 for all three)
-    int32_t A[3], B[3];
-    float area, z0, dz1, dz2;
-    uint32_t idKey, bias12; // bias12: bit 0 = bias of edge 1, bit 1 = bias of edge 2 (to recover the unbiased values)
+// One warp's staging area: up to 32 large triangles (one per lane), SoA so the per-lane writes are conflict-free
+// and the per-record reads are broadcasts.  Edge values are relative to the block's first pixel centre.
+struct WarpStage {
+    long long E[3][32];         // biased edge value at the block origin (covered iff E + A*dx + B*dy >= 0 for all three)
+    int32_t A[3][32], B[3][32];
+    float inv[32], z0[32], dz1[32], dz2[32];   // inv = 1 / |A2|
+    uint32_t idKey[32], bias12[32];   // bias12: bit 0 = bias of edge 1, bit 1 = bias of edge 2 (to recover the unbiased values)
 };
 
-struct TileShared {
-    EdgeRec stage[STAGE];
-    uint32_t liveMask[2];
-};
-
-// Build the staged record of triangle r for the tile whose first pixel is (tx0, ty0); returns false when the
-// triangle cannot touch any pixel centre of the tile (bbox + edge reject at the most-interior corner).
-template <int ROWS>
-__device__ __forceinline__ bool stage_record(const LargeRec& r, int tx0, int ty0, EdgeRec& e) {
+// Stage triangle r for the block whose first pixel is (bx0, by0) and that spans BLK_W x rows pixels; returns false
+// when the triangle cannot touch any pixel centre of the block (bbox + edge reject at the most-interior corner).
+__device__ __forceinline__ bool stage_record(const LargeRec& r, int bx0, int by0, int rows, WarpStage& ws, unsigned lane) {
     const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
     const int32_t minX = min(r.X0, min(r.X1, r.X2)), maxX = max(r.X0, max(r.X1, r.X2));
     const int32_t minY = min(r.Y0, min(r.Y1, r.Y2)), maxY = max(r.Y0, max(r.Y1, r.Y2));
-    const long long cx0 = 256ll * tx0 + 128, cy0 = 256ll * ty0 + 128;
-    const long long spanX = 256ll * (TILE_W - 1), spanY = 256ll * (ROWS - 1);
+    const long long cx0 = 256ll * bx0 + 128, cy0 = 256ll * by0 + 128;
+    const long long spanX = 256ll * (BLK_W - 1), spanY = 256ll * (rows - 1);
     bool live = !(maxX < cx0 || minX > cx0 + spanX || maxY < cy0 || minY > cy0 + spanY);
     uint32_t bias12 = 0;
 #pragma unroll
@@ -44,195 +46,201 @@ __device__ __forceinline__ bool stage_record(const LargeRec& r, int tx0, int ty0
         const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
         const int32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
         const long long E = (long long)A * (cx0 - X[a]) + (long long)B * (cy0 - Y[a]) - bias;
-        e.A[k] = A; e.B[k] = B; e.E[k] = E;
+        ws.A[k][lane] = A; ws.B[k][lane] = B; ws.E[k][lane] = E;
         const long long Emax = E + (A > 0 ? (long long)A * spanX : 0ll) + (B > 0 ? (long long)B * spanY : 0ll);
         live = live && (Emax >= 0);
         if (k > 0) bias12 |= (uint32_t)bias << (k - 1);
     }
     const long long A2 = (long long)(X[1] - X[0]) * (long long)(Y[2] - Y[0]) - (long long)(X[2] - X[0]) * (long long)(Y[1] - Y[0]);
-    e.area = (float)(-A2);
-    e.z0 = r.z0; e.dz1 = r.z1 - r.z0; e.dz2 = r.z2 - r.z0;
-    e.idKey = ~r.triId; e.bias12 = bias12;
+    ws.inv[lane] = 1.0f / (float)(-A2);
+    ws.z0[lane] = r.z0; ws.dz1[lane] = r.z1 - r.z0; ws.dz2[lane] = r.z2 - r.z0;
+    ws.idKey[lane] = ~r.triId; ws.bias12[lane] = bias12;
     return live;
 }
 
-// Merge a list of large triangles into this thread's key (depthBits<<32 | ~triId, or the bare depth bits for the
-// shadow pass; minimum wins).  idx == nullptr: records src[begin..end) directly (broadcast list); otherwise
-// src[idx[i]] for i in [begin, end) (binned list).  (lx, ly) = sample position inside the tile.
-template <bool SHADOW>
-__device__ __forceinline__ unsigned long long merge_large(const LargeRec* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t begin,
-                                                          uint32_t end, int tx0, int ty0, int lx, int ly, unsigned long long key, TileShared& sm) {
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const int32_t dx = 256 * lx, dy = 256 * ly;
-    for (uint32_t base = begin; base < end; base += STAGE) {
-        const uint32_t n = min((uint32_t)STAGE, end - base);
-        __syncthreads();
-        if (warp < 2) {
-            bool live = false;
-            if (threadIdx.x < n) {
-                const LargeRec r = src[idx ? __ldcg(idx + base + threadIdx.x) : base + threadIdx.x];
-                live = stage_record<TILE_H>(r, tx0, ty0, sm.stage[threadIdx.x]);
-            }
-            const unsigned m = __ballot_sync(0xFFFFFFFFu, live);
-            if (lane == 0) sm.liveMask[warp] = m;
-        }
-        __syncthreads();
+// Inner test of one staged triangle against this lane's SUB samples (F* = biased edge values at sample 0, s* = their
+// step to the next sample BLK_ROWS rows below).
+template <bool SHADOW, int SUB>
+__device__ __forceinline__ void test_samples(long long F0, long long F1, long long F2, long long s0, long long s1, long long s2, uint32_t bias12,
+                                             float inv, float z0, float dz1, float dz2, uint32_t idKey, unsigned long long (&key)[SUB]) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            unsigned m = sm.liveMask[h];   // CTA-uniform
-            while (m) {
-                const EdgeRec& e = sm.stage[32 * h + __ffs(m) - 1];
-                m &= m - 1;
-                const long long F0 = e.E[0] + (long long)e.A[0] * dx + (long long)e.B[0] * dy;
-                const long long F1 = e.E[1] + (long long)e.A[1] * dx + (long long)e.B[1] * dy;
-                const long long F2 = e.E[2] + (long long)e.A[2] * dx + (long long)e.B[2] * dy;
-                if ((F0 | F1 | F2) < 0) continue;
-                const float z = depth_from((float)(F1 + (long long)(e.bias12 & 1u)), (float)(F2 + (long long)(e.bias12 >> 1)), e.area, e.z0, e.dz1, e.dz2);
-                if (!(z >= 0.0f && z <= 1.0f)) continue;
-                const unsigned long long k = SHADOW ? (unsigned long long)__float_as_uint(z)
-                                                    : (((unsigned long long)__float_as_uint(z) << 32) | e.idKey);
-                if (k < key) key = k;   // early-Z + later-primitive-wins in one compare
-            }
-        }
-    }
-    return key;
-}
-
-// sample position of this thread inside its tile: warp w owns the 8 x 4 block at (8 * (w & 3), 4 * (w >> 2))
-__device__ __forceinline__ void tile_sample(int& lx, int& ly) {
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    lx = (int)(8u * (warp & 3u) + (lane & 7u));
-    ly = (int)(4u * (warp >> 2) + (lane >> 3));
-}
-
-// Broadcast-list merge for a block of SUB vertically stacked tiles: every thread carries SUB samples (same
-// column, rows ly + TILE_H * r), so the staging cost and the load latency are amortised over SUB samples.
-template <int SUB>
-__device__ __forceinline__ void merge_huge_shadow(const LargeRec* __restrict__ src, uint32_t count, int tx0, int ty0, int lx, int ly,
-                                                  unsigned long long (&key)[SUB], TileShared& sm) {
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const int32_t dx = 256 * lx, dy = 256 * ly;
-    for (uint32_t base = 0; base < count; base += STAGE) {
-        const uint32_t n = min((uint32_t)STAGE, count - base);
-        __syncthreads();
-        if (warp < 2) {
-            bool live = false;
-            if (threadIdx.x < n) live = stage_record<SUB * TILE_H>(src[base + threadIdx.x], tx0, ty0, sm.stage[threadIdx.x]);
-            const unsigned m = __ballot_sync(0xFFFFFFFFu, live);
-            if (lane == 0) sm.liveMask[warp] = m;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            unsigned m = sm.liveMask[h];   // CTA-uniform
-            while (m) {
-                const EdgeRec& e = sm.stage[32 * h + __ffs(m) - 1];
-                m &= m - 1;
-                long long F0 = e.E[0] + (long long)e.A[0] * dx + (long long)e.B[0] * dy;
-                long long F1 = e.E[1] + (long long)e.A[1] * dx + (long long)e.B[1] * dy;
-                long long F2 = e.E[2] + (long long)e.A[2] * dx + (long long)e.B[2] * dy;
-                const long long s0 = (long long)e.B[0] * (256 * TILE_H), s1 = (long long)e.B[1] * (256 * TILE_H), s2 = (long long)e.B[2] * (256 * TILE_H);
-#pragma unroll
-                for (int r = 0; r < SUB; ++r, F0 += s0, F1 += s1, F2 += s2) {
-                    if ((F0 | F1 | F2) < 0) continue;
-                    const float z = depth_from((float)(F1 + (long long)(e.bias12 & 1u)), (float)(F2 + (long long)(e.bias12 >> 1)), e.area, e.z0, e.dz1, e.dz2);
-                    if (!(z >= 0.0f && z <= 1.0f)) continue;
-                    const unsigned long long k = (unsigned long long)__float_as_uint(z);
-                    if (k < key[r]) key[r] = k;
-                }
-            }
-        }
+    for (int r = 0; r < SUB; ++r, F0 += s0, F1 += s1, F2 += s2) {
+        if ((F0 | F1 | F2) < 0) continue;
+        const float z = depth_from((float)(F1 + (long long)(bias12 & 1u)), (float)(F2 + (long long)(bias12 >> 1)), inv, z0, dz1, dz2);
+        if (!(z >= 0.0f && z <= 1.0f)) continue;
+        const unsigned long long k = SHADOW ? (unsigned long long)__float_as_uint(z) : (((unsigned long long)__float_as_uint(z) << 32) | idKey);
+        if (k < key[r]) key[r] = k;   // early-Z + later-primitive-wins in one compare
     }
 }
 
-// Shadow pass tile stage: only tiles touched by large triangles do work (the small ones were resolved by K1's
-// atomics).  One CTA per column of SHADOW_SUB stacked tiles, SHADOW_SUB samples per thread, all loads up front.
+// Merge a binned list of large triangles (src[idx[i]], i in [begin, end)) into this lane's SUB keys (depthBits<<32 |
+// ~triId, or the bare depth bits for the shadow pass; minimum wins).  Lane sample r sits at (lx, ly + BLK_ROWS * r)
+// inside the block.  begin / end / bx0 / by0 are warp-uniform.
+template <bool SHADOW, int SUB>
+__device__ __forceinline__ void merge_large(const LargeRec* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t begin, uint32_t end,
+                                            int bx0, int by0, int lx, int ly, unsigned long long (&key)[SUB], WarpStage& ws, unsigned lane) {
+    const int32_t dx = 256 * lx, dy = 256 * ly;
+    for (uint32_t base = begin; base < end; base += 32u) {
+        const uint32_t n = min(32u, end - base);
+        bool live = false;
+        if (lane < n) {
+            const LargeRec r = src[__ldcg(idx + base + lane)];
+            live = stage_record(r, bx0, by0, BLK_ROWS * SUB, ws, lane);
+        }
+        unsigned m = __ballot_sync(0xFFFFFFFFu, live);
+        __syncwarp();
+        while (m) {
+            const int s = __ffs(m) - 1;
+            m &= m - 1;
+            const long long F0 = ws.E[0][s] + mulw(ws.A[0][s], dx) + mulw(ws.B[0][s], dy);
+            const long long F1 = ws.E[1][s] + mulw(ws.A[1][s], dx) + mulw(ws.B[1][s], dy);
+            const long long F2 = ws.E[2][s] + mulw(ws.A[2][s], dx) + mulw(ws.B[2][s], dy);
+            test_samples<SHADOW, SUB>(F0, F1, F2, mulw(ws.B[0][s], 256 * BLK_ROWS), mulw(ws.B[1][s], 256 * BLK_ROWS), mulw(ws.B[2][s], 256 * BLK_ROWS), ws.bias12[s], ws.inv[s], ws.z0[s], ws.dz1[s], ws.dz2[s], ws.idKey[s], key);
+        }
+        __syncwarp();
+    }
+}
+
+// The broadcast list (triangles covering > HUGE_TILES tiles) as screen-space edge equations, built once per CTA.
+struct HugeStage {
+    long long E[3][HUGE_CAP];       // biased edge value at the centre of pixel (0, 0)
+    int32_t A[3][HUGE_CAP], B[3][HUGE_CAP];
+    int32_t minX[HUGE_CAP], maxX[HUGE_CAP], minY[HUGE_CAP], maxY[HUGE_CAP];
+    float inv[HUGE_CAP], z0[HUGE_CAP], dz1[HUGE_CAP], dz2[HUGE_CAP];
+    uint32_t idKey[HUGE_CAP], bias12[HUGE_CAP];
+};
+
+__device__ __forceinline__ void stage_huge(const LargeRec* __restrict__ huge, uint32_t nHuge, HugeStage& hs) {
+    const uint32_t i = threadIdx.x;
+    if (i >= nHuge) return;
+    const LargeRec r = huge[i];
+    const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
+    hs.minX[i] = min(r.X0, min(r.X1, r.X2)); hs.maxX[i] = max(r.X0, max(r.X1, r.X2));
+    hs.minY[i] = min(r.Y0, min(r.Y1, r.Y2)); hs.maxY[i] = max(r.Y0, max(r.Y1, r.Y2));
+    uint32_t bias12 = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int a = (k + 1) % 3, b = (k + 2) % 3;
+        const int32_t A = Y[b] - Y[a], B = -(X[b] - X[a]);
+        const int32_t bias = ((A > 0) || (A == 0 && B > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
+        hs.A[k][i] = A; hs.B[k][i] = B;
+        hs.E[k][i] = (long long)A * (128ll - X[a]) + (long long)B * (128ll - Y[a]) - bias;
+        if (k > 0) bias12 |= (uint32_t)bias << (k - 1);
+    }
+    const long long A2 = (long long)(X[1] - X[0]) * (long long)(Y[2] - Y[0]) - (long long)(X[2] - X[0]) * (long long)(Y[1] - Y[0]);
+    hs.inv[i] = 1.0f / (float)(-A2);
+    hs.z0[i] = r.z0; hs.dz1[i] = r.z1 - r.z0; hs.dz2[i] = r.z2 - r.z0;
+    hs.idKey[i] = ~r.triId; hs.bias12[i] = bias12;
+}
+
+// Merge the broadcast list into this lane's SUB keys; (x, y) = absolute pixel of sample 0, block = [bx0, bx0 + BLK_W) x
+// [by0, by0 + BLK_ROWS * SUB).  One lane per record decides whether the record can touch the block at all.
+template <bool SHADOW, int SUB>
+__device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, int bx0, int by0, int x, int y, unsigned long long (&key)[SUB], unsigned lane) {
+    const long long cx0 = 256ll * bx0 + 128, cy0 = 256ll * by0 + 128;
+    const long long spanX = 256ll * (BLK_W - 1), spanY = 256ll * (BLK_ROWS * SUB - 1);
+    for (uint32_t base = 0; base < nHuge; base += 32u) {
+        const uint32_t i = base + lane;
+        bool live = false;
+        if (i < nHuge) {
+            live = !(hs.maxX[i] < cx0 || hs.minX[i] > cx0 + spanX || hs.maxY[i] < cy0 || hs.minY[i] > cy0 + spanY);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int32_t A = hs.A[k][i], B = hs.B[k][i];
+                const long long Emax = hs.E[k][i] + mulw(A, 256 * bx0) + mulw(B, 256 * by0) + (A > 0 ? mulw(A, (int32_t)spanX) : 0ll) + (B > 0 ? mulw(B, (int32_t)spanY) : 0ll);
+                live = live && (Emax >= 0);
+            }
+        }
+        unsigned m = __ballot_sync(0xFFFFFFFFu, live);
+        while (m) {
+            const int s = (int)base + __ffs(m) - 1;
+            m &= m - 1;
+            const long long F0 = hs.E[0][s] + mulw(hs.A[0][s], 256 * x) + mulw(hs.B[0][s], 256 * y);
+            const long long F1 = hs.E[1][s] + mulw(hs.A[1][s], 256 * x) + mulw(hs.B[1][s], 256 * y);
+            const long long F2 = hs.E[2][s] + mulw(hs.A[2][s], 256 * x) + mulw(hs.B[2][s], 256 * y);
+            test_samples<SHADOW, SUB>(F0, F1, F2, mulw(hs.B[0][s], 256 * BLK_ROWS), mulw(hs.B[1][s], 256 * BLK_ROWS), mulw(hs.B[2][s], 256 * BLK_ROWS), hs.bias12[s], hs.inv[s], hs.z0[s], hs.dz1[s], hs.dz2[s], hs.idKey[s], key);
+        }
+    }
+}
+
+// Shadow pass tile stage: only blocks touched by large triangles do work (the small ones were resolved by K1's
+// atomics).  CTA = 32 x 32 px, warp = 8 x 16 px (SHADOW_SUB samples per lane).  The map is only written.
 constexpr int SHADOW_SUB = 4;
-__global__ void __launch_bounds__(256) k_tile_shadow(const __grid_constant__ PassConst pc) {
-    __shared__ TileShared sm;
+__global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constant__ PassConst pc) {
+    __shared__ WarpStage stage[KT_WARPS];
+    __shared__ HugeStage hs;
     pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
     const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    uint32_t begin[SHADOW_SUB], end[SHADOW_SUB];
-    bool anyList = false;
+    if (nLarge == 0 && nHuge == 0) return;
+    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }   // the only CTA barrier: once per CTA, CTA-uniform
+    const int bx0 = (int)blockIdx.x * TILE_W + BLK_W * (int)(warp & 3u);
+    const int by0 = (int)blockIdx.y * (BLK_ROWS * SHADOW_SUB * 2) + BLK_ROWS * SHADOW_SUB * (int)(warp >> 2);
+    if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
+    uint32_t begin[2] = {0, 0}, end[2] = {0, 0};
+    if (nLarge) {
 #pragma unroll
-    for (int r = 0; r < SHADOW_SUB; ++r) {
-        begin[r] = end[r] = 0;
-        const uint32_t tyR = blockIdx.y * SHADOW_SUB + r;
-        if (nLarge && tyR < pc.tilesY) {
-            const uint32_t tile = tyR * pc.tilesX + blockIdx.x;
+        for (int t = 0; t < 2; ++t) {
+            const uint32_t ty = (uint32_t)by0 / TILE_H + t;
+            if (ty >= pc.tilesY) continue;
+            const uint32_t tile = ty * pc.tilesX + blockIdx.x;
             const uint32_t cnt = __ldcg(pc.tileCount + tile);
             if (cnt) {
                 const uint32_t start = __ldcg(pc.tileStart + tile);
-                begin[r] = min(start, pc.listCap); end[r] = min(start + cnt, pc.listCap);
-                if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm the bin counter for the next pass (only this CTA touches it here)
-                anyList = anyList || begin[r] != end[r];
+                begin[t] = min(start, pc.listCap); end[t] = min(start + cnt, pc.listCap);
             }
         }
     }
-    if (nHuge == 0 && !anyList) return;   // CTA-uniform
-    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * (TILE_H * SHADOW_SUB);
-    int lx, ly;
-    tile_sample(lx, ly);
-    const int x = tx0 + lx;
-    unsigned long long cur[SHADOW_SUB], key[SHADOW_SUB];
+    const int lx = (int)(lane & 7u), ly = (int)(lane >> 3);
+    const int x = bx0 + lx;
+    unsigned long long key[SHADOW_SUB];
+#pragma unroll
+    for (int r = 0; r < SHADOW_SUB; ++r) key[r] = 0xFFFFFFFFull;
+    if (nHuge) merge_huge<true, SHADOW_SUB>(hs, nHuge, bx0, by0, x, by0 + ly, key, lane);
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+        if (begin[t] != end[t]) merge_large<true, SHADOW_SUB>(pc.large, pc.tileList, begin[t], end[t], bx0, by0, lx, ly, key, stage[warp], lane);
 #pragma unroll
     for (int r = 0; r < SHADOW_SUB; ++r) {
-        const int y = ty0 + TILE_H * r + ly;
-        const bool inb = x < (int)pc.W && y < (int)pc.H;
-        cur[r] = inb ? (unsigned long long)__ldcg(pc.depthBits + (size_t)y * pc.W + x) : 0ull;
-        key[r] = cur[r];
-    }
-    if (nHuge) merge_huge_shadow<SHADOW_SUB>(pc.huge, nHuge, tx0, ty0, lx, ly, key, sm);
-#pragma unroll
-    for (int r = 0; r < SHADOW_SUB; ++r)
-        if (begin[r] != end[r]) key[r] = merge_large<true>(pc.large, pc.tileList, begin[r], end[r], tx0, ty0 + TILE_H * r, lx, ly, key[r], sm);
-#pragma unroll
-    for (int r = 0; r < SHADOW_SUB; ++r) {
-        const int y = ty0 + TILE_H * r + ly;
-        if (key[r] < cur[r]) pc.depthBits[(size_t)y * pc.W + x] = (uint32_t)key[r];   // cur = 0 out of bounds, so never taken there
+        const int y = by0 + BLK_ROWS * r + ly;
+        if (key[r] != 0xFFFFFFFFull && x < (int)pc.W && y < (int)pc.H) atomicMin(pc.depthBits + (size_t)y * pc.W + x, (uint32_t)key[r]);
     }
 }
 
 // Forward pass tile stage: consume (and reset) the visibility keys, merge large triangles, shade, write.
+// Persistent, warp-autonomous: a warp draws 32 x 8 tiles from a global counter (the draw for the tile after next is
+// in flight while the current one is processed) and walks the tile's eight 8 x 4 blocks; the visibility keys of the
+// next block are loaded before the current block is shaded.
 #ifndef KT_MIN_BLOCKS
 #define KT_MIN_BLOCKS 3
 #endif
+__device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, uint32_t tile, uint32_t b, int lx, int ly) {
+    const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+    const int x = (int)tx * TILE_W + BLK_W * (int)(b & 3u) + lx, y = (int)ty * TILE_H + BLK_ROWS * (int)(b >> 2) + ly;
+    if (x >= (int)pc.W || y >= (int)pc.H || !row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return VIS_CLEAR;
+    return __ldcg(pc.vis + (size_t)y * pc.W + x);
+}
+
+// One 8 x 4 block: re-arm vis, merge large triangles, shade, write.  All arguments but key are warp-uniform.
 template <bool TEXTURED>
-__global__ void __launch_bounds__(256, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
-    __shared__ TileShared sm;
-    pdl_enter();
-    const uint32_t tile = blockIdx.y * pc.tilesX + blockIdx.x;
-    const int tx0 = (int)blockIdx.x * TILE_W, ty0 = (int)blockIdx.y * TILE_H;
-    int lx, ly;
-    tile_sample(lx, ly);
-    const int x = tx0 + lx, y = ty0 + ly;
+__device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& sh, unsigned long long key0, int bx0, int by0, int lx, int ly, uint32_t nHuge,
+                                         const HugeStage& hs, uint32_t begin, uint32_t end, WarpStage& ws, unsigned lane) {
+    if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
+    unsigned long long key[1] = {key0};
+    const int x = bx0 + lx, y = by0 + ly;
     const bool inb = x < (int)pc.W && y < (int)pc.H;
     const size_t p = (size_t)y * pc.W + x;
-    const bool owned = row_owned((uint32_t)ty0, pc.rank, pc.nRanks, pc.bandH);
-    unsigned long long key = VIS_CLEAR;
-    if (inb && owned) key = __ldcg(pc.vis + p);
-    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    uint32_t begin = 0, end = 0;
-    if (nLarge) {
-        const uint32_t cnt = __ldcg(pc.tileCount + tile);
-        if (cnt) {
-            const uint32_t start = __ldcg(pc.tileStart + tile);
-            begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
-            if (threadIdx.x == 0) pc.tileCount[tile] = 0;   // re-arm (only this CTA touches this counter here)
-        }
-    }
-    if (!owned) return;
-    if (inb && key != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
-    if (nHuge) key = merge_large<false>(pc.huge, nullptr, 0, nHuge, tx0, ty0, lx, ly, key, sm);
-    if (begin != end) key = merge_large<false>(pc.large, pc.tileList, begin, end, tx0, ty0, lx, ly, key, sm);
+    if (inb && key[0] != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
+    if (nHuge) merge_huge<false, 1>(hs, nHuge, bx0, by0, x, y, key, lane);
+    if (begin != end) merge_large<false, 1>(pc.large, pc.tileList, begin, end, bx0, by0, lx, ly, key, ws, lane);
     if (!inb) return;
-
     float depth = 1.0f;                    // depth clear 1.0 (RenderScene.cpp:219)
     uint32_t tri = TRI_NONE;
     float4 col = make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (0,0,0,1) (RenderScene.cpp:218)
-    if (key != VIS_CLEAR) {
-        depth = __uint_as_float((uint32_t)(key >> 32));
-        tri = ~(uint32_t)key;
+    if (key[0] != VIS_CLEAR) {
+        depth = __uint_as_float((uint32_t)(key[0] >> 32));
+        tri = ~(uint32_t)key[0];
         if (sh.outSRGB8 || sh.outF32) col = shade_pixel<TEXTURED>(pc, sh, x, y, tri);
     }
     if (sh.outDepth) sh.outDepth[p] = depth;
@@ -241,14 +249,109 @@ __global__ void __launch_bounds__(256, KT_MIN_BLOCKS) k_tile_forward(const __gri
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
 }
 
-void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
-    launch_k(k_tile_shadow, dim3(pc.tilesX, (pc.tilesY + SHADOW_SUB - 1) / SHADOW_SUB), dim3(256), st, true, pc);
+__device__ __forceinline__ void kt_tile_list(const PassConst& pc, uint32_t tile, uint32_t nLarge, uint32_t& begin, uint32_t& end) {
+    begin = end = 0;
+    if (!nLarge) return;
+    const uint32_t cnt = __ldcg(pc.tileCount + tile);
+    if (!cnt) return;
+    const uint32_t start = __ldcg(pc.tileStart + tile);
+    begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
 }
 
-void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st) {
+#ifndef KT_MODE
+#define KT_MODE 1
+#endif
+template <bool TEXTURED>
+__global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
+    __shared__ WarpStage stage[KT_WARPS];
+    __shared__ HugeStage hs;
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
+    const int lx = (int)(lane & 7u), ly = (int)(lane >> 3);
+    const uint32_t nTiles = pc.tilesX * pc.tilesY;
+    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
+#if KT_MODE == 0
+    // one CTA per tile (hardware CTA scheduling), warp = block
+    const uint32_t tile = blockIdx.x;
+    const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+    if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return;
+    const unsigned long long key = kt_load_key(pc, tile, warp, lx, ly);
+    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
+    uint32_t begin, end;
+    kt_tile_list(pc, tile, nLarge, begin, end);
+    kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
+                       stage[warp], lane);
+#elif KT_MODE == 1
+    // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
+    uint32_t tile = blockIdx.x;
+    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, tile, warp, lx, ly) : VIS_CLEAR;
+    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
+    for (; tile < nTiles; tile += gridDim.x) {
+        const unsigned long long key = keyNext;
+        if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, tile + gridDim.x, warp, lx, ly);
+        const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+        if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) continue;
+        uint32_t begin, end;
+        kt_tile_list(pc, tile, nLarge, begin, end);
+        kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
+                           end, stage[warp], lane);
+    }
+#else
+    // persistent autonomous warps: a warp owns whole tiles (first two static, the rest drawn from a counter)
+    uint32_t* const counter = pc.status + 6;
+    const uint32_t totalWarps = gridDim.x * KT_WARPS, gw = blockIdx.x * KT_WARPS + warp;
+    uint32_t tile = gw, draw = totalWarps + gw;
+    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
+    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, tile, 0, lx, ly) : VIS_CLEAR;
+    while (tile < nTiles) {
+        const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+        const bool owned = row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH);
+        uint32_t begin = 0, end = 0;
+        if (owned) kt_tile_list(pc, tile, nLarge, begin, end);
+        uint32_t tileNext = nTiles;
+#pragma unroll 1
+        for (uint32_t b = 0; b < 8u; ++b) {
+            const unsigned long long key = keyNext;
+            if (b < 7u) keyNext = kt_load_key(pc, tile, b + 1u, lx, ly);   // in flight while this block is shaded
+            else {
+                tileNext = __shfl_sync(0xFFFFFFFFu, draw, 0);
+                if (lane == 0) draw = 2u * totalWarps + atomicAdd(counter, 1u);
+                keyNext = tileNext < nTiles ? kt_load_key(pc, tileNext, 0, lx, ly) : VIS_CLEAR;
+            }
+            if (!owned) continue;
+            kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(b & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(b >> 2), lx, ly, nHuge, hs, begin, end,
+                               stage[warp], lane);
+        }
+        tile = tileNext;
+    }
+#endif
+}
+
+void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
+    const uint32_t bh = BLK_ROWS * SHADOW_SUB * 2;
+    launch_k(k_tile_shadow, dim3(pc.tilesX, (pc.H + bh - 1) / bh), dim3(KT_THREADS), st, true, pc);
+}
+
+void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st) {
     // the textured variant carries the uv derivatives + sampler state; untextured scenes keep the leaner kernel
-    if (sh.nTextures && pc.vtxUV) launch_k(k_tile_forward<true>, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
-    else launch_k(k_tile_forward<false>, dim3(pc.tilesX, pc.tilesY), dim3(256), st, true, pc, sh);
+    const bool tex = sh.nTextures && pc.vtxUV;
+    static int perSM[2] = {0, 0};
+    if (!perSM[tex]) {
+        int n = 0;
+        if (tex) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_tile_forward<true>, KT_THREADS, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_tile_forward<false>, KT_THREADS, 0);
+        perSM[tex] = n > 0 ? n : 1;
+    }
+#if KT_MODE == 0
+    const uint32_t grid = pc.tilesX * pc.tilesY;
+#elif KT_MODE == 1
+    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[tex]));
+#else
+    const uint32_t grid = std::min<uint32_t>((pc.tilesX * pc.tilesY + KT_WARPS - 1) / KT_WARPS, (uint32_t)(numSMs * perSM[tex]));
+#endif
+    if (tex) launch_k(k_tile_forward<true>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
+    else launch_k(k_tile_forward<false>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
 }
 
 }  // namespace reb

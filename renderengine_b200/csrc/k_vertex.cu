@@ -71,6 +71,10 @@ template <bool SHADOW>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
     pdl_enter();
     const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
+    // pass prologue (K0 is the first kernel of a pass and is stream-ordered after the previous pass): reset the pass
+    // status words and the per-tile list counters, so the pass needs no memset node and the tile stage no re-arm
+    if (blockIdx.x == 0 && threadIdx.x < 8) pc.status[threadIdx.x] = 0u;
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
     if (SHADOW) {
         // fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice
         const size_t nPix = (size_t)pc.W * pc.H, n4 = nPix / 4u;

@@ -59,7 +59,8 @@ struct reb_ctx {
     uint32_t* tileCount = nullptr; uint32_t* tileStart = nullptr; uint32_t tileCap = 0;
     uint32_t* tileList = nullptr; uint32_t listCap = 0;
     uint32_t* dStatus = nullptr;     // 2 x 8 words
-    uint32_t* hStatus = nullptr;     // pinned mirror
+    uint32_t* hStatus = nullptr;     // pinned + mapped mirror, written by the tile stage kernels
+    uint32_t* hStatusDev = nullptr;  // device-side address of hStatus
     PassState pass[2];
     uint64_t launches = 0, regrows = 0;
     bool profiling = false; cudaEvent_t ev[2][7] = {}; float kernelMs[2][6] = {};   // per-kernel timing slots (diagnostics)
@@ -277,6 +278,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.flatSlots = ps.flatSlots;
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + 8 * kind;
+    pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
     if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
     else { pc.rank = 0; pc.nRanks = 1; pc.bandH = 64; }
 }
@@ -307,7 +309,7 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     const uint32_t nTiles = pc.tilesX * pc.tilesY;
     if ((rc = ensure_tiles(ctx, nTiles))) return rc;
     fill_pass(ctx, kind, pc);
-    CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
+    if (!ps.nTris) CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));   // otherwise K0's prologue resets status + tile counters
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
     auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
@@ -334,10 +336,9 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
         sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
-        launch_tile_forward(pc, sh, ctx->stream); ctx->launches++;
+        launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++;
     }
     mark(5);
-    CU(cudaMemcpyAsync(ctx->hStatus + 8 * kind, pc.status, 32, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaGetLastError());
     ps.pending = true;
     if (kind == 0) ctx->shadowValid = true;

@@ -38,7 +38,8 @@ int reb_create(const reb_params* params, reb_ctx** out) {
     if ((rc = alloc_targets(ctx))) return bail(rc);
     if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 64) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 64) != cudaSuccess ||
         cudaMalloc(reinterpret_cast<void**>(&ctx->huge), 2 * HUGE_CAP * sizeof(LargeRec)) != cudaSuccess ||
-        cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocDefault) != cudaSuccess)
+        cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->hStatusDev), ctx->hStatus, 0) != cudaSuccess)
         return bail(fail(ctx, REB_E_CUDA, "status buffers allocation failed"));
     std::memset(ctx->hStatus, 0, 64);
     ctx->listCap = 4u << 20;

@@ -78,6 +78,7 @@ struct PassConst {
     const uint32_t* triBlockDraw; // draw containing the first triangle of every 256-triangle block
     const uint32_t* slotBlockDraw;// draw containing the first cache slot of every 256-slot block
     uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket [6] block counter
+    uint32_t* hostStatus;         // mapped pinned mirror of status[0..7], written by the tile stage (no D2H copy node)
     uint32_t rank, nRanks, bandH; // sort-first row bands (forward only)
 };
 
@@ -93,6 +94,8 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 struct V3 { float x, y, z; };
+
+__device__ __forceinline__ long long mulw(int32_t a, int32_t b) { return (long long)a * (long long)b; }   // one IMAD.WIDE
 
 // glm::mat4 * glm::vec4: (m0*x + m1*y) + (m2*z + m3*w) — ThirdParty/glm/glm/detail/type_mat4x4.inl:562-573
 __device__ __forceinline__ float4 mat4_mul_point(const float* __restrict__ m, float x, float y, float z) {
@@ -146,10 +149,11 @@ __device__ __forceinline__ VtxA viewport_snap(float4 c, uint32_t W, uint32_t H) 
     return a;
 }
 
-// Appendix B.8: depth from the unbiased edge values of vertices 1 and 2 (dz1 = z1 - z0, dz2 = z2 - z0).
-__device__ __forceinline__ float depth_from(float fF1, float fF2, float area, float z0, float dz1, float dz2) {
-    float b1 = fF1 / area;
-    float b2 = fF2 / area;
+// Appendix B.8 (revision r1b): depth from the unbiased edge values of vertices 1 and 2 (dz1 = z1 - z0, dz2 = z2 - z0);
+// inv = 1.0f / float(|A2|), one IEEE reciprocal per triangle.
+__device__ __forceinline__ float depth_from(float fF1, float fF2, float inv, float z0, float dz1, float dz2) {
+    float b1 = fF1 * inv;
+    float b2 = fF2 * inv;
     float z = (z0 + b1 * dz1) + b2 * dz2;
     if (z == 0.0f) z = 0.0f;
     return z;

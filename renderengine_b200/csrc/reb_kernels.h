@@ -39,6 +39,6 @@ void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
 void launch_tile_shadow(const PassConst& pc, cudaStream_t st);
-void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, cudaStream_t st);
+void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
 
 }  // namespace reb

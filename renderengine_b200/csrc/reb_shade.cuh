@@ -185,21 +185,19 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
         world[k] = {b.x, b.y, b.z}; invw[k] = b.w;
         nrm[k] = {c.x, c.y, c.z};
     }
-    const long long A2 = (long long)(X[1] - X[0]) * (long long)(Y[2] - Y[0]) - (long long)(X[2] - X[0]) * (long long)(Y[1] - Y[0]);
-    const long long Px = 256ll * x + 128, Py = 256ll * y + 128;
-    const float area = (float)(-A2);
+    const long long A2 = mulw(X[1] - X[0], Y[2] - Y[0]) - mulw(X[2] - X[0], Y[1] - Y[0]);
+    const int32_t Px = 256 * x + 128, Py = 256 * y + 128;   // |X|, |Y| <= 2^28 (guard band), so every difference below fits int32
+    const float inv = 1.0f / (float)(-A2);      // Appendix B.8/B.10 revision r1b: one reciprocal per triangle ...
     float q[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int a = (k + 1) % 3, b = (k + 2) % 3;
-        const long long A = (long long)Y[b] - Y[a];
-        const long long B = -((long long)X[b] - X[a]);
-        const long long F = A * (Px - X[a]) + B * (Py - Y[a]);
-        const float bk = (float)F / area;
+        const long long F = mulw(Y[b] - Y[a], Px - X[a]) + mulw(-(X[b] - X[a]), Py - Y[a]);
+        const float bk = (float)F * inv;
         q[k] = bk * invw[k];
     }
-    const float den = (q[0] + q[1]) + q[2];
-#define REB_INTERP(a0, a1, a2) (((q[0] * (a0) + q[1] * (a1)) + q[2] * (a2)) / den)
+    const float rden = 1.0f / ((q[0] + q[1]) + q[2]);   // ... and one per fragment
+#define REB_INTERP(a0, a1, a2) (((q[0] * (a0) + q[1] * (a1)) + q[2] * (a2)) * rden)
     const V3 fragPos = {REB_INTERP(world[0].x, world[1].x, world[2].x), REB_INTERP(world[0].y, world[1].y, world[2].y),
                         REB_INTERP(world[0].z, world[1].z, world[2].z)};
     const V3 normal = {REB_INTERP(nrm[0].x, nrm[1].x, nrm[2].x), REB_INTERP(nrm[0].y, nrm[1].y, nrm[2].y),
@@ -226,19 +224,17 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
         float tu[3], tv[3];
 #pragma unroll
         for (int n = 0; n < 3; ++n) {
-            const long long Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
+            const int32_t Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
             float qq[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const int a = (k + 1) % 3, b = (k + 2) % 3;
-                const long long A = (long long)Y[b] - Y[a];
-                const long long B = -((long long)X[b] - X[a]);
-                const long long F = A * (Qx - X[a]) + B * (Qy - Y[a]);
-                qq[k] = ((float)F / area) * invw[k];
+                const long long F = mulw(Y[b] - Y[a], Qx - X[a]) + mulw(-(X[b] - X[a]), Qy - Y[a]);
+                qq[k] = ((float)F * inv) * invw[k];
             }
-            const float dd = (qq[0] + qq[1]) + qq[2];
-            tu[n] = ((qq[0] * uvv[0].x + qq[1] * uvv[1].x) + qq[2] * uvv[2].x) / dd;
-            tv[n] = ((qq[0] * uvv[0].y + qq[1] * uvv[1].y) + qq[2] * uvv[2].y) / dd;
+            const float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
+            tu[n] = ((qq[0] * uvv[0].x + qq[1] * uvv[1].x) + qq[2] * uvv[2].x) * rdd;
+            tv[n] = ((qq[0] * uvv[0].y + qq[1] * uvv[1].y) + qq[2] * uvv[2].y) * rdd;
         }
         const float dudx = tu[1] - tu[0], dvdx = tv[1] - tv[0], dudy = tu[2] - tu[0], dvdy = tv[2] - tv[0];
         if (texD < texLimit) {
