@@ -188,6 +188,7 @@ def main():
             else:
                 if rank == 0:
                     ctx.render_shadow(draws)
+                    ctx.flush()                                  # the recorded depth pass must be on the stream before the broadcast
                 parallel.broadcast_shadow(shadow_t, src=0)   # NCCL over NVLink; ordered on the current stream
                 if rank != 0:
                     ctx.shadow_mark_valid()

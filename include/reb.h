@@ -94,6 +94,12 @@ int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, ui
 /* RenderScene::RenderBasePass -> MaterialSystem::Draw — RenderScene.cpp:210-242, MaterialSystem.cpp:88-101 */
 int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n);
 
+/* Submit recorded work without waiting (the reference's CommandRingBuffer submit, RenderLoop.cpp:124-132).
+ * reb_render_shadow only RECORDS the depth pass; it is submitted together with the next reb_render_forward (both
+ * vertex stages then run as one kernel when the draw lists match), or by reb_flush / reb_sync / reb_readback /
+ * reb_get_output.  Call reb_flush before consuming the shadow map on the stream yourself (e.g. an NCCL broadcast). */
+int reb_flush(reb_ctx* ctx);
+
 /* swapchain resolve / present (Swapchain.cpp:200-237, RenderLoop.cpp:124-132) become headless buffers */
 int reb_get_output(reb_ctx* ctx, reb_output_kind kind, void** devPtr, uint64_t* bytes);
 int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host);

@@ -335,7 +335,8 @@ inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t 
     for (int k = 0; k < 3; ++k) if (!(c[k].w > 0.0f)) return NEEDS_CLIP;
     float hw = 0.5f * (float)pp.W, hh = 0.5f * (float)pp.H;
     for (int k = 0; k < 3; ++k) {
-        float nx = c[k].x / c[k].w, ny = c[k].y / c[k].w, nz = c[k].z / c[k].w;   // B.4
+        float rw = 1.0f / c[k].w;                                            // B.4 (revision r1b): one IEEE reciprocal per vertex,
+        float nx = c[k].x * rw, ny = c[k].y * rw, nz = c[k].z * rw;          // the same 1/w the varyings use (B.10)
         float xf = hw * nx + hw;
         float yf = hh * ny + hh;
         if (!(std::fabs(xf) <= GUARD_PX) || !(std::fabs(yf) <= GUARD_PX)) return NEEDS_CLIP;

@@ -60,15 +60,19 @@ __device__ __forceinline__ bool stage_record(const LargeRec& r, int bx0, int by0
 
 // Inner test of one staged triangle against this lane's SUB samples (F* = biased edge values at sample 0, s* = their
 // step to the next sample BLK_ROWS rows below).
+template <bool SHADOW> struct KeyOf { typedef unsigned long long type; };
+template <> struct KeyOf<true> { typedef uint32_t type; };   // shadow pass: the bare depth bits
+
 template <bool SHADOW, int SUB>
 __device__ __forceinline__ void test_samples(long long F0, long long F1, long long F2, long long s0, long long s1, long long s2, uint32_t bias12,
-                                             float inv, float z0, float dz1, float dz2, uint32_t idKey, unsigned long long (&key)[SUB]) {
+                                             float inv, float z0, float dz1, float dz2, uint32_t idKey, typename KeyOf<SHADOW>::type (&key)[SUB]) {
 #pragma unroll
     for (int r = 0; r < SUB; ++r, F0 += s0, F1 += s1, F2 += s2) {
         if ((F0 | F1 | F2) < 0) continue;
         const float z = depth_from((float)(F1 + (long long)(bias12 & 1u)), (float)(F2 + (long long)(bias12 >> 1)), inv, z0, dz1, dz2);
         if (!(z >= 0.0f && z <= 1.0f)) continue;
-        const unsigned long long k = SHADOW ? (unsigned long long)__float_as_uint(z) : (((unsigned long long)__float_as_uint(z) << 32) | idKey);
+        const typename KeyOf<SHADOW>::type k = SHADOW ? (typename KeyOf<SHADOW>::type)__float_as_uint(z)
+                                                      : (typename KeyOf<SHADOW>::type)(((unsigned long long)__float_as_uint(z) << 32) | idKey);
         if (k < key[r]) key[r] = k;   // early-Z + later-primitive-wins in one compare
     }
 }
@@ -78,7 +82,7 @@ __device__ __forceinline__ void test_samples(long long F0, long long F1, long lo
 // inside the block.  begin / end / bx0 / by0 are warp-uniform.
 template <bool SHADOW, int SUB>
 __device__ __forceinline__ void merge_large(const LargeRec* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t begin, uint32_t end,
-                                            int bx0, int by0, int lx, int ly, unsigned long long (&key)[SUB], WarpStage& ws, unsigned lane) {
+                                            int bx0, int by0, int lx, int ly, typename KeyOf<SHADOW>::type (&key)[SUB], WarpStage& ws, unsigned lane) {
     const int32_t dx = 256 * lx, dy = 256 * ly;
     for (uint32_t base = begin; base < end; base += 32u) {
         const uint32_t n = min(32u, end - base);
@@ -100,6 +104,8 @@ __device__ __forceinline__ void merge_large(const LargeRec* __restrict__ src, co
         __syncwarp();
     }
 }
+
+constexpr int HUGE_DIRECT = 6;   // broadcast lists up to this long skip the per-block liveness pass
 
 // The broadcast list (triangles covering > HUGE_TILES tiles) as screen-space edge equations, built once per CTA.
 struct HugeStage {
@@ -136,9 +142,22 @@ __device__ __forceinline__ void stage_huge(const LargeRec* __restrict__ huge, ui
 // Merge the broadcast list into this lane's SUB keys; (x, y) = absolute pixel of sample 0, block = [bx0, bx0 + BLK_W) x
 // [by0, by0 + BLK_ROWS * SUB).  One lane per record decides whether the record can touch the block at all.
 template <bool SHADOW, int SUB>
-__device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, int bx0, int by0, int x, int y, unsigned long long (&key)[SUB], unsigned lane) {
-    const long long cx0 = 256ll * bx0 + 128, cy0 = 256ll * by0 + 128;
-    const long long spanX = 256ll * (BLK_W - 1), spanY = 256ll * (BLK_ROWS * SUB - 1);
+__device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, int bx0, int by0, int x, int y, typename KeyOf<SHADOW>::type (&key)[SUB], unsigned lane) {
+    const int32_t cx0 = 256 * bx0 + 128, cy0 = 256 * by0 + 128;
+    const int32_t spanX = 256 * (BLK_W - 1), spanY = 256 * (BLK_ROWS * SUB - 1);
+    if (nHuge <= (uint32_t)HUGE_DIRECT) {
+        // short list (a ground plane is two triangles): a warp-uniform bbox reject, then every lane tests its samples
+        // (cheaper than one lane per record deciding liveness with 64-bit edge evaluations)
+        for (uint32_t s = 0; s < nHuge; ++s) {
+            if (hs.maxX[s] < cx0 || hs.minX[s] > cx0 + spanX || hs.maxY[s] < cy0 || hs.minY[s] > cy0 + spanY) continue;
+            const long long F0 = hs.E[0][s] + mulw(hs.A[0][s], 256 * x) + mulw(hs.B[0][s], 256 * y);
+            const long long F1 = hs.E[1][s] + mulw(hs.A[1][s], 256 * x) + mulw(hs.B[1][s], 256 * y);
+            const long long F2 = hs.E[2][s] + mulw(hs.A[2][s], 256 * x) + mulw(hs.B[2][s], 256 * y);
+            test_samples<SHADOW, SUB>(F0, F1, F2, mulw(hs.B[0][s], 256 * BLK_ROWS), mulw(hs.B[1][s], 256 * BLK_ROWS), mulw(hs.B[2][s], 256 * BLK_ROWS),
+                                      hs.bias12[s], hs.inv[s], hs.z0[s], hs.dz1[s], hs.dz2[s], hs.idKey[s], key);
+        }
+        return;
+    }
     for (uint32_t base = 0; base < nHuge; base += 32u) {
         const uint32_t i = base + lane;
         bool live = false;
@@ -147,7 +166,7 @@ __device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, 
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const int32_t A = hs.A[k][i], B = hs.B[k][i];
-                const long long Emax = hs.E[k][i] + mulw(A, 256 * bx0) + mulw(B, 256 * by0) + (A > 0 ? mulw(A, (int32_t)spanX) : 0ll) + (B > 0 ? mulw(B, (int32_t)spanY) : 0ll);
+                const long long Emax = hs.E[k][i] + mulw(A, 256 * bx0) + mulw(B, 256 * by0) + (A > 0 ? mulw(A, spanX) : 0ll) + (B > 0 ? mulw(B, spanY) : 0ll);
                 live = live && (Emax >= 0);
             }
         }
@@ -163,48 +182,81 @@ __device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, 
     }
 }
 
+__device__ __forceinline__ void kt_tile_list(const PassConst& pc, uint32_t tile, uint32_t nLarge, uint32_t& begin, uint32_t& end) {
+    begin = end = 0;
+    if (!nLarge) return;
+    const uint32_t cnt = __ldcg(pc.tileCount + tile);
+    if (!cnt) return;
+    const uint32_t start = __ldcg(pc.tileStart + tile);
+    begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
+}
+
 // Shadow pass tile stage: only blocks touched by large triangles do work (the small ones were resolved by K1's
-// atomics).  CTA = 32 x 32 px, warp = 8 x 16 px (SHADOW_SUB samples per lane).  The map is only written.
+// atomics).  Persistent CTAs stride over 32 x 32 px regions (the status words and the broadcast list are fetched
+// once per CTA, so a region costs no dependent memory round trip); warp = 8 x 16 px (SHADOW_SUB samples per lane).
+// The map is only written.
+#ifdef SHADOW_SUB_D
+constexpr int SHADOW_SUB = SHADOW_SUB_D;
+#else
 constexpr int SHADOW_SUB = 4;
+#endif
+#ifndef SHADOW_RMW
+#define SHADOW_RMW 0
+#endif
+constexpr int SHADOW_REGION_H = BLK_ROWS * SHADOW_SUB * 2;
 __global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constant__ PassConst pc) {
     __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
+    if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
     const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
     if (nLarge == 0 && nHuge == 0) return;
     if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }   // the only CTA barrier: once per CTA, CTA-uniform
-    const int bx0 = (int)blockIdx.x * TILE_W + BLK_W * (int)(warp & 3u);
-    const int by0 = (int)blockIdx.y * (BLK_ROWS * SHADOW_SUB * 2) + BLK_ROWS * SHADOW_SUB * (int)(warp >> 2);
-    if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
-    uint32_t begin[2] = {0, 0}, end[2] = {0, 0};
-    if (nLarge) {
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            const uint32_t ty = (uint32_t)by0 / TILE_H + t;
-            if (ty >= pc.tilesY) continue;
-            const uint32_t tile = ty * pc.tilesX + blockIdx.x;
-            const uint32_t cnt = __ldcg(pc.tileCount + tile);
-            if (cnt) {
-                const uint32_t start = __ldcg(pc.tileStart + tile);
-                begin[t] = min(start, pc.listCap); end[t] = min(start + cnt, pc.listCap);
-            }
-        }
-    }
+    const uint32_t regionsY = (pc.H + SHADOW_REGION_H - 1) / SHADOW_REGION_H, nRegions = pc.tilesX * regionsY;
+    const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;
+    uint32_t ry = blockIdx.x / pc.tilesX, rx = blockIdx.x - ry * pc.tilesX;
     const int lx = (int)(lane & 7u), ly = (int)(lane >> 3);
-    const int x = bx0 + lx;
-    unsigned long long key[SHADOW_SUB];
+    for (uint32_t region = blockIdx.x; region < nRegions; region += gridDim.x) {
+        const int bx0 = (int)rx * TILE_W + BLK_W * (int)(warp & 3u);
+        const int by0 = (int)ry * SHADOW_REGION_H + BLK_ROWS * SHADOW_SUB * (int)(warp >> 2);
+        const uint32_t tileX = rx;
+        rx += stepX; ry += stepY;
+        if (rx >= pc.tilesX) { rx -= pc.tilesX; ++ry; }
+        if (bx0 >= (int)pc.W || by0 >= (int)pc.H) continue;   // warp-uniform
+        constexpr int NT = (BLK_ROWS * SHADOW_SUB + TILE_H - 1) / TILE_H;   // 32 x 8 tiles a warp's block spans vertically
+        uint32_t begin[NT], end[NT];
 #pragma unroll
-    for (int r = 0; r < SHADOW_SUB; ++r) key[r] = 0xFFFFFFFFull;
-    if (nHuge) merge_huge<true, SHADOW_SUB>(hs, nHuge, bx0, by0, x, by0 + ly, key, lane);
+        for (int t = 0; t < NT; ++t) {
+            begin[t] = end[t] = 0;
+            const uint32_t ty = (uint32_t)by0 / TILE_H + t;
+            if (nLarge && ty < pc.tilesY) kt_tile_list(pc, ty * pc.tilesX + tileX, nLarge, begin[t], end[t]);
+        }
+        const int x = bx0 + lx;
+        uint32_t key[SHADOW_SUB];
 #pragma unroll
-    for (int t = 0; t < 2; ++t)
-        if (begin[t] != end[t]) merge_large<true, SHADOW_SUB>(pc.large, pc.tileList, begin[t], end[t], bx0, by0, lx, ly, key, stage[warp], lane);
+        for (int r = 0; r < SHADOW_SUB; ++r) key[r] = 0xFFFFFFFFu;
+#if SHADOW_RMW
+        uint32_t cur[SHADOW_SUB];   // K1 has completed, every sample belongs to one lane: plain read-compare-write, loads in flight during the merge
 #pragma unroll
-    for (int r = 0; r < SHADOW_SUB; ++r) {
-        const int y = by0 + BLK_ROWS * r + ly;
-        if (key[r] != 0xFFFFFFFFull && x < (int)pc.W && y < (int)pc.H) atomicMin(pc.depthBits + (size_t)y * pc.W + x, (uint32_t)key[r]);
+        for (int r = 0; r < SHADOW_SUB; ++r) {
+            const int y = by0 + BLK_ROWS * r + ly;
+            cur[r] = (x < (int)pc.W && y < (int)pc.H) ? __ldcg(pc.depthBits + (size_t)y * pc.W + x) : 0u;
+        }
+#endif
+        if (nHuge) merge_huge<true, SHADOW_SUB>(hs, nHuge, bx0, by0, x, by0 + ly, key, lane);
+#pragma unroll
+        for (int t = 0; t < NT; ++t)
+            if (begin[t] != end[t]) merge_large<true, SHADOW_SUB>(pc.large, pc.tileList, begin[t], end[t], bx0, by0, lx, ly, key, stage[warp], lane);
+#pragma unroll
+        for (int r = 0; r < SHADOW_SUB; ++r) {
+            const int y = by0 + BLK_ROWS * r + ly;
+#if SHADOW_RMW
+            if (key[r] < cur[r]) pc.depthBits[(size_t)y * pc.W + x] = key[r];   // cur = 0 out of bounds
+#else
+            if (key[r] != 0xFFFFFFFFu && x < (int)pc.W && y < (int)pc.H) atomicMin(pc.depthBits + (size_t)y * pc.W + x, key[r]);
+#endif
+        }
     }
 }
 
@@ -215,8 +267,7 @@ __global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constan
 #ifndef KT_MIN_BLOCKS
 #define KT_MIN_BLOCKS 3
 #endif
-__device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, uint32_t tile, uint32_t b, int lx, int ly) {
-    const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+__device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, uint32_t tx, uint32_t ty, uint32_t b, int lx, int ly) {
     const int x = (int)tx * TILE_W + BLK_W * (int)(b & 3u) + lx, y = (int)ty * TILE_H + BLK_ROWS * (int)(b >> 2) + ly;
     if (x >= (int)pc.W || y >= (int)pc.H || !row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return VIS_CLEAR;
     return __ldcg(pc.vis + (size_t)y * pc.W + x);
@@ -249,15 +300,6 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
 }
 
-__device__ __forceinline__ void kt_tile_list(const PassConst& pc, uint32_t tile, uint32_t nLarge, uint32_t& begin, uint32_t& end) {
-    begin = end = 0;
-    if (!nLarge) return;
-    const uint32_t cnt = __ldcg(pc.tileCount + tile);
-    if (!cnt) return;
-    const uint32_t start = __ldcg(pc.tileStart + tile);
-    begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
-}
-
 #ifndef KT_MODE
 #define KT_MODE 1
 #endif
@@ -276,7 +318,7 @@ __global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(cons
     const uint32_t tile = blockIdx.x;
     const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
     if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return;
-    const unsigned long long key = kt_load_key(pc, tile, warp, lx, ly);
+    const unsigned long long key = kt_load_key(pc, tx, ty, warp, lx, ly);
     if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
     uint32_t begin, end;
     kt_tile_list(pc, tile, nLarge, begin, end);
@@ -285,52 +327,30 @@ __global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(cons
 #elif KT_MODE == 1
     // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
     uint32_t tile = blockIdx.x;
-    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, tile, warp, lx, ly) : VIS_CLEAR;
+    const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;   // the only divisions: once per CTA
+    uint32_t tyN = tile / pc.tilesX, txN = tile - tyN * pc.tilesX;
+    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, txN, tyN, warp, lx, ly) : VIS_CLEAR;
     if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
     for (; tile < nTiles; tile += gridDim.x) {
         const unsigned long long key = keyNext;
-        if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, tile + gridDim.x, warp, lx, ly);
-        const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+        const uint32_t tx = txN, ty = tyN;
+        txN += stepX; tyN += stepY;
+        if (txN >= pc.tilesX) { txN -= pc.tilesX; ++tyN; }
+        if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
         if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) continue;
         uint32_t begin, end;
         kt_tile_list(pc, tile, nLarge, begin, end);
         kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
                            end, stage[warp], lane);
     }
-#else
-    // persistent autonomous warps: a warp owns whole tiles (first two static, the rest drawn from a counter)
-    uint32_t* const counter = pc.status + 6;
-    const uint32_t totalWarps = gridDim.x * KT_WARPS, gw = blockIdx.x * KT_WARPS + warp;
-    uint32_t tile = gw, draw = totalWarps + gw;
-    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
-    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, tile, 0, lx, ly) : VIS_CLEAR;
-    while (tile < nTiles) {
-        const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
-        const bool owned = row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH);
-        uint32_t begin = 0, end = 0;
-        if (owned) kt_tile_list(pc, tile, nLarge, begin, end);
-        uint32_t tileNext = nTiles;
-#pragma unroll 1
-        for (uint32_t b = 0; b < 8u; ++b) {
-            const unsigned long long key = keyNext;
-            if (b < 7u) keyNext = kt_load_key(pc, tile, b + 1u, lx, ly);   // in flight while this block is shaded
-            else {
-                tileNext = __shfl_sync(0xFFFFFFFFu, draw, 0);
-                if (lane == 0) draw = 2u * totalWarps + atomicAdd(counter, 1u);
-                keyNext = tileNext < nTiles ? kt_load_key(pc, tileNext, 0, lx, ly) : VIS_CLEAR;
-            }
-            if (!owned) continue;
-            kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(b & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(b >> 2), lx, ly, nHuge, hs, begin, end,
-                               stage[warp], lane);
-        }
-        tile = tileNext;
-    }
 #endif
 }
 
-void launch_tile_shadow(const PassConst& pc, cudaStream_t st) {
-    const uint32_t bh = BLK_ROWS * SHADOW_SUB * 2;
-    launch_k(k_tile_shadow, dim3(pc.tilesX, (pc.H + bh - 1) / bh), dim3(KT_THREADS), st, true, pc);
+void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st) {
+    static int perSM = 0;
+    if (!perSM) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_tile_shadow, KT_THREADS, 0); if (perSM < 1) perSM = 1; }
+    const uint32_t nRegions = pc.tilesX * ((pc.H + SHADOW_REGION_H - 1) / SHADOW_REGION_H);
+    launch_k(k_tile_shadow, dim3(std::min<uint32_t>(nRegions, (uint32_t)(numSMs * perSM))), dim3(KT_THREADS), st, true, pc);
 }
 
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st) {
@@ -345,10 +365,8 @@ void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, 
     }
 #if KT_MODE == 0
     const uint32_t grid = pc.tilesX * pc.tilesY;
-#elif KT_MODE == 1
-    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[tex]));
 #else
-    const uint32_t grid = std::min<uint32_t>((pc.tilesX * pc.tilesY + KT_WARPS - 1) / KT_WARPS, (uint32_t)(numSMs * perSM[tex]));
+    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[tex]));
 #endif
     if (tex) launch_k(k_tile_forward<true>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
     else launch_k(k_tile_forward<false>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);

@@ -67,24 +67,48 @@ __device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t
     }
 }
 
+// Pass prologue (K0 is the first kernel of a pass and is stream-ordered after the previous use of these buffers): reset
+// the pass status words and the per-tile list counters, so the pass needs no memset node and the tile stage no re-arm.
+__device__ __forceinline__ void k0_prologue(const PassConst& pc) {
+    if (blockIdx.x == 0 && threadIdx.x < 8) pc.status[threadIdx.x] = 0u;
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
+}
+// Fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice.
+__device__ __forceinline__ void k0_clear_shadow(const PassConst& pc) {
+    const size_t nPix = (size_t)pc.W * pc.H, n4 = nPix / 4u;
+    if (blockIdx.x == 0 && threadIdx.x < (nPix & 3u)) pc.depthBits[4u * n4 + threadIdx.x] = 0x3F800000u;
+    const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
+    const size_t lo = per * blockIdx.x, hi = lo + per < n4 ? lo + per : n4;
+    uint4* dst = reinterpret_cast<uint4*>(pc.depthBits);
+    const uint4 one = make_uint4(0x3F800000u, 0x3F800000u, 0x3F800000u, 0x3F800000u);
+    for (size_t i = lo + threadIdx.x; i < hi; i += 256u) dst[i] = one;
+}
+
+// Both vertex stages of a frame in one launch: used when the shadow and forward draw lists are identical (the
+// reference's shadow list is the opaque list followed by the translucent one, RenderScene.cpp:191-208), so both
+// post-transform caches have the same layout and every source vertex is fetched once.
+__global__ void __launch_bounds__(256) k_vertex_both(const __grid_constant__ PassConst ps, const __grid_constant__ PassConst pf) {
+    pdl_enter();
+    const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
+    k0_prologue(ps);
+    k0_prologue(pf);
+    k0_clear_shadow(ps);
+    K0In in[K0_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<false>(pf, base + 256u * k);
+#pragma unroll
+    for (int k = 0; k < K0_PER_THREAD; ++k) {
+        k0_transform_store<true>(ps, base + 256u * k, in[k]);
+        k0_transform_store<false>(pf, base + 256u * k, in[k]);
+    }
+}
+
 template <bool SHADOW>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
     pdl_enter();
     const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
-    // pass prologue (K0 is the first kernel of a pass and is stream-ordered after the previous pass): reset the pass
-    // status words and the per-tile list counters, so the pass needs no memset node and the tile stage no re-arm
-    if (blockIdx.x == 0 && threadIdx.x < 8) pc.status[threadIdx.x] = 0u;
-    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
-    if (SHADOW) {
-        // fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice
-        const size_t nPix = (size_t)pc.W * pc.H, n4 = nPix / 4u;
-        if (blockIdx.x == 0 && threadIdx.x < (nPix & 3u)) pc.depthBits[4u * n4 + threadIdx.x] = 0x3F800000u;
-        const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
-        const size_t lo = per * blockIdx.x, hi = lo + per < n4 ? lo + per : n4;
-        uint4* dst = reinterpret_cast<uint4*>(pc.depthBits);
-        const uint4 one = make_uint4(0x3F800000u, 0x3F800000u, 0x3F800000u, 0x3F800000u);
-        for (size_t i = lo + threadIdx.x; i < hi; i += 256u) dst[i] = one;
-    }
+    k0_prologue(pc);
+    if (SHADOW) k0_clear_shadow(pc);
     K0In in[K0_PER_THREAD];
 #pragma unroll
     for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW>(pc, base + 256u * k);
@@ -135,6 +159,12 @@ void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) 
     const uint32_t grid = (pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
     if (shadow) launch_k(k_vertex<true>, dim3(grid), dim3(256), st, pdl, pc);
     else launch_k(k_vertex<false>, dim3(grid), dim3(256), st, pdl, pc);
+}
+
+void launch_vertex_both(const PassConst& ps, const PassConst& pf, cudaStream_t st) {
+    if (pf.cacheSize == 0) return;
+    const uint32_t grid = (pf.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
+    launch_k(k_vertex_both, dim3(grid), dim3(256), st, false, ps, pf);
 }
 
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st) {

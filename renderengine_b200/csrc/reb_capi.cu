@@ -44,6 +44,7 @@ struct reb_ctx {
     float* transforms = nullptr; float* nmats = nullptr; uint32_t nNodes = 0;
     uint8_t* materials = nullptr; uint32_t materialStride = 0, nMaterials = 0;
     uint8_t* lights = nullptr; uint32_t lightStride = 0, nLights = 0;
+    float lightsHost[SHADE_CONST_LIGHTS][28] = {};   // host mirror of the first records (ShadeConst::lightsC)
     // bindless textures (TextureHandle = running index, Bindless.cpp:221-224)
     std::vector<TexDev> texHost; std::vector<void*> texAllocs; TexDev* dTextures = nullptr; size_t texTableCap = 0; bool texDirty = false;
     // view
@@ -56,7 +57,9 @@ struct reb_ctx {
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
     LargeRec* huge = nullptr;        // 2 x HUGE_CAP
-    uint32_t* tileCount = nullptr; uint32_t* tileStart = nullptr; uint32_t tileCap = 0;
+    uint32_t* tileCount[2] = {nullptr, nullptr}; uint32_t tileCap[2] = {0, 0};   // per pass: both may be in flight behind one fused K0
+    uint32_t* tileStart = nullptr; uint32_t tileStartCap = 0;
+    bool shadowDeferred = false; float recordedSPV[16];   // reb_render_shadow recorded, not yet submitted
     uint32_t* tileList = nullptr; uint32_t listCap = 0;
     uint32_t* dStatus = nullptr;     // 2 x 8 words
     uint32_t* hStatus = nullptr;     // pinned + mapped mirror, written by the tile stage kernels
@@ -142,14 +145,19 @@ int alloc_targets(reb_ctx* ctx) {
     return REB_OK;
 }
 
-int ensure_tiles(reb_ctx* ctx, uint32_t nTiles) {
-    if (nTiles + 1 <= ctx->tileCap) return REB_OK;
+int ensure_tiles(reb_ctx* ctx, int kind, uint32_t nTiles) {
     int rc;
-    CU(cudaStreamSynchronize(ctx->stream));
-    if ((rc = dev_alloc(ctx, &ctx->tileCount, (size_t)nTiles + 1))) return rc;
-    if ((rc = dev_alloc(ctx, &ctx->tileStart, (size_t)nTiles + 1))) return rc;
-    CU(cudaMemsetAsync(ctx->tileCount, 0, ((size_t)nTiles + 1) * 4, ctx->stream));   // the tile stage re-arms them after each pass
-    ctx->tileCap = nTiles + 1;
+    if (nTiles + 1 > ctx->tileCap[kind]) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        if ((rc = dev_alloc(ctx, &ctx->tileCount[kind], (size_t)nTiles + 1))) return rc;
+        CU(cudaMemsetAsync(ctx->tileCount[kind], 0, ((size_t)nTiles + 1) * 4, ctx->stream));   // K0's prologue zeroes them every pass
+        ctx->tileCap[kind] = nTiles + 1;
+    }
+    if (nTiles + 1 > ctx->tileStartCap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        if ((rc = dev_alloc(ctx, &ctx->tileStart, (size_t)nTiles + 1))) return rc;
+        ctx->tileStartCap = nTiles + 1;
+    }
     return REB_OK;
 }
 
@@ -274,7 +282,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
-    pc.tileCount = ctx->tileCount; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
+    pc.tileCount = ctx->tileCount[kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
     pc.flatSlots = ps.flatSlots;
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + 8 * kind;
@@ -283,9 +291,9 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     else { pc.rank = 0; pc.nRanks = 1; pc.bandH = 64; }
 }
 
-int enqueue_pass(reb_ctx* ctx, int kind) {
+// Everything a pass needs before its kernels can be enqueued: queue capacities, texture table, kernel parameters.
+int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     PassState& ps = ctx->pass[kind];
-    PassConst pc;
     int rc;
     if ((rc = ensure_large(ctx, ps.nTris))) return rc;
     if (kind == 1 && !ctx->texHost.empty()) {
@@ -306,24 +314,31 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         }
     }
     fill_pass(ctx, kind, pc);
-    const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    if ((rc = ensure_tiles(ctx, nTiles))) return rc;
+    if ((rc = ensure_tiles(ctx, kind, pc.tilesX * pc.tilesY))) return rc;
     fill_pass(ctx, kind, pc);
-    if (!ps.nTris) CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));   // otherwise K0's prologue resets status + tile counters
+    return REB_OK;
+}
+
+// Enqueue the kernels of one pass: K0 vertex stage (unless the fused two-pass K0 already ran), K1 setup + small raster,
+// K2 bin scatter, K3 tile stage.  Every kernel after the first is PDL-chained.
+int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
+    PassState& ps = ctx->pass[kind];
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
     auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
-    // the shadow-map clear is fused into the vertex kernel; an empty draw list still has to clear
-    if (kind == 0 && !ps.nTris) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
+    if (!ps.nTris) {   // no K0 to run the pass prologue: reset status here; an empty shadow list still has to clear the map
+        CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
+        if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
+    }
     mark(1);
-    if (ps.nTris) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
+    if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
     if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(3);
     if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(4);
     if (kind == 0) {
-        launch_tile_shadow(pc, ctx->stream); ctx->launches++;
+        launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++;
     } else {
         ShadeConst sh;
         std::memset(&sh, 0, sizeof sh);
@@ -332,6 +347,7 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
         sh.nLights = ctx->nLights;
         sh.materials = ctx->materials; sh.materialStride = ctx->materialStride; sh.nMaterials = ctx->nMaterials;
         sh.lights = ctx->lights; sh.lightStride = ctx->lightStride;
+        std::memcpy(sh.lightsC, ctx->lightsHost, sizeof sh.lightsC);
         const bool useShadow = ctx->shadowMap && ctx->shadowValid && ctx->haveShadowXf;
         sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
         sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
@@ -341,8 +357,43 @@ int enqueue_pass(reb_ctx* ctx, int kind) {
     mark(5);
     CU(cudaGetLastError());
     ps.pending = true;
-    if (kind == 0) ctx->shadowValid = true;
     return REB_OK;
+}
+
+// The shadow pass is RECORDED by reb_render_shadow and submitted with the forward pass (the reference records both
+// passes into one command buffer per frame, RenderScene.cpp:168-184, and submits once): when both draw lists are the
+// same the two vertex stages run as one kernel.  Anything that needs the shadow map earlier flushes the recording.
+int flush_deferred(reb_ctx* ctx) {
+    if (!ctx->shadowDeferred) return REB_OK;
+    ctx->shadowDeferred = false;
+    PassConst pc;
+    int rc = prepare_pass(ctx, 0, pc);
+    if (rc) return rc;
+    std::memcpy(pc.PV, ctx->recordedSPV, 64);
+    return run_pass(ctx, 0, pc, false);
+}
+
+int submit_forward(reb_ctx* ctx) {
+    PassConst pf, psh;
+    int rc;
+    if ((rc = prepare_pass(ctx, 1, pf))) return rc;
+    const PassState &s0 = ctx->pass[0], &s1 = ctx->pass[1];
+    const bool fuse = ctx->shadowDeferred && s0.nTris && s1.nTris && s0.deindexed == s1.deindexed && s0.cacheSize == s1.cacheSize &&
+                      s0.draws.size() == s1.draws.size() && std::memcmp(s0.draws.data(), s1.draws.data(), s0.draws.size() * sizeof(reb_draw)) == 0 &&
+                      !std::getenv("REB_NO_FUSED_VERTEX");
+    if (!fuse) {
+        if ((rc = flush_deferred(ctx))) return rc;
+        if ((rc = prepare_pass(ctx, 1, pf))) return rc;   // the flush may have grown shared queues
+        return run_pass(ctx, 1, pf, false);
+    }
+    ctx->shadowDeferred = false;
+    if ((rc = prepare_pass(ctx, 0, psh))) return rc;
+    if ((rc = prepare_pass(ctx, 1, pf))) return rc;
+    std::memcpy(psh.PV, ctx->recordedSPV, 64);
+    if (ctx->profiling) cudaEventRecord(ctx->ev[0][0], ctx->stream);
+    launch_vertex_both(psh, pf, ctx->stream); ctx->launches++;
+    if ((rc = run_pass(ctx, 0, psh, true))) return rc;
+    return run_pass(ctx, 1, pf, true);
 }
 
 // After a stream sync: look at the status words of the passes enqueued since the last check; grow the
@@ -363,8 +414,13 @@ int check_and_recover(reb_ctx* ctx) {
         if (rc) return rc;
         ctx->listCap = need; ctx->regrows++; ctx->counters[3] = ctx->regrows;
         const bool p0 = ctx->pass[0].pending, p1 = ctx->pass[1].pending;
-        if (p0 && (rc = enqueue_pass(ctx, 0))) return rc;
-        if (p1 && (rc = enqueue_pass(ctx, 1))) return rc;
+        for (int k = 0; k < 2; ++k) {
+            if (!(k == 0 ? p0 : p1)) continue;
+            PassConst pc;
+            if ((rc = prepare_pass(ctx, k, pc))) return rc;
+            if (k == 0) std::memcpy(pc.PV, ctx->recordedSPV, 64);
+            if ((rc = run_pass(ctx, k, pc, false))) return rc;
+        }
         CU(cudaStreamSynchronize(ctx->stream));
     }
     return fail(ctx, REB_E_OVERFLOW, "tile-list queue kept overflowing after 8 regrow attempts");

@@ -54,7 +54,7 @@ int reb_destroy(reb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
-                    ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount, ctx->tileStart,
+                    ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};
@@ -73,6 +73,7 @@ int reb_upload_geometry(reb_ctx* ctx, const void* verts, uint64_t nVerts, const 
     if ((!verts && nVerts) || (!idx && nIdx)) return fail(ctx, REB_E_INVALID, "reb_upload_geometry: null buffer");
     if (nVerts >= 0xFFFFFFFFull || nIdx >= 0xFFFFFFFFull) return fail(ctx, REB_E_INVALID, "reb_upload_geometry: counts must fit u32");
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     int rc;
     if ((rc = dev_alloc(ctx, &ctx->pos4, nVerts))) return rc;
@@ -99,6 +100,7 @@ int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
     CHECK_CTX();
     if (!m && nNodes) return fail(ctx, REB_E_INVALID, "reb_upload_transforms: null buffer");
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     int rc;
     if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
@@ -117,6 +119,7 @@ int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
 static int upload_records(reb_ctx* ctx, uint8_t** dst, const void* records, uint32_t stride, uint32_t n, uint32_t minStride, const char* what) {
     if ((!records && n) || stride < minStride || stride % 16) return fail(ctx, REB_E_INVALID, std::string(what) + ": bad records / stride (16-B multiple required)");
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     int rc;
     if ((rc = dev_alloc(ctx, dst, (size_t)stride * n))) return rc;
@@ -137,7 +140,10 @@ int reb_upload_materials(reb_ctx* ctx, const void* records, uint32_t stride, uin
 int reb_upload_lights(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n) {
     CHECK_CTX();
     int rc = upload_records(ctx, &ctx->lights, records, stride, n, 112, "reb_upload_lights");
-    if (rc == REB_OK) { ctx->lightStride = stride; ctx->nLights = n; }
+    if (rc == REB_OK) {
+        ctx->lightStride = stride; ctx->nLights = n;
+        for (uint32_t i = 0; i < n && i < (uint32_t)SHADE_CONST_LIGHTS; ++i) std::memcpy(ctx->lightsHost[i], static_cast<const uint8_t*>(records) + (size_t)i * stride, 112);
+    }
     return rc;
 }
 
@@ -221,8 +227,12 @@ int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, ui
     int rc;
     if ((rc = ready_to_render(ctx))) return rc;
     CU(cudaSetDevice(ctx->device));
+    if ((rc = flush_deferred(ctx))) return rc;   // a previous recording that was never paired with a forward pass
     if ((rc = set_draws(ctx, 0, draws, n))) return rc;
-    return enqueue_pass(ctx, 0);
+    std::memcpy(ctx->recordedSPV, ctx->SPV, 64);
+    ctx->shadowDeferred = true;                  // submitted by reb_render_forward / reb_flush / anything that needs the map
+    ctx->shadowValid = true;
+    return REB_OK;
 }
 
 int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
@@ -235,12 +245,19 @@ int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
     if (ctx->nLights && !ctx->lights) return fail(ctx, REB_E_INVALID, "reb_render_forward: lights missing");
     CU(cudaSetDevice(ctx->device));
     if ((rc = set_draws(ctx, 1, draws, n))) return rc;
-    return enqueue_pass(ctx, 1);
+    return submit_forward(ctx);
+}
+
+int reb_flush(reb_ctx* ctx) {
+    CHECK_CTX();
+    CU(cudaSetDevice(ctx->device));
+    return flush_deferred(ctx);
 }
 
 int reb_sync(reb_ctx* ctx) {
     CHECK_CTX();
     CU(cudaSetDevice(ctx->device));
+    { int rc = flush_deferred(ctx); if (rc) return rc; }
     CU(cudaStreamSynchronize(ctx->stream));
     return check_and_recover(ctx);
 }
@@ -261,6 +278,7 @@ static int output_info(reb_ctx* ctx, reb_output_kind kind, void** p, uint64_t* b
 
 int reb_get_output(reb_ctx* ctx, reb_output_kind kind, void** devPtr, uint64_t* bytes) {
     CHECK_CTX();
+    if (ctx->shadowDeferred) { cudaSetDevice(ctx->device); int frc = flush_deferred(ctx); if (frc) return frc; }   // the caller may read the map on the stream
     void* p = nullptr; uint64_t b = 0;
     int rc = output_info(ctx, kind, &p, &b);
     if (rc) return rc;
@@ -274,7 +292,7 @@ int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host) {
     if (!host) return fail(ctx, REB_E_INVALID, "reb_readback: null host buffer");
     CU(cudaSetDevice(ctx->device));
     int rc;
-    if (ctx->pass[0].pending || ctx->pass[1].pending) { if ((rc = reb_sync(ctx))) return rc; }
+    if (ctx->shadowDeferred || ctx->pass[0].pending || ctx->pass[1].pending) { if ((rc = reb_sync(ctx))) return rc; }
     void* p = nullptr; uint64_t b = 0;
     if ((rc = output_info(ctx, kind, &p, &b))) return rc;
     CU(cudaMemcpyAsync(host, p, b, cudaMemcpyDeviceToHost, ctx->stream));
@@ -286,6 +304,7 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
     CHECK_CTX();
     if (nRanks == 0 || rank >= nRanks || bandH == 0 || bandH % TILE_H) return fail(ctx, REB_E_INVALID, "reb_set_partition: need rank < nRanks and bandH a multiple of 8");
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     ctx->rank = rank; ctx->nRanks = nRanks; ctx->bandH = bandH;
     return alloc_targets(ctx);   // re-clear: pixels outside this rank's bands keep the clear values
@@ -294,6 +313,7 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId) {
     CHECK_CTX();
     if (shadowId != 0 || !ctx->shadowMap) return fail(ctx, REB_E_INVALID, "reb_shadow_mark_valid: unknown shadow id");
+    if (ctx->shadowDeferred) { cudaSetDevice(ctx->device); int frc = flush_deferred(ctx); if (frc) return frc; }
     ctx->shadowValid = true;
     return REB_OK;
 }
@@ -308,6 +328,7 @@ int reb_get_counters(reb_ctx* ctx, uint64_t* c) {
 int reb_set_profiling(reb_ctx* ctx, int on) {
     CHECK_CTX();
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     if (on && !ctx->ev[0][0])
         for (int k = 0; k < 2; ++k) for (int i = 0; i < 6; ++i) CU(cudaEventCreate(&ctx->ev[k][i]));
     ctx->profiling = on != 0;
@@ -318,6 +339,7 @@ int reb_get_kernel_times(reb_ctx* ctx, int pass, float* ms6) {
     CHECK_CTX();
     if (pass < 0 || pass > 1 || !ms6 || !ctx->ev[0][0]) return fail(ctx, REB_E_INVALID, "reb_get_kernel_times: profiling not enabled / bad args");
     CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     ms6[5] = 0.0f;
     for (int i = 0; i < 5; ++i) {

@@ -122,9 +122,8 @@ __device__ __forceinline__ float glm_min(float x, float y) { return (y < x) ? y 
 template <bool DIVIDE>
 __device__ __forceinline__ float4 vertex_stage(const float* __restrict__ PV, const float* __restrict__ T, float px, float py, float pz, V3* world) {
     float4 wH = mat4_mul_point(T, px, py, pz);
-    V3 w;
-    if (DIVIDE) w = {wH.x / wH.w, wH.y / wH.w, wH.z / wH.w};
-    else w = {wH.x, wH.y, wH.z};
+    V3 w = {wH.x, wH.y, wH.z};
+    if (DIVIDE && wH.w != 1.0f) w = {wH.x / wH.w, wH.y / wH.w, wH.z / wH.w};   // x / 1.0f == x exactly: affine nodes skip the divides
     if (world) *world = w;
     return mat4_mul_point(PV, w.x, w.y, w.z);
 }
@@ -138,7 +137,8 @@ __device__ __forceinline__ VtxA viewport_snap(float4 c, uint32_t W, uint32_t H) 
     f |= (c.z < 0.0f) ? 16u : 0u; f |= (c.z > c.w) ? 32u : 0u;
     if (!(c.w > 0.0f)) { a.X = 0; a.Y = 0; a.z = 0.0f; a.flags = f | VF_W; return a; }
     const float hw = 0.5f * (float)W, hh = 0.5f * (float)H;
-    const float nx = c.x / c.w, ny = c.y / c.w, nz = c.z / c.w;
+    const float rw = 1.0f / c.w;                                   // Appendix B.4 (revision r1b): one IEEE reciprocal per vertex
+    const float nx = c.x * rw, ny = c.y * rw, nz = c.z * rw;
     const float xf = hw * nx + hw;
     const float yf = hh * ny + hh;
     if (!(fabsf(xf) <= GUARD_PX) || !(fabsf(yf) <= GUARD_PX)) { a.X = 0; a.Y = 0; a.z = nz; a.flags = f | VF_GUARD; return a; }

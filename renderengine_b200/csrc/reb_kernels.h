@@ -6,11 +6,14 @@
 
 namespace reb {
 
+constexpr int SHADE_CONST_LIGHTS = 4;   // Light records (112 B std430, phong.glsl:20-37) carried in the kernel parameters
+
 struct ShadeConst {
     float STR[16];                 // shadowProj*shadowView (ShadowSystem.cpp:303)
     float viewPos[3]; uint32_t nLights;
     const uint8_t* materials; uint32_t materialStride; uint32_t nMaterials;
     const uint8_t* lights; uint32_t lightStride;
+    float4 lightsC[SHADE_CONST_LIGHTS][7];   // copy of the first records of `lights`
     const float* shadowMap; uint32_t shadowSize;   // NULL / 0: shadow = 0
     uint32_t maxDescriptors; uint32_t nTextures;
     const TexDev* textures;
@@ -30,6 +33,7 @@ inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream
 }
 
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st);
+void launch_vertex_both(const PassConst& shadowPass, const PassConst& forwardPass, cudaStream_t st);   // identical cache layouts
 void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
@@ -38,7 +42,7 @@ void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);   // 
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
-void launch_tile_shadow(const PassConst& pc, cudaStream_t st);
+void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
 
 }  // namespace reb

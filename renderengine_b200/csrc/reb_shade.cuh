@@ -27,6 +27,17 @@ __device__ __forceinline__ LightDev load_light(const uint8_t* __restrict__ base)
     return l;
 }
 
+__device__ __forceinline__ LightDev const_light(const ShadeConst& sh, uint32_t i) {
+    const float4* q = sh.lightsC[i];
+    LightDev l;
+    l.type = __float_as_uint(q[0].x);
+    l.position = {q[1].x, q[1].y, q[1].z};
+    l.direction = {q[2].x, q[2].y, q[2].z};
+    l.ambient = q[3]; l.diffuse = q[4]; l.specular = q[5];
+    l.innerCutoff = q[6].x; l.outerCutoff = q[6].y; l.shadowIndex = __float_as_uint(q[6].z);
+    return l;
+}
+
 // PhongLighting (phong.glsl:39-81).  Colour is held to <= 1 LSB of the sRGB8 target / PSNR >= 50 dB on the f32
 // buffer (BASELINE.json), not to bit-exactness, so this block — and only this block plus the sRGB encode — uses the
 // SFU approximations (MUFU rsqrt / lg2 / ex2, relative error ~1e-6); everything that feeds a discontinuous
@@ -105,8 +116,7 @@ __device__ __forceinline__ float compute_shadow(const LightDev& light, V3 fragPo
             const float depth = shadow_fetch(map, S, mu + (float)x * texel, mv + (float)y * texel);
             shadow += (ref > depth) ? 1.0f : 0.0f;
         }
-    shadow /= 9.0f;
-    return shadow;
+    return shadow * (1.0f / 9.0f);   // shadow /= 9.0 (shadow.glsl:54); feeds colour only (tolerance, not bit-exactness)
 }
 
 // ---- bindless textures: isotropic trilinear, repeat, RGBA16 UNORM, optional sRGB decode after filtering.
@@ -153,18 +163,17 @@ __device__ __forceinline__ float4 sample_texture(const TexDev* __restrict__ tabl
     return a;
 }
 
-__device__ __forceinline__ uint32_t quant8(float x) {
-    if (!(x > 0.0f)) return 0u;
-    if (x >= 1.0f) return 255u;
-    return (uint32_t)(int)floorf(x * 255.0f + 0.5f);
-}
-__device__ __forceinline__ float srgb_oetf(float x) {              // SFU pow: see the tolerance note above phong_lighting
-    if (!(x > 0.0f)) return 0.0f;
-    if (x >= 1.0f) return 1.0f;
-    return (x <= 0.0031308f) ? 12.92f * x : 1.055f * exp2f((1.0f / 2.4f) * __log2f(x)) - 0.055f;
+// sRGB8 encode of the R8G8B8A8_SRGB target (Swapchain.cpp:14): clamp, OETF, round(x * 255).  Colour is held to <= 1 LSB,
+// so this uses the SFU lg2 / ex2 and explicit FMAs (see the tolerance note above phong_lighting).
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ uint32_t quant8(float x01) { return (uint32_t)__float2int_rd(__fmaf_rn(x01, 255.0f, 0.5f)); }   // x01 in [0, 1]
+__device__ __forceinline__ float srgb_oetf(float x) {
+    x = __saturatef(x);                                            // NaN -> 0
+    const float hi = __fmaf_rn(1.055f, ex2_approx((1.0f / 2.4f) * __log2f(x)), -0.055f);   // x = 0: ex2(-inf) = 0, selected away below
+    return (x <= 0.0031308f) ? 12.92f * x : hi;
 }
 __device__ __forceinline__ uint32_t pack_srgb8(float4 c) {
-    return quant8(srgb_oetf(c.x)) | (quant8(srgb_oetf(c.y)) << 8) | (quant8(srgb_oetf(c.z)) << 16) | (quant8(c.w) << 24);
+    return quant8(srgb_oetf(c.x)) | (quant8(srgb_oetf(c.y)) << 8) | (quant8(srgb_oetf(c.z)) << 16) | (quant8(__saturatef(c.w)) << 24);
 }
 
 // Shade the sample at pixel (x, y) won by primitive `tri`: re-derive the barycentrics from the cached snapped
@@ -250,7 +259,8 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
     const V3 viewPos = {sh.viewPos[0], sh.viewPos[1], sh.viewPos[2]};
     float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (uint32_t l = 0; l < sh.nLights; ++l) {
-        const LightDev L = load_light(sh.lights + (size_t)l * sh.lightStride);
+        // the first SHADE_CONST_LIGHTS records ride in the kernel parameters (constant bank: no loads, no registers held)
+        const LightDev L = l < (uint32_t)SHADE_CONST_LIGHTS ? const_light(sh, l) : load_light(sh.lights + (size_t)l * sh.lightStride);
         float shadow = 0.0f;
         if (sh.shadowMap != nullptr && L.type == LIGHT_TYPE_DIRECTIONAL && L.shadowIndex == 0u)
             shadow = compute_shadow(L, fragPos, normal, sh.STR, sh.shadowMap, sh.shadowSize);

@@ -70,6 +70,7 @@ void Renderer::Check(int status, const char* what) const {
     throw std::runtime_error(msg);
 }
 void Renderer::WaitIdle() const { Check(reb_sync(m_ctx), "reb_sync"); }
+void Renderer::Submit() const { Check(reb_flush(m_ctx), "reb_flush"); }
 void Renderer::Readback(reb_output_kind kind, void* host) const { Check(reb_readback(m_ctx, kind, host), "reb_readback"); }
 std::vector<reb_draw> Renderer::ToDraws(const std::vector<MeshDrawInfo>& drawCalls) {
     std::vector<reb_draw> d(drawCalls.size());

@@ -262,6 +262,7 @@ public:
     uint32_t GetHeight() const { return m_height; }
     void Check(int status, const char* what) const;       // throws std::runtime_error with reb_last_error()
     void WaitIdle() const;                                 // reb_sync (vkDeviceWaitIdle analogue)
+    void Submit() const;                                   // reb_flush (CommandRingBuffer submit analogue, RenderLoop.cpp:124-132)
     void Readback(reb_output_kind kind, void* host) const; // swapchain image -> host (headless present)
     static std::vector<reb_draw> ToDraws(const std::vector<MeshDrawInfo>& drawCalls);
 private:
