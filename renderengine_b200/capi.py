@@ -14,7 +14,7 @@ REB_COLOR_SRGB8, REB_COLOR_F32, REB_DEPTH_F32, REB_TRIID_U32, REB_SHADOW_F32 = 0
 SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
-    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
@@ -65,6 +65,7 @@ def load():
     lib.reb_readback.argtypes = [vp, C.c_int, vp]
     lib.reb_sync.argtypes = [vp]
     lib.reb_flush.argtypes = [vp]
+    lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
     lib.reb_get_counters.argtypes = [vp, vp]
@@ -203,6 +204,10 @@ class Context:
     def readback_into(self, kind, host_ptr):
         """D2H into a caller-owned (e.g. pinned) buffer given as an integer address."""
         self._ck(self.lib.reb_readback(self.h, kind, C.c_void_p(host_ptr)))
+
+    def readback_async_into(self, kind, host_ptr):
+        """Enqueue the D2H copy into a pinned buffer and return; valid after the next sync() (sRGB8: copy stream + 2 images)."""
+        self._ck(self.lib.reb_readback_async(self.h, kind, C.c_void_p(host_ptr)))
 
     def set_partition(self, rank, n_ranks, band_h=64):
         self._ck(self.lib.reb_set_partition(self.h, rank, n_ranks, band_h))

@@ -53,6 +53,11 @@ struct reb_ctx {
     uint32_t S = 0; float* shadowMap = nullptr; float sview[16], sproj[16], SPV[16]; bool haveShadowXf = false, shadowValid = false;
     // outputs + visibility buffer
     uint8_t* outSRGB8 = nullptr; float* outF32 = nullptr; float* outDepth = nullptr; uint32_t* outTriId = nullptr;
+    // two-image "swapchain" for the sRGB8 target (the reference presents from >= 2 swapchain images, Swapchain.cpp:200-237):
+    // reb_readback_async copies image i on a copy stream while the next frame renders into image i ^ 1
+    uint8_t* swap[2] = {nullptr, nullptr}; int swapCur = 0; bool copyInFlight[2] = {false, false};
+    cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[2] = {nullptr, nullptr};
+    void* asyncHost = nullptr; bool asyncOutstanding = false;   // last reb_readback_async target (re-copied if the frame is replayed)
     unsigned long long* vis = nullptr;
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
@@ -127,8 +132,11 @@ int alloc_targets(reb_ctx* ctx) {
     if ((rc = dev_alloc(ctx, &ctx->vis, px))) return rc;
     launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->vis), 0xFFFFFFFFu, px * 2, ctx->numSMs, ctx->stream); ctx->launches++;
     if (ctx->outputs & REB_OUT_COLOR_SRGB8) {
-        if ((rc = dev_alloc(ctx, &ctx->outSRGB8, px * 4))) return rc;
-        launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->outSRGB8), 0xFF000000u, px, ctx->numSMs, ctx->stream); ctx->launches++;
+        for (int i = 0; i < 2; ++i) {
+            if ((rc = dev_alloc(ctx, &ctx->swap[i], px * 4))) return rc;
+            launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->swap[i]), 0xFF000000u, px, ctx->numSMs, ctx->stream); ctx->launches++;
+        }
+        ctx->swapCur = 0; ctx->outSRGB8 = ctx->swap[0];
     }
     if (ctx->outputs & REB_OUT_COLOR_F32) {
         if ((rc = dev_alloc(ctx, &ctx->outF32, px * 4))) return rc;
@@ -324,7 +332,8 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
 int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     PassState& ps = ctx->pass[kind];
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
-    auto mark = [&](int i) { if (ctx->profiling) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
+    const bool fusedShadow = vertexDone && kind == 0;   // slots 0-1 were stamped before the fused two-pass vertex kernel
+    auto mark = [&](int i) { if (ctx->profiling && !(fusedShadow && i < 2)) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
     if (!ps.nTris) {   // no K0 to run the pass prologue: reset status here; an empty shadow list still has to clear the map
         CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
@@ -340,6 +349,10 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     if (kind == 0) {
         launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++;
     } else {
+        if (ctx->swap[0]) {   // acquire the other swapchain image; wait for an async readback still draining it
+            ctx->swapCur ^= 1; ctx->outSRGB8 = ctx->swap[ctx->swapCur];
+            if (ctx->copyInFlight[ctx->swapCur]) { CU(cudaStreamWaitEvent(ctx->stream, ctx->evCopied[ctx->swapCur], 0)); ctx->copyInFlight[ctx->swapCur] = false; }
+        }
         ShadeConst sh;
         std::memset(&sh, 0, sizeof sh);
         std::memcpy(sh.STR, ctx->SPV, 64);
@@ -390,7 +403,7 @@ int submit_forward(reb_ctx* ctx) {
     if ((rc = prepare_pass(ctx, 0, psh))) return rc;
     if ((rc = prepare_pass(ctx, 1, pf))) return rc;
     std::memcpy(psh.PV, ctx->recordedSPV, 64);
-    if (ctx->profiling) cudaEventRecord(ctx->ev[0][0], ctx->stream);
+    if (ctx->profiling) { cudaEventRecord(ctx->ev[0][0], ctx->stream); cudaEventRecord(ctx->ev[0][1], ctx->stream); }
     launch_vertex_both(psh, pf, ctx->stream); ctx->launches++;
     if ((rc = run_pass(ctx, 0, psh, true))) return rc;
     return run_pass(ctx, 1, pf, true);
@@ -409,7 +422,15 @@ int check_and_recover(reb_ctx* ctx) {
             ctx->counters[1] = st[0]; ctx->counters[2] = st[3];
             if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
         }
-        if (!overflow) { ctx->pass[0].pending = ctx->pass[1].pending = false; return REB_OK; }
+        if (!overflow) {
+            ctx->pass[0].pending = ctx->pass[1].pending = false;
+            if (iter > 0 && ctx->asyncOutstanding && ctx->asyncHost && ctx->outSRGB8) {   // the frame was replayed: refresh the async copy
+                CU(cudaMemcpyAsync(ctx->asyncHost, ctx->outSRGB8, (size_t)ctx->W * ctx->H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                CU(cudaStreamSynchronize(ctx->stream));
+            }
+            ctx->asyncOutstanding = false;
+            return REB_OK;
+        }
         int rc = dev_alloc(ctx, &ctx->tileList, (size_t)need);
         if (rc) return rc;
         ctx->listCap = need; ctx->regrows++; ctx->counters[3] = ctx->regrows;

@@ -54,7 +54,7 @@ int reb_destroy(reb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
-                    ctx->outSRGB8, ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
+                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};
@@ -63,6 +63,9 @@ int reb_destroy(reb_ctx* ctx) {
     if (ctx->dTextures) cudaFree(ctx->dTextures);
     if (ctx->pass[1].vtxUV) cudaFree(ctx->pass[1].vtxUV);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
+    if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
+    if (ctx->evRendered) cudaEventDestroy(ctx->evRendered);
+    for (int i = 0; i < 2; ++i) if (ctx->evCopied[i]) cudaEventDestroy(ctx->evCopied[i]);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return REB_OK;
@@ -259,6 +262,8 @@ int reb_sync(reb_ctx* ctx) {
     CU(cudaSetDevice(ctx->device));
     { int rc = flush_deferred(ctx); if (rc) return rc; }
     CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->copyStream) CU(cudaStreamSynchronize(ctx->copyStream));
+    ctx->copyInFlight[0] = ctx->copyInFlight[1] = false;
     return check_and_recover(ctx);
 }
 
@@ -297,6 +302,32 @@ int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host) {
     if ((rc = output_info(ctx, kind, &p, &b))) return rc;
     CU(cudaMemcpyAsync(host, p, b, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    return REB_OK;
+}
+
+int reb_readback_async(reb_ctx* ctx, reb_output_kind kind, void* host) {
+    CHECK_CTX();
+    if (!host) return fail(ctx, REB_E_INVALID, "reb_readback_async: null host buffer");
+    CU(cudaSetDevice(ctx->device));
+    int rc;
+    if ((rc = flush_deferred(ctx))) return rc;
+    void* p = nullptr; uint64_t b = 0;
+    if ((rc = output_info(ctx, kind, &p, &b))) return rc;
+    if (kind != REB_COLOR_SRGB8) {   // single-buffered outputs: ordered copy on the render stream
+        CU(cudaMemcpyAsync(host, p, b, cudaMemcpyDeviceToHost, ctx->stream));
+        return REB_OK;
+    }
+    if (!ctx->copyStream) {
+        CU(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&ctx->evRendered, cudaEventDisableTiming));
+        for (int i = 0; i < 2; ++i) CU(cudaEventCreateWithFlags(&ctx->evCopied[i], cudaEventDisableTiming));
+    }
+    CU(cudaEventRecord(ctx->evRendered, ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->copyStream, ctx->evRendered, 0));
+    CU(cudaMemcpyAsync(host, p, b, cudaMemcpyDeviceToHost, ctx->copyStream));
+    CU(cudaEventRecord(ctx->evCopied[ctx->swapCur], ctx->copyStream));
+    ctx->copyInFlight[ctx->swapCur] = true;
+    ctx->asyncHost = host; ctx->asyncOutstanding = true;
     return REB_OK;
 }
 
