@@ -3,11 +3,14 @@
 Phong + 3x3-PCF shadow, 1080p; achieved HBM GB/s as a fraction of the measured B200 peak).
 
 A "step" is one full frame of config C2 (1,003,522 triangles, 1920x1080, 2048^2 shadow
-map): shadow depth pass + forward pass, every step.  N > 1 (torchrun): view-parallel batch — rank 0 renders
-the shadow map once per step and NCCL-broadcasts it, every rank renders its own camera view (weak
-scaling); `--mode tiles` runs the sort-first row-band split of one frame instead (strong scaling).
+map): shadow depth pass + forward pass, every step.  N > 1 (torchrun): view-parallel batch — every rank
+renders a full frame (its own shadow pass + its own camera view) per step, no data-path collective (weak
+scaling; `--shadow-share broadcast` renders the shadow map on rank 0 only and NCCL-broadcasts it over NVLink
+instead, which pays off when many views share one map).  `--mode tiles` runs the sort-first row-band split of
+ONE frame (strong scaling): shadow map rendered once on rank 0 and NCCL-broadcast, as BASELINE.json config 4 asks.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config C2] [--mode views|tiles]
+                    [--shadow-share replicate|broadcast]
 """
 import argparse
 import json
@@ -37,6 +40,8 @@ def profiled_traffic(kind, slot):
         try:
             with open(path) as f:
                 t = json.load(f)["dram_bytes_per_launch"]
+            if slot == "vertex" and kind == 0 and "k_vertex_both" in t:   # fused two-pass vertex kernel (timed in the shadow slot)
+                return int(t["k_vertex_both"]), os.path.basename(path)
             if name in t:
                 return int(t[name]), os.path.basename(path)
         except Exception:
@@ -142,6 +147,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2")
     ap.add_argument("--mode", default="views", choices=["views", "tiles"])
+    ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -166,6 +172,8 @@ def main():
     scene = sc.make_scene(args.config)
     T, W, H, S = scene["n_triangles"], scene["width"], scene["height"], scene["shadow_size"]
     tiles = args.mode == "tiles" and world > 1
+    share = args.shadow_share or ("broadcast" if tiles else "replicate")
+    bcast = world > 1 and share == "broadcast"
     st = torch.cuda.Stream()
     outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32
     ctx = capi.Context(W, H, device=local_rank, stream=st.cuda_stream, outputs=outputs,
@@ -175,7 +183,7 @@ def main():
         ctx.set_view(sc.view_for_azimuth(scene, 2 * np.pi * rank / world))   # one camera view per rank
     draws = scene["draws"]
     shadow_t = None
-    if S and world > 1:
+    if S and bcast:
         ptr, _ = ctx.output_ptr(capi.REB_SHADOW_F32)
         shadow_t = torch.as_tensor(_DevArray(ptr, (S, S), "<f4"), device=f"cuda:{local_rank}")
 
@@ -183,7 +191,7 @@ def main():
 
     def step():
         if S:
-            if world == 1:
+            if not bcast:
                 ctx.render_shadow(draws)
             else:
                 if rank == 0:
@@ -231,12 +239,12 @@ def main():
         n_prof = 20
         for _ in range(n_prof):
             flush.add_(1)
-            if S and (world == 1 or rank == 0):
+            if S and (not bcast or rank == 0):
                 ctx.render_shadow(draws)
             ctx.render_forward(draws)
             ctx.sync()
             for k in (0, 1):
-                if k == 0 and not (S and (world == 1 or rank == 0)):
+                if k == 0 and not (S and (not bcast or rank == 0)):
                     continue
                 for name, v in ctx.kernel_times_ms(k).items():
                     acc[k][name] = acc[k].get(name, 0.0) + v / n_prof
@@ -280,7 +288,7 @@ def main():
             (1, "vertex"): 32 * V, (1, "setup_raster"): 12 * T, (1, "bin_scatter"): 0,
             (1, "tile_stage"): (min(36 * W * H, 4 * S * S) if S else 0) + 12 * W * H,
         }
-        if S and world == 1 and acc[1].get("vertex", 1.0) < 0.2 * acc[0].get("vertex", 0.0):   # fused two-pass vertex kernel: timed in the shadow slot
+        if S and not bcast and acc[1].get("vertex", 1.0) < 0.2 * acc[0].get("vertex", 0.0):   # fused two-pass vertex kernel: timed in the shadow slot
             alg[(0, "vertex")] = 12 * V + 32 * V; alg[(1, "vertex")] = 0
         kt = {f"{'shadow' if k == 0 else 'forward'}.{n}": v for k in (0, 1) for n, v in acc[k].items()}
         dom = max(((k, n) for k in (0, 1) for n in acc[k]), key=lambda kn: acc[kn[0]][kn[1]])
@@ -294,7 +302,7 @@ def main():
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
             "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step",
-                       "parallelism": ("sort-first row bands x%d" % world) if tiles else ("view-parallel x%d, shadow map NCCL-broadcast" % world if world > 1 else "1 GPU"),
+                       "parallelism": ("sort-first row bands x%d" % world) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
                           "frac_of_peak": frame_bytes / (ms * 1e-3) / 1e9 / peak / world, "peak_gbs": peak, "peak_source": peak_src},

@@ -15,7 +15,10 @@
 
 namespace reb {
 
-constexpr int K0_PER_THREAD = 4;   // cache slots per thread: four independent load chains in flight
+#ifndef K0_PER_THREAD_D
+#define K0_PER_THREAD_D 4
+#endif
+constexpr int K0_PER_THREAD = K0_PER_THREAD_D;   // cache slots per thread: four independent load chains in flight
 
 struct K0In { float4 p, n; uint32_t node; bool valid; };
 
