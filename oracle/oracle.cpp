@@ -27,6 +27,7 @@
 namespace {
 
 constexpr uint32_t LIGHT_TYPE_DIRECTIONAL = 1;   // phong.glsl:16
+constexpr uint32_t LIGHT_TYPE_POINT = 2;         // pbr.glsl:283-285
 constexpr uint32_t LIGHT_TYPE_SPOT = 3;          // phong.glsl:18
 constexpr float GUARD_PX = 1048576.0f;           // |x_f|,|y_f| <= 2^20 px keeps 24.8 fixed point in int32
 constexpr uint32_t TRI_NONE = 0xFFFFFFFFu;
@@ -391,6 +392,153 @@ inline float depth_at(const Setup& s, int64_t F1, int64_t F2) {
     return z;
 }
 
+// ---------------------------------------------------------------------------------------------
+// PBR fragment path — the reference's LIVE shader: surface_pbr.frag:38-50 -> BRDF_Lighting, pbr.glsl:368-451,
+// restated statement for statement with glm's operation order (normalize = v * (1 / sqrt(dot)), clamp = min(max()),
+// vec3 products left to right).  Pinned bit-for-bit against oracle/_ref (tests/test_oracle_golden.py).
+// ---------------------------------------------------------------------------------------------
+struct PbrLight {        // std430 layout of pbr.glsl:288-299 (80 B)
+    V3 color, position, direction; float intensity, falloffRadius, cosInnerAngle, cosOuterAngle; uint32_t shadowIndex, type;
+};
+PbrLight load_pbr_light(const uint8_t* p) {
+    PbrLight l;
+    std::memcpy(&l.color, p + 0, 12); std::memcpy(&l.position, p + 16, 12); std::memcpy(&l.direction, p + 32, 12);
+    std::memcpy(&l.intensity, p + 44, 4); std::memcpy(&l.falloffRadius, p + 48, 4); std::memcpy(&l.cosInnerAngle, p + 52, 4);
+    std::memcpy(&l.cosOuterAngle, p + 56, 4); std::memcpy(&l.shadowIndex, p + 60, 4); std::memcpy(&l.type, p + 64, 4);
+    return l;
+}
+struct PbrMaterial {     // MaterialProperties, MaterialSystem.h:41-51 <-> Material, pbr.glsl:78-94 (80 B)
+    V4 baseColor, emissive; float f0, metallic, perceptualRoughness, ambientOcclusion; uint32_t tex[5];
+};
+PbrMaterial load_pbr_material(const uint8_t* p) {
+    PbrMaterial m;
+    std::memcpy(&m.baseColor, p + 0, 16); std::memcpy(&m.emissive, p + 16, 16); std::memcpy(&m.f0, p + 32, 16); std::memcpy(m.tex, p + 48, 20);
+    return m;
+}
+struct PbrRemapped { V3 normal; V4 baseColor; V3 diffuseColor; V4 emissive; V3 f0; float metallic, roughness, occlusion; };
+inline float glm_abs(float x) { return x >= 0.0f ? x : -x; }   // glm/detail/func_common.inl compute_abs (keeps -0)
+inline float glm_clamp(float x, float lo, float hi) { return glm_min(glm_max(x, lo), hi); }
+inline V3 cross3(V3 x, V3 y) { return {x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y}; }   // glm/detail/func_geometric.inl:130-134
+inline V3 scale3(V3 v, float s) { return {v.x * s, v.y * s, v.z * s}; }
+constexpr float PBR_PI = 3.14159265359f;
+
+// GetNormal, pbr.glsl:125-148; tn = texture(normals).xyz when hasMap; derivatives of fragPos / uv in screen x and y
+V3 pbr_get_normal(bool hasMap, V3 tn, V3 q1, V3 q2, const float st1[2], const float st2[2], V3 fragNormal) {
+    if (!hasMap) return fragNormal;
+    V3 tangentNormal = {tn.x * 2.0f - 1.0f, tn.y * 2.0f - 1.0f, tn.z * 2.0f - 1.0f};
+    V3 N = normalize3(fragNormal);
+    V3 T = normalize3(sub3(scale3(q1, st2[1]), scale3(q2, st1[1])));
+    V3 B = neg3(normalize3(cross3(N, T)));
+    V3 r = {(T.x * tangentNormal.x + B.x * tangentNormal.y) + N.x * tangentNormal.z,     // mat3(T, B, N) * v
+            (T.y * tangentNormal.x + B.y * tangentNormal.y) + N.y * tangentNormal.z,
+            (T.z * tangentNormal.x + B.z * tangentNormal.y) + N.z * tangentNormal.z};
+    return normalize3(r);
+}
+
+// BRDF_Lighting, pbr.glsl:368-451, after the texture fetches (which pass their results in `m`)
+V4 pbr_lighting(const PbrRemapped& material, const std::vector<PbrLight>& lights, uint32_t lightCount, V3 fragPos, V3 viewPosition,
+                float exposure, uint32_t debugInput, uint32_t debugEquation, bool haveShadow, const float* STR, const float* shadowMap, uint32_t S) {
+    const V3 n = material.normal;
+    const V3 v = normalize3(sub3(viewPosition, fragPos));
+    V3 Fd = {0, 0, 0}, F = {0, 0, 0}, Fr = {0, 0, 0}; float D = 0.0f, G = 0.0f, NoV = 0.0f, NoL = 0.0f;   // brdf / pbr of the LAST light (debug views)
+    V3 l0 = {0.0f, 0.0f, 0.0f};
+    for (uint32_t li = 0; li < lightCount; ++li) {
+        const PbrLight& light = lights[li];
+        V3 l = normalize3(sub3(light.position, fragPos));                       // GetLightDirection, pbr.glsl:303-311
+        if (light.type == LIGHT_TYPE_DIRECTIONAL) l = normalize3(neg3(light.direction));
+        const V3 h = normalize3(add3(v, l));
+        NoV = glm_abs(dot3(n, v)) + 1e-5f;
+        const float NoH = glm_clamp(dot3(n, h), 0.0f, 1.0f);
+        NoL = glm_clamp(dot3(n, l), 0.0f, 1.0f);
+        const float HoL = glm_clamp(dot3(h, l), 0.0f, 1.0f);
+        {   // BRDF, pbr.glsl:262-279
+            const float a = material.roughness;
+            { const float a2 = a * a; const float f = (NoH * a2 - NoH) * NoH + 1.0f; D = a2 / (PBR_PI * f * f); }   // D_GGX
+            { const float p5 = std::pow((1.0f - HoL), 5.0f);                                                          // F_Schlick
+              F = {material.f0.x + (1.0f - material.f0.x) * p5, material.f0.y + (1.0f - material.f0.y) * p5, material.f0.z + (1.0f - material.f0.z) * p5}; }
+            { const float a2 = a * a;                                                                                 // G_SmithGGXCorrelated
+              const float GGXL = NoV * std::sqrt((-NoL * a2 + NoL) * NoL + a2);
+              const float GGXV = NoL * std::sqrt((-NoV * a2 + NoV) * NoV + a2);
+              G = 0.5f / (GGXV + GGXL); }
+            const float DG = D * G;
+            Fr = {DG * F.x, DG * F.y, DG * F.z};
+            const float lambert = 1.0f / PBR_PI;
+            Fd = {(((1.0f - F.x) * material.occlusion) * material.diffuseColor.x) * lambert, (((1.0f - F.y) * material.occlusion) * material.diffuseColor.y) * lambert,
+                  (((1.0f - F.z) * material.occlusion) * material.diffuseColor.z) * lambert};
+        }
+        const V3 FrFd = add3(Fr, Fd);
+        float attenuation = 1.0f;                                               // EvaluatePunctualLight, pbr.glsl:335-352
+        if (light.type == LIGHT_TYPE_POINT || light.type == LIGHT_TYPE_SPOT) {
+            {   // ComputeSquareFalloff(pbr.l, falloffRadius): l is the NORMALISED direction here, as in the reference
+                const float inverseFalloffRadius = 1.0f / glm_max(light.falloffRadius, 0.083f);
+                const float distanceSquare = dot3(l, l);
+                const float factor = distanceSquare * inverseFalloffRadius * inverseFalloffRadius;
+                const float smoothFactor = glm_max(1.0f - factor * factor, 0.0f);
+                attenuation = (smoothFactor * smoothFactor) / glm_max(distanceSquare, 1e-4f);
+            }
+            if (light.type == LIGHT_TYPE_SPOT) {
+                const float spotScale = 1.0f / glm_max(light.cosInnerAngle - light.cosOuterAngle, 1e-4f);
+                const float spotOffset = -light.cosOuterAngle * spotScale;
+                const float cd = dot3(normalize3(neg3(light.direction)), l);
+                const float att = glm_clamp(cd * spotScale + spotOffset, 0.0f, 1.0f);
+                attenuation = attenuation * (att * att);
+            }
+        }
+        const V3 lightResult = {(((FrFd.x * light.intensity) * attenuation) * NoL) * light.color.x, (((FrFd.y * light.intensity) * attenuation) * NoL) * light.color.y,
+                                (((FrFd.z * light.intensity) * attenuation) * NoL) * light.color.z};
+        float shadow = 0.0f;
+        if (light.type == LIGHT_TYPE_DIRECTIONAL && haveShadow && light.shadowIndex == 0) {
+            Light sl; sl.type = (int32_t)light.type; sl.position = light.position;   // ComputeShadow only reads type / position / shadowIndex
+            shadow = compute_shadow(sl, fragPos, n, STR, shadowMap, S);
+        }
+        const float k = 1.0f - shadow;
+        l0 = {l0.x + k * lightResult.x, l0.y + k * lightResult.y, l0.z + k * lightResult.z};
+    }
+    switch (debugInput) {                                                       // pbr.glsl:409-425
+        case 1: return material.baseColor;
+        case 2: return {material.diffuseColor.x, material.diffuseColor.y, material.diffuseColor.z, 1.0f};
+        case 3: return {material.normal.x, material.normal.y, material.normal.z, 1.0f};
+        case 4: return {material.occlusion, material.occlusion, material.occlusion, 1.0f};
+        case 5: return {material.emissive.x * material.emissive.w, material.emissive.y * material.emissive.w, material.emissive.z * material.emissive.w, 1.0f};
+        case 6: return {material.metallic, material.metallic, material.metallic, 1.0f};
+        case 7: return {material.roughness, material.roughness, material.roughness, 1.0f};
+        default: break;
+    }
+    switch (debugEquation) {                                                    // pbr.glsl:427-439
+        case 1: return {Fd.x, Fd.y, Fd.z, 1.0f};
+        case 2: return {F.x, F.y, F.z, 1.0f};
+        case 3: { const float g = (G * 4.0f) * (glm_abs(NoL) * glm_abs(NoV)); return {g, g, g, 1.0f}; }
+        case 4: return {D, D, D, 1.0f};
+        case 5: return {Fr.x, Fr.y, Fr.z, 1.0f};
+        default: break;
+    }
+    V3 color = l0;
+    color = {color.x + material.emissive.x * material.emissive.w, color.y + material.emissive.y * material.emissive.w, color.z + material.emissive.z * material.emissive.w};
+    color = scale3(color, exposure);
+    const V3 ambient = {(0.03f * material.baseColor.x) * material.occlusion, (0.03f * material.baseColor.y) * material.occlusion, (0.03f * material.baseColor.z) * material.occlusion};
+    color = add3(color, ambient);
+    return {color.x, color.y, color.z, material.baseColor.w};
+}
+
+// RemapMaterial, pbr.glsl:186-206, from the already-fetched texture values (each defaults to "no texture")
+PbrRemapped pbr_remap(const PbrMaterial& m, V3 normal, const V4* baseTex, const V4* emissiveTex, const V4* ormTex) {
+    PbrRemapped r;
+    r.normal = normal;
+    r.baseColor = m.baseColor;
+    if (baseTex) r.baseColor = {m.baseColor.x * baseTex->x, m.baseColor.y * baseTex->y, m.baseColor.z * baseTex->z, m.baseColor.w * baseTex->w};
+    r.emissive = m.emissive;
+    if (emissiveTex) r.emissive = {m.emissive.x * emissiveTex->x, m.emissive.y * emissiveTex->y, m.emissive.z * emissiveTex->z, m.emissive.w * emissiveTex->w};
+    V3 orm = {m.ambientOcclusion, m.perceptualRoughness, m.metallic};
+    if (ormTex) orm = {m.ambientOcclusion * ormTex->x, m.perceptualRoughness * ormTex->y, m.metallic * ormTex->z};
+    r.occlusion = orm.x;
+    { const float rr = glm_clamp(orm.y, 0.089f, 1.0f); r.roughness = rr * rr; }
+    r.metallic = orm.z;
+    r.diffuseColor = {(1.0f - r.metallic) * r.baseColor.x, (1.0f - r.metallic) * r.baseColor.y, (1.0f - r.metallic) * r.baseColor.z};
+    const float f0s = m.f0 * (1.0f - r.metallic);
+    r.f0 = {f0s + r.baseColor.x * r.metallic, f0s + r.baseColor.y * r.metallic, f0s + r.baseColor.z * r.metallic};
+    return r;
+}
+
 struct DrawRec { uint32_t indexOffset, nbIndices, materialRaw, sceneNode; };
 
 struct Frontend {
@@ -558,7 +706,11 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
     std::vector<float> nmat((size_t)sc->nNodes * 9);
     for (uint32_t n = 0; n < sc->nNodes; ++n) normal_matrix(sc->transforms + 16 * (size_t)n, &nmat[9 * (size_t)n]);
     std::vector<Light> lights(sc->nLights);
-    for (uint32_t l = 0; l < sc->nLights; ++l) lights[l] = load_light(sc->lights + (size_t)l * sc->lightStride);
+    std::vector<PbrLight> pbrLights(sc->nLights);
+    for (uint32_t l = 0; l < sc->nLights; ++l) {
+        if (sc->shadingModel == 1) pbrLights[l] = load_pbr_light(sc->lights + (size_t)l * sc->lightStride);
+        else lights[l] = load_light(sc->lights + (size_t)l * sc->lightStride);
+    }
     std::vector<Texture> textures;
     for (uint32_t t = 0; t < sc->nTextures; ++t) textures.push_back(build_texture(sc->textures[t]));
 
@@ -604,6 +756,42 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                                  interp(nrm[0].z, nrm[1].z, nrm[2].z)};
                     uint32_t matIndex = dr.materialRaw >> 4;   // MaterialHandle::GetIndex (MaterialDefines.h:88-96)
                     const uint8_t* mr = sc->materials + (size_t)matIndex * sc->materialStride;
+                    if (sc->shadingModel == 1) {   // ---- reference's live PBR fragment path (surface_pbr.frag:38-50) ----
+                        const PbrMaterial pm = load_pbr_material(mr);
+                        auto live = [&](uint32_t h) { return h < sc->maxDescriptors && h < textures.size(); };
+                        const bool anyTex = live(pm.tex[0]) || live(pm.tex[1]) || live(pm.tex[2]) || live(pm.tex[3]);
+                        V3 nrmOut = normal;
+                        V4 tb, te, to; const V4 *pb = nullptr, *pe = nullptr, *po = nullptr;
+                        if (anyTex) {
+                            // attributes here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
+                            float tuv[3][2]; V3 tpos[3];
+                            for (int n = 0; n < 3; ++n) {
+                                int64_t Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
+                                float qq[3];
+                                for (int k = 0; k < 3; ++k) {
+                                    int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
+                                    qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
+                                }
+                                float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
+                                auto ip = [&](float a0, float a1, float a2) { return ((qq[0] * a0 + qq[1] * a1) + qq[2] * a2) * rdd; };
+                                tuv[n][0] = ip(uv[0][0], uv[1][0], uv[2][0]); tuv[n][1] = ip(uv[0][1], uv[1][1], uv[2][1]);
+                                tpos[n] = {ip(world[0].x, world[1].x, world[2].x), ip(world[0].y, world[1].y, world[2].y), ip(world[0].z, world[1].z, world[2].z)};
+                            }
+                            const float st1[2] = {tuv[1][0] - tuv[0][0], tuv[1][1] - tuv[0][1]}, st2[2] = {tuv[2][0] - tuv[0][0], tuv[2][1] - tuv[0][1]};
+                            auto samp = [&](uint32_t h) { return sample_texture(textures[h], tuv[0][0], tuv[0][1], st1[0], st1[1], st2[0], st2[1]); };
+                            if (live(pm.tex[3])) { V4 t = samp(pm.tex[3]); nrmOut = pbr_get_normal(true, {t.x, t.y, t.z}, sub3(tpos[1], tpos[0]), sub3(tpos[2], tpos[0]), st1, st2, normal); }
+                            if (live(pm.tex[0])) { tb = samp(pm.tex[0]); pb = &tb; }
+                            if (live(pm.tex[1])) { te = samp(pm.tex[1]); pe = &te; }
+                            if (live(pm.tex[2])) { to = samp(pm.tex[2]); po = &to; }
+                        }
+                        const PbrRemapped rm = pbr_remap(pm, nrmOut, pb, pe, po);
+                        float exposure; uint32_t dbgIn, dbgEq;
+                        std::memcpy(&exposure, sc->view + 140, 4); std::memcpy(&dbgIn, sc->view + 144, 4); std::memcpy(&dbgEq, sc->view + 148, 4);
+                        out = pbr_lighting(rm, pbrLights, sc->nLights, fragPos, viewPos, exposure, dbgIn, dbgEq, haveShadow, STR, shadowMap, sc->shadowSize);
+                        if (colorF32) { colorF32[4 * p + 0] = out.x; colorF32[4 * p + 1] = out.y; colorF32[4 * p + 2] = out.z; colorF32[4 * p + 3] = out.w; }
+                        if (colorSRGB8) orc_srgb8(&out.x, colorSRGB8 + 4 * p);
+                        continue;
+                    }
                     PhongProps props;
                     uint32_t texHandle[2];
                     std::memcpy(&props.diffuse, mr + 0, 16);
@@ -656,6 +844,18 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
             }
     });
     return 0;
+}
+
+// BRDF_Lighting for one untextured 80-B material and nLights 80-B PBR lights (pins pbr_lighting / pbr_remap against oracle/_ref)
+void orc_pbr_lighting(const uint8_t* material80, const uint8_t* lights80, uint32_t nLights, const float* fragPos, const float* normal, const float* viewPos,
+                      float exposure, uint32_t debugInput, uint32_t debugEquation, const float* transform16, const float* shadowMap, uint32_t S, float* out4) {
+    std::vector<PbrLight> L(nLights);
+    for (uint32_t i = 0; i < nLights; ++i) L[i] = load_pbr_light(lights80 + 80 * (size_t)i);
+    const PbrRemapped rm = pbr_remap(load_pbr_material(material80), {normal[0], normal[1], normal[2]}, nullptr, nullptr, nullptr);
+    const float one = 1.0f;
+    const V4 r = pbr_lighting(rm, L, nLights, {fragPos[0], fragPos[1], fragPos[2]}, {viewPos[0], viewPos[1], viewPos[2]}, exposure, debugInput, debugEquation,
+                              true, transform16, (shadowMap && S) ? shadowMap : &one, (shadowMap && S) ? S : 1u);
+    out4[0] = r.x; out4[1] = r.y; out4[2] = r.z; out4[3] = r.w;
 }
 
 }  // extern "C"

@@ -51,7 +51,8 @@ typedef struct orc_scene {
     uint32_t        nThreads;     /* 0 = hardware_concurrency */
     /* sort-first tile split: only pixels with ((y / bandH) % nRanks) == rank are owned.
        nRanks <= 1 disables. */
-    uint32_t        rank, nRanks, bandH, pad0;
+    uint32_t        rank, nRanks, bandH;
+    uint32_t        shadingModel; /* 0 = Phong (48-B materials, 112-B lights), 1 = PBR (80-B MaterialProperties, 80-B Light: pbr.glsl) */
 } orc_scene;
 
 /* counters[0] = triangles dropped because they need true clipping (w<=0 or guard band),
@@ -70,6 +71,8 @@ void orc_phong_lighting(const uint8_t* light112, const float* props9 /* diffuse4
 float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal,
                          const float* transform16, const float* shadowMap, uint32_t S);
 void orc_srgb8(const float* rgba, uint8_t* out4);
+void orc_pbr_lighting(const uint8_t* material80, const uint8_t* lights80, uint32_t nLights, const float* fragPos, const float* normal, const float* viewPos,
+                      float exposure, uint32_t debugInput, uint32_t debugEquation, const float* transform16, const float* shadowMap, uint32_t S, float* out4);
 
 #ifdef __cplusplus
 }

@@ -36,7 +36,7 @@ class OrcScene(C.Structure):
         ("shadowSize", C.c_uint32), ("maxDescriptors", C.c_uint32),
         ("shadowView", fp), ("shadowProj", fp),
         ("textures", C.POINTER(OrcTexture)), ("nTextures", C.c_uint32), ("nThreads", C.c_uint32),
-        ("rank", C.c_uint32), ("nRanks", C.c_uint32), ("bandH", C.c_uint32), ("pad0", C.c_uint32),
+        ("rank", C.c_uint32), ("nRanks", C.c_uint32), ("bandH", C.c_uint32), ("shadingModel", C.c_uint32),
     ]
 
 
@@ -102,6 +102,7 @@ class Oracle:
             s.textures = arr; s.nTextures = len(texs)
         s.nThreads = n_threads
         s.rank, s.nRanks, s.bandH = rank, n_ranks, band_h
+        s.shadingModel = int(scene.get("shading_model", 0))
         self.s = s
         self.counters = np.zeros(4, np.uint64)
 

@@ -38,7 +38,58 @@ inline vec2 textureSize(const Sampler2D& s, int) { return vec2((float)s.S, (floa
 #include "shadow.inc"
 }  // namespace glsl
 
+// The reference's LIVE fragment path (surface_pbr.frag:38-50 -> pbr.glsl BRDF_Lighting) in its own namespace: pbr.glsl
+// declares its own Light / LIGHT_TYPE_* and re-includes shadow.glsl for that Light.  Untextured materials only here
+// (handles >= MAX_DESCRIPTOR_COUNT), so texture() of a material map and dFdx/dFdy are never reached.
+namespace glsl_pbr {
+using namespace glm;
+typedef unsigned int uint;
+#define MAX_DESCRIPTOR_COUNT 1024
+struct View { mat4 view; mat4 proj; vec3 pos; float exposure; uint debugInput; uint debugEquation; };   // view.glsl:1-9
+using glsl::Sampler2D;
+using glsl::uGlobalTextures2D;
+using glsl::texture;
+using glsl::textureSize;
+#define GetTexture2D(index) uGlobalTextures2D[(index) & 3u]
+inline vec3 dFdx(vec3) { return vec3(0.0f); }
+inline vec3 dFdy(vec3) { return vec3(0.0f); }
+inline vec2 dFdx(vec2) { return vec2(0.0f); }
+inline vec2 dFdy(vec2) { return vec2(0.0f); }
+#include "pbr.inc"
+}  // namespace glsl_pbr
+
 extern "C" {
+
+// BRDF_Lighting (pbr.glsl:368-451) for one untextured material record (80 B, MaterialSystem.h:41-51) and nLights
+// 80-B std430 Light records (pbr.glsl:288-299); shadowMap may be NULL (then S = 0 and directional lights get a map of 1.0).
+void ref_pbr_lighting(const uint8_t* material80, const uint8_t* lights80, uint32_t nLights, const float* fragPos, const float* uv,
+                      const float* normal, const float* viewPos, float exposure, uint32_t debugInput, uint32_t debugEquation,
+                      const float* transform16, const float* shadowMap, uint32_t S, float* out4) {
+    static glsl_pbr::Material mats[1];
+    static glsl_pbr::Light lts[16];
+    static glsl_pbr::MaterialShadowData storage[1];
+    static const float one = 1.0f;
+    std::memcpy(&mats[0], material80, 80);
+    for (uint32_t i = 0; i < nLights && i < 16; ++i) {
+        const uint8_t* p = lights80 + 80 * (size_t)i;
+        std::memcpy(&lts[i].color, p + 0, 12); std::memcpy(&lts[i].position, p + 16, 12); std::memcpy(&lts[i].direction, p + 32, 12);
+        std::memcpy(&lts[i].intensity, p + 44, 4); std::memcpy(&lts[i].falloffRadius, p + 48, 4);
+        std::memcpy(&lts[i].cosInnerAngle, p + 52, 4); std::memcpy(&lts[i].cosOuterAngle, p + 56, 4);
+        std::memcpy(&lts[i].shadowIndex, p + 60, 4); std::memcpy(&lts[i].type, p + 64, 4);
+        lts[i].shadowIndex = 0;
+    }
+    storage[0].transform = glm::make_mat4(transform16);
+    storage[0].shadowMapTextureHandle = 0;
+    glsl_pbr::g_MaterialBuffer = reinterpret_cast<glsl_pbr::MaterialBuffer*>(mats);
+    glsl_pbr::g_LightBuffer = reinterpret_cast<glsl_pbr::LightBuffer*>(lts);
+    glsl_pbr::g_MaterialShadowDataBuffer = reinterpret_cast<glsl_pbr::MaterialShadowDataBuffer*>(storage);
+    if (shadowMap && S) glsl::uGlobalTextures2D[0] = {shadowMap, S}; else glsl::uGlobalTextures2D[0] = {&one, 1};
+    glsl_pbr::View view;
+    view.exposure = exposure; view.debugInput = debugInput; view.debugEquation = debugEquation;
+    glm::vec4 r = glsl_pbr::BRDF_Lighting(glm::make_vec3(fragPos), glm::make_vec2(uv), glm::make_vec3(normal), glm::make_vec3(viewPos),
+                                          0u, 0u, 0u, nLights, 0u, view);
+    std::memcpy(out4, glm::value_ptr(r), 16);
+}
 
 void ref_mat4_mul(const float* a, const float* b, float* out) {
     glm::mat4 r = glm::make_mat4(a) * glm::make_mat4(b);
