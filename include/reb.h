@@ -89,6 +89,16 @@ int reb_shadow_set_transform(reb_ctx* ctx, uint32_t shadowId, const float* view1
 /* CameraViewSystem::Update — CameraViewSystem.cpp:61-72: the 160-B ViewProperties block */
 int reb_set_view(reb_ctx* ctx, const void* viewProperties160);
 
+/* Which fragment path reb_render_forward runs.  REB_SHADING_PHONG (default): phong.glsl PhongLighting, 48-B Phong material
+ * records, 112-B Phong Light records (the north star's path).  REB_SHADING_PBR: the reference's live fragment shader,
+ * surface_pbr.frag:38-50 -> BRDF_Lighting pbr.glsl:368-451 — materials are the reference's 80-B MaterialProperties
+ * (MaterialSystem.h:41-51: baseColor@0 emissive@16 f0@32 metallic@36 perceptualRoughness@40 ambientOcclusion@44
+ * textures[5]@48 = baseColor, emissive, ORM, normals, AO), lights its 80-B Light (LightSystem.h:22-33 / pbr.glsl:288-299);
+ * exposure / debugInput / debugEquation are read from the ViewProperties block (@140 / @144 / @148). */
+#define REB_SHADING_PHONG 0u
+#define REB_SHADING_PBR   1u
+int reb_set_shading_model(reb_ctx* ctx, uint32_t model);
+
 /* ShadowSystem::Render(drawCommands) — ShadowSystem.cpp:319-376 */
 int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, uint32_t n);
 /* RenderScene::RenderBasePass -> MaterialSystem::Draw — RenderScene.cpp:210-242, MaterialSystem.cpp:88-101 */

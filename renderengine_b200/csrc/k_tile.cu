@@ -14,6 +14,7 @@
 // Reference: fixed-function raster/depth state GraphicsPipelineCache.cpp:280-340; fragment work
 // phong.glsl:39-81 + shadow.glsl:24-56; clears RenderScene.cpp:217-220 / ShadowSystem.cpp:111-127.
 #include "reb_shade.cuh"
+#include "reb_shade_pbr.cuh"
 #include <algorithm>
 
 namespace reb {
@@ -274,7 +275,7 @@ __device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, u
 }
 
 // One 8 x 4 block: re-arm vis, merge large triangles, shade, write.  All arguments but key are warp-uniform.
-template <bool TEXTURED>
+template <bool TEXTURED, bool PBR>
 __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& sh, unsigned long long key0, int bx0, int by0, int lx, int ly, uint32_t nHuge,
                                          const HugeStage& hs, uint32_t begin, uint32_t end, WarpStage& ws, unsigned lane) {
     if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
@@ -292,7 +293,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     if (key[0] != VIS_CLEAR) {
         depth = __uint_as_float((uint32_t)(key[0] >> 32));
         tri = ~(uint32_t)key[0];
-        if (sh.outSRGB8 || sh.outF32) col = shade_pixel<TEXTURED>(pc, sh, x, y, tri);
+        if (sh.outSRGB8 || sh.outF32) col = PBR ? shade_pixel_pbr<TEXTURED>(pc, sh, x, y, tri) : shade_pixel<TEXTURED>(pc, sh, x, y, tri);
     }
     if (sh.outDepth) sh.outDepth[p] = depth;
     if (sh.outTriId) sh.outTriId[p] = tri;
@@ -303,7 +304,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
 #ifndef KT_MODE
 #define KT_MODE 1
 #endif
-template <bool TEXTURED>
+template <bool TEXTURED, bool PBR>
 __global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
@@ -322,7 +323,7 @@ __global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(cons
     if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
     uint32_t begin, end;
     kt_tile_list(pc, tile, nLarge, begin, end);
-    kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
+    kt_block<TEXTURED, PBR>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
                        stage[warp], lane);
 #elif KT_MODE == 1
     // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
@@ -340,7 +341,7 @@ __global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(cons
         if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) continue;
         uint32_t begin, end;
         kt_tile_list(pc, tile, nLarge, begin, end);
-        kt_block<TEXTURED>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
+        kt_block<TEXTURED, PBR>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
                            end, stage[warp], lane);
     }
 #endif
@@ -354,22 +355,23 @@ void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st) {
 }
 
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st) {
-    // the textured variant carries the uv derivatives + sampler state; untextured scenes keep the leaner kernel
-    const bool tex = sh.nTextures && pc.vtxUV;
-    static int perSM[2] = {0, 0};
-    if (!perSM[tex]) {
+    // the textured variants carry the uv derivatives + sampler state; untextured scenes keep the leaner kernels
+    const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
+    using Kern = void (*)(PassConst, ShadeConst);
+    static const Kern kern[4] = {k_tile_forward<false, false>, k_tile_forward<true, false>, k_tile_forward<false, true>, k_tile_forward<true, true>};
+    const int v = (tex ? 1 : 0) | (pbr ? 2 : 0);
+    static int perSM[4] = {0, 0, 0, 0};
+    if (!perSM[v]) {
         int n = 0;
-        if (tex) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_tile_forward<true>, KT_THREADS, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_tile_forward<false>, KT_THREADS, 0);
-        perSM[tex] = n > 0 ? n : 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], KT_THREADS, 0);
+        perSM[v] = n > 0 ? n : 1;
     }
 #if KT_MODE == 0
     const uint32_t grid = pc.tilesX * pc.tilesY;
 #else
-    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[tex]));
+    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[v]));
 #endif
-    if (tex) launch_k(k_tile_forward<true>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
-    else launch_k(k_tile_forward<false>, dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
+    launch_k(kern[v], dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
 }
 
 }  // namespace reb

@@ -49,6 +49,8 @@ struct reb_ctx {
     std::vector<TexDev> texHost; std::vector<void*> texAllocs; TexDev* dTextures = nullptr; size_t texTableCap = 0; bool texDirty = false;
     // view
     float view[16], proj[16], PV[16], viewPos[3]; bool haveView = false;
+    float exposure = 1.0f; uint32_t debugInput = 0, debugEquation = 0;   // ViewProperties @140 / @144 / @148 (PBR path)
+    uint32_t shadingModel = 0;                                           // REB_SHADING_PHONG / REB_SHADING_PBR
     // shadow (one directional shadow map, F10)
     uint32_t S = 0; float* shadowMap = nullptr; float sview[16], sproj[16], SPV[16]; bool haveShadowXf = false, shadowValid = false;
     // outputs + visibility buffer
@@ -363,6 +365,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         std::memcpy(sh.lightsC, ctx->lightsHost, sizeof sh.lightsC);
         const bool useShadow = ctx->shadowMap && ctx->shadowValid && ctx->haveShadowXf;
         sh.shadowMap = useShadow ? ctx->shadowMap : nullptr; sh.shadowSize = useShadow ? ctx->S : 0;
+        sh.shadingModel = ctx->shadingModel; sh.exposure = ctx->exposure; sh.debugInput = ctx->debugInput; sh.debugEquation = ctx->debugEquation;
         sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
         launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++;

@@ -142,10 +142,10 @@ int reb_upload_materials(reb_ctx* ctx, const void* records, uint32_t stride, uin
 
 int reb_upload_lights(reb_ctx* ctx, const void* records, uint32_t stride, uint32_t n) {
     CHECK_CTX();
-    int rc = upload_records(ctx, &ctx->lights, records, stride, n, 112, "reb_upload_lights");
+    int rc = upload_records(ctx, &ctx->lights, records, stride, n, 80, "reb_upload_lights");
     if (rc == REB_OK) {
         ctx->lightStride = stride; ctx->nLights = n;
-        for (uint32_t i = 0; i < n && i < (uint32_t)SHADE_CONST_LIGHTS; ++i) std::memcpy(ctx->lightsHost[i], static_cast<const uint8_t*>(records) + (size_t)i * stride, 112);
+        for (uint32_t i = 0; i < n && i < (uint32_t)SHADE_CONST_LIGHTS; ++i) std::memcpy(ctx->lightsHost[i], static_cast<const uint8_t*>(records) + (size_t)i * stride, std::min<uint32_t>(stride, 112u));
     }
     return rc;
 }
@@ -211,6 +211,7 @@ int reb_set_view(reb_ctx* ctx, const void* vp) {
     if (!vp) return fail(ctx, REB_E_INVALID, "reb_set_view: null");
     const float* f = static_cast<const float*>(vp);
     std::memcpy(ctx->view, f, 64); std::memcpy(ctx->proj, f + 16, 64); std::memcpy(ctx->viewPos, f + 32, 12);
+    std::memcpy(&ctx->exposure, f + 35, 4); std::memcpy(&ctx->debugInput, f + 36, 4); std::memcpy(&ctx->debugEquation, f + 37, 4);   // view.glsl:1-9
     mat4_mul(ctx->proj, ctx->view, ctx->PV);      // primitive.vert:53
     ctx->haveView = true;
     return REB_OK;
@@ -246,9 +247,20 @@ int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
     if ((rc = ready_to_render(ctx))) return rc;
     if (!ctx->materials || !ctx->nMaterials) return fail(ctx, REB_E_INVALID, "reb_render_forward before reb_upload_materials");
     if (ctx->nLights && !ctx->lights) return fail(ctx, REB_E_INVALID, "reb_render_forward: lights missing");
+    if (ctx->shadingModel == REB_SHADING_PBR && (ctx->materialStride < 80 || (ctx->nLights && ctx->lightStride < 80)))
+        return fail(ctx, REB_E_INVALID, "reb_render_forward: the PBR model needs 80-B MaterialProperties and 80-B Light records");
+    if (ctx->shadingModel == REB_SHADING_PHONG && ctx->nLights && ctx->lightStride < 112)
+        return fail(ctx, REB_E_INVALID, "reb_render_forward: the Phong model needs 112-B Light records (phong.glsl:20-37)");
     CU(cudaSetDevice(ctx->device));
     if ((rc = set_draws(ctx, 1, draws, n))) return rc;
     return submit_forward(ctx);
+}
+
+int reb_set_shading_model(reb_ctx* ctx, uint32_t model) {
+    CHECK_CTX();
+    if (model != REB_SHADING_PHONG && model != REB_SHADING_PBR) return fail(ctx, REB_E_INVALID, "reb_set_shading_model: unknown model");
+    ctx->shadingModel = model;
+    return REB_OK;
 }
 
 int reb_flush(reb_ctx* ctx) {

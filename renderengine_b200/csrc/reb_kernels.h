@@ -15,6 +15,8 @@ struct ShadeConst {
     const uint8_t* lights; uint32_t lightStride;
     float4 lightsC[SHADE_CONST_LIGHTS][7];   // copy of the first records of `lights`
     const float* shadowMap; uint32_t shadowSize;   // NULL / 0: shadow = 0
+    uint32_t shadingModel;                         // 0 = Phong (phong.glsl), 1 = PBR (pbr.glsl, the reference's live fragment path)
+    float exposure; uint32_t debugInput, debugEquation;   // View (view.glsl:1-9), read by the PBR path only
     uint32_t maxDescriptors; uint32_t nTextures;
     const TexDev* textures;
     uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;

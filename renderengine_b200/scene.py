@@ -170,6 +170,82 @@ def pack_material(diffuse, specular, shininess, diffuse_tex=INVALID_HANDLE, spec
     return rec
 
 
+PBR_MATERIAL_STRIDE = 80
+PBR_LIGHT_STRIDE = 80
+
+
+def pack_pbr_light(ltype, color, position, direction, intensity, falloff_radius=10.0, cos_inner=1.0, cos_outer=0.0, shadow_index=0):
+    """80-B std430 Light of the reference's live shader (LightSystem.h:22-33 / pbr.glsl:288-299)."""
+    rec = np.zeros(PBR_LIGHT_STRIDE, np.uint8)
+    f = rec.view(f32); u = rec.view(np.uint32)
+    f[0:3] = color; f[4:7] = position; f[8:11] = direction
+    f[11] = intensity; f[12] = falloff_radius; f[13] = cos_inner; f[14] = cos_outer
+    u[15] = shadow_index; u[16] = ltype
+    return rec
+
+
+def pack_pbr_material(base_color, emissive, f0, metallic, roughness, occlusion, textures=(INVALID_HANDLE,) * 5):
+    """80-B MaterialProperties (MaterialSystem.h:41-51 <-> Material, pbr.glsl:78-94); textures = baseColor, emissive, ORM, normals, AO."""
+    rec = np.zeros(PBR_MATERIAL_STRIDE, np.uint8)
+    f = rec.view(f32); u = rec.view(np.uint32)
+    f[0:4] = base_color; f[4:8] = emissive; f[8] = f0; f[9] = metallic; f[10] = roughness; f[11] = occlusion
+    u[12:17] = np.asarray(textures, np.uint32)
+    return rec
+
+
+def make_pbr_textures(n_sets, size, seed=1234):
+    """n_sets x 4 procedural RGBA16 maps per set: [4k] base colour (sRGB), [4k+1] emissive (sRGB), [4k+2] occlusion /
+    roughness / metallic (linear), [4k+3] tangent-space normals (linear, smooth bumps)."""
+    rng = np.random.default_rng(seed + 991)
+    yy, xx = np.mgrid[0:size, 0:size]
+    out = []
+    for k in range(n_sets):
+        cell = 2 << (k % 3)
+        checker = (((xx // cell) + (yy // cell)) & 1).astype(np.float64)[..., None]
+        base = np.clip(checker * rng.uniform(0.3, 1.0, 3) + (1 - checker) * rng.uniform(0.05, 0.6, 3) + rng.uniform(-0.05, 0.05, (size, size, 1)), 0, 1)
+        emis = np.clip((1 - checker) * rng.uniform(0.0, 0.4, 3), 0, 1)
+        orm = np.clip(np.stack([0.7 + 0.3 * checker[..., 0], 0.25 + 0.6 * ((xx + yy) % 16) / 15.0, checker[..., 0] * (k % 2)], axis=2), 0, 1)
+        fx, fy = 2 * np.pi * (1 + k % 3) / size, 2 * np.pi * (1 + (k + 1) % 3) / size
+        nx, ny = 0.35 * np.cos(fx * xx), 0.35 * np.sin(fy * yy)
+        nz = np.sqrt(np.maximum(1 - nx * nx - ny * ny, 0.1))
+        nrm = np.stack([nx, ny, nz], axis=2) * 0.5 + 0.5
+        one = np.ones((size, size, 1))
+        for tex, srgb in ((base, 1), (emis, 1), (orm, 0), (nrm, 0)):
+            out.append(dict(texels=np.round(np.concatenate([tex, one], axis=2) * 65535.0).astype(np.uint16), srgb=srgb))
+    return out
+
+
+def to_pbr(scene, seed=1234, n_texture_sets=0, tex_size=64, extra_lights=True, exposure=1.0, debug_input=0, debug_equation=0):
+    """Re-dress a scene dict for the reference's live PBR fragment path: 80-B materials / lights, optional texture sets
+    (every second material fully textured, incl. normal map), a point and a spot light next to the shadowed directional one."""
+    rng = np.random.default_rng(seed + 5)
+    s = dict(scene)
+    n_mat = scene["materials"].shape[0]
+    s["textures"] = make_pbr_textures(n_texture_sets, tex_size, seed) if n_texture_sets else []
+    mats = []
+    for k in range(n_mat):
+        tex = [INVALID_HANDLE] * 5
+        if n_texture_sets and k % 2 == 0:
+            b = 4 * ((k // 2) % n_texture_sets)
+            tex = [b, b + 1 if k % 4 == 0 else INVALID_HANDLE, b + 2, b + 3 if k % 3 != 1 else INVALID_HANDLE, INVALID_HANDLE]
+        mats.append(pack_pbr_material(np.r_[rng.uniform(0.2, 1.0, 3), 1.0].astype(f32), np.r_[rng.uniform(0.0, 0.2, 3), f32(k % 3 == 0)].astype(f32),
+                                      0.04, f32((k % 4 == 1) * 1.0 + (k % 4 == 2) * 0.5), f32(rng.uniform(0.15, 0.9)), f32(rng.uniform(0.6, 1.0)), tex))
+    s["materials"] = np.stack(mats)
+    ldir = _norm([-0.3, -1.0, -0.2])
+    ex, ez = scene["extent"]
+    lights = [pack_pbr_light(LIGHT_DIRECTIONAL, [1.0, 0.97, 0.9], (-ldir * f32(50)).astype(f32), ldir, 2.5)]
+    if extra_lights:
+        lights.append(pack_pbr_light(LIGHT_POINT, [0.3, 0.5, 1.0], [f32(-0.4 * ex), f32(2.5), f32(0.3 * ez)], [0, -1, 0], 40.0, falloff_radius=25.0))
+        lights.append(pack_pbr_light(LIGHT_SPOT, [1.0, 0.4, 0.3], [f32(0.5 * ex), f32(3.0), f32(-0.2 * ez)], _norm([-0.2, -1.0, 0.1]), 60.0,
+                                     falloff_radius=30.0, cos_inner=0.92, cos_outer=0.75))
+    s["lights"] = np.stack(lights)
+    v = np.array(scene["view"], copy=True)
+    v.view(f32)[35] = exposure; v.view(np.uint32)[36] = debug_input; v.view(np.uint32)[37] = debug_equation
+    s["view"] = v
+    s["shading_model"] = 1
+    return s
+
+
 # ---------------------------------------------------------------------------------------------
 # geometry
 # ---------------------------------------------------------------------------------------------

@@ -275,3 +275,59 @@ def test_async_readback_swapchain_matches_blocking_readback():
     for w, h in zip(want, host):
         assert np.array_equal(w.reshape(h.shape), h.numpy())
     assert not np.array_equal(want[0], want[1])
+
+
+# ---- the reference's live PBR fragment path (surface_pbr.frag -> pbr.glsl BRDF_Lighting), SURVEY.md 8f row 1 -------------
+@pytest.mark.parametrize("config", ["small", "C1"])
+def test_parity_pbr_untextured(config):
+    """80-B MaterialProperties / Light records, directional (shadowed) + point + spot lights, GGX / Smith / Schlick."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    base = sc.make_scene(config) if config != "C1" else sc.make_scene(config, shadow_size=1024)
+    s = sc.to_pbr(base)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    check_parity(s, gpu, ref_shadow, ref)
+    assert ref["color_f32"][..., :3].max() > 1.5   # there are specular highlights above the sRGB range (HDR buffer exercised)
+
+
+def test_parity_pbr_textured_normal_mapped():
+    """Base-colour (sRGB), emissive, ORM and tangent-space normal maps through the bindless table; the perturbed normal
+    feeds the PCF bias, so a tap can flip where `depth - bias` ties with the map to the last ulp: such pixels are bounded."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.to_pbr(sc.make_scene("small"), n_texture_sets=3)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    assert np.array_equal(gpu["shadow"].view(np.uint32), ref_shadow.view(np.uint32))
+    assert np.array_equal(gpu["tri_id"], ref["tri_id"]) and np.array_equal(gpu["depth"].view(np.uint32), ref["depth"].view(np.uint32))
+    d8 = np.abs(gpu["color_srgb8"].astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max(axis=2)
+    assert (d8 > 1).mean() <= 1e-4, f"{np.count_nonzero(d8 > 1)} pixels beyond 1 LSB (max {d8.max()})"
+    assert _psnr(gpu["color_f32"], ref["color_f32"]) >= 50.0
+
+
+@pytest.mark.parametrize("dbg", [(1, 0), (3, 0), (5, 0), (7, 0), (0, 1), (0, 2), (0, 3), (0, 4), (0, 5)])
+def test_parity_pbr_debug_views(dbg):
+    """view.debugInput / view.debugEquation (pbr.glsl:409-439; CameraViewSystem::SetViewDebug)."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.to_pbr(sc.make_scene("tiny"), debug_input=dbg[0], debug_equation=dbg[1])
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    check_parity(s, gpu, ref_shadow, ref)
+
+
+def test_pbr_rejects_phong_records():
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("tiny")
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.set_shading_model(1)   # 48-B Phong materials are too short for the PBR path
+    with pytest.raises(RuntimeError):
+        ctx.render_forward(s["draws"])
