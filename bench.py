@@ -110,10 +110,17 @@ def cpu_reference_frames(scene, n_frames, warm=1):
     return times, cores
 
 
+def build_scene(args):
+    scene = sc.make_scene(args.config)
+    if args.shading == "pbr":
+        scene = sc.to_pbr(scene)
+    return scene
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    scene = sc.make_scene(args.config)
+    scene = build_scene(args)
     budget_s = 150.0
     probe, cores = cpu_reference_frames(scene, 1, warm=1)
     steps = max(1, min(args.steps, int(budget_s / max(probe[0], 1e-3))))
@@ -125,7 +132,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "frames_per_s": 1e3 / ms,
-        "config": {"workload": f"{args.config}: {scene['n_triangles']} tris, {scene['width']}x{scene['height']}, shadow {scene['shadow_size']}^2 3x3 PCF, full frame (shadow + forward) per step"},
+        "config": {"workload": f"{args.config}: {scene['n_triangles']} tris, {scene['width']}x{scene['height']}, shadow {scene['shadow_size']}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong")},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{steps} full frames of the same workload on the CPU oracle (reference Vulkan/lavapipe path unavailable on this box)"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -148,6 +155,8 @@ def main():
     ap.add_argument("--config", default="C2")
     ap.add_argument("--mode", default="views", choices=["views", "tiles"])
     ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast"])
+    ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
+                    help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -169,7 +178,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    scene = sc.make_scene(args.config)
+    scene = build_scene(args)
     T, W, H, S = scene["n_triangles"], scene["width"], scene["height"], scene["shadow_size"]
     tiles = args.mode == "tiles" and world > 1
     share = args.shadow_share or ("broadcast" if tiles else "replicate")
@@ -301,7 +310,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
-            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step",
+            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong"),
                        "parallelism": ("sort-first row bands x%d" % world) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,

@@ -304,8 +304,11 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
 #ifndef KT_MODE
 #define KT_MODE 1
 #endif
+#ifndef KT_PBR_MIN_BLOCKS
+#define KT_PBR_MIN_BLOCKS 3
+#endif
 template <bool TEXTURED, bool PBR>
-__global__ void __launch_bounds__(KT_THREADS, KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
+__global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
     pdl_enter();

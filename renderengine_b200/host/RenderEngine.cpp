@@ -70,6 +70,14 @@ void Renderer::Check(int status, const char* what) const {
     throw std::runtime_error(msg);
 }
 void Renderer::WaitIdle() const { Check(reb_sync(m_ctx), "reb_sync"); }
+void Renderer::SetShadingModel(uint32_t model) const { Check(reb_set_shading_model(m_ctx, model), "reb_set_shading_model"); }
+void pbr::LightSystem::UploadToGPU(Renderer& renderer) {
+    renderer.Check(reb_upload_lights(renderer.GetContext(), m_lights.data(), sizeof(Light), (uint32_t)m_lights.size()), "pbr::LightSystem::UploadToGPU");
+}
+void pbr::MaterialSystem::UploadToGPU(Renderer& renderer) {
+    renderer.Check(reb_upload_materials(renderer.GetContext(), m_properties.data(), sizeof(MaterialProperties), (uint32_t)m_properties.size()),
+                   "pbr::MaterialSystem::UploadToGPU");
+}
 void Renderer::Submit() const { Check(reb_flush(m_ctx), "reb_flush"); }
 void Renderer::Readback(reb_output_kind kind, void* host) const { Check(reb_readback(m_ctx, kind, host), "reb_readback"); }
 std::vector<reb_draw> Renderer::ToDraws(const std::vector<MeshDrawInfo>& drawCalls) {

@@ -208,6 +208,46 @@ private:
     std::vector<MaterialPipelineProperties> m_pipelineProperties;
 };
 
+// ---- PBR records: the reference's OWN GPU-visible structs for its live fragment path (surface_pbr.frag -> pbr.glsl) --------------
+// Use with Renderer::SetShadingModel(REB_SHADING_PBR): pbr::LightSystem / pbr::MaterialSystem upload 80-B records.
+namespace pbr {
+struct alignas(16) Light {   // LightSystem.h:22-33 <-> pbr.glsl:288-299 (std430, 80 B)
+    float color[3] = {1, 1, 1}; float pad0 = 0;
+    float position[3] = {0, 0, 0}; float pad1 = 0;
+    float direction[3] = {0, -1, 0}; float intensity = 1.0f;
+    float falloffRadius = 1.0f, cosInnerAngle = 1.0f, cosOuterAngle = 0.0f; uint32_t shadowIndex = 0;
+    uint32_t type = static_cast<uint32_t>(LightType::Directional); uint32_t pad2[3] = {0, 0, 0};
+};
+static_assert(sizeof(Light) == 80, "pbr::Light must match the std430 layout of pbr.glsl:288-299");
+struct MaterialProperties {   // MaterialSystem.h:41-51 <-> Material, pbr.glsl:78-94 (80 B)
+    float baseColor[4] = {1, 1, 1, 1}, emissive[4] = {0, 0, 0, 0};
+    float f0 = 0.04f, metallic = 0.0f, perceptualRoughness = 0.5f, ambientOcclusion = 1.0f;
+    TextureHandle baseColorTexture = TextureHandle::Invalid, emissiveTexture = TextureHandle::Invalid, occlusionMetallicRoughnessTexture = TextureHandle::Invalid,
+                  normalsTexture = TextureHandle::Invalid, ambientOcclusionTexture = TextureHandle::Invalid;
+    uint32_t padding[3] = {0, 0, 0};
+};
+static_assert(sizeof(MaterialProperties) == 80, "pbr::MaterialProperties must keep the reference's 80-byte layout");
+class LightSystem {
+public:
+    LightID AddLight(Light light) { m_lights.push_back(light); return static_cast<LightID>(m_lights.size() - 1); }
+    void SetLightShadowID(LightID id, uint32_t shadowID) { m_lights.at(id).shadowIndex = shadowID; }
+    uint32_t GetLightCount() const { return static_cast<uint32_t>(m_lights.size()); }
+    void UploadToGPU(Renderer& renderer);
+private:
+    std::vector<Light> m_lights;
+};
+class MaterialSystem {
+public:
+    MaterialHandle CreateMaterialInstance(const MaterialProperties& properties) {
+        m_properties.push_back(properties);
+        return MaterialHandle(MaterialShadingDomain::Surface, MaterialShadingModel::Lit, (uint32_t)m_properties.size() - 1);
+    }
+    void UploadToGPU(Renderer& renderer);
+private:
+    std::vector<MaterialProperties> m_properties;
+};
+}  // namespace pbr
+
 // ---- ViewProperties (ViewProperties.h:27-35, 160 B) + CameraViewSystem (CameraViewSystem.h:17-40) ---------------------------
 struct alignas(16) ViewProperties {
     float view[16]; float proj[16]; float position[3]; float exposure = 1.0f; uint32_t debugInput = 0, debugEquation = 0; uint32_t pad[2] = {0, 0};
@@ -262,6 +302,7 @@ public:
     uint32_t GetHeight() const { return m_height; }
     void Check(int status, const char* what) const;       // throws std::runtime_error with reb_last_error()
     void WaitIdle() const;                                 // reb_sync (vkDeviceWaitIdle analogue)
+    void SetShadingModel(uint32_t model) const;            // REB_SHADING_PHONG (default) / REB_SHADING_PBR (surface_pbr.frag)
     void Submit() const;                                   // reb_flush (CommandRingBuffer submit analogue, RenderLoop.cpp:124-132)
     void Readback(reb_output_kind kind, void* host) const; // swapchain image -> host (headless present)
     static std::vector<reb_draw> ToDraws(const std::vector<MeshDrawInfo>& drawCalls);
