@@ -323,9 +323,9 @@ inline V4 vertex_stage(const PassParams& pp, const float* T, const float* pos, V
     return mat4_mul(pp.PV, {world.x, world.y, world.z, 1.0f});
 }
 
-inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t triId, Setup& s) {
-    // B.2 trivial reject: all three outside one clip plane
-    bool allL = true, allR = true, allT = true, allB = true, allN = true, allF = true;
+inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t triId, Setup& s, bool skipTrivialReject = false) {
+    // B.2 trivial reject: all three outside one clip plane (the parent of clipped children already passed it)
+    bool allL = !skipTrivialReject, allR = allL, allT = allL, allB = allL, allN = allL, allF = allL;
     for (int k = 0; k < 3; ++k) {
         allL = allL && (c[k].x < -c[k].w); allR = allR && (c[k].x > c[k].w);
         allT = allT && (c[k].y < -c[k].w); allB = allB && (c[k].y > c[k].w);
@@ -359,6 +359,62 @@ inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t 
     if (s.x0 > s.x1 || s.y0 > s.y1) return NO_SAMPLE;
     s.triId = triId;
     return KEEP;
+}
+
+// ---------------------------------------------------------------------------------------------
+// B.3 clipping (revision r1c): a triangle with a vertex at or behind the eye plane (w <= 0) or outside the guard
+// band is clipped in clip space with Sutherland-Hodgman, fp32, fixed plane order (near z >= 0, then the four guard
+// planes |x| <= Gx*w, |y| <= Gy*w with G = (GUARD_PX / 2) / (extent / 2), so a clipped vertex lands within 2^19 px
+// (+ half the extent) of the origin), every intersection computed FROM THE INSIDE vertex towards the outside one:
+// t = d_in / (d_in - d_out), v = v_in + t * (v_out - v_in).  The polygon (<= 8 vertices) is fanned from its first
+// vertex; every child runs the ordinary B.4-B.8 setup and inherits the parent's triId.  Varyings of a clipped parent
+// are interpolated in homogeneous form at shading time (homogeneous_weights below), so children carry positions only.
+// ---------------------------------------------------------------------------------------------
+inline float clip_dist(int plane, const V4& v, float Gx, float Gy) {
+    switch (plane) {
+        case 0: return v.z;
+        case 1: return v.x + Gx * v.w;
+        case 2: return Gx * v.w - v.x;
+        case 3: return v.y + Gy * v.w;
+        default: return Gy * v.w - v.y;
+    }
+}
+inline int clip_polygon(const PassParams& pp, const V4 in[3], V4 out[9]) {
+    const float Gx = (0.5f * GUARD_PX) / (0.5f * (float)pp.W), Gy = (0.5f * GUARD_PX) / (0.5f * (float)pp.H);
+    V4 a[9], b[9];
+    int n = 3;
+    for (int k = 0; k < 3; ++k) a[k] = in[k];
+    for (int plane = 0; plane < 5; ++plane) {
+        int m = 0;
+        for (int i = 0; i < n; ++i) {
+            const V4& P = a[i]; const V4& Q = a[(i + 1) % n];
+            const float dP = clip_dist(plane, P, Gx, Gy), dQ = clip_dist(plane, Q, Gx, Gy);
+            const bool inP = dP >= 0.0f, inQ = dQ >= 0.0f;
+            if (inP) b[m++] = P;
+            if (inP != inQ) {
+                const V4& I = inP ? P : Q; const V4& O = inP ? Q : P;
+                const float dI = inP ? dP : dQ, dO = inP ? dQ : dP;
+                const float t = dI / (dI - dO);
+                b[m++] = {I.x + t * (O.x - I.x), I.y + t * (O.y - I.y), I.z + t * (O.z - I.z), I.w + t * (O.w - I.w)};
+            }
+        }
+        n = m;
+        if (n < 3) return 0;
+        for (int k = 0; k < n; ++k) a[k] = b[k];
+    }
+    for (int k = 0; k < n; ++k) out[k] = a[k];
+    return n;
+}
+
+// Perspective-correct weights of the PARENT triangle at pixel centre (x, y) from its clip-space vertices: lambda = adj([c0 c1 c2]) * (xn, yn, 1)
+// over the (x, y, w) rows; attribute = ((l0 a0 + l1 a1) + l2 a2) * (1 / ((l0 + l1) + l2)).
+inline void homogeneous_weights(const PassParams& pp, const V4 c[3], float px, float py, float l[3]) {
+    const float hw = 0.5f * (float)pp.W, hh = 0.5f * (float)pp.H;
+    const float xn = ((px + 0.5f) - hw) / hw, yn = ((py + 0.5f) - hh) / hh;
+    for (int k = 0; k < 3; ++k) {
+        const V4& u = c[(k + 1) % 3]; const V4& v = c[(k + 2) % 3];
+        l[k] = ((u.y * v.w - u.w * v.y) * xn + (u.w * v.x - u.x * v.w) * yn) + (u.x * v.y - u.y * v.x);
+    }
 }
 
 // B.7 edge functions with interior positive (for A2 < 0) and the top-left bias folded in.
@@ -582,7 +638,17 @@ void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe) {
             Setup s;
             SetupResult r = setup_triangle(pp, c, (uint32_t)tri, s);
             if (r == KEEP) parts[t].push_back(s);
-            else if (r == NEEDS_CLIP) ++clip[t];
+            else if (r == NEEDS_CLIP) {   // B.3: clip, fan, set the children up like any triangle (same triId, parent's place in the order)
+                V4 poly[9];
+                const int n = clip_polygon(pp, c, poly);
+                for (int i = 1; i + 1 < n; ++i) {
+                    const V4 cc[3] = {poly[0], poly[i], poly[i + 1]};
+                    Setup cs;
+                    SetupResult cr = setup_triangle(pp, cc, (uint32_t)tri, cs, /*skipTrivialReject=*/true);
+                    if (cr == KEEP) parts[t].push_back(cs);
+                    else if (cr == NEEDS_CLIP) ++clip[t];   // cannot happen for finite inputs; counted, dropped
+                }
+            }
         }
     });
     size_t n = 0;
@@ -737,16 +803,21 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                         uv[k][0] = v[6]; uv[k][1] = v[7];
                     }
                     Setup s;
-                    setup_triangle(pp, c, tri, s);
-                    Edges e = make_edges(s);
-                    int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
-                    float inv = 1.0f / (float)(-s.A2);
-                    float b[3], q[3];
-                    for (int k = 0; k < 3; ++k) {
-                        int64_t F = e.A[k] * Px + e.B[k] * Py + e.C[k];
-                        b[k] = (float)F * inv;
-                        q[k] = b[k] * (1.0f / s.w[k]);   // B.10 perspective-correct weights
-                    }
+                    const bool clippedParent = setup_triangle(pp, c, tri, s) == NEEDS_CLIP;   // B.3: the pixel was won by one of its clipped children
+                    Edges e{}; float inv = 0.0f;
+                    if (!clippedParent) { e = make_edges(s); inv = 1.0f / (float)(-s.A2); }
+                    const int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
+                    // B.10 perspective-correct weights at pixel (x + ox, y + oy): from the snapped vertices, or in homogeneous form for a clipped parent
+                    auto weights = [&](int ox, int oy, float qq[3]) {
+                        if (clippedParent) { homogeneous_weights(pp, c, (float)(x + ox), (float)(y + oy), qq); return; }
+                        const int64_t Qx = Px + 256 * ox, Qy = Py + 256 * oy;
+                        for (int k = 0; k < 3; ++k) {
+                            int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
+                            qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
+                        }
+                    };
+                    float q[3];
+                    weights(0, 0, q);
                     float den = (q[0] + q[1]) + q[2];
                     float rden = 1.0f / den;             // r1b: one reciprocal per fragment, then multiplies
                     auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) * rden; };
@@ -766,12 +837,8 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                             // attributes here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
                             float tuv[3][2]; V3 tpos[3];
                             for (int n = 0; n < 3; ++n) {
-                                int64_t Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
                                 float qq[3];
-                                for (int k = 0; k < 3; ++k) {
-                                    int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
-                                    qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
-                                }
+                                weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
                                 float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
                                 auto ip = [&](float a0, float a1, float a2) { return ((qq[0] * a0 + qq[1] * a1) + qq[2] * a2) * rdd; };
                                 tuv[n][0] = ip(uv[0][0], uv[1][0], uv[2][0]); tuv[n][1] = ip(uv[0][1], uv[1][1], uv[2][1]);
@@ -806,12 +873,8 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                         // uv here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
                         float tuv[3][2];
                         for (int n = 0; n < 3; ++n) {
-                            int64_t Qx = Px + (n == 1 ? 256 : 0), Qy = Py + (n == 2 ? 256 : 0);
                             float qq[3];
-                            for (int k = 0; k < 3; ++k) {
-                                int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
-                                qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
-                            }
+                            weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
                             float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
                             tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) * rdd;
                             tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) * rdd;

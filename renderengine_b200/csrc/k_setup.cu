@@ -289,11 +289,12 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         const uint32_t tri = batch * 32u + lane;
         k1_gather(pc, tri, k1_load_slots(pc, tri), q);
     }
+    uint3 ns = k1_load_slots(pc, (batch + totalWarps) * 32u + lane);   // slot stream runs two batches ahead of the raster stages
     uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
     while (batch < nBatches) {
         const uint32_t nbatch = batch + totalWarps;
         const uint32_t tri = batch * 32u + lane, ntri = nbatch * 32u + lane;
-        const uint3 ns = k1_load_slots(pc, ntri);                  // in flight during classification
+        const uint3 nns = k1_load_slots(pc, (nbatch + totalWarps) * 32u + lane);   // in flight for a whole iteration
 
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
@@ -307,6 +308,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         ringPos += __popc(smallMask);
         rowTail += __shfl_sync(0xFFFFFFFFu, hIncl, 31);
         k1_gather(pc, ntri, ns, q);                                 // in flight during the raster stages
+        ns = nns;
         __syncwarp();
 
         // ---- 2./3. rows -> samples -> resolve ----------------------------------------------------------------

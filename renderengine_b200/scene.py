@@ -400,6 +400,15 @@ def view_for_azimuth(scene, azimuth):
     return pack_view(view, proj, eye)
 
 
+def view_from(scene, eye, look, fov=45.0, near=0.01, far=100.0):
+    """A 160-B ViewProperties record for an arbitrary camera (e.g. INSIDE the scene, so geometry crosses the eye plane
+    and the guard band and takes the clipping path, Appendix B.3)."""
+    eye = np.asarray(eye, f32)
+    view = camera_view(eye, np.asarray(look, f32), np.array([0, 1, 0], f32))
+    proj = perspective_clip(fov, f32(scene["width"]) / f32(scene["height"]), near, far)
+    return pack_view(view, proj, eye)
+
+
 def algorithmic_bytes(scene, hdr=False):
     """Compulsory HBM traffic per frame: returns (B_shadow, B_forward)."""
     V, T = scene["n_vertices"], scene["n_triangles"]
