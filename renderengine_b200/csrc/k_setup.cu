@@ -101,25 +101,24 @@ struct K1Warp {
 };
 struct K1Shared {
     K1Warp w[K1_WARPS];
-    uint32_t cursor, isLast;
 };
 
 struct K1Tri {
     VtxA a[3];
     long long A2;
     int32_t x0, x1, y0, y1;
-    bool isSmall, isLarge;
+    bool isSmall, isLarge, needsClip;
 };
 
 __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, const uint4 q[3], K1Tri& t) {
-    t.isSmall = t.isLarge = false;
+    t.isSmall = t.isLarge = t.needsClip = false;
     t.A2 = 0; t.x0 = t.y0 = 0; t.x1 = t.y1 = -1;
 #pragma unroll
     for (int k = 0; k < 3; ++k) t.a[k] = {(int32_t)q[k].x, (int32_t)q[k].y, __uint_as_float(q[k].z), q[k].w};
     if (!valid) return;
     const uint32_t f0 = t.a[0].flags, f1 = t.a[1].flags, f2 = t.a[2].flags;
     if ((f0 & f1 & f2 & VF_PLANES) != 0u) return;                                   // Appendix B.2 trivial reject
-    if (((f0 | f1 | f2) & VF_NEEDS_CLIP) != 0u) { atomicAdd(&pc.status[1], 1u); return; }   // Appendix B.3 (counted, dropped)
+    if (((f0 | f1 | f2) & VF_NEEDS_CLIP) != 0u) { t.needsClip = true; return; }    // Appendix B.3: clipped by the whole warp below
     const VtxA &a0 = t.a[0], &a1 = t.a[1], &a2 = t.a[2];
     t.A2 = (long long)(a1.X - a0.X) * (long long)(a2.Y - a0.Y) - (long long)(a2.X - a0.X) * (long long)(a1.Y - a0.Y);
     if (t.A2 >= 0) return;                                                          // Appendix B.6: front = CCW = A2 < 0
@@ -170,6 +169,97 @@ __device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uin
         const uint32_t s = __shfl_sync(0xFFFFFFFFu, slot, src);
         if (s < pc.largeCap) tile_walk<false>(pc, X0, Y0, X1, Y1, X2, Y2, s, lane);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Appendix B.3 (revision r1c), the rare path: a triangle with a vertex at / behind the eye plane or outside the guard band.
+// All 32 lanes run this with the SAME triangle (warp-uniform, no divergence): re-run the vertex stage on its three source
+// vertices (the cache holds no clip coordinates), clip in clip space with Sutherland-Hodgman (near z >= 0, then the four
+// guard planes; intersections computed from the inside vertex: t = d_in / (d_in - d_out)), fan the polygon from its
+// first vertex, and send every child through the ordinary viewport / snap / facing / bbox steps into the large-triangle
+// path with the parent's triId.  Returns true when a child was queued into the binned path.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float k1_clip_dist(int plane, float4 v, float Gx, float Gy) {
+    switch (plane) {
+        case 0: return v.z;
+        case 1: return v.x + Gx * v.w;
+        case 2: return Gx * v.w - v.x;
+        case 3: return v.y + Gy * v.w;
+        default: return Gy * v.w - v.y;
+    }
+}
+template <bool SHADOW>
+__device__ __noinline__ bool k1_clip_emit(const PassConst& pc, uint32_t tri, unsigned lane) {
+    const uint32_t d = find_draw<false>(pc.draws, pc.nDraws, tri);
+    const uint32_t* ix = pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri));
+    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * __ldg(&pc.draws[d].node);
+    float T[16];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float4 q = __ldg(Tq + k); T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
+    float4 a[9], b[9];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 p = __ldg(pc.pos4 + __ldg(ix + k));
+        a[k] = vertex_stage<!SHADOW>(pc.PV, T, p.x, p.y, p.z, nullptr);
+    }
+    const float Gx = (0.5f * GUARD_PX) / (0.5f * (float)pc.W), Gy = (0.5f * GUARD_PX) / (0.5f * (float)pc.H);
+    int n = 3;
+    for (int plane = 0; plane < 5; ++plane) {
+        int m = 0;
+        for (int i = 0; i < n; ++i) {
+            const float4 P = a[i], Q = a[i + 1 == n ? 0 : i + 1];
+            const float dP = k1_clip_dist(plane, P, Gx, Gy), dQ = k1_clip_dist(plane, Q, Gx, Gy);
+            const bool inP = dP >= 0.0f, inQ = dQ >= 0.0f;
+            if (inP) b[m++] = P;
+            if (inP != inQ) {
+                const float4 I = inP ? P : Q, O = inP ? Q : P;
+                const float dI = inP ? dP : dQ, dO = inP ? dQ : dP;
+                const float t = dI / (dI - dO);
+                b[m++] = make_float4(I.x + t * (O.x - I.x), I.y + t * (O.y - I.y), I.z + t * (O.z - I.z), I.w + t * (O.w - I.w));
+            }
+        }
+        n = m;
+        if (n < 3) return false;
+        for (int k = 0; k < n; ++k) a[k] = b[k];
+    }
+    bool queued = false;
+    const VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
+    for (int i = 1; i + 1 < n; ++i) {
+        K1Tri t;
+        t.a[0] = v0; t.a[1] = viewport_snap(a[i], pc.W, pc.H); t.a[2] = viewport_snap(a[i + 1], pc.W, pc.H);
+        if (((t.a[0].flags | t.a[1].flags | t.a[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
+            if (lane == 0) atomicAdd(&pc.status[1], 1u);
+            continue;
+        }
+        t.A2 = (long long)(t.a[1].X - t.a[0].X) * (long long)(t.a[2].Y - t.a[0].Y) - (long long)(t.a[2].X - t.a[0].X) * (long long)(t.a[1].Y - t.a[0].Y);
+        if (t.A2 >= 0) continue;                                                        // Appendix B.6 applies to the child
+        const int32_t minX = min(t.a[0].X, min(t.a[1].X, t.a[2].X)), maxX = max(t.a[0].X, max(t.a[1].X, t.a[2].X));
+        const int32_t minY = min(t.a[0].Y, min(t.a[1].Y, t.a[2].Y)), maxY = max(t.a[0].Y, max(t.a[1].Y, t.a[2].Y));
+        t.x0 = max((minX + 127) >> 8, 0); t.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+        t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+        if (t.x0 > t.x1 || t.y0 > t.y1) continue;
+        const LargeRec rec = k1_large_rec(t, tri);
+        const int ntiles = (t.x1 / TILE_W - t.x0 / TILE_W + 1) * (t.y1 / TILE_H - t.y0 / TILE_H + 1);
+        uint32_t slot = 0xFFFFFFFFu;   // 0xFFFFFFFF = went to the broadcast list
+        if (lane == 0) {
+            bool binned = true;
+            if (ntiles > HUGE_TILES) {
+                const uint32_t h = atomicAdd(&pc.status[4], 1u);
+                if (h < (uint32_t)HUGE_CAP) { pc.huge[h] = rec; binned = false; }
+            }
+            if (binned) {
+                slot = atomicAdd(&pc.status[0], 1u);
+                if (slot < pc.largeCap) pc.large[slot] = rec;
+                else { atomicOr(&pc.status[2], OVF_LARGE); slot = 0xFFFFFFFEu; }
+            }
+        }
+        slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+        if (slot < pc.largeCap) {
+            queued = true;
+            tile_walk<false>(pc, rec.X0, rec.Y0, rec.X1, rec.Y1, rec.X2, rec.Y2, slot, lane);
+        }
+    }
+    return queued;
 }
 
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
@@ -279,7 +369,6 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     K1Warp& ws = sm.w[warp];
     const uint32_t nBatches = (pc.nTris + 31u) / 32u;
     const uint32_t totalWarps = gridDim.x * K1_WARPS;
-    bool anyLarge = false;
 
     // static schedule: warp g takes batches g, g + totalWarps, ... (a shared work counter would serialise on one
     // L2 atomic unit: ~10 cycles per same-address atomic-with-return chip-wide, measured as the top stall)
@@ -299,8 +388,11 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
         k1_classify(pc, tri < pc.nTris, q, t);
-        anyLarge = anyLarge || t.isLarge;
         k1_emit_large(pc, t, tri, lane);
+        if (t.needsClip) {   // Appendix B.3, rare: handed to k_clip_layout (keeps the clipper out of this kernel's register budget)
+            const uint32_t qi = atomicAdd(&pc.status[6], 1u);
+            if (qi < pc.clipCap) pc.clipQueue[qi] = tri; else atomicOr(&pc.status[2], OVF_LARGE);
+        }
         const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
         const uint32_t h = t.isSmall ? (uint32_t)(t.y1 - t.y0 + 1) : 0u;
         const uint32_t hIncl = warp_incl_scan(h, lane);
@@ -327,31 +419,46 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         while (pixTail != pixHead) { const uint32_t c = min(32u, pixTail - pixHead); k1_pixels<SHADOW>(pc, ws, pixHead, c, lane); pixHead += c; }
     }
 
-    // ---- tail: the last CTA to get here lays out the per-tile lists of the large triangles ------------------
-    // (only the tile counts have to be visible, so CTAs that queued nothing skip the fence)
-    const int ctaLarge = __syncthreads_or(anyLarge ? 1 : 0);
-    if (ctaLarge) __threadfence();
+    // the tile lists are laid out by k_clip_layout, after the clipped triangles (if any) have been counted too
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1c: clip + layout.  Warps stride over the queue of triangles K1 found to need true clipping (Appendix B.3; empty for
+// ordinary frames) and send their children into the large-triangle path; then the last CTA to finish lays out the
+// per-tile lists (start = running cursor; no ordered scan is needed because list order inside a tile is irrelevant to
+// the min-key resolve; the counts become K2's scatter cursors).
+// ---------------------------------------------------------------------------------------------
+constexpr int KC_THREADS = 128;
+template <bool SHADOW>
+__global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constant__ PassConst pc) {
+    __shared__ uint32_t cursor, isLast;
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t nClip = min(pc.status[6], pc.clipCap);
+    const uint32_t warpsPerGrid = (gridDim.x * KC_THREADS) >> 5;
+    for (uint32_t i = (blockIdx.x * KC_THREADS + threadIdx.x) >> 5; i < nClip; i += warpsPerGrid) k1_clip_emit<SHADOW>(pc, __ldcg(pc.clipQueue + i), lane);
+    __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) { sm.isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; sm.cursor = 0u; }
+    if (threadIdx.x == 0) { isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; cursor = 0u; }
     __syncthreads();
-    if (!sm.isLast) return;
+    if (!isLast) return;
     __threadfence();
     const uint32_t nLarge = min(*reinterpret_cast<volatile uint32_t*>(&pc.status[0]), pc.largeCap);
     if (nLarge == 0) return;
     const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    for (uint32_t i0 = 0; i0 < nTiles; i0 += K1_THREADS) {
+    for (uint32_t i0 = 0; i0 < nTiles; i0 += KC_THREADS) {
         const uint32_t i = i0 + threadIdx.x;
         const uint32_t c = i < nTiles ? __ldcg(pc.tileCount + i) : 0u;
         const uint32_t inc = warp_incl_scan(c, lane);
         uint32_t wbase = 0;
-        if (lane == 31 && inc) wbase = atomicAdd(&sm.cursor, inc);
+        if (lane == 31 && inc) wbase = atomicAdd(&cursor, inc);
         wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
         if (i < nTiles && c) { pc.tileStart[i] = wbase + inc - c; pc.tileCount[i] = 0u; }   // counts become the scatter cursors
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        pc.status[3] = sm.cursor;
-        if (sm.cursor > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
+        pc.status[3] = cursor;
+        if (cursor > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
     }
 }
 
@@ -423,6 +530,11 @@ void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStrea
     const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[shadow]));
     if (shadow) launch_k(k_setup_raster<true>, dim3(grid), dim3(K1_THREADS), st, true, pc);
     else launch_k(k_setup_raster<false>, dim3(grid), dim3(K1_THREADS), st, true, pc);
+}
+
+void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
+    if (shadow) launch_k(k_clip_layout<true>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
+    else launch_k(k_clip_layout<false>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
 }
 
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) {

@@ -63,6 +63,8 @@ struct reb_ctx {
     unsigned long long* vis = nullptr;
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
+    uint32_t* clipQueue = nullptr;   // largeCap entries
+    uint32_t largeAlloc = 0; bool largeWorstCase = false;
     LargeRec* huge = nullptr;        // 2 x HUGE_CAP
     uint32_t* tileCount[2] = {nullptr, nullptr}; uint32_t tileCap[2] = {0, 0};   // per pass: both may be in flight behind one fused K0
     uint32_t* tileStart = nullptr; uint32_t tileStartCap = 0;
@@ -171,12 +173,22 @@ int ensure_tiles(reb_ctx* ctx, int kind, uint32_t nTiles) {
     return REB_OK;
 }
 
+// Large-triangle queue: one slot per triangle plus room for the children of clipped triangles (a clipped parent yields up
+// to 6; the slack starts at 25 % and is raised to the worst case by overflow recovery).  The clip queue holds triangle ids.
 int ensure_large(reb_ctx* ctx, uint32_t nTris) {
-    if (nTris <= ctx->largeCap) return REB_OK;
-    CU(cudaStreamSynchronize(ctx->stream));
-    int rc = dev_alloc(ctx, &ctx->large, (size_t)nTris);
-    if (rc) return rc;
-    ctx->largeCap = nTris;
+    const uint64_t need = (uint64_t)nTris + 64u + (ctx->largeWorstCase ? 6ull * nTris : nTris / 4u);
+    if (need > 0xFFFFFFF0ull) return fail(ctx, REB_E_OVERFLOW, "large-triangle queue would exceed 2^32 records");
+    int rc;
+    if (need > ctx->largeAlloc) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        if ((rc = dev_alloc(ctx, &ctx->large, (size_t)need))) return rc;
+        ctx->largeAlloc = (uint32_t)need;
+    }
+    if (nTris > ctx->largeCap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        if ((rc = dev_alloc(ctx, &ctx->clipQueue, (size_t)nTris))) return rc;
+        ctx->largeCap = nTris;
+    }
     return REB_OK;
 }
 
@@ -290,7 +302,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.nrm4 = ctx->nrm4; pc.transforms = ctx->transforms; pc.nmats = ctx->nmats;
     pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC; pc.vtxUV = (kind == 1 && !ctx->texHost.empty()) ? ps.vtxUV : nullptr;
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
-    pc.large = ctx->large; pc.largeCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
+    pc.large = ctx->large; pc.largeCap = ctx->largeAlloc; pc.clipQueue = ctx->clipQueue; pc.clipCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
     pc.tileCount = ctx->tileCount[kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
     pc.flatSlots = ps.flatSlots;
@@ -345,6 +357,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
     if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
+    if (ps.nTris) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(3);
     if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
     mark(4);
@@ -423,6 +436,7 @@ int check_and_recover(reb_ctx* ctx) {
             const uint32_t* st = ctx->hStatus + 8 * k;
             ctx->counters[0] = (k == 0 ? 0 : ctx->counters[0]) + st[1];
             ctx->counters[1] = st[0]; ctx->counters[2] = st[3];
+            if (st[2] & OVF_LARGE) { overflow = true; ctx->largeWorstCase = true; }   // clip children outgrew the slack: size for the worst case
             if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
         }
         if (!overflow) {

@@ -54,7 +54,7 @@ int reb_destroy(reb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
-                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
+                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};

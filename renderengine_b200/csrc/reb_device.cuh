@@ -69,6 +69,7 @@ struct PassConst {
     unsigned long long* vis;      // forward: W*H 64-bit keys
     uint32_t* depthBits;          // shadow: S*S depth bits (the shadow map itself)
     LargeRec* large; uint32_t largeCap;
+    uint32_t* clipQueue; uint32_t clipCap;   // triangles that need true clipping (Appendix B.3), queued by K1 for k_clip_layout
     LargeRec* huge;               // HUGE_CAP records tested by every tile
     uint32_t tilesX, tilesY;
     uint32_t* tileCount;          // per tile: entries in its large-triangle list (zero outside a pass)
@@ -77,7 +78,7 @@ struct PassConst {
     const uint32_t* flatSlots;    // 3 cache slots per triangle in submission order (indexed mode)
     const uint32_t* triBlockDraw; // draw containing the first triangle of every 256-triangle block
     const uint32_t* slotBlockDraw;// draw containing the first cache slot of every 256-slot block
-    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket [6] block counter
+    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket (k_clip_layout) [6] clip-queue length
     uint32_t* hostStatus;         // mapped pinned mirror of status[0..7], written by the tile stage (no D2H copy node)
     uint32_t rank, nRanks, bandH; // sort-first row bands (forward only)
 };

@@ -39,6 +39,7 @@ void launch_vertex_both(const PassConst& shadowPass, const PassConst& forwardPas
 void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
+void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);   // K1c: Appendix B.3 clipping + tile-list layout
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);
 void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);   // PDL-chained after K1
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);

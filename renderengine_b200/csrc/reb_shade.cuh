@@ -176,6 +176,21 @@ __device__ __forceinline__ uint32_t pack_srgb8(float4 c) {
     return quant8(srgb_oetf(c.x)) | (quant8(srgb_oetf(c.y)) << 8) | (quant8(srgb_oetf(c.z)) << 16) | (quant8(__saturatef(c.w)) << 24);
 }
 
+// Appendix B.3 / B.10 (revision r1c): perspective-correct weights of a CLIPPED parent triangle at pixel centre (px, py), in
+// homogeneous form from its clip-space vertices c_k = PV * (world_k, 1) (exactly what K0 computed):
+// lambda = adj([c0 c1 c2]) * (xn, yn, 1) over the (x, y, w) rows.  Rare path, kept out of line.
+__device__ __noinline__ float4 homogeneous_weights(const PassConst& pc, V3 w0, V3 w1, V3 w2, float px, float py) {
+    const float hw = 0.5f * (float)pc.W, hh = 0.5f * (float)pc.H;
+    const float xn = ((px + 0.5f) - hw) / hw, yn = ((py + 0.5f) - hh) / hh;
+    const float4 c0 = mat4_mul_point(pc.PV, w0.x, w0.y, w0.z), c1 = mat4_mul_point(pc.PV, w1.x, w1.y, w1.z), c2 = mat4_mul_point(pc.PV, w2.x, w2.y, w2.z);
+    float4 l;
+    l.x = ((c1.y * c2.w - c1.w * c2.y) * xn + (c1.w * c2.x - c1.x * c2.w) * yn) + (c1.x * c2.y - c1.y * c2.x);
+    l.y = ((c2.y * c0.w - c2.w * c0.y) * xn + (c2.w * c0.x - c2.x * c0.w) * yn) + (c2.x * c0.y - c2.y * c0.x);
+    l.z = ((c0.y * c1.w - c0.w * c1.y) * xn + (c0.w * c1.x - c0.x * c1.w) * yn) + (c0.x * c1.y - c0.y * c1.x);
+    l.w = 0.0f;
+    return l;
+}
+
 // Shade the sample at pixel (x, y) won by primitive `tri`: re-derive the barycentrics from the cached snapped
 // vertices (exactly the integers triangle setup used), interpolate perspective-correct (Appendix B.10), then the
 // builder-defined Phong main() (Appendix B.11) over phong.glsl + shadow.glsl.
@@ -183,17 +198,18 @@ template <bool TEXTURED>
 __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
     const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
     const uint32_t materialRaw = __ldg(&pc.draws[d].material);
-    int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3];
+    int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3]; uint32_t vflags = 0u;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         const float4* bc = reinterpret_cast<const float4*>(pc.vtxBC + slot);
         const float4 b = __ldg(bc), c = __ldg(bc + 1);
-        X[k] = (int32_t)a.x; Y[k] = (int32_t)a.y;
+        X[k] = (int32_t)a.x; Y[k] = (int32_t)a.y; vflags |= a.w;
         world[k] = {b.x, b.y, b.z}; invw[k] = b.w;
         nrm[k] = {c.x, c.y, c.z};
     }
+    const bool clippedParent = (vflags & VF_NEEDS_CLIP) != 0u;   // the sample was won by a clipped child: no snapped parent vertices
     const long long A2 = mulw(X[1] - X[0], Y[2] - Y[0]) - mulw(X[2] - X[0], Y[1] - Y[0]);
     const int32_t Px = 256 * x + 128, Py = 256 * y + 128;   // |X|, |Y| <= 2^28 (guard band), so every difference below fits int32
     const float inv = 1.0f / (float)(-A2);      // Appendix B.8/B.10 revision r1b: one reciprocal per triangle ...
@@ -205,6 +221,7 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
         const float bk = (float)F * inv;
         q[k] = bk * invw[k];
     }
+    if (clippedParent) { const float4 l = homogeneous_weights(pc, world[0], world[1], world[2], (float)x, (float)y); q[0] = l.x; q[1] = l.y; q[2] = l.z; }
     const float rden = 1.0f / ((q[0] + q[1]) + q[2]);   // ... and one per fragment
 #define REB_INTERP(a0, a1, a2) (((q[0] * (a0) + q[1] * (a1)) + q[2] * (a2)) * rden)
     const V3 fragPos = {REB_INTERP(world[0].x, world[1].x, world[2].x), REB_INTERP(world[0].y, world[1].y, world[2].y),
@@ -241,6 +258,7 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
                 const long long F = mulw(Y[b] - Y[a], Qx - X[a]) + mulw(-(X[b] - X[a]), Qy - Y[a]);
                 qq[k] = ((float)F * inv) * invw[k];
             }
+            if (clippedParent) { const float4 l = homogeneous_weights(pc, world[0], world[1], world[2], (float)(x + (n == 1)), (float)(y + (n == 2))); qq[0] = l.x; qq[1] = l.y; qq[2] = l.z; }
             const float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
             tu[n] = ((qq[0] * uvv[0].x + qq[1] * uvv[1].x) + qq[2] * uvv[2].x) * rdd;
             tv[n] = ((qq[0] * uvv[0].y + qq[1] * uvv[1].y) + qq[2] * uvv[2].y) * rdd;

@@ -119,7 +119,7 @@ template <bool TEXTURED>
 __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
     const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
     const uint32_t materialRaw = __ldg(&pc.draws[d].material);
-    int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3]; uint32_t slots[3];
+    int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3]; uint32_t slots[3]; uint32_t vflags = 0u;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
@@ -127,10 +127,11 @@ __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const Sha
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         const float4* bc = reinterpret_cast<const float4*>(pc.vtxBC + slot);
         const float4 b = __ldg(bc), c = __ldg(bc + 1);
-        X[k] = (int32_t)a.x; Y[k] = (int32_t)a.y;
+        X[k] = (int32_t)a.x; Y[k] = (int32_t)a.y; vflags |= a.w;
         world[k] = {b.x, b.y, b.z}; invw[k] = b.w;
         nrm[k] = {c.x, c.y, c.z};
     }
+    const bool clippedParent = (vflags & VF_NEEDS_CLIP) != 0u;   // Appendix B.3: won by a clipped child, weights in homogeneous form
     const long long A2 = mulw(X[1] - X[0], Y[2] - Y[0]) - mulw(X[2] - X[0], Y[1] - Y[0]);
     const int32_t Px = 256 * x + 128, Py = 256 * y + 128;
     const float inv = 1.0f / (float)(-A2);
@@ -141,6 +142,10 @@ __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const Sha
             const int a = (k + 1) % 3, b = (k + 2) % 3;
             const long long F = mulw(Y[b] - Y[a], Qx - X[a]) + mulw(-(X[b] - X[a]), Qy - Y[a]);
             q[k] = ((float)F * inv) * invw[k];
+        }
+        if (clippedParent) {
+            const float4 l = homogeneous_weights(pc, world[0], world[1], world[2], (float)((Qx - 128) >> 8), (float)((Qy - 128) >> 8));
+            q[0] = l.x; q[1] = l.y; q[2] = l.z;
         }
         rden = 1.0f / ((q[0] + q[1]) + q[2]);
     };

@@ -331,3 +331,55 @@ def test_pbr_rejects_phong_records():
     ctx.set_shading_model(1)   # 48-B Phong materials are too short for the PBR path
     with pytest.raises(RuntimeError):
         ctx.render_forward(s["draws"])
+
+
+# ---- Appendix B.3: triangles crossing the eye plane / guard band are clipped (K1 rare path + homogeneous varyings) ------------
+INSIDE_VIEWS = [((0.3, 0.2, 0.4), (3.0, -0.2, 2.0)), ((0.0, -0.5, 0.0), (1.0, -0.6, 0.2)), ((1.2, 0.1, 1.3), (-2.0, 0.0, -1.5)),
+                ((0.4, -0.9, -0.3), (-2.0, -1.0, 1.5))]
+
+
+@pytest.mark.parametrize("pbr", [False, True])
+def test_parity_camera_inside_scene_clipping(pbr):
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    if pbr:
+        s = sc.to_pbr(s, n_texture_sets=2)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ground = s["n_triangles"] - 2
+    for eye, look in INSIDE_VIEWS:
+        v = sc.view_from(s, eye, look)
+        o.set_view(v); ctx.set_view(v)
+        ref = o.render_forward(ref_shadow)
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+        gpu = dict(shadow=ctx.readback(capi.REB_SHADOW_F32), tri_id=ctx.readback(capi.REB_TRIID_U32), depth=ctx.readback(capi.REB_DEPTH_F32),
+                   color_f32=ctx.readback(capi.REB_COLOR_F32), color_srgb8=ctx.readback(capi.REB_COLOR_SRGB8))
+        assert ctx.counters()[0] == 0 and o.counters[0] == 0          # nothing dropped
+        if pbr:   # normal-mapped materials: see test_parity_pbr_textured_normal_mapped
+            assert np.array_equal(gpu["tri_id"], ref["tri_id"]) and np.array_equal(gpu["depth"].view(np.uint32), ref["depth"].view(np.uint32))
+            d8 = np.abs(gpu["color_srgb8"].astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max(axis=2)
+            assert (d8 > 1).mean() <= 1e-4 and _psnr(gpu["color_f32"], ref["color_f32"]) >= 50.0
+        else:
+            check_parity(s, gpu, ref_shadow, ref)
+    assert (ref["tri_id"] >= ground).mean() > 0.05                      # the clipped ground plane is on screen
+
+
+def test_parity_shadow_pass_guard_band_clipping():
+    """A light frustum zoomed 4000x into the scene pushes the ground plane and many sphere triangles far outside the
+    2^20-px guard band of the shadow pass: they are clipped (K1<shadow> rare path), not dropped."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.make_scene("small")
+    p = np.array(s["shadow_proj"], np.float32).copy()
+    p[[0, 4, 8, 12]] *= 4000.0; p[[1, 5, 9, 13]] *= 4000.0   # rows x and y of the column-major matrix
+    s["shadow_proj"] = p
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    assert gpu["counters"][0] == 0 and o.counters[0] == 0
+    check_parity(s, gpu, ref_shadow, ref)
+    assert (ref_shadow < 1.0).mean() > 0.5
