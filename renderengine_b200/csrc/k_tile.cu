@@ -275,7 +275,7 @@ __device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, u
 }
 
 // One 8 x 4 block: re-arm vis, merge large triangles, shade, write.  All arguments but key are warp-uniform.
-template <bool TEXTURED, bool PBR>
+template <bool TEXTURED, bool PBR, bool AFFINE>
 __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& sh, unsigned long long key0, int bx0, int by0, int lx, int ly, uint32_t nHuge,
                                          const HugeStage& hs, uint32_t begin, uint32_t end, WarpStage& ws, unsigned lane) {
     if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
@@ -293,7 +293,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     if (key[0] != VIS_CLEAR) {
         depth = __uint_as_float((uint32_t)(key[0] >> 32));
         tri = ~(uint32_t)key[0];
-        if (sh.outSRGB8 || sh.outF32) col = PBR ? shade_pixel_pbr<TEXTURED>(pc, sh, x, y, tri) : shade_pixel<TEXTURED>(pc, sh, x, y, tri);
+        if (sh.outSRGB8 || sh.outF32) col = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri);
     }
     if (sh.outDepth) sh.outDepth[p] = depth;
     if (sh.outTriId) sh.outTriId[p] = tri;
@@ -307,7 +307,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
 #ifndef KT_PBR_MIN_BLOCKS
 #define KT_PBR_MIN_BLOCKS 3
 #endif
-template <bool TEXTURED, bool PBR>
+template <bool TEXTURED, bool PBR, bool AFFINE>
 __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
     if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
     uint32_t begin, end;
     kt_tile_list(pc, tile, nLarge, begin, end);
-    kt_block<TEXTURED, PBR>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
+    kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
                        stage[warp], lane);
 #elif KT_MODE == 1
     // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
         if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) continue;
         uint32_t begin, end;
         kt_tile_list(pc, tile, nLarge, begin, end);
-        kt_block<TEXTURED, PBR>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
+        kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
                            end, stage[warp], lane);
     }
 #endif
@@ -361,9 +361,12 @@ void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, 
     // the textured variants carry the uv derivatives + sampler state; untextured scenes keep the leaner kernels
     const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
     using Kern = void (*)(PassConst, ShadeConst);
-    static const Kern kern[4] = {k_tile_forward<false, false>, k_tile_forward<true, false>, k_tile_forward<false, true>, k_tile_forward<true, true>};
-    const int v = (tex ? 1 : 0) | (pbr ? 2 : 0);
-    static int perSM[4] = {0, 0, 0, 0};
+    // shadow transform with last row exactly (0, 0, 0, 1) (every orthographic light): w == 1.0f exactly, shadow.glsl's three divisions are identities
+    const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
+    static const Kern kern[8] = {k_tile_forward<false, false, false>, k_tile_forward<true, false, false>, k_tile_forward<false, true, false>, k_tile_forward<true, true, false>,
+                                 k_tile_forward<false, false, true>,  k_tile_forward<true, false, true>,  k_tile_forward<false, true, true>,  k_tile_forward<true, true, true>};
+    const int v = (tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0);
+    static int perSM[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (!perSM[v]) {
         int n = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], KT_THREADS, 0);

@@ -96,15 +96,18 @@ __device__ __forceinline__ float shadow_fetch(const float* __restrict__ map, uin
     return __ldg(map + (size_t)j * S + i);
 }
 
+// AFFINE: the host found STR's last row to be exactly (0, 0, 0, 1) — every directional light's orthographic transform — so
+// fragPosLightSpace.w is exactly 1.0f for any finite point and the three divisions of shadow.glsl:31 are exact identities.
+template <bool AFFINE>
 __device__ __forceinline__ float compute_shadow(const LightDev& light, V3 fragPos, V3 normal, const float* __restrict__ STR,
                                                 const float* __restrict__ map, uint32_t S) {
     if (light.type != LIGHT_TYPE_DIRECTIONAL) return 0.0f;
     const float4 flp = mat4_mul_point(STR, fragPos.x, fragPos.y, fragPos.z);
     const V3 lightDir = normalize3(sub3(light.position, fragPos));
-    const float currentDepth = flp.z / flp.w;
+    const float currentDepth = AFFINE ? flp.z : flp.z / flp.w;
     if (currentDepth > 1.0f) return 0.0f;
-    const float mu = 0.5f * (flp.x / flp.w) + 0.5f;
-    const float mv = 0.5f * (flp.y / flp.w) + 0.5f;
+    const float mu = 0.5f * (AFFINE ? flp.x : flp.x / flp.w) + 0.5f;
+    const float mv = 0.5f * (AFFINE ? flp.y : flp.y / flp.w) + 0.5f;
     const float bias = glm_max(0.05f * (1.0f - dot3(normal, lightDir)), 0.005f);
     const float texel = 1.0f / (float)S;
     const float ref = currentDepth - bias;
@@ -194,7 +197,7 @@ __device__ __noinline__ float4 homogeneous_weights(const PassConst& pc, V3 w0, V
 // Shade the sample at pixel (x, y) won by primitive `tri`: re-derive the barycentrics from the cached snapped
 // vertices (exactly the integers triangle setup used), interpolate perspective-correct (Appendix B.10), then the
 // builder-defined Phong main() (Appendix B.11) over phong.glsl + shadow.glsl.
-template <bool TEXTURED>
+template <bool TEXTURED, bool AFFINE>
 __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
     const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
     const uint32_t materialRaw = __ldg(&pc.draws[d].material);
@@ -281,7 +284,7 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
         const LightDev L = l < (uint32_t)SHADE_CONST_LIGHTS ? const_light(sh, l) : load_light(sh.lights + (size_t)l * sh.lightStride);
         float shadow = 0.0f;
         if (sh.shadowMap != nullptr && L.type == LIGHT_TYPE_DIRECTIONAL && L.shadowIndex == 0u)
-            shadow = compute_shadow(L, fragPos, normal, sh.STR, sh.shadowMap, sh.shadowSize);
+            shadow = compute_shadow<AFFINE>(L, fragPos, normal, sh.STR, sh.shadowMap, sh.shadowSize);
         const float4 cl = phong_lighting(L, pDiffuse, pSpecular, shininess, normal, fragPos, viewPos, shadow);
         acc = make_float4(acc.x + cl.x, acc.y + cl.y, acc.z + cl.z, acc.w + cl.w);
     }

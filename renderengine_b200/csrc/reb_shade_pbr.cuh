@@ -35,6 +35,7 @@ __device__ __forceinline__ V3 scale3(V3 v, float s) { return {v.x * s, v.y * s, 
 struct PbrRemapped { V3 normal; float4 baseColor; V3 diffuseColor; float4 emissive; V3 f0; float metallic, roughness, occlusion; };
 
 // BRDF_Lighting after the texture fetches (pbr.glsl:368-451)
+template <bool AFFINE>
 __device__ __forceinline__ float4 pbr_lighting(const ShadeConst& sh, const PbrRemapped& m, V3 fragPos, V3 viewPos) {
     const float PI = 3.14159265359f;
     const V3 n = m.normal;
@@ -84,7 +85,7 @@ __device__ __forceinline__ float4 pbr_lighting(const ShadeConst& sh, const PbrRe
         float shadow = 0.0f;
         if (light.type == LIGHT_TYPE_DIRECTIONAL && sh.shadowMap != nullptr && light.shadowIndex == 0u) {
             LightDev sl; sl.type = light.type; sl.position = light.position;   // ComputeShadow reads only these (shadow.glsl:24-56)
-            shadow = compute_shadow(sl, fragPos, n, sh.STR, sh.shadowMap, sh.shadowSize);
+            shadow = compute_shadow<AFFINE>(sl, fragPos, n, sh.STR, sh.shadowMap, sh.shadowSize);
         }
         const float k = 1.0f - shadow;
         l0 = {l0.x + k * lightResult.x, l0.y + k * lightResult.y, l0.z + k * lightResult.z};
@@ -115,7 +116,7 @@ __device__ __forceinline__ float4 pbr_lighting(const ShadeConst& sh, const PbrRe
 
 // Shade the sample at pixel (x, y) won by primitive `tri` with the PBR model (same attribute reconstruction as
 // shade_pixel: Appendix B.10 from the cached snapped vertices).
-template <bool TEXTURED>
+template <bool TEXTURED, bool AFFINE>
 __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
     const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
     const uint32_t materialRaw = __ldg(&pc.draws[d].material);
@@ -217,7 +218,7 @@ __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const Sha
     const float f0s = mScal.x * (1.0f - m.metallic);
     m.f0 = {f0s + m.baseColor.x * m.metallic, f0s + m.baseColor.y * m.metallic, f0s + m.baseColor.z * m.metallic};
     const V3 viewPos = {sh.viewPos[0], sh.viewPos[1], sh.viewPos[2]};
-    return pbr_lighting(sh, m, fragPos, viewPos);
+    return pbr_lighting<AFFINE>(sh, m, fragPos, viewPos);
 }
 
 }  // namespace reb

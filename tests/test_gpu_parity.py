@@ -383,3 +383,21 @@ def test_parity_shadow_pass_guard_band_clipping():
     assert gpu["counters"][0] == 0 and o.counters[0] == 0
     check_parity(s, gpu, ref_shadow, ref)
     assert (ref_shadow < 1.0).mean() > 0.5
+
+
+def test_parity_perspective_shadow_transform():
+    """A shadow transform whose w is not 1 (perspective light frustum placed inside the scene): the forward pass takes the
+    general divide-by-w path of shadow.glsl:31 (the orthographic fast path is a separate kernel variant), and the shadow
+    pass clips geometry behind the light's eye plane."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.make_scene("small")
+    s["shadow_view"] = sc.to_flat(sc.camera_view(np.array([0.5, 6.0, 0.8], np.float32), np.array([0.0, -1.0, 0.0], np.float32), np.array([0, 0, 1], np.float32)))
+    s["shadow_proj"] = sc.to_flat(sc.perspective_clip(100.0, np.float32(1.0), 0.5, 40.0))
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    assert gpu["counters"][0] == 0 and o.counters[0] == 0
+    check_parity(s, gpu, ref_shadow, ref)
+    assert 0.2 < (ref_shadow < 1.0).mean()
