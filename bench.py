@@ -95,8 +95,9 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_frames(scene, n_frames, warm=1):
-    """Times the CPU oracle (the port of the reference path) on all host cores: full frames of the same workload."""
+def cpu_reference_frames(scene, n_frames, warm=1, keep=None):
+    """Times the CPU oracle (the port of the reference path) on all host cores: full frames of the same workload.
+    `keep` (a dict) receives the last frame's buffers so the caller can compare them with the device's."""
     from oracle import orc
     o = orc.Oracle(scene)
     cores = os.cpu_count() or 1
@@ -104,9 +105,11 @@ def cpu_reference_frames(scene, n_frames, warm=1):
     for i in range(warm + n_frames):
         t0 = time.perf_counter()
         sm = o.render_shadow() if scene["shadow_size"] else None
-        o.render_forward(sm)
+        out = o.render_forward(sm)
         if i >= warm:
             times.append(time.perf_counter() - t0)
+    if keep is not None:
+        keep.update(out); keep["shadow"] = sm
     return times, cores
 
 
@@ -234,13 +237,25 @@ def main():
         barrier()
         clocks = sampler.stop() if rank == 0 else None
         launches = ctx.launch_count() - l0
-        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+        per_frame = np.array([a.elapsed_time(b) for a, b in ev])
+        total_ms = float(per_frame.sum())
         tt = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms = float(tt.item()) / args.steps
         frames_per_step = 1 if tiles else world
         value = frames_per_step * T / (ms * 1e3)
+
+        # ---- forward-only frames with the cached shadow map: what the reference does after its first frame
+        # (RenderScene.cpp:171-175 renders the shadow map once); SURVEY 8d asks for both figures ------------------------
+        fwd_only = None
+        if world == 1:
+            evf = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(min(args.steps, 50))]
+            for a, b in evf:
+                flush.add_(1)
+                a.record(st); ctx.render_forward(draws); b.record(st)
+            ctx.sync()
+            fwd_only = np.array([a.elapsed_time(b) for a, b in evf])
 
         # ---- per-kernel timing + roofline of the dominant kernel (separate, instrumented frames) ----------
         ctx.set_profiling(True)
@@ -322,13 +337,28 @@ def main():
             "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 160 + 128 + 2 * 16 * len(draws),
                     "d2h_bytes_per_step": W * H * 4, "note": "wall clock through reb_set_view/reb_render_*/reb_readback_async + final reb_sync with host buffers (pinned, 2-image swapchain: the copy of frame i overlaps frame i+1); geometry is static and resident as in the reference frame loop"},
             "gpu_launches": int(launches), "clocks": clocks,
+            "frame_us": {"median": 1e3 * float(np.median(per_frame)), "p95": 1e3 * float(np.percentile(per_frame, 95)), "rank": 0},
             "counters": {"needs_clip": int(counters[0]), "binned_triangles": int(counters[1]), "tile_list_entries": int(counters[2]), "regrows": int(counters[3])},
         }
+        if fwd_only is not None:
+            fms = float(np.median(fwd_only))
+            line["forward_only"] = {"ms_per_frame": fms, "value": T / (fms * 1e3), "unit": UNIT, "algorithmic_bytes": b_forward,
+                                    "achieved_gbs": b_forward / (fms * 1e-3) / 1e9, "frac_of_peak": b_forward / (fms * 1e-3) / 1e9 / peak,
+                                    "note": "forward pass alone against the cached shadow map (the reference renders the shadow map once, RenderScene.cpp:171-175)"}
         if world == 1 and not args.no_cpu_baseline:
-            times, cores = cpu_reference_frames(scene, 5, warm=1)
+            keep = {}
+            times, cores = cpu_reference_frames(scene, 5, warm=1, keep=keep)
             cms = 1e3 * float(np.mean(times))
+            # the same frame on the device, compared bit for bit where the contract is bit-exact ("must hash-equal")
+            ctx.set_view(np.array(scene["view"]))
+            step(); ctx.sync()
+            same = bool(np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), keep["depth"].view(np.uint32))
+                        and np.array_equal(ctx.readback(capi.REB_TRIID_U32), keep["tri_id"])
+                        and (not S or np.array_equal(ctx.readback(capi.REB_SHADOW_F32).view(np.uint32), np.asarray(keep["shadow"], np.float32).view(np.uint32))))
+            d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int16) - keep["color_srgb8"].astype(np.int16))
             line["cpu_baseline"] = {"value": T / (cms * 1e3), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_frame": cms,
-                                    "sample": "5 full frames (shadow + forward) of the same workload on the CPU oracle, all host cores"}
+                                    "sample": "5 full frames (shadow + forward) of the same workload on the CPU oracle, all host cores",
+                                    "gpu_matches_bit_exact": {"depth_triid_shadow": same, "srgb8_max_lsb": int(d8.max())}}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -99,6 +99,15 @@ int reb_set_view(reb_ctx* ctx, const void* viewProperties160);
 #define REB_SHADING_PBR   1u
 int reb_set_shading_model(reb_ctx* ctx, uint32_t model);
 
+/* Skybox::Skybox / Skybox::Render — Skybox.cpp:58-92,126-140; TextureCache::LoadCubeMapFaces — TextureCache.cpp:199-290;
+ * skybox.vert:32-37, skybox.frag:28-31.  Installs the cube map the forward pass shows wherever the depth buffer still
+ * holds 1.0 (the reference draws its cube last at depth 1.0 under LessOrEqual, RenderScene.cpp:226-229).
+ * facesRGBA16: six width x height R16G16B16A16_UNORM images, contiguous, in Vulkan layer order +X -X +Y -Y +Z -Z (the
+ * reference's right, left, top, bottom, front, back, Skybox.cpp:71-78); one mip, linear filter, seamless edges; the
+ * texel values are written to the colour target as they are (no sRGB decode, skybox.frag:30).  The buffer is consumed
+ * before the call returns.  NULL removes the skybox (background = clear colour (0,0,0,1)). */
+int reb_set_skybox(reb_ctx* ctx, const void* facesRGBA16, uint32_t width, uint32_t height);
+
 /* ShadowSystem::Render(drawCommands) — ShadowSystem.cpp:319-376 */
 int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, uint32_t n);
 /* RenderScene::RenderBasePass -> MaterialSystem::Draw — RenderScene.cpp:210-242, MaterialSystem.cpp:88-101 */

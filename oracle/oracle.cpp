@@ -702,8 +702,108 @@ void rasterize(const orc_scene* sc, const PassParams& pp, const Frontend& fe, fl
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Skybox (Appendix B.11).  The reference draws a unit cube last with
+// gl_Position = (proj * mat4(mat3(view)) * (p, 1)).xyww (skybox.vert:32-37): depth exactly 1.0, test LessOrEqual
+// (RenderScene.cpp:226-229), so it shows wherever the depth buffer still holds 1.0; the fragment colour is
+// texture(cube, p) (skybox.frag:28-31) and a cube lookup depends only on the direction of p.  The direction of the
+// view ray through a pixel centre is p ~ A^-1 (xn, yn, 1) with A = rows x, y, w of proj * mat4(mat3(view))
+// restricted to its 3x3 part (exact when the projection has no translation in x, y, w — every perspective matrix).
+// A^-1 is formed in double (adjugate / determinant) and rounded to float once per frame.
+// ---------------------------------------------------------------------------------------------
+struct SkyParams { float Ainv[9]; float hw, hh, rhw, rhh; const uint16_t* faces; uint32_t w, h; };
+
+inline void sky_setup(const float* view, const float* proj, uint32_t W, uint32_t H, SkyParams& sp) {
+    // M = proj * mat4(mat3(view)), column-major; A = rows {0, 1, 3} x columns {0, 1, 2}
+    double A[3][3];
+    const int rows[3] = {0, 1, 3};
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+            double acc = 0.0;
+            for (int k = 0; k < 3; ++k) acc += (double)proj[4 * k + rows[r]] * (double)view[4 * c + k];
+            A[r][c] = acc;
+        }
+    const double c00 = A[1][1] * A[2][2] - A[1][2] * A[2][1], c01 = A[1][2] * A[2][0] - A[1][0] * A[2][2], c02 = A[1][0] * A[2][1] - A[1][1] * A[2][0];
+    const double det = A[0][0] * c00 + A[0][1] * c01 + A[0][2] * c02;
+    const double adj[3][3] = {
+        {c00, A[0][2] * A[2][1] - A[0][1] * A[2][2], A[0][1] * A[1][2] - A[0][2] * A[1][1]},
+        {c01, A[0][0] * A[2][2] - A[0][2] * A[2][0], A[0][2] * A[1][0] - A[0][0] * A[1][2]},
+        {c02, A[0][1] * A[2][0] - A[0][0] * A[2][1], A[0][0] * A[1][1] - A[0][1] * A[1][0]}};
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) sp.Ainv[3 * c + r] = (float)(adj[r][c] / det);   // column-major 3x3
+    sp.hw = 0.5f * (float)W; sp.hh = 0.5f * (float)H;
+    sp.rhw = 1.0f / sp.hw; sp.rhh = 1.0f / sp.hh;
+}
+
+// Vulkan cube face selection (spec "Cube Map Face Selection"; ties: z over y over x): face, sc, tc, |ma|
+inline int cube_face(float rx, float ry, float rz, float& sc, float& tc, float& ma) {
+    const float ax = glm_abs(rx), ay = glm_abs(ry), az = glm_abs(rz);
+    if (az >= ax && az >= ay) { ma = az; if (rz >= 0.0f) { sc = rx; tc = -ry; return 4; } sc = -rx; tc = -ry; return 5; }
+    if (ay >= ax) { ma = ay; if (ry >= 0.0f) { sc = rx; tc = rz; return 2; } sc = rx; tc = -rz; return 3; }
+    ma = ax;
+    if (rx >= 0.0f) { sc = -rz; tc = -ry; return 0; }
+    sc = rz; tc = -ry; return 1;
+}
+inline V4 cube_fetch(const uint16_t* faces, uint32_t w, uint32_t h, int f, int i, int j) {
+    const uint16_t* t = faces + (((size_t)f * h + (size_t)j) * w + (size_t)i) * 4;
+    const float k = 1.0f / 65535.0f;
+    return {(float)t[0] * k, (float)t[1] * k, (float)t[2] * k, (float)t[3] * k};
+}
+// texel (i, j) of face f; coordinates outside the face are carried over the edge (seamless filtering): the texel
+// centre is lifted to its 3-D position on the extended face plane, the face re-selected, the nearest texel taken
+inline V4 cube_texel(const uint16_t* faces, uint32_t w, uint32_t h, int f, int i, int j) {
+    if (i >= 0 && j >= 0 && i < (int)w && j < (int)h) return cube_fetch(faces, w, h, f, i, j);
+    const float sc = (2.0f * ((float)i + 0.5f)) / (float)w - 1.0f, tc = (2.0f * ((float)j + 0.5f)) / (float)h - 1.0f;
+    float rx, ry, rz;
+    switch (f) {
+        case 0: rx = 1.0f; ry = -tc; rz = -sc; break;
+        case 1: rx = -1.0f; ry = -tc; rz = sc; break;
+        case 2: rx = sc; ry = 1.0f; rz = tc; break;
+        case 3: rx = sc; ry = -1.0f; rz = -tc; break;
+        case 4: rx = sc; ry = -tc; rz = 1.0f; break;
+        default: rx = -sc; ry = -tc; rz = -1.0f; break;
+    }
+    float s2, t2, ma;
+    const int f2 = cube_face(rx, ry, rz, s2, t2, ma);
+    const float s = 0.5f * (s2 / ma) + 0.5f, t = 0.5f * (t2 / ma) + 0.5f;
+    int i2 = (int)std::floor(s * (float)w), j2 = (int)std::floor(t * (float)h);
+    i2 = i2 < 0 ? 0 : (i2 > (int)w - 1 ? (int)w - 1 : i2);
+    j2 = j2 < 0 ? 0 : (j2 > (int)h - 1 ? (int)h - 1 : j2);
+    return cube_fetch(faces, w, h, f2, i2, j2);
+}
+inline V4 sky_lookup(const uint16_t* faces, uint32_t w, uint32_t h, float rx, float ry, float rz) {
+    float sc, tc, ma;
+    const int f = cube_face(rx, ry, rz, sc, tc, ma);
+    const float s = 0.5f * (sc / ma) + 0.5f, t = 0.5f * (tc / ma) + 0.5f;
+    const float u = s * (float)w - 0.5f, v = t * (float)h - 0.5f;
+    const float fu0 = std::floor(u), fv0 = std::floor(v);
+    const int i0 = (int)fu0, j0 = (int)fv0;
+    const float fu = u - fu0, fv = v - fv0;
+    const V4 t00 = cube_texel(faces, w, h, f, i0, j0), t10 = cube_texel(faces, w, h, f, i0 + 1, j0);
+    const V4 t01 = cube_texel(faces, w, h, f, i0, j0 + 1), t11 = cube_texel(faces, w, h, f, i0 + 1, j0 + 1);
+    const float gu = 1.0f - fu, gv = 1.0f - fv;
+    auto mix = [&](float a, float b, float c, float d) { return (a * gu + b * fu) * gv + (c * gu + d * fu) * fv; };
+    return {mix(t00.x, t10.x, t01.x, t11.x), mix(t00.y, t10.y, t01.y, t11.y), mix(t00.z, t10.z, t01.z, t11.z), mix(t00.w, t10.w, t01.w, t11.w)};
+}
+inline V4 sky_pixel(const SkyParams& sp, int x, int y) {
+    const float xn = (((float)x + 0.5f) - sp.hw) * sp.rhw, yn = (((float)y + 0.5f) - sp.hh) * sp.rhh;
+    const float* a = sp.Ainv;
+    const float rx = (a[0] * xn + a[3] * yn) + a[6], ry = (a[1] * xn + a[4] * yn) + a[7], rz = (a[2] * xn + a[5] * yn) + a[8];
+    return sky_lookup(sp.faces, sp.w, sp.h, rx, ry, rz);
+}
+
 extern "C" {
 
+void orc_sky_pixel(const uint8_t* view160, uint32_t W, uint32_t H, const uint16_t* faces, uint32_t w, uint32_t h, uint32_t x, uint32_t y, float* out4) {
+    const float* view = reinterpret_cast<const float*>(view160);
+    SkyParams sp; sky_setup(view, view + 16, W, H, sp); sp.faces = faces; sp.w = w; sp.h = h;
+    const V4 c = sky_pixel(sp, (int)x, (int)y);
+    out4[0] = c.x; out4[1] = c.y; out4[2] = c.z; out4[3] = c.w;
+}
+void orc_sky_lookup(const uint16_t* faces, uint32_t w, uint32_t h, const float* d, float* out4) {
+    const V4 c = sky_lookup(faces, w, h, d[0], d[1], d[2]);
+    out4[0] = c.x; out4[1] = c.y; out4[2] = c.z; out4[3] = c.w;
+}
 void orc_mat4_mul(const float* a, const float* b, float* out) { mat4_mul_mat4(a, b, out); }
 void orc_mat4_mul_vec4(const float* m, const float* v, float* out) {
     V4 r = mat4_mul(m, {v[0], v[1], v[2], v[3]});
@@ -780,6 +880,10 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
     std::vector<Texture> textures;
     for (uint32_t t = 0; t < sc->nTextures; ++t) textures.push_back(build_texture(sc->textures[t]));
 
+    const bool haveSky = sc->skyFaces != nullptr && sc->skyW && sc->skyH;
+    SkyParams sky{};
+    if (haveSky) { sky_setup(view, proj, sc->width, sc->height, sky); sky.faces = sc->skyFaces; sky.w = sc->skyW; sky.h = sc->skyH; }
+
     unsigned nT = thread_count(sc);
     const int W = (int)sc->width, H = (int)sc->height;
     parallel_for(nT, [&](unsigned t) {
@@ -789,6 +893,10 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
                 size_t p = (size_t)y * W + x;
                 V4 out = {0.0f, 0.0f, 0.0f, 1.0f};   // clear colour (RenderScene.cpp:217-220)
                 uint32_t tri = triId[p];
+                if (haveSky && depth[p] == 1.0f) {   // drawn last at depth 1.0, LessOrEqual (Appendix B.11)
+                    out = sky_pixel(sky, x, y);
+                    tri = TRI_NONE;
+                }
                 if (tri != TRI_NONE) {
                     uint32_t d = (uint32_t)(std::upper_bound(fe.triPrefix.begin(), fe.triPrefix.end(), (uint64_t)tri) - fe.triPrefix.begin()) - 1;
                     const DrawRec& dr = draws[d];

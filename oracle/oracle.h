@@ -53,6 +53,10 @@ typedef struct orc_scene {
        nRanks <= 1 disables. */
     uint32_t        rank, nRanks, bandH;
     uint32_t        shadingModel; /* 0 = Phong (48-B materials, 112-B lights), 1 = PBR (80-B MaterialProperties, 80-B Light: pbr.glsl) */
+    /* skybox (Skybox.cpp:58-92, skybox.vert:32-37, skybox.frag:28-31): cube map of 6 RGBA16 UNORM faces, one mip
+       (TextureCache.cpp:251-266), layers +X -X +Y -Y +Z -Z, each skyW x skyH row-major.  NULL = no skybox. */
+    const uint16_t* skyFaces;
+    uint32_t        skyW, skyH;
 } orc_scene;
 
 /* counters[0] = triangles dropped because they need true clipping (w<=0 or guard band),
@@ -71,6 +75,9 @@ void orc_phong_lighting(const uint8_t* light112, const float* props9 /* diffuse4
 float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal,
                          const float* transform16, const float* shadowMap, uint32_t S);
 void orc_srgb8(const float* rgba, uint8_t* out4);
+/* Appendix B.11: skybox colour of pixel (x, y) for the 160-B view block; and the cube lookup on its own */
+void orc_sky_pixel(const uint8_t* view160, uint32_t W, uint32_t H, const uint16_t* faces, uint32_t w, uint32_t h, uint32_t x, uint32_t y, float* out4);
+void orc_sky_lookup(const uint16_t* faces, uint32_t w, uint32_t h, const float* dir3, float* out4);
 void orc_pbr_lighting(const uint8_t* material80, const uint8_t* lights80, uint32_t nLights, const float* fragPos, const float* normal, const float* viewPos,
                       float exposure, uint32_t debugInput, uint32_t debugEquation, const float* transform16, const float* shadowMap, uint32_t S, float* out4);
 

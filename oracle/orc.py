@@ -37,6 +37,7 @@ class OrcScene(C.Structure):
         ("shadowView", fp), ("shadowProj", fp),
         ("textures", C.POINTER(OrcTexture)), ("nTextures", C.c_uint32), ("nThreads", C.c_uint32),
         ("rank", C.c_uint32), ("nRanks", C.c_uint32), ("bandH", C.c_uint32), ("shadingModel", C.c_uint32),
+        ("skyFaces", u16p), ("skyW", C.c_uint32), ("skyH", C.c_uint32),
     ]
 
 
@@ -59,7 +60,22 @@ def lib():
         _LIB.orc_phong_lighting.argtypes = [u8p, fp, fp, fp, fp, C.c_float, fp]
         _LIB.orc_compute_shadow.argtypes = [u8p, fp, fp, fp, fp, C.c_uint32]
         _LIB.orc_compute_shadow.restype = C.c_float
+        _LIB.orc_sky_pixel.argtypes = [u8p, C.c_uint32, C.c_uint32, u16p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, fp]
+        _LIB.orc_sky_lookup.argtypes = [u16p, C.c_uint32, C.c_uint32, fp, fp]
     return _LIB
+
+
+def sky_lookup(faces, direction):
+    """Appendix B.11 cube lookup (seamless bilinear) of one direction; faces = (6, h, w, 4) uint16."""
+    f = np.ascontiguousarray(faces, np.uint16); d = np.ascontiguousarray(direction, np.float32); out = np.empty(4, np.float32)
+    lib().orc_sky_lookup(_p(f, u16p), f.shape[2], f.shape[1], _p(d, fp), _p(out, fp))
+    return out
+
+
+def sky_pixel(view160, W, H, faces, x, y):
+    f = np.ascontiguousarray(faces, np.uint16); v = np.ascontiguousarray(view160, np.uint8); out = np.empty(4, np.float32)
+    lib().orc_sky_pixel(_p(v, u8p), W, H, _p(f, u16p), f.shape[2], f.shape[1], x, y, _p(out, fp))
+    return out
 
 
 def _p(a, t):
@@ -103,6 +119,10 @@ class Oracle:
         s.nThreads = n_threads
         s.rank, s.nRanks, s.bandH = rank, n_ranks, band_h
         s.shadingModel = int(scene.get("shading_model", 0))
+        sky = scene.get("skybox")
+        if sky is not None:
+            f = hold(sky, np.uint16)                  # (6, h, w, 4) RGBA16, layers +X -X +Y -Y +Z -Z
+            s.skyFaces = _p(f, u16p); s.skyH, s.skyW = f.shape[1], f.shape[2]
         self.s = s
         self.counters = np.zeros(4, np.uint64)
 

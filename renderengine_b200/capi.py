@@ -14,7 +14,7 @@ REB_COLOR_SRGB8, REB_COLOR_F32, REB_DEPTH_F32, REB_TRIID_U32, REB_SHADOW_F32 = 0
 SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
-    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
@@ -66,6 +66,7 @@ def load():
     lib.reb_sync.argtypes = [vp]
     lib.reb_flush.argtypes = [vp]
     lib.reb_set_shading_model.argtypes = [vp, u32]
+    lib.reb_set_skybox.argtypes = [vp, vp, u32, u32]
     lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
@@ -159,6 +160,8 @@ class Context:
 
     def upload_scene(self, scene):
         self.set_shading_model(scene.get("shading_model", 0))
+        if scene.get("skybox") is not None:
+            self.set_skybox(scene["skybox"])
         self.upload_geometry(scene["verts"], scene["indices"])
         self.upload_transforms(scene["transforms"])
         self.upload_materials(scene["materials"])
@@ -184,6 +187,16 @@ class Context:
 
     def set_shading_model(self, model):
         self._ck(self.lib.reb_set_shading_model(self.h, int(model)))
+
+    def set_skybox(self, faces):
+        """faces: (6, h, w, 4) uint16 cube map (+X -X +Y -Y +Z -Z), or None to remove it (Skybox.cpp:58-92)."""
+        if faces is None:
+            self._ck(self.lib.reb_set_skybox(self.h, None, 0, 0))
+            return
+        f = np.ascontiguousarray(faces, dtype=np.uint16)
+        if f.ndim != 4 or f.shape[0] != 6 or f.shape[3] != 4:
+            raise ValueError("skybox faces must have shape (6, h, w, 4)")
+        self._ck(self.lib.reb_set_skybox(self.h, _ptr(f), f.shape[2], f.shape[1]))
 
     def flush(self):
         """Submit the recorded shadow pass now (before consuming the shadow map on the stream, e.g. an NCCL broadcast)."""

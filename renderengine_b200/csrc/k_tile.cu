@@ -15,6 +15,7 @@
 // phong.glsl:39-81 + shadow.glsl:24-56; clears RenderScene.cpp:217-220 / ShadowSystem.cpp:111-127.
 #include "reb_shade.cuh"
 #include "reb_shade_pbr.cuh"
+#include "reb_sky.cuh"
 #include <algorithm>
 
 namespace reb {
@@ -290,11 +291,13 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     float depth = 1.0f;                    // depth clear 1.0 (RenderScene.cpp:219)
     uint32_t tri = TRI_NONE;
     float4 col = make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (0,0,0,1) (RenderScene.cpp:218)
-    if (key[0] != VIS_CLEAR) {
+    const bool hit = key[0] != VIS_CLEAR;
+    if (hit) {
         depth = __uint_as_float((uint32_t)(key[0] >> 32));
         tri = ~(uint32_t)key[0];
-        if (sh.outSRGB8 || sh.outF32) col = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri);
     }
+    if (sh.skyFaces && depth == 1.0f) col = sky_pixel(sh, x, y);   // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.11)
+    else if (hit && (sh.outSRGB8 || sh.outF32)) col = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri);
     if (sh.outDepth) sh.outDepth[p] = depth;
     if (sh.outTriId) sh.outTriId[p] = tri;
     if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(col);

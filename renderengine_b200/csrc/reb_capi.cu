@@ -51,6 +51,7 @@ struct reb_ctx {
     float view[16], proj[16], PV[16], viewPos[3]; bool haveView = false;
     float exposure = 1.0f; uint32_t debugInput = 0, debugEquation = 0;   // ViewProperties @140 / @144 / @148 (PBR path)
     uint32_t shadingModel = 0;                                           // REB_SHADING_PHONG / REB_SHADING_PBR
+    uint16_t* skyFaces = nullptr; uint32_t skyW = 0, skyH = 0;          // skybox cube map (reb_set_skybox), six RGBA16 faces
     // shadow (one directional shadow map, F10)
     uint32_t S = 0; float* shadowMap = nullptr; float sview[16], sproj[16], SPV[16]; bool haveShadowXf = false, shadowValid = false;
     // outputs + visibility buffer
@@ -343,6 +344,27 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
 
 // Enqueue the kernels of one pass: K0 vertex stage (unless the fused two-pass K0 already ran), K1 setup + small raster,
 // K2 bin scatter, K3 tile stage.  Every kernel after the first is PDL-chained.
+// Appendix B.11: inverse of A = rows x, y, w of proj * mat4(mat3(view)) restricted to 3x3 — maps (xn, yn, 1) to the
+// direction of the view ray (skybox.vert:32-37).  Adjugate / determinant in double, rounded to float once per frame.
+static void sky_ray_matrix(const float* view, const float* proj, float* out9) {
+    double A[3][3];
+    const int rows[3] = {0, 1, 3};
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+            double acc = 0.0;
+            for (int k = 0; k < 3; ++k) acc += (double)proj[4 * k + rows[r]] * (double)view[4 * c + k];
+            A[r][c] = acc;
+        }
+    const double c00 = A[1][1] * A[2][2] - A[1][2] * A[2][1], c01 = A[1][2] * A[2][0] - A[1][0] * A[2][2], c02 = A[1][0] * A[2][1] - A[1][1] * A[2][0];
+    const double det = A[0][0] * c00 + A[0][1] * c01 + A[0][2] * c02;
+    const double adj[3][3] = {
+        {c00, A[0][2] * A[2][1] - A[0][1] * A[2][2], A[0][1] * A[1][2] - A[0][2] * A[1][1]},
+        {c01, A[0][0] * A[2][2] - A[0][2] * A[2][0], A[0][2] * A[1][0] - A[0][0] * A[1][2]},
+        {c02, A[0][1] * A[2][0] - A[0][0] * A[2][1], A[0][0] * A[1][1] - A[0][1] * A[1][0]}};
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) out9[3 * c + r] = (float)(adj[r][c] / det);
+}
+
 int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     PassState& ps = ctx->pass[kind];
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
@@ -381,6 +403,12 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         sh.shadingModel = ctx->shadingModel; sh.exposure = ctx->exposure; sh.debugInput = ctx->debugInput; sh.debugEquation = ctx->debugEquation;
         sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
+        if (ctx->skyFaces) {
+            sh.skyFaces = ctx->skyFaces; sh.skyW = ctx->skyW; sh.skyH = ctx->skyH;
+            sky_ray_matrix(ctx->view, ctx->proj, sh.skyAinv);
+            sh.skyHw = 0.5f * (float)ctx->W; sh.skyHh = 0.5f * (float)ctx->H;
+            sh.skyRhw = 1.0f / sh.skyHw; sh.skyRhh = 1.0f / sh.skyHh;
+        }
         launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++;
     }
     mark(5);

@@ -61,6 +61,7 @@ int reb_destroy(reb_ctx* ctx) {
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
+    if (ctx->skyFaces) cudaFree(ctx->skyFaces);
     if (ctx->pass[1].vtxUV) cudaFree(ctx->pass[1].vtxUV);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
@@ -260,6 +261,27 @@ int reb_set_shading_model(reb_ctx* ctx, uint32_t model) {
     CHECK_CTX();
     if (model != REB_SHADING_PHONG && model != REB_SHADING_PBR) return fail(ctx, REB_E_INVALID, "reb_set_shading_model: unknown model");
     ctx->shadingModel = model;
+    return REB_OK;
+}
+
+int reb_set_skybox(reb_ctx* ctx, const void* facesRGBA16, uint32_t width, uint32_t height) {
+    CHECK_CTX();
+    CU(cudaSetDevice(ctx->device));
+    { int rc = flush_deferred(ctx); if (rc) return rc; }
+    if (!facesRGBA16) {                                   // remove the skybox: the background is the clear colour again
+        if (ctx->skyFaces) { CU(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->skyFaces); }
+        ctx->skyFaces = nullptr; ctx->skyW = ctx->skyH = 0;
+        return REB_OK;
+    }
+    if (width == 0 || height == 0 || width > 16384 || height > 16384) return fail(ctx, REB_E_INVALID, "reb_set_skybox: face extent must be in 1..16384");
+    const size_t bytes = (size_t)6 * width * height * 8;
+    uint16_t* dev = nullptr;
+    CU(cudaMalloc(reinterpret_cast<void**>(&dev), bytes));
+    cudaError_t e = cudaMemcpyAsync(dev, facesRGBA16, bytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // the host buffer is consumed before returning; earlier frames are done
+    if (e != cudaSuccess) { cudaFree(dev); return fail(ctx, REB_E_CUDA, std::string("reb_set_skybox: ") + cudaGetErrorString(e)); }
+    if (ctx->skyFaces) cudaFree(ctx->skyFaces);
+    ctx->skyFaces = dev; ctx->skyW = width; ctx->skyH = height;
     return REB_OK;
 }
 

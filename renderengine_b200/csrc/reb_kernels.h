@@ -20,6 +20,9 @@ struct ShadeConst {
     uint32_t maxDescriptors; uint32_t nTextures;
     const TexDev* textures;
     uint8_t* outSRGB8; float* outF32; float* outDepth; uint32_t* outTriId;
+    // skybox (reb_sky.cuh): six RGBA16 faces, A^-1 of the view-ray map (column-major 3x3), half extents and their reciprocals
+    const uint16_t* skyFaces; uint32_t skyW, skyH;
+    float skyAinv[9]; float skyHw, skyHh, skyRhw, skyRhh;
 };
 
 // <<<>>> with the programmatic-stream-serialization attribute (PDL) when `pdl` is set

@@ -78,6 +78,21 @@ void pbr::MaterialSystem::UploadToGPU(Renderer& renderer) {
     renderer.Check(reb_upload_materials(renderer.GetContext(), m_properties.data(), sizeof(MaterialProperties), (uint32_t)m_properties.size()),
                    "pbr::MaterialSystem::UploadToGPU");
 }
+void Skybox::SetCubeMapFaces(const uint16_t* facesRGBA16, uint32_t width, uint32_t height) {
+    if (!facesRGBA16 || !width || !height) throw std::invalid_argument("Skybox::SetCubeMapFaces: six non-empty faces are required");   // TextureCache.cpp:201-202
+    m_faces.assign(facesRGBA16, facesRGBA16 + (size_t)6 * width * height * 4);
+    m_width = width; m_height = height;
+}
+void Skybox::UploadToGPU() {
+    if (m_faces.empty()) return;   // no cube map staged: the base pass keeps the clear colour
+    m_renderer->Check(reb_set_skybox(m_renderer->GetContext(), m_faces.data(), m_width, m_height), "Skybox::UploadToGPU");
+    m_faces.clear(); m_faces.shrink_to_fit();
+    m_uploaded = true;
+}
+void Skybox::Remove() {
+    m_renderer->Check(reb_set_skybox(m_renderer->GetContext(), nullptr, 0, 0), "Skybox::Remove");
+    m_uploaded = false;
+}
 void Renderer::Submit() const { Check(reb_flush(m_ctx), "reb_flush"); }
 void Renderer::Readback(reb_output_kind kind, void* host) const { Check(reb_readback(m_ctx, kind, host), "reb_readback"); }
 std::vector<reb_draw> Renderer::ToDraws(const std::vector<MeshDrawInfo>& drawCalls) {
@@ -214,7 +229,7 @@ void ShadowSystem::Render(const std::vector<MeshDrawInfo>& drawCommands) const {
 RenderScene::RenderScene(Renderer& renderer, uint32_t shadowMapExtent)
     : m_renderer(&renderer), m_meshAllocator(new MeshAllocator()), m_sceneTree(new SceneTree()), m_lightSystem(new LightSystem()),
       m_shadowSystem(new ShadowSystem(shadowMapExtent, renderer, *this)),
-      m_cameraViewSystem(new CameraViewSystem(renderer.GetWidth(), renderer.GetHeight())), m_materialSystem(new MaterialSystem()) {}
+      m_cameraViewSystem(new CameraViewSystem(renderer.GetWidth(), renderer.GetHeight())), m_materialSystem(new MaterialSystem()), m_skybox(new Skybox(renderer)) {}
 
 void RenderScene::Init() {
     PopulateMeshDrawCalls();
@@ -227,6 +242,7 @@ void RenderScene::UploadToGPU() {   // same order as RenderScene.cpp:80-92
     m_lightSystem->UploadToGPU(*m_renderer);
     m_shadowSystem->UploadToGPU();
     m_materialSystem->UploadToGPU(*m_renderer);
+    m_skybox->UploadToGPU();
 }
 void RenderScene::PopulateMeshDrawCalls() {
     m_opaqueMeshes.clear(); m_translucentMeshes.clear();

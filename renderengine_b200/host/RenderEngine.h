@@ -16,6 +16,7 @@
 //   MaterialSystem       Renderer/MaterialSystem.h:72-154            reb::MaterialSystem (PhongProperties of phong.glsl:2-12)
 //   CameraViewSystem     Renderer/CameraViewSystem.h:17-40           reb::CameraViewSystem
 //   Camera               Renderer/Camera.h:8-130                     reb::Camera
+//   Skybox               Renderer/Skybox.h:17-55                     reb::Skybox        (cube-map background, reb_set_skybox)
 //   BoundingBox          BoundingBox.h:7-65                          reb::BoundingBox
 //
 // Vulkan-only arguments (CommandRingBuffer&, RenderCommandEncoder&, vk::Extent2D) are dropped or replaced by
@@ -232,6 +233,7 @@ public:
     LightID AddLight(Light light) { m_lights.push_back(light); return static_cast<LightID>(m_lights.size() - 1); }
     void SetLightShadowID(LightID id, uint32_t shadowID) { m_lights.at(id).shadowIndex = shadowID; }
     uint32_t GetLightCount() const { return static_cast<uint32_t>(m_lights.size()); }
+    const std::vector<Light>& GetLights() const { return m_lights; }
     void UploadToGPU(Renderer& renderer);
 private:
     std::vector<Light> m_lights;
@@ -242,6 +244,7 @@ public:
         m_properties.push_back(properties);
         return MaterialHandle(MaterialShadingDomain::Surface, MaterialShadingModel::Lit, (uint32_t)m_properties.size() - 1);
     }
+    const std::vector<MaterialProperties>& GetProperties() const { return m_properties; }   // (facade extension)
     void UploadToGPU(Renderer& renderer);
 private:
     std::vector<MaterialProperties> m_properties;
@@ -311,6 +314,23 @@ private:
     uint32_t m_width, m_height;
 };
 
+// ---- Skybox (Skybox.h:17-55, Skybox.cpp:58-140) --------------------------------------------------------------------------------------
+// The reference loads six face images through TextureCache::LoadCubeMapFaces (TextureCache.cpp:199-290, stb_image -> RGBA16);
+// image decoding is outside the hot path, so the faces arrive decoded: +X -X +Y -Y +Z -Z = right, left, top, bottom, front, back.
+class Skybox {
+public:
+    explicit Skybox(Renderer& renderer) : m_renderer(&renderer) {}
+    void SetCubeMapFaces(const uint16_t* facesRGBA16, uint32_t width, uint32_t height);   // staged until UploadToGPU
+    void UploadToGPU();                                                                   // Skybox.cpp:107-124 -> reb_set_skybox
+    void Remove();                                                                        // background = clear colour again
+    bool IsLoaded() const { return m_uploaded; }
+private:
+    Renderer* m_renderer;
+    std::vector<uint16_t> m_faces;
+    uint32_t m_width = 0, m_height = 0;
+    bool m_uploaded = false;
+};
+
 // ---- RenderScene (RenderScene.h:21-69, RenderScene.cpp:55-242) -------------------------------------------------------------------
 class RenderScene {
 public:
@@ -327,6 +347,7 @@ public:
     ShadowSystem* GetShadowSystem() const { return m_shadowSystem.get(); }
     CameraViewSystem* GetCameraViewSystem() const { return m_cameraViewSystem.get(); }
     MaterialSystem* GetMaterialSystem() const { return m_materialSystem.get(); }
+    Skybox* GetSkybox() const { return m_skybox.get(); }                                  // RenderScene.h:41
     const std::vector<MeshDrawInfo>& GetOpaqueMeshes() const { return m_opaqueMeshes; }
     const std::vector<MeshDrawInfo>& GetTranslucentMeshes() const { return m_translucentMeshes; }
 private:
@@ -342,6 +363,7 @@ private:
     std::unique_ptr<ShadowSystem> m_shadowSystem;
     std::unique_ptr<CameraViewSystem> m_cameraViewSystem;
     std::unique_ptr<MaterialSystem> m_materialSystem;
+    std::unique_ptr<Skybox> m_skybox;
     std::vector<MeshDrawInfo> m_opaqueMeshes, m_translucentMeshes;
     bool m_areShadowsDirty = true;
 };

@@ -52,11 +52,12 @@ template <class T> void put(FILE* f, const T* p, size_t n) { std::fwrite(p, size
 }  // namespace
 
 int main(int argc, char** argv) {
-    if (argc < 8) { std::fprintf(stderr, "usage: %s nx nz level width height shadowSize frames [dump.bin]\n", argv[0]); return 2; }
+    if (argc < 8) { std::fprintf(stderr, "usage: %s nx nz level width height shadowSize frames [dump.bin [skyFaceSize]]\n", argv[0]); return 2; }
     const int nx = std::atoi(argv[1]), nz = std::atoi(argv[2]), level = std::atoi(argv[3]);
     const uint32_t W = (uint32_t)std::atoi(argv[4]), H = (uint32_t)std::atoi(argv[5]), S = (uint32_t)std::atoi(argv[6]);
     const int frames = std::atoi(argv[7]);
     const char* dump = argc > 8 ? argv[8] : nullptr;
+    const uint32_t skyN = argc > 9 ? (uint32_t)std::atoi(argv[9]) : 0u;
     try {
         Renderer renderer(W, H);
         RenderScene scene(renderer, S ? S : 4096);
@@ -124,6 +125,17 @@ int main(int argc, char** argv) {
         cam.SetImageExtent((int)W, (int)H);
         cam.SetCameraView(normalize(vec3(1, 1, 1)) * dist, vec3(0, 0, 0), vec3(0, 1, 0));
 
+        // optional cube-map background (Skybox.cpp:58-92): a procedural gradient, one tone per face
+        std::vector<uint16_t> skyFaces((size_t)6 * skyN * skyN * 4);
+        for (uint32_t face = 0; face < 6 && skyN; ++face)
+            for (uint32_t j = 0; j < skyN; ++j)
+                for (uint32_t i = 0; i < skyN; ++i) {
+                    uint16_t* t = &skyFaces[(((size_t)face * skyN + j) * skyN + i) * 4];
+                    t[0] = (uint16_t)(65535u * i / std::max(skyN - 1u, 1u)); t[1] = (uint16_t)(65535u * j / std::max(skyN - 1u, 1u));
+                    t[2] = (uint16_t)(9000u * (face + 1u)); t[3] = 65535u;
+                }
+        if (skyN) scene.GetSkybox()->SetCubeMapFaces(skyFaces.data(), skyN, skyN);
+
         scene.Init();
         const auto t0 = std::chrono::steady_clock::now();
         for (int f = 0; f < frames; ++f) {
@@ -161,6 +173,7 @@ int main(int argc, char** argv) {
             renderer.Readback(REB_COLOR_SRGB8, col8.data()); renderer.Readback(REB_COLOR_F32, colf.data());
             put(f, shadow.data(), shadow.size()); put(f, depth.data(), depth.size()); put(f, tri.data(), tri.size());
             put(f, col8.data(), col8.size()); put(f, colf.data(), colf.size());
+            if (skyN) { put(f, &skyN, 1); put(f, skyFaces.data(), skyFaces.size()); }
             std::fclose(f);
         }
     } catch (const std::exception& e) {

@@ -409,6 +409,33 @@ def view_from(scene, eye, look, fov=45.0, near=0.01, far=100.0):
     return pack_view(view, proj, eye)
 
 
+def make_skybox(size=64, seed=1234):
+    """Procedural cube map in the reference's layout (TextureCache.cpp:199-290: six RGBA16 UNORM faces, one mip, layers
+    +X -X +Y -Y +Z -Z = right, left, top, bottom, front, back of Skybox.cpp:71-78): a vertical sky gradient that is
+    continuous across the faces, a sun disc, and a faint per-face checker so filtering and face seams are exercised."""
+    j, i = np.meshgrid(np.arange(size, dtype=np.float64), np.arange(size, dtype=np.float64), indexing="ij")
+    sc = 2.0 * (i + 0.5) / size - 1.0
+    tc = 2.0 * (j + 0.5) / size - 1.0
+    one = np.ones_like(sc)
+    dirs = [(one, -tc, -sc), (-one, -tc, sc), (sc, one, tc), (sc, -one, -tc), (sc, -tc, one), (-sc, -tc, -one)]
+    sun = _norm(np.array([0.3, 1.0, 0.2]))
+    rng = np.random.default_rng(seed)
+    tint = rng.uniform(0.9, 1.0, size=(6, 3))
+    faces = np.empty((6, size, size, 4), np.uint16)
+    for f, (x, y, z) in enumerate(dirs):
+        n = np.sqrt(x * x + y * y + z * z)
+        x, y, z = x / n, y / n, z / n
+        up = 0.5 * y + 0.5
+        col = np.stack([0.25 + 0.35 * (1 - up), 0.35 + 0.35 * (1 - up), 0.55 + 0.4 * up], -1)
+        s_dot = np.clip(x * sun[0] + y * sun[1] + z * sun[2], 0.0, 1.0)
+        col += (s_dot[..., None] ** 64) * np.array([1.0, 0.9, 0.6])
+        chk = (((i.astype(np.int64) >> 2) + (j.astype(np.int64) >> 2)) & 1).astype(np.float64)
+        col *= (0.92 + 0.08 * chk)[..., None] * tint[f]
+        faces[f, ..., :3] = np.round(np.clip(col, 0.0, 1.0) * 65535.0).astype(np.uint16)
+        faces[f, ..., 3] = 65535
+    return faces
+
+
 def algorithmic_bytes(scene, hdr=False):
     """Compulsory HBM traffic per frame: returns (B_shadow, B_forward)."""
     V, T = scene["n_vertices"], scene["n_triangles"]

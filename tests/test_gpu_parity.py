@@ -401,3 +401,47 @@ def test_parity_perspective_shadow_transform():
     assert gpu["counters"][0] == 0 and o.counters[0] == 0
     check_parity(s, gpu, ref_shadow, ref)
     assert 0.2 < (ref_shadow < 1.0).mean()
+
+
+@pytest.mark.parametrize("pbr", [False, True])
+def test_parity_skybox_background(pbr):
+    """the cube-map background (skybox.vert / skybox.frag, Appendix B.11) behind Phong and PBR frames,
+    for the framing camera, a camera inside the scene looking at the horizon, and straight up (face seams and corners)."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    if pbr:
+        s = sc.to_pbr(s)
+    s["skybox"] = sc.make_skybox(48)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    views = [np.asarray(s["view"]), sc.view_from(s, (0.3, 1.2, 0.4), (6.0, 1.4, 5.0)), sc.view_from(s, (0.0, 1.5, 0.0), (0.05, 9.0, 0.02)),
+             sc.view_from(s, (0.0, 1.0, 0.0), (5.0, 5.0, 5.0), fov=100.0)]
+    for v in views:
+        o.set_view(v); ctx.set_view(v)
+        ref = o.render_forward(ref_shadow)
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+        gpu = dict(shadow=ctx.readback(capi.REB_SHADOW_F32), tri_id=ctx.readback(capi.REB_TRIID_U32), depth=ctx.readback(capi.REB_DEPTH_F32),
+                   color_f32=ctx.readback(capi.REB_COLOR_F32), color_srgb8=ctx.readback(capi.REB_COLOR_SRGB8))
+        check_parity(s, gpu, ref_shadow, ref)
+        sky = ref["tri_id"] == 0xFFFFFFFF
+        assert sky.mean() > 0.02
+        # the background is the same individually rounded arithmetic on both sides: bit-exact
+        assert np.array_equal(gpu["color_f32"][sky].view(np.uint32), ref["color_f32"][sky].view(np.uint32))
+        assert (ref["color_f32"][sky][:, :3].max(axis=1) > 0.05).all()
+    # removing the skybox restores the clear colour
+    ctx.set_skybox(None)
+    ctx.render_forward(s["draws"])
+    c = ctx.readback(capi.REB_COLOR_SRGB8)
+    assert (c[sky] == np.array([0, 0, 0, 255], np.uint8)).all()
+
+
+def test_set_skybox_rejects_bad_arguments():
+    from renderengine_b200 import capi
+    ctx = capi.Context(64, 64)
+    with pytest.raises(ValueError):
+        ctx.set_skybox(np.zeros((5, 8, 8, 4), np.uint16))
+    with pytest.raises(capi.RebError):
+        ctx._ck(ctx.lib.reb_set_skybox(ctx.h, np.zeros(8, np.uint16).ctypes.data, 0, 4))

@@ -29,6 +29,9 @@ def load_dump(path):
     s["shadow_view"] = take(64, np.float32, (16,)); s["shadow_proj"] = take(64, np.float32, (16,))
     out = dict(shadow=take(S * S * 4, np.float32, (S, S)), depth=take(W * H * 4, np.float32, (H, W)), tri_id=take(W * H * 4, np.uint32, (H, W)),
                color_srgb8=take(W * H * 4, np.uint8, (H, W, 4)), color_f32=take(W * H * 16, np.float32, (H, W, 4)))
+    if off[0] != raw.size:   # optional trailer: skybox faces
+        n = int(take(4, np.uint32, (1,))[0])
+        s["skybox"] = take(6 * n * n * 8, np.uint16, (6, n, n, 4))
     assert off[0] == raw.size
     s["n_triangles"] = nI // 3; s["n_vertices"] = nV
     return s, out
@@ -55,6 +58,27 @@ def test_host_facade_frame_matches_oracle(tmp_path):
     # draws arrive sorted by (material handle, scene node) as RenderScene::SortOpaqueMeshes leaves them
     keys = [(int(d[2]), int(d[3])) for d in s["draws"]]
     assert keys == sorted(keys)
+
+
+@pytest.mark.gpu
+def test_host_facade_skybox_matches_oracle(tmp_path):
+    """reb::Skybox (Skybox.h:17-55) staged before RenderScene::Init, uploaded with the scene, behind the Phong frame."""
+    from oracle import orc
+    from renderengine_b200 import build
+    exe = build.build_host()
+    dump = str(tmp_path / "sky.bin")
+    r = subprocess.run([exe, "2", "2", "2", "320", "180", "256", "2", dump, "16"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s, gpu = load_dump(dump)
+    assert s["skybox"].shape == (6, 16, 16, 4)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    assert np.array_equal(gpu["tri_id"], ref["tri_id"]) and np.array_equal(gpu["depth"].view(np.uint32), ref["depth"].view(np.uint32))
+    assert np.abs(gpu["color_srgb8"].astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
+    sky = ref["tri_id"] == 0xFFFFFFFF
+    assert sky.mean() > 0.05 and np.array_equal(gpu["color_f32"][sky].view(np.uint32), ref["color_f32"][sky].view(np.uint32))
+    assert (gpu["color_f32"][sky][:, 2] > 0.1).all()       # every face tone is >= 9000 / 65535
 
 
 @pytest.mark.gpu

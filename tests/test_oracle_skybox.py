@@ -1,0 +1,82 @@
+"""CPU checks of the oracle's skybox (Appendix B.11; skybox.vert:32-37, skybox.frag:28-31): the restated cube lookup
+against the Vulkan face-selection table, and the per-pixel view ray against the reference's vertex-shader formula
+evaluated in float64."""
+import numpy as np
+import pytest
+
+from oracle import orc
+from renderengine_b200 import scene as sc
+
+
+def _const_faces(size=8):
+    f = np.zeros((6, size, size, 4), np.uint16)
+    for k in range(6):
+        f[k, ..., 0] = 10000 * (k + 1)
+        f[k, ..., 3] = 65535
+    return f
+
+
+@pytest.mark.parametrize("d,face", [((1, 0.2, -0.3), 0), ((-1, 0.2, 0.3), 1), ((0.1, 1, 0.3), 2), ((0.1, -1, 0.3), 3), ((0.2, -0.3, 1), 4), ((0.2, 0.3, -1), 5),
+                                    ((0.5, 0.5, 1), 4), ((0.5, 1, 0.4), 2), ((-0.5, -0.5, -1), 5)])
+def test_face_selection_matches_vulkan_table(d, face):
+    c = orc.sky_lookup(_const_faces(), np.array(d, np.float32) * 3.0)     # scale-invariant
+    assert abs(c[0] * 65535.0 - 10000 * (face + 1)) < 0.51 and c[3] == 1.0
+
+
+def test_lookup_st_orientation_and_bilinear():
+    size = 4
+    f = np.zeros((6, size, size, 4), np.uint16)
+    f[0, :, :, 0] = (np.arange(size)[None, :] * 1000)       # +X face: red = 1000 * i (s axis)
+    f[0, :, :, 1] = (np.arange(size)[:, None] * 1000)       # green = 1000 * j (t axis)
+    # +X: sc = -rz, tc = -ry.  direction (1, -0.5, -0.25): s = 0.5*0.25+0.5 = 0.625, t = 0.5*0.5+0.5 = 0.75
+    c = orc.sky_lookup(f, np.array([1, -0.5, -0.25], np.float32))
+    u, v = 0.625 * size - 0.5, 0.75 * size - 0.5             # 2.0, 2.5
+    assert abs(c[0] * 65535.0 - 1000 * u) < 0.01 and abs(c[1] * 65535.0 - 1000 * v) < 0.01
+
+
+def test_seam_is_continuous():
+    """Seamless filtering: walking a direction across the +X / +Z edge changes the colour smoothly (no clamp plateau / jump)."""
+    faces = sc.make_skybox(16)
+    prev = None
+    for a in np.linspace(np.pi / 4 - 0.08, np.pi / 4 + 0.08, 41):
+        c = orc.sky_lookup(faces, np.array([np.sin(a), 0.1, np.cos(a)], np.float32))
+        if prev is not None:
+            assert np.abs(c - prev).max() < 0.03
+        prev = c
+
+
+def test_pixel_ray_matches_reference_vertex_shader():
+    """skybox.vert: clip = proj * mat4(mat3(view)) * (p, 1), gl_Position = clip.xyww.  A cube point p projects to the
+    pixel whose oracle ray is parallel to p: check by projecting the oracle's own ray in float64."""
+    s = sc.make_scene("C1")
+    W, H = s["width"], s["height"]
+    view = np.frombuffer(np.asarray(s["view"], np.uint8).tobytes(), np.float32)
+    V = view[:16].reshape(4, 4).T.astype(np.float64)
+    P = view[16:32].reshape(4, 4).T.astype(np.float64)
+    R = np.eye(4); R[:3, :3] = V[:3, :3]
+    # a cube whose texel colour encodes the direction: use lookups of pure directions instead of an image
+    A = (P @ R)[[0, 1, 3]][:, :3]
+    Ainv = np.linalg.inv(A)
+    for (x, y) in [(0, 0), (W - 1, 0), (W // 2, H // 2), (17, H - 3), (W - 1, H - 1)]:
+        xn = ((x + 0.5) - 0.5 * W) / (0.5 * W); yn = ((y + 0.5) - 0.5 * H) / (0.5 * H)
+        p = Ainv @ np.array([xn, yn, 1.0])
+        clip = P @ R @ np.array([p[0], p[1], p[2], 1.0])
+        assert clip[3] > 0 and abs(clip[0] / clip[3] - xn) < 1e-9 and abs(clip[1] / clip[3] - yn) < 1e-9
+        faces = sc.make_skybox(32)
+        got = orc.sky_pixel(s["view"], W, H, faces, x, y)
+        want = orc.sky_lookup(faces, p.astype(np.float32))
+        assert np.abs(got - want).max() < 2e-4             # float32 ray vs float64 ray through a smooth cube
+
+
+def test_forward_fills_background_only():
+    s = sc.make_scene("C1", width=160, height=90)
+    base = orc.Oracle(s).render_forward(None)
+    s2 = dict(s); s2["skybox"] = sc.make_skybox(32)
+    sky = orc.Oracle(s2).render_forward(None)
+    empty = base["tri_id"] == 0xFFFFFFFF
+    assert empty.any() and (~empty).any()
+    assert np.array_equal(base["depth"], sky["depth"]) and np.array_equal(base["tri_id"], sky["tri_id"])
+    assert np.array_equal(base["color_srgb8"][~empty], sky["color_srgb8"][~empty])
+    assert (sky["color_f32"][empty][:, :3].max(axis=1) > 0.1).all()          # background now holds the cube map
+    x, y = np.argwhere(empty)[0][::-1]
+    assert np.array_equal(sky["color_f32"][y, x], orc.sky_pixel(s["view"], 160, 90, s2["skybox"], int(x), int(y)))
