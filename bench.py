@@ -33,10 +33,14 @@ METRIC, UNIT = "Mtri/s", "Mtri/s"
 def profiled_traffic(kind, slot):
     """dram__bytes_read+write per launch of the named kernel from the newest committed ncu capture (profiles/*_traffic.json)."""
     import glob
+    import re
     name = {"tile_stage": "k_tile_forward" if kind == 1 else "k_tile_shadow",
             "setup_raster": "k_setup_raster<%s>" % ("forward" if kind == 1 else "shadow"),
             "vertex": "k_vertex<%s>" % ("forward" if kind == 1 else "shadow")}.get(slot)
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+
+    def natural(path):   # r1_v10 after r1_v9
+        return [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", os.path.basename(path))]
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), key=natural, reverse=True):
         try:
             with open(path) as f:
                 t = json.load(f)["dram_bytes_per_launch"]
