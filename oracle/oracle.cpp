@@ -312,7 +312,13 @@ struct PassParams {
     const float* PV;     // proj*view (formed once with mat4_mul_mat4)
     bool divideWorldByW; // primitive.vert:51 (forward) vs shadow_map.vert:49 (shadow)
     uint32_t W, H;
+    // Appendix B.12 (multisampling): sample k of a pixel sits at (x + sx, y + sy) instead of the centre.  Edge functions
+    // and depth are translation-invariant, so sampling there equals sampling the centre of the primitive moved by
+    // (128 - 256 sx, 128 - 256 sy) sub-pixel units — an exact integer shift of the snapped vertices.
+    int32_t shiftX = 0, shiftY = 0;
 };
+// Vulkan standard sample locations for 4 samples ((0.375, 0.125), (0.875, 0.375), (0.125, 0.625), (0.625, 0.875)) as shifts
+static const int32_t MSAA4_SHIFT[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};
 
 inline V4 vertex_stage(const PassParams& pp, const float* T, const float* pos, V3* worldOut) {
     V4 wH = mat4_mul(T, {pos[0], pos[1], pos[2], 1.0f});
@@ -341,8 +347,8 @@ inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t 
         float xf = hw * nx + hw;
         float yf = hh * ny + hh;
         if (!(std::fabs(xf) <= GUARD_PX) || !(std::fabs(yf) <= GUARD_PX)) return NEEDS_CLIP;
-        s.X[k] = (int32_t)std::lrintf(xf * 256.0f);   // B.5 round-half-even, 8 sub-pixel bits
-        s.Y[k] = (int32_t)std::lrintf(yf * 256.0f);
+        s.X[k] = (int32_t)std::lrintf(xf * 256.0f) + pp.shiftX;   // B.5 round-half-even, 8 sub-pixel bits (+ B.12 sample shift)
+        s.Y[k] = (int32_t)std::lrintf(yf * 256.0f) + pp.shiftY;
         s.z[k] = nz;
         s.w[k] = c[k].w;
     }
@@ -850,8 +856,10 @@ int orc_render_shadow(const orc_scene* sc, float* shadowMap, uint64_t* counters)
 
 // Forward pass: MaterialSystem::Draw (MaterialSystem.cpp:88-101) + primitive.vert:49-57 + the
 // builder-defined Phong main() of Appendix B.11 over phong.glsl / shadow.glsl.
-int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth, uint32_t* triId, float* colorF32,
-                       uint8_t* colorSRGB8, uint64_t* counters) {
+namespace {
+// depth / triId hold nSamples planes of W x H (1 = the 1-sample contract, 4 = Appendix B.12)
+int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* depth, uint32_t* triId, float* colorF32,
+                        uint8_t* colorSRGB8, uint64_t* counters, int nSamples) {
     if (!sc || !depth || !triId) return -1;
     const float* view = reinterpret_cast<const float*>(sc->view);
     const float* proj = view + 16;
@@ -860,11 +868,21 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
     mat4_mul_mat4(proj, view, PV);   // GetView().proj * GetView().view (primitive.vert:53)
     const bool haveShadow = sc->shadowSize > 0 && shadowMap != nullptr;
     if (haveShadow) mat4_mul_mat4(sc->shadowProj, sc->shadowView, STR);   // ShadowSystem.cpp:303
-    PassParams pp{PV, true, sc->width, sc->height};
+    PassParams pp{PV, true, sc->width, sc->height};   // unshifted: shading happens at pixel centres
     Frontend fe;
-    run_frontend(sc, pp, fe);
     uint64_t frags = 0;
-    rasterize(sc, pp, fe, depth, triId, true, &frags);
+    if (nSamples == 1) {
+        run_frontend(sc, pp, fe);
+        rasterize(sc, pp, fe, depth, triId, true, &frags);
+    } else {
+        for (int k = 0; k < nSamples; ++k) {
+            PassParams ps = pp;
+            ps.shiftX = MSAA4_SHIFT[k][0]; ps.shiftY = MSAA4_SHIFT[k][1];
+            fe = Frontend();
+            run_frontend(sc, ps, fe);
+            rasterize(sc, ps, fe, depth + (size_t)k * sc->width * sc->height, triId + (size_t)k * sc->width * sc->height, true, &frags);
+        }
+    }
     if (counters) { counters[0] = fe.needsClip; counters[1] = fe.setups.size(); counters[2] = frags; counters[3] = 0; }
     if (!colorF32 && !colorSRGB8) return 0;
 
@@ -884,137 +902,169 @@ int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth
     SkyParams sky{};
     if (haveSky) { sky_setup(view, proj, sc->width, sc->height, sky); sky.faces = sc->skyFaces; sky.w = sc->skyW; sky.h = sc->skyH; }
 
+    // colour of triangle `tri` shaded at the centre of pixel (x, y) (the fragment shader runs once per pixel and primitive)
+    auto shadeTri = [&](int x, int y, uint32_t tri) -> V4 {
+        uint32_t d = (uint32_t)(std::upper_bound(fe.triPrefix.begin(), fe.triPrefix.end(), (uint64_t)tri) - fe.triPrefix.begin()) - 1;
+        const DrawRec& dr = draws[d];
+        const uint32_t* ix = sc->indices + dr.indexOffset + 3 * ((uint64_t)tri - fe.triPrefix[d]);
+        const float* T = sc->transforms + 16 * (size_t)dr.sceneNode;
+        const float* N = &nmat[9 * (size_t)dr.sceneNode];
+        V4 c[3]; V3 world[3], nrm[3]; float uv[3][2];
+        for (int k = 0; k < 3; ++k) {
+            const float* v = sc->verts + 8 * (size_t)ix[k];
+            c[k] = vertex_stage(pp, T, v, &world[k]);
+            nrm[k] = normalize3(mat3_mul(N, {v[3], v[4], v[5]}));   // primitive.vert:55
+            uv[k][0] = v[6]; uv[k][1] = v[7];
+        }
+        Setup s;
+        const bool clippedParent = setup_triangle(pp, c, tri, s) == NEEDS_CLIP;   // B.3: the pixel was won by one of its clipped children
+        Edges e{}; float inv = 0.0f;
+        if (!clippedParent) { e = make_edges(s); inv = 1.0f / (float)(-s.A2); }
+        const int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
+        // B.10 perspective-correct weights at pixel (x + ox, y + oy): from the snapped vertices, or in homogeneous form for a clipped parent
+        auto weights = [&](int ox, int oy, float qq[3]) {
+            if (clippedParent) { homogeneous_weights(pp, c, (float)(x + ox), (float)(y + oy), qq); return; }
+            const int64_t Qx = Px + 256 * ox, Qy = Py + 256 * oy;
+            for (int k = 0; k < 3; ++k) {
+                int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
+                qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
+            }
+        };
+        float q[3];
+        weights(0, 0, q);
+        float den = (q[0] + q[1]) + q[2];
+        float rden = 1.0f / den;             // r1b: one reciprocal per fragment, then multiplies
+        auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) * rden; };
+        V3 fragPos = {interp(world[0].x, world[1].x, world[2].x), interp(world[0].y, world[1].y, world[2].y),
+                      interp(world[0].z, world[1].z, world[2].z)};
+        V3 normal = {interp(nrm[0].x, nrm[1].x, nrm[2].x), interp(nrm[0].y, nrm[1].y, nrm[2].y),
+                     interp(nrm[0].z, nrm[1].z, nrm[2].z)};
+        uint32_t matIndex = dr.materialRaw >> 4;   // MaterialHandle::GetIndex (MaterialDefines.h:88-96)
+        const uint8_t* mr = sc->materials + (size_t)matIndex * sc->materialStride;
+        if (sc->shadingModel == 1) {   // ---- reference's live PBR fragment path (surface_pbr.frag:38-50) ----
+            const PbrMaterial pm = load_pbr_material(mr);
+            auto live = [&](uint32_t h) { return h < sc->maxDescriptors && h < textures.size(); };
+            const bool anyTex = live(pm.tex[0]) || live(pm.tex[1]) || live(pm.tex[2]) || live(pm.tex[3]);
+            V3 nrmOut = normal;
+            V4 tb, te, to; const V4 *pb = nullptr, *pe = nullptr, *po = nullptr;
+            if (anyTex) {
+                // attributes here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
+                float tuv[3][2]; V3 tpos[3];
+                for (int n = 0; n < 3; ++n) {
+                    float qq[3];
+                    weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
+                    float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
+                    auto ip = [&](float a0, float a1, float a2) { return ((qq[0] * a0 + qq[1] * a1) + qq[2] * a2) * rdd; };
+                    tuv[n][0] = ip(uv[0][0], uv[1][0], uv[2][0]); tuv[n][1] = ip(uv[0][1], uv[1][1], uv[2][1]);
+                    tpos[n] = {ip(world[0].x, world[1].x, world[2].x), ip(world[0].y, world[1].y, world[2].y), ip(world[0].z, world[1].z, world[2].z)};
+                }
+                const float st1[2] = {tuv[1][0] - tuv[0][0], tuv[1][1] - tuv[0][1]}, st2[2] = {tuv[2][0] - tuv[0][0], tuv[2][1] - tuv[0][1]};
+                auto samp = [&](uint32_t h) { return sample_texture(textures[h], tuv[0][0], tuv[0][1], st1[0], st1[1], st2[0], st2[1]); };
+                if (live(pm.tex[3])) { V4 t = samp(pm.tex[3]); nrmOut = pbr_get_normal(true, {t.x, t.y, t.z}, sub3(tpos[1], tpos[0]), sub3(tpos[2], tpos[0]), st1, st2, normal); }
+                if (live(pm.tex[0])) { tb = samp(pm.tex[0]); pb = &tb; }
+                if (live(pm.tex[1])) { te = samp(pm.tex[1]); pe = &te; }
+                if (live(pm.tex[2])) { to = samp(pm.tex[2]); po = &to; }
+            }
+            const PbrRemapped rm = pbr_remap(pm, nrmOut, pb, pe, po);
+            float exposure; uint32_t dbgIn, dbgEq;
+            std::memcpy(&exposure, sc->view + 140, 4); std::memcpy(&dbgIn, sc->view + 144, 4); std::memcpy(&dbgEq, sc->view + 148, 4);
+            return pbr_lighting(rm, pbrLights, sc->nLights, fragPos, viewPos, exposure, dbgIn, dbgEq, haveShadow, STR, shadowMap, sc->shadowSize);
+        }
+        PhongProps props;
+        uint32_t texHandle[2];
+        std::memcpy(&props.diffuse, mr + 0, 16);
+        std::memcpy(&props.specular, mr + 16, 16);
+        std::memcpy(&props.shininess, mr + 32, 4);
+        std::memcpy(texHandle, mr + 36, 8);          // diffuseTex, specularTex (phong.glsl:8-12)
+
+        // bindless texture lookup (pattern of pbr.glsl:100-108): a handle is live iff < MAX_DESCRIPTOR_COUNT
+        const bool useTex[2] = {texHandle[0] < sc->maxDescriptors && texHandle[0] < textures.size(),
+                                texHandle[1] < sc->maxDescriptors && texHandle[1] < textures.size()};
+        if (useTex[0] || useTex[1]) {
+            // uv here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
+            float tuv[3][2];
+            for (int n = 0; n < 3; ++n) {
+                float qq[3];
+                weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
+                float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
+                tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) * rdd;
+                tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) * rdd;
+            }
+            const float dudx = tuv[1][0] - tuv[0][0], dvdx = tuv[1][1] - tuv[0][1];
+            const float dudy = tuv[2][0] - tuv[0][0], dvdy = tuv[2][1] - tuv[0][1];
+            if (useTex[0]) {
+                V4 tcol = sample_texture(textures[texHandle[0]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
+                props.diffuse = {props.diffuse.x * tcol.x, props.diffuse.y * tcol.y, props.diffuse.z * tcol.z, props.diffuse.w * tcol.w};
+            }
+            if (useTex[1]) {
+                V4 tcol = sample_texture(textures[texHandle[1]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
+                props.specular = {props.specular.x * tcol.x, props.specular.y * tcol.y, props.specular.z * tcol.z, props.specular.w * tcol.w};
+            }
+        }
+
+        V4 acc = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (uint32_t l = 0; l < sc->nLights; ++l) {
+            const Light& L = lights[l];
+            float shadow = 0.0f;
+            if (haveShadow && (uint32_t)L.type == LIGHT_TYPE_DIRECTIONAL && L.shadowIndex == 0)
+                shadow = compute_shadow(L, fragPos, normal, STR, shadowMap, sc->shadowSize);
+            V4 cl = phong_lighting(L, props, normal, fragPos, viewPos, shadow);
+            acc = {acc.x + cl.x, acc.y + cl.y, acc.z + cl.z, acc.w + cl.w};
+        }
+        return {acc.x, acc.y, acc.z, props.diffuse.w};
+    };
+    const V4 clearColour = {0.0f, 0.0f, 0.0f, 1.0f};   // RenderScene.cpp:217-220
+
     unsigned nT = thread_count(sc);
     const int W = (int)sc->width, H = (int)sc->height;
+    const size_t plane = (size_t)W * H;
     parallel_for(nT, [&](unsigned t) {
         int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
         for (int y = r0; y < r1; ++y)
             for (int x = 0; x < W; ++x) {
                 size_t p = (size_t)y * W + x;
-                V4 out = {0.0f, 0.0f, 0.0f, 1.0f};   // clear colour (RenderScene.cpp:217-220)
-                uint32_t tri = triId[p];
-                if (haveSky && depth[p] == 1.0f) {   // drawn last at depth 1.0, LessOrEqual (Appendix B.11)
-                    out = sky_pixel(sky, x, y);
-                    tri = TRI_NONE;
-                }
-                if (tri != TRI_NONE) {
-                    uint32_t d = (uint32_t)(std::upper_bound(fe.triPrefix.begin(), fe.triPrefix.end(), (uint64_t)tri) - fe.triPrefix.begin()) - 1;
-                    const DrawRec& dr = draws[d];
-                    const uint32_t* ix = sc->indices + dr.indexOffset + 3 * ((uint64_t)tri - fe.triPrefix[d]);
-                    const float* T = sc->transforms + 16 * (size_t)dr.sceneNode;
-                    const float* N = &nmat[9 * (size_t)dr.sceneNode];
-                    V4 c[3]; V3 world[3], nrm[3]; float uv[3][2];
-                    for (int k = 0; k < 3; ++k) {
-                        const float* v = sc->verts + 8 * (size_t)ix[k];
-                        c[k] = vertex_stage(pp, T, v, &world[k]);
-                        nrm[k] = normalize3(mat3_mul(N, {v[3], v[4], v[5]}));   // primitive.vert:55
-                        uv[k][0] = v[6]; uv[k][1] = v[7];
+                V4 out;
+                if (nSamples == 1) {
+                    // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.11)
+                    if (haveSky && depth[p] == 1.0f) out = sky_pixel(sky, x, y);
+                    else if (triId[p] != TRI_NONE) out = shadeTri(x, y, triId[p]);
+                    else out = clearColour;
+                } else {
+                    // Appendix B.12: every sample takes the colour its winning primitive was shaded with at the pixel centre
+                    // (one shader invocation per pixel and primitive); the resolve is the average in linear float, (s0 + s1) + (s2 + s3)
+                    V4 col[4];
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t tri = triId[k * plane + p];
+                        const bool skyHere = haveSky && depth[k * plane + p] == 1.0f;
+                        int same = -1;
+                        for (int j = 0; j < k && same < 0; ++j) {
+                            const bool skyJ = haveSky && depth[j * plane + p] == 1.0f;
+                            if (skyJ == skyHere && (skyHere || triId[j * plane + p] == tri)) same = j;
+                        }
+                        if (same >= 0) col[k] = col[same];
+                        else if (skyHere) col[k] = sky_pixel(sky, x, y);
+                        else if (tri != TRI_NONE) col[k] = shadeTri(x, y, tri);
+                        else col[k] = clearColour;
                     }
-                    Setup s;
-                    const bool clippedParent = setup_triangle(pp, c, tri, s) == NEEDS_CLIP;   // B.3: the pixel was won by one of its clipped children
-                    Edges e{}; float inv = 0.0f;
-                    if (!clippedParent) { e = make_edges(s); inv = 1.0f / (float)(-s.A2); }
-                    const int64_t Px = 256 * (int64_t)x + 128, Py = 256 * (int64_t)y + 128;
-                    // B.10 perspective-correct weights at pixel (x + ox, y + oy): from the snapped vertices, or in homogeneous form for a clipped parent
-                    auto weights = [&](int ox, int oy, float qq[3]) {
-                        if (clippedParent) { homogeneous_weights(pp, c, (float)(x + ox), (float)(y + oy), qq); return; }
-                        const int64_t Qx = Px + 256 * ox, Qy = Py + 256 * oy;
-                        for (int k = 0; k < 3; ++k) {
-                            int64_t F = e.A[k] * Qx + e.B[k] * Qy + e.C[k];
-                            qq[k] = ((float)F * inv) * (1.0f / s.w[k]);
-                        }
-                    };
-                    float q[3];
-                    weights(0, 0, q);
-                    float den = (q[0] + q[1]) + q[2];
-                    float rden = 1.0f / den;             // r1b: one reciprocal per fragment, then multiplies
-                    auto interp = [&](float a0, float a1, float a2) { return ((q[0] * a0 + q[1] * a1) + q[2] * a2) * rden; };
-                    V3 fragPos = {interp(world[0].x, world[1].x, world[2].x), interp(world[0].y, world[1].y, world[2].y),
-                                  interp(world[0].z, world[1].z, world[2].z)};
-                    V3 normal = {interp(nrm[0].x, nrm[1].x, nrm[2].x), interp(nrm[0].y, nrm[1].y, nrm[2].y),
-                                 interp(nrm[0].z, nrm[1].z, nrm[2].z)};
-                    uint32_t matIndex = dr.materialRaw >> 4;   // MaterialHandle::GetIndex (MaterialDefines.h:88-96)
-                    const uint8_t* mr = sc->materials + (size_t)matIndex * sc->materialStride;
-                    if (sc->shadingModel == 1) {   // ---- reference's live PBR fragment path (surface_pbr.frag:38-50) ----
-                        const PbrMaterial pm = load_pbr_material(mr);
-                        auto live = [&](uint32_t h) { return h < sc->maxDescriptors && h < textures.size(); };
-                        const bool anyTex = live(pm.tex[0]) || live(pm.tex[1]) || live(pm.tex[2]) || live(pm.tex[3]);
-                        V3 nrmOut = normal;
-                        V4 tb, te, to; const V4 *pb = nullptr, *pe = nullptr, *po = nullptr;
-                        if (anyTex) {
-                            // attributes here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
-                            float tuv[3][2]; V3 tpos[3];
-                            for (int n = 0; n < 3; ++n) {
-                                float qq[3];
-                                weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
-                                float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
-                                auto ip = [&](float a0, float a1, float a2) { return ((qq[0] * a0 + qq[1] * a1) + qq[2] * a2) * rdd; };
-                                tuv[n][0] = ip(uv[0][0], uv[1][0], uv[2][0]); tuv[n][1] = ip(uv[0][1], uv[1][1], uv[2][1]);
-                                tpos[n] = {ip(world[0].x, world[1].x, world[2].x), ip(world[0].y, world[1].y, world[2].y), ip(world[0].z, world[1].z, world[2].z)};
-                            }
-                            const float st1[2] = {tuv[1][0] - tuv[0][0], tuv[1][1] - tuv[0][1]}, st2[2] = {tuv[2][0] - tuv[0][0], tuv[2][1] - tuv[0][1]};
-                            auto samp = [&](uint32_t h) { return sample_texture(textures[h], tuv[0][0], tuv[0][1], st1[0], st1[1], st2[0], st2[1]); };
-                            if (live(pm.tex[3])) { V4 t = samp(pm.tex[3]); nrmOut = pbr_get_normal(true, {t.x, t.y, t.z}, sub3(tpos[1], tpos[0]), sub3(tpos[2], tpos[0]), st1, st2, normal); }
-                            if (live(pm.tex[0])) { tb = samp(pm.tex[0]); pb = &tb; }
-                            if (live(pm.tex[1])) { te = samp(pm.tex[1]); pe = &te; }
-                            if (live(pm.tex[2])) { to = samp(pm.tex[2]); po = &to; }
-                        }
-                        const PbrRemapped rm = pbr_remap(pm, nrmOut, pb, pe, po);
-                        float exposure; uint32_t dbgIn, dbgEq;
-                        std::memcpy(&exposure, sc->view + 140, 4); std::memcpy(&dbgIn, sc->view + 144, 4); std::memcpy(&dbgEq, sc->view + 148, 4);
-                        out = pbr_lighting(rm, pbrLights, sc->nLights, fragPos, viewPos, exposure, dbgIn, dbgEq, haveShadow, STR, shadowMap, sc->shadowSize);
-                        if (colorF32) { colorF32[4 * p + 0] = out.x; colorF32[4 * p + 1] = out.y; colorF32[4 * p + 2] = out.z; colorF32[4 * p + 3] = out.w; }
-                        if (colorSRGB8) orc_srgb8(&out.x, colorSRGB8 + 4 * p);
-                        continue;
-                    }
-                    PhongProps props;
-                    uint32_t texHandle[2];
-                    std::memcpy(&props.diffuse, mr + 0, 16);
-                    std::memcpy(&props.specular, mr + 16, 16);
-                    std::memcpy(&props.shininess, mr + 32, 4);
-                    std::memcpy(texHandle, mr + 36, 8);          // diffuseTex, specularTex (phong.glsl:8-12)
-
-                    // bindless texture lookup (pattern of pbr.glsl:100-108): a handle is live iff < MAX_DESCRIPTOR_COUNT
-                    const bool useTex[2] = {texHandle[0] < sc->maxDescriptors && texHandle[0] < textures.size(),
-                                            texHandle[1] < sc->maxDescriptors && texHandle[1] < textures.size()};
-                    if (useTex[0] || useTex[1]) {
-                        // uv here and at the +x / +y neighbour pixel centres of the same primitive (implicit derivatives)
-                        float tuv[3][2];
-                        for (int n = 0; n < 3; ++n) {
-                            float qq[3];
-                            weights(n == 1 ? 1 : 0, n == 2 ? 1 : 0, qq);
-                            float rdd = 1.0f / ((qq[0] + qq[1]) + qq[2]);
-                            tuv[n][0] = ((qq[0] * uv[0][0] + qq[1] * uv[1][0]) + qq[2] * uv[2][0]) * rdd;
-                            tuv[n][1] = ((qq[0] * uv[0][1] + qq[1] * uv[1][1]) + qq[2] * uv[2][1]) * rdd;
-                        }
-                        const float dudx = tuv[1][0] - tuv[0][0], dvdx = tuv[1][1] - tuv[0][1];
-                        const float dudy = tuv[2][0] - tuv[0][0], dvdy = tuv[2][1] - tuv[0][1];
-                        if (useTex[0]) {
-                            V4 tcol = sample_texture(textures[texHandle[0]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
-                            props.diffuse = {props.diffuse.x * tcol.x, props.diffuse.y * tcol.y, props.diffuse.z * tcol.z, props.diffuse.w * tcol.w};
-                        }
-                        if (useTex[1]) {
-                            V4 tcol = sample_texture(textures[texHandle[1]], tuv[0][0], tuv[0][1], dudx, dvdx, dudy, dvdy);
-                            props.specular = {props.specular.x * tcol.x, props.specular.y * tcol.y, props.specular.z * tcol.z, props.specular.w * tcol.w};
-                        }
-                    }
-
-                    V4 acc = {0.0f, 0.0f, 0.0f, 0.0f};
-                    for (uint32_t l = 0; l < sc->nLights; ++l) {
-                        const Light& L = lights[l];
-                        float shadow = 0.0f;
-                        if (haveShadow && (uint32_t)L.type == LIGHT_TYPE_DIRECTIONAL && L.shadowIndex == 0)
-                            shadow = compute_shadow(L, fragPos, normal, STR, shadowMap, sc->shadowSize);
-                        V4 cl = phong_lighting(L, props, normal, fragPos, viewPos, shadow);
-                        acc = {acc.x + cl.x, acc.y + cl.y, acc.z + cl.z, acc.w + cl.w};
-                    }
-                    out = {acc.x, acc.y, acc.z, props.diffuse.w};
+                    // pairwise sum: a pixel whose four samples agree resolves to exactly the 1-sample colour
+                    out = {((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f, ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f,
+                           ((col[0].z + col[1].z) + (col[2].z + col[3].z)) * 0.25f, ((col[0].w + col[1].w) + (col[2].w + col[3].w)) * 0.25f};
                 }
                 if (colorF32) { colorF32[4 * p + 0] = out.x; colorF32[4 * p + 1] = out.y; colorF32[4 * p + 2] = out.z; colorF32[4 * p + 3] = out.w; }
                 if (colorSRGB8) orc_srgb8(&out.x, colorSRGB8 + 4 * p);
             }
     });
     return 0;
+}
+}  // namespace
+
+int orc_render_forward(const orc_scene* sc, const float* shadowMap, float* depth, uint32_t* triId, float* colorF32,
+                       uint8_t* colorSRGB8, uint64_t* counters) {
+    return render_forward_impl(sc, shadowMap, depth, triId, colorF32, colorSRGB8, counters, 1);
+}
+int orc_render_forward_msaa4(const orc_scene* sc, const float* shadowMap, float* depth4, uint32_t* triId4, float* colorF32,
+                             uint8_t* colorSRGB8, uint64_t* counters) {
+    return render_forward_impl(sc, shadowMap, depth4, triId4, colorF32, colorSRGB8, counters, 4);
 }
 
 // BRDF_Lighting for one untextured 80-B material and nLights 80-B PBR lights (pins pbr_lighting / pbr_remap against oracle/_ref)

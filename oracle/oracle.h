@@ -66,6 +66,12 @@ int orc_render_forward(const orc_scene* s, const float* shadowMap /* S*S or NULL
                        float* depth, uint32_t* triId, float* colorF32 /* RGBA or NULL */,
                        uint8_t* colorSRGB8 /* RGBA or NULL */, uint64_t* counters);
 
+/* Appendix B.12: the base pass with 4 samples per pixel at the Vulkan standard locations and an average resolve (the
+   reference's actual base-pass state, Swapchain.cpp:110-123,212; PhysicalDevice.cpp:172-186).  depth4 / triId4 hold
+   four W x H planes (sample-major); the colour outputs are the resolved image. */
+int orc_render_forward_msaa4(const orc_scene* s, const float* shadowMap, float* depth4, uint32_t* triId4,
+                             float* colorF32, uint8_t* colorSRGB8, uint64_t* counters);
+
 /* unit-level entry points used to pin the restatement against oracle/_ref */
 void orc_mat4_mul(const float* a, const float* b, float* out);
 void orc_mat4_mul_vec4(const float* m, const float* v, float* out);

@@ -60,6 +60,7 @@ def lib():
         _LIB.orc_phong_lighting.argtypes = [u8p, fp, fp, fp, fp, C.c_float, fp]
         _LIB.orc_compute_shadow.argtypes = [u8p, fp, fp, fp, fp, C.c_uint32]
         _LIB.orc_compute_shadow.restype = C.c_float
+        _LIB.orc_render_forward_msaa4.argtypes = [C.POINTER(OrcScene), fp, fp, u32p, fp, u8p, u64p]
         _LIB.orc_sky_pixel.argtypes = [u8p, C.c_uint32, C.c_uint32, u16p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, fp]
         _LIB.orc_sky_lookup.argtypes = [u16p, C.c_uint32, C.c_uint32, fp, fp]
     return _LIB
@@ -137,6 +138,16 @@ class Oracle:
         rc = lib().orc_render_shadow(C.byref(self.s), _p(out, fp), _p(self.counters, u64p))
         assert rc == 0
         return out
+
+    def render_forward_msaa4(self, shadow_map=None):
+        """Appendix B.12: 4 samples per pixel (Vulkan standard locations) + average resolve.  depth / tri_id: (4, H, W)."""
+        W, H = self.s.width, self.s.height
+        depth = np.empty((4, H, W), np.float32); tri = np.empty((4, H, W), np.uint32)
+        cf = np.empty((H, W, 4), np.float32); c8 = np.empty((H, W, 4), np.uint8)
+        sm = np.ascontiguousarray(shadow_map, np.float32) if shadow_map is not None else None
+        rc = lib().orc_render_forward_msaa4(C.byref(self.s), _p(sm, fp), _p(depth, fp), _p(tri, u32p), _p(cf, fp), _p(c8, u8p), _p(self.counters, u64p))
+        assert rc == 0
+        return {"depth": depth, "tri_id": tri, "color_f32": cf, "color_srgb8": c8}
 
     def render_forward(self, shadow_map=None, color=True):
         W, H = self.s.width, self.s.height
