@@ -41,7 +41,9 @@ typedef enum reb_status {
 #define REB_OUT_TRIID_U32   8u
 
 typedef enum reb_output_kind {
-    REB_COLOR_SRGB8 = 0, REB_COLOR_F32 = 1, REB_DEPTH_F32 = 2, REB_TRIID_U32 = 3, REB_SHADOW_F32 = 4
+    REB_COLOR_SRGB8 = 0, REB_COLOR_F32 = 1, REB_DEPTH_F32 = 2, REB_TRIID_U32 = 3, REB_SHADOW_F32 = 4,
+    /* with reb_set_sample_count(ctx, 4): the four per-sample planes (sample-major, 4 x H x W) the resolve read */
+    REB_MS_DEPTH_F32 = 5, REB_MS_TRIID_U32 = 6
 } reb_output_kind;
 
 /* Renderer ctor (Source/Runtime/Renderer/Renderer.cpp:38-51): runtime parameters that the
@@ -107,6 +109,14 @@ int reb_set_shading_model(reb_ctx* ctx, uint32_t model);
  * texel values are written to the colour target as they are (no sRGB decode, skybox.frag:30).  The buffer is consumed
  * before the call returns.  NULL removes the skybox (background = clear colour (0,0,0,1)). */
 int reb_set_skybox(reb_ctx* ctx, const void* facesRGBA16, uint32_t width, uint32_t height);
+
+/* Multisampling of the base pass — Swapchain.cpp:110-123,212 (multisampled colour / depth attachments + resolve),
+ * PhysicalDevice.cpp:172-186 (sample count), GraphicsPipelineCache.cpp:224,302.  samples = 1 (default; the 1-sample
+ * parity contract) or 4: four samples per pixel at the Vulkan standard locations, depth-tested per sample, every
+ * primitive shaded once per pixel at the pixel centre, average resolve in linear float before the sRGB encode.
+ * The depth / triangle-ID outputs then hold sample 0; REB_MS_* expose all four planes.  The shadow pass stays 1 sample
+ * (ShadowSystem.cpp:44). */
+int reb_set_sample_count(reb_ctx* ctx, uint32_t samples);
 
 /* ShadowSystem::Render(drawCommands) — ShadowSystem.cpp:319-376 */
 int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, uint32_t n);

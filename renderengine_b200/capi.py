@@ -10,11 +10,12 @@ LIB_PATH = os.environ.get("REB_LIB") or os.path.join(HERE, "libreb.so")   # REB_
 
 REB_OUT_COLOR_SRGB8, REB_OUT_COLOR_F32, REB_OUT_DEPTH_F32, REB_OUT_TRIID_U32 = 1, 2, 4, 8
 REB_COLOR_SRGB8, REB_COLOR_F32, REB_DEPTH_F32, REB_TRIID_U32, REB_SHADOW_F32 = 0, 1, 2, 3, 4
+REB_MS_DEPTH_F32, REB_MS_TRIID_U32 = 5, 6
 
 SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
-    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
@@ -67,6 +68,7 @@ def load():
     lib.reb_flush.argtypes = [vp]
     lib.reb_set_shading_model.argtypes = [vp, u32]
     lib.reb_set_skybox.argtypes = [vp, vp, u32, u32]
+    lib.reb_set_sample_count.argtypes = [vp, u32]
     lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
@@ -188,6 +190,11 @@ class Context:
     def set_shading_model(self, model):
         self._ck(self.lib.reb_set_shading_model(self.h, int(model)))
 
+    def set_sample_count(self, samples):
+        """1 (default) or 4 samples per pixel for the base pass (Appendix B.12)."""
+        self._ck(self.lib.reb_set_sample_count(self.h, int(samples)))
+        self.samples = int(samples)
+
     def set_skybox(self, faces):
         """faces: (6, h, w, 4) uint16 cube map (+X -X +Y -Y +Z -Z), or None to remove it (Skybox.cpp:58-92)."""
         if faces is None:
@@ -209,7 +216,9 @@ class Context:
         return p.value, b.value
 
     def readback(self, kind, out=None):
-        if kind == REB_SHADOW_F32:
+        if kind in (REB_MS_DEPTH_F32, REB_MS_TRIID_U32):
+            shape, dt = (getattr(self, "samples", 1), self.height, self.width), (np.float32 if kind == REB_MS_DEPTH_F32 else np.uint32)
+        elif kind == REB_SHADOW_F32:
             shape, dt = (self.shadow_size, self.shadow_size), np.float32
         else:
             dt, ch = _KIND_INFO[kind]

@@ -110,11 +110,13 @@ struct K1Tri {
     bool isSmall, isLarge, needsClip;
 };
 
+template <bool SHIFT>
 __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, const uint4 q[3], K1Tri& t) {
     t.isSmall = t.isLarge = t.needsClip = false;
     t.A2 = 0; t.x0 = t.y0 = 0; t.x1 = t.y1 = -1;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) t.a[k] = {(int32_t)q[k].x, (int32_t)q[k].y, __uint_as_float(q[k].z), q[k].w};
+    for (int k = 0; k < 3; ++k)   // SHIFT: + B.12 sample shift (its own instantiation: the 1-sample kernels keep their register budget)
+        t.a[k] = {(int32_t)q[k].x + (SHIFT ? pc.shiftX : 0), (int32_t)q[k].y + (SHIFT ? pc.shiftY : 0), __uint_as_float(q[k].z), q[k].w};
     if (!valid) return;
     const uint32_t f0 = t.a[0].flags, f1 = t.a[1].flags, f2 = t.a[2].flags;
     if ((f0 & f1 & f2 & VF_PLANES) != 0u) return;                                   // Appendix B.2 trivial reject
@@ -223,10 +225,12 @@ __device__ __noinline__ bool k1_clip_emit(const PassConst& pc, uint32_t tri, uns
         for (int k = 0; k < n; ++k) a[k] = b[k];
     }
     bool queued = false;
-    const VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
+    VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
+    v0.X += pc.shiftX; v0.Y += pc.shiftY;   // B.12 sample shift
     for (int i = 1; i + 1 < n; ++i) {
         K1Tri t;
         t.a[0] = v0; t.a[1] = viewport_snap(a[i], pc.W, pc.H); t.a[2] = viewport_snap(a[i + 1], pc.W, pc.H);
+        t.a[1].X += pc.shiftX; t.a[1].Y += pc.shiftY; t.a[2].X += pc.shiftX; t.a[2].Y += pc.shiftY;
         if (((t.a[0].flags | t.a[1].flags | t.a[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
             if (lane == 0) atomicAdd(&pc.status[1], 1u);
             continue;
@@ -361,7 +365,7 @@ __device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws,
 #ifndef K1_MIN_BLOCKS
 #define K1_MIN_BLOCKS 6
 #endif
-template <bool SHADOW>
+template <bool SHADOW, bool SHIFT>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(const __grid_constant__ PassConst pc) {
     __shared__ K1Shared sm;
     pdl_enter();
@@ -387,7 +391,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
 
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
-        k1_classify(pc, tri < pc.nTris, q, t);
+        k1_classify<SHIFT>(pc, tri < pc.nTris, q, t);
         k1_emit_large(pc, t, tri, lane);
         if (t.needsClip) {   // Appendix B.3, rare: handed to k_clip_layout (keeps the clipper out of this kernel's register budget)
             const uint32_t qi = atomicAdd(&pc.status[6], 1u);
@@ -519,22 +523,34 @@ __global__ void k_split_vertices(const float4* __restrict__ aos, float4* __restr
 // ---------------------------------------------------------------------------------------------
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
     if (pc.nTris == 0) return;
-    static int perSM[2] = {0, 0};
-    if (!perSM[shadow]) {
+    using Kern = void (*)(PassConst);
+    static const Kern kern[3] = {k_setup_raster<false, false>, k_setup_raster<true, false>, k_setup_raster<false, true>};
+    const int v = shadow ? 1 : ((pc.shiftX | pc.shiftY) ? 2 : 0);   // 2: a sample pass of a multisampled frame (Appendix B.12)
+    static int perSM[3] = {0, 0, 0};
+    if (!perSM[v]) {
         int n = 0;
-        if (shadow) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_setup_raster<true>, K1_THREADS, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_setup_raster<false>, K1_THREADS, 0);
-        perSM[shadow] = n > 0 ? n : 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], K1_THREADS, 0);
+        perSM[v] = n > 0 ? n : 1;
     }
     const uint32_t nBatches = (pc.nTris + 31u) / 32u;
-    const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[shadow]));
-    if (shadow) launch_k(k_setup_raster<true>, dim3(grid), dim3(K1_THREADS), st, true, pc);
-    else launch_k(k_setup_raster<false>, dim3(grid), dim3(K1_THREADS), st, true, pc);
+    const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[v]));
+    launch_k(kern[v], dim3(grid), dim3(K1_THREADS), st, true, pc);
 }
 
 void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
     if (shadow) launch_k(k_clip_layout<true>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
     else launch_k(k_clip_layout<false>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
+}
+
+// Between the sample passes of a multisampled frame: re-arm the pass status words and the per-tile counters (K0's
+// prologue does this once per frame).  The overflow word stays sticky so the host sees an overflow of any sample pass.
+__global__ void __launch_bounds__(256) k_pass_reset(const __grid_constant__ PassConst pc) {
+    pdl_enter();
+    if (blockIdx.x == 0 && threadIdx.x < 8 && threadIdx.x != 2) pc.status[threadIdx.x] = 0u;
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
+}
+void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
+    launch_k(k_pass_reset, dim3((unsigned)numSMs), dim3(256), st, true, pc);
 }
 
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) {

@@ -353,6 +353,59 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
 #endif
 }
 
+// Multisample resolve (Appendix B.12; the reference's base pass is multisampled with an average resolve,
+// Swapchain.cpp:110-123,212).  The four sample planes were rasterised by four runs of K1..K3 with shifted vertices; here
+// every pixel shades each DISTINCT primitive among its samples once at the pixel centre (one fragment-shader invocation per
+// pixel and primitive), gives every sample the colour of its primitive (sky / clear colour for uncovered samples) and
+// averages (s0 + s1) + (s2 + s3) in linear float.  Warp = 8 x 4 px block as in the tile stage (texture / shadow-map locality).
+template <bool TEXTURED, bool PBR, bool AFFINE>
+__global__ void __launch_bounds__(KT_THREADS, 2) k_msaa_resolve(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh,
+                                                                const float* __restrict__ msDepth, const uint32_t* __restrict__ msTriId) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * TILE_W + BLK_W * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2) + (int)(lane >> 3);
+    if (x >= (int)pc.W || y >= (int)pc.H) return;
+    const size_t p = (size_t)y * pc.W + x, plane = (size_t)pc.W * pc.H;
+    uint32_t tri[4]; bool sky[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        tri[k] = __ldg(msTriId + k * plane + p);
+        sky[k] = sh.skyFaces && __ldg(msDepth + k * plane + p) == 1.0f;   // the skybox is drawn last at depth 1.0 under LessOrEqual
+        if (sky[k]) tri[k] = TRI_NONE;
+    }
+    float4 col[4];
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+        int same = -1;
+        for (int j = 0; j < k; ++j)
+            if (same < 0 && sky[j] == sky[k] && tri[j] == tri[k]) same = j;
+        if (same >= 0) { col[k] = col[same]; continue; }
+        if (sky[k]) col[k] = sky_pixel(sh, x, y);
+        else if (tri[k] != TRI_NONE) col[k] = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri[k]) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri[k]);
+        else col[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (RenderScene.cpp:218)
+    }
+    float4 out;
+    out.x = ((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f;
+    out.y = ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f;
+    out.z = ((col[0].z + col[1].z) + (col[2].z + col[3].z)) * 0.25f;
+    out.w = ((col[0].w + col[1].w) + (col[2].w + col[3].w)) * 0.25f;
+    if (sh.outDepth) sh.outDepth[p] = __ldg(msDepth + p);      // depth / triangle ID targets: sample 0
+    if (sh.outTriId) sh.outTriId[p] = __ldg(msTriId + p);
+    if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(out);
+    if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = out;
+}
+
+void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st) {
+    const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
+    const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
+    using Kern = void (*)(PassConst, ShadeConst, const float*, const uint32_t*);
+    static const Kern kern[8] = {k_msaa_resolve<false, false, false>, k_msaa_resolve<true, false, false>, k_msaa_resolve<false, true, false>, k_msaa_resolve<true, true, false>,
+                                 k_msaa_resolve<false, false, true>,  k_msaa_resolve<true, false, true>,  k_msaa_resolve<false, true, true>,  k_msaa_resolve<true, true, true>};
+    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(pc.tilesX * pc.tilesY), dim3(KT_THREADS), st, true, pc, sh, msDepth, msTriId);
+}
+
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st) {
     static int perSM = 0;
     if (!perSM) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_tile_shadow, KT_THREADS, 0); if (perSM < 1) perSM = 1; }

@@ -62,6 +62,8 @@ struct reb_ctx {
     cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[2] = {nullptr, nullptr};
     void* asyncHost = nullptr; bool asyncOutstanding = false;   // last reb_readback_async target (re-copied if the frame is replayed)
     unsigned long long* vis = nullptr;
+    // multisampling (Appendix B.12): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
+    uint32_t samples = 1; float* msDepth = nullptr; uint32_t* msTriId = nullptr;
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
     uint32_t* clipQueue = nullptr;   // largeCap entries
@@ -134,8 +136,10 @@ template <class T> int dev_alloc(reb_ctx* ctx, T** p, size_t count) {
 int alloc_targets(reb_ctx* ctx) {
     const size_t px = (size_t)ctx->W * ctx->H;
     int rc;
-    if ((rc = dev_alloc(ctx, &ctx->vis, px))) return rc;
-    launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->vis), 0xFFFFFFFFu, px * 2, ctx->numSMs, ctx->stream); ctx->launches++;
+    if ((rc = dev_alloc(ctx, &ctx->vis, px * ctx->samples))) return rc;
+    launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->vis), 0xFFFFFFFFu, px * 2 * ctx->samples, ctx->numSMs, ctx->stream); ctx->launches++;
+    if ((rc = dev_alloc(ctx, &ctx->msDepth, ctx->samples > 1 ? px * ctx->samples : 0))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->msTriId, ctx->samples > 1 ? px * ctx->samples : 0))) return rc;
     if (ctx->outputs & REB_OUT_COLOR_SRGB8) {
         for (int i = 0; i < 2; ++i) {
             if ((rc = dev_alloc(ctx, &ctx->swap[i], px * 4))) return rc;
@@ -378,19 +382,12 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     mark(1);
     if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
-    if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
-    if (ps.nTris) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
-    mark(3);
-    if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
-    mark(4);
-    if (kind == 0) {
-        launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++;
-    } else {
+    ShadeConst sh;
+    if (kind == 1) {
         if (ctx->swap[0]) {   // acquire the other swapchain image; wait for an async readback still draining it
             ctx->swapCur ^= 1; ctx->outSRGB8 = ctx->swap[ctx->swapCur];
             if (ctx->copyInFlight[ctx->swapCur]) { CU(cudaStreamWaitEvent(ctx->stream, ctx->evCopied[ctx->swapCur], 0)); ctx->copyInFlight[ctx->swapCur] = false; }
         }
-        ShadeConst sh;
         std::memset(&sh, 0, sizeof sh);
         std::memcpy(sh.STR, ctx->SPV, 64);
         std::memcpy(sh.viewPos, ctx->viewPos, 12);
@@ -409,7 +406,36 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
             sh.skyHw = 0.5f * (float)ctx->W; sh.skyHh = 0.5f * (float)ctx->H;
             sh.skyRhw = 1.0f / sh.skyHw; sh.skyRhh = 1.0f / sh.skyHh;
         }
-        launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++;
+    }
+    if (kind == 1 && ctx->samples == 4) {
+        // Appendix B.12: four raster passes over the same post-transform cache, one per Vulkan standard sample location
+        // ((0.375, 0.125), (0.875, 0.375), (0.125, 0.625), (0.625, 0.875)), each an exact shift of the snapped vertices by
+        // (128 - 256 s) sub-pixel units; every pass leaves its depth / triangle-ID plane, the resolve kernel shades.
+        static const int32_t shift[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};
+        const size_t px = (size_t)ctx->W * ctx->H;
+        for (int k = 0; k < 4; ++k) {
+            PassConst pk = pc;
+            pk.vis = ctx->vis + (size_t)k * px; pk.shiftX = shift[k][0]; pk.shiftY = shift[k][1];
+            ShadeConst sk = sh;
+            sk.outSRGB8 = nullptr; sk.outF32 = nullptr; sk.skyFaces = nullptr;   // visibility only
+            sk.outDepth = ctx->msDepth + (size_t)k * px; sk.outTriId = ctx->msTriId + (size_t)k * px;
+            if (k > 0 && ps.nTris) { launch_pass_reset(pk, ctx->numSMs, ctx->stream); ctx->launches++; }
+            if (ps.nTris) {
+                launch_setup_raster(pk, false, ctx->numSMs, ctx->stream); launch_clip_layout(pk, false, ctx->numSMs, ctx->stream);
+                launch_bin_scatter(pk, ctx->numSMs, ctx->stream); ctx->launches += 3;
+            }
+            launch_tile_forward(pk, sk, ctx->numSMs, ctx->stream); ctx->launches++;
+        }
+        mark(3); mark(4);
+        launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
+    } else {
+        if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
+        if (ps.nTris) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
+        mark(3);
+        if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
+        mark(4);
+        if (kind == 0) { launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
+        else { launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++; }
     }
     mark(5);
     CU(cudaGetLastError());

@@ -62,6 +62,8 @@ int reb_destroy(reb_ctx* ctx) {
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
     if (ctx->skyFaces) cudaFree(ctx->skyFaces);
+    if (ctx->msDepth) cudaFree(ctx->msDepth);
+    if (ctx->msTriId) cudaFree(ctx->msTriId);
     if (ctx->pass[1].vtxUV) cudaFree(ctx->pass[1].vtxUV);
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
@@ -281,7 +283,26 @@ int reb_set_skybox(reb_ctx* ctx, const void* facesRGBA16, uint32_t width, uint32
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // the host buffer is consumed before returning; earlier frames are done
     if (e != cudaSuccess) { cudaFree(dev); return fail(ctx, REB_E_CUDA, std::string("reb_set_skybox: ") + cudaGetErrorString(e)); }
     if (ctx->skyFaces) cudaFree(ctx->skyFaces);
+    if (ctx->msDepth) cudaFree(ctx->msDepth);
+    if (ctx->msTriId) cudaFree(ctx->msTriId);
     ctx->skyFaces = dev; ctx->skyW = width; ctx->skyH = height;
+    return REB_OK;
+}
+
+int reb_set_sample_count(reb_ctx* ctx, uint32_t samples) {
+    CHECK_CTX();
+    if (samples != 1u && samples != 4u) return fail(ctx, REB_E_UNSUPPORTED, "reb_set_sample_count: 1 or 4 samples per pixel");
+    if (samples == ctx->samples) return REB_OK;
+    CU(cudaSetDevice(ctx->device));
+    { int rc = flush_deferred(ctx); if (rc) return rc; }
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->samples = samples;
+    const size_t px = (size_t)ctx->W * ctx->H;
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->vis, px * samples))) return rc;
+    launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->vis), 0xFFFFFFFFu, px * 2 * samples, ctx->numSMs, ctx->stream); ctx->launches++;
+    if ((rc = dev_alloc(ctx, &ctx->msDepth, samples > 1 ? px * samples : 0))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->msTriId, samples > 1 ? px * samples : 0))) return rc;
     return REB_OK;
 }
 
@@ -309,6 +330,8 @@ static int output_info(reb_ctx* ctx, reb_output_kind kind, void** p, uint64_t* b
         case REB_DEPTH_F32: *p = ctx->outDepth; *bytes = px * 4; break;
         case REB_TRIID_U32: *p = ctx->outTriId; *bytes = px * 4; break;
         case REB_SHADOW_F32: *p = ctx->shadowMap; *bytes = (uint64_t)ctx->S * ctx->S * 4; break;
+        case REB_MS_DEPTH_F32: *p = ctx->msDepth; *bytes = px * 4 * ctx->samples; break;
+        case REB_MS_TRIID_U32: *p = ctx->msTriId; *bytes = px * 4 * ctx->samples; break;
         default: return fail(ctx, REB_E_INVALID, "unknown output kind");
     }
     if (!*p) return fail(ctx, REB_E_INVALID, "requested output is not enabled on this context");

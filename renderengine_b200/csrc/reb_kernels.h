@@ -50,5 +50,8 @@ void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, 
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
+void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st);   // between the sample passes of a multisampled frame
+// Appendix B.12 resolve: per pixel, shade every distinct primitive of the 4 sample planes once at the pixel centre, average
+void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st);
 
 }  // namespace reb

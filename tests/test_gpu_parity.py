@@ -445,3 +445,52 @@ def test_set_skybox_rejects_bad_arguments():
         ctx.set_skybox(np.zeros((5, 8, 8, 4), np.uint16))
     with pytest.raises(capi.RebError):
         ctx._ck(ctx.lib.reb_set_skybox(ctx.h, np.zeros(8, np.uint16).ctypes.data, 0, 4))
+
+
+@pytest.mark.parametrize("variant", ["phong", "pbr_sky", "textured"])
+def test_parity_msaa4(variant):
+    """the base pass with 4 samples per pixel at the Vulkan standard locations, one shading
+    per pixel and primitive, average resolve.  All four depth / triangle-ID planes bit-exact, resolved colour <= 1 LSB."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small_tex" if variant == "textured" else "small")
+    if variant == "pbr_sky":
+        s = sc.to_pbr(s)
+        s["skybox"] = sc.make_skybox(32)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.set_sample_count(4)
+    views = [np.asarray(s["view"]), sc.view_from(s, (0.3, 1.2, 0.4), (6.0, 0.0, 5.0))]   # framing camera; inside the scene (clipped ground)
+    for v in views:
+        o.set_view(v); ctx.set_view(v)
+        ref = o.render_forward_msaa4(ref_shadow)
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+        assert np.array_equal(ctx.readback(capi.REB_SHADOW_F32).view(np.uint32), ref_shadow.view(np.uint32))
+        tri = ctx.readback(capi.REB_MS_TRIID_U32); dep = ctx.readback(capi.REB_MS_DEPTH_F32)
+        for k in range(4):
+            assert np.array_equal(tri[k], ref["tri_id"][k]), f"sample {k}: triangle IDs differ at {np.count_nonzero(tri[k] != ref['tri_id'][k])} pixels"
+            assert np.array_equal(dep[k].view(np.uint32), ref["depth"][k].view(np.uint32)), f"sample {k}: depth not bit-exact"
+        assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"][0])           # the 1-plane targets hold sample 0
+        assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), ref["depth"][0].view(np.uint32))
+        c8 = ctx.readback(capi.REB_COLOR_SRGB8); cf = ctx.readback(capi.REB_COLOR_F32)
+        d8 = np.abs(c8.astype(np.int32) - ref["color_srgb8"].astype(np.int32))
+        assert d8.max() <= 1, f"sRGB8 colour differs by {d8.max()} LSB at {np.count_nonzero(d8 > 1)} channel samples"
+        assert _psnr(cf, ref["color_f32"]) >= 50.0
+        t = ref["tri_id"]
+        assert (~((t[0] == t[1]) & (t[1] == t[2]) & (t[2] == t[3]))).mean() > 0.01          # there are edge pixels to resolve
+    # back to one sample: the ordinary contract again
+    ctx.set_sample_count(1)
+    ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+    one = o.render_forward(ref_shadow)
+    assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), one["tri_id"])
+    assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - one["color_srgb8"].astype(np.int32)).max() <= 1
+
+
+def test_set_sample_count_rejects_unsupported_counts():
+    from renderengine_b200 import capi
+    ctx = capi.Context(64, 64)
+    for n in (0, 2, 8):
+        with pytest.raises(capi.RebError):
+            ctx.set_sample_count(n)
