@@ -164,6 +164,8 @@ def main():
     ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast"])
     ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
                     help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
+    ap.add_argument("--samples", type=int, default=1, choices=[1, 4],
+                    help="samples per pixel of the base pass (4 = Appendix B.12 multisampling; the headline metric is quoted at 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -195,6 +197,8 @@ def main():
     ctx = capi.Context(W, H, device=local_rank, stream=st.cuda_stream, outputs=outputs,
                        rank=rank if tiles else 0, n_ranks=world if tiles else 1, band_h=64)
     ctx.upload_scene(scene)
+    if args.samples != 1:
+        ctx.set_sample_count(args.samples)
     if not tiles and world > 1:
         ctx.set_view(sc.view_for_azimuth(scene, 2 * np.pi * rank / world))   # one camera view per rank
     draws = scene["draws"]
@@ -329,7 +333,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
-            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong"),
+            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong") + (", 4x MSAA base pass" if args.samples == 4 else ""),
                        "parallelism": ("sort-first row bands x%d" % world) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
@@ -349,7 +353,7 @@ def main():
             line["forward_only"] = {"ms_per_frame": fms, "value": T / (fms * 1e3), "unit": UNIT, "algorithmic_bytes": b_forward,
                                     "achieved_gbs": b_forward / (fms * 1e-3) / 1e9, "frac_of_peak": b_forward / (fms * 1e-3) / 1e9 / peak,
                                     "note": "forward pass alone against the cached shadow map (the reference renders the shadow map once, RenderScene.cpp:171-175)"}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.samples == 1:
             keep = {}
             times, cores = cpu_reference_frames(scene, 5, warm=1, keep=keep)
             cms = 1e3 * float(np.mean(times))

@@ -70,6 +70,7 @@ void Renderer::Check(int status, const char* what) const {
     throw std::runtime_error(msg);
 }
 void Renderer::WaitIdle() const { Check(reb_sync(m_ctx), "reb_sync"); }
+void Renderer::SetSampleCount(uint32_t samples) const { Check(reb_set_sample_count(m_ctx, samples), "reb_set_sample_count"); }
 void Renderer::SetShadingModel(uint32_t model) const { Check(reb_set_shading_model(m_ctx, model), "reb_set_shading_model"); }
 void pbr::LightSystem::UploadToGPU(Renderer& renderer) {
     renderer.Check(reb_upload_lights(renderer.GetContext(), m_lights.data(), sizeof(Light), (uint32_t)m_lights.size()), "pbr::LightSystem::UploadToGPU");

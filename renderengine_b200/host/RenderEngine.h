@@ -306,6 +306,7 @@ public:
     void Check(int status, const char* what) const;       // throws std::runtime_error with reb_last_error()
     void WaitIdle() const;                                 // reb_sync (vkDeviceWaitIdle analogue)
     void SetShadingModel(uint32_t model) const;            // REB_SHADING_PHONG (default) / REB_SHADING_PBR (surface_pbr.frag)
+    void SetSampleCount(uint32_t samples) const;           // 1 (default) or 4: PhysicalDevice::GetMsaaSamples analogue (PhysicalDevice.cpp:172-186), Swapchain.cpp:110-123
     void Submit() const;                                   // reb_flush (CommandRingBuffer submit analogue, RenderLoop.cpp:124-132)
     void Readback(reb_output_kind kind, void* host) const; // swapchain image -> host (headless present)
     static std::vector<reb_draw> ToDraws(const std::vector<MeshDrawInfo>& drawCalls);
