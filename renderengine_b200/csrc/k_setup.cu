@@ -439,14 +439,21 @@ __global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constan
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t nClip = min(pc.status[6], pc.clipCap);
-    const uint32_t warpsPerGrid = (gridDim.x * KC_THREADS) >> 5;
-    for (uint32_t i = (blockIdx.x * KC_THREADS + threadIdx.x) >> 5; i < nClip; i += warpsPerGrid) k1_clip_emit<SHADOW>(pc, __ldcg(pc.clipQueue + i), lane);
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) { isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; cursor = 0u; }
-    __syncthreads();
-    if (!isLast) return;
-    __threadfence();
+    if (nClip == 0) {
+        // nothing to clip (the usual frame): no CTA depends on another, so CTA 0 lays the lists out and the rest leave at once
+        if (blockIdx.x != 0 || pc.status[0] == 0u) return;
+        if (threadIdx.x == 0) cursor = 0u;
+        __syncthreads();
+    } else {
+        const uint32_t warpsPerGrid = (gridDim.x * KC_THREADS) >> 5;
+        for (uint32_t i = (blockIdx.x * KC_THREADS + threadIdx.x) >> 5; i < nClip; i += warpsPerGrid) k1_clip_emit<SHADOW>(pc, __ldcg(pc.clipQueue + i), lane);
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) { isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; cursor = 0u; }
+        __syncthreads();
+        if (!isLast) return;
+        __threadfence();
+    }
     const uint32_t nLarge = min(*reinterpret_cast<volatile uint32_t*>(&pc.status[0]), pc.largeCap);
     if (nLarge == 0) return;
     const uint32_t nTiles = pc.tilesX * pc.tilesY;
