@@ -357,34 +357,79 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
 // Swapchain.cpp:110-123,212).  The four sample planes were rasterised by four runs of K1..K3 with shifted vertices; here
 // every pixel shades each DISTINCT primitive among its samples once at the pixel centre (one fragment-shader invocation per
 // pixel and primitive), gives every sample the colour of its primitive (sky / clear colour for uncovered samples) and
-// averages (s0 + s1) + (s2 + s3) in linear float.  Warp = 8 x 4 px block as in the tile stage (texture / shadow-map locality).
+// averages (s0 + s1) + (s2 + s3) in linear float.  Warp = 8 x 4 px block as in the tile stage (texture / shadow-map locality);
+// the block's (pixel, primitive) pairs are compacted through shared memory so the shading rounds run with full lanes.
+__device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v, unsigned lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, v, o); if (lane >= (unsigned)o) v += n; }
+    return v;
+}
+struct ResolveStage {                 // per warp: the block's shading tasks, compacted, and their colours
+    uint32_t task[128];               // bits 0-4 owner lane, 5-6 owner slot, 7 sky; the primitive is triOf[]
+    uint32_t triOf[128];
+    float4 colour[32][4];             // [owner lane][owner slot]
+};
+#ifndef KR_MIN_BLOCKS
+#define KR_MIN_BLOCKS 3
+#endif
 template <bool TEXTURED, bool PBR, bool AFFINE>
-__global__ void __launch_bounds__(KT_THREADS, 2) k_msaa_resolve(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh,
+__global__ void __launch_bounds__(KT_THREADS, KR_MIN_BLOCKS) k_msaa_resolve(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh,
                                                                 const float* __restrict__ msDepth, const uint32_t* __restrict__ msTriId) {
+    __shared__ ResolveStage stage[KT_WARPS];
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    ResolveStage& rs = stage[warp];
     const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
     if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return;
-    const int x = (int)tx * TILE_W + BLK_W * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2) + (int)(lane >> 3);
-    if (x >= (int)pc.W || y >= (int)pc.H) return;
+    const int bx0 = (int)tx * TILE_W + BLK_W * (int)(warp & 3u), by0 = (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2);
+    if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
+    const int x = bx0 + (int)(lane & 7u), y = by0 + (int)(lane >> 3);
+    const bool inb = x < (int)pc.W && y < (int)pc.H;
     const size_t p = (size_t)y * pc.W + x, plane = (size_t)pc.W * pc.H;
-    uint32_t tri[4]; bool sky[4];
+    // 1. this pixel's samples -> distinct (primitive | sky | clear) slots; src[k] = slot whose colour sample k takes
+    uint32_t tri[4]; bool sky[4]; int src[4]; uint32_t nTasks = 0, slotTask[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        tri[k] = __ldg(msTriId + k * plane + p);
-        sky[k] = sh.skyFaces && __ldg(msDepth + k * plane + p) == 1.0f;   // the skybox is drawn last at depth 1.0 under LessOrEqual
+        tri[k] = inb ? __ldg(msTriId + k * plane + p) : TRI_NONE;
+        sky[k] = inb && sh.skyFaces && __ldg(msDepth + k * plane + p) == 1.0f;   // the skybox is drawn last at depth 1.0 under LessOrEqual
         if (sky[k]) tri[k] = TRI_NONE;
+        src[k] = k;
+#pragma unroll
+        for (int j = k - 1; j >= 0; --j)
+            if (sky[j] == sky[k] && tri[j] == tri[k]) src[k] = src[j];
+        slotTask[k] = 0xFFFFFFFFu;
+        if (src[k] == k && (sky[k] || tri[k] != TRI_NONE)) slotTask[k] = nTasks++;   // clear-colour slots need no shading
     }
+    // 2. compact the warp's tasks so the shading rounds run with full lanes (small triangles: most pixels hold 2-3 primitives)
+    const uint32_t incl = warp_incl_scan_u32(nTasks, lane);
+    const uint32_t base = incl - nTasks, total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (slotTask[k] != 0xFFFFFFFFu) {
+            rs.task[base + slotTask[k]] = lane | ((uint32_t)k << 5) | (sky[k] ? 128u : 0u);
+            rs.triOf[base + slotTask[k]] = tri[k];
+        }
+    __syncwarp();
+    // 3. shade: one fragment-shader invocation per pixel and primitive, at the pixel centre
+    for (uint32_t t0 = 0; t0 < total; t0 += 32u) {
+        const uint32_t t = t0 + lane;
+        if (t < total) {
+            const uint32_t task = rs.task[t], owner = task & 31u, slot = (task >> 5) & 3u;
+            const int ox = bx0 + (int)(owner & 7u), oy = by0 + (int)(owner >> 3);
+            float4 c;
+            if (task & 128u) c = sky_pixel(sh, ox, oy);
+            else c = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, ox, oy, rs.triOf[t]) : shade_pixel<TEXTURED, AFFINE>(pc, sh, ox, oy, rs.triOf[t]);
+            rs.colour[owner][slot] = c;
+        }
+    }
+    __syncwarp();
+    if (!inb) return;
+    // 4. resolve: every sample takes its slot's colour; (s0 + s1) + (s2 + s3), then 1/4
     float4 col[4];
-#pragma unroll 1
+#pragma unroll
     for (int k = 0; k < 4; ++k) {
-        int same = -1;
-        for (int j = 0; j < k; ++j)
-            if (same < 0 && sky[j] == sky[k] && tri[j] == tri[k]) same = j;
-        if (same >= 0) { col[k] = col[same]; continue; }
-        if (sky[k]) col[k] = sky_pixel(sh, x, y);
-        else if (tri[k] != TRI_NONE) col[k] = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri[k]) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri[k]);
-        else col[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (RenderScene.cpp:218)
+        const bool shaded = sky[src[k]] || tri[src[k]] != TRI_NONE;
+        col[k] = shaded ? rs.colour[lane][src[k]] : make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (RenderScene.cpp:218)
     }
     float4 out;
     out.x = ((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f;
