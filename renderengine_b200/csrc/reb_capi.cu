@@ -429,11 +429,10 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         mark(3); mark(4);
         launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
     } else {
-        static const int skipBin = getenv("REB_EXPERIMENT_SKIP_BIN") ? atoi(getenv("REB_EXPERIMENT_SKIP_BIN")) : 0;   // timing experiment only
         if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
-        if (ps.nTris && !(skipBin & 1)) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
+        if (ps.nTris) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
         mark(3);
-        if (ps.nTris && !(skipBin & 2)) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
+        if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
         mark(4);
         if (kind == 0) { launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
         else { launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++; }
