@@ -190,7 +190,7 @@ def main():
     scene = build_scene(args)
     T, W, H, S = scene["n_triangles"], scene["width"], scene["height"], scene["shadow_size"]
     tiles = args.mode == "tiles" and world > 1
-    share = args.shadow_share or ("broadcast" if tiles else "replicate")
+    share = args.shadow_share or "replicate"   # measured: re-rendering the shadow map per rank beats render-on-0 + NCCL broadcast in both modes
     bcast = world > 1 and share == "broadcast"
     st = torch.cuda.Stream()
     outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32
