@@ -161,7 +161,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2")
     ap.add_argument("--mode", default="views", choices=["views", "tiles"])
-    ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast"])
+    ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast", "slabs"],
+                    help="N > 1: every rank renders the map (replicate), rank 0 renders + NCCL broadcast, or every rank renders a 1/N row slab + NCCL all-gather")
+    ap.add_argument("--bands", default="contiguous", choices=["contiguous", "interleaved"],
+                    help="--mode tiles: one contiguous row band per rank (lets per-draw culling skip geometry) or interleaved 64-row bands")
     ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
                     help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
     ap.add_argument("--samples", type=int, default=1, choices=[1, 4],
@@ -190,20 +193,28 @@ def main():
     scene = build_scene(args)
     T, W, H, S = scene["n_triangles"], scene["width"], scene["height"], scene["shadow_size"]
     tiles = args.mode == "tiles" and world > 1
-    share = args.shadow_share or "replicate"   # measured: re-rendering the shadow map per rank beats render-on-0 + NCCL broadcast in both modes
+    # measured: re-rendering the shadow map per rank beats render-on-0 + NCCL broadcast in both modes; in tiles mode the
+    # row-slab split (each rank culls the draws outside its slab, one all-gather) beats both
+    share = args.shadow_share or ("slabs" if tiles and parallel.slab_rows(S, world) else "replicate")
+    if share == "slabs" and not (world > 1 and parallel.slab_rows(S, world)):
+        share = "replicate"
     bcast = world > 1 and share == "broadcast"
+    slabs = world > 1 and share == "slabs"
+    band_h = parallel.contiguous_band(H, world) if (tiles and args.bands == "contiguous") else 64
     st = torch.cuda.Stream()
     outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32
     ctx = capi.Context(W, H, device=local_rank, stream=st.cuda_stream, outputs=outputs,
-                       rank=rank if tiles else 0, n_ranks=world if tiles else 1, band_h=64)
+                       rank=rank if tiles else 0, n_ranks=world if tiles else 1, band_h=band_h)
     ctx.upload_scene(scene)
+    if slabs:
+        ctx.set_shadow_partition(rank, world, parallel.slab_rows(S, world))
     if args.samples != 1:
         ctx.set_sample_count(args.samples)
     if not tiles and world > 1:
         ctx.set_view(sc.view_for_azimuth(scene, 2 * np.pi * rank / world))   # one camera view per rank
     draws = scene["draws"]
     shadow_t = None
-    if S and bcast:
+    if S and (bcast or slabs):
         ptr, _ = ctx.output_ptr(capi.REB_SHADOW_F32)
         shadow_t = torch.as_tensor(_DevArray(ptr, (S, S), "<f4"), device=f"cuda:{local_rank}")
 
@@ -211,7 +222,12 @@ def main():
 
     def step():
         if S:
-            if not bcast:
+            if slabs:
+                ctx.render_shadow(draws)
+                ctx.flush()                                      # the recorded depth pass must be on the stream before the exchange
+                parallel.allgather_shadow_slabs(shadow_t)        # NCCL over NVLink; ordered on the current stream
+                ctx.shadow_mark_valid()
+            elif not bcast:
                 ctx.render_shadow(draws)
             else:
                 if rank == 0:
@@ -334,7 +350,7 @@ def main():
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
             "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong") + (", 4x MSAA base pass" if args.samples == 4 else ""),
-                       "parallelism": ("sort-first row bands x%d" % world) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
+                       "parallelism": ("sort-first row bands x%d (%s, band_h %d, per-draw culling), shadow map: %s" % (world, args.bands, band_h, share)) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
                           "frac_of_peak": frame_bytes / (ms * 1e-3) / 1e9 / peak / world, "peak_gbs": peak, "peak_source": peak_src},

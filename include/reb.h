@@ -140,6 +140,12 @@ int reb_readback_async(reb_ctx* ctx, reb_output_kind kind, void* host);
 
 /* multi-GPU helpers */
 int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH);
+/* Row split of the shadow pass: this rank rasterises only the shadow-map rows ((y / bandH) % nRanks == rank) (bandH a
+ * multiple of 32) and skips draws that cannot touch them; the other rows keep the clear value until the caller fills them
+ * (e.g. an in-place NCCL all-gather of the slabs on the buffer reb_get_output(REB_SHADOW_F32) returns, after reb_flush)
+ * and calls reb_shadow_mark_valid.  With reb_set_partition (or reb_params.rank / n_ranks) the forward pass likewise skips
+ * draws whose projected bounds touch none of this rank's rows. */
+int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH);
 /* marks the shadow map as valid after its storage (reb_get_output REB_SHADOW_F32) was filled externally,
  * e.g. by an NCCL broadcast from the rank that rendered it */
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);

@@ -15,7 +15,7 @@ REB_MS_DEPTH_F32, REB_MS_TRIID_U32 = 5, 6
 SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
-    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
@@ -69,6 +69,7 @@ def load():
     lib.reb_set_shading_model.argtypes = [vp, u32]
     lib.reb_set_skybox.argtypes = [vp, vp, u32, u32]
     lib.reb_set_sample_count.argtypes = [vp, u32]
+    lib.reb_set_shadow_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
@@ -238,6 +239,10 @@ class Context:
 
     def set_partition(self, rank, n_ranks, band_h=64):
         self._ck(self.lib.reb_set_partition(self.h, rank, n_ranks, band_h))
+
+    def set_shadow_partition(self, rank, n_ranks, band_h):
+        """Row split of the shadow pass (slabs of band_h rows, band_h % 32 == 0); fill the other rows, then shadow_mark_valid()."""
+        self._ck(self.lib.reb_set_shadow_partition(self.h, rank, n_ranks, band_h))
 
     def shadow_mark_valid(self):
         self._ck(self.lib.reb_shadow_mark_valid(self.h, self.shadow_id))

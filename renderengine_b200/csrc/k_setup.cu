@@ -297,20 +297,26 @@ __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint3
 
 // Cache slots of the three corners of triangle `tri` (flatSlots: the draw list's index stream re-based into
 // cache-slot space in submission order, built when the draw list changes; de-indexed mode needs no table).
+// CULL (sort-first split): triangles of a draw none of whose rows belong to this rank come back as the sentinel and are
+// gathered as an all-zero (degenerate, hence culled) triangle; their cache slots were not written by K0 either.
+constexpr uint32_t SLOT_CULLED = 0xFFFFFFFFu;
+template <bool CULL>
 __device__ __forceinline__ uint3 k1_load_slots(const PassConst& pc, uint32_t tri) {
     if (tri >= pc.nTris) return make_uint3(0u, 0u, 0u);
+    if (CULL && __ldg(pc.drawVisible + find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri)) == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
     if (pc.deindexed) return make_uint3(3u * tri, 3u * tri + 1u, 3u * tri + 2u);
     const uint32_t* f = pc.flatSlots + 3ull * tri;
     return make_uint3(__ldg(f), __ldg(f + 1), __ldg(f + 2));
 }
+template <bool CULL>
 __device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uint3 s, uint4 q[3]) {
-    if (tri >= pc.nTris) { q[0] = q[1] = q[2] = make_uint4(0, 0, 0, 0); return; }
+    if (tri >= pc.nTris || (CULL && s.x == SLOT_CULLED)) { q[0] = q[1] = q[2] = make_uint4(0, 0, 0, 0); return; }
     const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
     q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
 }
 
 // Row stage: `cnt` (<= 32) pending rows, one per lane -> coverage masks -> pixel queue entries.
-template <bool SHADOW>
+template <bool SHADOW, bool CULL = false>
 __device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_t rowHead, uint32_t cnt, uint32_t& pixTail, unsigned lane) {
     bool active = lane < cnt;
     uint32_t slot = 0, j = 0, whb = 0;
@@ -318,7 +324,7 @@ __device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_
         const uint32_t e = ws.rowq[(rowHead + lane) & (K1_ROWQ - 1)];
         slot = e & 0xFFu; j = e >> 8;
         whb = ws.whb[slot];
-        if (!SHADOW && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
+        if ((!SHADOW || CULL) && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;   // shadow slabs only in the split build
     }
     const uint32_t w = active ? (whb & 0xFFu) : 0u;
     const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
@@ -365,7 +371,7 @@ __device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws,
 #ifndef K1_MIN_BLOCKS
 #define K1_MIN_BLOCKS 6
 #endif
-template <bool SHADOW, bool SHIFT>
+template <bool SHADOW, bool SHIFT, bool CULL>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(const __grid_constant__ PassConst pc) {
     __shared__ K1Shared sm;
     pdl_enter();
@@ -380,14 +386,14 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     uint4 q[3];
     {
         const uint32_t tri = batch * 32u + lane;
-        k1_gather(pc, tri, k1_load_slots(pc, tri), q);
+        k1_gather<CULL>(pc, tri, k1_load_slots<CULL>(pc, tri), q);
     }
-    uint3 ns = k1_load_slots(pc, (batch + totalWarps) * 32u + lane);   // slot stream runs two batches ahead of the raster stages
+    uint3 ns = k1_load_slots<CULL>(pc, (batch + totalWarps) * 32u + lane);   // slot stream runs two batches ahead of the raster stages
     uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
     while (batch < nBatches) {
         const uint32_t nbatch = batch + totalWarps;
         const uint32_t tri = batch * 32u + lane, ntri = nbatch * 32u + lane;
-        const uint3 nns = k1_load_slots(pc, (nbatch + totalWarps) * 32u + lane);   // in flight for a whole iteration
+        const uint3 nns = k1_load_slots<CULL>(pc, (nbatch + totalWarps) * 32u + lane);   // in flight for a whole iteration
 
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
@@ -403,13 +409,13 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         if (t.isSmall) k1_store_small(ws, t, tri, (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1), rowTail + hIncl - h);
         ringPos += __popc(smallMask);
         rowTail += __shfl_sync(0xFFFFFFFFu, hIncl, 31);
-        k1_gather(pc, ntri, ns, q);                                 // in flight during the raster stages
+        k1_gather<CULL>(pc, ntri, ns, q);                            // in flight during the raster stages
         ns = nns;
         __syncwarp();
 
         // ---- 2./3. rows -> samples -> resolve ----------------------------------------------------------------
         while (rowTail - rowHead >= 32u) {
-            k1_rows<SHADOW>(pc, ws, rowHead, 32u, pixTail, lane);
+            k1_rows<SHADOW, CULL>(pc, ws, rowHead, 32u, pixTail, lane);
             rowHead += 32u;
             while (pixTail - pixHead >= 32u) { k1_pixels<SHADOW>(pc, ws, pixHead, 32u, lane); pixHead += 32u; }
         }
@@ -419,7 +425,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         batch = nbatch;
     }
     if (rowTail != rowHead) {   // drain the rows left over from sparse batches
-        k1_rows<SHADOW>(pc, ws, rowHead, rowTail - rowHead, pixTail, lane);
+        k1_rows<SHADOW, CULL>(pc, ws, rowHead, rowTail - rowHead, pixTail, lane);
         while (pixTail != pixHead) { const uint32_t c = min(32u, pixTail - pixHead); k1_pixels<SHADOW>(pc, ws, pixHead, c, lane); pixHead += c; }
     }
 
@@ -531,9 +537,11 @@ __global__ void k_split_vertices(const float4* __restrict__ aos, float4* __restr
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
     if (pc.nTris == 0) return;
     using Kern = void (*)(PassConst);
-    static const Kern kern[3] = {k_setup_raster<false, false>, k_setup_raster<true, false>, k_setup_raster<false, true>};
-    const int v = shadow ? 1 : ((pc.shiftX | pc.shiftY) ? 2 : 0);   // 2: a sample pass of a multisampled frame (Appendix B.12)
-    static int perSM[3] = {0, 0, 0};
+    static const Kern kern[6] = {k_setup_raster<false, false, false>, k_setup_raster<true, false, false>, k_setup_raster<false, true, false>,
+                                 k_setup_raster<false, false, true>,  k_setup_raster<true, false, true>,  k_setup_raster<false, true, true>};
+    // +1: shadow pass; 2: a sample pass of a multisampled frame (Appendix B.12); +3: per-draw culling for the sort-first split
+    const int v = (shadow ? 1 : ((pc.shiftX | pc.shiftY) ? 2 : 0)) + (pc.drawVisible ? 3 : 0);
+    static int perSM[6] = {0, 0, 0, 0, 0, 0};
     if (!perSM[v]) {
         int n = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], K1_THREADS, 0);

@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constan
         rx += stepX; ry += stepY;
         if (rx >= pc.tilesX) { rx -= pc.tilesX; ++ry; }
         if (bx0 >= (int)pc.W || by0 >= (int)pc.H) continue;   // warp-uniform
+        if (pc.nRanks > 1 && !row_owned((uint32_t)by0, pc.rank, pc.nRanks, pc.bandH)) continue;   // shadow slabs (bandH % 32 == 0), warp-uniform
         constexpr int NT = (BLK_ROWS * SHADOW_SUB + TILE_H - 1) / TILE_H;   // 32 x 8 tiles a warp's block spans vertically
         uint32_t begin[NT], end[NT];
 #pragma unroll

@@ -12,6 +12,7 @@
 // coalesced.  De-indexed mode (draws referencing sparse / shared vertex ranges): slot = 3*tri + corner.
 #include "reb_device.cuh"
 #include "reb_kernels.h"
+#include <algorithm>
 
 namespace reb {
 
@@ -22,7 +23,7 @@ constexpr int K0_PER_THREAD = K0_PER_THREAD_D;   // cache slots per thread: four
 
 struct K0In { float4 p, n; uint32_t node; bool valid; };
 
-template <bool SHADOW>
+template <bool SHADOW, bool CULL = false>
 __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     K0In in;
     in.valid = slot < pc.cacheSize;
@@ -37,6 +38,7 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     } else {
         v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
     }
+    if (CULL && __ldg(pc.drawVisible + d) == 0u) { in.valid = false; return in; }   // no row of this draw belongs to this rank
     in.node = __ldg(&pc.draws[d].node);
     in.p = __ldg(pc.pos4 + v);
     if (!SHADOW) in.n = __ldg(pc.nrm4 + v);
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(256) k_vertex_both(const __grid_constant__ Pas
     }
 }
 
-template <bool SHADOW>
+template <bool SHADOW, bool CULL>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
     pdl_enter();
     const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassCons
     if (SHADOW) k0_clear_shadow(pc);
     K0In in[K0_PER_THREAD];
 #pragma unroll
-    for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW>(pc, base + 256u * k);
+    for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW, CULL>(pc, base + 256u * k);
 #pragma unroll
     for (int k = 0; k < K0_PER_THREAD; ++k) k0_transform_store<SHADOW>(pc, base + 256u * k, in[k]);
 }
@@ -160,8 +162,82 @@ void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint3
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) {
     if (pc.cacheSize == 0) return;
     const uint32_t grid = (pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
-    if (shadow) launch_k(k_vertex<true>, dim3(grid), dim3(256), st, pdl, pc);
-    else launch_k(k_vertex<false>, dim3(grid), dim3(256), st, pdl, pc);
+    using Kern = void (*)(PassConst);
+    static const Kern kern[4] = {k_vertex<false, false>, k_vertex<true, false>, k_vertex<false, true>, k_vertex<true, true>};
+    launch_k(kern[(shadow ? 1 : 0) | (pc.drawVisible ? 2 : 0)], dim3(grid), dim3(256), st, pdl, pc);
+}
+
+// ---- per-draw culling for the sort-first split ("each GPU runs K1 on all triangles (or culls to its region)") ------
+// Object-space bounds of every draw, reduced once when a draw list changes.  Floats are kept in an order-preserving
+// unsigned encoding so the reduction is atomicMin / atomicMax: bounds[6 d + 0..2] = min xyz, [3..5] = max xyz.
+__device__ __forceinline__ uint32_t enc_ordered(float f) { const uint32_t b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+__device__ __forceinline__ float dec_ordered(uint32_t e) { return __uint_as_float((e & 0x80000000u) ? (e & 0x7FFFFFFFu) : ~e); }
+__global__ void __launch_bounds__(256) k_draw_bounds(const uint32_t* __restrict__ indices, const float4* __restrict__ pos4, const DrawDev* __restrict__ draws,
+                                                     uint32_t nDraws, uint32_t* __restrict__ bounds) {
+    const uint32_t d = blockIdx.y;
+    if (d >= nDraws) return;
+    const uint32_t off = draws[d].indexOffset, n = 3u * (draws[d + 1].firstTri - draws[d].firstTri);
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 p = __ldg(pos4 + __ldg(indices + off + i));
+        const uint32_t e[3] = {enc_ordered(p.x), enc_ordered(p.y), enc_ordered(p.z)};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { lo[c] = min(lo[c], e[c]); hi[c] = max(hi[c], e[c]); }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        lo[c] = __reduce_min_sync(0xFFFFFFFFu, lo[c]); hi[c] = __reduce_max_sync(0xFFFFFFFFu, hi[c]);
+        if ((threadIdx.x & 31u) == 0 && lo[c] <= hi[c]) { atomicMin(&bounds[6 * d + c], lo[c]); atomicMax(&bounds[6 * d + 3 + c], hi[c]); }
+    }
+}
+void launch_draw_bounds(const uint32_t* indices, const float4* pos4, const DrawDev* draws, uint32_t nDraws, uint32_t* bounds, cudaStream_t st) {
+    for (uint32_t d0 = 0; d0 < nDraws; d0 += 65535u) {
+        const uint32_t nd = std::min(65535u, nDraws - d0);
+        k_draw_bounds<<<dim3(32, nd), 256, 0, st>>>(indices, pos4, draws + d0, nd, bounds + 6 * (size_t)d0);
+    }
+}
+// Once per pass and frame, ahead of K0: a draw is kept iff the rows its transformed bounding box can touch (one pixel of
+// slack for rounding and the sample shifts) include a row band of this rank, and it is not off-screen sideways.  The eight
+// corners go through the pass's own vertex stage; a corner at or behind the eye plane keeps the draw (the clipper decides).
+template <bool SHADOW>
+__global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ visible) {
+    const uint32_t d = blockIdx.x * 128u + threadIdx.x;
+    if (d >= pc.nDraws) return;
+    const uint32_t* b = bounds + 6 * (size_t)d;
+    if (b[0] > b[3]) { visible[d] = 0u; return; }   // draw without primitives
+    const float mn[3] = {dec_ordered(b[0]), dec_ordered(b[1]), dec_ordered(b[2])}, mx[3] = {dec_ordered(b[3]), dec_ordered(b[4]), dec_ordered(b[5])};
+    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * pc.draws[d].node;
+    float T[16];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float4 q = Tq[k]; T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
+    const float hw = 0.5f * (float)pc.W, hh = 0.5f * (float)pc.H;
+    float x0 = 3.0e38f, x1 = -3.0e38f, y0 = 3.0e38f, y1 = -3.0e38f;
+    bool keep = false;
+    for (int c = 0; c < 8; ++c) {
+        V3 world;
+        const float4 q = vertex_stage<!SHADOW>(pc.PV, T, (c & 1) ? mx[0] : mn[0], (c & 2) ? mx[1] : mn[1], (c & 4) ? mx[2] : mn[2], &world);
+        if (!(q.w > 0.0f)) { keep = true; continue; }       // also catches NaN
+        const float xf = hw * (q.x / q.w) + hw, yf = hh * (q.y / q.w) + hh;
+        if (!(fabsf(xf) < 1.0e30f) || !(fabsf(yf) < 1.0e30f)) { keep = true; continue; }
+        x0 = fminf(x0, xf); x1 = fmaxf(x1, xf); y0 = fminf(y0, yf); y1 = fmaxf(y1, yf);
+    }
+    uint32_t v = 1u;
+    if (!keep) {
+        if (x1 < -1.0f || x0 > (float)pc.W + 1.0f || y1 < -1.0f || y0 > (float)pc.H + 1.0f) v = 0u;
+        else if (pc.nRanks > 1) {
+            const uint32_t r0 = (uint32_t)fmaxf(y0 - 1.0f, 0.0f), r1 = (uint32_t)fminf(fmaxf(y1 + 1.0f, 0.0f), (float)(pc.H - 1u));
+            const uint32_t b0 = r0 / pc.bandH, b1 = r1 / pc.bandH;
+            v = 0u;
+            if (b1 - b0 + 1u >= pc.nRanks) v = 1u;
+            else for (uint32_t q = b0; q <= b1; ++q) if (q % pc.nRanks == pc.rank) v = 1u;
+        }
+    }
+    visible[d] = v;
+}
+void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, cudaStream_t st) {
+    if (pc.nDraws == 0) return;
+    if (shadow) k_cull_draws<true><<<(pc.nDraws + 127u) / 128u, 128, 0, st>>>(pc, bounds, visible);
+    else k_cull_draws<false><<<(pc.nDraws + 127u) / 128u, 128, 0, st>>>(pc, bounds, visible);
 }
 
 void launch_vertex_both(const PassConst& ps, const PassConst& pf, cudaStream_t st) {

@@ -27,6 +27,7 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward
     uint32_t* blockDraw = nullptr; size_t blockDrawCap = 0; uint32_t triBlocks = 0;   // [triBlocks] by triangle, then by cache slot
     uint32_t* flatSlots = nullptr; size_t flatCap = 0;   // 3 cache slots per triangle, submission order (indexed mode)
     uint32_t cacheSize = 0, deindexed = 0;
+    uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
     bool pending = false;        // enqueued since the last overflow check
 };
@@ -39,6 +40,7 @@ struct reb_ctx {
     std::string err;
     uint32_t W = 0, H = 0, outputs = 0, maxDesc = 8192;
     uint32_t rank = 0, nRanks = 1, bandH = 64;
+    uint32_t sRank = 0, sNRanks = 1, sBandH = 64;   // row split of the shadow map (reb_set_shadow_partition)
     // geometry (SoA streams)
     float4* pos4 = nullptr; float4* nrm4 = nullptr; uint32_t* indices = nullptr; uint64_t nVerts = 0, nIdx = 0;
     float* transforms = nullptr; float* nmats = nullptr; uint32_t nNodes = 0;
@@ -281,6 +283,18 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         ps.triBlocks = tb;
     }
     ps.nDraws = n; ps.nTris = (uint32_t)tri;
+    if (n) {   // object-space bounds per draw, for the per-rank draw culling of the sort-first split
+        if (n > ps.cullCap) {
+            int rc;
+            if ((rc = dev_alloc(ctx, &ps.drawBounds, (size_t)n * 6)) || (rc = dev_alloc(ctx, &ps.drawVisible, (size_t)n))) return rc;
+            ps.cullCap = n;
+        }
+        std::vector<uint32_t> init((size_t)n * 6);
+        for (uint32_t i = 0; i < n; ++i) for (int c = 0; c < 6; ++c) init[6 * (size_t)i + c] = c < 3 ? 0xFFFFFFFFu : 0u;
+        CU(cudaMemcpyAsync(ps.drawBounds, init.data(), init.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        launch_draw_bounds(ctx->indices, ctx->pos4, ps.dDraws, n, ps.drawBounds, ctx->stream); ctx->launches++;
+        CU(cudaStreamSynchronize(ctx->stream));   // init is a stack-lifetime staging buffer
+    }
     if (!ps.deindexed && tri) {   // index stream re-based into cache-slot space
         if (3 * tri > ps.flatCap) {
             int rc = dev_alloc(ctx, &ps.flatSlots, (size_t)(3 * tri));
@@ -315,7 +329,9 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.status = ctx->dStatus + 8 * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
     if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
-    else { pc.rank = 0; pc.nRanks = 1; pc.bandH = 64; }
+    else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; }
+    static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
+    pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
 }
 
 // Everything a pass needs before its kernels can be enqueued: queue capacities, texture table, kernel parameters.
@@ -380,6 +396,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
     }
     mark(1);
+    if (ps.nTris && pc.drawVisible) { launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ctx->stream); ctx->launches++; }
     if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
     ShadeConst sh;
@@ -463,6 +480,7 @@ int submit_forward(reb_ctx* ctx) {
     const PassState &s0 = ctx->pass[0], &s1 = ctx->pass[1];
     const bool fuse = ctx->shadowDeferred && s0.nTris && s1.nTris && s0.deindexed == s1.deindexed && s0.cacheSize == s1.cacheSize &&
                       s0.draws.size() == s1.draws.size() && std::memcmp(s0.draws.data(), s1.draws.data(), s0.draws.size() * sizeof(reb_draw)) == 0 &&
+                      ctx->nRanks <= 1 && ctx->sNRanks <= 1 &&   // a split pass culls draws per rank: its K0 is not the other pass's
                       !std::getenv("REB_NO_FUSED_VERTEX");
     if (!fuse) {
         if ((rc = flush_deferred(ctx))) return rc;

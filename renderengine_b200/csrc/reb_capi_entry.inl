@@ -57,7 +57,8 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
-                    ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots};
+                    ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots,
+                    ctx->pass[0].drawBounds, ctx->pass[1].drawBounds, ctx->pass[0].drawVisible, ctx->pass[1].drawVisible};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
@@ -396,6 +397,15 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
     CU(cudaStreamSynchronize(ctx->stream));
     ctx->rank = rank; ctx->nRanks = nRanks; ctx->bandH = bandH;
     return alloc_targets(ctx);   // re-clear: pixels outside this rank's bands keep the clear values
+}
+
+int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH) {
+    CHECK_CTX();
+    if (nRanks == 0 || rank >= nRanks || bandH == 0 || bandH % 32u) return fail(ctx, REB_E_INVALID, "reb_set_shadow_partition: need rank < nRanks and bandH a multiple of 32");
+    CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
+    ctx->sRank = rank; ctx->sNRanks = nRanks; ctx->sBandH = bandH;
+    return REB_OK;
 }
 
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId) {

@@ -84,6 +84,8 @@ struct PassConst {
     // Appendix B.12 (multisampling): this raster pass samples at pixel centre - shift / 256, implemented as an exact integer
     // shift of the snapped vertices (edge functions and depth are translation-invariant).  0 for 1-sample passes.
     int32_t shiftX, shiftY;
+    // per-draw visibility for this rank's rows (sort-first split): written by k_cull_draws before K0, NULL = no culling
+    const uint32_t* drawVisible;
 };
 
 // status[2] bits

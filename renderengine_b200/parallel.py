@@ -31,6 +31,34 @@ def broadcast_shadow(shadow_tensor, src=0):
     return shadow_tensor
 
 
+def slab_rows(size, world):
+    """Rows per rank of a contiguous, equal split of a `size`-row map into `world` slabs whose height is a multiple of 32
+    (reb_set_shadow_partition's granularity); None when the map does not divide that way."""
+    if world <= 0 or size % (32 * world):
+        return None
+    return size // world
+
+
+def allgather_shadow_slabs(shadow_tensor):
+    """Shadow pass split by rows: every rank rendered slab `rank` of the map (reb_set_shadow_partition with band_h =
+    slab_rows(S, world)); one in-place all-gather (4*S*S/N bytes sent per rank) completes the map on every rank."""
+    import torch.distributed as dist
+    if not (dist.is_initialized() and dist.get_world_size() > 1):
+        return shadow_tensor
+    world, rank = dist.get_world_size(), dist.get_rank()
+    rows = slab_rows(shadow_tensor.shape[0], world)
+    if rows is None:
+        raise ValueError("shadow map rows must divide into equal slabs of a multiple of 32 rows")
+    dist.all_gather_into_tensor(shadow_tensor, shadow_tensor[rank * rows:(rank + 1) * rows])
+    return shadow_tensor
+
+
+def contiguous_band(height, world):
+    """band_h that gives every rank ONE contiguous band of the frame (multiple of 8): with per-draw culling this is what
+    lets a rank skip most of the geometry."""
+    return ((height + world - 1) // world + 7) // 8 * 8
+
+
 def gather_bands(local_frame, band_h=64):
     """Sort-first final exchange: all-gather every rank's frame (clear values outside its bands) and compose the
     full image from the owned rows.  local_frame: torch tensor [H, W, ...]; returns the composed tensor on every rank."""

@@ -494,3 +494,53 @@ def test_set_sample_count_rejects_unsupported_counts():
     for n in (0, 2, 8):
         with pytest.raises(capi.RebError):
             ctx.set_sample_count(n)
+
+
+def test_shadow_pass_row_slabs_compose_the_full_map():
+    """reb_set_shadow_partition: every rank rasterises only its slab of shadow-map rows (draws outside it are culled per
+    rank); the slabs put together are the oracle's map bit for bit, the rows a rank does not own keep the clear value."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("small")
+    S, world = s["shadow_size"], 4
+    rows = parallel.slab_rows(S, world)
+    ref = orc.Oracle(s).render_shadow()
+    merged = np.zeros_like(ref)
+    for rank in range(world):
+        ctx = capi.Context(s["width"], s["height"])
+        ctx.upload_scene(s)
+        ctx.set_shadow_partition(rank, world, rows)
+        ctx.render_shadow(s["draws"]); ctx.sync()
+        got = ctx.readback(capi.REB_SHADOW_F32)
+        own = slice(rank * rows, (rank + 1) * rows)
+        assert np.array_equal(got[own].view(np.uint32), ref[own].view(np.uint32))
+        other = np.ones(S, bool); other[own] = False
+        assert (got[other] == 1.0).all()
+        merged[own] = got[own]
+        assert ctx.counters()[0] == 0
+    assert np.array_equal(merged.view(np.uint32), ref.view(np.uint32)) and (ref < 1.0).mean() > 0.05
+
+
+@pytest.mark.parametrize("inside", [False, True])
+def test_sort_first_contiguous_bands_with_draw_culling(inside):
+    """One contiguous band per rank: draws whose projected bounds miss the band are skipped by K0 / K1 (k_cull_draws); the
+    result is still the oracle's band bit for bit — also with the camera inside the scene, where bounding boxes cross the
+    eye plane (kept, the clipper decides)."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("small")
+    if inside:
+        s = dict(s); s["view"] = sc.view_from(s, (0.3, 1.2, 0.4), (6.0, 0.0, 5.0))
+    world = 4
+    band = parallel.contiguous_band(s["height"], world)
+    full = orc.Oracle(s)
+    ref_shadow = full.render_shadow()
+    whole = full.render_forward(ref_shadow)
+    merged = np.full_like(whole["tri_id"], 0xFFFFFFFF)
+    for rank in range(world):
+        ref = orc.Oracle(s, rank=rank, n_ranks=world, band_h=band).render_forward(ref_shadow)
+        gpu = render_gpu(s, rank=rank, n_ranks=world, band_h=band)
+        check_parity(s, gpu, ref_shadow, ref)
+        own = ((np.arange(s["height"]) // band) % world == rank)
+        merged[own] = gpu["tri_id"][own]
+    assert np.array_equal(merged, whole["tri_id"])

@@ -81,3 +81,34 @@ def test_two_rank_sort_first_and_view_parallel():
         for v, h in r[4]:
             o.set_view(sc.view_for_azimuth(s, 2 * np.pi * v / 5))
             assert h == int(o.render_forward(ref_shadow)["tri_id"].astype(np.uint64).sum())
+
+
+def _slab_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        S = 128
+        rows = parallel.slab_rows(S, world)
+        full = torch.arange(S * S, dtype=torch.float32).reshape(S, S)
+        mine = torch.ones((S, S), dtype=torch.float32)                      # rows outside the slab hold the clear value
+        mine[rank * rows:(rank + 1) * rows] = full[rank * rows:(rank + 1) * rows]
+        parallel.allgather_shadow_slabs(mine)
+        q.put((rank, bool(torch.equal(mine, full))))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_shadow_slab_allgather():
+    """Shadow pass split by rows (reb_set_shadow_partition): the in-place all-gather of the slabs completes the map."""
+    assert parallel.slab_rows(2048, 8) == 256 and parallel.slab_rows(512, 4) == 128 and parallel.slab_rows(2048, 3) is None
+    assert parallel.contiguous_band(4320, 8) == 544 and parallel.contiguous_band(360, 4) == 96 and parallel.contiguous_band(1080, 1) == 1080
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_slab_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]
