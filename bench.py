@@ -163,8 +163,9 @@ def main():
     ap.add_argument("--mode", default="views", choices=["views", "tiles"])
     ap.add_argument("--shadow-share", default=None, choices=["replicate", "broadcast", "slabs"],
                     help="N > 1: every rank renders the map (replicate), rank 0 renders + NCCL broadcast, or every rank renders a 1/N row slab + NCCL all-gather")
-    ap.add_argument("--bands", default="contiguous", choices=["contiguous", "interleaved"],
-                    help="--mode tiles: one contiguous row band per rank (lets per-draw culling skip geometry) or interleaved 64-row bands")
+    ap.add_argument("--bands-per-rank", type=int, default=2,
+                    help="--mode tiles: row bands per rank, interleaved (1 = one contiguous band: least geometry per rank after per-draw "
+                         "culling but unbalanced; 0 = 64-row bands: balanced, nothing to cull)")
     ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
                     help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
     ap.add_argument("--samples", type=int, default=1, choices=[1, 4],
@@ -200,7 +201,7 @@ def main():
         share = "replicate"
     bcast = world > 1 and share == "broadcast"
     slabs = world > 1 and share == "slabs"
-    band_h = parallel.contiguous_band(H, world) if (tiles and args.bands == "contiguous") else 64
+    band_h = parallel.contiguous_band(H, world * args.bands_per_rank) if (tiles and args.bands_per_rank > 0) else 64
     st = torch.cuda.Stream()
     outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32
     ctx = capi.Context(W, H, device=local_rank, stream=st.cuda_stream, outputs=outputs,
@@ -350,7 +351,7 @@ def main():
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
             "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong") + (", 4x MSAA base pass" if args.samples == 4 else ""),
-                       "parallelism": ("sort-first row bands x%d (%s, band_h %d, per-draw culling), shadow map: %s" % (world, args.bands, band_h, share)) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
+                       "parallelism": ("sort-first row bands x%d (band_h %d, per-draw culling), shadow map: %s" % (world, band_h, share)) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
                           "frac_of_peak": frame_bytes / (ms * 1e-3) / 1e9 / peak / world, "peak_gbs": peak, "peak_source": peak_src},

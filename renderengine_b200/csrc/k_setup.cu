@@ -384,9 +384,12 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     // L2 atomic unit: ~10 cycles per same-address atomic-with-return chip-wide, measured as the top stall)
     uint32_t batch = blockIdx.x * K1_WARPS + warp;
     uint4 q[3];
+    bool curCulled = false;   // CULL: every triangle of the current batch belongs to a culled draw (warp-uniform)
     {
         const uint32_t tri = batch * 32u + lane;
-        k1_gather<CULL>(pc, tri, k1_load_slots<CULL>(pc, tri), q);
+        const uint3 s0 = k1_load_slots<CULL>(pc, tri);
+        if (CULL) curCulled = __all_sync(0xFFFFFFFFu, s0.x == SLOT_CULLED || tri >= pc.nTris);
+        k1_gather<CULL>(pc, tri, s0, q);
     }
     uint3 ns = k1_load_slots<CULL>(pc, (batch + totalWarps) * 32u + lane);   // slot stream runs two batches ahead of the raster stages
     uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
@@ -394,6 +397,12 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         const uint32_t nbatch = batch + totalWarps;
         const uint32_t tri = batch * 32u + lane, ntri = nbatch * 32u + lane;
         const uint3 nns = k1_load_slots<CULL>(pc, (nbatch + totalWarps) * 32u + lane);   // in flight for a whole iteration
+        if (CULL && curCulled) {   // nothing of this batch is ours: only advance the software pipeline
+            curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
+            k1_gather<CULL>(pc, ntri, ns, q);
+            ns = nns; batch = nbatch;
+            continue;
+        }
 
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
@@ -409,6 +418,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         if (t.isSmall) k1_store_small(ws, t, tri, (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1), rowTail + hIncl - h);
         ringPos += __popc(smallMask);
         rowTail += __shfl_sync(0xFFFFFFFFu, hIncl, 31);
+        if (CULL) curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
         k1_gather<CULL>(pc, ntri, ns, q);                            // in flight during the raster stages
         ns = nns;
         __syncwarp();

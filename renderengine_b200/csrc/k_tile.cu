@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constan
 #endif
 __device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, uint32_t tx, uint32_t ty, uint32_t b, int lx, int ly) {
     const int x = (int)tx * TILE_W + BLK_W * (int)(b & 3u) + lx, y = (int)ty * TILE_H + BLK_ROWS * (int)(b >> 2) + ly;
-    if (x >= (int)pc.W || y >= (int)pc.H || !row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return VIS_CLEAR;
+    if (x >= (int)pc.W || y >= (int)pc.H) return VIS_CLEAR;   // callers visit owned tile rows only
     return __ldcg(pc.vis + (size_t)y * pc.W + x);
 }
 
@@ -311,7 +311,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
 #ifndef KT_PBR_MIN_BLOCKS
 #define KT_PBR_MIN_BLOCKS 3
 #endif
-template <bool TEXTURED, bool PBR, bool AFFINE>
+template <bool TEXTURED, bool PBR, bool AFFINE, bool PART>
 __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
     __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
@@ -319,7 +319,6 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
     const int lx = (int)(lane & 7u), ly = (int)(lane >> 3);
-    const uint32_t nTiles = pc.tilesX * pc.tilesY;
     const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
 #if KT_MODE == 0
     // one CTA per tile (hardware CTA scheduling), warp = block
@@ -333,23 +332,49 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
     kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
                        stage[warp], lane);
 #elif KT_MODE == 1
-    // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
-    uint32_t tile = blockIdx.x;
-    const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;   // the only divisions: once per CTA
-    uint32_t tyN = tile / pc.tilesX, txN = tile - tyN * pc.tilesX;
-    unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, txN, tyN, warp, lx, ly) : VIS_CLEAR;
-    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
-    for (; tile < nTiles; tile += gridDim.x) {
-        const unsigned long long key = keyNext;
-        const uint32_t tx = txN, ty = tyN;
-        txN += stepX; tyN += stepY;
-        if (txN >= pc.tilesX) { txN -= pc.tilesX; ++tyN; }
-        if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
-        if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) continue;
-        uint32_t begin, end;
-        kt_tile_list(pc, tile, nLarge, begin, end);
-        kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
-                           end, stage[warp], lane);
+    if (!PART) {
+        // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
+        const uint32_t nTiles = pc.tilesX * pc.tilesY;
+        uint32_t tile = blockIdx.x;
+        const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;   // the only divisions: once per CTA
+        uint32_t tyN = tile / pc.tilesX, txN = tile - tyN * pc.tilesX;
+        unsigned long long keyNext = tile < nTiles ? kt_load_key(pc, txN, tyN, warp, lx, ly) : VIS_CLEAR;
+        if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
+        for (; tile < nTiles; tile += gridDim.x) {
+            const unsigned long long key = keyNext;
+            const uint32_t tx = txN, ty = tyN;
+            txN += stepX; tyN += stepY;
+            if (txN >= pc.tilesX) { txN -= pc.tilesX; ++tyN; }
+            if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
+            uint32_t begin, end;
+            kt_tile_list(pc, tile, nLarge, begin, end);
+            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
+                               end, stage[warp], lane);
+        }
+    } else {
+        // sort-first split: the same loop over the tile rows of this rank's bands only ("virtual" rows vy = the owned rows in
+        // order; row vy is real row vy + (vy / bandRows) * (nRanks - 1) * bandRows + rank * bandRows), so a rank's tile stage
+        // costs what its share of the frame costs — visiting every tile to skip most of them was a fixed ~0.2 ms at 8K
+        uint32_t vtile = blockIdx.x;
+        const uint32_t nVirtual = pc.tilesX * pc.vTilesY;
+        const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;
+        const uint32_t bandSkip = (pc.nRanks - 1u) * pc.bandRows, bandBase = pc.rank * pc.bandRows;
+        uint32_t vyN = vtile / pc.tilesX, txN = vtile - vyN * pc.tilesX;
+        uint32_t tyN = vyN + (vyN / pc.bandRows) * bandSkip + bandBase;
+        unsigned long long keyNext = vtile < nVirtual ? kt_load_key(pc, txN, tyN, warp, lx, ly) : VIS_CLEAR;
+        if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
+        for (; vtile < nVirtual; vtile += gridDim.x) {
+            const unsigned long long key = keyNext;
+            const uint32_t tx = txN, ty = tyN;
+            txN += stepX; vyN += stepY;
+            if (txN >= pc.tilesX) { txN -= pc.tilesX; ++vyN; }
+            tyN = vyN + (vyN / pc.bandRows) * bandSkip + bandBase;
+            if (vtile + gridDim.x < nVirtual) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
+            uint32_t begin, end;
+            kt_tile_list(pc, ty * pc.tilesX + tx, nLarge, begin, end);
+            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
+                               end, stage[warp], lane);
+        }
     }
 #endif
 }
@@ -465,10 +490,12 @@ void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, 
     using Kern = void (*)(PassConst, ShadeConst);
     // shadow transform with last row exactly (0, 0, 0, 1) (every orthographic light): w == 1.0f exactly, shadow.glsl's three divisions are identities
     const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
-    static const Kern kern[8] = {k_tile_forward<false, false, false>, k_tile_forward<true, false, false>, k_tile_forward<false, true, false>, k_tile_forward<true, true, false>,
-                                 k_tile_forward<false, false, true>,  k_tile_forward<true, false, true>,  k_tile_forward<false, true, true>,  k_tile_forward<true, true, true>};
-    const int v = (tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0);
-    static int perSM[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define KTF(T, P, A) k_tile_forward<T, P, A, false>, k_tile_forward<T, P, A, true>
+    static const Kern kern[16] = {KTF(false, false, false), KTF(true, false, false), KTF(false, true, false), KTF(true, true, false),
+                                  KTF(false, false, true),  KTF(true, false, true),  KTF(false, true, true),  KTF(true, true, true)};
+#undef KTF
+    const int v = 2 * ((tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)) + (pc.nRanks > 1 ? 1 : 0);
+    static int perSM[16] = {0};
     if (!perSM[v]) {
         int n = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], KT_THREADS, 0);
@@ -477,7 +504,7 @@ void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, 
 #if KT_MODE == 0
     const uint32_t grid = pc.tilesX * pc.tilesY;
 #else
-    const uint32_t grid = std::min<uint32_t>(pc.tilesX * pc.tilesY, (uint32_t)(numSMs * perSM[v]));
+    const uint32_t grid = std::max(1u, std::min<uint32_t>(pc.tilesX * pc.vTilesY, (uint32_t)(numSMs * perSM[v])));
 #endif
     launch_k(kern[v], dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
 }

@@ -330,6 +330,11 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
     if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
     else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; }
+    pc.bandRows = pc.tilesY; pc.vTilesY = pc.tilesY;
+    if (pc.nRanks > 1) {
+        pc.bandRows = pc.bandH / TILE_H; pc.vTilesY = 0;
+        for (uint32_t b = pc.rank; b * pc.bandRows < pc.tilesY; b += pc.nRanks) pc.vTilesY += std::min(pc.bandRows, pc.tilesY - b * pc.bandRows);
+    }
     static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
     pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
 }
