@@ -18,7 +18,7 @@ sel = [s for s in ('Kernel Name', 'gpu__time_duration.sum', 'dram__bytes_read.su
                    'sm__inst_executed.avg.per_cycle_elapsed', 'sm__warps_active.avg.pct_of_peak_sustained_active', 'launch__registers_per_thread',
                    'lts__t_sector_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
                    'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed') if s in ix]
-names = {'k_vertex_both': 'k_vertex_both', 'k_setup_raster<1>': 'k_setup_raster<shadow>', 'k_setup_raster<0>': 'k_setup_raster<forward>',
+names = {'k_vertex_both': 'k_vertex_both', 'k_setup_raster<1': 'k_setup_raster<shadow>', 'k_setup_raster<0': 'k_setup_raster<forward>',
          'k_clip_layout<1>': 'k_clip_layout<shadow>', 'k_clip_layout<0>': 'k_clip_layout<forward>',
          'k_tile_shadow': 'k_tile_shadow', 'k_tile_forward': 'k_tile_forward', 'k_bin_scatter': 'k_bin_scatter'}
 mul = {'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1, 'Gbyte': 1e9}
