@@ -544,3 +544,30 @@ def test_sort_first_contiguous_bands_with_draw_culling(inside):
         own = ((np.arange(s["height"]) // band) % world == rank)
         merged[own] = gpu["tri_id"][own]
     assert np.array_equal(merged, whole["tri_id"])
+
+
+def test_msaa4_and_skybox_under_the_sort_first_split():
+    """The widened paths compose with the split: a rank renders its bands of the 4x multisampled, skybox-backed frame."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("small")
+    s["skybox"] = sc.make_skybox(32)
+    world = 2
+    band = parallel.contiguous_band(s["height"], world * 2)
+    ref_shadow = orc.Oracle(s).render_shadow()
+    whole = orc.Oracle(s).render_forward_msaa4(ref_shadow)
+    merged = np.zeros_like(whole["color_srgb8"])
+    for rank in range(world):
+        ref = orc.Oracle(s, rank=rank, n_ranks=world, band_h=band).render_forward_msaa4(ref_shadow)
+        ctx = capi.Context(s["width"], s["height"], rank=rank, n_ranks=world, band_h=band)
+        ctx.upload_scene(s)
+        ctx.set_sample_count(4)
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+        own = ((np.arange(s["height"]) // band) % world == rank)
+        tri = ctx.readback(capi.REB_MS_TRIID_U32); dep = ctx.readback(capi.REB_MS_DEPTH_F32)
+        for k in range(4):
+            assert np.array_equal(tri[k][own], ref["tri_id"][k][own]) and np.array_equal(dep[k][own].view(np.uint32), ref["depth"][k][own].view(np.uint32))
+        c8 = ctx.readback(capi.REB_COLOR_SRGB8)
+        assert np.abs(c8[own].astype(np.int32) - whole["color_srgb8"][own].astype(np.int32)).max() <= 1
+        merged[own] = c8[own]
+    assert np.abs(merged.astype(np.int32) - whole["color_srgb8"].astype(np.int32)).max() <= 1
