@@ -196,9 +196,34 @@ void launch_draw_bounds(const uint32_t* indices, const float4* pos4, const DrawD
         k_draw_bounds<<<dim3(32, nd), 256, 0, st>>>(indices, pos4, draws + d0, nd, bounds + 6 * (size_t)d0);
     }
 }
-// Once per pass and frame, ahead of K0: a draw is kept iff the rows its transformed bounding box can touch (one pixel of
-// slack for rounding and the sample shifts) include a row band of this rank, and it is not off-screen sideways.  The eight
-// corners go through the pass's own vertex stage; a corner at or behind the eye plane keeps the draw (the clipper decides).
+// Can the box [mn, mx] (object space, node transform T) touch a row of this rank?  The eight corners go through the pass's
+// own vertex stage; a corner at or behind the eye plane keeps it (the clipper decides); one pixel of slack.
+template <bool SHADOW>
+__device__ __forceinline__ uint32_t box_touches_rank(const PassConst& pc, const float* T, const float mn[3], const float mx[3]) {
+    const float hw = 0.5f * (float)pc.W, hh = 0.5f * (float)pc.H;
+    float x0 = 3.0e38f, x1 = -3.0e38f, y0 = 3.0e38f, y1 = -3.0e38f;
+    for (int c = 0; c < 8; ++c) {
+        V3 world;
+        const float4 q = vertex_stage<!SHADOW>(pc.PV, T, (c & 1) ? mx[0] : mn[0], (c & 2) ? mx[1] : mn[1], (c & 4) ? mx[2] : mn[2], &world);
+        if (!(q.w > 0.0f)) return 1u;       // also catches NaN
+        const float xf = hw * (q.x / q.w) + hw, yf = hh * (q.y / q.w) + hh;
+        if (!(fabsf(xf) < 1.0e30f) || !(fabsf(yf) < 1.0e30f)) return 1u;
+        x0 = fminf(x0, xf); x1 = fmaxf(x1, xf); y0 = fminf(y0, yf); y1 = fmaxf(y1, yf);
+    }
+    if (x1 < -1.0f || x0 > (float)pc.W + 1.0f || y1 < -1.0f || y0 > (float)pc.H + 1.0f) return 0u;
+    if (pc.nRanks <= 1) return 1u;
+    const uint32_t r0 = (uint32_t)fmaxf(y0 - 1.0f, 0.0f), r1 = (uint32_t)fminf(fmaxf(y1 + 1.0f, 0.0f), (float)(pc.H - 1u));
+    const uint32_t b0 = r0 / pc.bandH, b1 = r1 / pc.bandH;
+    if (b1 - b0 + 1u >= pc.nRanks) return 1u;
+    for (uint32_t q = b0; q <= b1; ++q) if (q % pc.nRanks == pc.rank) return 1u;
+    return 0u;
+}
+__device__ __forceinline__ void load_node_transform(const PassConst& pc, uint32_t node, float T[16]) {
+    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * node;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float4 q = Tq[k]; T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
+}
+// Once per pass and frame, ahead of K0: per-draw visibility (K0 skips the vertices of the other draws) ...
 template <bool SHADOW>
 __global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ visible) {
     const uint32_t d = blockIdx.x * 128u + threadIdx.x;
@@ -206,33 +231,66 @@ __global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ Pass
     const uint32_t* b = bounds + 6 * (size_t)d;
     if (b[0] > b[3]) { visible[d] = 0u; return; }   // draw without primitives
     const float mn[3] = {dec_ordered(b[0]), dec_ordered(b[1]), dec_ordered(b[2])}, mx[3] = {dec_ordered(b[3]), dec_ordered(b[4]), dec_ordered(b[5])};
-    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * pc.draws[d].node;
     float T[16];
+    load_node_transform(pc, pc.draws[d].node, T);
+    visible[d] = box_touches_rank<SHADOW>(pc, T, mn, mx);
+}
+// ... and per 256-triangle block (K1 skips the other blocks: meshes come out of subdivision / the importer in spatially coherent
+// index order, so a block is a small patch).  blockBox[8 tb]: min xyz, draw (0xFFFFFFFF: the block spans draws), max xyz, pad.
+template <bool SHADOW>
+__global__ void __launch_bounds__(128) k_cull_blocks(const __grid_constant__ PassConst pc, const float4* __restrict__ blockBox, const uint32_t* __restrict__ drawVisible,
+                                                     uint32_t nBlocks, uint32_t* __restrict__ visible) {
+    const uint32_t tb = blockIdx.x * 128u + threadIdx.x;
+    if (tb >= nBlocks) return;
+    const float4 lo = blockBox[2 * (size_t)tb], hi = blockBox[2 * (size_t)tb + 1];
+    const uint32_t d = __float_as_uint(lo.w);
+    if (d == 0xFFFFFFFFu) { visible[tb] = 1u; return; }
+    if (drawVisible[d] == 0u) { visible[tb] = 0u; return; }
+    const float mn[3] = {lo.x, lo.y, lo.z}, mx[3] = {hi.x, hi.y, hi.z};
+    float T[16];
+    load_node_transform(pc, pc.draws[d].node, T);
+    visible[tb] = box_touches_rank<SHADOW>(pc, T, mn, mx);
+}
+// Object-space box of every 256-triangle block, once per draw list: one CTA per block, one triangle per thread.
+__global__ void __launch_bounds__(256) k_block_bounds(const __grid_constant__ PassConst pc, float4* __restrict__ blockBox) {
+    __shared__ float red[8][6];
+    __shared__ uint32_t dFirst, dLast;
+    const uint32_t tb = blockIdx.x, tri = tb * 256u + threadIdx.x;
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    if (tri < pc.nTris) {
+        const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
+        const uint32_t* ix = pc.indices + pc.draws[d].indexOffset + 3u * (tri - pc.draws[d].firstTri);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const float4 q = Tq[k]; T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
-    const float hw = 0.5f * (float)pc.W, hh = 0.5f * (float)pc.H;
-    float x0 = 3.0e38f, x1 = -3.0e38f, y0 = 3.0e38f, y1 = -3.0e38f;
-    bool keep = false;
-    for (int c = 0; c < 8; ++c) {
-        V3 world;
-        const float4 q = vertex_stage<!SHADOW>(pc.PV, T, (c & 1) ? mx[0] : mn[0], (c & 2) ? mx[1] : mn[1], (c & 4) ? mx[2] : mn[2], &world);
-        if (!(q.w > 0.0f)) { keep = true; continue; }       // also catches NaN
-        const float xf = hw * (q.x / q.w) + hw, yf = hh * (q.y / q.w) + hh;
-        if (!(fabsf(xf) < 1.0e30f) || !(fabsf(yf) < 1.0e30f)) { keep = true; continue; }
-        x0 = fminf(x0, xf); x1 = fmaxf(x1, xf); y0 = fminf(y0, yf); y1 = fmaxf(y1, yf);
-    }
-    uint32_t v = 1u;
-    if (!keep) {
-        if (x1 < -1.0f || x0 > (float)pc.W + 1.0f || y1 < -1.0f || y0 > (float)pc.H + 1.0f) v = 0u;
-        else if (pc.nRanks > 1) {
-            const uint32_t r0 = (uint32_t)fmaxf(y0 - 1.0f, 0.0f), r1 = (uint32_t)fminf(fmaxf(y1 + 1.0f, 0.0f), (float)(pc.H - 1u));
-            const uint32_t b0 = r0 / pc.bandH, b1 = r1 / pc.bandH;
-            v = 0u;
-            if (b1 - b0 + 1u >= pc.nRanks) v = 1u;
-            else for (uint32_t q = b0; q <= b1; ++q) if (q % pc.nRanks == pc.rank) v = 1u;
+        for (int k = 0; k < 3; ++k) {
+            const float4 p = __ldg(pc.pos4 + __ldg(ix + k));
+            lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+            hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
         }
+        if (threadIdx.x == 0) dFirst = d;
+        if (tri == min(pc.nTris, tb * 256u + 256u) - 1u) dLast = d;
     }
-    visible[d] = v;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[c] = fminf(lo[c], __shfl_xor_sync(0xFFFFFFFFu, lo[c], o));
+            hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xFFFFFFFFu, hi[c], o));
+        }
+    if ((threadIdx.x & 31u) == 0) for (int c = 0; c < 3; ++c) { red[threadIdx.x >> 5][c] = lo[c]; red[threadIdx.x >> 5][3 + c] = hi[c]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) for (int c = 0; c < 3; ++c) { lo[c] = fminf(lo[c], red[w][c]); hi[c] = fmaxf(hi[c], red[w][3 + c]); }
+        blockBox[2 * (size_t)tb] = make_float4(lo[0], lo[1], lo[2], __uint_as_float(dFirst == dLast ? dFirst : 0xFFFFFFFFu));
+        blockBox[2 * (size_t)tb + 1] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+    }
+}
+void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st) {
+    if (pc.nTris == 0) return;
+    k_block_bounds<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, blockBox);
+}
+void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, cudaStream_t st) {
+    if (nBlocks == 0) return;
+    if (shadow) k_cull_blocks<true><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible);
+    else k_cull_blocks<false><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible);
 }
 void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, cudaStream_t st) {
     if (pc.nDraws == 0) return;

@@ -27,7 +27,8 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward
     uint32_t* blockDraw = nullptr; size_t blockDrawCap = 0; uint32_t triBlocks = 0;   // [triBlocks] by triangle, then by cache slot
     uint32_t* flatSlots = nullptr; size_t flatCap = 0;   // 3 cache slots per triangle, submission order (indexed mode)
     uint32_t cacheSize = 0, deindexed = 0;
-    uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
+    uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;
+    float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
     bool pending = false;        // enqueued since the last overflow check
 };
@@ -294,6 +295,14 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         CU(cudaMemcpyAsync(ps.drawBounds, init.data(), init.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
         launch_draw_bounds(ctx->indices, ctx->pos4, ps.dDraws, n, ps.drawBounds, ctx->stream); ctx->launches++;
         CU(cudaStreamSynchronize(ctx->stream));   // init is a stack-lifetime staging buffer
+        if (ps.triBlocks > ps.blockCullCap) {
+            int rc;
+            if ((rc = dev_alloc(ctx, &ps.blockBox, (size_t)ps.triBlocks * 2)) || (rc = dev_alloc(ctx, &ps.blockVisible, (size_t)ps.triBlocks))) return rc;
+            ps.blockCullCap = ps.triBlocks;
+        }
+        PassConst pcb;
+        fill_pass(ctx, kind, pcb);
+        launch_block_bounds(pcb, ps.blockBox, ctx->stream); ctx->launches++;
     }
     if (!ps.deindexed && tri) {   // index stream re-based into cache-slot space
         if (3 * tri > ps.flatCap) {
@@ -337,6 +346,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     }
     static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
     pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
+    pc.blockVisible = pc.drawVisible ? ps.blockVisible : nullptr;
 }
 
 // Everything a pass needs before its kernels can be enqueued: queue capacities, texture table, kernel parameters.
@@ -401,7 +411,10 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
     }
     mark(1);
-    if (ps.nTris && pc.drawVisible) { launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ctx->stream); ctx->launches++; }
+    if (ps.nTris && pc.drawVisible) {
+        launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ctx->stream);
+        launch_cull_blocks(pc, kind == 0, ps.blockBox, ps.drawVisible, ps.triBlocks, ps.blockVisible, ctx->stream); ctx->launches += 2;
+    }
     if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
     ShadeConst sh;

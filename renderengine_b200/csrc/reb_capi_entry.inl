@@ -58,7 +58,8 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots,
-                    ctx->pass[0].drawBounds, ctx->pass[1].drawBounds, ctx->pass[0].drawVisible, ctx->pass[1].drawVisible};
+                    ctx->pass[0].drawBounds, ctx->pass[1].drawBounds, ctx->pass[0].drawVisible, ctx->pass[1].drawVisible,
+                    ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);

@@ -86,6 +86,7 @@ struct PassConst {
     int32_t shiftX, shiftY;
     // per-draw visibility for this rank's rows (sort-first split): written by k_cull_draws before K0, NULL = no culling
     const uint32_t* drawVisible;
+    const uint32_t* blockVisible;   // the same per 256-triangle block (K1), written by k_cull_blocks
     // tile rows of this rank's bands, in order ("virtual" rows the forward tile stage iterates): bandRows = bandH / TILE_H,
     // vTilesY = how many tile rows the rank owns; without a split bandRows = vTilesY = tilesY
     uint32_t bandRows, vTilesY;

@@ -43,6 +43,8 @@ void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint3
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_draw_bounds(const uint32_t* indices, const float4* pos4, const DrawDev* draws, uint32_t nDraws, uint32_t* bounds, cudaStream_t st);
 void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, cudaStream_t st);   // sort-first split: per-draw row-band culling
+void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st);   // per 256-triangle block, once per draw list
+void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
 void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);   // K1c: Appendix B.3 clipping + tile-list layout
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);

@@ -13,6 +13,8 @@ Reference conventions followed:
   ComputeShadowTransform               Source/Runtime/Renderer/ShadowSystem.cpp:129-204 (F8: up = cross(dir, right))
   Phong Light (std430, 112 B)          Assets/Shaders/phong.glsl:20-37
 """
+import os
+
 import numpy as np
 
 f32 = np.float32
@@ -252,10 +254,13 @@ def to_pbr(scene, seed=1234, n_texture_sets=0, tex_size=64, extra_lights=True, e
 _ICO_CACHE = {}
 
 
-def icosphere(level):
-    """Unit icosphere: 10*4^L + 2 shared vertices, 20*4^L CCW-outward triangles."""
-    if level in _ICO_CACHE:
-        return _ICO_CACHE[level]
+def icosphere(level, order="breadth"):
+    """Unit icosphere: 10*4^L + 2 shared vertices, 20*4^L CCW-outward triangles.  order = "breadth" (default, the headline
+    scenes): every subdivision emits all first-corner children, then all second-corner ones, ... — consecutive triangles
+    are scattered over the sphere; "hierarchical": the four children of a triangle stay together, so any run of triangles
+    is a compact patch (what exporters that write faces in construction order produce).  Same triangles, same vertices."""
+    if (level, order) in _ICO_CACHE:
+        return _ICO_CACHE[(level, order)]
     t = (1.0 + 5.0 ** 0.5) / 2.0
     v = np.array([[-1, t, 0], [1, t, 0], [-1, -t, 0], [1, -t, 0], [0, -1, t], [0, 1, t], [0, -1, -t], [0, 1, -t],
                   [t, 0, -1], [t, 0, 1], [-t, 0, -1], [-t, 0, 1]], np.float64)
@@ -276,13 +281,13 @@ def icosphere(level):
         n = len(tri)
         m01, m12, m20 = base + inv[:n], base + inv[n:2 * n], base + inv[2 * n:]
         a, b, c = tri[:, 0], tri[:, 1], tri[:, 2]
-        tri = np.concatenate([np.stack([a, m01, m20], 1), np.stack([b, m12, m01], 1), np.stack([c, m20, m12], 1),
-                              np.stack([m01, m12, m20], 1)])
+        kids = [np.stack([a, m01, m20], 1), np.stack([b, m12, m01], 1), np.stack([c, m20, m12], 1), np.stack([m01, m12, m20], 1)]
+        tri = np.stack(kids, 1).reshape(-1, 3) if order == "hierarchical" else np.concatenate(kids)
     pos = v.astype(f32)
     uv = np.stack([np.arctan2(v[:, 2], v[:, 0]) / (2 * np.pi) + 0.5, np.arcsin(np.clip(v[:, 1], -1, 1)) / np.pi + 0.5], 1).astype(f32)
     verts = np.concatenate([pos, pos, uv], axis=1).astype(f32)   # normal = position on the unit sphere
-    _ICO_CACHE[level] = (verts, tri.astype(np.uint32))
-    return _ICO_CACHE[level]
+    _ICO_CACHE[(level, order)] = (verts, tri.astype(np.uint32))
+    return _ICO_CACHE[(level, order)]
 
 
 CONFIGS = {
@@ -339,7 +344,7 @@ def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
     W, H, S, M = cfg["width"], cfg["height"], cfg["shadow_size"], cfg["n_materials"]
     n_tex, tex_size = cfg.get("n_textures", 0), cfg.get("tex_size", 64)
     rng = np.random.default_rng(seed)
-    sv, st = icosphere(level)
+    sv, st = icosphere(level, cfg.get("tri_order", os.environ.get("REB_SCENE_TRI_ORDER", "breadth")))
     n_s = nx * nz
     nv, nt = len(sv), len(st)
     spacing = 2.5
