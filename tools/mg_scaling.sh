@@ -5,4 +5,4 @@ run() { n=$1; shift; name=$1; shift; timeout 400 python -m torch.distributed.run
 run 2 tiles2 --mode tiles --config C4
 run 4 tiles4 --mode tiles --config C4
 run 8 tiles8 --mode tiles --config C4
-run 8 tiles8_rep --mode tiles --config C4 --shadow-share replicate
+REB_SCENE_TRI_ORDER=hierarchical run 8 tiles8_coherent --mode tiles --config C4
