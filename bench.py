@@ -169,7 +169,7 @@ def main():
     ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
                     help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
     ap.add_argument("--samples", type=int, default=1, choices=[1, 4],
-                    help="samples per pixel of the base pass (4 = Appendix B.12 multisampling; the headline metric is quoted at 1)")
+                    help="samples per pixel of the base pass (4 = Appendix B.15 multisampling; the headline metric is quoted at 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -312,7 +312,7 @@ struct PassParams {
     const float* PV;     // proj*view (formed once with mat4_mul_mat4)
     bool divideWorldByW; // primitive.vert:51 (forward) vs shadow_map.vert:49 (shadow)
     uint32_t W, H;
-    // Appendix B.12 (multisampling): sample k of a pixel sits at (x + sx, y + sy) instead of the centre.  Edge functions
+    // Appendix B.15 (multisampling): sample k of a pixel sits at (x + sx, y + sy) instead of the centre.  Edge functions
     // and depth are translation-invariant, so sampling there equals sampling the centre of the primitive moved by
     // (128 - 256 sx, 128 - 256 sy) sub-pixel units — an exact integer shift of the snapped vertices.
     int32_t shiftX = 0, shiftY = 0;
@@ -347,7 +347,7 @@ inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t 
         float xf = hw * nx + hw;
         float yf = hh * ny + hh;
         if (!(std::fabs(xf) <= GUARD_PX) || !(std::fabs(yf) <= GUARD_PX)) return NEEDS_CLIP;
-        s.X[k] = (int32_t)std::lrintf(xf * 256.0f) + pp.shiftX;   // B.5 round-half-even, 8 sub-pixel bits (+ B.12 sample shift)
+        s.X[k] = (int32_t)std::lrintf(xf * 256.0f) + pp.shiftX;   // B.5 round-half-even, 8 sub-pixel bits (+ B.15 sample shift)
         s.Y[k] = (int32_t)std::lrintf(yf * 256.0f) + pp.shiftY;
         s.z[k] = nz;
         s.w[k] = c[k].w;
@@ -709,7 +709,7 @@ void rasterize(const orc_scene* sc, const PassParams& pp, const Frontend& fe, fl
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
-// Skybox (Appendix B.11).  The reference draws a unit cube last with
+// Skybox (Appendix B.14).  The reference draws a unit cube last with
 // gl_Position = (proj * mat4(mat3(view)) * (p, 1)).xyww (skybox.vert:32-37): depth exactly 1.0, test LessOrEqual
 // (RenderScene.cpp:226-229), so it shows wherever the depth buffer still holds 1.0; the fragment colour is
 // texture(cube, p) (skybox.frag:28-31) and a cube lookup depends only on the direction of p.  The direction of the
@@ -857,7 +857,7 @@ int orc_render_shadow(const orc_scene* sc, float* shadowMap, uint64_t* counters)
 // Forward pass: MaterialSystem::Draw (MaterialSystem.cpp:88-101) + primitive.vert:49-57 + the
 // builder-defined Phong main() of Appendix B.11 over phong.glsl / shadow.glsl.
 namespace {
-// depth / triId hold nSamples planes of W x H (1 = the 1-sample contract, 4 = Appendix B.12)
+// depth / triId hold nSamples planes of W x H (1 = the 1-sample contract, 4 = Appendix B.15)
 int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* depth, uint32_t* triId, float* colorF32,
                         uint8_t* colorSRGB8, uint64_t* counters, int nSamples) {
     if (!sc || !depth || !triId) return -1;
@@ -1025,12 +1025,12 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
                 size_t p = (size_t)y * W + x;
                 V4 out;
                 if (nSamples == 1) {
-                    // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.11)
+                    // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.14)
                     if (haveSky && depth[p] == 1.0f) out = sky_pixel(sky, x, y);
                     else if (triId[p] != TRI_NONE) out = shadeTri(x, y, triId[p]);
                     else out = clearColour;
                 } else {
-                    // Appendix B.12: every sample takes the colour its winning primitive was shaded with at the pixel centre
+                    // Appendix B.15: every sample takes the colour its winning primitive was shaded with at the pixel centre
                     // (one shader invocation per pixel and primitive); the resolve is the average in linear float, (s0 + s1) + (s2 + s3)
                     V4 col[4];
                     for (int k = 0; k < 4; ++k) {

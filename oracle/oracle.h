@@ -66,7 +66,7 @@ int orc_render_forward(const orc_scene* s, const float* shadowMap /* S*S or NULL
                        float* depth, uint32_t* triId, float* colorF32 /* RGBA or NULL */,
                        uint8_t* colorSRGB8 /* RGBA or NULL */, uint64_t* counters);
 
-/* Appendix B.12: the base pass with 4 samples per pixel at the Vulkan standard locations and an average resolve (the
+/* Appendix B.15: the base pass with 4 samples per pixel at the Vulkan standard locations and an average resolve (the
    reference's actual base-pass state, Swapchain.cpp:110-123,212; PhysicalDevice.cpp:172-186).  depth4 / triId4 hold
    four W x H planes (sample-major); the colour outputs are the resolved image. */
 int orc_render_forward_msaa4(const orc_scene* s, const float* shadowMap, float* depth4, uint32_t* triId4,
@@ -81,7 +81,7 @@ void orc_phong_lighting(const uint8_t* light112, const float* props9 /* diffuse4
 float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal,
                          const float* transform16, const float* shadowMap, uint32_t S);
 void orc_srgb8(const float* rgba, uint8_t* out4);
-/* Appendix B.11: skybox colour of pixel (x, y) for the 160-B view block; and the cube lookup on its own */
+/* Appendix B.14: skybox colour of pixel (x, y) for the 160-B view block; and the cube lookup on its own */
 void orc_sky_pixel(const uint8_t* view160, uint32_t W, uint32_t H, const uint16_t* faces, uint32_t w, uint32_t h, uint32_t x, uint32_t y, float* out4);
 void orc_sky_lookup(const uint16_t* faces, uint32_t w, uint32_t h, const float* dir3, float* out4);
 void orc_pbr_lighting(const uint8_t* material80, const uint8_t* lights80, uint32_t nLights, const float* fragPos, const float* normal, const float* viewPos,

@@ -67,7 +67,7 @@ def lib():
 
 
 def sky_lookup(faces, direction):
-    """Appendix B.11 cube lookup (seamless bilinear) of one direction; faces = (6, h, w, 4) uint16."""
+    """Appendix B.14 cube lookup (seamless bilinear) of one direction; faces = (6, h, w, 4) uint16."""
     f = np.ascontiguousarray(faces, np.uint16); d = np.ascontiguousarray(direction, np.float32); out = np.empty(4, np.float32)
     lib().orc_sky_lookup(_p(f, u16p), f.shape[2], f.shape[1], _p(d, fp), _p(out, fp))
     return out
@@ -140,7 +140,7 @@ class Oracle:
         return out
 
     def render_forward_msaa4(self, shadow_map=None):
-        """Appendix B.12: 4 samples per pixel (Vulkan standard locations) + average resolve.  depth / tri_id: (4, H, W)."""
+        """Appendix B.15: 4 samples per pixel (Vulkan standard locations) + average resolve.  depth / tri_id: (4, H, W)."""
         W, H = self.s.width, self.s.height
         depth = np.empty((4, H, W), np.float32); tri = np.empty((4, H, W), np.uint32)
         cf = np.empty((H, W, 4), np.float32); c8 = np.empty((H, W, 4), np.uint8)

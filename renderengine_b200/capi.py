@@ -192,7 +192,7 @@ class Context:
         self._ck(self.lib.reb_set_shading_model(self.h, int(model)))
 
     def set_sample_count(self, samples):
-        """1 (default) or 4 samples per pixel for the base pass (Appendix B.12)."""
+        """1 (default) or 4 samples per pixel for the base pass (Appendix B.15)."""
         self._ck(self.lib.reb_set_sample_count(self.h, int(samples)))
         self.samples = int(samples)
 

@@ -115,7 +115,7 @@ __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, con
     t.isSmall = t.isLarge = t.needsClip = false;
     t.A2 = 0; t.x0 = t.y0 = 0; t.x1 = t.y1 = -1;
 #pragma unroll
-    for (int k = 0; k < 3; ++k)   // SHIFT: + B.12 sample shift (its own instantiation: the 1-sample kernels keep their register budget)
+    for (int k = 0; k < 3; ++k)   // SHIFT: + B.15 sample shift (its own instantiation: the 1-sample kernels keep their register budget)
         t.a[k] = {(int32_t)q[k].x + (SHIFT ? pc.shiftX : 0), (int32_t)q[k].y + (SHIFT ? pc.shiftY : 0), __uint_as_float(q[k].z), q[k].w};
     if (!valid) return;
     const uint32_t f0 = t.a[0].flags, f1 = t.a[1].flags, f2 = t.a[2].flags;
@@ -226,7 +226,7 @@ __device__ __noinline__ bool k1_clip_emit(const PassConst& pc, uint32_t tri, uns
     }
     bool queued = false;
     VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
-    v0.X += pc.shiftX; v0.Y += pc.shiftY;   // B.12 sample shift
+    v0.X += pc.shiftX; v0.Y += pc.shiftY;   // B.15 sample shift
     for (int i = 1; i + 1 < n; ++i) {
         K1Tri t;
         t.a[0] = v0; t.a[1] = viewport_snap(a[i], pc.W, pc.H); t.a[2] = viewport_snap(a[i + 1], pc.W, pc.H);
@@ -549,7 +549,7 @@ void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStrea
     using Kern = void (*)(PassConst);
     static const Kern kern[6] = {k_setup_raster<false, false, false>, k_setup_raster<true, false, false>, k_setup_raster<false, true, false>,
                                  k_setup_raster<false, false, true>,  k_setup_raster<true, false, true>,  k_setup_raster<false, true, true>};
-    // +1: shadow pass; 2: a sample pass of a multisampled frame (Appendix B.12); +3: per-draw culling for the sort-first split
+    // +1: shadow pass; 2: a sample pass of a multisampled frame (Appendix B.15); +3: per-draw culling for the sort-first split
     const int v = (shadow ? 1 : ((pc.shiftX | pc.shiftY) ? 2 : 0)) + (pc.drawVisible ? 3 : 0);
     static int perSM[6] = {0, 0, 0, 0, 0, 0};
     if (!perSM[v]) {

@@ -297,7 +297,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
         depth = __uint_as_float((uint32_t)(key[0] >> 32));
         tri = ~(uint32_t)key[0];
     }
-    if (sh.skyFaces && depth == 1.0f) col = sky_pixel(sh, x, y);   // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.11)
+    if (sh.skyFaces && depth == 1.0f) col = sky_pixel(sh, x, y);   // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.14)
     else if (hit && (sh.outSRGB8 || sh.outF32)) col = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, tri) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, tri);
     if (sh.outDepth) sh.outDepth[p] = depth;
     if (sh.outTriId) sh.outTriId[p] = tri;
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
 #endif
 }
 
-// Multisample resolve (Appendix B.12; the reference's base pass is multisampled with an average resolve,
+// Multisample resolve (Appendix B.15; the reference's base pass is multisampled with an average resolve,
 // Swapchain.cpp:110-123,212).  The four sample planes were rasterised by four runs of K1..K3 with shifted vertices; here
 // every pixel shades each DISTINCT primitive among its samples once at the pixel centre (one fragment-shader invocation per
 // pixel and primitive), gives every sample the colour of its primitive (sky / clear colour for uncovered samples) and

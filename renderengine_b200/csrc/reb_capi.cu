@@ -65,7 +65,7 @@ struct reb_ctx {
     cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[2] = {nullptr, nullptr};
     void* asyncHost = nullptr; bool asyncOutstanding = false;   // last reb_readback_async target (re-copied if the frame is replayed)
     unsigned long long* vis = nullptr;
-    // multisampling (Appendix B.12): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
+    // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
     uint32_t samples = 1; float* msDepth = nullptr; uint32_t* msTriId = nullptr;
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
@@ -379,7 +379,7 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
 
 // Enqueue the kernels of one pass: K0 vertex stage (unless the fused two-pass K0 already ran), K1 setup + small raster,
 // K2 bin scatter, K3 tile stage.  Every kernel after the first is PDL-chained.
-// Appendix B.11: inverse of A = rows x, y, w of proj * mat4(mat3(view)) restricted to 3x3 — maps (xn, yn, 1) to the
+// Appendix B.14: inverse of A = rows x, y, w of proj * mat4(mat3(view)) restricted to 3x3 — maps (xn, yn, 1) to the
 // direction of the view ray (skybox.vert:32-37).  Adjugate / determinant in double, rounded to float once per frame.
 static void sky_ray_matrix(const float* view, const float* proj, float* out9) {
     double A[3][3];
@@ -443,7 +443,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         }
     }
     if (kind == 1 && ctx->samples == 4) {
-        // Appendix B.12: four raster passes over the same post-transform cache, one per Vulkan standard sample location
+        // Appendix B.15: four raster passes over the same post-transform cache, one per Vulkan standard sample location
         // ((0.375, 0.125), (0.875, 0.375), (0.125, 0.625), (0.625, 0.875)), each an exact shift of the snapped vertices by
         // (128 - 256 s) sub-pixel units; every pass leaves its depth / triangle-ID plane, the resolve kernel shades.
         static const int32_t shift[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};

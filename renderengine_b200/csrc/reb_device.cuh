@@ -81,7 +81,7 @@ struct PassConst {
     uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket (k_clip_layout) [6] clip-queue length
     uint32_t* hostStatus;         // mapped pinned mirror of status[0..7], written by the tile stage (no D2H copy node)
     uint32_t rank, nRanks, bandH; // sort-first row bands (forward only)
-    // Appendix B.12 (multisampling): this raster pass samples at pixel centre - shift / 256, implemented as an exact integer
+    // Appendix B.15 (multisampling): this raster pass samples at pixel centre - shift / 256, implemented as an exact integer
     // shift of the snapped vertices (edge functions and depth are translation-invariant).  0 for 1-sample passes.
     int32_t shiftX, shiftY;
     // per-draw visibility for this rank's rows (sort-first split): written by k_cull_draws before K0, NULL = no culling

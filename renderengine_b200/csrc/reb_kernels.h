@@ -55,7 +55,7 @@ void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t n
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st);   // between the sample passes of a multisampled frame
-// Appendix B.12 resolve: per pixel, shade every distinct primitive of the 4 sample planes once at the pixel centre, average
+// Appendix B.15 resolve: per pixel, shade every distinct primitive of the 4 sample planes once at the pixel centre, average
 void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st);
 
 }  // namespace reb

@@ -1,4 +1,4 @@
-// reb_sky.cuh — skybox background (Appendix B.11 of DESIGN.md).
+// reb_sky.cuh — skybox background (Appendix B.14 of DESIGN.md).
 //
 // The reference draws a unit cube last with gl_Position = (proj * mat4(mat3(view)) * (p, 1)).xyww, i.e. at depth
 // exactly 1.0 under LessOrEqual (skybox.vert:32-37, RenderScene.cpp:226-229, Skybox.cpp:126-140), and colours it with

@@ -405,7 +405,7 @@ def test_parity_perspective_shadow_transform():
 
 @pytest.mark.parametrize("pbr", [False, True])
 def test_parity_skybox_background(pbr):
-    """the cube-map background (skybox.vert / skybox.frag, Appendix B.11) behind Phong and PBR frames,
+    """the cube-map background (skybox.vert / skybox.frag, Appendix B.14) behind Phong and PBR frames,
     for the framing camera, a camera inside the scene looking at the horizon, and straight up (face seams and corners)."""
     from oracle import orc
     from renderengine_b200 import capi, scene as sc
@@ -449,7 +449,7 @@ def test_set_skybox_rejects_bad_arguments():
 
 @pytest.mark.parametrize("variant", ["phong", "pbr_sky", "textured"])
 def test_parity_msaa4(variant):
-    """SURVEY 8f row 2 / Appendix B.12: the base pass with 4 samples per pixel at the Vulkan standard locations, one shading
+    """SURVEY 8f row 2 / Appendix B.15: the base pass with 4 samples per pixel at the Vulkan standard locations, one shading
     per pixel and primitive, average resolve.  All four depth / triangle-ID planes bit-exact, resolved colour <= 1 LSB."""
     from oracle import orc
     from renderengine_b200 import capi, scene as sc

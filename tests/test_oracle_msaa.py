@@ -1,4 +1,4 @@
-"""CPU checks of the oracle's 4x multisampled base pass (Appendix B.12; Swapchain.cpp:110-123,212): sample placement by
+"""CPU checks of the oracle's 4x multisampled base pass (Appendix B.15; Swapchain.cpp:110-123,212): sample placement by
 exact vertex shifts, one shading per pixel and primitive, average resolve."""
 import numpy as np
 

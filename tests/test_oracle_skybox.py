@@ -1,4 +1,4 @@
-"""CPU checks of the oracle's skybox (Appendix B.11; skybox.vert:32-37, skybox.frag:28-31): the restated cube lookup
+"""CPU checks of the oracle's skybox (Appendix B.14; skybox.vert:32-37, skybox.frag:28-31): the restated cube lookup
 against the Vulkan face-selection table, and the per-pixel view ray against the reference's vertex-shader formula
 evaluated in float64."""
 import numpy as np
