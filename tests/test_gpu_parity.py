@@ -571,3 +571,12 @@ def test_msaa4_and_skybox_under_the_sort_first_split():
         assert np.abs(c8[own].astype(np.int32) - whole["color_srgb8"][own].astype(np.int32)).max() <= 1
         merged[own] = c8[own]
     assert np.abs(merged.astype(np.int32) - whole["color_srgb8"].astype(np.int32)).max() <= 1
+
+
+def test_set_shadow_partition_rejects_bad_arguments():
+    from renderengine_b200 import capi
+    ctx = capi.Context(64, 64)
+    for args in ((2, 2, 32), (0, 0, 32), (0, 2, 0), (0, 2, 24)):      # rank >= n, n == 0, band 0, band not a multiple of 32
+        with pytest.raises(capi.RebError):
+            ctx.set_shadow_partition(*args)
+    ctx.set_shadow_partition(1, 2, 64)
