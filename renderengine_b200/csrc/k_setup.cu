@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constan
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        pc.status[3] = cursor;
+        atomicMax(&pc.status[3], cursor);   // max over the sample passes of a multisampled frame (k_pass_reset keeps it)
         if (cursor > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
     }
 }
@@ -568,10 +568,11 @@ void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream
 }
 
 // Between the sample passes of a multisampled frame: re-arm the pass status words and the per-tile counters (K0's
-// prologue does this once per frame).  The overflow word stays sticky so the host sees an overflow of any sample pass.
+// prologue does this once per frame).  The overflow word and the largest list length stay, so the host sees an overflow of
+// any sample pass and sizes the regrow for the longest one.
 __global__ void __launch_bounds__(256) k_pass_reset(const __grid_constant__ PassConst pc) {
     pdl_enter();
-    if (blockIdx.x == 0 && threadIdx.x < 8 && threadIdx.x != 2) pc.status[threadIdx.x] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x < 8 && threadIdx.x != 2 && threadIdx.x != 3) pc.status[threadIdx.x] = 0u;
     for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
 }
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
