@@ -316,6 +316,8 @@ struct PassParams {
     // and depth are translation-invariant, so sampling there equals sampling the centre of the primitive moved by
     // (128 - 256 sx, 128 - 256 sy) sub-pixel units — an exact integer shift of the snapped vertices.
     int32_t shiftX = 0, shiftY = 0;
+    // Appendix B.16 (translucent draws, cull none): a triangle with A2 > 0 is rasterised with its vertices 1 and 2 swapped
+    bool twoSided = false;
 };
 // Vulkan standard sample locations for 4 samples ((0.375, 0.125), (0.875, 0.375), (0.125, 0.625), (0.625, 0.875)) as shifts
 static const int32_t MSAA4_SHIFT[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};
@@ -354,6 +356,10 @@ inline SetupResult setup_triangle(const PassParams& pp, const V4 c[3], uint32_t 
     }
     // B.6 facing: front = CCW = A2 < 0; cull back (A2 > 0) and degenerate (A2 == 0)
     s.A2 = (int64_t)(s.X[1] - s.X[0]) * (int64_t)(s.Y[2] - s.Y[0]) - (int64_t)(s.X[2] - s.X[0]) * (int64_t)(s.Y[1] - s.Y[0]);
+    if (pp.twoSided && s.A2 > 0) {
+        std::swap(s.X[1], s.X[2]); std::swap(s.Y[1], s.Y[2]); std::swap(s.z[1], s.z[2]); std::swap(s.w[1], s.w[2]);
+        s.A2 = -s.A2;
+    }
     if (s.A2 >= 0) return CULLED;
     int32_t minX = std::min(s.X[0], std::min(s.X[1], s.X[2])), maxX = std::max(s.X[0], std::max(s.X[1], s.X[2]));
     int32_t minY = std::min(s.Y[0], std::min(s.Y[1], s.Y[2])), maxY = std::max(s.Y[0], std::max(s.Y[1], s.Y[2]));
@@ -621,12 +627,15 @@ template <class F> void parallel_for(unsigned nThreads, F f) {
     for (auto& x : th) x.join();
 }
 
-void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe) {
-    const DrawRec* draws = reinterpret_cast<const DrawRec*>(sc->draws);
-    fe.triPrefix.resize(sc->nDraws + 1);
+// drawList / nDrawsIn default to the scene's opaque list; idBase is added to the running primitive counter (the translucent
+// list continues the numbering of the opaque one)
+void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe, const uint32_t* drawList = nullptr, uint32_t nDrawsIn = 0, uint64_t idBase = 0) {
+    const DrawRec* draws = reinterpret_cast<const DrawRec*>(drawList ? drawList : sc->draws);
+    const uint32_t nDraws = drawList ? nDrawsIn : sc->nDraws;
+    fe.triPrefix.resize(nDraws + 1);
     uint64_t total = 0;
-    for (uint32_t d = 0; d < sc->nDraws; ++d) { fe.triPrefix[d] = total; total += draws[d].nbIndices / 3; }
-    fe.triPrefix[sc->nDraws] = total;
+    for (uint32_t d = 0; d < nDraws; ++d) { fe.triPrefix[d] = total; total += draws[d].nbIndices / 3; }
+    fe.triPrefix[nDraws] = total;
     unsigned nT = thread_count(sc);
     std::vector<std::vector<Setup>> parts(nT);
     std::vector<uint64_t> clip(nT, 0);
@@ -642,7 +651,7 @@ void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe) {
             V4 c[3];
             for (int k = 0; k < 3; ++k) c[k] = vertex_stage(pp, T, sc->verts + 8 * (size_t)ix[k], nullptr);
             Setup s;
-            SetupResult r = setup_triangle(pp, c, (uint32_t)tri, s);
+            SetupResult r = setup_triangle(pp, c, (uint32_t)(tri + idBase), s);
             if (r == KEEP) parts[t].push_back(s);
             else if (r == NEEDS_CLIP) {   // B.3: clip, fan, set the children up like any triangle (same triId, parent's place in the order)
                 V4 poly[9];
@@ -650,7 +659,7 @@ void run_frontend(const orc_scene* sc, const PassParams& pp, Frontend& fe) {
                 for (int i = 1; i + 1 < n; ++i) {
                     const V4 cc[3] = {poly[0], poly[i], poly[i + 1]};
                     Setup cs;
-                    SetupResult cr = setup_triangle(pp, cc, (uint32_t)tri, cs, /*skipTrivialReject=*/true);
+                    SetupResult cr = setup_triangle(pp, cc, (uint32_t)(tri + idBase), cs, /*skipTrivialReject=*/true);
                     if (cr == KEEP) parts[t].push_back(cs);
                     else if (cr == NEEDS_CLIP) ++clip[t];   // cannot happen for finite inputs; counted, dropped
                 }
@@ -903,10 +912,14 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
     if (haveSky) { sky_setup(view, proj, sc->width, sc->height, sky); sky.faces = sc->skyFaces; sky.w = sc->skyW; sky.h = sc->skyH; }
 
     // colour of triangle `tri` shaded at the centre of pixel (x, y) (the fragment shader runs once per pixel and primitive)
+    // (tri is relative to the draw list being shaded: curDraws / curPrefix switch to the translucent list for Appendix B.16)
+    const DrawRec* curDraws = draws;
+    const std::vector<uint64_t>* curPrefix = &fe.triPrefix;
     auto shadeTri = [&](int x, int y, uint32_t tri) -> V4 {
-        uint32_t d = (uint32_t)(std::upper_bound(fe.triPrefix.begin(), fe.triPrefix.end(), (uint64_t)tri) - fe.triPrefix.begin()) - 1;
-        const DrawRec& dr = draws[d];
-        const uint32_t* ix = sc->indices + dr.indexOffset + 3 * ((uint64_t)tri - fe.triPrefix[d]);
+        const std::vector<uint64_t>& prefix = *curPrefix;
+        uint32_t d = (uint32_t)(std::upper_bound(prefix.begin(), prefix.end(), (uint64_t)tri) - prefix.begin()) - 1;
+        const DrawRec& dr = curDraws[d];
+        const uint32_t* ix = sc->indices + dr.indexOffset + 3 * ((uint64_t)tri - prefix[d]);
         const float* T = sc->transforms + 16 * (size_t)dr.sceneNode;
         const float* N = &nmat[9 * (size_t)dr.sceneNode];
         V4 c[3]; V3 world[3], nrm[3]; float uv[3][2];
@@ -1018,6 +1031,11 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
     unsigned nT = thread_count(sc);
     const int W = (int)sc->width, H = (int)sc->height;
     const size_t plane = (size_t)W * H;
+    // translucent draws blend over the opaque frame in linear float and are drawn BEFORE the skybox (RenderScene.cpp:226-228)
+    const bool haveTranslucent = nSamples == 1 && sc->translucentDraws && sc->nTranslucentDraws;
+    std::vector<float> hdrTmp;
+    if (haveTranslucent && !colorF32) { hdrTmp.resize(plane * 4); colorF32 = hdrTmp.data(); }
+    const bool skyNow = haveSky && !haveTranslucent;
     parallel_for(nT, [&](unsigned t) {
         int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
         for (int y = r0; y < r1; ++y)
@@ -1026,7 +1044,7 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
                 V4 out;
                 if (nSamples == 1) {
                     // the skybox is drawn last at depth 1.0 under LessOrEqual (Appendix B.14)
-                    if (haveSky && depth[p] == 1.0f) out = sky_pixel(sky, x, y);
+                    if (skyNow && depth[p] == 1.0f) out = sky_pixel(sky, x, y);
                     else if (triId[p] != TRI_NONE) out = shadeTri(x, y, triId[p]);
                     else out = clearColour;
                 } else {
@@ -1052,6 +1070,57 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
                 }
                 if (colorF32) { colorF32[4 * p + 0] = out.x; colorF32[4 * p + 1] = out.y; colorF32[4 * p + 2] = out.z; colorF32[4 * p + 3] = out.w; }
                 if (colorSRGB8) orc_srgb8(&out.x, colorSRGB8 + 4 * p);
+            }
+    });
+    if (!haveTranslucent) return 0;
+
+    // ---- Appendix B.16: the translucent list, in order, over the opaque frame --------------------------------------------------
+    // Same front end with cull none (a back-facing triangle is rasterised with vertices 1 and 2 swapped); every fragment that
+    // passes LessOrEqual against the current depth is shaded (at its pixel centre, attributes in the triangle's own vertex
+    // order), blended  C = Cs * As + Cd * (1 - As),  A = As * (1 - As)  (GraphicsPipelineCache.cpp:305-315) in linear float —
+    // the target is encoded once at the end — and writes its depth and ID.  The skybox comes after (depth still 1.0).
+    PassParams pt = pp; pt.twoSided = true;
+    Frontend ft;
+    const uint64_t idBase = fe.triPrefix.back();
+    run_frontend(sc, pt, ft, sc->translucentDraws, sc->nTranslucentDraws, idBase);
+    curDraws = reinterpret_cast<const DrawRec*>(sc->translucentDraws);
+    curPrefix = &ft.triPrefix;
+    parallel_for(nT, [&](unsigned t) {
+        int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
+        for (const Setup& s : ft.setups) {
+            int ya = std::max(s.y0, r0), yb = std::min(s.y1, r1 - 1);
+            if (ya > yb) continue;
+            Edges e = make_edges(s);
+            for (int y = ya; y <= yb; ++y) {
+                if (!row_owned(sc, y)) continue;
+                int64_t Py = 256 * (int64_t)y + 128;
+                for (int x = s.x0; x <= s.x1; ++x) {
+                    int64_t Px = 256 * (int64_t)x + 128;
+                    int64_t F0 = e.A[0] * Px + e.B[0] * Py + e.C[0];
+                    int64_t F1 = e.A[1] * Px + e.B[1] * Py + e.C[1];
+                    int64_t F2 = e.A[2] * Px + e.B[2] * Py + e.C[2];
+                    if (F0 - e.bias[0] < 0 || F1 - e.bias[1] < 0 || F2 - e.bias[2] < 0) continue;
+                    float z = depth_at(s, F1, F2);
+                    if (!(z >= 0.0f && z <= 1.0f)) continue;
+                    size_t p = (size_t)y * W + x;
+                    if (!(z <= depth[p])) continue;
+                    const V4 src = shadeTri(x, y, (uint32_t)(s.triId - idBase));
+                    float* dst = colorF32 + 4 * p;
+                    const float a = src.w, ia = 1.0f - a;
+                    dst[0] = src.x * a + dst[0] * ia; dst[1] = src.y * a + dst[1] * ia; dst[2] = src.z * a + dst[2] * ia;
+                    dst[3] = a * ia;
+                    depth[p] = z; triId[p] = s.triId;
+                }
+            }
+        }
+        for (int y = r0; y < r1; ++y)
+            for (int x = 0; x < W; ++x) {
+                size_t p = (size_t)y * W + x;
+                if (haveSky && depth[p] == 1.0f && row_owned(sc, y)) {
+                    const V4 c = sky_pixel(sky, x, y);
+                    colorF32[4 * p + 0] = c.x; colorF32[4 * p + 1] = c.y; colorF32[4 * p + 2] = c.z; colorF32[4 * p + 3] = c.w;
+                }
+                if (colorSRGB8) orc_srgb8(colorF32 + 4 * p, colorSRGB8 + 4 * p);
             }
     });
     return 0;

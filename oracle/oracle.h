@@ -57,6 +57,12 @@ typedef struct orc_scene {
        (TextureCache.cpp:251-266), layers +X -X +Y -Y +Z -Z, each skyW x skyH row-major.  NULL = no skybox. */
     const uint16_t* skyFaces;
     uint32_t        skyW, skyH;
+    /* translucent meshes (AlphaMode::eBlend, MaterialSystem.cpp:42,133): drawn after the opaque list in the same base pass
+       (RenderScene.cpp:226-227), in the order given (the caller sorts them back to front, RenderScene.cpp:127-159), cull
+       none, depth test LessOrEqual + depth write, src-alpha blending (GraphicsPipelineCache.cpp:305-315).  Same 4 x u32
+       records as `draws`; triangle IDs continue after the opaque list's.  Appendix B.16. */
+    const uint32_t* translucentDraws;
+    uint32_t        nTranslucentDraws;
 } orc_scene;
 
 /* counters[0] = triangles dropped because they need true clipping (w<=0 or guard band),

@@ -38,6 +38,7 @@ class OrcScene(C.Structure):
         ("textures", C.POINTER(OrcTexture)), ("nTextures", C.c_uint32), ("nThreads", C.c_uint32),
         ("rank", C.c_uint32), ("nRanks", C.c_uint32), ("bandH", C.c_uint32), ("shadingModel", C.c_uint32),
         ("skyFaces", u16p), ("skyW", C.c_uint32), ("skyH", C.c_uint32),
+        ("translucentDraws", u32p), ("nTranslucentDraws", C.c_uint32),
     ]
 
 
@@ -120,6 +121,9 @@ class Oracle:
         s.nThreads = n_threads
         s.rank, s.nRanks, s.bandH = rank, n_ranks, band_h
         s.shadingModel = int(scene.get("shading_model", 0))
+        td = scene.get("translucent_draws")
+        if td is not None and len(td):
+            tdh = hold(td, np.uint32); s.translucentDraws = _p(tdh, u32p); s.nTranslucentDraws = tdh.shape[0]
         sky = scene.get("skybox")
         if sky is not None:
             f = hold(sky, np.uint16)                  # (6, h, w, 4) RGBA16, layers +X -X +Y -Y +Z -Z

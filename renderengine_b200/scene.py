@@ -414,6 +414,35 @@ def view_from(scene, eye, look, fov=45.0, near=0.01, far=100.0):
     return pack_view(view, proj, eye)
 
 
+def to_translucent(scene, every=3, alpha=0.45, view=None):
+    """Make every `every`-th material translucent (AlphaMode::eBlend, alpha in the material's diffuse / base-colour alpha)
+    and split the draw list the way RenderScene does: opaque draws stay in `draws` (sorted by material, node:
+    RenderScene.cpp:105-125), translucent ones go to `translucent_draws` sorted back to front by
+    dot(viewInverse[2], cameraPosition - nodeTranslation), then material, then node (RenderScene.cpp:127-159)."""
+    s = dict(scene)
+    mats = np.array(scene["materials"], np.uint8).copy()
+    n_mat = mats.shape[0]
+    tl = np.zeros(n_mat, bool)
+    tl[np.arange(0, n_mat, every)] = True
+    for m in np.nonzero(tl)[0]:
+        mats[m, 12:16] = np.frombuffer(f32(alpha).tobytes(), np.uint8)
+    s["materials"] = mats
+    draws = np.asarray(scene["draws"], np.uint32)
+    is_t = tl[(draws[:, 2] >> 4).astype(np.int64)]
+    vw = np.frombuffer(np.asarray(view if view is not None else scene["view"], np.uint8).tobytes(), f32)
+    V = vw[:16].reshape(4, 4).T.astype(np.float64)
+    Vi = np.linalg.inv(V)
+    cam, front = Vi[:3, 3], Vi[:3, 2]
+    T = np.asarray(scene["transforms"], f32).reshape(-1, 16)
+    def key(d):
+        dist = float(np.dot(front, cam - T[int(d[3]), 12:15].astype(np.float64)))
+        return (-dist, int(d[2]), int(d[3]))
+    s["draws"] = draws[~is_t]
+    s["translucent_draws"] = np.array(sorted((tuple(int(v) for v in d) for d in draws[is_t]), key=key), np.uint32).reshape(-1, 4)
+    s["n_triangles"] = int(scene["n_triangles"])
+    return s
+
+
 def make_skybox(size=64, seed=1234):
     """Procedural cube map in the reference's layout (TextureCache.cpp:199-290: six RGBA16 UNORM faces, one mip, layers
     +X -X +Y -Y +Z -Z = right, left, top, bottom, front, back of Skybox.cpp:71-78): a vertical sky gradient that is
