@@ -101,6 +101,16 @@ int reb_set_view(reb_ctx* ctx, const void* viewProperties160);
 #define REB_SHADING_PBR   1u
 int reb_set_shading_model(reb_ctx* ctx, uint32_t model);
 
+/* The whole base pass of RenderScene::RenderBasePass (RenderScene.cpp:210-242): the opaque list, then the translucent list
+ * (AlphaMode::eBlend materials, MaterialSystem.cpp:42,133) in the order given — the caller sorts it back to front as
+ * RenderScene::SortTranslucentMeshes does (RenderScene.cpp:127-159) — with cull none, depth test LessOrEqual + depth
+ * write and src-alpha blending (GraphicsPipelineCache.cpp:305-315), then the skybox.  Triangle IDs of the translucent
+ * list continue after the opaque list's.  reb_render_forward(ctx, d, n) == reb_render_forward2(ctx, d, n, NULL, 0).
+ * Limits of this version: 1 sample per pixel only; a pixel keeps at most 16 translucent fragments and a frame
+ * max(4 * W * H, 2^20) of them; translucent triangles that cross the eye plane / guard band are dropped — all counted in
+ * reb_get_counters()[0]. */
+int reb_render_forward2(reb_ctx* ctx, const reb_draw* opaque, uint32_t nOpaque, const reb_draw* translucent, uint32_t nTranslucent);
+
 /* Skybox::Skybox / Skybox::Render — Skybox.cpp:58-92,126-140; TextureCache::LoadCubeMapFaces — TextureCache.cpp:199-290;
  * skybox.vert:32-37, skybox.frag:28-31.  Installs the cube map the forward pass shows wherever the depth buffer still
  * holds 1.0 (the reference draws its cube last at depth 1.0 under LessOrEqual, RenderScene.cpp:226-229).

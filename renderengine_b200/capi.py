@@ -15,7 +15,7 @@ REB_MS_DEPTH_F32, REB_MS_TRIID_U32 = 5, 6
 SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
-    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition",
+    "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition", "reb_render_forward2",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
@@ -62,6 +62,7 @@ def load():
     lib.reb_set_view.argtypes = [vp, vp]
     lib.reb_render_shadow.argtypes = [vp, u32, vp, u32]
     lib.reb_render_forward.argtypes = [vp, vp, u32]
+    lib.reb_render_forward2.argtypes = [vp, vp, u32, vp, u32]
     lib.reb_get_output.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(u64)]
     lib.reb_readback.argtypes = [vp, C.c_int, vp]
     lib.reb_sync.argtypes = [vp]
@@ -181,9 +182,14 @@ class Context:
         d = np.ascontiguousarray(draws, np.uint32).reshape(-1, 4)
         self._ck(self.lib.reb_render_shadow(self.h, self.shadow_id, _ptr(d), d.shape[0]))
 
-    def render_forward(self, draws):
+    def render_forward(self, draws, translucent=None):
+        """Base pass: the opaque list and, optionally, the translucent list drawn after it (Appendix B.16)."""
         d = np.ascontiguousarray(draws, np.uint32).reshape(-1, 4)
-        self._ck(self.lib.reb_render_forward(self.h, _ptr(d), d.shape[0]))
+        if translucent is None or len(translucent) == 0:
+            self._ck(self.lib.reb_render_forward(self.h, _ptr(d), d.shape[0]))
+            return
+        t = np.ascontiguousarray(translucent, np.uint32).reshape(-1, 4)
+        self._ck(self.lib.reb_render_forward2(self.h, _ptr(d), d.shape[0], _ptr(t), t.shape[0]))
 
     def sync(self):
         self._ck(self.lib.reb_sync(self.h))

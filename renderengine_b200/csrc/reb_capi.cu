@@ -17,7 +17,7 @@ namespace {
 
 std::string g_createError;
 
-struct PassState {               // per pass kind: 0 = shadow, 1 = forward
+struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaque), 2 = the translucent list of the base pass
     std::vector<reb_draw> draws; // last submitted list (host copy, for change detection and replay)
     DrawDev* dDraws = nullptr; uint32_t drawCap = 0;   // nDraws + 1 records (sentinel last)
     uint32_t nDraws = 0, nTris = 0;
@@ -65,6 +65,11 @@ struct reb_ctx {
     cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[2] = {nullptr, nullptr};
     void* asyncHost = nullptr; bool asyncOutstanding = false;   // last reb_readback_async target (re-copied if the frame is replayed)
     unsigned long long* vis = nullptr;
+    // translucent list (Appendix B.16, k_translucent.cu): per-pixel list heads, node pool, device counters {nodes, dropped, needs-clip};
+    // internal linear-colour / depth targets when the caller did not enable those outputs
+    uint32_t* tlHead = nullptr; uint4* tlNodes = nullptr; uint32_t tlCap = 0; uint32_t* tlCounters = nullptr;
+    float* tlHdr = nullptr; float* tlDepth = nullptr; size_t tlPx = 0;
+    bool tlFollows = false, tlPending = false; ShadeConst tlShade; uint32_t tlIdBase = 0; uint64_t tlDropped = 0;
     // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
     uint32_t samples = 1; float* msDepth = nullptr; uint32_t* msTriId = nullptr;
     // queues
@@ -76,10 +81,10 @@ struct reb_ctx {
     uint32_t* tileStart = nullptr; uint32_t tileStartCap = 0;
     bool shadowDeferred = false; float recordedSPV[16];   // reb_render_shadow recorded, not yet submitted
     uint32_t* tileList = nullptr; uint32_t listCap = 0;
-    uint32_t* dStatus = nullptr;     // 2 x 8 words
+    uint32_t* dStatus = nullptr;     // 3 x 8 words
     uint32_t* hStatus = nullptr;     // pinned + mapped mirror, written by the tile stage kernels
     uint32_t* hStatusDev = nullptr;  // device-side address of hStatus
-    PassState pass[2];
+    PassState pass[3];
     uint64_t launches = 0, regrows = 0;
     bool profiling = false; cudaEvent_t ev[2][7] = {}; float kernelMs[2][6] = {};   // per-kernel timing slots (diagnostics)
     uint64_t counters[4] = {0, 0, 0, 0};
@@ -261,7 +266,7 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
     if (slots > ps.cacheCap) {
         int rc;
         if ((rc = dev_alloc(ctx, &ps.vtxA, (size_t)slots))) return rc;
-        if (kind == 1 && (rc = dev_alloc(ctx, &ps.vtxBC, (size_t)slots))) return rc;
+        if (kind >= 1 && (rc = dev_alloc(ctx, &ps.vtxBC, (size_t)slots))) return rc;
         ps.cacheCap = (size_t)slots;
     }
     ps.cacheSize = (uint32_t)slots;
@@ -328,16 +333,16 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.nTris = ps.nTris; pc.nDraws = ps.nDraws;
     pc.cacheSize = ps.cacheSize; pc.deindexed = ps.deindexed;
     pc.indices = ctx->indices; pc.pos4 = ctx->pos4; pc.nrm4 = ctx->nrm4; pc.transforms = ctx->transforms; pc.nmats = ctx->nmats;
-    pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC; pc.vtxUV = (kind == 1 && !ctx->texHost.empty()) ? ps.vtxUV : nullptr;
+    pc.draws = ps.dDraws; pc.vtxA = ps.vtxA; pc.vtxBC = ps.vtxBC; pc.vtxUV = (kind >= 1 && !ctx->texHost.empty()) ? ps.vtxUV : nullptr;
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeAlloc; pc.clipQueue = ctx->clipQueue; pc.clipCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
-    pc.tileCount = ctx->tileCount[kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
+    pc.tileCount = ctx->tileCount[kind == 2 ? 1 : kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
     pc.flatSlots = ps.flatSlots;
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + 8 * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
-    if (kind == 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
+    if (kind >= 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
     else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; }
     pc.bandRows = pc.tilesY; pc.vTilesY = pc.tilesY;
     if (pc.nRanks > 1) {
@@ -354,7 +359,7 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     PassState& ps = ctx->pass[kind];
     int rc;
     if ((rc = ensure_large(ctx, ps.nTris))) return rc;
-    if (kind == 1 && !ctx->texHost.empty()) {
+    if (kind >= 1 && !ctx->texHost.empty()) {
         if (ps.cacheSize > ps.uvCap) {
             CU(cudaStreamSynchronize(ctx->stream));
             if ((rc = dev_alloc(ctx, &ps.vtxUV, (size_t)ps.cacheSize))) return rc;
@@ -372,7 +377,7 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
         }
     }
     fill_pass(ctx, kind, pc);
-    if ((rc = ensure_tiles(ctx, kind, pc.tilesX * pc.tilesY))) return rc;
+    if (kind < 2 && (rc = ensure_tiles(ctx, kind, pc.tilesX * pc.tilesY))) return rc;
     fill_pass(ctx, kind, pc);
     return REB_OK;
 }
@@ -435,11 +440,21 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         sh.shadingModel = ctx->shadingModel; sh.exposure = ctx->exposure; sh.debugInput = ctx->debugInput; sh.debugEquation = ctx->debugEquation;
         sh.maxDescriptors = ctx->maxDesc; sh.nTextures = (uint32_t)ctx->texHost.size(); sh.textures = ctx->dTextures;
         sh.outSRGB8 = ctx->outSRGB8; sh.outF32 = ctx->outF32; sh.outDepth = ctx->outDepth; sh.outTriId = ctx->outTriId;
+        ctx->tlShade = sh;   // (outputs as the caller enabled them; the translucent resolve writes these)
+        if (ctx->tlFollows) {   // Appendix B.16: the opaque pass leaves linear colour + depth for the translucent list; sky and encode come after it
+            sh.outSRGB8 = nullptr;
+            sh.outF32 = ctx->outF32 ? ctx->outF32 : ctx->tlHdr;
+            sh.outDepth = ctx->outDepth ? ctx->outDepth : ctx->tlDepth;
+        }
         if (ctx->skyFaces) {
             sh.skyFaces = ctx->skyFaces; sh.skyW = ctx->skyW; sh.skyH = ctx->skyH;
             sky_ray_matrix(ctx->view, ctx->proj, sh.skyAinv);
             sh.skyHw = 0.5f * (float)ctx->W; sh.skyHh = 0.5f * (float)ctx->H;
             sh.skyRhw = 1.0f / sh.skyHw; sh.skyRhh = 1.0f / sh.skyHh;
+            ShadeConst& t = ctx->tlShade;   // the same sky parameters for the translucent resolve, which draws it in that case
+            t.skyFaces = sh.skyFaces; t.skyW = sh.skyW; t.skyH = sh.skyH; std::memcpy(t.skyAinv, sh.skyAinv, sizeof t.skyAinv);
+            t.skyHw = sh.skyHw; t.skyHh = sh.skyHh; t.skyRhw = sh.skyRhw; t.skyRhh = sh.skyRhh;
+            if (ctx->tlFollows) sh.skyFaces = nullptr;
         }
     }
     if (kind == 1 && ctx->samples == 4) {
@@ -517,6 +532,31 @@ int submit_forward(reb_ctx* ctx) {
 
 // After a stream sync: look at the status words of the passes enqueued since the last check; grow the
 // tile-list queue and replay the frame if it overflowed (failure detection / recovery).
+// Appendix B.16: the translucent list of the base pass, after the opaque kernels on the same stream (k_translucent.cu).
+int run_translucent(reb_ctx* ctx) {
+    PassConst pc;
+    int rc;
+    if ((rc = prepare_pass(ctx, 2, pc))) return rc;
+    pc.tilesX = pc.tilesY = 0;                       // K0's prologue has no tile counters to re-arm for this list
+    pc.drawVisible = nullptr; pc.blockVisible = nullptr;
+    pc.status = ctx->dStatus + 16;
+    pc.hostStatus = nullptr;
+    ShadeConst sh = ctx->tlShade;
+    float* hdr = ctx->outF32 ? ctx->outF32 : ctx->tlHdr;
+    float* depth = ctx->outDepth ? ctx->outDepth : ctx->tlDepth;
+    CU(cudaMemsetAsync(ctx->tlCounters, 0, 16, ctx->stream));
+    if (pc.nTris) {
+        launch_vertex(pc, false, /*pdl=*/false, ctx->stream);
+        launch_tl_raster(pc, depth, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlCounters, ctx->numSMs, ctx->stream);
+        ctx->launches += 2;
+    }
+    pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
+    launch_tl_resolve(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, hdr, depth, ctx->tlCounters, ctx->stream); ctx->launches++;
+    CU(cudaGetLastError());
+    ctx->tlPending = true;
+    return REB_OK;
+}
+
 int check_and_recover(reb_ctx* ctx) {
     for (int iter = 0; iter < 8; ++iter) {
         bool overflow = false;
@@ -531,6 +571,13 @@ int check_and_recover(reb_ctx* ctx) {
         }
         if (!overflow) {
             ctx->pass[0].pending = ctx->pass[1].pending = false;
+            if (ctx->tlPending) {   // fragments / triangles the translucent pass had to drop (list capacity, Appendix B.3 clipping)
+                uint32_t c[4] = {0, 0, 0, 0};
+                CU(cudaMemcpy(c, ctx->tlCounters, 16, cudaMemcpyDeviceToHost));
+                ctx->tlDropped = (uint64_t)c[1] + c[2];
+                ctx->counters[0] += ctx->tlDropped;
+                ctx->tlPending = false;
+            }
             if (iter > 0 && ctx->asyncOutstanding && ctx->asyncHost && ctx->outSRGB8) {   // the frame was replayed: refresh the async copy
                 CU(cudaMemcpyAsync(ctx->asyncHost, ctx->outSRGB8, (size_t)ctx->W * ctx->H * 4, cudaMemcpyDeviceToHost, ctx->stream));
                 CU(cudaStreamSynchronize(ctx->stream));
@@ -549,6 +596,7 @@ int check_and_recover(reb_ctx* ctx) {
             if (k == 0) std::memcpy(pc.PV, ctx->recordedSPV, 64);
             if ((rc = run_pass(ctx, k, pc, false))) return rc;
         }
+        if (p1 && ctx->tlPending && (rc = run_translucent(ctx))) return rc;   // the opaque frame was replayed under it
         CU(cudaStreamSynchronize(ctx->stream));
     }
     return fail(ctx, REB_E_OVERFLOW, "tile-list queue kept overflowing after 8 regrow attempts");

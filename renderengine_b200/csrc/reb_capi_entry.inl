@@ -36,7 +36,7 @@ int reb_create(const reb_params* params, reb_ctx** out) {
     if (ctx->rank >= ctx->nRanks || ctx->bandH % TILE_H) return bail(fail(ctx, REB_E_INVALID, "reb_create: bad partition (rank < n_ranks, band_h multiple of 8)"));
     int rc;
     if ((rc = alloc_targets(ctx))) return bail(rc);
-    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 64) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 64) != cudaSuccess ||
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 96) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 96) != cudaSuccess ||
         cudaMalloc(reinterpret_cast<void**>(&ctx->huge), 2 * HUGE_CAP * sizeof(LargeRec)) != cudaSuccess ||
         cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->hStatusDev), ctx->hStatus, 0) != cudaSuccess)
@@ -59,7 +59,10 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots,
                     ctx->pass[0].drawBounds, ctx->pass[1].drawBounds, ctx->pass[0].drawVisible, ctx->pass[1].drawVisible,
-                    ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible};
+                    ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible,
+                    ctx->pass[2].dDraws, ctx->pass[2].vtxA, ctx->pass[2].vtxBC, ctx->pass[2].blockDraw, ctx->pass[2].flatSlots, ctx->pass[2].drawBounds,
+                    ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
+                    ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
@@ -88,7 +91,7 @@ int reb_upload_geometry(reb_ctx* ctx, const void* verts, uint64_t nVerts, const 
     if ((rc = dev_alloc(ctx, &ctx->nrm4, nVerts))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->indices, nIdx))) return rc;
     ctx->nVerts = nVerts; ctx->nIdx = nIdx;
-    ctx->pass[0].valid = ctx->pass[1].valid = false;
+    ctx->pass[0].valid = ctx->pass[1].valid = ctx->pass[2].valid = false;
     if (nVerts) {
         float4* aos = nullptr;
         CU(cudaMalloc(reinterpret_cast<void**>(&aos), nVerts * 32));
@@ -114,7 +117,7 @@ int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
     if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->nmats, (size_t)nNodes * 12))) return rc;
     ctx->nNodes = nNodes;
-    ctx->pass[0].valid = ctx->pass[1].valid = false;   // draws are validated against the node count
+    ctx->pass[0].valid = ctx->pass[1].valid = ctx->pass[2].valid = false;   // draws are validated against the node count
     if (!nNodes) return REB_OK;
     std::vector<float> nm((size_t)nNodes * 12);
     for (uint32_t n = 0; n < nNodes; ++n) normal_matrix12(m + 16 * (size_t)n, &nm[12 * (size_t)n]);
@@ -244,7 +247,7 @@ int reb_render_shadow(reb_ctx* ctx, uint32_t shadowId, const reb_draw* draws, ui
     return REB_OK;
 }
 
-int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
+static int render_base_pass(reb_ctx* ctx, const reb_draw* draws, uint32_t n, const reb_draw* translucent, uint32_t nTranslucent) {
     CHECK_CTX();
     if (!ctx->haveView) return fail(ctx, REB_E_INVALID, "reb_render_forward before reb_set_view");
     if (!draws && n) return fail(ctx, REB_E_INVALID, "reb_render_forward: null draws");
@@ -258,7 +261,34 @@ int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) {
         return fail(ctx, REB_E_INVALID, "reb_render_forward: the Phong model needs 112-B Light records (phong.glsl:20-37)");
     CU(cudaSetDevice(ctx->device));
     if ((rc = set_draws(ctx, 1, draws, n))) return rc;
-    return submit_forward(ctx);
+    ctx->tlFollows = nTranslucent > 0;
+    if (!ctx->tlFollows) return submit_forward(ctx);
+    // Appendix B.16: the translucent list of the same base pass (RenderScene.cpp:226-227)
+    if (!translucent) return fail(ctx, REB_E_INVALID, "reb_render_forward2: null translucent draws");
+    if (ctx->samples != 1) return fail(ctx, REB_E_UNSUPPORTED, "reb_render_forward2: translucent draws are not supported with 4x multisampling yet");
+    if ((rc = set_draws(ctx, 2, translucent, nTranslucent))) return rc;
+    const size_t px = (size_t)ctx->W * ctx->H;
+    if (ctx->tlPx != px) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        const uint32_t cap = (uint32_t)std::min<size_t>(std::max<size_t>(4 * px, (size_t)1 << 20), (size_t)1 << 28);
+        if ((rc = dev_alloc(ctx, &ctx->tlHead, px)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)4)) ||
+            (rc = dev_alloc(ctx, &ctx->tlHdr, ctx->outF32 ? 0 : px * 4)) || (rc = dev_alloc(ctx, &ctx->tlDepth, ctx->outDepth ? 0 : px))) return rc;
+        launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, px, ctx->numSMs, ctx->stream); ctx->launches++;
+        ctx->tlCap = cap; ctx->tlPx = px;
+    }
+    uint64_t nOpaque = 0;
+    for (uint32_t i = 0; i < n; ++i) nOpaque += draws[i].nbIndices / 3;
+    ctx->tlIdBase = (uint32_t)nOpaque;               // triangle IDs continue after the opaque list
+    if ((rc = submit_forward(ctx))) { ctx->tlFollows = false; return rc; }
+    rc = run_translucent(ctx);
+    ctx->tlFollows = false;
+    return rc;
+}
+
+int reb_render_forward(reb_ctx* ctx, const reb_draw* draws, uint32_t n) { return render_base_pass(ctx, draws, n, nullptr, 0); }
+
+int reb_render_forward2(reb_ctx* ctx, const reb_draw* opaque, uint32_t nOpaque, const reb_draw* translucent, uint32_t nTranslucent) {
+    return render_base_pass(ctx, opaque, nOpaque, translucent, nTranslucent);
 }
 
 int reb_set_shading_model(reb_ctx* ctx, uint32_t model) {

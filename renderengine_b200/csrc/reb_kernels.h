@@ -54,6 +54,10 @@ void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, 
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
+// Appendix B.16 (k_translucent.cu): per-pixel fragment lists of the translucent triangles, then the ordered blend
+void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, int numSMs, cudaStream_t st);
+void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,
+                       uint32_t* counters, cudaStream_t st);
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st);   // between the sample passes of a multisampled frame
 // Appendix B.15 resolve: per pixel, shade every distinct primitive of the 4 sample planes once at the pixel centre, average
 void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st);

@@ -182,7 +182,7 @@ __device__ __forceinline__ uint32_t pack_srgb8(float4 c) {
 // Appendix B.3 / B.10 (revision r1c): perspective-correct weights of a CLIPPED parent triangle at pixel centre (px, py), in
 // homogeneous form from its clip-space vertices c_k = PV * (world_k, 1) (exactly what K0 computed):
 // lambda = adj([c0 c1 c2]) * (xn, yn, 1) over the (x, y, w) rows.  Rare path, kept out of line.
-__device__ __noinline__ float4 homogeneous_weights(const PassConst& pc, V3 w0, V3 w1, V3 w2, float px, float py) {
+static __device__ __noinline__ float4 homogeneous_weights(const PassConst& pc, V3 w0, V3 w1, V3 w2, float px, float py) {
     const float hw = 0.5f * (float)pc.W, hh = 0.5f * (float)pc.H;
     const float xn = ((px + 0.5f) - hw) / hw, yn = ((py + 0.5f) - hh) / hh;
     const float4 c0 = mat4_mul_point(pc.PV, w0.x, w0.y, w0.z), c1 = mat4_mul_point(pc.PV, w1.x, w1.y, w1.z), c2 = mat4_mul_point(pc.PV, w2.x, w2.y, w2.z);

@@ -51,7 +51,7 @@ __device__ __forceinline__ float4 cube_texel(const uint16_t* __restrict__ faces,
 
 // Colour of the skybox through the centre of pixel (x, y).  Kept out of line: it runs for background pixels only and
 // must not weigh on the register budget of the shading path.
-__device__ __noinline__ float4 sky_pixel(const ShadeConst& sh, int x, int y) {
+static __device__ __noinline__ float4 sky_pixel(const ShadeConst& sh, int x, int y) {
     const float xn = (((float)x + 0.5f) - sh.skyHw) * sh.skyRhw, yn = (((float)y + 0.5f) - sh.skyHh) * sh.skyRhh;
     const float* a = sh.skyAinv;
     const float rx = (a[0] * xn + a[3] * yn) + a[6], ry = (a[1] * xn + a[4] * yn) + a[7], rz = (a[2] * xn + a[5] * yn) + a[8];
