@@ -152,6 +152,10 @@ void MaterialSystem::Draw(Renderer& renderer, const std::vector<MeshDrawInfo>& d
     const std::vector<reb_draw> d = Renderer::ToDraws(drawCalls);
     renderer.Check(reb_render_forward(renderer.GetContext(), d.data(), (uint32_t)d.size()), "MaterialSystem::Draw");
 }
+void MaterialSystem::Draw(Renderer& renderer, const std::vector<MeshDrawInfo>& opaque, const std::vector<MeshDrawInfo>& translucent) const {
+    const std::vector<reb_draw> o = Renderer::ToDraws(opaque), t = Renderer::ToDraws(translucent);
+    renderer.Check(reb_render_forward2(renderer.GetContext(), o.data(), (uint32_t)o.size(), t.data(), (uint32_t)t.size()), "MaterialSystem::Draw");
+}
 
 // ---- CameraViewSystem -------------------------------------------------------------------------------------------------
 CameraViewSystem::CameraViewSystem(uint32_t imageWidth, uint32_t imageHeight)
@@ -289,12 +293,9 @@ void RenderScene::RenderShadowDepthPass() const {   // RenderScene.cpp:191-208: 
     m_shadowSystem->Render(drawCalls);
 }
 void RenderScene::RenderBasePass() const {
-    // RenderScene.cpp:210-232 issues the opaque list then the translucent list inside one render pass.  The CUDA forward
-    // pass resolves one frame per call, so both lists go down together in that order; src-alpha blending of the
-    // translucent list (GraphicsPipelineCache.cpp:305-315) is a "next" row — they are drawn opaque.
-    std::vector<MeshDrawInfo> drawCalls(m_opaqueMeshes);
-    drawCalls.insert(drawCalls.end(), m_translucentMeshes.begin(), m_translucentMeshes.end());
-    m_materialSystem->Draw(*m_renderer, drawCalls);
+    // RenderScene.cpp:210-232 issues the opaque list, then the translucent list (sorted back to front by Update), then the
+    // skybox inside one render pass: one reb_render_forward2 call.
+    m_materialSystem->Draw(*m_renderer, m_opaqueMeshes, m_translucentMeshes);
 }
 
 }  // namespace reb

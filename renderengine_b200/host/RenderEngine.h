@@ -201,6 +201,8 @@ public:
     MaterialHandle CreateMaterialInstance(const MaterialInstanceInfo& materialInfo);   // MaterialSystem.cpp:49-59
     void UploadToGPU(Renderer& renderer);                                               // MaterialSystem.cpp:68-86
     void Draw(Renderer& renderer, const std::vector<MeshDrawInfo>& drawCalls) const;     // MaterialSystem.cpp:88-101 -> reb_render_forward
+    // both Draw calls of RenderScene::RenderBasePass (RenderScene.cpp:226-227) as one base pass -> reb_render_forward2
+    void Draw(Renderer& renderer, const std::vector<MeshDrawInfo>& opaque, const std::vector<MeshDrawInfo>& translucent) const;
     size_t GetMaterialInstanceCount() const { return m_properties.size(); }
     const std::vector<MaterialProperties>& GetProperties() const { return m_properties; }   // (facade extension)
     bool IsTranslucent(MaterialHandle h) const { return m_pipelineProperties.at(h.GetIndex()).alphaMode == AlphaMode::eBlend; }

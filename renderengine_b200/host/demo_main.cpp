@@ -52,12 +52,13 @@ template <class T> void put(FILE* f, const T* p, size_t n) { std::fwrite(p, size
 }  // namespace
 
 int main(int argc, char** argv) {
-    if (argc < 8) { std::fprintf(stderr, "usage: %s nx nz level width height shadowSize frames [dump.bin [skyFaceSize]]\n", argv[0]); return 2; }
+    if (argc < 8) { std::fprintf(stderr, "usage: %s nx nz level width height shadowSize frames [dump.bin [skyFaceSize [translucentEvery]]]\n", argv[0]); return 2; }
     const int nx = std::atoi(argv[1]), nz = std::atoi(argv[2]), level = std::atoi(argv[3]);
     const uint32_t W = (uint32_t)std::atoi(argv[4]), H = (uint32_t)std::atoi(argv[5]), S = (uint32_t)std::atoi(argv[6]);
     const int frames = std::atoi(argv[7]);
     const char* dump = argc > 8 ? argv[8] : nullptr;
     const uint32_t skyN = argc > 9 ? (uint32_t)std::atoi(argv[9]) : 0u;
+    const int translucentEvery = argc > 10 ? std::atoi(argv[10]) : 0;   // every k-th material is AlphaMode::eBlend with alpha 0.5
     try {
         Renderer renderer(W, H);
         RenderScene scene(renderer, S ? S : 4096);
@@ -72,6 +73,7 @@ int main(int argc, char** argv) {
             MaterialInstanceInfo info;
             for (int c = 0; c < 3; ++c) { info.properties.diffuse[c] = palette[m][c]; info.properties.specular[c] = 0.5f; }
             info.properties.shininess = (float)(8 << (m % 4));
+            if (translucentEvery > 0 && m % translucentEvery == 0) { info.properties.diffuse[3] = 0.5f; info.pipelineProperties.alphaMode = AlphaMode::eBlend; }
             mats.push_back(materials.CreateMaterialInstance(info));
         }
         MaterialInstanceInfo groundInfo;
@@ -173,7 +175,9 @@ int main(int argc, char** argv) {
             renderer.Readback(REB_COLOR_SRGB8, col8.data()); renderer.Readback(REB_COLOR_F32, colf.data());
             put(f, shadow.data(), shadow.size()); put(f, depth.data(), depth.size()); put(f, tri.data(), tri.size());
             put(f, col8.data(), col8.size()); put(f, colf.data(), colf.size());
-            if (skyN) { put(f, &skyN, 1); put(f, skyFaces.data(), skyFaces.size()); }
+            const uint32_t trailer[2] = {skyN, (uint32_t)scene.GetTranslucentMeshes().size()};   // the last trailer[1] draws are the translucent list
+            put(f, trailer, 2);
+            if (skyN) put(f, skyFaces.data(), skyFaces.size());
             std::fclose(f);
         }
     } catch (const std::exception& e) {

@@ -29,9 +29,12 @@ def load_dump(path):
     s["shadow_view"] = take(64, np.float32, (16,)); s["shadow_proj"] = take(64, np.float32, (16,))
     out = dict(shadow=take(S * S * 4, np.float32, (S, S)), depth=take(W * H * 4, np.float32, (H, W)), tri_id=take(W * H * 4, np.uint32, (H, W)),
                color_srgb8=take(W * H * 4, np.uint8, (H, W, 4)), color_f32=take(W * H * 16, np.float32, (H, W, 4)))
-    if off[0] != raw.size:   # optional trailer: skybox faces
-        n = int(take(4, np.uint32, (1,))[0])
+    n, n_tl = (int(v) for v in take(8, np.uint32, (2,)))   # trailer: skybox face size, length of the translucent list
+    if n:
         s["skybox"] = take(6 * n * n * 8, np.uint16, (6, n, n, 4))
+    if n_tl:
+        s["translucent_draws"] = s["draws"][nD - n_tl:].copy()
+        s["draws"] = s["draws"][:nD - n_tl].copy()
     assert off[0] == raw.size
     s["n_triangles"] = nI // 3; s["n_vertices"] = nV
     return s, out
@@ -79,6 +82,28 @@ def test_host_facade_skybox_matches_oracle(tmp_path):
     sky = ref["tri_id"] == 0xFFFFFFFF
     assert sky.mean() > 0.05 and np.array_equal(gpu["color_f32"][sky].view(np.uint32), ref["color_f32"][sky].view(np.uint32))
     assert (gpu["color_f32"][sky][:, 2] > 0.1).all()       # every face tone is >= 9000 / 65535
+
+
+@pytest.mark.gpu
+def test_host_facade_translucent_meshes_match_oracle(tmp_path):
+    """AlphaMode::eBlend materials: RenderScene splits the meshes, sorts the translucent ones back to front every Update
+    (RenderScene.cpp:127-159) and draws them after the opaque list in one base pass (reb_render_forward2)."""
+    from oracle import orc
+    from renderengine_b200 import build
+    exe = build.build_host()
+    dump = str(tmp_path / "tl.bin")
+    r = subprocess.run([exe, "3", "3", "2", "320", "180", "256", "2", dump, "8", "2"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s, gpu = load_dump(dump)
+    assert len(s["translucent_draws"]) > 0 and len(s["draws"]) > 0
+    s_all = dict(s, draws=np.concatenate([s["draws"], s["translucent_draws"]])); s_all.pop("translucent_draws")
+    ref_shadow = orc.Oracle(s_all).render_shadow()
+    assert np.array_equal(gpu["shadow"].view(np.uint32), ref_shadow.view(np.uint32))
+    ref = orc.Oracle(s).render_forward(ref_shadow)
+    assert np.array_equal(gpu["tri_id"], ref["tri_id"]) and np.array_equal(gpu["depth"].view(np.uint32), ref["depth"].view(np.uint32))
+    assert np.abs(gpu["color_srgb8"].astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
+    n_opaque = int(sum(int(d[1]) // 3 for d in s["draws"]))
+    assert ((ref["tri_id"] != 0xFFFFFFFF) & (ref["tri_id"] >= n_opaque)).mean() > 0.03
 
 
 @pytest.mark.gpu
