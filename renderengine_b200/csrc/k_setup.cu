@@ -181,49 +181,11 @@ __device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uin
 // first vertex, and send every child through the ordinary viewport / snap / facing / bbox steps into the large-triangle
 // path with the parent's triId.  Returns true when a child was queued into the binned path.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float k1_clip_dist(int plane, float4 v, float Gx, float Gy) {
-    switch (plane) {
-        case 0: return v.z;
-        case 1: return v.x + Gx * v.w;
-        case 2: return Gx * v.w - v.x;
-        case 3: return v.y + Gy * v.w;
-        default: return Gy * v.w - v.y;
-    }
-}
 template <bool SHADOW>
 __device__ __noinline__ bool k1_clip_emit(const PassConst& pc, uint32_t tri, unsigned lane) {
-    const uint32_t d = find_draw<false>(pc.draws, pc.nDraws, tri);
-    const uint32_t* ix = pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri));
-    const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * __ldg(&pc.draws[d].node);
-    float T[16];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { const float4 q = __ldg(Tq + k); T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
-    float4 a[9], b[9];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const float4 p = __ldg(pc.pos4 + __ldg(ix + k));
-        a[k] = vertex_stage<!SHADOW>(pc.PV, T, p.x, p.y, p.z, nullptr);
-    }
-    const float Gx = (0.5f * GUARD_PX) / (0.5f * (float)pc.W), Gy = (0.5f * GUARD_PX) / (0.5f * (float)pc.H);
-    int n = 3;
-    for (int plane = 0; plane < 5; ++plane) {
-        int m = 0;
-        for (int i = 0; i < n; ++i) {
-            const float4 P = a[i], Q = a[i + 1 == n ? 0 : i + 1];
-            const float dP = k1_clip_dist(plane, P, Gx, Gy), dQ = k1_clip_dist(plane, Q, Gx, Gy);
-            const bool inP = dP >= 0.0f, inQ = dQ >= 0.0f;
-            if (inP) b[m++] = P;
-            if (inP != inQ) {
-                const float4 I = inP ? P : Q, O = inP ? Q : P;
-                const float dI = inP ? dP : dQ, dO = inP ? dQ : dP;
-                const float t = dI / (dI - dO);
-                b[m++] = make_float4(I.x + t * (O.x - I.x), I.y + t * (O.y - I.y), I.z + t * (O.z - I.z), I.w + t * (O.w - I.w));
-            }
-        }
-        n = m;
-        if (n < 3) return false;
-        for (int k = 0; k < n; ++k) a[k] = b[k];
-    }
+    float4 a[9];
+    const int n = clip_parent<SHADOW>(pc, tri, a);
+    if (n < 3) return false;
     bool queued = false;
     VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
     v0.X += pc.shiftX; v0.Y += pc.shiftY;   // B.15 sample shift

@@ -11,8 +11,7 @@
 //                 A = As*(1-As) in linear float on the colour the opaque pass left, depth / ID write — then the skybox
 //                 (drawn after the translucent list, RenderScene.cpp:228) where the depth is still 1.0, then the encode.
 // Same individually rounded operations as oracle/oracle.cpp.  Limits of this first version: a pixel keeps at most
-// TL_MAX_FRAGS fragments and the frame at most `cap` list nodes (the excess is dropped and counted); translucent
-// triangles that need Appendix B.3 clipping are dropped and counted.
+// TL_MAX_FRAGS fragments and the frame at most `cap` list nodes (the excess is dropped and counted).
 #include "reb_shade.cuh"
 #include "reb_shade_pbr.cuh"
 #include "reb_sky.cuh"
@@ -21,6 +20,62 @@ namespace reb {
 
 constexpr uint32_t TL_NONE = 0xFFFFFFFFu;
 constexpr int TL_MAX_FRAGS = 16;
+
+// One snapped triangle (a parent or a clip child), rasterised by the whole CTA: warps over rows, lanes over columns.
+__device__ __forceinline__ void tl_raster_tri(const PassConst& pc, VtxA a[3], uint32_t tri, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
+                                              uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, unsigned lane, unsigned warp) {
+    long long A2 = mulw(a[1].X - a[0].X, a[2].Y - a[0].Y) - mulw(a[2].X - a[0].X, a[1].Y - a[0].Y);
+    if (A2 == 0) return;
+    if (A2 > 0) { const VtxA t = a[1]; a[1] = a[2]; a[2] = t; A2 = -A2; }                          // cull none (Appendix B.16)
+    const int32_t minX = min(a[0].X, min(a[1].X, a[2].X)), maxX = max(a[0].X, max(a[1].X, a[2].X));
+    const int32_t minY = min(a[0].Y, min(a[1].Y, a[2].Y)), maxY = max(a[0].Y, max(a[1].Y, a[2].Y));
+    const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+    const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+    if (x0 > x1 || y0 > y1) return;
+    int32_t A[3], B[3], bias[3]; long long E[3];   // unbiased edge value at the centre of pixel (0, 0)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int p = (k + 1) % 3, q = (k + 2) % 3;
+        A[k] = a[q].Y - a[p].Y; B[k] = -(a[q].X - a[p].X);
+        bias[k] = ((A[k] > 0) || (A[k] == 0 && B[k] > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
+        E[k] = mulw(A[k], 128 - a[p].X) + mulw(B[k], 128 - a[p].Y);
+    }
+    const float inv = 1.0f / (float)(-A2);
+    const float z0 = a[0].z, dz1 = a[1].z - a[0].z, dz2 = a[2].z - a[0].z;
+    for (int y = y0 + (int)warp; y <= y1; y += 8) {
+        if (!row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) continue;
+        for (int x = x0 + (int)lane; x <= x1; x += 32) {
+            const long long F0 = E[0] + mulw(A[0], 256 * x) + mulw(B[0], 256 * y);
+            const long long F1 = E[1] + mulw(A[1], 256 * x) + mulw(B[1], 256 * y);
+            const long long F2 = E[2] + mulw(A[2], 256 * x) + mulw(B[2], 256 * y);
+            if (((F0 - bias[0]) | (F1 - bias[1]) | (F2 - bias[2])) < 0) continue;
+            const float z = depth_from((float)F1, (float)F2, inv, z0, dz1, dz2);
+            if (!(z >= 0.0f && z <= 1.0f)) continue;                                              // Appendix B.8 depth clip
+            const size_t p = (size_t)y * pc.W + x;
+            if (!(z <= __ldg(opaqueDepth + p))) continue;     // the running depth only ever gets nearer than the opaque depth
+            const uint32_t idx = atomicAdd(&counters[0], 1u);
+            if (idx >= cap) { atomicAdd(&counters[1], 1u); continue; }
+            nodes[idx] = make_uint4(atomicExch(&head[p], idx), tri, __float_as_uint(z), 0u);
+        }
+    }
+}
+
+// Appendix B.3 for a translucent parent (CTA-uniform: every thread clips the same triangle): the children of the fan go
+// through the same snap / facing / raster steps and append the PARENT's ID (children of one fan share edges, which the
+// top-left rule assigns to exactly one of them).
+__device__ __noinline__ void tl_clip_raster(const PassConst& pc, uint32_t tri, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
+                                            uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, unsigned lane, unsigned warp) {
+    float4 c[9];
+    const int n = clip_parent<false>(pc, tri, c);
+    for (int i = 1; i + 1 < n; ++i) {
+        VtxA a[3] = {viewport_snap(c[0], pc.W, pc.H), viewport_snap(c[i], pc.W, pc.H), viewport_snap(c[i + 1], pc.W, pc.H)};
+        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
+            if (threadIdx.x == 0) atomicAdd(&counters[2], 1u);
+            continue;
+        }
+        tl_raster_tri(pc, a, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
+    }
+}
 
 __global__ void __launch_bounds__(256) k_tl_raster(const __grid_constant__ PassConst pc, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
                                                    uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters) {
@@ -37,41 +92,8 @@ __global__ void __launch_bounds__(256) k_tl_raster(const __grid_constant__ PassC
             a[k] = {(int32_t)q.x, (int32_t)q.y, __uint_as_float(q.z), q.w};
         }
         if ((a[0].flags & a[1].flags & a[2].flags & VF_PLANES) != 0u) continue;                       // Appendix B.2
-        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) { if (threadIdx.x == 0) atomicAdd(&counters[2], 1u); continue; }
-        long long A2 = mulw(a[1].X - a[0].X, a[2].Y - a[0].Y) - mulw(a[2].X - a[0].X, a[1].Y - a[0].Y);
-        if (A2 == 0) continue;
-        if (A2 > 0) { const VtxA t = a[1]; a[1] = a[2]; a[2] = t; A2 = -A2; }                          // cull none (Appendix B.16)
-        const int32_t minX = min(a[0].X, min(a[1].X, a[2].X)), maxX = max(a[0].X, max(a[1].X, a[2].X));
-        const int32_t minY = min(a[0].Y, min(a[1].Y, a[2].Y)), maxY = max(a[0].Y, max(a[1].Y, a[2].Y));
-        const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
-        const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
-        if (x0 > x1 || y0 > y1) continue;
-        int32_t A[3], B[3], bias[3]; long long E[3];   // unbiased edge value at the centre of pixel (0, 0)
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int p = (k + 1) % 3, q = (k + 2) % 3;
-            A[k] = a[q].Y - a[p].Y; B[k] = -(a[q].X - a[p].X);
-            bias[k] = ((A[k] > 0) || (A[k] == 0 && B[k] > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
-            E[k] = mulw(A[k], 128 - a[p].X) + mulw(B[k], 128 - a[p].Y);
-        }
-        const float inv = 1.0f / (float)(-A2);
-        const float z0 = a[0].z, dz1 = a[1].z - a[0].z, dz2 = a[2].z - a[0].z;
-        for (int y = y0 + (int)warp; y <= y1; y += 8) {
-            if (!row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) continue;
-            for (int x = x0 + (int)lane; x <= x1; x += 32) {
-                const long long F0 = E[0] + mulw(A[0], 256 * x) + mulw(B[0], 256 * y);
-                const long long F1 = E[1] + mulw(A[1], 256 * x) + mulw(B[1], 256 * y);
-                const long long F2 = E[2] + mulw(A[2], 256 * x) + mulw(B[2], 256 * y);
-                if (((F0 - bias[0]) | (F1 - bias[1]) | (F2 - bias[2])) < 0) continue;
-                const float z = depth_from((float)F1, (float)F2, inv, z0, dz1, dz2);
-                if (!(z >= 0.0f && z <= 1.0f)) continue;                                              // Appendix B.8 depth clip
-                const size_t p = (size_t)y * pc.W + x;
-                if (!(z <= __ldg(opaqueDepth + p))) continue;     // the running depth only ever gets nearer than the opaque depth
-                const uint32_t idx = atomicAdd(&counters[0], 1u);
-                if (idx >= cap) { atomicAdd(&counters[1], 1u); continue; }
-                nodes[idx] = make_uint4(atomicExch(&head[p], idx), tri, __float_as_uint(z), 0u);
-            }
-        }
+        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) tl_clip_raster(pc, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
+        else tl_raster_tri(pc, a, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
     }
 }
 

@@ -414,8 +414,8 @@ def view_from(scene, eye, look, fov=45.0, near=0.01, far=100.0):
     return pack_view(view, proj, eye)
 
 
-def to_translucent(scene, every=3, alpha=0.45, view=None):
-    """Make every `every`-th material translucent (AlphaMode::eBlend, alpha in the material's diffuse / base-colour alpha)
+def to_translucent(scene, every=3, alpha=0.45, view=None, which=None):
+    """Make every `every`-th material (or the materials listed in `which`) translucent (AlphaMode::eBlend, alpha in the material's diffuse / base-colour alpha)
     and split the draw list the way RenderScene does: opaque draws stay in `draws` (sorted by material, node:
     RenderScene.cpp:105-125), translucent ones go to `translucent_draws` sorted back to front by
     dot(viewInverse[2], cameraPosition - nodeTranslation), then material, then node (RenderScene.cpp:127-159)."""
@@ -423,7 +423,7 @@ def to_translucent(scene, every=3, alpha=0.45, view=None):
     mats = np.array(scene["materials"], np.uint8).copy()
     n_mat = mats.shape[0]
     tl = np.zeros(n_mat, bool)
-    tl[np.arange(0, n_mat, every)] = True
+    tl[np.arange(0, n_mat, every) if which is None else np.asarray(which, np.int64)] = True
     for m in np.nonzero(tl)[0]:
         mats[m, 12:16] = np.frombuffer(f32(alpha).tobytes(), np.uint8)
     s["materials"] = mats

@@ -644,3 +644,35 @@ def test_parity_translucent_pass(variant):
     ref = orc.Oracle(so).render_forward(ref_shadow)
     assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"])
     assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
+
+
+def test_parity_translucent_triangles_clipped_at_the_eye_plane():
+    """Appendix B.3 on the translucent list: camera inside the scene, the translucent ground plane crosses the eye plane and
+    the guard band — its clip children are rasterised (cull none applies per child) and blended with the parent's ID."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    n_mat = np.asarray(s["materials"]).shape[0]
+    which = [1, 3, n_mat - 1]                                   # the last material is the ground plane's
+    ref_shadow = orc.Oracle(dict(s)).render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(sc.to_translucent(s, which=which))
+    for eye, look in INSIDE_VIEWS:
+        v = sc.view_from(s, eye, look)
+        st = sc.to_translucent(s, which=which, view=v)
+        st["view"] = v
+        ground_id = int(sum(int(d[1]) // 3 for d in st["draws"])) + int(sum(int(d[1]) // 3 for d in st["translucent_draws"][:[int(d[1]) for d in st["translucent_draws"]].index(6)]))
+        o = orc.Oracle(st)
+        ref = o.render_forward(ref_shadow)
+        ctx.set_view(v)
+        ctx.render_shadow(np.concatenate([st["draws"], st["translucent_draws"]]))
+        ctx.render_forward(st["draws"], st["translucent_draws"])
+        gpu = dict(tri_id=ctx.readback(capi.REB_TRIID_U32), depth=ctx.readback(capi.REB_DEPTH_F32),
+                   color_f32=ctx.readback(capi.REB_COLOR_F32), color_srgb8=ctx.readback(capi.REB_COLOR_SRGB8))
+        assert ctx.counters()[0] == 0 and o.counters[0] == 0    # nothing dropped
+        assert np.array_equal(gpu["tri_id"], ref["tri_id"]), f"triangle IDs differ at {np.count_nonzero(gpu['tri_id'] != ref['tri_id'])} pixels"
+        assert np.array_equal(gpu["depth"].view(np.uint32), ref["depth"].view(np.uint32))
+        d8 = np.abs(gpu["color_srgb8"].astype(np.int32) - ref["color_srgb8"].astype(np.int32))
+        assert d8.max() <= 1, f"sRGB8 colour differs by {d8.max()} LSB at {np.count_nonzero(d8 > 1)} channel samples"
+        assert _psnr(gpu["color_f32"], ref["color_f32"]) >= 50.0
+    assert ((ref["tri_id"] == ground_id) | (ref["tri_id"] == ground_id + 1)).mean() > 0.05       # the clipped translucent ground is on screen
