@@ -121,6 +121,8 @@ def build_scene(args):
     scene = sc.make_scene(args.config)
     if args.shading == "pbr":
         scene = sc.to_pbr(scene)
+    if getattr(args, "translucent_every", 0) > 0:
+        scene = sc.to_translucent(scene, every=args.translucent_every)
     return scene
 
 
@@ -170,6 +172,8 @@ def main():
                     help="phong = BASELINE.json's path (default); pbr = the reference's live surface_pbr.frag path (SURVEY 8f row 1)")
     ap.add_argument("--samples", type=int, default=1, choices=[1, 4],
                     help="samples per pixel of the base pass (4 = Appendix B.15 multisampling; the headline metric is quoted at 1)")
+    ap.add_argument("--translucent-every", type=int, default=0,
+                    help="make every K-th material AlphaMode::eBlend (alpha 0.45): its draws go through the translucent pass (SURVEY 8f row 3); 0 = all opaque (headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -214,6 +218,8 @@ def main():
     if not tiles and world > 1:
         ctx.set_view(sc.view_for_azimuth(scene, 2 * np.pi * rank / world))   # one camera view per rank
     draws = scene["draws"]
+    tl_draws = scene.get("translucent_draws")                    # drawn after the opaque list, blended (reb_render_forward2)
+    shadow_draws = draws if tl_draws is None else np.concatenate([draws, tl_draws])   # RenderScene.cpp:191-208: both lists cast shadows
     shadow_t = None
     if S and (bcast or slabs):
         ptr, _ = ctx.output_ptr(capi.REB_SHADOW_F32)
@@ -224,20 +230,20 @@ def main():
     def step():
         if S:
             if slabs:
-                ctx.render_shadow(draws)
+                ctx.render_shadow(shadow_draws)
                 ctx.flush()                                      # the recorded depth pass must be on the stream before the exchange
                 parallel.allgather_shadow_slabs(shadow_t)        # NCCL over NVLink; ordered on the current stream
                 ctx.shadow_mark_valid()
             elif not bcast:
-                ctx.render_shadow(draws)
+                ctx.render_shadow(shadow_draws)
             else:
                 if rank == 0:
-                    ctx.render_shadow(draws)
+                    ctx.render_shadow(shadow_draws)
                     ctx.flush()                                  # the recorded depth pass must be on the stream before the broadcast
                 parallel.broadcast_shadow(shadow_t, src=0)   # NCCL over NVLink; ordered on the current stream
                 if rank != 0:
                     ctx.shadow_mark_valid()
-        ctx.render_forward(draws)
+        ctx.render_forward(draws, tl_draws)
 
     def barrier():
         torch.cuda.synchronize()
@@ -278,7 +284,7 @@ def main():
             evf = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(min(args.steps, 50))]
             for a, b in evf:
                 flush.add_(1)
-                a.record(st); ctx.render_forward(draws); b.record(st)
+                a.record(st); ctx.render_forward(draws, tl_draws); b.record(st)
             ctx.sync()
             fwd_only = np.array([a.elapsed_time(b) for a, b in evf])
 
@@ -289,8 +295,8 @@ def main():
         for _ in range(n_prof):
             flush.add_(1)
             if S and (not bcast or rank == 0):
-                ctx.render_shadow(draws)
-            ctx.render_forward(draws)
+                ctx.render_shadow(shadow_draws)
+            ctx.render_forward(draws, tl_draws)
             ctx.sync()
             for k in (0, 1):
                 if k == 0 and not (S and (not bcast or rank == 0)):
@@ -350,7 +356,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "frames_per_s": frames_per_step * 1e3 / ms,
-            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong") + (", 4x MSAA base pass" if args.samples == 4 else ""),
+            "config": {"workload": f"{args.config}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + (", PBR fragment path (3 lights)" if args.shading == "pbr" else ", Phong") + (", 4x MSAA base pass" if args.samples == 4 else "") + (f", {len(tl_draws)} of {len(shadow_draws)} draws translucent" if tl_draws is not None else ""),
                        "parallelism": ("sort-first row bands x%d (band_h %d, per-draw culling), shadow map: %s" % (world, band_h, share)) if tiles else (("view-parallel x%d, " % world + ("shadow map rendered on rank 0 + NCCL broadcast" if bcast else "every rank renders its own shadow map (no collective)")) if world > 1 else "1 GPU"),
                        "l2": "256 MiB flush write between timed steps", "outputs": "sRGB8 + depth f32 + triID u32"},
             "hbm_frame": {"algorithmic_bytes": frame_bytes, "achieved_gbs": frame_bytes / (ms * 1e-3) / 1e9,
@@ -359,7 +365,7 @@ def main():
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "kernel_ms": dom_ms, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs, burst copy)"},
             "kernel_ms": kt,
-            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 160 + 128 + 2 * 16 * len(draws),
+            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 160 + 128 + 2 * 16 * len(shadow_draws),
                     "d2h_bytes_per_step": W * H * 4, "note": "wall clock through reb_set_view/reb_render_*/reb_readback_async + final reb_sync with host buffers (pinned, 2-image swapchain: the copy of frame i overlaps frame i+1); geometry is static and resident as in the reference frame loop"},
             "gpu_launches": int(launches), "clocks": clocks,
             "frame_us": {"median": 1e3 * float(np.median(per_frame)), "p95": 1e3 * float(np.percentile(per_frame, 95)), "rank": 0},
@@ -370,7 +376,7 @@ def main():
             line["forward_only"] = {"ms_per_frame": fms, "value": T / (fms * 1e3), "unit": UNIT, "algorithmic_bytes": b_forward,
                                     "achieved_gbs": b_forward / (fms * 1e-3) / 1e9, "frac_of_peak": b_forward / (fms * 1e-3) / 1e9 / peak,
                                     "note": "forward pass alone against the cached shadow map (the reference renders the shadow map once, RenderScene.cpp:171-175)"}
-        if world == 1 and not args.no_cpu_baseline and args.samples == 1:
+        if world == 1 and not args.no_cpu_baseline and args.samples == 1 and tl_draws is None:
             keep = {}
             times, cores = cpu_reference_frames(scene, 5, warm=1, keep=keep)
             cms = 1e3 * float(np.mean(times))

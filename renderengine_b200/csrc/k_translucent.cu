@@ -4,7 +4,8 @@
 // per mesh by the caller (RenderScene.cpp:127-159,226-227), with cull none, depth test LessOrEqual + depth write and
 // src-alpha blending (GraphicsPipelineCache.cpp:305-315,330-340): per pixel the result depends on the ORDER of the
 // fragments, which the visibility-buffer resolve of the opaque pass cannot express.  Two kernels:
-//   k_tl_raster   one CTA per translucent triangle (cull none: vertices 1 and 2 swap when A2 > 0): every covered pixel whose
+//   k_tl_raster   the translucent triangles (cull none: vertices 1 and 2 swap when A2 > 0), small ones per lane, medium ones
+//                 per warp, large / clipped ones per CTA and 256 x 8 tile of their box (k_tl_raster_large): every covered pixel whose
 //                 depth passes against the OPAQUE depth appends {id, z} to that pixel's linked list (any order);
 //   k_tl_resolve  per pixel: pull the list, sort by submission-order ID, replay it — LessOrEqual against the running
 //                 depth, shade at the pixel centre with the ordinary shade_pixel* code, C = Cs*As + Cd*(1-As),
@@ -21,79 +22,232 @@ namespace reb {
 constexpr uint32_t TL_NONE = 0xFFFFFFFFu;
 constexpr int TL_MAX_FRAGS = 16;
 
-// One snapped triangle (a parent or a clip child), rasterised by the whole CTA: warps over rows, lanes over columns.
-__device__ __forceinline__ void tl_raster_tri(const PassConst& pc, VtxA a[3], uint32_t tri, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
-                                              uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, unsigned lane, unsigned warp) {
+constexpr int TL_SMALL = 8;      // bounding box <= 8 x 8 pixel centres: rasterised by the lane that set it up
+constexpr int TL_MEDIUM = 64;    // <= 64 x 64: by its warp; larger (or needs clipping): listed for k_tl_raster_large
+constexpr int TL_TILE_W = 256, TL_TILE_H = 8;   // work item of a large triangle: one row per warp, 8 column steps
+
+struct TlSetup {                 // Appendix B.6-B.8 of one snapped triangle, front-facing after the B.16 swap
+    int32_t A[3], B[3], bias[3]; long long E[3];   // E = unbiased edge value at the centre of pixel (0, 0)
+    float inv, z0, dz1, dz2;
+    int x0, x1, y0, y1;
+};
+
+__device__ __forceinline__ void tl_load(const PassConst& pc, uint32_t tri, VtxA a[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
+        a[k] = {(int32_t)q.x, (int32_t)q.y, __uint_as_float(q.z), q.w};
+    }
+}
+
+__device__ __forceinline__ bool tl_setup(const PassConst& pc, VtxA a[3], TlSetup& s) {
     long long A2 = mulw(a[1].X - a[0].X, a[2].Y - a[0].Y) - mulw(a[2].X - a[0].X, a[1].Y - a[0].Y);
-    if (A2 == 0) return;
+    if (A2 == 0) return false;
     if (A2 > 0) { const VtxA t = a[1]; a[1] = a[2]; a[2] = t; A2 = -A2; }                          // cull none (Appendix B.16)
     const int32_t minX = min(a[0].X, min(a[1].X, a[2].X)), maxX = max(a[0].X, max(a[1].X, a[2].X));
     const int32_t minY = min(a[0].Y, min(a[1].Y, a[2].Y)), maxY = max(a[0].Y, max(a[1].Y, a[2].Y));
-    const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
-    const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
-    if (x0 > x1 || y0 > y1) return;
-    int32_t A[3], B[3], bias[3]; long long E[3];   // unbiased edge value at the centre of pixel (0, 0)
+    s.x0 = max((minX + 127) >> 8, 0); s.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+    s.y0 = max((minY + 127) >> 8, 0); s.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+    if (s.x0 > s.x1 || s.y0 > s.y1) return false;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int p = (k + 1) % 3, q = (k + 2) % 3;
-        A[k] = a[q].Y - a[p].Y; B[k] = -(a[q].X - a[p].X);
-        bias[k] = ((A[k] > 0) || (A[k] == 0 && B[k] > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
-        E[k] = mulw(A[k], 128 - a[p].X) + mulw(B[k], 128 - a[p].Y);
+        s.A[k] = a[q].Y - a[p].Y; s.B[k] = -(a[q].X - a[p].X);
+        s.bias[k] = ((s.A[k] > 0) || (s.A[k] == 0 && s.B[k] > 0)) ? 0 : 1;   // top-left rule (Appendix B.7)
+        s.E[k] = mulw(s.A[k], 128 - a[p].X) + mulw(s.B[k], 128 - a[p].Y);
     }
-    const float inv = 1.0f / (float)(-A2);
-    const float z0 = a[0].z, dz1 = a[1].z - a[0].z, dz2 = a[2].z - a[0].z;
-    for (int y = y0 + (int)warp; y <= y1; y += 8) {
-        if (!row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) continue;
-        for (int x = x0 + (int)lane; x <= x1; x += 32) {
-            const long long F0 = E[0] + mulw(A[0], 256 * x) + mulw(B[0], 256 * y);
-            const long long F1 = E[1] + mulw(A[1], 256 * x) + mulw(B[1], 256 * y);
-            const long long F2 = E[2] + mulw(A[2], 256 * x) + mulw(B[2], 256 * y);
-            if (((F0 - bias[0]) | (F1 - bias[1]) | (F2 - bias[2])) < 0) continue;
-            const float z = depth_from((float)F1, (float)F2, inv, z0, dz1, dz2);
-            if (!(z >= 0.0f && z <= 1.0f)) continue;                                              // Appendix B.8 depth clip
-            const size_t p = (size_t)y * pc.W + x;
-            if (!(z <= __ldg(opaqueDepth + p))) continue;     // the running depth only ever gets nearer than the opaque depth
-            const uint32_t idx = atomicAdd(&counters[0], 1u);
-            if (idx >= cap) { atomicAdd(&counters[1], 1u); continue; }
-            nodes[idx] = make_uint4(atomicExch(&head[p], idx), tri, __float_as_uint(z), 0u);
-        }
-    }
+    s.inv = 1.0f / (float)(-A2);
+    s.z0 = a[0].z; s.dz1 = a[1].z - a[0].z; s.dz2 = a[2].z - a[0].z;
+    return true;
 }
 
-// Appendix B.3 for a translucent parent (CTA-uniform: every thread clips the same triangle): the children of the fan go
-// through the same snap / facing / raster steps and append the PARENT's ID (children of one fan share edges, which the
-// top-left rule assigns to exactly one of them).
-__device__ __noinline__ void tl_clip_raster(const PassConst& pc, uint32_t tri, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
-                                            uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, unsigned lane, unsigned warp) {
-    float4 c[9];
-    const int n = clip_parent<false>(pc, tri, c);
-    for (int i = 1; i + 1 < n; ++i) {
-        VtxA a[3] = {viewport_snap(c[0], pc.W, pc.H), viewport_snap(c[i], pc.W, pc.H), viewport_snap(c[i + 1], pc.W, pc.H)};
-        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
-            if (threadIdx.x == 0) atomicAdd(&counters[2], 1u);
-            continue;
-        }
-        tl_raster_tri(pc, a, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
-    }
+// Coverage + depth of pixel (x, y); a fragment that can still pass (z <= opaque depth: the running depth only ever gets
+// nearer than that) is appended to the pixel's list.  The node index comes from one atomicAdd per converged group of lanes.
+__device__ __forceinline__ void tl_sample(const PassConst& pc, const TlSetup& s, int x, int y, uint32_t tri, const float* __restrict__ opaqueDepth,
+                                          uint32_t* __restrict__ head, uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters) {
+    const long long F0 = s.E[0] + mulw(s.A[0], 256 * x) + mulw(s.B[0], 256 * y);
+    const long long F1 = s.E[1] + mulw(s.A[1], 256 * x) + mulw(s.B[1], 256 * y);
+    const long long F2 = s.E[2] + mulw(s.A[2], 256 * x) + mulw(s.B[2], 256 * y);
+    if (((F0 - s.bias[0]) | (F1 - s.bias[1]) | (F2 - s.bias[2])) < 0) return;
+    const float z = depth_from((float)F1, (float)F2, s.inv, s.z0, s.dz1, s.dz2);
+    if (!(z >= 0.0f && z <= 1.0f)) return;                                                       // Appendix B.8 depth clip
+    const size_t p = (size_t)y * pc.W + x;
+    if (!(z <= __ldg(opaqueDepth + p))) return;
+    const unsigned m = __activemask();
+    const unsigned lane = threadIdx.x & 31u;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(&counters[0], (uint32_t)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    const uint32_t idx = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+    if (idx >= cap) { atomicAdd(&counters[1], 1u); return; }
+    nodes[idx] = make_uint4(atomicExch(&head[p], idx), tri, __float_as_uint(z), 0u);
 }
 
+// Coverage / depth only: true when pixel (x, y) yields a fragment that can still pass; z returned.
+__device__ __forceinline__ bool tl_covers(const PassConst& pc, const TlSetup& s, int x, int y, const float* __restrict__ opaqueDepth, float& z) {
+    const long long F0 = s.E[0] + mulw(s.A[0], 256 * x) + mulw(s.B[0], 256 * y);
+    const long long F1 = s.E[1] + mulw(s.A[1], 256 * x) + mulw(s.B[1], 256 * y);
+    const long long F2 = s.E[2] + mulw(s.A[2], 256 * x) + mulw(s.B[2], 256 * y);
+    if (((F0 - s.bias[0]) | (F1 - s.bias[1]) | (F2 - s.bias[2])) < 0) return false;
+    z = depth_from((float)F1, (float)F2, s.inv, s.z0, s.dz1, s.dz2);
+    if (!(z >= 0.0f && z <= 1.0f)) return false;                                                 // Appendix B.8 depth clip
+    return z <= __ldg(opaqueDepth + (size_t)y * pc.W + x);
+}
+
+// Pass A: one lane per translucent triangle, 32 at a time per warp.  Small triangles (the common case for dense meshes) are
+// rasterised by their lane — coverage of the <= 8 x 8 box into a 64-bit mask first, then ONE node-pool atomicAdd for the
+// whole warp, then the nodes; medium ones by the whole warp, one after the other; large ones and the ones that need
+// Appendix B.3 clipping are listed for pass B with the number of 256 x 8 target tiles they may touch.
 __global__ void __launch_bounds__(256) k_tl_raster(const __grid_constant__ PassConst pc, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
-                                                   uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters) {
+                                                   uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, uint2* __restrict__ largeList) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nWarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = gwarp * 32u; base < pc.nTris; base += nWarps * 32u) {
+        const uint32_t tri = base + lane;
+        int cls = 0;                                   // 0 nothing, 1 small, 2 medium, 3 large / needs clipping
+        uint32_t nTiles = 0;
+        TlSetup s;
+        if (tri < pc.nTris) {
+            VtxA a[3];
+            tl_load(pc, tri, a);
+            if ((a[0].flags & a[1].flags & a[2].flags & VF_PLANES) != 0u) cls = 0;                // Appendix B.2
+            else if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) {
+                cls = 3; nTiles = ((pc.W + TL_TILE_W - 1) / TL_TILE_W) * ((pc.H + TL_TILE_H - 1) / TL_TILE_H);   // children: anywhere on the target
+            } else if (tl_setup(pc, a, s)) {
+                const int w = s.x1 - s.x0 + 1, h = s.y1 - s.y0 + 1;
+                cls = (w <= TL_SMALL && h <= TL_SMALL) ? 1 : (w <= TL_MEDIUM && h <= TL_MEDIUM) ? 2 : 3;
+                nTiles = (uint32_t)((s.x1 / TL_TILE_W - s.x0 / TL_TILE_W + 1) * (s.y1 / TL_TILE_H - s.y0 / TL_TILE_H + 1));
+            }
+        }
+        if (cls == 3) {   // one 64-bit atomic hands out the list slot (high word) and the first work item (low word) consistently
+            const unsigned long long t = atomicAdd(reinterpret_cast<unsigned long long*>(counters + 4), (1ull << 32) | nTiles);
+            largeList[(uint32_t)(t >> 32)] = make_uint2(tri, (uint32_t)t);
+        }
+        // ---- small: coverage mask, one allocation per warp, emit
+        unsigned long long mask = 0ull;
+        int w = 1;
+        if (cls == 1) {
+            w = s.x1 - s.x0 + 1;
+            int bit = 0;
+            for (int y = s.y0; y <= s.y1; ++y) {
+                const bool mine = row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH);
+                for (int x = s.x0; x <= s.x1; ++x, ++bit) {
+                    float z;
+                    if (mine && tl_covers(pc, s, x, y, opaqueDepth, z)) mask |= 1ull << bit;
+                }
+            }
+        }
+        const uint32_t cnt = (uint32_t)__popcll(mask);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if ((int)lane >= d) incl += v; }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (total) {
+            uint32_t wbase = 0;
+            if (lane == 0) wbase = atomicAdd(&counters[0], total);
+            uint32_t idx = __shfl_sync(0xFFFFFFFFu, wbase, 0) + incl - cnt;
+            while (mask) {
+                const int bit = __ffsll((long long)mask) - 1;
+                mask &= mask - 1;
+                const int y = s.y0 + bit / w, x = s.x0 + bit - (bit / w) * w;
+                float z;
+                tl_covers(pc, s, x, y, opaqueDepth, z);
+                if (idx >= cap) atomicAdd(&counters[1], 1u);
+                else nodes[idx] = make_uint4(atomicExch(&head[(size_t)y * pc.W + x], idx), tri, __float_as_uint(z), 0u);
+                ++idx;
+            }
+        }
+        // ---- medium: the whole warp, one triangle after the other
+        unsigned mm = __ballot_sync(0xFFFFFFFFu, cls == 2);
+        while (mm) {
+            const int src = __ffs(mm) - 1;
+            mm &= mm - 1;
+            const uint32_t t2 = base + (uint32_t)src;
+            VtxA a[3];
+            tl_load(pc, t2, a);
+            TlSetup m;
+            tl_setup(pc, a, m);
+            for (int y = m.y0; y <= m.y1; ++y) {
+                if (!row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) continue;
+                for (int x = m.x0 + (int)lane; x <= m.x1; x += 32) tl_sample(pc, m, x, y, t2, opaqueDepth, head, nodes, cap, counters);
+            }
+        }
+    }
+}
+
+// The part of one snapped triangle (a parent or a clip child) inside target tile (tx, ty) by the whole CTA: one row per warp, lanes over columns.
+__device__ __forceinline__ void tl_raster_tile(const PassConst& pc, VtxA a[3], uint32_t tri, int tx, int ty, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
+                                               uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, unsigned lane, unsigned warp) {
+    TlSetup s;
+    if (!tl_setup(pc, a, s)) return;
+    const int y = ty * TL_TILE_H + (int)warp;
+    if (y < s.y0 || y > s.y1 || !row_owned((uint32_t)y, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int xa = max(s.x0, tx * TL_TILE_W), xb = min(s.x1, tx * TL_TILE_W + TL_TILE_W - 1);
+    // all eight column steps in flight: coverage + depth first (independent loads), ONE node-pool atomicAdd for the row, then the nodes
+    float z[TL_TILE_W / 32];
+    unsigned covered = 0u;
+#pragma unroll
+    for (int k = 0; k < TL_TILE_W / 32; ++k) {
+        const int x = xa + (int)lane + 32 * k;
+        z[k] = 0.0f;
+        if (x <= xb && tl_covers(pc, s, x, y, opaqueDepth, z[k])) covered |= 1u << k;
+    }
+    const uint32_t cnt = (uint32_t)__popc(covered);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if ((int)lane >= d) incl += v; }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (!total) return;
+    uint32_t wbase = 0;
+    if (lane == 0) wbase = atomicAdd(&counters[0], total);
+    uint32_t idx = __shfl_sync(0xFFFFFFFFu, wbase, 0) + incl - cnt;
+#pragma unroll
+    for (int k = 0; k < TL_TILE_W / 32; ++k) {
+        if (!((covered >> k) & 1u)) continue;
+        const int x = xa + (int)lane + 32 * k;
+        if (idx >= cap) atomicAdd(&counters[1], 1u);
+        else nodes[idx] = make_uint4(atomicExch(&head[(size_t)y * pc.W + x], idx), tri, __float_as_uint(z[k]), 0u);
+        ++idx;
+    }
+}
+
+// Pass B: the listed triangles, one CTA per (triangle, 256 x 8 tile of its bounding box).  Appendix B.3 for a translucent
+// parent runs CTA-uniform (every thread clips the same triangle); the children of the fan go through the same snap / facing /
+// raster steps and append the PARENT's ID (children of one fan share edges, which the top-left rule assigns to exactly one).
+__global__ void __launch_bounds__(256) k_tl_raster_large(const __grid_constant__ PassConst pc, const float* __restrict__ opaqueDepth, uint32_t* __restrict__ head,
+                                                         uint4* __restrict__ nodes, uint32_t cap, uint32_t* __restrict__ counters, const uint2* __restrict__ largeList) {
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    for (uint32_t tri = blockIdx.x; tri < pc.nTris; tri += gridDim.x) {
-        uint32_t slot[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) slot[k] = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+    const uint32_t nItems = __ldcg(&counters[4]), nLarge = __ldcg(&counters[5]);
+    for (uint32_t item = blockIdx.x; item < nItems; item += gridDim.x) {
+        uint32_t lo = 0, hi = nLarge;                // last entry whose first work item is <= item
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldcg(&largeList[mid].y) <= item) lo = mid; else hi = mid; }
+        const uint2 e = __ldcg(largeList + lo);
+        const uint32_t tri = e.x, local = item - e.y;
         VtxA a[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const uint4 q = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot[k]);
-            a[k] = {(int32_t)q.x, (int32_t)q.y, __uint_as_float(q.z), q.w};
+        tl_load(pc, tri, a);
+        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) == 0u) {
+            TlSetup s;
+            VtxA b[3] = {a[0], a[1], a[2]};
+            if (!tl_setup(pc, b, s)) continue;
+            const int tx0 = s.x0 / TL_TILE_W, tw = s.x1 / TL_TILE_W - tx0 + 1;
+            tl_raster_tile(pc, a, tri, tx0 + (int)(local % (uint32_t)tw), s.y0 / TL_TILE_H + (int)(local / (uint32_t)tw), opaqueDepth, head, nodes, cap, counters, lane, warp);
+            continue;
         }
-        if ((a[0].flags & a[1].flags & a[2].flags & VF_PLANES) != 0u) continue;                       // Appendix B.2
-        if (((a[0].flags | a[1].flags | a[2].flags) & VF_NEEDS_CLIP) != 0u) tl_clip_raster(pc, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
-        else tl_raster_tri(pc, a, tri, opaqueDepth, head, nodes, cap, counters, lane, warp);
+        const uint32_t tw = (pc.W + TL_TILE_W - 1) / TL_TILE_W;
+        float4 c[9];
+        const int n = clip_parent<false>(pc, tri, c);
+        for (int i = 1; i + 1 < n; ++i) {
+            VtxA ch[3] = {viewport_snap(c[0], pc.W, pc.H), viewport_snap(c[i], pc.W, pc.H), viewport_snap(c[i + 1], pc.W, pc.H)};
+            if (((ch[0].flags | ch[1].flags | ch[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
+                if (threadIdx.x == 0 && local == 0) atomicAdd(&counters[2], 1u);
+                continue;
+            }
+            tl_raster_tile(pc, ch, tri, (int)(local % tw), (int)(local / tw), opaqueDepth, head, nodes, cap, counters, lane, warp);
+        }
     }
 }
 
@@ -147,10 +301,12 @@ __global__ void __launch_bounds__(256, 2) k_tl_resolve(const __grid_constant__ P
     else reinterpret_cast<float4*>(hdr)[p] = col;
 }
 
-void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, int numSMs, cudaStream_t st) {
+void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, uint2* largeList, int numSMs,
+                      cudaStream_t st) {
     if (pc.nTris == 0) return;
-    const uint32_t grid = std::min<uint32_t>(pc.nTris, (uint32_t)numSMs * 8u);
-    launch_k(k_tl_raster, dim3(grid), dim3(256), st, true, pc, opaqueDepth, head, nodes, cap, counters);
+    const uint32_t grid = std::min<uint32_t>((pc.nTris + 255u) / 256u, (uint32_t)numSMs * 8u);
+    launch_k(k_tl_raster, dim3(grid), dim3(256), st, true, pc, opaqueDepth, head, nodes, cap, counters, largeList);
+    launch_k(k_tl_raster_large, dim3((uint32_t)numSMs * 4u), dim3(256), st, true, pc, opaqueDepth, head, nodes, cap, counters, (const uint2*)largeList);
 }
 
 void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,

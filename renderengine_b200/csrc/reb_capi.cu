@@ -67,7 +67,7 @@ struct reb_ctx {
     unsigned long long* vis = nullptr;
     // translucent list (Appendix B.16, k_translucent.cu): per-pixel list heads, node pool, device counters {nodes, dropped, needs-clip};
     // internal linear-colour / depth targets when the caller did not enable those outputs
-    uint32_t* tlHead = nullptr; uint4* tlNodes = nullptr; uint32_t tlCap = 0; uint32_t* tlCounters = nullptr;
+    uint32_t* tlHead = nullptr; uint4* tlNodes = nullptr; uint32_t tlCap = 0; uint32_t* tlCounters = nullptr; uint2* tlLarge = nullptr; uint32_t tlLargeCap = 0;
     float* tlHdr = nullptr; float* tlDepth = nullptr; size_t tlPx = 0;
     bool tlFollows = false, tlPending = false; ShadeConst tlShade; uint32_t tlIdBase = 0; uint64_t tlDropped = 0;
     // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
@@ -544,11 +544,16 @@ int run_translucent(reb_ctx* ctx) {
     ShadeConst sh = ctx->tlShade;
     float* hdr = ctx->outF32 ? ctx->outF32 : ctx->tlHdr;
     float* depth = ctx->outDepth ? ctx->outDepth : ctx->tlDepth;
-    CU(cudaMemsetAsync(ctx->tlCounters, 0, 16, ctx->stream));
+    if (pc.nTris > ctx->tlLargeCap) {                 // list of the triangles pass B rasterises (worst case: all of them)
+        CU(cudaStreamSynchronize(ctx->stream));
+        if ((rc = dev_alloc(ctx, &ctx->tlLarge, (size_t)pc.nTris))) return rc;
+        ctx->tlLargeCap = pc.nTris;
+    }
+    CU(cudaMemsetAsync(ctx->tlCounters, 0, 32, ctx->stream));
     if (pc.nTris) {
         launch_vertex(pc, false, /*pdl=*/false, ctx->stream);
-        launch_tl_raster(pc, depth, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlCounters, ctx->numSMs, ctx->stream);
-        ctx->launches += 2;
+        launch_tl_raster(pc, depth, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlCounters, ctx->tlLarge, ctx->numSMs, ctx->stream);
+        ctx->launches += 3;
     }
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
     launch_tl_resolve(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, hdr, depth, ctx->tlCounters, ctx->stream); ctx->launches++;
@@ -572,9 +577,10 @@ int check_and_recover(reb_ctx* ctx) {
         if (!overflow) {
             ctx->pass[0].pending = ctx->pass[1].pending = false;
             if (ctx->tlPending) {   // fragments / triangles the translucent pass had to drop (list capacity, Appendix B.3 clipping)
-                uint32_t c[4] = {0, 0, 0, 0};
-                CU(cudaMemcpy(c, ctx->tlCounters, 16, cudaMemcpyDeviceToHost));
+                uint32_t c[8] = {};   // nodes, dropped fragments, dropped clip children, -, work items of pass B, triangles of pass B
+                CU(cudaMemcpy(c, ctx->tlCounters, 32, cudaMemcpyDeviceToHost));
                 ctx->tlDropped = (uint64_t)c[1] + c[2];
+                if (std::getenv("REB_TL_DEBUG")) std::fprintf(stderr, "[reb] translucent pass: %u list nodes, %u fragments dropped, %u clip children dropped, %u triangles / %u tiles in pass B\n", c[0], c[1], c[2], c[5], c[4]);
                 ctx->counters[0] += ctx->tlDropped;
                 ctx->tlPending = false;
             }

@@ -62,7 +62,7 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible,
                     ctx->pass[2].dDraws, ctx->pass[2].vtxA, ctx->pass[2].vtxBC, ctx->pass[2].blockDraw, ctx->pass[2].flatSlots, ctx->pass[2].drawBounds,
                     ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
-                    ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth};
+                    ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
@@ -271,7 +271,7 @@ static int render_base_pass(reb_ctx* ctx, const reb_draw* draws, uint32_t n, con
     if (ctx->tlPx != px) {
         CU(cudaStreamSynchronize(ctx->stream));
         const uint32_t cap = (uint32_t)std::min<size_t>(std::max<size_t>(4 * px, (size_t)1 << 20), (size_t)1 << 28);
-        if ((rc = dev_alloc(ctx, &ctx->tlHead, px)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)4)) ||
+        if ((rc = dev_alloc(ctx, &ctx->tlHead, px)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)8)) ||
             (rc = dev_alloc(ctx, &ctx->tlHdr, ctx->outF32 ? 0 : px * 4)) || (rc = dev_alloc(ctx, &ctx->tlDepth, ctx->outDepth ? 0 : px))) return rc;
         launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, px, ctx->numSMs, ctx->stream); ctx->launches++;
         ctx->tlCap = cap; ctx->tlPx = px;

@@ -55,7 +55,8 @@ void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t n
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
 // Appendix B.16 (k_translucent.cu): per-pixel fragment lists of the translucent triangles, then the ordered blend
-void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, int numSMs, cudaStream_t st);
+void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, uint2* largeList, int numSMs,
+                      cudaStream_t st);
 void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,
                        uint32_t* counters, cudaStream_t st);
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st);   // between the sample passes of a multisampled frame

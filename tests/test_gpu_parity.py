@@ -676,3 +676,28 @@ def test_parity_translucent_triangles_clipped_at_the_eye_plane():
         assert d8.max() <= 1, f"sRGB8 colour differs by {d8.max()} LSB at {np.count_nonzero(d8 > 1)} channel samples"
         assert _psnr(gpu["color_f32"], ref["color_f32"]) >= 50.0
     assert ((ref["tri_id"] == ground_id) | (ref["tri_id"] == ground_id + 1)).mean() > 0.05       # the clipped translucent ground is on screen
+
+
+def test_translucent_pass_under_the_sort_first_split():
+    """The translucent list composes with the row-band split: each rank builds fragment lists only for its own rows (draw /
+    block culling applies to the opaque list; the translucent list is rasterised unculled) and the bands merge to the full frame."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    base = sc.make_scene("small")
+    base["skybox"] = sc.make_skybox(32)
+    s = sc.to_translucent(base, every=2)
+    world = 2
+    band = parallel.contiguous_band(s["height"], world * 2)
+    ref_shadow = orc.Oracle(dict(base)).render_shadow()
+    whole = orc.Oracle(s).render_forward(ref_shadow)
+    merged8 = np.zeros_like(whole["color_srgb8"]); merged_id = np.zeros_like(whole["tri_id"]); merged_z = np.zeros_like(whole["depth"])
+    for rank in range(world):
+        ctx = capi.Context(s["width"], s["height"], rank=rank, n_ranks=world, band_h=band)
+        ctx.upload_scene(s)
+        ctx.render_shadow(np.concatenate([s["draws"], s["translucent_draws"]])); ctx.render_forward(s["draws"], s["translucent_draws"])
+        own = ((np.arange(s["height"]) // band) % world == rank)
+        merged8[own] = ctx.readback(capi.REB_COLOR_SRGB8)[own]
+        merged_id[own] = ctx.readback(capi.REB_TRIID_U32)[own]; merged_z[own] = ctx.readback(capi.REB_DEPTH_F32)[own]
+        assert ctx.counters()[0] == 0
+    assert np.array_equal(merged_id, whole["tri_id"]) and np.array_equal(merged_z.view(np.uint32), whole["depth"].view(np.uint32))
+    assert np.abs(merged8.astype(np.int32) - whole["color_srgb8"].astype(np.int32)).max() <= 1
