@@ -566,10 +566,12 @@ int check_and_recover(reb_ctx* ctx) {
     for (int iter = 0; iter < 8; ++iter) {
         bool overflow = false;
         uint32_t need = ctx->listCap;
+        bool first = true;                           // counters[0] = drops of the passes checked now (not carried over from earlier frames)
         for (int k = 0; k < 2; ++k) {
             if (!ctx->pass[k].pending) continue;
             const uint32_t* st = ctx->hStatus + 8 * k;
-            ctx->counters[0] = (k == 0 ? 0 : ctx->counters[0]) + st[1];
+            ctx->counters[0] = (first ? 0 : ctx->counters[0]) + st[1];
+            first = false;
             ctx->counters[1] = st[0]; ctx->counters[2] = st[3];
             if (st[2] & OVF_LARGE) { overflow = true; ctx->largeWorstCase = true; }   // clip children outgrew the slack: size for the worst case
             if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }

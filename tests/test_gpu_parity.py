@@ -701,3 +701,31 @@ def test_translucent_pass_under_the_sort_first_split():
         assert ctx.counters()[0] == 0
     assert np.array_equal(merged_id, whole["tri_id"]) and np.array_equal(merged_z.view(np.uint32), whole["depth"].view(np.uint32))
     assert np.abs(merged8.astype(np.int32) - whole["color_srgb8"].astype(np.int32)).max() <= 1
+
+
+def test_translucent_many_layers_and_the_per_pixel_fragment_cap():
+    """The same translucent draws submitted 3 times: coincident fragments pass LessOrEqual every time, so sphere pixels blend
+    6 layers (front + back face per repeat; 12 where two spheres overlap) in submission order — parity as usual.  Submitted 10 times a pixel holds more
+    than the 16 fragments this version keeps: the excess is dropped, COUNTED (reb_get_counters()[0]) and nothing else breaks."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.to_translucent(sc.make_scene("small"), every=2, alpha=0.2)
+    ref_shadow = orc.Oracle(dict(sc.make_scene("small"))).render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.render_shadow(np.concatenate([s["draws"], s["translucent_draws"]]))
+    s5 = dict(s); s5["translucent_draws"] = np.concatenate([s["translucent_draws"]] * 3)
+    ref = orc.Oracle(s5).render_forward(ref_shadow)
+    ctx.render_forward(s5["draws"], s5["translucent_draws"])
+    ctx.sync()
+    assert ctx.counters()[0] == 0
+    tid = ctx.readback(capi.REB_TRIID_U32)
+    assert np.array_equal(tid, ref["tri_id"]), f"triangle IDs differ at {np.count_nonzero(tid != ref['tri_id'])} pixels"
+    assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), ref["depth"].view(np.uint32))
+    assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
+    assert _psnr(ctx.readback(capi.REB_COLOR_F32), ref["color_f32"]) >= 50.0
+    ctx.render_forward(s["draws"], np.concatenate([s["translucent_draws"]] * 10))
+    ctx.sync()
+    assert ctx.counters()[0] > 0                              # fragments beyond 16 per pixel: dropped and reported
+    ctx.render_forward(s5["draws"], s5["translucent_draws"])  # and the context keeps working
+    assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"]) and ctx.counters()[0] == 0
