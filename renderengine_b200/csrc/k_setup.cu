@@ -234,6 +234,9 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
     return v;
 }
 
+static_assert(SMALL_MAX + 1 < 16, "pixq packs 4-bit row and column counts");
+static_assert(31 + 32 * (SMALL_MAX + 1) <= 512, "row / pixel rings: < 32 pending + 32 * (SMALL_MAX + 1) new");
+
 __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint32_t tri, uint32_t slot, uint32_t rowPos) {
     const int32_t X[3] = {t.a[0].X, t.a[1].X, t.a[2].X}, Y[3] = {t.a[0].Y, t.a[1].Y, t.a[2].Y};
     const int32_t Px = 256 * t.x0 + 128, Py = 256 * t.y0 + 128;
@@ -406,48 +409,48 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
 
 // ---------------------------------------------------------------------------------------------
 // K1c: clip + layout.  Warps stride over the queue of triangles K1 found to need true clipping (Appendix B.3; empty for
-// ordinary frames) and send their children into the large-triangle path; then the last CTA to finish lays out the
-// per-tile lists (start = running cursor; no ordered scan is needed because list order inside a tile is irrelevant to
-// the min-key resolve; the counts become K2's scatter cursors).
+// ordinary frames) and send their children into the large-triangle path; then the per-tile lists are laid out: start =
+// a running cursor (status[7]) bumped once per warp of 32 tiles — no ordered scan is needed because list order inside a
+// tile is irrelevant to the min-key resolve — and the counts become K2's scatter cursors.  Without clipping no CTA
+// depends on another and the whole grid shares the tiles (one CTA walking the 16 k tiles of a 2048^2 map took 64 us, the
+// 65 k tiles of a 4096^2 map 250 us); with clipping the last CTA to finish its share of the queue does it alone.
 // ---------------------------------------------------------------------------------------------
 constexpr int KC_THREADS = 128;
 template <bool SHADOW>
 __global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constant__ PassConst pc) {
-    __shared__ uint32_t cursor, isLast;
+    __shared__ uint32_t isLast;
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t nClip = min(pc.status[6], pc.clipCap);
+    uint32_t first = blockIdx.x * KC_THREADS, stride = gridDim.x * KC_THREADS;
     if (nClip == 0) {
-        // nothing to clip (the usual frame): no CTA depends on another, so CTA 0 lays the lists out and the rest leave at once
-        if (blockIdx.x != 0 || pc.status[0] == 0u) return;
-        if (threadIdx.x == 0) cursor = 0u;
-        __syncthreads();
+        if (pc.status[0] == 0u) return;   // nothing binned (the usual frame of small triangles)
     } else {
         const uint32_t warpsPerGrid = (gridDim.x * KC_THREADS) >> 5;
         for (uint32_t i = (blockIdx.x * KC_THREADS + threadIdx.x) >> 5; i < nClip; i += warpsPerGrid) k1_clip_emit<SHADOW>(pc, __ldcg(pc.clipQueue + i), lane);
         __threadfence();
         __syncthreads();
-        if (threadIdx.x == 0) { isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u; cursor = 0u; }
+        if (threadIdx.x == 0) isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u;
         __syncthreads();
         if (!isLast) return;
         __threadfence();
+        first = 0u; stride = KC_THREADS;
     }
     const uint32_t nLarge = min(*reinterpret_cast<volatile uint32_t*>(&pc.status[0]), pc.largeCap);
     if (nLarge == 0) return;
     const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    for (uint32_t i0 = 0; i0 < nTiles; i0 += KC_THREADS) {
+    for (uint32_t i0 = first; i0 < nTiles; i0 += stride) {
         const uint32_t i = i0 + threadIdx.x;
         const uint32_t c = i < nTiles ? __ldcg(pc.tileCount + i) : 0u;
         const uint32_t inc = warp_incl_scan(c, lane);
         uint32_t wbase = 0;
-        if (lane == 31 && inc) wbase = atomicAdd(&cursor, inc);
+        if (lane == 31 && inc) {
+            wbase = atomicAdd(&pc.status[7], inc);
+            atomicMax(&pc.status[3], wbase + inc);   // = the final cursor once every warp is through; max over the sample passes of a multisampled frame (k_pass_reset keeps it)
+            if (wbase + inc > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
+        }
         wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
         if (i < nTiles && c) { pc.tileStart[i] = wbase + inc - c; pc.tileCount[i] = 0u; }   // counts become the scatter cursors
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        atomicMax(&pc.status[3], cursor);   // max over the sample passes of a multisampled frame (k_pass_reset keeps it)
-        if (cursor > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
     }
 }
 

@@ -21,6 +21,7 @@ namespace reb {
 #endif
 constexpr int K0_PER_THREAD = K0_PER_THREAD_D;   // cache slots per thread: four independent load chains in flight
 
+constexpr uint32_t K0_MIN_GRID = 296u;           // two CTAs per SM
 struct K0In { float4 p, n; uint32_t node; bool valid; };
 
 template <bool SHADOW, bool CULL = false>
@@ -161,7 +162,9 @@ void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint3
 
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) {
     if (pc.cacheSize == 0) return;
-    const uint32_t grid = (pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
+    // at least K0_MIN_GRID CTAs: the pass prologue and the shadow-map clear are sliced over the grid (a 2 k-vertex scene
+    // otherwise streams the 16-MB clear through three CTAs: 107 us); CTAs past the cache only do their slice
+    const uint32_t grid = std::max((pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD), K0_MIN_GRID);
     using Kern = void (*)(PassConst);
     static const Kern kern[4] = {k_vertex<false, false>, k_vertex<true, false>, k_vertex<false, true>, k_vertex<true, true>};
     launch_k(kern[(shadow ? 1 : 0) | (pc.drawVisible ? 2 : 0)], dim3(grid), dim3(256), st, pdl, pc);
@@ -300,7 +303,7 @@ void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds,
 
 void launch_vertex_both(const PassConst& ps, const PassConst& pf, cudaStream_t st) {
     if (pf.cacheSize == 0) return;
-    const uint32_t grid = (pf.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD);
+    const uint32_t grid = std::max((pf.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD), K0_MIN_GRID);
     launch_k(k_vertex_both, dim3(grid), dim3(256), st, false, ps, pf);
 }
 

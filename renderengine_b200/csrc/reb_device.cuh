@@ -15,7 +15,10 @@ constexpr float GUARD_PX = 1048576.0f;                            // |x_f|,|y_f|
 constexpr int TILE_W = 32, TILE_H = 8;                            // one CTA (256 threads) per screen tile
 constexpr int HUGE_TILES = 256;                                   // bbox covering more tiles than this: broadcast list
 constexpr int HUGE_CAP = 64;                                      // capacity of the broadcast list (overflow -> binned path)
-constexpr int SMALL_MAX = 8;                                      // bbox spans <= 8 px: rasterised inside the setup kernel
+#ifndef SMALL_MAX_D
+#define SMALL_MAX_D 14
+#endif
+constexpr int SMALL_MAX = SMALL_MAX_D;                                      // bbox spans <= 14 px: rasterised inside the setup kernel (8 was a cliff: C2 with the reference's 4096^2 map has ~6-10 px triangles, 630 -> 226 us / frame)
 constexpr uint32_t LIGHT_TYPE_DIRECTIONAL = 1, LIGHT_TYPE_SPOT = 3;   // phong.glsl:16-18
 
 // Post-transform vertex flags (VtxA.flags): bits 0-5 = outside x<-w, x>w, y<-w, y>w, z<0, z>w (Appendix B.2);

@@ -340,6 +340,10 @@ def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
     """Build a scene dict for a named config. All arrays are host numpy."""
     cfg = dict(CONFIGS[config]) if isinstance(config, str) else dict(config)
     cfg.update(overrides)
+    if os.environ.get("REB_SHADOW_SIZE") and cfg["shadow_size"]:   # e.g. 4096, the reference's default map (ShadowSystem.h)
+        cfg["shadow_size"] = int(os.environ["REB_SHADOW_SIZE"])
+    if os.environ.get("REB_SCENE_LEVEL"):   # triangle-size sweeps of a named config (tools/kt.py)
+        cfg["level"] = int(os.environ["REB_SCENE_LEVEL"])
     nx, nz = cfg["grid"]; level = cfg["level"]
     W, H, S, M = cfg["width"], cfg["height"], cfg["shadow_size"], cfg["n_materials"]
     n_tex, tex_size = cfg.get("n_textures", 0), cfg.get("tex_size", 64)
