@@ -96,8 +96,8 @@ struct K1Warp {
     uint32_t whb[K1_RING];          // w | h << 8 | top-left bias of edge k << (16 + k)
     float z0[K1_RING], dz1[K1_RING], dz2[K1_RING], inv[K1_RING];   // inv = 1 / |A2|
     uint32_t idKey[K1_RING];
-    uint16_t rowq[K1_ROWQ];         // slot | j << 8
-    uint16_t pixq[K1_PIXQ];         // slot | i << 6 | j << 10
+    uint16_t rowq[K1_ROWQ];         // slot | entry << 6   (entry = row, or 2 * row + half when the bbox is wider than K1_SPLIT)
+    uint16_t pixq[K1_PIXQ];         // slot | i << 6 | j << 11
 };
 struct K1Shared {
     K1Warp w[K1_WARPS];
@@ -130,7 +130,7 @@ __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, con
     t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
     if (t.x0 > t.x1 || t.y0 > t.y1) return;                                         // no pixel centre inside the bbox
     // unclamped spans keep the 32-bit edge math of the row stage exact
-    t.isSmall = (maxX - minX) <= SMALL_MAX * 256 && (maxY - minY) <= SMALL_MAX * 256;
+    t.isSmall = (maxX - minX) <= SMALL_LIMIT * 256 && (maxY - minY) <= SMALL_LIMIT * 256;
     t.isLarge = !t.isSmall;
 }
 
@@ -234,10 +234,10 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
     return v;
 }
 
-static_assert(SMALL_MAX + 1 < 16, "pixq packs 4-bit row and column counts");
+constexpr uint32_t K1_SPLIT = SMALL_MAX + 1;   // widest (half) row of the row stage; row entries appended per lane and round
 static_assert(31 + 32 * (SMALL_MAX + 1) <= 512, "row / pixel rings: < 32 pending + 32 * (SMALL_MAX + 1) new");
 
-__device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint32_t tri, uint32_t slot, uint32_t rowPos) {
+__device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint32_t tri, uint32_t slot) {
     const int32_t X[3] = {t.a[0].X, t.a[1].X, t.a[2].X}, Y[3] = {t.a[0].Y, t.a[1].Y, t.a[2].Y};
     const int32_t Px = 256 * t.x0 + 128, Py = 256 * t.y0 + 128;
     const uint32_t h = (uint32_t)(t.y1 - t.y0 + 1);
@@ -257,7 +257,6 @@ __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint3
     ws.z0[slot] = t.a[0].z; ws.dz1[slot] = t.a[1].z - t.a[0].z; ws.dz2[slot] = t.a[2].z - t.a[0].z;
     ws.inv[slot] = 1.0f / (float)(-t.A2);
     ws.idKey[slot] = ~tri;
-    for (uint32_t j = 0; j < h; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(slot | (j << 8));
 }
 
 // Cache slots of the three corners of triangle `tri` (flatSlots: the draw list's index stream re-based into
@@ -284,21 +283,23 @@ __device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uin
 template <bool SHADOW, bool CULL = false>
 __device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_t rowHead, uint32_t cnt, uint32_t& pixTail, unsigned lane) {
     bool active = lane < cnt;
-    uint32_t slot = 0, j = 0, whb = 0;
+    uint32_t slot = 0, j = 0, whb = 0, xo = 0;
     if (active) {
         const uint32_t e = ws.rowq[(rowHead + lane) & (K1_ROWQ - 1)];
-        slot = e & 0xFFu; j = e >> 8;
+        slot = e & 0x3Fu;
         whb = ws.whb[slot];
+        const uint32_t wide = (whb & 0xFFu) > K1_SPLIT ? 1u : 0u;   // two half rows per row
+        j = (e >> 6) >> wide; xo = ((e >> 6) & wide) * K1_SPLIT;
         if ((!SHADOW || CULL) && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;   // shadow slabs only in the split build
     }
-    const uint32_t w = active ? (whb & 0xFFu) : 0u;
+    const uint32_t w = active ? min((whb & 0xFFu) - xo, K1_SPLIT) : 0u;
     const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
     uint32_t mask = 0;
     {
         const int32_t s0 = ws.Ax[0][slot], s1 = ws.Ax[1][slot], s2 = ws.Ax[2][slot];
-        int32_t F0 = ws.C[0][slot] + (int32_t)j * ws.By[0][slot] - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
-        int32_t F1 = ws.C[1][slot] + (int32_t)j * ws.By[1][slot] - (int32_t)((whb >> 17) & 1u);
-        int32_t F2 = ws.C[2][slot] + (int32_t)j * ws.By[2][slot] - (int32_t)((whb >> 18) & 1u);
+        int32_t F0 = ws.C[0][slot] + (int32_t)j * ws.By[0][slot] + (int32_t)xo * s0 - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
+        int32_t F1 = ws.C[1][slot] + (int32_t)j * ws.By[1][slot] + (int32_t)xo * s1 - (int32_t)((whb >> 17) & 1u);
+        int32_t F2 = ws.C[2][slot] + (int32_t)j * ws.By[2][slot] + (int32_t)xo * s2 - (int32_t)((whb >> 18) & 1u);
 #pragma unroll 1
         for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
     }
@@ -307,11 +308,11 @@ __device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_
     const uint32_t incl = warp_incl_scan(n, lane);
     uint32_t pos = pixTail + incl - n;
     pixTail += __shfl_sync(0xFFFFFFFFu, incl, 31);
-    const uint32_t tag = slot | (j << 10);
+    const uint32_t tag = slot | (xo << 6) | (j << 11);   // i + xo < 32: the add cannot carry into j
     while (mask) {
         const uint32_t i = (uint32_t)__ffs(mask) - 1u;
         mask &= mask - 1u;
-        ws.pixq[pos++ & (K1_PIXQ - 1)] = (uint16_t)(tag | (i << 6));
+        ws.pixq[pos++ & (K1_PIXQ - 1)] = (uint16_t)(tag + (i << 6));
     }
     __syncwarp();
 }
@@ -322,7 +323,7 @@ __device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws,
     if (lane >= cnt) return;
     const uint32_t e = ws.pixq[(pixHead + lane) & (K1_PIXQ - 1)];
     const uint32_t slot = e & 0x3Fu;
-    const int32_t pi = (int32_t)((e >> 6) & 0xFu), pj = (int32_t)(e >> 10);
+    const int32_t pi = (int32_t)((e >> 6) & 0x1Fu), pj = (int32_t)(e >> 11);
     const int32_t u1 = ws.C[1][slot] + pj * ws.By[1][slot] + pi * ws.Ax[1][slot];   // unbiased edge values (Appendix B.8)
     const int32_t u2 = ws.C[2][slot] + pj * ws.By[2][slot] + pi * ws.Ax[2][slot];
     const float z = depth_from((float)u1, (float)u2, ws.inv[slot], ws.z0[slot], ws.dz1[slot], ws.dz2[slot]);
@@ -378,22 +379,31 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
             if (qi < pc.clipCap) pc.clipQueue[qi] = tri; else atomicOr(&pc.status[2], OVF_LARGE);
         }
         const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
-        const uint32_t h = t.isSmall ? (uint32_t)(t.y1 - t.y0 + 1) : 0u;
-        const uint32_t hIncl = warp_incl_scan(h, lane);
-        if (t.isSmall) k1_store_small(ws, t, tri, (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1), rowTail + hIncl - h);
+        const uint32_t mySlot = (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1);
+        // row entries of this lane's triangle: one per bbox row, two (half rows) when the bbox is wider than K1_SPLIT
+        const uint32_t nEnt = t.isSmall ? (uint32_t)(t.y1 - t.y0 + 1) << ((t.x1 - t.x0 + 1) > (int32_t)K1_SPLIT ? 1 : 0) : 0u;
+        if (t.isSmall) k1_store_small(ws, t, tri, mySlot);
         ringPos += __popc(smallMask);
-        rowTail += __shfl_sync(0xFFFFFFFFu, hIncl, 31);
         if (CULL) curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
         k1_gather<CULL>(pc, ntri, ns, q);                            // in flight during the raster stages
         ns = nns;
-        __syncwarp();
 
-        // ---- 2./3. rows -> samples -> resolve ----------------------------------------------------------------
-        while (rowTail - rowHead >= 32u) {
-            k1_rows<SHADOW, CULL>(pc, ws, rowHead, 32u, pixTail, lane);
-            rowHead += 32u;
-            while (pixTail - pixHead >= 32u) { k1_pixels<SHADOW>(pc, ws, pixHead, 32u, lane); pixHead += 32u; }
-        }
+        // ---- 2./3. rows -> samples -> resolve; <= K1_SPLIT row entries per lane and round keep the rings within capacity ----
+        uint32_t done = 0;
+        do {
+            const uint32_t c = min(nEnt - done, K1_SPLIT);
+            const uint32_t cIncl = warp_incl_scan(c, lane);
+            const uint32_t rowPos = rowTail + cIncl - c;
+            for (uint32_t j = 0; j < c; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(mySlot | ((done + j) << 6));
+            rowTail += __shfl_sync(0xFFFFFFFFu, cIncl, 31);
+            done += c;
+            __syncwarp();
+            while (rowTail - rowHead >= 32u) {
+                k1_rows<SHADOW, CULL>(pc, ws, rowHead, 32u, pixTail, lane);
+                rowHead += 32u;
+                while (pixTail - pixHead >= 32u) { k1_pixels<SHADOW>(pc, ws, pixHead, 32u, lane); pixHead += 32u; }
+            }
+        } while (SMALL_LIMIT > SMALL_MAX && __any_sync(0xFFFFFFFFu, done < nEnt));
         // queued samples reference ring slots of this batch or the one before: drain them before the ring advances
         if (pixTail != pixHead) { k1_pixels<SHADOW>(pc, ws, pixHead, pixTail - pixHead, lane); pixHead = pixTail; }
         __syncwarp();

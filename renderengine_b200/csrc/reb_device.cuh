@@ -18,7 +18,16 @@ constexpr int HUGE_CAP = 64;                                      // capacity of
 #ifndef SMALL_MAX_D
 #define SMALL_MAX_D 14
 #endif
-constexpr int SMALL_MAX = SMALL_MAX_D;                                      // bbox spans <= 14 px: rasterised inside the setup kernel (8 was a cliff: C2 with the reference's 4096^2 map has ~6-10 px triangles, 630 -> 226 us / frame)
+#ifndef MED_MAX_D
+#define MED_MAX_D 29
+#endif
+// K1 rasterises a triangle itself when its bbox spans <= SMALL_LIMIT px (everything larger is binned for the tile stage).  The unit
+// of work of its row stage is one row of <= SMALL_MAX + 1 pixel centres: a bbox wider than that contributes two half rows per
+// row.  History: 8 was a cliff (C2 with the reference's 4096^2 map has 6-10 px triangles: 630 -> 226 us / frame at 14); 29
+// keeps 15-30 px triangles (ordinary game meshes) out of the binned path.
+constexpr int SMALL_MAX = SMALL_MAX_D;
+constexpr int SMALL_LIMIT = MED_MAX_D > SMALL_MAX_D ? MED_MAX_D : SMALL_MAX_D;
+static_assert(SMALL_LIMIT + 1 <= 2 * (SMALL_MAX + 1) && SMALL_LIMIT + 1 <= 32, "two half rows per row; 5-bit row / column numbers");
 constexpr uint32_t LIGHT_TYPE_DIRECTIONAL = 1, LIGHT_TYPE_SPOT = 3;   // phong.glsl:16-18
 
 // Post-transform vertex flags (VtxA.flags): bits 0-5 = outside x<-w, x>w, y<-w, y>w, z<0, z>w (Appendix B.2);

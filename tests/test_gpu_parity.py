@@ -136,16 +136,31 @@ def test_parity_large_and_huge_triangles(n_quads):
 
 
 def test_parity_lowpoly_binned_path():
-    """Level-1 icospheres at 640x360: triangles of ~30 px go through the binned tile lists."""
+    """Level-1 icospheres at 1280x720: triangles of ~60 px go through the binned tile lists (K1 rasterises up to 30-px boxes itself)."""
     from oracle import orc
     from renderengine_b200 import scene as sc
-    s = sc.make_scene("small", level=1)
+    s = sc.make_scene("small", level=1, width=1280, height=720)
     o = orc.Oracle(s)
     ref_shadow = o.render_shadow()
     ref = o.render_forward(ref_shadow)
     gpu = render_gpu(s)
     check_parity(s, gpu, ref_shadow, ref)
     assert gpu["counters"][1] > 100
+
+
+@pytest.mark.parametrize("level,width,height,shadow", [(2, 640, 360, 512), (2, 1280, 720, 1024), (1, 640, 360, 512), (3, 1920, 1080, 2048)])
+def test_parity_medium_triangles_half_rows(level, width, height, shadow):
+    """Triangles of 10 - 30 px: K1's own raster takes bboxes up to 30 x 30 pixel centres as rows of one or two half rows
+    (SMALL_LIMIT, reb_device.cuh), appended <= 15 entries per lane and round; larger ones stay binned.  Both sides of both limits."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.make_scene("small", level=level, width=width, height=height, shadow_size=shadow)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    check_parity(s, gpu, ref_shadow, ref)
+    assert (ref["tri_id"] != 0xFFFFFFFF).mean() > 0.05
 
 
 def test_parity_deindexed_cache(monkeypatch):
