@@ -8,6 +8,7 @@
 #include "reb_device.cuh"
 #include "reb_kernels.h"
 #include <algorithm>
+#include <cstdlib>
 
 namespace reb {
 
@@ -343,8 +344,11 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     K1Warp& ws = sm.w[warp];
-    const uint32_t nBatches = (pc.nTris + 31u) / 32u;
+    const uint32_t bl = pc.batchLog2, tpb = 1u << bl;
+    const uint32_t nBatches = (pc.nTris + tpb - 1u) >> bl;
     const uint32_t totalWarps = gridDim.x * K1_WARPS;
+    const uint32_t laneTri = lane < tpb ? lane : 0xFFFFFFFFu;   // lanes past the batch see triangle index >= nTris (nothing to do)
+#define K1_TRI(b) (laneTri == 0xFFFFFFFFu ? 0xFFFFFFFFu : ((b) << bl) + laneTri)
 
     // static schedule: warp g takes batches g, g + totalWarps, ... (a shared work counter would serialise on one
     // L2 atomic unit: ~10 cycles per same-address atomic-with-return chip-wide, measured as the top stall)
@@ -352,17 +356,17 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     uint4 q[3];
     bool curCulled = false;   // CULL: every triangle of the current batch belongs to a culled draw (warp-uniform)
     {
-        const uint32_t tri = batch * 32u + lane;
+        const uint32_t tri = K1_TRI(batch);
         const uint3 s0 = k1_load_slots<CULL>(pc, tri);
         if (CULL) curCulled = __all_sync(0xFFFFFFFFu, s0.x == SLOT_CULLED || tri >= pc.nTris);
         k1_gather<CULL>(pc, tri, s0, q);
     }
-    uint3 ns = k1_load_slots<CULL>(pc, (batch + totalWarps) * 32u + lane);   // slot stream runs two batches ahead of the raster stages
+    uint3 ns = k1_load_slots<CULL>(pc, K1_TRI(batch + totalWarps));   // slot stream runs two batches ahead of the raster stages
     uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
     while (batch < nBatches) {
         const uint32_t nbatch = batch + totalWarps;
-        const uint32_t tri = batch * 32u + lane, ntri = nbatch * 32u + lane;
-        const uint3 nns = k1_load_slots<CULL>(pc, (nbatch + totalWarps) * 32u + lane);   // in flight for a whole iteration
+        const uint32_t tri = K1_TRI(batch), ntri = K1_TRI(nbatch);
+        const uint3 nns = k1_load_slots<CULL>(pc, K1_TRI(nbatch + totalWarps));   // in flight for a whole iteration
         if (CULL && curCulled) {   // nothing of this batch is ours: only advance the software pipeline
             curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
             k1_gather<CULL>(pc, ntri, ns, q);
@@ -415,6 +419,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     }
 
     // the tile lists are laid out by k_clip_layout, after the clipped triangles (if any) have been counted too
+#undef K1_TRI
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -532,9 +537,16 @@ void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStrea
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], K1_THREADS, 0);
         perSM[v] = n > 0 ? n : 1;
     }
-    const uint32_t nBatches = (pc.nTris + 31u) / 32u;
+    // short draw lists: fewer triangles per batch until at least half the resident warps have one (16 k triangles of 25 px in
+    // 512 batches kept 512 warps busy for 43 us while 3 000 idled; C1's 64 k triangles in 2 000 full batches are best left alone)
+    const uint32_t maxWarps = (uint32_t)(numSMs * perSM[v]) * K1_WARPS;
+    PassConst pk = pc;
+    pk.batchLog2 = 5u;
+    static const bool fullBatches = std::getenv("REB_K1_FULL_BATCHES") != nullptr;   // A/B switch
+    while (!fullBatches && pk.batchLog2 > 0u && ((pc.nTris + (1u << pk.batchLog2) - 1u) >> pk.batchLog2) < maxWarps / 2u) --pk.batchLog2;
+    const uint32_t nBatches = (pc.nTris + (1u << pk.batchLog2) - 1u) >> pk.batchLog2;
     const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[v]));
-    launch_k(kern[v], dim3(grid), dim3(K1_THREADS), st, true, pc);
+    launch_k(kern[v], dim3(grid), dim3(K1_THREADS), st, true, pk);
 }
 
 void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {

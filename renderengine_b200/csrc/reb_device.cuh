@@ -96,6 +96,9 @@ struct PassConst {
     // Appendix B.15 (multisampling): this raster pass samples at pixel centre - shift / 256, implemented as an exact integer
     // shift of the snapped vertices (edge functions and depth are translation-invariant).  0 for 1-sample passes.
     int32_t shiftX, shiftY;
+    // K1: log2 of the triangles a warp takes per batch (5 = one per lane; launch_setup_raster lowers it for short draw lists
+    // so that every resident warp gets a batch: the row and sample stages spread the work over the lanes anyway)
+    uint32_t batchLog2;
     // per-draw visibility for this rank's rows (sort-first split): written by k_cull_draws before K0, NULL = no culling
     const uint32_t* drawVisible;
     const uint32_t* blockVisible;   // the same per 256-triangle block (K1), written by k_cull_blocks
