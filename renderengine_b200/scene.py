@@ -342,6 +342,8 @@ def make_scene(config="C2", seed=1234, ground=True, azimuth=0.0, **overrides):
     cfg.update(overrides)
     if os.environ.get("REB_SHADOW_SIZE") and cfg["shadow_size"]:   # e.g. 4096, the reference's default map (ShadowSystem.h)
         cfg["shadow_size"] = int(os.environ["REB_SHADOW_SIZE"])
+    if os.environ.get("REB_SCENE_GRID"):    # "100x100": many small draws (one draw per sphere)
+        cfg["grid"] = tuple(int(v) for v in os.environ["REB_SCENE_GRID"].split("x"))
     if os.environ.get("REB_SCENE_LEVEL"):   # triangle-size sweeps of a named config (tools/kt.py)
         cfg["level"] = int(os.environ["REB_SCENE_LEVEL"])
     nx, nz = cfg["grid"]; level = cfg["level"]
