@@ -470,7 +470,7 @@ __global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constan
 }
 
 // Re-bases a draw list's index stream into cache-slot space, in submission order (runs when the list changes).
-__global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ PassConst pc, uint32_t* __restrict__ flat) {
+__global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ PassConst pc, uint32_t* __restrict__ flat, uint32_t* __restrict__ triMaterial) {
     const uint32_t tri = blockIdx.x * 256u + threadIdx.x;
     if (tri >= pc.nTris) return;
     const uint32_t d = find_draw<false>(pc.draws, pc.nDraws, tri);
@@ -478,6 +478,7 @@ __global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ P
     const int32_t off = pc.draws[d].cacheOffset;
 #pragma unroll
     for (int k = 0; k < 3; ++k) flat[3ull * tri + k] = (uint32_t)((int32_t)ix[k] + off);
+    triMaterial[tri] = pc.draws[d].material;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -566,9 +567,9 @@ void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
     launch_k(k_pass_reset, dim3((unsigned)numSMs), dim3(256), st, true, pc);
 }
 
-void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st) {
+void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st) {
     if (pc.nTris == 0) return;
-    k_flatten_slots<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, flat);
+    k_flatten_slots<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, flat, triMaterial);
 }
 
 void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st) {

@@ -33,9 +33,11 @@ struct TlSetup {                 // Appendix B.6-B.8 of one snapped triangle, fr
 };
 
 __device__ __forceinline__ void tl_load(const PassConst& pc, uint32_t tri, VtxA a[3]) {
+    uint32_t s3[3] = {3u * tri, 3u * tri + 1u, 3u * tri + 2u};
+    if (!pc.deindexed) { const uint32_t* f = pc.flatSlots + 3ull * tri; s3[0] = __ldg(f); s3[1] = __ldg(f + 1); s3[2] = __ldg(f + 2); }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+        const uint32_t slot = s3[k];
         const uint4 q = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         a[k] = {(int32_t)q.x, (int32_t)q.y, __uint_as_float(q.z), q.w};
     }

@@ -25,7 +25,7 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaq
     VtxA* vtxA = nullptr; VtxBC* vtxBC = nullptr; size_t cacheCap = 0;
     float2* vtxUV = nullptr; size_t uvCap = 0;          // forward pass, only once textures are registered
     uint32_t* blockDraw = nullptr; size_t blockDrawCap = 0; uint32_t triBlocks = 0;   // [triBlocks] by triangle, then by cache slot
-    uint32_t* flatSlots = nullptr; size_t flatCap = 0;   // 3 cache slots per triangle, submission order (indexed mode)
+    uint32_t* flatSlots = nullptr; uint32_t* triMaterial = nullptr; size_t flatCap = 0;   // 3 cache slots + the material handle per triangle, submission order (indexed mode); flatCap in triangles
     uint32_t cacheSize = 0, deindexed = 0;
     uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;
     float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
@@ -310,14 +310,14 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         launch_block_bounds(pcb, ps.blockBox, ctx->stream); ctx->launches++;
     }
     if (!ps.deindexed && tri) {   // index stream re-based into cache-slot space
-        if (3 * tri > ps.flatCap) {
-            int rc = dev_alloc(ctx, &ps.flatSlots, (size_t)(3 * tri));
-            if (rc) return rc;
-            ps.flatCap = (size_t)(3 * tri);
+        if (tri > ps.flatCap) {
+            int rc;
+            if ((rc = dev_alloc(ctx, &ps.flatSlots, (size_t)(3 * tri))) || (rc = dev_alloc(ctx, &ps.triMaterial, (size_t)tri))) return rc;
+            ps.flatCap = (size_t)tri;
         }
         PassConst pc;
         fill_pass(ctx, kind, pc);
-        launch_flatten_slots(pc, ps.flatSlots, ctx->stream); ctx->launches++;
+        launch_flatten_slots(pc, ps.flatSlots, ps.triMaterial, ctx->stream); ctx->launches++;
         CU(cudaStreamSynchronize(ctx->stream));
     }
     ps.draws.assign(draws, draws + n);
@@ -338,7 +338,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.large = ctx->large; pc.largeCap = ctx->largeAlloc; pc.clipQueue = ctx->clipQueue; pc.clipCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
     pc.tileCount = ctx->tileCount[kind == 2 ? 1 : kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
-    pc.flatSlots = ps.flatSlots;
+    pc.flatSlots = ps.flatSlots; pc.triMaterial = ps.triMaterial;
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + 8 * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;

@@ -62,7 +62,7 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible,
                     ctx->pass[2].dDraws, ctx->pass[2].vtxA, ctx->pass[2].vtxBC, ctx->pass[2].blockDraw, ctx->pass[2].flatSlots, ctx->pass[2].drawBounds,
                     ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
-                    ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge};
+                    ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);

@@ -88,6 +88,7 @@ struct PassConst {
     uint32_t* tileStart;          // per tile: first entry of its list inside tileList
     uint32_t* tileList; uint32_t listCap;
     const uint32_t* flatSlots;    // 3 cache slots per triangle in submission order (indexed mode)
+    const uint32_t* triMaterial;  // raw material handle of every triangle's draw (indexed mode; shading reads it instead of walking to the draw record)
     const uint32_t* triBlockDraw; // draw containing the first triangle of every 256-triangle block
     const uint32_t* slotBlockDraw;// draw containing the first cache slot of every 256-slot block
     uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket (k_clip_layout) [6] clip-queue length
@@ -205,6 +206,25 @@ __device__ __forceinline__ uint32_t find_draw_block(const DrawDev* __restrict__ 
     uint32_t d = __ldg(blockDraw + (v >> 8));
     while (d + 1 < nDraws && draw_key<BY_CACHE>(draws, d + 1) <= v) ++d;
     return d;
+}
+
+// What shading needs to know about triangle `tri`: the cache slots of its corners and its draw's material handle.  Indexed
+// mode: four independent loads from the tables k_flatten_slots wrote (the material handle used to sit behind the blockDraw ->
+// draw key -> draw record chain; packing all four words into one 16-byte record instead made the tile stage 2 us faster but
+// K1, which streams the slots of every triangle, 3 us slower per pass on C2 and 22 us on C3); de-indexed mode derives the
+// slots and walks to the draw.
+struct TriRef { uint32_t s[3]; uint32_t materialRaw; };
+__device__ __forceinline__ TriRef tri_ref(const PassConst& pc, uint32_t tri) {
+    TriRef r;
+    if (pc.deindexed) {
+        r.s[0] = 3u * tri; r.s[1] = 3u * tri + 1u; r.s[2] = 3u * tri + 2u;
+        const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
+        r.materialRaw = __ldg(&pc.draws[d].material);
+    } else {
+        const uint32_t* f = pc.flatSlots + 3ull * tri;
+        r.s[0] = __ldg(f); r.s[1] = __ldg(f + 1); r.s[2] = __ldg(f + 2); r.materialRaw = __ldg(pc.triMaterial + tri);
+    }
+    return r;
 }
 
 // Appendix B.3 (revision r1c): the clip-space polygon of parent triangle `tri` — vertex stage re-run on its three source

@@ -47,7 +47,7 @@ void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st)
 void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
 void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);   // K1c: Appendix B.3 clipping + tile-list layout
-void launch_flatten_slots(const PassConst& pc, uint32_t* flat, cudaStream_t st);
+void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st);
 void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);   // PDL-chained after K1
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);

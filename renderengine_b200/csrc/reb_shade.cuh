@@ -199,12 +199,12 @@ static __device__ __noinline__ float4 homogeneous_weights(const PassConst& pc, V
 // builder-defined Phong main() (Appendix B.11) over phong.glsl + shadow.glsl.
 template <bool TEXTURED, bool AFFINE>
 __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
-    const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
-    const uint32_t materialRaw = __ldg(&pc.draws[d].material);
+    const TriRef tr = tri_ref(pc, tri);
+    const uint32_t materialRaw = tr.materialRaw;
     int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3]; uint32_t vflags = 0u;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+        const uint32_t slot = tr.s[k];
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         const float4* bc = reinterpret_cast<const float4*>(pc.vtxBC + slot);
         const float4 b = __ldg(bc), c = __ldg(bc + 1);
@@ -247,7 +247,7 @@ __device__ __forceinline__ float4 shade_pixel(const PassConst& pc, const ShadeCo
         float2 uvv[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+            const uint32_t slot = tr.s[k];
             uvv[k] = __ldg(pc.vtxUV + slot);
         }
         float tu[3], tv[3];

@@ -118,12 +118,12 @@ __device__ __forceinline__ float4 pbr_lighting(const ShadeConst& sh, const PbrRe
 // shade_pixel: Appendix B.10 from the cached snapped vertices).
 template <bool TEXTURED, bool AFFINE>
 __device__ __forceinline__ float4 shade_pixel_pbr(const PassConst& pc, const ShadeConst& sh, int x, int y, uint32_t tri) {
-    const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
-    const uint32_t materialRaw = __ldg(&pc.draws[d].material);
+    const TriRef tr = tri_ref(pc, tri);
+    const uint32_t materialRaw = tr.materialRaw;
     int32_t X[3], Y[3]; float invw[3]; V3 world[3], nrm[3]; uint32_t slots[3]; uint32_t vflags = 0u;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const uint32_t slot = pc.deindexed ? 3u * tri + (uint32_t)k : __ldg(pc.flatSlots + 3ull * tri + k);
+        const uint32_t slot = tr.s[k];
         slots[k] = slot;
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         const float4* bc = reinterpret_cast<const float4*>(pc.vtxBC + slot);
