@@ -68,8 +68,10 @@ __device__ __noinline__ void tile_walk(const PassConst& pc, int32_t X0, int32_t 
 // cache gathers of batch n+1 are issued before batch n is rasterised):
 //   1. gather 3 VtxA (16 B each) through the flattened slot stream, clip-flag logic, facing (int64
 //      shoelace), pixel-centre bbox, classification:
-//        small (spans <= SMALL_MAX px) -> edge equations appended to the warp's 64-slot record ring, one
-//                                         entry per covered pixel ROW appended to the warp's row ring;
+//        small (spans <= SMALL_LIMIT px) -> edge equations appended to the warp's 64-slot record ring, one
+//                                         entry per bbox ROW (two half rows when the bbox is wider than
+//                                         SMALL_MAX + 1) appended to the warp's row ring, <= SMALL_MAX + 1
+//                                         entries per lane and round;
 //        huge  (> HUGE_TILES tiles)    -> short broadcast list tested by every tile;
 //        large (everything else)       -> warp-aggregated append to the LargeRec queue; the warp walks the
 //                                         triangle's tiles and bumps the per-tile counts.
