@@ -148,9 +148,10 @@ def test_parity_lowpoly_binned_path():
     assert gpu["counters"][1] > 100
 
 
-@pytest.mark.parametrize("level,width,height,shadow", [(2, 640, 360, 512), (2, 1280, 720, 1024), (1, 640, 360, 512), (3, 1920, 1080, 2048)])
+@pytest.mark.parametrize("level,width,height,shadow", [(2, 640, 360, 512), (2, 1280, 720, 1024), (1, 640, 360, 512), (3, 1920, 1080, 2048),
+                                                        (1, 960, 540, 768), (1, 1280, 720, 1024), (0, 640, 360, 512)])
 def test_parity_medium_triangles_half_rows(level, width, height, shadow):
-    """Triangles of 10 - 30 px: K1's own raster takes bboxes up to 30 x 30 pixel centres as rows of one or two half rows
+    """Triangles of 10 - 120 px: K1's own raster takes bboxes up to 30 x 30 pixel centres as rows of one or two half rows
     (SMALL_LIMIT, reb_device.cuh), appended <= 15 entries per lane and round; larger ones stay binned.  Both sides of both limits."""
     from oracle import orc
     from renderengine_b200 import scene as sc
