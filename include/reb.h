@@ -22,6 +22,7 @@ extern "C" {
 #endif
 
 #define REB_ABI_VERSION 1
+#define REB_MAX_EXTENT 16384u   /* largest width / height of a render target, shadow map or texture */
 
 typedef struct reb_ctx reb_ctx;
 
@@ -106,9 +107,9 @@ int reb_set_shading_model(reb_ctx* ctx, uint32_t model);
  * RenderScene::SortTranslucentMeshes does (RenderScene.cpp:127-159) — with cull none, depth test LessOrEqual + depth
  * write and src-alpha blending (GraphicsPipelineCache.cpp:305-315), then the skybox.  Triangle IDs of the translucent
  * list continue after the opaque list's.  reb_render_forward(ctx, d, n) == reb_render_forward2(ctx, d, n, NULL, 0).
- * Limits of this version: 1 sample per pixel only; a pixel keeps at most 16 translucent fragments and a frame
- * max(4 * W * H, 2^20) of them; translucent triangles that cross the eye plane / guard band are dropped — all counted in
- * reb_get_counters()[0]. */
+ * Translucent triangles that cross the eye plane / guard band are clipped like opaque ones.
+ * Limits of this version: a pixel keeps at most 16 translucent fragments and a frame max(4 * W * H, 2^20) of them;
+ * fragments beyond either limit are dropped and counted in reb_get_counters()[0]. */
 int reb_render_forward2(reb_ctx* ctx, const reb_draw* opaque, uint32_t nOpaque, const reb_draw* translucent, uint32_t nTranslucent);
 
 /* Skybox::Skybox / Skybox::Render — Skybox.cpp:58-92,126-140; TextureCache::LoadCubeMapFaces — TextureCache.cpp:199-290;
@@ -160,7 +161,8 @@ int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint3
  * e.g. by an NCCL broadcast from the rank that rendered it */
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);
 
-/* diagnostics: counters[0] triangles needing true clipping (dropped; outside the bit-exact domain),
+/* diagnostics: counters[0] clip children that could not be set up (non-finite input) + translucent fragments dropped by a
+ * capacity limit — 0 for every finite scene within the limits above (triangles crossing the eye plane are CLIPPED, not dropped),
  * [1] triangles sent to the binned tile path in the last pass, [2] tile-list entries, [3] queue regrow count */
 int reb_get_counters(reb_ctx* ctx, uint64_t* counters4);
 /* number of kernels this library has launched on the context since creation */

@@ -826,6 +826,29 @@ void orc_mat4_mul_vec4(const float* m, const float* v, float* out) {
 }
 void orc_normal_matrix(const float* mat4, float* out9) { normal_matrix(mat4, out9); }
 
+// The composed vertex stages exactly as the raster front end and the shading stage call them (vertex_stage + the per-node
+// normal matrix), for pinning against the reference's shaders run through glm (tests/golden: vs_primitive / vs_shadow).
+// primitive.vert:49-57: out10 = clip(4) world(3) normal(3); shadow_map.vert:48-52: out4 = clip.
+void orc_primitive_vert(const float* transform, const float* view, const float* proj, const float* pos, const float* nrm, float* out10) {
+    float PV[16];
+    mat4_mul_mat4(proj, view, PV);
+    PassParams pp{}; pp.PV = PV; pp.divideWorldByW = true; pp.W = pp.H = 1;
+    V3 world;
+    const V4 c = vertex_stage(pp, transform, pos, &world);
+    float N[9];
+    normal_matrix(transform, N);
+    const V3 n = normalize3(mat3_mul(N, {nrm[0], nrm[1], nrm[2]}));
+    out10[0] = c.x; out10[1] = c.y; out10[2] = c.z; out10[3] = c.w;
+    out10[4] = world.x; out10[5] = world.y; out10[6] = world.z; out10[7] = n.x; out10[8] = n.y; out10[9] = n.z;
+}
+void orc_shadow_vert(const float* transform, const float* view, const float* proj, const float* pos, float* out4) {
+    float PV[16];
+    mat4_mul_mat4(proj, view, PV);
+    PassParams pp{}; pp.PV = PV; pp.divideWorldByW = false; pp.W = pp.H = 1;
+    const V4 c = vertex_stage(pp, transform, pos, nullptr);
+    out4[0] = c.x; out4[1] = c.y; out4[2] = c.z; out4[3] = c.w;
+}
+
 void orc_phong_lighting(const uint8_t* light112, const float* p, const float* normal, const float* fragPos,
                         const float* viewPos, float shadow, float* out4) {
     Light l = load_light(light112);

@@ -82,6 +82,9 @@ int orc_render_forward_msaa4(const orc_scene* s, const float* shadowMap, float* 
 void orc_mat4_mul(const float* a, const float* b, float* out);
 void orc_mat4_mul_vec4(const float* m, const float* v, float* out);
 void orc_normal_matrix(const float* mat4, float* out9);
+/* the composed vertex stages as the renderer calls them: primitive.vert:49-57 -> clip(4) world(3) normal(3); shadow_map.vert:48-52 -> clip */
+void orc_primitive_vert(const float* transform16, const float* view16, const float* proj16, const float* pos3, const float* nrm3, float* out10);
+void orc_shadow_vert(const float* transform16, const float* view16, const float* proj16, const float* pos3, float* out4);
 void orc_phong_lighting(const uint8_t* light112, const float* props9 /* diffuse4 specular4 shininess */,
                         const float* normal, const float* fragPos, const float* viewPos, float shadow, float* out4);
 float orc_compute_shadow(const uint8_t* light112, const float* fragPos, const float* normal,

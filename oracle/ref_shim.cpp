@@ -189,4 +189,37 @@ void ref_mat4_inverse(const float* m16, float* out16) {
     std::memcpy(out16, glm::value_ptr(m), 64);
 }
 
+// ComputeDirectionalLightViewMatrix + ComputeShadowTransform (ShadowSystem.cpp:129-204).  That file needs the Vulkan headers and
+// cannot be compiled here, so its statements are replayed over the reference's OWN compiled pieces — Camera::ComputeFrustrumCorners
+// (Camera.cpp:3-25), BoundingBox::FromPoints / operator* / Transform / Intersects / Union (BoundingBox.{h,cpp}), glm::lookAt /
+// inverse / ortho, glm_vk::kClip — in the reference's order.  One deviation, SURVEY.md F8: ShadowSystem.cpp:136 reads `up`
+// uninitialised (`up = cross(lightDirection, up)`); the evident intent `cross(lightDirection, right)` is used.
+void ref_shadow_transform(const float* lightDir, const float* eye, const float* lookat, const float* up, float fov, float nearP, float farP, int w, int h,
+                          const float* sceneMin, const float* sceneMax, const float* boxes6, const float* transforms16, int nBoxes,
+                          float* view16, float* proj16, float* transform16) {
+    Camera camera(glm::make_vec3(eye), glm::make_vec3(lookat), glm::make_vec3(up), fov, nearP, farP, w, h);
+    camera.SetImageExtent(w, h);
+    const glm::vec3 lightDirection = glm::make_vec3(lightDir);
+    glm::vec3 right(0.0f, 0.0f, 1.0f);
+    if (std::abs(glm::dot(lightDirection, right)) > 0.9999f) right = glm::vec3(1.0f, 0.0f, 0.0f);
+    const glm::vec3 lup = glm::cross(lightDirection, right);
+    const glm::mat4 shadowView = glm::lookAt(glm::vec3(0.0f, 0.0f, 0.0f), lightDirection, lup);
+    BoundingBox sceneBox; sceneBox.min = glm::make_vec3(sceneMin); sceneBox.max = glm::make_vec3(sceneMax);
+    BoundingBox camBox_world = BoundingBox::FromPoints(camera.ComputeFrustrumCorners());
+    BoundingBox camBox_view = shadowView * camBox_world;
+    BoundingBox sceneBox_view = shadowView * sceneBox;
+    camBox_view.max.z = sceneBox_view.max.z;
+    camBox_world = camBox_view.Transform(glm::inverse(shadowView));
+    BoundingBox lightBox_world;
+    for (int i = 0; i < nBoxes; ++i) {
+        BoundingBox box_local; box_local.min = glm::make_vec3(boxes6 + 6 * i); box_local.max = glm::make_vec3(boxes6 + 6 * i + 3);
+        BoundingBox box_world = box_local.Transform(glm::make_mat4(transforms16 + 16 * i));
+        if (box_world.Intersects(camBox_world)) lightBox_world = lightBox_world.Union(box_world);
+    }
+    BoundingBox lightBox_view = lightBox_world.Transform(shadowView);
+    const glm::mat4 proj = glm_vk::kClip * glm::ortho(lightBox_view.min.x, lightBox_view.max.x, lightBox_view.min.y, lightBox_view.max.y, lightBox_view.min.z, lightBox_view.max.z);
+    const glm::mat4 transform = proj * shadowView;   // ShadowSystem.cpp:303
+    std::memcpy(view16, glm::value_ptr(shadowView), 64); std::memcpy(proj16, glm::value_ptr(proj), 64); std::memcpy(transform16, glm::value_ptr(transform), 64);
+}
+
 }  // extern "C"

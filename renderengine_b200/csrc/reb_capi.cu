@@ -602,7 +602,11 @@ int check_and_recover(reb_ctx* ctx) {
             PassConst pc;
             if ((rc = prepare_pass(ctx, k, pc))) return rc;
             if (k == 0) std::memcpy(pc.PV, ctx->recordedSPV, 64);
-            if ((rc = run_pass(ctx, k, pc, false))) return rc;
+            // the replayed opaque pass must leave what the translucent list composites over (linear colour + depth, sky / encode deferred)
+            if (k == 1) ctx->tlFollows = ctx->tlPending;
+            rc = run_pass(ctx, k, pc, false);
+            if (k == 1) ctx->tlFollows = false;
+            if (rc) return rc;
         }
         if (p1 && ctx->tlPending && (rc = run_translucent(ctx))) return rc;   // the opaque frame was replayed under it
         CU(cudaStreamSynchronize(ctx->stream));

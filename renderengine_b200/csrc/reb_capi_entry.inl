@@ -12,6 +12,8 @@ int reb_create(const reb_params* params, reb_ctx** out) {
     reb_ctx* ctx = nullptr;
     if (!params || !out || params->struct_size != sizeof(reb_params)) return fail(nullptr, REB_E_INVALID, "reb_create: bad params / struct_size");
     if (params->width == 0 || params->height == 0) return fail(nullptr, REB_E_INVALID, "reb_create: zero extent");
+    if (params->width > REB_MAX_EXTENT || params->height > REB_MAX_EXTENT)   // K1 packs x0 | y0 << 16 and 16-bit ring fields; same limit as shadow maps / textures
+        return fail(nullptr, REB_E_INVALID, "reb_create: extent must be in 1..16384");
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail(nullptr, REB_E_NO_DEVICE, "reb_create: no CUDA device (there is no CPU fallback)");
     if (params->device < 0 || params->device >= count) return fail(nullptr, REB_E_INVALID, "reb_create: device ordinal out of range");
@@ -315,8 +317,6 @@ int reb_set_skybox(reb_ctx* ctx, const void* facesRGBA16, uint32_t width, uint32
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // the host buffer is consumed before returning; earlier frames are done
     if (e != cudaSuccess) { cudaFree(dev); return fail(ctx, REB_E_CUDA, std::string("reb_set_skybox: ") + cudaGetErrorString(e)); }
     if (ctx->skyFaces) cudaFree(ctx->skyFaces);
-    if (ctx->msDepth) cudaFree(ctx->msDepth);
-    if (ctx->msTriId) cudaFree(ctx->msTriId);
     ctx->skyFaces = dev; ctx->skyW = width; ctx->skyH = height;
     return REB_OK;
 }
@@ -426,6 +426,8 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
     CU(cudaSetDevice(ctx->device));
     { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->copyStream) CU(cudaStreamSynchronize(ctx->copyStream));   // an async readback may still be draining a swapchain image
+    ctx->copyInFlight[0] = ctx->copyInFlight[1] = false; ctx->asyncOutstanding = false;
     ctx->rank = rank; ctx->nRanks = nRanks; ctx->bandH = bandH;
     return alloc_targets(ctx);   // re-clear: pixels outside this rank's bands keep the clear values
 }

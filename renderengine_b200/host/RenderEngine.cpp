@@ -170,7 +170,6 @@ void CameraViewSystem::Update(Renderer& renderer) {
 }
 
 // ---- ShadowSystem -----------------------------------------------------------------------------------------------------
-namespace {
 // ComputeDirectionalLightViewMatrix (ShadowSystem.cpp:129-147).  The reference reads `up` uninitialised
 // (`up = cross(lightDirection, up)`, `right` unused): the evident intent, cross(lightDirection, right), is used.
 mat4 ComputeDirectionalLightViewMatrix(vec3 lightDirection) {
@@ -179,7 +178,26 @@ mat4 ComputeDirectionalLightViewMatrix(vec3 lightDirection) {
     const vec3 up = cross(lightDirection, right);
     return lookAt(vec3(0.0f, 0.0f, 0.0f), lightDirection, up);
 }
-}  // namespace
+// ComputeShadowTransform (ShadowSystem.cpp:148-204): light view, ortho fit of the scene boxes that intersect the camera box
+// stretched towards the light, proj = kClip * ortho.  Pure host arithmetic; checked bit for bit against the reference's own
+// Camera / BoundingBox / glm code by tests/cpp/test_golden_math.cpp.
+ShadowTransform ComputeShadowTransform(vec3 lightDirection, const Camera& camera, BoundingBox sceneBox, const std::vector<BoundingBox>& boxes,
+                                       const std::vector<mat4>& transforms) {
+    BoundingBox camBox_world = BoundingBox::FromPoints(camera.ComputeFrustrumCorners());
+    const mat4 shadowView = ComputeDirectionalLightViewMatrix(lightDirection);
+    BoundingBox camBox_view = shadowView * camBox_world;
+    const BoundingBox sceneBox_view = shadowView * sceneBox;
+    camBox_view.max.z = sceneBox_view.max.z;   // keep every caster between the light and the camera frustum
+    camBox_world = camBox_view.Transform(inverse(shadowView));
+    BoundingBox lightBox_world;
+    for (size_t i = 0; i < boxes.size(); ++i) {
+        const BoundingBox box_world = boxes[i].Transform(transforms[i]);
+        if (box_world.Intersects(camBox_world)) lightBox_world = lightBox_world.Union(box_world);
+    }
+    const BoundingBox lightBox_view = lightBox_world.Transform(shadowView);
+    const mat4 proj = ortho(lightBox_view.min.x, lightBox_view.max.x, lightBox_view.min.y, lightBox_view.max.y, lightBox_view.min.z, lightBox_view.max.z);
+    return {shadowView, kClip() * proj};
+}
 
 ShadowSystem::ShadowSystem(uint32_t shadowMapExtent, Renderer& renderer, RenderScene& scene) : m_extent(shadowMapExtent), m_renderer(&renderer), m_scene(&scene) {}
 
@@ -194,8 +212,7 @@ void ShadowSystem::UploadToGPU() {
     for (size_t i = 0; i < m_lights.size(); ++i)
         if (m_deviceIds[i] == 0xFFFFFFFFu) m_renderer->Check(reb_shadow_create(m_renderer->GetContext(), m_extent, &m_deviceIds[i]), "ShadowSystem::UploadToGPU");
 }
-// ComputeShadowTransform + Update (ShadowSystem.cpp:148-204, 277-317): light view, ortho fit of the scene boxes that
-// intersect the camera box stretched towards the light, proj = kClip * ortho, transform = proj * view.
+// Update (ShadowSystem.cpp:277-317): transform = proj * view (:303)
 void ShadowSystem::Update(const Camera& camera, BoundingBox /*sceneBoundingBox: recomputed from the tree as in ShadowSystem.cpp:289*/) {
     if (GetShadowCount() == 0) return;
     const SceneTree* sceneTree = m_scene->GetSceneTree();
@@ -203,23 +220,10 @@ void ShadowSystem::Update(const Camera& camera, BoundingBox /*sceneBoundingBox: 
     const BoundingBox sceneBox = sceneTree->ComputeWorldBoundingBox();
     for (ShadowID id = 0; id < m_lights.size(); ++id) {
         const Light& light = lightSystem->GetLight(m_lights[id]);
-        BoundingBox camBox_world = BoundingBox::FromPoints(camera.ComputeFrustrumCorners());
-        const mat4 shadowView = ComputeDirectionalLightViewMatrix(vec3(light.direction[0], light.direction[1], light.direction[2]));
-        BoundingBox camBox_view = shadowView * camBox_world;
-        const BoundingBox sceneBox_view = shadowView * sceneBox;
-        camBox_view.max.z = sceneBox_view.max.z;   // keep every caster between the light and the camera frustum
-        camBox_world = camBox_view.Transform(inverse(shadowView));
-        BoundingBox lightBox_world;
-        const auto& boxes = sceneTree->GetBoundingBoxes();
-        const auto& transforms = sceneTree->GetTransforms();
-        for (size_t i = 0; i < boxes.size(); ++i) {
-            const BoundingBox box_world = boxes[i].Transform(transforms[i]);
-            if (box_world.Intersects(camBox_world)) lightBox_world = lightBox_world.Union(box_world);
-        }
-        const BoundingBox lightBox_view = lightBox_world.Transform(shadowView);
-        const mat4 proj = ortho(lightBox_view.min.x, lightBox_view.max.x, lightBox_view.min.y, lightBox_view.max.y, lightBox_view.min.z, lightBox_view.max.z);
-        m_views[id] = shadowView;
-        m_projs[id] = kClip() * proj;
+        const ShadowTransform t = ComputeShadowTransform(vec3(light.direction[0], light.direction[1], light.direction[2]), camera, sceneBox,
+                                                         sceneTree->GetBoundingBoxes(), sceneTree->GetTransforms());
+        m_views[id] = t.view;
+        m_projs[id] = t.proj;
         m_transforms[id] = m_projs[id] * m_views[id];
         if (m_deviceIds[id] != 0xFFFFFFFFu)
             m_renderer->Check(reb_shadow_set_transform(m_renderer->GetContext(), m_deviceIds[id], m_views[id].data(), m_projs[id].data()), "ShadowSystem::Update");

@@ -82,6 +82,12 @@ private:
     int m_imageWidth = 1, m_imageHeight = 1;
 };
 
+// ---- the host arithmetic of ShadowSystem::Update (ShadowSystem.cpp:129-204), free functions as in the reference's anonymous namespace ----
+struct ShadowTransform { mat4 view, proj; };   // proj = kClip * ortho
+mat4 ComputeDirectionalLightViewMatrix(vec3 lightDirection);
+ShadowTransform ComputeShadowTransform(vec3 lightDirection, const Camera& camera, BoundingBox sceneBox, const std::vector<BoundingBox>& boxes,
+                                       const std::vector<mat4>& transforms);
+
 // ---- handles (BindlessDefines.h:6-8, SceneTree.h:15, LightSystem.h:35, ShadowSystem.h:37, MaterialDefines.h:26-97) ---------
 enum class SceneNodeHandle : uint32_t { Invalid = (std::numeric_limits<uint32_t>::max)() };
 enum class TextureHandle : uint32_t { Invalid = (std::numeric_limits<uint32_t>::max)() };

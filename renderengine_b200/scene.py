@@ -29,11 +29,43 @@ K_CLIP = np.array([[1, 0, 0, 0], [0, -1, 0, 0], [0, 0, 0.5, 0.5], [0, 0, 0, 1]],
 
 
 # ---------------------------------------------------------------------------------------------
-# small float32 linear algebra in glm conventions (matrices stored column-major as flat[16])
+# small float32 linear algebra, glm 1.0.2's operations in glm's order (matrices stored column-major as flat[16]; inside this
+# module a matrix is a 4x4 numpy array indexed [row, col]).  tests/test_golden_host.py checks every function below bit for bit
+# against vectors generated from the reference's own Camera.cpp / BoundingBox.cpp / glm (tests/golden/gen_golden*.py), so the
+# scenes the tests and the bench render use exactly the matrices the reference would compute for the same camera and light.
 # ---------------------------------------------------------------------------------------------
+def _tanf(x):
+    """glm::tan -> std::tan(float): the C library's tanf (numpy's float32 tan is a different implementation)."""
+    global _LIBM
+    try:
+        if _LIBM is None:
+            import ctypes
+            _LIBM = ctypes.CDLL("libm.so.6")
+            _LIBM.tanf.restype = ctypes.c_float; _LIBM.tanf.argtypes = [ctypes.c_float]
+        return f32(_LIBM.tanf(float(x)))
+    except OSError:
+        return np.tan(f32(x), dtype=f32)
+
+
+_LIBM = None
+
+
+def _dot3(a, b):
+    """glm compute_dot<vec3> (detail/func_geometric.inl:48-55): (x + y) + z."""
+    a = np.asarray(a, f32); b = np.asarray(b, f32)
+    return f32(f32(f32(a[0] * b[0]) + f32(a[1] * b[1])) + f32(a[2] * b[2]))
+
+
+def _cross(x, y):
+    """glm compute_cross (detail/func_geometric.inl:73-83)."""
+    x = np.asarray(x, f32); y = np.asarray(y, f32)
+    return np.array([x[1] * y[2] - y[1] * x[2], x[2] * y[0] - y[2] * x[0], x[0] * y[1] - y[0] * x[1]], f32)
+
+
 def _norm(v):
+    """glm normalize: v * inversesqrt(dot(v, v)), inversesqrt = 1 / sqrt (func_geometric.inl:98-105, func_exponential.inl:134-139)."""
     v = np.asarray(v, f32)
-    return (v * (f32(1) / np.sqrt(np.dot(v, v), dtype=f32))).astype(f32)
+    return (v * f32(f32(1) / np.sqrt(_dot3(v, v), dtype=f32))).astype(f32)
 
 
 def to_flat(m_rowmajor):
@@ -45,28 +77,75 @@ def from_flat(flat):
     return np.asarray(flat, f32).reshape(4, 4).T.copy()
 
 
+def mat4_mul(a, b):
+    """glm mat4 * mat4 (detail/type_mat4x4.inl:660-697): column c = ((A0 b.x + A1 b.y) + A2 b.z) + A3 b.w."""
+    a = np.asarray(a, f32); b = np.asarray(b, f32)
+    out = np.empty((4, 4), f32)
+    for c in range(4):
+        col = a[:, 0] * b[0, c]
+        col = col + a[:, 1] * b[1, c]
+        col = col + a[:, 2] * b[2, c]
+        col = col + a[:, 3] * b[3, c]
+        out[:, c] = col
+    return out
+
+
+def mat4_vec4(m, v):
+    """glm mat4 * vec4 (detail/type_mat4x4.inl:537-583): (m0 x + m1 y) + (m2 z + m3 w)."""
+    m = np.asarray(m, f32); v = np.asarray(v, f32)
+    return ((m[:, 0] * v[0] + m[:, 1] * v[1]) + (m[:, 2] * v[2] + m[:, 3] * v[3])).astype(f32)
+
+
+def mat4_inverse(a):
+    """glm::inverse(mat4) (detail/func_matrix.inl:388-446), all in fp32."""
+    a = np.asarray(a, f32)
+
+    def M(c, r):
+        return a[r, c]
+    c00 = M(2, 2) * M(3, 3) - M(3, 2) * M(2, 3); c02 = M(1, 2) * M(3, 3) - M(3, 2) * M(1, 3); c03 = M(1, 2) * M(2, 3) - M(2, 2) * M(1, 3)
+    c04 = M(2, 1) * M(3, 3) - M(3, 1) * M(2, 3); c06 = M(1, 1) * M(3, 3) - M(3, 1) * M(1, 3); c07 = M(1, 1) * M(2, 3) - M(2, 1) * M(1, 3)
+    c08 = M(2, 1) * M(3, 2) - M(3, 1) * M(2, 2); c10 = M(1, 1) * M(3, 2) - M(3, 1) * M(1, 2); c11 = M(1, 1) * M(2, 2) - M(2, 1) * M(1, 2)
+    c12 = M(2, 0) * M(3, 3) - M(3, 0) * M(2, 3); c14 = M(1, 0) * M(3, 3) - M(3, 0) * M(1, 3); c15 = M(1, 0) * M(2, 3) - M(2, 0) * M(1, 3)
+    c16 = M(2, 0) * M(3, 2) - M(3, 0) * M(2, 2); c18 = M(1, 0) * M(3, 2) - M(3, 0) * M(1, 2); c19 = M(1, 0) * M(2, 2) - M(2, 0) * M(1, 2)
+    c20 = M(2, 0) * M(3, 1) - M(3, 0) * M(2, 1); c22 = M(1, 0) * M(3, 1) - M(3, 0) * M(1, 1); c23 = M(1, 0) * M(2, 1) - M(2, 0) * M(1, 1)
+    f0 = np.array([c00, c00, c02, c03], f32); f1 = np.array([c04, c04, c06, c07], f32); f2 = np.array([c08, c08, c10, c11], f32)
+    f3 = np.array([c12, c12, c14, c15], f32); f4 = np.array([c16, c16, c18, c19], f32); f5 = np.array([c20, c20, c22, c23], f32)
+    v0 = np.array([M(1, 0), M(0, 0), M(0, 0), M(0, 0)], f32); v1 = np.array([M(1, 1), M(0, 1), M(0, 1), M(0, 1)], f32)
+    v2 = np.array([M(1, 2), M(0, 2), M(0, 2), M(0, 2)], f32); v3 = np.array([M(1, 3), M(0, 3), M(0, 3), M(0, 3)], f32)
+    sa = np.array([1, -1, 1, -1], f32); sb = np.array([-1, 1, -1, 1], f32)
+    inv = np.empty((4, 4), f32)                        # [row, col]
+    inv[:, 0] = ((v1 * f0 - v2 * f1) + v3 * f2) * sa
+    inv[:, 1] = ((v0 * f0 - v2 * f3) + v3 * f4) * sb
+    inv[:, 2] = ((v0 * f1 - v1 * f3) + v3 * f5) * sa
+    inv[:, 3] = ((v0 * f2 - v1 * f4) + v2 * f5) * sb
+    d = a[:, 0] * inv[0, :]                              # m[0] * (first row of the adjugate)
+    ood = f32(1) / f32(f32(d[0] + d[1]) + f32(d[2] + d[3]))
+    return (inv * ood).astype(f32)
+
+
 def look_at(eye, center, up):
     """glm::lookAtRH (ThirdParty/glm/glm/ext/matrix_transform.inl:153-174)."""
     eye, center, up = (np.asarray(a, f32) for a in (eye, center, up))
     f = _norm(center - eye)
-    s = _norm(np.cross(f, up).astype(f32))
-    u = np.cross(s, f).astype(f32)
+    s = _norm(_cross(f, up))
+    u = _cross(s, f)
     m = np.eye(4, dtype=f32)
     m[0, :3] = s; m[1, :3] = u; m[2, :3] = -f
-    m[0, 3] = -np.dot(s, eye); m[1, 3] = -np.dot(u, eye); m[2, 3] = np.dot(f, eye)
+    m[0, 3] = -_dot3(s, eye); m[1, 3] = -_dot3(u, eye); m[2, 3] = _dot3(f, eye)
     return m
 
 
 def perspective_clip(fov_deg, aspect, near, far):
-    """kClip * glm::perspectiveRH_ZO (Camera.h:110-117; matrix_clip_space.inl:233-246)."""
-    t = np.tan(np.radians(f32(fov_deg), dtype=f32) / f32(2), dtype=f32)
+    """kClip * glm::perspectiveRH_ZO(radians(fov), aspect, near, far) (Camera.h:110-117; matrix_clip_space.inl:233-246)."""
+    near, far, aspect = f32(near), f32(far), f32(aspect)
+    t = _tanf(f32(f32(fov_deg) * f32(0.01745329251994329576923690768489)) / f32(2))
     m = np.zeros((4, 4), f32)
-    m[0, 0] = f32(1) / (f32(aspect) * t)
+    m[0, 0] = f32(1) / f32(aspect * t)
     m[1, 1] = f32(1) / t
-    m[2, 2] = f32(far) / (f32(near) - f32(far))
+    m[2, 2] = far / f32(near - far)
     m[3, 2] = -1
-    m[2, 3] = -(f32(far) * f32(near)) / (f32(far) - f32(near))
-    return (K_CLIP @ m).astype(f32)
+    m[2, 3] = -f32(far * near) / f32(far - near)
+    return mat4_mul(K_CLIP, m)
 
 
 def ortho_clip(l, r, b, t, n, f):
@@ -75,63 +154,87 @@ def ortho_clip(l, r, b, t, n, f):
     m = np.eye(4, dtype=f32)
     m[0, 0] = f32(2) / (r - l); m[1, 1] = f32(2) / (t - b); m[2, 2] = -f32(1) / (f - n)
     m[0, 3] = -(r + l) / (r - l); m[1, 3] = -(t + b) / (t - b); m[2, 3] = -n / (f - n)
-    return (K_CLIP @ m).astype(f32)
+    return mat4_mul(K_CLIP, m)
 
 
 def camera_view(eye, look, up):
     """Camera::UpdateViewMatrix (Camera.h:93-108): re-orthogonalised up, then lookAt."""
     eye, look, up = (np.asarray(a, f32) for a in (eye, look, up))
     d = _norm(eye - look)
-    r = _norm(np.cross(up, d).astype(f32))
-    u = np.cross(d, r).astype(f32)
+    r = _norm(_cross(up, d))
+    u = _cross(d, r)
     return look_at(eye, look, u)
 
 
 def bbox_corners(mn, mx):
+    """BoundingBox::GetCorners (BoundingBox.h:33-45): x outermost, z innermost."""
     return np.array([[x, y, z] for x in (mn[0], mx[0]) for y in (mn[1], mx[1]) for z in (mn[2], mx[2])], f32)
 
 
+def _vmin(a, b):
+    return np.where(b < a, b, a).astype(f32)   # glm::min(x, y) = (y < x) ? y : x
+
+
+def _vmax(a, b):
+    return np.where(a < b, b, a).astype(f32)   # glm::max(x, y) = (x < y) ? y : x
+
+
+_FLT_MAX = np.finfo(f32).max
+
+
+def bbox_from_points(pts):
+    """BoundingBox::FromPoints (BoundingBox.cpp:18-29)."""
+    mn = np.full(3, _FLT_MAX, f32); mx = -mn
+    for p in np.asarray(pts, f32):
+        mn = _vmin(mn, p); mx = _vmax(mx, p)
+    return mn, mx
+
+
 def bbox_transform(mn, mx, m):
-    """BoundingBox::Transform (BoundingBox.h:47-60): 8 corners, divide by w, min/max."""
-    c = bbox_corners(mn, mx)
-    p = (np.c_[c, np.ones(8, f32)] @ m.T).astype(f32)
-    p = p[:, :3] / p[:, 3:4]
-    return p.min(0).astype(f32), p.max(0).astype(f32)
+    """BoundingBox::Transform / operator* (BoundingBox.h:47-60, BoundingBox.cpp:3-16): 8 corners, divide by w, min / max."""
+    omn = np.full(3, _FLT_MAX, f32); omx = -omn
+    for c in bbox_corners(np.asarray(mn, f32), np.asarray(mx, f32)):
+        p4 = mat4_vec4(m, np.array([c[0], c[1], c[2], 1], f32))
+        p = (p4[:3] / p4[3]).astype(f32)
+        omn = _vmin(omn, p); omx = _vmax(omx, p)
+    return omn, omx
 
 
 def frustum_corners(view, proj):
-    """Camera::ComputeFrustrumCorners (Camera.cpp:3-25)."""
-    t = (np.linalg.inv(view.astype(np.float64)) @ np.linalg.inv(proj.astype(np.float64))).astype(f32)
-    pts = np.array([[x, y, z, 1] for x in (-1, 1) for y in (-1, 1) for z in (-1, 1)], f32)
-    w = (pts @ t.T).astype(f32)
-    return (w[:, :3] / w[:, 3:4]).astype(f32)
+    """Camera::ComputeFrustrumCorners (Camera.cpp:3-25): inverse(view) * inverse(proj) applied to the NDC cube, divided by w."""
+    t = mat4_mul(mat4_inverse(view), mat4_inverse(proj))
+    out = []
+    for x in (-1, 1):
+        for y in (-1, 1):
+            for z in (-1, 1):
+                w = mat4_vec4(t, np.array([x, y, z, 1], f32))
+                out.append((w[:3] / w[3]).astype(f32))
+    return np.array(out, f32)
 
 
 def light_view_matrix(direction):
     """ComputeDirectionalLightViewMatrix (ShadowSystem.cpp:129-147) with up = cross(dir, right) (F8)."""
     d = np.asarray(direction, f32)
     right = np.array([0, 0, 1], f32)
-    if abs(float(np.dot(d, right))) > 0.9999:
+    if abs(_dot3(d, right)) > f32(0.9999):
         right = np.array([1, 0, 0], f32)
-    up = np.cross(d, right).astype(f32)
+    up = _cross(d, right)
     return look_at(np.zeros(3, f32), d, up)
 
 
 def compute_shadow_transform(light_dir, cam_view, cam_proj, scene_box, boxes, transforms):
-    """ComputeShadowTransform (ShadowSystem.cpp:148-204). Returns (view, proj) row/col numpy 4x4."""
-    cam_pts = frustum_corners(cam_view, cam_proj)
-    cam_min, cam_max = cam_pts.min(0), cam_pts.max(0)
+    """ComputeShadowTransform (ShadowSystem.cpp:148-204). Returns (view, proj) as [row, col] numpy 4x4; proj = kClip * ortho."""
+    cam_min, cam_max = bbox_from_points(frustum_corners(cam_view, cam_proj))
     sview = light_view_matrix(light_dir)
     cv_min, cv_max = bbox_transform(cam_min, cam_max, sview)
     sv_min, sv_max = bbox_transform(scene_box[0], scene_box[1], sview)
     cv_max[2] = sv_max[2]
-    sinv = np.linalg.inv(sview.astype(np.float64)).astype(f32)
-    cw_min, cw_max = bbox_transform(cv_min, cv_max, sinv)
-    lb_min = np.full(3, np.finfo(f32).max, f32); lb_max = -lb_min
+    cw_min, cw_max = bbox_transform(cv_min, cv_max, mat4_inverse(sview))
+    lb_min = np.full(3, _FLT_MAX, f32); lb_max = -lb_min
     for (bmn, bmx), t in zip(boxes, transforms):
         wmn, wmx = bbox_transform(bmn, bmx, from_flat(t))
-        if np.all(wmn <= cw_max) and np.all(wmx >= cw_min):
-            lb_min = np.minimum(lb_min, wmn); lb_max = np.maximum(lb_max, wmx)
+        if np.all(wmn <= cw_max) and np.all(wmx >= cw_min):                 # BoundingBox::Intersects (BoundingBox.h:25-31)
+            lb_min = _vmin(lb_min, wmn); lb_max = _vmax(lb_max, wmx)    # Union
     lv_min, lv_max = bbox_transform(lb_min, lb_max, sview)
     sproj = ortho_clip(lv_min[0], lv_max[0], lv_min[1], lv_max[1], lv_min[2], lv_max[2])
     return sview, sproj

@@ -51,6 +51,16 @@ def test_no_cpu_fallback_without_a_device():
     assert "no CUDA device" in str(e.value) or "failed" in str(e.value)
 
 
+def test_create_rejects_bad_extents_before_touching_a_device():
+    """Argument validation of reb_create needs no GPU: zero extents and extents above REB_MAX_EXTENT (K1 packs x | y << 16 and 16-bit
+    ring fields) are REB_E_INVALID with a message."""
+    from renderengine_b200 import capi
+    for w, h in ((0, 64), (64, 0), (16385, 64), (64, 70000)):
+        with pytest.raises(capi.RebError) as e:
+            capi.Context(w, h)
+        assert "(-1)" in str(e.value) and "extent" in str(e.value), str(e.value)
+
+
 def test_product_does_not_import_the_oracle():
     """oracle/ is test infrastructure: nothing under renderengine_b200/ may import, link or dlopen it."""
     bad = []

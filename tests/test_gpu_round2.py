@@ -1,0 +1,262 @@
+"""Round-2 device tests through the C ABI: regressions for the advisor's findings, Phong with every light type and more lights than
+ride in the kernel parameters, the full-size sort-first (C4) and view-batch (C5) configurations, run-twice determinism."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from test_gpu_parity import _psnr, _quads_scene, check_parity, render_gpu
+
+pytestmark = pytest.mark.gpu
+
+
+class _DevArray:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"data": (ptr, False), "shape": shape, "typestr": typestr, "version": 2}
+
+
+def _fill_shadow_map(ctx, host_map):
+    """What an NCCL all-gather / broadcast does on a rank: the map's storage (reb_get_output) filled externally, then marked valid."""
+    import torch
+    from renderengine_b200 import capi
+    S = ctx.shadow_size
+    ptr, _ = ctx.output_ptr(capi.REB_SHADOW_F32)
+    ctx.sync()
+    t = torch.as_tensor(_DevArray(ptr, (S, S), "<f4"), device="cuda:0")
+    t.copy_(torch.from_numpy(np.ascontiguousarray(host_map, np.float32)))
+    torch.cuda.synchronize()
+    ctx.shadow_mark_valid()
+
+
+def _frame(ctx, f32=True):
+    from renderengine_b200 import capi
+    out = dict(tri_id=ctx.readback(capi.REB_TRIID_U32), depth=ctx.readback(capi.REB_DEPTH_F32), color_srgb8=ctx.readback(capi.REB_COLOR_SRGB8))
+    if f32:
+        out["color_f32"] = ctx.readback(capi.REB_COLOR_F32)
+    return out
+
+
+# ---- advisor finding 1: reb_set_skybox must not touch the multisample planes -----------------------------------------------------------
+def test_skybox_installed_after_the_sample_count_keeps_the_sample_planes():
+    """Renderer::SetSampleCount(4) before RenderScene::Init (whose Skybox::UploadToGPU calls reb_set_skybox): the sample planes the
+    sample passes and the resolve use must survive the skybox upload (they were freed there and used afterwards)."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    sky = sc.make_skybox(32)
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.set_sample_count(4)                 # first the sample count ...
+    ctx.upload_scene(s)
+    ctx.set_skybox(sky)                     # ... then the skybox, twice (replacing an installed one)
+    ctx.set_skybox(sky)
+    s2 = dict(s); s2["skybox"] = sky
+    o = orc.Oracle(s2)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward_msaa4(ref_shadow)
+    for _ in range(2):
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"])
+        tri = ctx.readback(capi.REB_MS_TRIID_U32); dep = ctx.readback(capi.REB_MS_DEPTH_F32)
+        for k in range(4):
+            assert np.array_equal(tri[k], ref["tri_id"][k]) and np.array_equal(dep[k].view(np.uint32), ref["depth"][k].view(np.uint32))
+        assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
+    ctx.set_sample_count(1); ctx.set_sample_count(4)   # and the planes can still be re-sized / freed exactly once
+    ctx.render_forward(s["draws"]); ctx.sync()
+    ctx.close()
+
+
+# ---- advisor finding 2: culled draws inside a mixed 256-triangle block ------------------------------------------------------------------
+@pytest.mark.parametrize("world", [2, 4])
+def test_split_context_renders_a_sequence_of_views(world):
+    """One sort-first context, several camera views in a row (and a light that moves): a draw culled for this rank in view k shares
+    256-triangle blocks with visible draws, and its cache slots must read as rejected — not as the previous view's vertices."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("small", level=2)    # 320 triangles per sphere: every 256-triangle block spans two draws
+    band = parallel.contiguous_band(s["height"], world)
+    full = orc.Oracle(s)
+    views = [sc.view_for_azimuth(s, az) for az in (0.0, 1.3, 2.9, 4.4)] + [sc.view_from(s, (0.3, 1.2, 0.4), (6.0, 0.0, 5.0))]
+    ctxs = [capi.Context(s["width"], s["height"], rank=r, n_ranks=world, band_h=band) for r in range(world)]
+    for c in ctxs:
+        c.upload_scene(s)
+    rows = parallel.slab_rows(s["shadow_size"], world)
+    for k, v in enumerate(views):
+        full.set_view(v)
+        ref_shadow = full.render_shadow()
+        whole = full.render_forward(ref_shadow)
+        merged_id = np.full_like(whole["tri_id"], 0xFFFFFFFF); merged_z = np.ones_like(whole["depth"]); merged_c = np.zeros_like(whole["color_srgb8"])
+        for r, c in enumerate(ctxs):
+            c.set_view(v)
+            c.render_shadow(s["draws"]); c.render_forward(s["draws"])
+            own = ((np.arange(s["height"]) // band) % world == r)
+            g = _frame(c, f32=False)
+            merged_id[own] = g["tri_id"][own]; merged_z[own] = g["depth"][own]; merged_c[own] = g["color_srgb8"][own]
+            assert (g["tri_id"][~own] == 0xFFFFFFFF).all(), f"view {k}, rank {r}: pixels outside the rank's bands were written"
+            assert c.counters()[0] == 0
+        assert np.array_equal(merged_id, whole["tri_id"]), f"view {k}: {np.count_nonzero(merged_id != whole['tri_id'])} pixels differ"
+        assert np.array_equal(merged_z.view(np.uint32), whole["depth"].view(np.uint32))
+        assert np.abs(merged_c.astype(np.int32) - whole["color_srgb8"].astype(np.int32)).max() <= 1
+    # the same for the shadow pass split into row slabs, light direction changing between frames
+    for k, ld in enumerate([(-0.3, -1.0, -0.2), (0.6, -1.0, 0.1), (-0.1, -1.0, 0.7)]):
+        ldn = np.asarray(ld, np.float32); ldn = ldn / np.linalg.norm(ldn)
+        sv = sc.light_view_matrix(ldn)
+        s2 = dict(s); s2["shadow_view"] = sc.to_flat(sv)
+        ref = orc.Oracle(s2).render_shadow()
+        got = np.zeros_like(ref)
+        for r, c in enumerate(ctxs):
+            c.set_shadow_partition(r, world, rows)
+            c.shadow_set_transform(s2["shadow_view"], s2["shadow_proj"])
+            c.render_shadow(s["draws"]); c.sync()
+            got[r * rows:(r + 1) * rows] = c.readback(capi.REB_SHADOW_F32)[r * rows:(r + 1) * rows]
+        assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), f"light {k}"
+
+
+# ---- advisor finding 3: overflow replay of a frame with a translucent list, no f32 output enabled ---------------------------------------
+def test_translucent_frame_replayed_after_queue_overflow_without_f32_output():
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = _quads_scene(150)
+    s = sc.to_translucent(s, which=[1], alpha=0.4)
+    ref_shadow = orc.Oracle(dict(_quads_scene(150))).render_shadow()
+    ref = orc.Oracle(s).render_forward(ref_shadow)
+    ctx = capi.Context(s["width"], s["height"], outputs=capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_TRIID_U32)   # the bench's outputs: no f32 colour, no depth
+    ctx.upload_scene(s)
+    for frame in range(2):
+        ctx.render_shadow(np.concatenate([s["draws"], s["translucent_draws"]]))
+        ctx.render_forward(s["draws"], s["translucent_draws"])
+        ctx.sync()
+        if frame == 0:
+            assert ctx.counters()[3] > 0            # the tile-list queue was regrown and the frame replayed
+        assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"]), frame
+        d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32))
+        assert d8.max() <= 1, f"frame {frame}: {np.count_nonzero(d8 > 1)} channel samples beyond 1 LSB (max {d8.max()})"
+
+
+# ---- a10: PhongLighting for every light type, and more lights than the kernel parameters carry (phong.glsl:39-81) ---------------------------
+def _phong_lights(s, n_extra=0):
+    from renderengine_b200 import scene as sc
+    ex, ez = s["extent"]
+    ldir = sc._norm([-0.3, -1.0, -0.2])
+    f = np.float32
+    lights = [sc.pack_light(sc.LIGHT_DIRECTIONAL, (-ldir * f(50)).astype(f), ldir, [0.05] * 4, [0.7] * 4, [0.8] * 4),
+              sc.pack_light(sc.LIGHT_POINT, [f(-0.4 * ex), f(2.5), f(0.3 * ez)], [0, -1, 0], [0.02, 0.02, 0.05, 0], [0.6, 1.2, 2.0, 0], [0.5, 1.0, 2.0, 0]),
+              sc.pack_light(sc.LIGHT_SPOT, [f(0.5 * ex), f(3.0), f(-0.2 * ez)], sc._norm([-0.2, -1.0, 0.1]), [0.0] * 4, [3.0, 1.2, 0.8, 0], [2.0, 1.0, 0.5, 0],
+                            inner=0.92, outer=0.75)]
+    rng = np.random.default_rng(5)
+    for k in range(n_extra):
+        kind = sc.LIGHT_POINT if k % 2 == 0 else sc.LIGHT_SPOT
+        pos = np.array([rng.uniform(-ex, ex), rng.uniform(1.5, 4.0), rng.uniform(-ez, ez)], f)
+        lights.append(sc.pack_light(kind, pos, sc._norm([rng.uniform(-0.4, 0.4), -1.0, rng.uniform(-0.4, 0.4)]), [0.01] * 4,
+                                    np.r_[rng.uniform(0.3, 1.5, 3), 0].astype(f), np.r_[rng.uniform(0.3, 1.5, 3), 0].astype(f), inner=0.95, outer=0.6))
+    return np.stack(lights)
+
+
+@pytest.mark.parametrize("n_extra,config", [(0, "small"), (4, "small"), (9, "small_tex"), (3, "C1")])
+def test_parity_phong_directional_point_spot_and_many_lights(n_extra, config):
+    """3 lights = all of phong.glsl's branches (1 / distance attenuation, spot smooth-step, shadowed directional); 7 / 12 / 6 lights
+    also take the global-memory light path past SHADE_CONST_LIGHTS = 4."""
+    from oracle import orc
+    from renderengine_b200 import scene as sc
+    s = sc.make_scene(config) if config != "C1" else sc.make_scene(config, shadow_size=1024)
+    s["lights"] = _phong_lights(s, n_extra)
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ref = o.render_forward(ref_shadow)
+    gpu = render_gpu(s)
+    check_parity(s, gpu, ref_shadow, ref)
+    one = dict(s); one["lights"] = s["lights"][:1]
+    base = orc.Oracle(one).render_forward(ref_shadow)
+    drawn = ref["tri_id"] != 0xFFFFFFFF
+    assert (ref["color_f32"][drawn][:, :3] > base["color_f32"][drawn][:, :3] + 0.02).any(axis=1).mean() > 0.3   # the extra lights really light the frame
+
+
+# ---- full-size C4 (sort-first, 7680 x 4320, 10.5 M triangles, 4096 textures) and C5 (the 2 M-triangle view-batch scene) -----------------------
+def test_parity_full_size_c4_one_rank_of_eight():
+    """BASELINE.json config 4 at full size: rank 3 of 8 (two interleaved bands per rank, per-draw + per-block culling, shadow row slab):
+    its bands of the 8K frame and its slab of the shadow map against the oracle, bit for bit."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("C4")
+    world, rank = 8, 3
+    band = parallel.contiguous_band(s["height"], world * 2)
+    full = orc.Oracle(s)
+    ref_shadow = full.render_shadow()
+    ref = orc.Oracle(s, rank=rank, n_ranks=world, band_h=band).render_forward(ref_shadow)
+    outputs = capi.REB_OUT_COLOR_SRGB8 | capi.REB_OUT_DEPTH_F32 | capi.REB_OUT_TRIID_U32       # an 8K f32 colour target would be 531 MB more; sRGB8 carries the colour check
+    ctx = capi.Context(s["width"], s["height"], rank=rank, n_ranks=world, band_h=band, outputs=outputs)
+    ctx.upload_scene(s)
+    rows = parallel.slab_rows(s["shadow_size"], world)
+    ctx.set_shadow_partition(rank, world, rows)
+    ctx.render_shadow(s["draws"]); ctx.sync()
+    slab = ctx.readback(capi.REB_SHADOW_F32)[rank * rows:(rank + 1) * rows]
+    assert np.array_equal(slab.view(np.uint32), ref_shadow[rank * rows:(rank + 1) * rows].view(np.uint32))
+    # complete the map the way the all-gather would, then the rank's share of the forward pass
+    _fill_shadow_map(ctx, ref_shadow)
+    ctx.render_forward(s["draws"]); ctx.sync()
+    assert ctx.counters()[0] == 0
+    own = ((np.arange(s["height"]) // band) % world == rank)
+    tri = ctx.readback(capi.REB_TRIID_U32)
+    assert np.array_equal(tri[own], ref["tri_id"][own]), f"{np.count_nonzero(tri[own] != ref['tri_id'][own])} pixels differ"
+    assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32)[own].view(np.uint32), ref["depth"][own].view(np.uint32))
+    d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8)[own].astype(np.int32) - ref["color_srgb8"][own].astype(np.int32))
+    assert d8.max() <= 1
+    assert (tri[~own] == 0xFFFFFFFF).all() and (ref["tri_id"][own] != 0xFFFFFFFF).mean() > 0.2
+
+
+def test_parity_full_size_c5_views_share_one_shadow_map():
+    """BASELINE.json config 5's scene (2,007,042 triangles, 1080p): the shadow map rendered ONCE (RenderScene.cpp:171-175), then several
+    of the batch's camera views against it — every view bit-exact against the oracle."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("C5")
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.render_shadow(s["draws"])
+    for view_index in (0, 137, 401):
+        v = sc.view_for_azimuth(s, 2 * np.pi * view_index / 512)
+        o.set_view(v); ctx.set_view(v)
+        ref = o.render_forward(ref_shadow)
+        ctx.render_forward(s["draws"])
+        gpu = _frame(ctx)
+        if view_index == 0:
+            gpu["shadow"] = ctx.readback(capi.REB_SHADOW_F32)
+        check_parity(s, gpu, ref_shadow if view_index == 0 else None, ref)
+        assert ctx.counters()[0] == 0
+
+
+# ---- determinism — the same frame twice, every output hashed ----------------------------------------------------------------------
+@pytest.mark.parametrize("variant", ["phong", "binned", "msaa4", "translucent", "clipped_pbr_sky"])
+def test_render_twice_is_bit_identical(variant):
+    """Atomics decide every pixel (64-bit min keys, list-head exchanges), queues fill in a different order every run: the OUTPUT must
+    not depend on it.  Two contexts and two frames on one context, all outputs hashed."""
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    tl = None
+    if variant == "binned":
+        s = _quads_scene(150)
+    if variant == "translucent":
+        s = sc.to_translucent(s, every=2)
+        tl = s["translucent_draws"]
+    if variant == "clipped_pbr_sky":
+        s = sc.to_pbr(s, n_texture_sets=2)
+        s["skybox"] = sc.make_skybox(32)
+        s["view"] = sc.view_from(s, (0.3, 0.2, 0.4), (3.0, -0.2, 2.0))
+    shadow_draws = s["draws"] if tl is None else np.concatenate([s["draws"], tl])
+    digests = []
+    for c in range(2):
+        ctx = capi.Context(s["width"], s["height"])
+        ctx.upload_scene(s)
+        if variant == "msaa4":
+            ctx.set_sample_count(4)
+        for frame in range(2):
+            ctx.render_shadow(shadow_draws); ctx.render_forward(s["draws"], tl)
+            ctx.sync()
+            h = hashlib.sha256()
+            kinds = [capi.REB_SHADOW_F32, capi.REB_DEPTH_F32, capi.REB_TRIID_U32, capi.REB_COLOR_F32, capi.REB_COLOR_SRGB8]
+            if variant == "msaa4":
+                kinds += [capi.REB_MS_DEPTH_F32, capi.REB_MS_TRIID_U32]
+            for kind in kinds:
+                h.update(np.ascontiguousarray(ctx.readback(kind)).tobytes())
+            digests.append(h.hexdigest())
+    assert len(set(digests)) == 1, digests
