@@ -45,6 +45,7 @@ int reb_create(const reb_params* params, reb_ctx** out) {
         return bail(fail(ctx, REB_E_CUDA, "status buffers allocation failed"));
     std::memset(ctx->hStatus, 0, 64);
     ctx->listCap = 4u << 20;
+    if (const char* e = std::getenv("REB_TILE_LIST_CAP")) ctx->listCap = std::max(1024u, (uint32_t)std::strtoul(e, nullptr, 10));   // tests: force the regrow + replay path
     if (cudaMalloc(reinterpret_cast<void**>(&ctx->tileList), (size_t)ctx->listCap * 4) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "tile list allocation failed"));
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "stream sync failed in reb_create"));
     *out = ctx;

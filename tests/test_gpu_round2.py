@@ -111,9 +111,10 @@ def test_split_context_renders_a_sequence_of_views(world):
 
 
 # ---- advisor finding 3: overflow replay of a frame with a translucent list, no f32 output enabled ---------------------------------------
-def test_translucent_frame_replayed_after_queue_overflow_without_f32_output():
+def test_translucent_frame_replayed_after_queue_overflow_without_f32_output(monkeypatch):
     from oracle import orc
     from renderengine_b200 import capi, scene as sc
+    monkeypatch.setenv("REB_TILE_LIST_CAP", "2048")   # the first frame overflows the tile-list queue: regrow + replay
     s = _quads_scene(150)
     s = sc.to_translucent(s, which=[1], alpha=0.4)
     ref_shadow = orc.Oracle(dict(_quads_scene(150))).render_shadow()
@@ -199,7 +200,7 @@ def test_parity_full_size_c4_one_rank_of_eight():
     assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32)[own].view(np.uint32), ref["depth"][own].view(np.uint32))
     d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8)[own].astype(np.int32) - ref["color_srgb8"][own].astype(np.int32))
     assert d8.max() <= 1
-    assert (tri[~own] == 0xFFFFFFFF).all() and (ref["tri_id"][own] != 0xFFFFFFFF).mean() > 0.2
+    assert (tri[~own] == 0xFFFFFFFF).all() and (ref["tri_id"][own] != 0xFFFFFFFF).mean() > 0.1
 
 
 def test_parity_full_size_c5_views_share_one_shadow_map():
