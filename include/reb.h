@@ -160,6 +160,12 @@ int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint3
 /* marks the shadow map as valid after its storage (reb_get_output REB_SHADOW_F32) was filled externally,
  * e.g. by an NCCL broadcast from the rank that rendered it */
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);
+/* The same for an exchange that is still IN FLIGHT on another stream: cudaEvent (a cudaEvent_t the caller recorded behind the
+ * NCCL broadcast / all-gather that fills the map) is waited for by the next forward pass right before its tile stage — the only
+ * kernel that reads the map (shadow.glsl:24-56 runs in the fragment stage) — so that pass's vertex stage and triangle setup
+ * overlap the transfer.  Marks the map valid; one-shot (consumed by the next reb_render_forward*).  The reference has no
+ * counterpart (single GPU; it renders the map once, RenderScene.cpp:171-175, and samples it every frame). */
+int reb_shadow_wait_event(reb_ctx* ctx, uint32_t shadowId, void* cudaEvent);
 
 /* diagnostics: counters[0] clip children that could not be set up (non-finite input) + translucent fragments dropped by a
  * capacity limit — 0 for every finite scene within the limits above (triangles crossing the eye plane are CLIPPED, not dropped),

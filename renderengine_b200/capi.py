@@ -16,7 +16,7 @@ SYMBOLS = [
     "reb_abi_version", "reb_create", "reb_destroy", "reb_last_error", "reb_upload_geometry", "reb_upload_transforms",
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
     "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition", "reb_render_forward2",
-    "reb_set_partition", "reb_shadow_mark_valid", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
+    "reb_set_partition", "reb_shadow_mark_valid", "reb_shadow_wait_event", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
     "reb_get_kernel_times",
 ]
 
@@ -74,6 +74,7 @@ def load():
     lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
+    lib.reb_shadow_wait_event.argtypes = [vp, u32, vp]
     lib.reb_get_counters.argtypes = [vp, vp]
     lib.reb_get_launch_count.argtypes = [vp, C.POINTER(u64)]
     lib.reb_set_profiling.argtypes = [vp, C.c_int]
@@ -252,6 +253,11 @@ class Context:
 
     def shadow_mark_valid(self):
         self._ck(self.lib.reb_shadow_mark_valid(self.h, self.shadow_id))
+
+    def shadow_wait_event(self, cuda_event):
+        """The map is being filled on another stream (NCCL broadcast / all-gather): the next forward pass waits for `cuda_event`
+        (a raw cudaEvent_t, e.g. torch.cuda.Event.cuda_event) right before its tile stage, so its K0 / K1 overlap the transfer."""
+        self._ck(self.lib.reb_shadow_wait_event(self.h, self.shadow_id, C.c_void_p(int(cuda_event))))
 
     def counters(self):
         c = np.zeros(4, np.uint64)

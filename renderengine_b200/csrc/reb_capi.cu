@@ -79,6 +79,7 @@ struct reb_ctx {
     LargeRec* huge = nullptr;        // 2 x HUGE_CAP
     uint32_t* tileCount[2] = {nullptr, nullptr}; uint32_t tileCap[2] = {0, 0};   // per pass: both may be in flight behind one fused K0
     uint32_t* tileStart = nullptr; uint32_t tileStartCap = 0;
+    cudaEvent_t shadowReadyEvent = nullptr;   // reb_shadow_wait_event: waited for right before the next forward tile stage (one-shot)
     bool shadowDeferred = false; float recordedSPV[16];   // reb_render_shadow recorded, not yet submitted
     uint32_t* tileList = nullptr; uint32_t listCap = 0;
     uint32_t* dStatus = nullptr;     // 3 x 8 words
@@ -477,6 +478,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
             launch_tile_forward(pk, sk, ctx->numSMs, ctx->stream); ctx->launches++;
         }
         mark(3); mark(4);
+        if (ctx->shadowReadyEvent) { CU(cudaStreamWaitEvent(ctx->stream, ctx->shadowReadyEvent, 0)); ctx->shadowReadyEvent = nullptr; }
         launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
     } else {
         if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
@@ -485,7 +487,11 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
         mark(4);
         if (kind == 0) { launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
-        else { launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++; }
+        else {
+            // the shadow map is being filled by an exchange on another stream (reb_shadow_wait_event): only this kernel reads it
+            if (ctx->shadowReadyEvent) { CU(cudaStreamWaitEvent(ctx->stream, ctx->shadowReadyEvent, 0)); ctx->shadowReadyEvent = nullptr; }
+            launch_tile_forward(pc, sh, ctx->numSMs, ctx->stream); ctx->launches++;
+        }
     }
     mark(5);
     CU(cudaGetLastError());

@@ -450,6 +450,15 @@ int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId) {
     return REB_OK;
 }
 
+int reb_shadow_wait_event(reb_ctx* ctx, uint32_t shadowId, void* cudaEvent) {
+    CHECK_CTX();
+    if (shadowId != 0 || !ctx->shadowMap || !cudaEvent) return fail(ctx, REB_E_INVALID, "reb_shadow_wait_event: unknown shadow id or null event");
+    if (ctx->shadowDeferred) { cudaSetDevice(ctx->device); int frc = flush_deferred(ctx); if (frc) return frc; }
+    ctx->shadowReadyEvent = reinterpret_cast<cudaEvent_t>(cudaEvent);
+    ctx->shadowValid = true;
+    return REB_OK;
+}
+
 int reb_get_counters(reb_ctx* ctx, uint64_t* c) {
     CHECK_CTX();
     if (!c) return REB_E_INVALID;
