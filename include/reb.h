@@ -169,7 +169,7 @@ int reb_shadow_wait_event(reb_ctx* ctx, uint32_t shadowId, void* cudaEvent);
 
 /* diagnostics: counters[0] clip children that could not be set up (non-finite input) + translucent fragments dropped by a
  * capacity limit — 0 for every finite scene within the limits above (triangles crossing the eye plane are CLIPPED, not dropped),
- * [1] triangles sent to the binned tile path in the last pass, [2] tile-list entries, [3] queue regrow count */
+ * [1] triangles sent to the binned tile path by the passes of the last frame, [2] their tile-list entries, [3] queue regrow count */
 int reb_get_counters(reb_ctx* ctx, uint64_t* counters4);
 /* number of kernels this library has launched on the context since creation */
 int reb_get_launch_count(reb_ctx* ctx, uint64_t* out);

@@ -577,8 +577,9 @@ int check_and_recover(reb_ctx* ctx) {
             if (!ctx->pass[k].pending) continue;
             const uint32_t* st = ctx->hStatus + 8 * k;
             ctx->counters[0] = (first ? 0 : ctx->counters[0]) + st[1];
+            ctx->counters[1] = (first ? 0 : ctx->counters[1]) + st[0];    // binned triangles / tile-list entries: summed over the passes of the frame
+            ctx->counters[2] = (first ? 0 : ctx->counters[2]) + st[3];
             first = false;
-            ctx->counters[1] = st[0]; ctx->counters[2] = st[3];
             if (st[2] & OVF_LARGE) { overflow = true; ctx->largeWorstCase = true; }   // clip children outgrew the slack: size for the worst case
             if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
         }
