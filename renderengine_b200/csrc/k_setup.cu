@@ -1,63 +1,16 @@
-// k_setup.cu — K1: triangle setup + small-triangle raster + large-triangle tile counting;
-// K2: scatter of the large triangles into per-tile lists; clears; AoS -> SoA split.
+// k_setup.cu — K1: triangle setup + small-triangle raster + large-triangle queue / per-tile counts; clears; AoS -> SoA split.
+// (Clipping of queued parents, list layout and the record scatter run at the head of the tile stage: reb_bin.cuh.)
 //
 // Replaces, for the hot path, the fixed-function front end that the reference reaches through
 // vkCmdDrawIndexed (MaterialSystem.cpp:99, ShadowSystem.cpp:369) with the state of
 // GraphicsPipelineCache.cpp:257-365: viewport, cull back + CCW front (F5), 1 sample per pixel,
 // LessOrEqual depth.  The vertex stage itself is k_vertex.cu.
-#include "reb_device.cuh"
+#include "reb_bin.cuh"
 #include "reb_kernels.h"
 #include <algorithm>
 #include <cstdlib>
 
 namespace reb {
-
-// ---------------------------------------------------------------------------------------------
-// Tile walk of one large triangle by one warp: lanes stride over the TILE_W x TILE_H tiles of its
-// bbox; a tile is skipped when it lies entirely outside one edge (edge function evaluated at the
-// tile's most-interior pixel centre for that edge).  SCATTER = false counts (inside K1),
-// SCATTER = true writes the triangle's queue slot into the per-tile lists (K2).
-// All arguments are warp-uniform.
-// ---------------------------------------------------------------------------------------------
-template <bool SCATTER>
-__device__ __noinline__ void tile_walk(const PassConst& pc, int32_t X0, int32_t Y0, int32_t X1, int32_t Y1, int32_t X2, int32_t Y2,
-                                          uint32_t queueSlot, unsigned lane) {
-    const int32_t X[3] = {X0, X1, X2}, Y[3] = {Y0, Y1, Y2};
-    const int32_t minX = min(X0, min(X1, X2)), maxX = max(X0, max(X1, X2));
-    const int32_t minY = min(Y0, min(Y1, Y2)), maxY = max(Y0, max(Y1, Y2));
-    const int x0 = max((minX + 127) >> 8, 0), x1 = min((maxX - 128) >> 8, (int)pc.W - 1);
-    const int y0 = max((minY + 127) >> 8, 0), y1 = min((maxY - 128) >> 8, (int)pc.H - 1);
-    const int tx0 = x0 / TILE_W, tx1 = x1 / TILE_W, ty0 = y0 / TILE_H, ty1 = y1 / TILE_H;
-    const int tw = tx1 - tx0 + 1, n = tw * (ty1 - ty0 + 1);
-    long long A[3], B[3], C[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int a = (k + 1) % 3, b = (k + 2) % 3;
-        A[k] = (long long)Y[b] - Y[a];
-        B[k] = -((long long)X[b] - X[a]);
-        C[k] = -(A[k] * X[a]) - B[k] * Y[a];
-    }
-    for (int i = (int)lane; i < n; i += 32) {
-        const int tx = tx0 + i % tw, ty = ty0 + i / tw;
-        if (pc.nRanks > 1 && !row_owned((uint32_t)(ty * TILE_H), pc.rank, pc.nRanks, pc.bandH)) continue;
-        const long long cx0 = 256ll * (tx * TILE_W) + 128, cx1 = 256ll * (tx * TILE_W + TILE_W - 1) + 128;
-        const long long cy0 = 256ll * (ty * TILE_H) + 128, cy1 = 256ll * (ty * TILE_H + TILE_H - 1) + 128;
-        bool outside = false;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const long long Fmax = A[k] * (A[k] > 0 ? cx1 : cx0) + B[k] * (B[k] > 0 ? cy1 : cy0) + C[k];
-            outside = outside || (Fmax < 0);
-        }
-        if (outside) continue;
-        const uint32_t tile = (uint32_t)ty * pc.tilesX + (uint32_t)tx;
-        if (!SCATTER) {
-            atomicAdd(&pc.tileCount[tile], 1u);
-        } else {
-            const uint32_t slot = pc.tileStart[tile] + atomicAdd(&pc.tileCount[tile], 1u);
-            if (slot < pc.listCap) pc.tileList[slot] = queueSlot;
-        }
-    }
-}
 
 // ---------------------------------------------------------------------------------------------
 // K1: triangle setup + small-triangle raster, WARP-AUTONOMOUS: every warp is an independent persistent
@@ -82,8 +35,6 @@ __device__ __noinline__ void tile_walk(const PassConst& pc, int32_t X0, int32_t 
 //   3. one lane per covered sample: depth (two IEEE divides, Appendix B.8) and one atomicMin — 64-bit key
 //      depthBits<<32 | ~triId into the visibility buffer (forward) or the 32-bit depth bits into the
 //      shadow map itself (shadow).  Consecutive lanes hold consecutive samples of a row.
-// Tail (once per CTA): the last CTA to finish lays out the per-tile lists (start = running cursor; no
-// ordered scan is needed because list order inside a tile is irrelevant to the min-key resolve).
 // ---------------------------------------------------------------------------------------------
 constexpr int K1_THREADS = 128;                  // 4 autonomous warps per CTA (24.6 KB of queues)
 constexpr int K1_WARPS = K1_THREADS / 32;
@@ -104,13 +55,6 @@ struct K1Warp {
 };
 struct K1Shared {
     K1Warp w[K1_WARPS];
-};
-
-struct K1Tri {
-    VtxA a[3];
-    long long A2;
-    int32_t x0, x1, y0, y1;
-    bool isSmall, isLarge, needsClip;
 };
 
 template <bool SHIFT>
@@ -137,14 +81,6 @@ __device__ __forceinline__ void k1_classify(const PassConst& pc, bool valid, con
     t.isLarge = !t.isSmall;
 }
 
-__device__ __forceinline__ LargeRec k1_large_rec(const K1Tri& t, uint32_t tri) {
-    LargeRec r;
-    r.X0 = t.a[0].X; r.Y0 = t.a[0].Y; r.X1 = t.a[1].X; r.Y1 = t.a[1].Y;
-    r.X2 = t.a[2].X; r.Y2 = t.a[2].Y; r.z0 = t.a[0].z; r.z1 = t.a[1].z;
-    r.z2 = t.a[2].z; r.triId = tri; r.pad0 = 0; r.pad1 = 0;
-    return r;
-}
-
 // huge -> broadcast list; large -> queue + per-tile counts.  Called by all 32 lanes of the warp.
 __device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uint32_t tri, unsigned lane) {
     if (t.isLarge) {
@@ -165,76 +101,18 @@ __device__ __forceinline__ void k1_emit_large(const PassConst& pc, K1Tri& t, uin
         if (slot < pc.largeCap) pc.large[slot] = k1_large_rec(t, tri);
         else atomicOr(&pc.status[2], OVF_LARGE);
     }
+    const LargeRec mine = k1_large_rec(t, tri);
     while (lmask) {   // warp-cooperative tile counting, one large triangle at a time
         const int src = __ffs(lmask) - 1;
         lmask &= lmask - 1;
-        const int32_t X0 = __shfl_sync(0xFFFFFFFFu, t.a[0].X, src), Y0 = __shfl_sync(0xFFFFFFFFu, t.a[0].Y, src);
-        const int32_t X1 = __shfl_sync(0xFFFFFFFFu, t.a[1].X, src), Y1 = __shfl_sync(0xFFFFFFFFu, t.a[1].Y, src);
-        const int32_t X2 = __shfl_sync(0xFFFFFFFFu, t.a[2].X, src), Y2 = __shfl_sync(0xFFFFFFFFu, t.a[2].Y, src);
+        LargeRec r;
+        r.X0 = __shfl_sync(0xFFFFFFFFu, mine.X0, src); r.Y0 = __shfl_sync(0xFFFFFFFFu, mine.Y0, src);
+        r.X1 = __shfl_sync(0xFFFFFFFFu, mine.X1, src); r.Y1 = __shfl_sync(0xFFFFFFFFu, mine.Y1, src);
+        r.X2 = __shfl_sync(0xFFFFFFFFu, mine.X2, src); r.Y2 = __shfl_sync(0xFFFFFFFFu, mine.Y2, src);
+        r.z0 = r.z1 = r.z2 = 0.0f; r.triId = 0u; r.pad0 = r.pad1 = 0u;   // the count needs the footprint only
         const uint32_t s = __shfl_sync(0xFFFFFFFFu, slot, src);
-        if (s < pc.largeCap) tile_walk<false>(pc, X0, Y0, X1, Y1, X2, Y2, s, lane);
+        if (s < pc.largeCap) tile_walk<false>(pc, r, lane);
     }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Appendix B.3 (revision r1c), the rare path: a triangle with a vertex at / behind the eye plane or outside the guard band.
-// All 32 lanes run this with the SAME triangle (warp-uniform, no divergence): re-run the vertex stage on its three source
-// vertices (the cache holds no clip coordinates), clip in clip space with Sutherland-Hodgman (near z >= 0, then the four
-// guard planes; intersections computed from the inside vertex: t = d_in / (d_in - d_out)), fan the polygon from its
-// first vertex, and send every child through the ordinary viewport / snap / facing / bbox steps into the large-triangle
-// path with the parent's triId.  Returns true when a child was queued into the binned path.
-// ---------------------------------------------------------------------------------------------
-template <bool SHADOW>
-__device__ __noinline__ bool k1_clip_emit(const PassConst& pc, uint32_t tri, unsigned lane) {
-    float4 a[9];
-    const int n = clip_parent<SHADOW>(pc, tri, a);
-    if (n < 3) return false;
-    bool queued = false;
-    VtxA v0 = viewport_snap(a[0], pc.W, pc.H);
-    v0.X += pc.shiftX; v0.Y += pc.shiftY;   // B.15 sample shift
-    for (int i = 1; i + 1 < n; ++i) {
-        K1Tri t;
-        t.a[0] = v0; t.a[1] = viewport_snap(a[i], pc.W, pc.H); t.a[2] = viewport_snap(a[i + 1], pc.W, pc.H);
-        t.a[1].X += pc.shiftX; t.a[1].Y += pc.shiftY; t.a[2].X += pc.shiftX; t.a[2].Y += pc.shiftY;
-        if (((t.a[0].flags | t.a[1].flags | t.a[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
-            if (lane == 0) atomicAdd(&pc.status[1], 1u);
-            continue;
-        }
-        t.A2 = (long long)(t.a[1].X - t.a[0].X) * (long long)(t.a[2].Y - t.a[0].Y) - (long long)(t.a[2].X - t.a[0].X) * (long long)(t.a[1].Y - t.a[0].Y);
-        if (t.A2 >= 0) continue;                                                        // Appendix B.6 applies to the child
-        const int32_t minX = min(t.a[0].X, min(t.a[1].X, t.a[2].X)), maxX = max(t.a[0].X, max(t.a[1].X, t.a[2].X));
-        const int32_t minY = min(t.a[0].Y, min(t.a[1].Y, t.a[2].Y)), maxY = max(t.a[0].Y, max(t.a[1].Y, t.a[2].Y));
-        t.x0 = max((minX + 127) >> 8, 0); t.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
-        t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
-        if (t.x0 > t.x1 || t.y0 > t.y1) continue;
-        const LargeRec rec = k1_large_rec(t, tri);
-        const int ntiles = (t.x1 / TILE_W - t.x0 / TILE_W + 1) * (t.y1 / TILE_H - t.y0 / TILE_H + 1);
-        uint32_t slot = 0xFFFFFFFFu;   // 0xFFFFFFFF = went to the broadcast list
-        if (lane == 0) {
-            bool binned = true;
-            if (ntiles > HUGE_TILES) {
-                const uint32_t h = atomicAdd(&pc.status[4], 1u);
-                if (h < (uint32_t)HUGE_CAP) { pc.huge[h] = rec; binned = false; }
-            }
-            if (binned) {
-                slot = atomicAdd(&pc.status[0], 1u);
-                if (slot < pc.largeCap) pc.large[slot] = rec;
-                else { atomicOr(&pc.status[2], OVF_LARGE); slot = 0xFFFFFFFEu; }
-            }
-        }
-        slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
-        if (slot < pc.largeCap) {
-            queued = true;
-            tile_walk<false>(pc, rec.X0, rec.Y0, rec.X1, rec.Y1, rec.X2, rec.Y2, slot, lane);
-        }
-    }
-    return queued;
-}
-
-__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, v, o); if (lane >= (unsigned)o) v += n; }
-    return v;
 }
 
 constexpr uint32_t K1_SPLIT = SMALL_MAX + 1;   // widest (half) row of the row stage; row entries appended per lane and round
@@ -282,40 +160,78 @@ __device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uin
     q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
 }
 
-// Row stage: `cnt` (<= 32) pending rows, one per lane -> coverage masks -> pixel queue entries.
+// A "tiny" triangle — pixel-centre bbox of at most 4 x 4 and at most 15 centres (so a lane never emits more than the 15 samples a
+// row entry can, and the ring bound 31 + 32 * 15 holds) — is ONE row-queue entry covering its whole bbox: the coverage mask is
+// 2-D, bit i + 4 * j.  A frame of 1-3 px triangles (C2, C3) then costs one entry, one slot of the row stage and no scan in the
+// append per triangle instead of one per bbox row.
+__device__ __forceinline__ bool k1_is_tiny(uint32_t w, uint32_t h) { return w <= 4u && h <= 4u && w * h <= 15u; }
+
+// Row stage: `cnt` (<= 32) pending entries, one per lane -> coverage masks -> pixel queue entries.
 template <bool SHADOW, bool CULL = false>
 __device__ __forceinline__ void k1_rows(const PassConst& pc, K1Warp& ws, uint32_t rowHead, uint32_t cnt, uint32_t& pixTail, unsigned lane) {
     bool active = lane < cnt;
     uint32_t slot = 0, j = 0, whb = 0, xo = 0;
+    bool tiny = false;
     if (active) {
         const uint32_t e = ws.rowq[(rowHead + lane) & (K1_ROWQ - 1)];
         slot = e & 0x3Fu;
         whb = ws.whb[slot];
+        tiny = k1_is_tiny(whb & 0xFFu, (whb >> 8) & 0xFFu);
         const uint32_t wide = (whb & 0xFFu) > K1_SPLIT ? 1u : 0u;   // two half rows per row
-        j = (e >> 6) >> wide; xo = ((e >> 6) & wide) * K1_SPLIT;
-        if ((!SHADOW || CULL) && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;   // shadow slabs only in the split build
+        j = (e >> 6) >> wide; xo = ((e >> 6) & wide) * K1_SPLIT;      // tiny: entry 0 -> j = 0, xo = 0
+        // (sort-first / shadow slabs: a tiny entry spans up to 4 rows, which may straddle a band border: its rows are filtered below)
+        if (!tiny && (!SHADOW || CULL) && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
     }
     const uint32_t w = active ? min((whb & 0xFFu) - xo, K1_SPLIT) : 0u;
+    const uint32_t h = active ? (tiny ? ((whb >> 8) & 0xFFu) : 1u) : 0u;
     const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
+    const uint32_t hmax = __reduce_max_sync(0xFFFFFFFFu, h);
     uint32_t mask = 0;
     {
         const int32_t s0 = ws.Ax[0][slot], s1 = ws.Ax[1][slot], s2 = ws.Ax[2][slot];
         int32_t F0 = ws.C[0][slot] + (int32_t)j * ws.By[0][slot] + (int32_t)xo * s0 - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
         int32_t F1 = ws.C[1][slot] + (int32_t)j * ws.By[1][slot] + (int32_t)xo * s1 - (int32_t)((whb >> 17) & 1u);
         int32_t F2 = ws.C[2][slot] + (int32_t)j * ws.By[2][slot] + (int32_t)xo * s2 - (int32_t)((whb >> 18) & 1u);
+        if (hmax <= 1u) {   // warp-uniform: row entries only (or 1-row tiny ones)
 #pragma unroll 1
-        for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
+            for (uint32_t i = 0; i < wmax; ++i, F0 += s0, F1 += s1, F2 += s2) mask |= ((F0 | F1 | F2) >= 0 ? 1u : 0u) << i;
+            mask &= (1u << w) - 1u;
+        } else {
+            // rows 1 .. hmax - 1 exist for tiny entries only (<= 4 columns); a row entry in the same round is finished by row 0
+            const int32_t b0 = ws.By[0][slot], b1 = ws.By[1][slot], b2 = ws.By[2][slot];
+            const uint32_t wmaxT = __reduce_max_sync(0xFFFFFFFFu, tiny ? w : 0u);
+#pragma unroll 1
+            for (uint32_t i = 0; i < wmax; ++i) mask |= (((F0 + (int32_t)i * s0) | (F1 + (int32_t)i * s1) | (F2 + (int32_t)i * s2)) >= 0 ? 1u : 0u) << i;
+            mask &= (1u << w) - 1u;
+            if (tiny) {
+#pragma unroll 1
+                for (uint32_t jj = 1; jj < hmax; ++jj) {
+                    F0 += b0; F1 += b1; F2 += b2;
+#pragma unroll 1
+                    for (uint32_t i = 0; i < wmaxT; ++i)
+                        mask |= (((F0 + (int32_t)i * s0) | (F1 + (int32_t)i * s1) | (F2 + (int32_t)i * s2)) >= 0 ? 1u : 0u) << (4u * jj + i);
+                }
+                mask &= ((1u << w) - 1u) * (0x1111u & ((1u << (4u * h)) - 1u));
+                if ((!SHADOW || CULL) && pc.nRanks > 1) {   // rows of the bbox this rank does not own
+                    const uint32_t y0 = ws.xy[slot] >> 16;
+#pragma unroll
+                    for (uint32_t jj = 0; jj < 4u; ++jj)
+                        if (!row_owned(y0 + jj, pc.rank, pc.nRanks, pc.bandH)) mask &= ~(0xFu << (4u * jj));
+                }
+            }
+        }
     }
-    mask &= (1u << w) - 1u;
+    if (hmax <= 1u && tiny && (!SHADOW || CULL) && pc.nRanks > 1 && !row_owned(ws.xy[slot] >> 16, pc.rank, pc.nRanks, pc.bandH)) mask = 0u;   // 1-row tiny entry
     const uint32_t n = __popc(mask);
     const uint32_t incl = warp_incl_scan(n, lane);
     uint32_t pos = pixTail + incl - n;
     pixTail += __shfl_sync(0xFFFFFFFFu, incl, 31);
     const uint32_t tag = slot | (xo << 6) | (j << 11);   // i + xo < 32: the add cannot carry into j
     while (mask) {
-        const uint32_t i = (uint32_t)__ffs(mask) - 1u;
+        const uint32_t bpos = (uint32_t)__ffs(mask) - 1u;
         mask &= mask - 1u;
-        ws.pixq[pos++ & (K1_PIXQ - 1)] = (uint16_t)(tag + (i << 6));
+        const uint32_t i = tiny ? (bpos & 3u) : bpos, jj = tiny ? (bpos >> 2) : 0u;
+        ws.pixq[pos++ & (K1_PIXQ - 1)] = (uint16_t)(tag + (i << 6) + (jj << 11));
     }
     __syncwarp();
 }
@@ -380,14 +296,15 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         K1Tri t;
         k1_classify<SHIFT>(pc, tri < pc.nTris, q, t);
         k1_emit_large(pc, t, tri, lane);
-        if (t.needsClip) {   // Appendix B.3, rare: handed to k_clip_layout (keeps the clipper out of this kernel's register budget)
+        if (t.needsClip) {   // Appendix B.3, rare: queued for the tile stage's bin_phase (keeps the clipper out of this kernel's register budget)
             const uint32_t qi = atomicAdd(&pc.status[6], 1u);
             if (qi < pc.clipCap) pc.clipQueue[qi] = tri; else atomicOr(&pc.status[2], OVF_LARGE);
         }
         const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
         const uint32_t mySlot = (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1);
         // row entries of this lane's triangle: one per bbox row, two (half rows) when the bbox is wider than K1_SPLIT
-        const uint32_t nEnt = t.isSmall ? (uint32_t)(t.y1 - t.y0 + 1) << ((t.x1 - t.x0 + 1) > (int32_t)K1_SPLIT ? 1 : 0) : 0u;
+        const bool isTiny = t.isSmall && k1_is_tiny((uint32_t)(t.x1 - t.x0 + 1), (uint32_t)(t.y1 - t.y0 + 1));   // one entry for the whole bbox
+        const uint32_t nEnt = !t.isSmall ? 0u : (isTiny ? 1u : (uint32_t)(t.y1 - t.y0 + 1) << ((t.x1 - t.x0 + 1) > (int32_t)K1_SPLIT ? 1 : 0));
         if (t.isSmall) k1_store_small(ws, t, tri, mySlot);
         ringPos += __popc(smallMask);
         if (CULL) curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
@@ -396,12 +313,19 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
 
         // ---- 2./3. rows -> samples -> resolve; <= K1_SPLIT row entries per lane and round keep the rings within capacity ----
         uint32_t done = 0;
+        const bool oneEach = __all_sync(0xFFFFFFFFu, nEnt <= 1u);   // a batch of tiny (or culled) triangles: ballot instead of scan + loop
         do {
             const uint32_t c = min(nEnt - done, K1_SPLIT);
-            const uint32_t cIncl = warp_incl_scan(c, lane);
-            const uint32_t rowPos = rowTail + cIncl - c;
-            for (uint32_t j = 0; j < c; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(mySlot | ((done + j) << 6));
-            rowTail += __shfl_sync(0xFFFFFFFFu, cIncl, 31);
+            if (oneEach) {
+                const unsigned em = __ballot_sync(0xFFFFFFFFu, c != 0u);
+                if (c) ws.rowq[(rowTail + __popc(em & ((1u << lane) - 1u))) & (K1_ROWQ - 1)] = (uint16_t)mySlot;
+                rowTail += __popc(em);
+            } else {
+                const uint32_t cIncl = warp_incl_scan(c, lane);
+                const uint32_t rowPos = rowTail + cIncl - c;
+                for (uint32_t j = 0; j < c; ++j) ws.rowq[(rowPos + j) & (K1_ROWQ - 1)] = (uint16_t)(mySlot | ((done + j) << 6));
+                rowTail += __shfl_sync(0xFFFFFFFFu, cIncl, 31);
+            }
             done += c;
             __syncwarp();
             while (rowTail - rowHead >= 32u) {
@@ -420,55 +344,8 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         while (pixTail != pixHead) { const uint32_t c = min(32u, pixTail - pixHead); k1_pixels<SHADOW>(pc, ws, pixHead, c, lane); pixHead += c; }
     }
 
-    // the tile lists are laid out by k_clip_layout, after the clipped triangles (if any) have been counted too
+    // clipped parents and the per-tile lists are finished at the head of the tile stage (bin_phase, reb_bin.cuh)
 #undef K1_TRI
-}
-
-// ---------------------------------------------------------------------------------------------
-// K1c: clip + layout.  Warps stride over the queue of triangles K1 found to need true clipping (Appendix B.3; empty for
-// ordinary frames) and send their children into the large-triangle path; then the per-tile lists are laid out: start =
-// a running cursor (status[7]) bumped once per warp of 32 tiles — no ordered scan is needed because list order inside a
-// tile is irrelevant to the min-key resolve — and the counts become K2's scatter cursors.  Without clipping no CTA
-// depends on another and the whole grid shares the tiles (one CTA walking the 16 k tiles of a 2048^2 map took 64 us, the
-// 65 k tiles of a 4096^2 map 250 us); with clipping the last CTA to finish its share of the queue does it alone.
-// ---------------------------------------------------------------------------------------------
-constexpr int KC_THREADS = 128;
-template <bool SHADOW>
-__global__ void __launch_bounds__(KC_THREADS) k_clip_layout(const __grid_constant__ PassConst pc) {
-    __shared__ uint32_t isLast;
-    pdl_enter();
-    const unsigned lane = threadIdx.x & 31u;
-    const uint32_t nClip = min(pc.status[6], pc.clipCap);
-    uint32_t first = blockIdx.x * KC_THREADS, stride = gridDim.x * KC_THREADS;
-    if (nClip == 0) {
-        if (pc.status[0] == 0u) return;   // nothing binned (the usual frame of small triangles)
-    } else {
-        const uint32_t warpsPerGrid = (gridDim.x * KC_THREADS) >> 5;
-        for (uint32_t i = (blockIdx.x * KC_THREADS + threadIdx.x) >> 5; i < nClip; i += warpsPerGrid) k1_clip_emit<SHADOW>(pc, __ldcg(pc.clipQueue + i), lane);
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) isLast = (atomicAdd(&pc.status[5], 1u) == gridDim.x - 1u) ? 1u : 0u;
-        __syncthreads();
-        if (!isLast) return;
-        __threadfence();
-        first = 0u; stride = KC_THREADS;
-    }
-    const uint32_t nLarge = min(*reinterpret_cast<volatile uint32_t*>(&pc.status[0]), pc.largeCap);
-    if (nLarge == 0) return;
-    const uint32_t nTiles = pc.tilesX * pc.tilesY;
-    for (uint32_t i0 = first; i0 < nTiles; i0 += stride) {
-        const uint32_t i = i0 + threadIdx.x;
-        const uint32_t c = i < nTiles ? __ldcg(pc.tileCount + i) : 0u;
-        const uint32_t inc = warp_incl_scan(c, lane);
-        uint32_t wbase = 0;
-        if (lane == 31 && inc) {
-            wbase = atomicAdd(&pc.status[7], inc);
-            atomicMax(&pc.status[3], wbase + inc);   // = the final cursor once every warp is through; max over the sample passes of a multisampled frame (k_pass_reset keeps it)
-            if (wbase + inc > pc.listCap) atomicOr(&pc.status[2], OVF_LIST);
-        }
-        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
-        if (i < nTiles && c) { pc.tileStart[i] = wbase + inc - c; pc.tileCount[i] = 0u; }   // counts become the scatter cursors
-    }
 }
 
 // Re-bases a draw list's index stream into cache-slot space, in submission order (runs when the list changes).
@@ -481,22 +358,6 @@ __global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ P
 #pragma unroll
     for (int k = 0; k < 3; ++k) flat[3ull * tri + k] = (uint32_t)((int32_t)ix[k] + off);
     triMaterial[tri] = pc.draws[d].material;
-}
-
-// ---------------------------------------------------------------------------------------------
-// K2: scatter the queued large triangles into the per-tile lists laid out by K1's tail.
-// One warp per triangle (same tile walk as the count).  Does nothing when the queue is empty.
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_bin_scatter(const __grid_constant__ PassConst pc) {
-    pdl_enter();
-    const uint32_t nLarge = min(pc.status[0], pc.largeCap);
-    if (nLarge == 0) return;
-    const unsigned lane = threadIdx.x & 31u;
-    const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < nLarge; t += warpsPerGrid) {
-        const LargeRec r = pc.large[t];
-        tile_walk<true>(pc, r.X0, r.Y0, r.X1, r.Y1, r.X2, r.Y2, t, lane);
-    }
 }
 
 __global__ void k_fill_u32(uint32_t* __restrict__ p, uint32_t v, size_t n) {
@@ -552,18 +413,14 @@ void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStrea
     launch_k(kern[v], dim3(grid), dim3(K1_THREADS), st, true, pk);
 }
 
-void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
-    if (shadow) launch_k(k_clip_layout<true>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
-    else launch_k(k_clip_layout<false>, dim3(numSMs * 2), dim3(KC_THREADS), st, true, pc);
-}
-
 // Between the sample passes of a multisampled frame: re-arm the pass status words and the per-tile counters (K0's
 // prologue does this once per frame).  The overflow word and the largest list length stay, so the host sees an overflow of
 // any sample pass and sizes the regrow for the longest one.
 __global__ void __launch_bounds__(256) k_pass_reset(const __grid_constant__ PassConst pc) {
     pdl_enter();
-    if (blockIdx.x == 0 && threadIdx.x < 8 && threadIdx.x != 2 && threadIdx.x != 3) pc.status[threadIdx.x] = 0u;
-    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x < STATUS_WORDS && threadIdx.x != 2 && threadIdx.x != 3) pc.status[threadIdx.x] = 0u;
+    uint4* th = reinterpret_cast<uint4*>(pc.tileHead);
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) th[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
     launch_k(k_pass_reset, dim3((unsigned)numSMs), dim3(256), st, true, pc);
@@ -572,10 +429,6 @@ void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st) {
     if (pc.nTris == 0) return;
     k_flatten_slots<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, flat, triMaterial);
-}
-
-void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st) {
-    launch_k(k_bin_scatter, dim3(numSMs * 4), dim3(256), st, true, pc);
 }
 
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st) {

@@ -1,22 +1,28 @@
-// k_tile.cu — K3: the tile stage.  Every WARP is an independent worker that owns an 8-px-wide block of samples
-// (compact footprint: neighbouring samples share triangles, so the post-transform-cache gathers of a warp fall
-// into few sectors).  The visibility keys of the block live in registers; the large triangles that touch it
-// (broadcast list + binned list of the enclosing 32 x 8 tile) are staged 32 at a time — one per lane — into the
-// warp's private slice of shared memory as edge equations relative to the block origin, then tested by every lane
-// with the top-left rule, 64-bit edge functions and a min-key compare (early-Z and later-primitive-wins in one).
-// There is no CTA barrier anywhere in this file.
-//   shadow pass : the surviving depth of every covered sample is merged into the map with one fire-and-forget
-//                 atomicMin (the small triangles were resolved the same way by K1), so the map is never read here.
-//   forward pass: persistent CTAs stride over the tiles; the visibility key of the NEXT tile is loaded before the
-//                 current one is shaded (software prefetch), then every sample is shaded in place: attribute
-//                 reconstruction, bindless material fetch, Phong + 3x3 PCF.
+// k_tile.cu — the tile stages.  Every WARP is an independent worker that owns an 8-px-wide block of samples (compact footprint:
+// neighbouring samples share triangles, so the post-transform-cache gathers of a warp fall into few sectors).
+//   K2 k_tile_binned : the binned path of triangles too large for K1's own raster — leaves at once for the usual frame.  Clips
+//                      queued parents, lays out the per-tile lists, scatters the 48-B records (bin_phase, reb_bin.cuh), then
+//                      rasterises every tile's list: the list is a contiguous run of records, streamed into the warp's landing
+//                      buffer in shared memory by 1-D bulk asynchronous copies (cp.async.bulk + mbarrier; the next chunk lands
+//                      while the current one is tested), converted — one record per lane — into edge equations relative to the
+//                      block origin, tested by every lane with the top-left rule, 64-bit edge functions and a min-key compare
+//                      against the key held in a register, and merged with one atomicMin per covered sample.
+//   K3 shadow pass   : the broadcast list (triangles covering > 256 tiles, e.g. a ground plane) against every block; the surviving
+//                      depth of every covered sample is merged into the map with one fire-and-forget atomicMin (the small
+//                      triangles were resolved the same way by K1), so the map is never read here.
+//   K3 forward pass  : persistent CTAs stride over the tiles; the visibility key of the NEXT tile is loaded before the current one is
+//                      shaded (software prefetch); consumes + re-arms the visibility buffer, merges the broadcast list, then shades
+//                      every sample in place: attribute reconstruction, bindless material fetch, Phong + 3x3 PCF.
 //
 // Reference: fixed-function raster/depth state GraphicsPipelineCache.cpp:280-340; fragment work
 // phong.glsl:39-81 + shadow.glsl:24-56; clears RenderScene.cpp:217-220 / ShadowSystem.cpp:111-127.
+#include "reb_bin.cuh"
 #include "reb_shade.cuh"
 #include "reb_shade_pbr.cuh"
 #include "reb_sky.cuh"
 #include <algorithm>
+#include <string>
+#include <cstdlib>
 
 namespace reb {
 
@@ -32,14 +38,14 @@ struct WarpStage {
     uint32_t idKey[32], bias12[32];   // bias12: bit 0 = bias of edge 1, bit 1 = bias of edge 2 (to recover the unbiased values)
 };
 
-// Stage triangle r for the block whose first pixel is (bx0, by0) and that spans BLK_W x rows pixels; returns false
+// Stage triangle r for the block whose first pixel is (bx0, by0) and that spans cols x rows pixels; returns false
 // when the triangle cannot touch any pixel centre of the block (bbox + edge reject at the most-interior corner).
-__device__ __forceinline__ bool stage_record(const LargeRec& r, int bx0, int by0, int rows, WarpStage& ws, unsigned lane) {
+__device__ __forceinline__ bool stage_record(const LargeRec& r, int bx0, int by0, int cols, int rows, WarpStage& ws, unsigned lane) {
     const int32_t X[3] = {r.X0, r.X1, r.X2}, Y[3] = {r.Y0, r.Y1, r.Y2};
     const int32_t minX = min(r.X0, min(r.X1, r.X2)), maxX = max(r.X0, max(r.X1, r.X2));
     const int32_t minY = min(r.Y0, min(r.Y1, r.Y2)), maxY = max(r.Y0, max(r.Y1, r.Y2));
     const long long cx0 = 256ll * bx0 + 128, cy0 = 256ll * by0 + 128;
-    const long long spanX = 256ll * (BLK_W - 1), spanY = 256ll * (rows - 1);
+    const long long spanX = 256ll * (cols - 1), spanY = 256ll * (rows - 1);
     bool live = !(maxX < cx0 || minX > cx0 + spanX || maxY < cy0 || minY > cy0 + spanY);
     uint32_t bias12 = 0;
 #pragma unroll
@@ -79,32 +85,50 @@ __device__ __forceinline__ void test_samples(long long F0, long long F1, long lo
     }
 }
 
-// Merge a binned list of large triangles (src[idx[i]], i in [begin, end)) into this lane's SUB keys (depthBits<<32 |
-// ~triId, or the bare depth bits for the shadow pass; minimum wins).  Lane sample r sits at (lx, ly + BLK_ROWS * r)
-// inside the block.  begin / end / bx0 / by0 are warp-uniform.
-template <bool SHADOW, int SUB>
-__device__ __forceinline__ void merge_large(const LargeRec* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t begin, uint32_t end,
-                                            int bx0, int by0, int lx, int ly, typename KeyOf<SHADOW>::type (&key)[SUB], WarpStage& ws, unsigned lane) {
-    const int32_t dx = 256 * lx, dy = 256 * ly;
-    for (uint32_t base = begin; base < end; base += 32u) {
-        const uint32_t n = min(32u, end - base);
-        bool live = false;
-        if (lane < n) {
-            const LargeRec r = src[__ldcg(idx + base + lane)];
-            live = stage_record(r, bx0, by0, BLK_ROWS * SUB, ws, lane);
-        }
-        unsigned m = __ballot_sync(0xFFFFFFFFu, live);
-        __syncwarp();
-        while (m) {
-            const int s = __ffs(m) - 1;
-            m &= m - 1;
-            const long long F0 = ws.E[0][s] + mulw(ws.A[0][s], dx) + mulw(ws.B[0][s], dy);
-            const long long F1 = ws.E[1][s] + mulw(ws.A[1][s], dx) + mulw(ws.B[1][s], dy);
-            const long long F2 = ws.E[2][s] + mulw(ws.A[2][s], dx) + mulw(ws.B[2][s], dy);
-            test_samples<SHADOW, SUB>(F0, F1, F2, mulw(ws.B[0][s], 256 * BLK_ROWS), mulw(ws.B[1][s], 256 * BLK_ROWS), mulw(ws.B[2][s], 256 * BLK_ROWS), ws.bias12[s], ws.inv[s], ws.z0[s], ws.dz1[s], ws.dz2[s], ws.idKey[s], key);
-        }
-        __syncwarp();
+// ---- 1-D bulk asynchronous copy (TMA engine, no tensor map) global -> shared, completion on an mbarrier --------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// A warp's landing buffers for the raw records of the tile lists it walks: two 32-record buffers (1536 B each), one mbarrier
+// each.  The warp's tiles form one stream of <= 32-record chunks; chunk k + 1 (the next chunk of the same list, or the first
+// chunk of the warp's next non-empty tile) is copied by the TMA engine while chunk k is converted and tested.
+struct __align__(16) WarpRecs {
+    LargeRec rec[2][32];
+    uint64_t bar[2];
+};
+__device__ __forceinline__ void recs_init(WarpRecs& wr, unsigned lane) {
+    if (lane == 0) { mbar_init(&wr.bar[0], 1u); mbar_init(&wr.bar[1], 1u); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncwarp();
+}
+// lane 0 arms barrier b and starts the copy of n records into buffer b
+__device__ __forceinline__ void recs_issue(WarpRecs& wr, int b, const LargeRec* __restrict__ src, uint32_t n, unsigned lane) {
+#ifndef REB_NO_TMA
+    if (lane == 0) {
+        fence_proxy_async_smem();   // the buffer's earlier generic-proxy reads are ordered before the async-proxy write
+        const uint32_t bytes = n * (uint32_t)sizeof(LargeRec);
+        mbar_expect_tx(&wr.bar[b], bytes);
+        bulk_g2s(&wr.rec[b][0], src, bytes, &wr.bar[b]);
     }
+#endif
 }
 
 constexpr int HUGE_DIRECT = 6;   // broadcast lists up to this long skip the per-block liveness pass
@@ -184,15 +208,6 @@ __device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, 
     }
 }
 
-__device__ __forceinline__ void kt_tile_list(const PassConst& pc, uint32_t tile, uint32_t nLarge, uint32_t& begin, uint32_t& end) {
-    begin = end = 0;
-    if (!nLarge) return;
-    const uint32_t cnt = __ldcg(pc.tileCount + tile);
-    if (!cnt) return;
-    const uint32_t start = __ldcg(pc.tileStart + tile);
-    begin = min(start, pc.listCap); end = min(start + cnt, pc.listCap);
-}
-
 // Shadow pass tile stage: only blocks touched by large triangles do work (the small ones were resolved by K1's
 // atomics).  Persistent CTAs stride over 32 x 32 px regions (the status words and the broadcast list are fetched
 // once per CTA, so a region costs no dependent memory round trip); warp = 8 x 16 px (SHADOW_SUB samples per lane).
@@ -202,19 +217,124 @@ constexpr int SHADOW_SUB = SHADOW_SUB_D;
 #else
 constexpr int SHADOW_SUB = 4;
 #endif
-#ifndef SHADOW_RMW
-#define SHADOW_RMW 0
-#endif
 constexpr int SHADOW_REGION_H = BLK_ROWS * SHADOW_SUB * 2;
-__global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constant__ PassConst pc) {
+
+// Head of both tile-stage kernels: mirror the pass status words into mapped pinned memory for the host (overflow detection
+// without a device->host copy node); the binned path of this pass has completed by now (k_tile_binned).
+__device__ __forceinline__ void kt_head(const PassConst& pc, uint32_t& nHuge) {
+    if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = __ldcg(pc.status + threadIdx.x);
+    nHuge = min(__ldcg(pc.status + 4), (uint32_t)HUGE_CAP);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------------
+// K2 `k_tile_binned`: the tile rasteriser of the binned path.  Leaves at once when K1 queued nothing (the usual frame of small
+// triangles: one near-empty launch per pass).  Otherwise every warp of the persistent grid runs bin_phase (reb_bin.cuh: Appendix
+// B.3 clipping of queued parents -> per-tile list layout -> scatter of the 48-B records; every phase's work is claimed from a
+// global counter and nothing waits for a CTA that is not running), then every WARP strides over the 32 x 8 tiles with a non-empty list (lane = pixel column, 8 samples per lane): it streams
+// the tile's records through its two landing buffers (cp.async.bulk + mbarrier; the next chunk — of this list or of the warp's next
+// tile — lands while the current one is tested), tests them against its samples with the visibility keys in registers (top-left rule, early-Z and later-primitive-wins in one min-key compare) and merges the winner of every covered sample
+// into the pass's target with ONE atomicMin — the 64-bit visibility key (forward) or the depth bits of the map (shadow), exactly
+// what K1 does for the triangles it rasterises itself.  The shading / clear / broadcast-list stage (k_tile_forward, k_tile_shadow)
+// therefore carries no list code, no staging memory and none of this kernel's registers.
+// ---------------------------------------------------------------------------------------------------------------------------------
+// the warp's next tile (stride nWarps) with a non-empty list, the list clamped to the capacity; t >= nTiles: none left
+__device__ __forceinline__ uint32_t k2_next_tile(const PassConst& pc, uint32_t t, uint32_t stride, uint32_t nTiles, uint32_t& cnt, uint32_t& start) {
+    cnt = 0; start = 0;
+    for (; t < nTiles; t += stride) {
+        const uint2 h = __ldcg(reinterpret_cast<const uint2*>(pc.tileHead + t));   // {count, start}
+        if (!h.x || h.y >= pc.listCap) continue;            // empty, or an overflowed list (the host regrows and replays the frame)
+        start = h.y; cnt = min(h.x, pc.listCap - h.y);
+        break;
+    }
+    return t;
+}
+
+template <bool SHADOW>
+__global__ void __launch_bounds__(KT_THREADS, 3) k_tile_binned(const __grid_constant__ PassConst pc) {
     __shared__ WarpStage stage[KT_WARPS];
+    __shared__ WarpRecs recs[KT_WARPS];
+    __shared__ uint32_t claim;
+    pdl_enter();
+    if ((__ldcg(pc.status + 0) | __ldcg(pc.status + 6)) == 0u) return;   // grid-uniform: nothing has touched these words since K1 ended
+    bin_phase<SHADOW>(pc, &claim);
+    if (min(ld_acquire_u32(pc.status + 0), pc.largeCap) == 0u) return;   // (final: this warp has seen every phase complete)
+    typedef typename KeyOf<SHADOW>::type Key;
+    constexpr Key KEY_NONE = (Key)~0ull;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    WarpStage& ws = stage[warp];
+    WarpRecs& wr = recs[warp];
+    recs_init(wr, lane);
+    // one WARP per 32 x 8 tile: lane = pixel column, TILE_H samples per lane (one per row); tiles strided over all warps of the grid
+    const uint32_t nTiles = pc.tilesX * pc.tilesY, nWarps = (gridDim.x * KT_THREADS) >> 5;
+    uint32_t cnt, start, ncnt, nstart;
+    uint32_t tile = k2_next_tile(pc, blockIdx.x * KT_WARPS + warp, nWarps, nTiles, cnt, start);
+    if (tile >= nTiles) return;
+    uint32_t phase = 0u;
+    int buf = 0;
+    recs_issue(wr, 0, pc.tileRecs + start, min(32u, cnt), lane);
+    while (tile < nTiles) {
+        const uint32_t next = k2_next_tile(pc, tile + nWarps, nWarps, nTiles, ncnt, nstart);   // its loads overlap the copy in flight
+        const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
+        const int bx0 = (int)tx * TILE_W, by0 = (int)ty * TILE_H;
+        Key key[TILE_H];
+#pragma unroll
+        for (int r = 0; r < TILE_H; ++r) key[r] = KEY_NONE;
+        for (uint32_t off = 0; off < cnt; off += 32u, buf ^= 1) {
+            const uint32_t n = min(32u, cnt - off);
+            // the chunk after this one: the rest of this list, else the head of the next tile's list
+            if (off + 32u < cnt) recs_issue(wr, buf ^ 1, pc.tileRecs + start + off + 32u, min(32u, cnt - off - 32u), lane);
+            else if (next < nTiles) recs_issue(wr, buf ^ 1, pc.tileRecs + nstart, min(32u, ncnt), lane);
+            bool live = false;
+#ifndef REB_NO_TMA
+            mbar_wait(&wr.bar[buf], (phase >> buf) & 1u);
+            phase ^= 1u << buf;
+            if (lane < n) live = stage_record(wr.rec[buf][lane], bx0, by0, TILE_W, TILE_H, ws, lane);   // raw record -> edge equations (one per lane)
+#else
+            if (lane < n) {   // A/B build: one dependent 48-B load per lane instead of the bulk copy
+                const uint4* q = reinterpret_cast<const uint4*>(pc.tileRecs + start + off + lane);
+                union { LargeRec r; uint4 v[3]; } u;
+                u.v[0] = __ldcg(q); u.v[1] = __ldcg(q + 1); u.v[2] = __ldcg(q + 2);
+                live = stage_record(u.r, bx0, by0, TILE_W, TILE_H, ws, lane);
+            }
+#endif
+            unsigned m = __ballot_sync(0xFFFFFFFFu, live);
+            __syncwarp();
+            const int32_t dx = 256 * (int)lane;
+            while (m) {
+                const int s = __ffs(m) - 1;
+                m &= m - 1;
+                const long long F0 = ws.E[0][s] + mulw(ws.A[0][s], dx);
+                const long long F1 = ws.E[1][s] + mulw(ws.A[1][s], dx);
+                const long long F2 = ws.E[2][s] + mulw(ws.A[2][s], dx);
+                test_samples<SHADOW, TILE_H>(F0, F1, F2, mulw(ws.B[0][s], 256), mulw(ws.B[1][s], 256), mulw(ws.B[2][s], 256), ws.bias12[s], ws.inv[s], ws.z0[s], ws.dz1[s],
+                                             ws.dz2[s], ws.idKey[s], key);
+            }
+            __syncwarp();
+        }
+        // merge the winners into the pass target: one atomicMin per covered sample, 32 consecutive samples per row
+        const int x = bx0 + (int)lane;
+        if (x < (int)pc.W) {
+#pragma unroll
+            for (int r = 0; r < TILE_H; ++r) {
+                const int y = by0 + r;
+                if (key[r] == KEY_NONE || y >= (int)pc.H) continue;
+                if (SHADOW) atomicMin(pc.depthBits + (size_t)y * pc.W + x, (uint32_t)key[r]);
+                else atomicMin(pc.vis + (size_t)y * pc.W + x, (unsigned long long)key[r]);
+            }
+        }
+        tile = next; cnt = ncnt; start = nstart;
+    }
+}
+
+__global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constant__ PassConst pc) {
     __shared__ HugeStage hs;
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
-    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-    if (nLarge == 0 && nHuge == 0) return;
-    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }   // the only CTA barrier: once per CTA, CTA-uniform
+    uint32_t nHuge;
+    kt_head(pc, nHuge);
+    if (nHuge == 0) return;
+    stage_huge(pc.huge, nHuge, hs);
+    __syncthreads();   // once per CTA, CTA-uniform
     const uint32_t regionsY = (pc.H + SHADOW_REGION_H - 1) / SHADOW_REGION_H, nRegions = pc.tilesX * regionsY;
     const uint32_t stepY = gridDim.x / pc.tilesX, stepX = gridDim.x - stepY * pc.tilesX;
     uint32_t ry = blockIdx.x / pc.tilesX, rx = blockIdx.x - ry * pc.tilesX;
@@ -222,43 +342,19 @@ __global__ void __launch_bounds__(KT_THREADS) k_tile_shadow(const __grid_constan
     for (uint32_t region = blockIdx.x; region < nRegions; region += gridDim.x) {
         const int bx0 = (int)rx * TILE_W + BLK_W * (int)(warp & 3u);
         const int by0 = (int)ry * SHADOW_REGION_H + BLK_ROWS * SHADOW_SUB * (int)(warp >> 2);
-        const uint32_t tileX = rx;
         rx += stepX; ry += stepY;
         if (rx >= pc.tilesX) { rx -= pc.tilesX; ++ry; }
         if (bx0 >= (int)pc.W || by0 >= (int)pc.H) continue;   // warp-uniform
         if (pc.nRanks > 1 && !row_owned((uint32_t)by0, pc.rank, pc.nRanks, pc.bandH)) continue;   // shadow slabs (bandH % 32 == 0), warp-uniform
-        constexpr int NT = (BLK_ROWS * SHADOW_SUB + TILE_H - 1) / TILE_H;   // 32 x 8 tiles a warp's block spans vertically
-        uint32_t begin[NT], end[NT];
-#pragma unroll
-        for (int t = 0; t < NT; ++t) {
-            begin[t] = end[t] = 0;
-            const uint32_t ty = (uint32_t)by0 / TILE_H + t;
-            if (nLarge && ty < pc.tilesY) kt_tile_list(pc, ty * pc.tilesX + tileX, nLarge, begin[t], end[t]);
-        }
         const int x = bx0 + lx;
         uint32_t key[SHADOW_SUB];
 #pragma unroll
         for (int r = 0; r < SHADOW_SUB; ++r) key[r] = 0xFFFFFFFFu;
-#if SHADOW_RMW
-        uint32_t cur[SHADOW_SUB];   // K1 has completed, every sample belongs to one lane: plain read-compare-write, loads in flight during the merge
+        merge_huge<true, SHADOW_SUB>(hs, nHuge, bx0, by0, x, by0 + ly, key, lane);
 #pragma unroll
         for (int r = 0; r < SHADOW_SUB; ++r) {
             const int y = by0 + BLK_ROWS * r + ly;
-            cur[r] = (x < (int)pc.W && y < (int)pc.H) ? __ldcg(pc.depthBits + (size_t)y * pc.W + x) : 0u;
-        }
-#endif
-        if (nHuge) merge_huge<true, SHADOW_SUB>(hs, nHuge, bx0, by0, x, by0 + ly, key, lane);
-#pragma unroll
-        for (int t = 0; t < NT; ++t)
-            if (begin[t] != end[t]) merge_large<true, SHADOW_SUB>(pc.large, pc.tileList, begin[t], end[t], bx0, by0, lx, ly, key, stage[warp], lane);
-#pragma unroll
-        for (int r = 0; r < SHADOW_SUB; ++r) {
-            const int y = by0 + BLK_ROWS * r + ly;
-#if SHADOW_RMW
-            if (key[r] < cur[r]) pc.depthBits[(size_t)y * pc.W + x] = key[r];   // cur = 0 out of bounds
-#else
             if (key[r] != 0xFFFFFFFFu && x < (int)pc.W && y < (int)pc.H) atomicMin(pc.depthBits + (size_t)y * pc.W + x, key[r]);
-#endif
         }
     }
 }
@@ -276,10 +372,10 @@ __device__ __forceinline__ unsigned long long kt_load_key(const PassConst& pc, u
     return __ldcg(pc.vis + (size_t)y * pc.W + x);
 }
 
-// One 8 x 4 block: re-arm vis, merge large triangles, shade, write.  All arguments but key are warp-uniform.
+// One 8 x 4 block: re-arm vis, merge the broadcast list, shade, write.  All arguments but key are warp-uniform.
 template <bool TEXTURED, bool PBR, bool AFFINE>
 __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& sh, unsigned long long key0, int bx0, int by0, int lx, int ly, uint32_t nHuge,
-                                         const HugeStage& hs, uint32_t begin, uint32_t end, WarpStage& ws, unsigned lane) {
+                                         const HugeStage& hs, unsigned lane) {
     if (bx0 >= (int)pc.W || by0 >= (int)pc.H) return;   // warp-uniform
     unsigned long long key[1] = {key0};
     const int x = bx0 + lx, y = by0 + ly;
@@ -287,7 +383,6 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     const size_t p = (size_t)y * pc.W + x;
     if (inb && key[0] != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
     if (nHuge) merge_huge<false, 1>(hs, nHuge, bx0, by0, x, y, key, lane);
-    if (begin != end) merge_large<false, 1>(pc.large, pc.tileList, begin, end, bx0, by0, lx, ly, key, ws, lane);
     if (!inb) return;
     float depth = 1.0f;                    // depth clear 1.0 (RenderScene.cpp:219)
     uint32_t tri = TRI_NONE;
@@ -305,33 +400,17 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
 }
 
-#ifndef KT_MODE
-#define KT_MODE 1
-#endif
 #ifndef KT_PBR_MIN_BLOCKS
 #define KT_PBR_MIN_BLOCKS 3
 #endif
 template <bool TEXTURED, bool PBR, bool AFFINE, bool PART>
 __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_BLOCKS) k_tile_forward(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh) {
-    __shared__ WarpStage stage[KT_WARPS];
     __shared__ HugeStage hs;
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (blockIdx.x == 0 && threadIdx.x < 8 && pc.hostStatus) pc.hostStatus[threadIdx.x] = pc.status[threadIdx.x];
     const int lx = (int)(lane & 7u), ly = (int)(lane >> 3);
-    const uint32_t nLarge = pc.status[0], nHuge = min(pc.status[4], (uint32_t)HUGE_CAP);
-#if KT_MODE == 0
-    // one CTA per tile (hardware CTA scheduling), warp = block
-    const uint32_t tile = blockIdx.x;
-    const uint32_t ty = tile / pc.tilesX, tx = tile - ty * pc.tilesX;
-    if (!row_owned(ty * TILE_H, pc.rank, pc.nRanks, pc.bandH)) return;
-    const unsigned long long key = kt_load_key(pc, tx, ty, warp, lx, ly);
-    if (nHuge) { stage_huge(pc.huge, nHuge, hs); __syncthreads(); }
-    uint32_t begin, end;
-    kt_tile_list(pc, tile, nLarge, begin, end);
-    kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin, end,
-                       stage[warp], lane);
-#elif KT_MODE == 1
+    uint32_t nHuge;
+    kt_head(pc, nHuge);
     if (!PART) {
         // persistent CTAs, static striding over tiles, warp = block, next tile's key prefetched
         const uint32_t nTiles = pc.tilesX * pc.tilesY;
@@ -346,10 +425,7 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
             txN += stepX; tyN += stepY;
             if (txN >= pc.tilesX) { txN -= pc.tilesX; ++tyN; }
             if (tile + gridDim.x < nTiles) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
-            uint32_t begin, end;
-            kt_tile_list(pc, tile, nLarge, begin, end);
-            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
-                               end, stage[warp], lane);
+            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, lane);
         }
     } else {
         // sort-first split: the same loop over the tile rows of this rank's bands only ("virtual" rows vy = the owned rows in
@@ -370,13 +446,9 @@ __global__ void __launch_bounds__(KT_THREADS, PBR ? KT_PBR_MIN_BLOCKS : KT_MIN_B
             if (txN >= pc.tilesX) { txN -= pc.tilesX; ++vyN; }
             tyN = vyN + (vyN / pc.bandRows) * bandSkip + bandBase;
             if (vtile + gridDim.x < nVirtual) keyNext = kt_load_key(pc, txN, tyN, warp, lx, ly);
-            uint32_t begin, end;
-            kt_tile_list(pc, ty * pc.tilesX + tx, nLarge, begin, end);
-            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, begin,
-                               end, stage[warp], lane);
+            kt_block<TEXTURED, PBR, AFFINE>(pc, sh, key, (int)tx * TILE_W + BLK_W * (int)(warp & 3u), (int)ty * TILE_H + BLK_ROWS * (int)(warp >> 2), lx, ly, nHuge, hs, lane);
         }
     }
-#endif
 }
 
 // Multisample resolve (Appendix B.15; the reference's base pass is multisampled with an average resolve,
@@ -477,6 +549,20 @@ void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float*
     launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(pc.tilesX * pc.tilesY), dim3(KT_THREADS), st, true, pc, sh, msDepth, msTriId);
 }
 
+void launch_tile_binned(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {
+    static int perSM[2] = {0, 0};
+    const int v = shadow ? 1 : 0;
+    if (!perSM[v]) {
+        if (shadow) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM[v], k_tile_binned<true>, KT_THREADS, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM[v], k_tile_binned<false>, KT_THREADS, 0);
+        if (perSM[v] < 1) perSM[v] = 1;
+    }
+    // persistent; nothing in the kernel needs the CTAs to be resident at the same time (reb_bin.cuh)
+    const uint32_t grid = std::max(1u, std::min<uint32_t>((pc.tilesX * pc.tilesY + KT_WARPS - 1) / KT_WARPS, (uint32_t)(numSMs * perSM[v])));
+    if (shadow) launch_k(k_tile_binned<true>, dim3(grid), dim3(KT_THREADS), st, true, pc);
+    else launch_k(k_tile_binned<false>, dim3(grid), dim3(KT_THREADS), st, true, pc);
+}
+
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st) {
     static int perSM = 0;
     if (!perSM) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_tile_shadow, KT_THREADS, 0); if (perSM < 1) perSM = 1; }
@@ -501,11 +587,7 @@ void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, 
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], KT_THREADS, 0);
         perSM[v] = n > 0 ? n : 1;
     }
-#if KT_MODE == 0
-    const uint32_t grid = pc.tilesX * pc.tilesY;
-#else
     const uint32_t grid = std::max(1u, std::min<uint32_t>(pc.tilesX * pc.vTilesY, (uint32_t)(numSMs * perSM[v])));
-#endif
     launch_k(kern[v], dim3(grid), dim3(KT_THREADS), st, true, pc, sh);
 }
 

@@ -79,8 +79,9 @@ __device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t
 // Pass prologue (K0 is the first kernel of a pass and is stream-ordered after the previous use of these buffers): reset
 // the pass status words and the per-tile list counters, so the pass needs no memset node and the tile stage no re-arm.
 __device__ __forceinline__ void k0_prologue(const PassConst& pc) {
-    if (blockIdx.x == 0 && threadIdx.x < 8) pc.status[threadIdx.x] = 0u;
-    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) pc.tileCount[i] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x < STATUS_WORDS) pc.status[threadIdx.x] = 0u;
+    uint4* th = reinterpret_cast<uint4*>(pc.tileHead);
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < pc.tilesX * pc.tilesY; i += gridDim.x * 256u) th[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 // Fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice.
 __device__ __forceinline__ void k0_clear_shadow(const PassConst& pc) {

@@ -77,12 +77,11 @@ struct reb_ctx {
     uint32_t* clipQueue = nullptr;   // largeCap entries
     uint32_t largeAlloc = 0; bool largeWorstCase = false;
     LargeRec* huge = nullptr;        // 2 x HUGE_CAP
-    uint32_t* tileCount[2] = {nullptr, nullptr}; uint32_t tileCap[2] = {0, 0};   // per pass: both may be in flight behind one fused K0
-    uint32_t* tileStart = nullptr; uint32_t tileStartCap = 0;
+    TileHead* tileHead[2] = {nullptr, nullptr}; uint32_t tileCap[2] = {0, 0};   // per pass: both may be in flight behind one fused K0
     cudaEvent_t shadowReadyEvent = nullptr;   // reb_shadow_wait_event: waited for right before the next forward tile stage (one-shot)
     bool shadowDeferred = false; float recordedSPV[16];   // reb_render_shadow recorded, not yet submitted
-    uint32_t* tileList = nullptr; uint32_t listCap = 0;
-    uint32_t* dStatus = nullptr;     // 3 x 8 words
+    LargeRec* tileList = nullptr; uint32_t listCap = 0;   // per-tile lists of 48-B records (listCap records)
+    uint32_t* dStatus = nullptr;     // 3 x STATUS_WORDS words
     uint32_t* hStatus = nullptr;     // pinned + mapped mirror, written by the tile stage kernels
     uint32_t* hStatusDev = nullptr;  // device-side address of hStatus
     PassState pass[3];
@@ -175,14 +174,9 @@ int ensure_tiles(reb_ctx* ctx, int kind, uint32_t nTiles) {
     int rc;
     if (nTiles + 1 > ctx->tileCap[kind]) {
         CU(cudaStreamSynchronize(ctx->stream));
-        if ((rc = dev_alloc(ctx, &ctx->tileCount[kind], (size_t)nTiles + 1))) return rc;
-        CU(cudaMemsetAsync(ctx->tileCount[kind], 0, ((size_t)nTiles + 1) * 4, ctx->stream));   // K0's prologue zeroes them every pass
+        if ((rc = dev_alloc(ctx, &ctx->tileHead[kind], (size_t)nTiles + 1))) return rc;
+        CU(cudaMemsetAsync(ctx->tileHead[kind], 0, ((size_t)nTiles + 1) * sizeof(TileHead), ctx->stream));   // K0's prologue zeroes them every pass
         ctx->tileCap[kind] = nTiles + 1;
-    }
-    if (nTiles + 1 > ctx->tileStartCap) {
-        CU(cudaStreamSynchronize(ctx->stream));
-        if ((rc = dev_alloc(ctx, &ctx->tileStart, (size_t)nTiles + 1))) return rc;
-        ctx->tileStartCap = nTiles + 1;
     }
     return REB_OK;
 }
@@ -277,7 +271,12 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         uint32_t d = 0;
         for (uint32_t b = 0; b < tb; ++b) { while (d + 1 < n && dd[d + 1].firstTri <= b * 256ull) ++d; tbl[b] = d; }
         d = 0;
-        for (uint32_t b = 0; b < sb; ++b) { while (d + 1 < n && dd[d + 1].cacheBase <= b * 256ull) ++d; tbl[(size_t)tb + b] = d; }
+        for (uint32_t b = 0; b < sb; ++b) {
+            while (d + 1 < n && dd[d + 1].cacheBase <= b * 256ull) ++d;
+            // dd[n] is the sentinel (cacheBase = cache size): a block that ends before the next draw begins lies inside draw d
+            const bool oneDraw = n > 0 && (uint64_t)dd[d + 1].cacheBase >= (b + 1) * 256ull;
+            tbl[(size_t)tb + b] = d | (oneDraw ? BLOCK_ONE_DRAW : 0u);
+        }
         if (tbl.size() > ps.blockDrawCap) {
             int rc = dev_alloc(ctx, &ps.blockDraw, tbl.size());
             if (rc) return rc;
@@ -338,10 +337,10 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.vis = ctx->vis; pc.depthBits = reinterpret_cast<uint32_t*>(ctx->shadowMap);
     pc.large = ctx->large; pc.largeCap = ctx->largeAlloc; pc.clipQueue = ctx->clipQueue; pc.clipCap = ctx->largeCap; pc.huge = ctx->huge + (size_t)kind * HUGE_CAP;
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
-    pc.tileCount = ctx->tileCount[kind == 2 ? 1 : kind]; pc.tileStart = ctx->tileStart; pc.tileList = ctx->tileList; pc.listCap = ctx->listCap;
+    pc.tileHead = ctx->tileHead[kind == 2 ? 1 : kind]; pc.tileRecs = ctx->tileList; pc.listCap = ctx->listCap;
     pc.flatSlots = ps.flatSlots; pc.triMaterial = ps.triMaterial;
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
-    pc.status = ctx->dStatus + 8 * kind;
+    pc.status = ctx->dStatus + STATUS_WORDS * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
     if (kind >= 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
     else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; }
@@ -384,7 +383,8 @@ int prepare_pass(reb_ctx* ctx, int kind, PassConst& pc) {
 }
 
 // Enqueue the kernels of one pass: K0 vertex stage (unless the fused two-pass K0 already ran), K1 setup + small raster,
-// K2 bin scatter, K3 tile stage.  Every kernel after the first is PDL-chained.
+// K2 binned path (clip + list layout + scatter + TMA-staged tile raster; leaves at once when K1 queued nothing), K3 tile stage.
+// Every kernel after the first is PDL-chained.
 // Appendix B.14: inverse of A = rows x, y, w of proj * mat4(mat3(view)) restricted to 3x3 — maps (xn, yn, 1) to the
 // direction of the view ray (skybox.vert:32-37).  Adjugate / determinant in double, rounded to float once per frame.
 static void sky_ray_matrix(const float* view, const float* proj, float* out9) {
@@ -413,7 +413,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     auto mark = [&](int i) { if (ctx->profiling && !(fusedShadow && i < 2)) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
     mark(0);
     if (!ps.nTris) {   // no K0 to run the pass prologue: reset status here; an empty shadow list still has to clear the map
-        CU(cudaMemsetAsync(pc.status, 0, 32, ctx->stream));
+        CU(cudaMemsetAsync(pc.status, 0, STATUS_WORDS * 4, ctx->stream));
         if (kind == 0) { launch_fill_u32(pc.depthBits, 0x3F800000u, (size_t)ctx->S * ctx->S, ctx->numSMs, ctx->stream); ctx->launches++; }
     }
     mark(1);
@@ -471,10 +471,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
             sk.outSRGB8 = nullptr; sk.outF32 = nullptr; sk.skyFaces = nullptr;   // visibility only
             sk.outDepth = ctx->msDepth + (size_t)k * px; sk.outTriId = ctx->msTriId + (size_t)k * px;
             if (k > 0 && ps.nTris) { launch_pass_reset(pk, ctx->numSMs, ctx->stream); ctx->launches++; }
-            if (ps.nTris) {
-                launch_setup_raster(pk, false, ctx->numSMs, ctx->stream); launch_clip_layout(pk, false, ctx->numSMs, ctx->stream);
-                launch_bin_scatter(pk, ctx->numSMs, ctx->stream); ctx->launches += 3;
-            }
+            if (ps.nTris) { launch_setup_raster(pk, false, ctx->numSMs, ctx->stream); launch_tile_binned(pk, false, ctx->numSMs, ctx->stream); ctx->launches += 2; }
             launch_tile_forward(pk, sk, ctx->numSMs, ctx->stream); ctx->launches++;
         }
         mark(3); mark(4);
@@ -482,9 +479,8 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
     } else {
         if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
-        if (ps.nTris) { launch_clip_layout(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
         mark(3);
-        if (ps.nTris) { launch_bin_scatter(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
+        if (ps.nTris) { launch_tile_binned(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }   // K2: leaves at once when K1 queued nothing
         mark(4);
         if (kind == 0) { launch_tile_shadow(pc, ctx->numSMs, ctx->stream); ctx->launches++; }
         else {
@@ -545,7 +541,7 @@ int run_translucent(reb_ctx* ctx) {
     if ((rc = prepare_pass(ctx, 2, pc))) return rc;
     pc.tilesX = pc.tilesY = 0;                       // K0's prologue has no tile counters to re-arm for this list
     pc.drawVisible = nullptr; pc.blockVisible = nullptr;
-    pc.status = ctx->dStatus + 16;
+    pc.status = ctx->dStatus + 2 * STATUS_WORDS;
     pc.hostStatus = nullptr;
     ShadeConst sh = ctx->tlShade;
     float* hdr = ctx->outF32 ? ctx->outF32 : ctx->tlHdr;

@@ -38,15 +38,15 @@ int reb_create(const reb_params* params, reb_ctx** out) {
     if (ctx->rank >= ctx->nRanks || ctx->bandH % TILE_H) return bail(fail(ctx, REB_E_INVALID, "reb_create: bad partition (rank < n_ranks, band_h multiple of 8)"));
     int rc;
     if ((rc = alloc_targets(ctx))) return bail(rc);
-    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 96) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 96) != cudaSuccess ||
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 3 * STATUS_WORDS * 4) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 3 * STATUS_WORDS * 4) != cudaSuccess ||
         cudaMalloc(reinterpret_cast<void**>(&ctx->huge), 2 * HUGE_CAP * sizeof(LargeRec)) != cudaSuccess ||
         cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->hStatusDev), ctx->hStatus, 0) != cudaSuccess)
         return bail(fail(ctx, REB_E_CUDA, "status buffers allocation failed"));
     std::memset(ctx->hStatus, 0, 64);
-    ctx->listCap = 4u << 20;
+    ctx->listCap = 1u << 20;   // records of 48 B; grown on overflow (check_and_recover)
     if (const char* e = std::getenv("REB_TILE_LIST_CAP")) ctx->listCap = std::max(1024u, (uint32_t)std::strtoul(e, nullptr, 10));   // tests: force the regrow + replay path
-    if (cudaMalloc(reinterpret_cast<void**>(&ctx->tileList), (size_t)ctx->listCap * 4) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "tile list allocation failed"));
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->tileList), (size_t)ctx->listCap * sizeof(LargeRec)) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "tile list allocation failed"));
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "stream sync failed in reb_create"));
     *out = ctx;
     return REB_OK;
@@ -57,7 +57,7 @@ int reb_destroy(reb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
-                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileCount[0], ctx->tileCount[1], ctx->tileStart,
+                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileHead[0], ctx->tileHead[1],
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots,

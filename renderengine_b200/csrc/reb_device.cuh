@@ -63,6 +63,12 @@ struct __align__(16) LargeRec {
     float z2; uint32_t triId; uint32_t pad0, pad1;
 };
 
+// Per-tile list header of the binned path (one 16-B word group per 32 x 8 tile, zeroed by K0's prologue):
+//   count = records the list will hold (K1 / the clipper count while classifying); start = first record inside tileRecs (layout
+//   phase); pos = scatter cursor.
+struct __align__(16) TileHead { uint32_t count, start, pos, pad; };
+constexpr int STATUS_WORDS = 16;   // per pass
+
 struct PassConst {
     float PV[16];                 // proj*view (forward) or shadowProj*shadowView (shadow), column-major
     uint32_t W, H;                // target extent of this pass
@@ -84,14 +90,14 @@ struct PassConst {
     uint32_t* clipQueue; uint32_t clipCap;   // triangles that need true clipping (Appendix B.3), queued by K1 for k_clip_layout
     LargeRec* huge;               // HUGE_CAP records tested by every tile
     uint32_t tilesX, tilesY;
-    uint32_t* tileCount;          // per tile: entries in its large-triangle list (zero outside a pass)
-    uint32_t* tileStart;          // per tile: first entry of its list inside tileList
-    uint32_t* tileList; uint32_t listCap;
+    TileHead* tileHead;           // per tile: its large-triangle list (16 B, zeroed by the pass prologue)
+    LargeRec* tileRecs; uint32_t listCap;   // per-tile lists: contiguous runs of 48-B records (listCap records), streamed by the tile stage with bulk async copies
     const uint32_t* flatSlots;    // 3 cache slots per triangle in submission order (indexed mode)
     const uint32_t* triMaterial;  // raw material handle of every triangle's draw (indexed mode; shading reads it instead of walking to the draw record)
     const uint32_t* triBlockDraw; // draw containing the first triangle of every 256-triangle block
     const uint32_t* slotBlockDraw;// draw containing the first cache slot of every 256-slot block
-    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] CTA ticket (k_clip_layout) [6] clip-queue length
+    uint32_t* status;             // [0] largeCount [1] needsClip [2] overflow flags [3] tile-list total [4] hugeCount [5] - [6] clip-queue length [7] list allocation cursor
+                                  // k_tile_binned's phase queues: [8] / [9] clip items claimed / done, [11] / [12] tile blocks, [10] / [13] queued triangles
     uint32_t* hostStatus;         // mapped pinned mirror of status[0..7], written by the tile stage (no D2H copy node)
     uint32_t rank, nRanks, bandH; // sort-first row bands (forward only)
     // Appendix B.15 (multisampling): this raster pass samples at pixel centre - shift / 256, implemented as an exact integer
@@ -201,9 +207,14 @@ __device__ __forceinline__ uint32_t find_draw(const DrawDev* __restrict__ draws,
 }
 // Table-assisted variant: blockDraw[v >> 8] is the draw holding key (v & ~255) (host-built when the draw list
 // changes), followed by a short forward walk.  Relies on the sentinel record draws[nDraws].
+// Bit 31 of a table entry (BLOCK_ONE_DRAW, set by the host for the cache-slot table): the whole 256-element block lies inside that
+// draw, so the walk — a dependent load of the next draw's key, 24 % of the vertex kernel's stall samples — is skipped.
+constexpr uint32_t BLOCK_ONE_DRAW = 0x80000000u;
 template <bool BY_CACHE>
 __device__ __forceinline__ uint32_t find_draw_block(const DrawDev* __restrict__ draws, uint32_t nDraws, const uint32_t* __restrict__ blockDraw, uint32_t v) {
-    uint32_t d = __ldg(blockDraw + (v >> 8));
+    const uint32_t e = __ldg(blockDraw + (v >> 8));
+    uint32_t d = e & ~BLOCK_ONE_DRAW;
+    if (e & BLOCK_ONE_DRAW) return d;
     while (d + 1 < nDraws && draw_key<BY_CACHE>(draws, d + 1) <= v) ++d;
     return d;
 }

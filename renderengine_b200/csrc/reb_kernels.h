@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 #include "reb_device.cuh"
 
 namespace reb {
@@ -33,7 +34,8 @@ inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = pdl ? 1u : 0u;
+    static const bool noPdl = std::getenv("REB_NO_PDL") != nullptr;   // A/B + debugging switch
+    cfg.attrs = at; cfg.numAttrs = (pdl && !noPdl) ? 1u : 0u;
     cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
@@ -46,12 +48,11 @@ void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds,
 void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st);   // per 256-triangle block, once per draw list
 void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, cudaStream_t st);
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
-void launch_clip_layout(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);   // K1c: Appendix B.3 clipping + tile-list layout
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st);
-void launch_bin_scatter(const PassConst& pc, int numSMs, cudaStream_t st);   // PDL-chained after K1
 void launch_fill_u32(uint32_t* p, uint32_t v, size_t n, int numSMs, cudaStream_t st);
 void launch_fill_u32x4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, size_t n4, int numSMs, cudaStream_t st);
 void launch_split_vertices(const void* aos, float4* pos4, float4* nrm4, size_t nVerts, cudaStream_t st);
+void launch_tile_binned(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);   // K2: clip + list layout + record scatter + TMA-staged tile raster of the binned triangles
 void launch_tile_shadow(const PassConst& pc, int numSMs, cudaStream_t st);
 void launch_tile_forward(const PassConst& pc, const ShadeConst& sh, int numSMs, cudaStream_t st);
 // Appendix B.16 (k_translucent.cu): per-pixel fragment lists of the translucent triangles, then the ordered blend

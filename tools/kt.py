@@ -30,5 +30,8 @@ with torch.cuda.stream(st):
         for k in ((0, 1) if S else (1,)):
             for n, v in ctx.kernel_times_ms(k).items():
                 acc[("sh." if k == 0 else "fw.") + n] = acc.get(("sh." if k == 0 else "fw.") + n, 0) + v / 10
+slow = [round(t, 2) for t in ts if t > 5 * ts[0]]
+if slow:
+    print("   SLOW FRAMES (ms):", len(slow), slow[:8])
 print(os.environ.get("REB_LIB", "default"), cfg, f"frame median {1e3*ts[len(ts)//2]:.1f} us  min {1e3*ts[0]:.1f}  Mtri/s {s['n_triangles']/ts[len(ts)//2]/1e3:.0f}")
 print("   " + "  ".join(f"{k}={1e3*v:.1f}" for k, v in acc.items()), " counters", ctx.counters())
