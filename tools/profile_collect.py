@@ -8,7 +8,7 @@ rep = f"gpurun_out/{tag}_full.ncu-rep"
 shutil.copy(f"gpurun_out/{tag}_launches.csv", f"profiles/{tag}_launches.csv")
 with open(f"profiles/{tag}_ncu_summary.txt", "w") as f:
     f.write(subprocess.run([sys.executable, "tools/ncu_summary.py", rep], capture_output=True, text=True).stdout)
-    for k in ("k_tile_forward", "k_setup_raster", "k_tile_shadow", "k_vertex_both", "k_clip_layout"):
+    for k in ("k_tile_forward", "k_setup_raster", "k_tile_shadow", "k_vertex_both", "k_tile_binned"):
         out = subprocess.run([sys.executable, "tools/ncu_lines.py", rep, k, "18"], capture_output=True, text=True).stdout
         f.write("\n".join(line[:160] for line in out.splitlines()) + "\n")
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
@@ -19,8 +19,8 @@ sel = [s for s in ('Kernel Name', 'gpu__time_duration.sum', 'dram__bytes_read.su
                    'lts__t_sector_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
                    'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed') if s in ix]
 names = {'k_vertex_both': 'k_vertex_both', 'k_setup_raster<1': 'k_setup_raster<shadow>', 'k_setup_raster<0': 'k_setup_raster<forward>',
-         'k_clip_layout<1>': 'k_clip_layout<shadow>', 'k_clip_layout<0>': 'k_clip_layout<forward>',
-         'k_tile_shadow': 'k_tile_shadow', 'k_tile_forward': 'k_tile_forward', 'k_bin_scatter': 'k_bin_scatter'}
+         'k_tile_binned<1>': 'k_tile_binned<shadow>', 'k_tile_binned<0>': 'k_tile_binned<forward>',
+         'k_tile_shadow': 'k_tile_shadow', 'k_tile_forward': 'k_tile_forward'}
 mul = {'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1, 'Gbyte': 1e9}
 t = {}
 with open(f"profiles/{tag}_ncu_raw_selected.csv", "w", newline="") as f:
