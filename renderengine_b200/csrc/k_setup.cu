@@ -143,12 +143,18 @@ __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint3
 // Cache slots of the three corners of triangle `tri` (flatSlots: the draw list's index stream re-based into
 // cache-slot space in submission order, built when the draw list changes; de-indexed mode needs no table).
 // CULL (sort-first split): triangles of a 256-triangle block whose box touches no row of this rank come back as the sentinel
-// and are gathered as an all-zero (degenerate, hence culled) triangle; K0 skipped the vertices of wholly invisible draws.
+// and are gathered as an all-zero (degenerate, hence culled) triangle; K0 skipped the vertices of wholly invisible draws, so in a
+// block that spans draws the triangle's own draw is looked up.
 constexpr uint32_t SLOT_CULLED = 0xFFFFFFFFu;
 template <bool CULL>
 __device__ __forceinline__ uint3 k1_load_slots(const PassConst& pc, uint32_t tri) {
     if (tri >= pc.nTris) return make_uint3(0u, 0u, 0u);
-    if (CULL && __ldg(pc.blockVisible + (tri >> 8)) == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
+    if (CULL) {
+        const uint32_t vis = __ldg(pc.blockVisible + (tri >> 8));
+        if (vis == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
+        // a block that spans draws: K0 did not run the vertices of a culled draw, so its triangles must not be gathered
+        if (vis == BLOCK_MIXED && __ldg(pc.drawVisible + find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri)) == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
+    }
     if (pc.deindexed) return make_uint3(3u * tri, 3u * tri + 1u, 3u * tri + 2u);
     const uint32_t* f = pc.flatSlots + 3ull * tri;
     return make_uint3(__ldg(f), __ldg(f + 1), __ldg(f + 2));

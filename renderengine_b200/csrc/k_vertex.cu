@@ -22,12 +22,12 @@ namespace reb {
 constexpr int K0_PER_THREAD = K0_PER_THREAD_D;   // cache slots per thread: four independent load chains in flight
 
 constexpr uint32_t K0_MIN_GRID = 296u;           // two CTAs per SM
-struct K0In { float4 p, n; uint32_t node; bool valid, culled; };
+struct K0In { float4 p, n; uint32_t node; bool valid; };
 
 template <bool SHADOW, bool CULL = false>
 __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     K0In in;
-    in.valid = slot < pc.cacheSize; in.culled = false;
+    in.valid = slot < pc.cacheSize;
     in.node = 0; in.p = in.n = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!in.valid) return in;
     // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
@@ -39,9 +39,9 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     } else {
         v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
     }
-    // no row of this draw belongs to this rank: its slots get a trivially rejected record (a 256-triangle block that spans two
-    // draws is kept by k_cull_blocks, so K1 may still gather them — never stale data from an earlier view)
-    if (CULL && __ldg(pc.drawVisible + d) == 0u) { in.valid = false; in.culled = true; return in; }
+    // no row of this draw belongs to this rank: nothing is fetched, transformed or stored (K1 never gathers these slots: it skips
+    // the draw's 256-triangle blocks, and resolves the draw per triangle in a block that spans two draws)
+    if (CULL && __ldg(pc.drawVisible + d) == 0u) { in.valid = false; return in; }
     in.node = __ldg(&pc.draws[d].node);
     in.p = __ldg(pc.pos4 + v);
     if (!SHADOW) in.n = __ldg(pc.nrm4 + v);
@@ -50,7 +50,6 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
 
 template <bool SHADOW>
 __device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t slot, const K0In& in) {
-    if (in.culled) { reinterpret_cast<uint4*>(pc.vtxA)[slot] = make_uint4(0u, 0u, 0u, VF_PLANES); return; }   // Appendix B.2 rejects it
     if (!in.valid) return;
     const float4* Tq = reinterpret_cast<const float4*>(pc.transforms) + 4u * in.node;
     float T[16];
@@ -251,7 +250,7 @@ __global__ void __launch_bounds__(128) k_cull_blocks(const __grid_constant__ Pas
     if (tb >= nBlocks) return;
     const float4 lo = blockBox[2 * (size_t)tb], hi = blockBox[2 * (size_t)tb + 1];
     const uint32_t d = __float_as_uint(lo.w);
-    if (d == 0xFFFFFFFFu) { visible[tb] = 1u; return; }
+    if (d == 0xFFFFFFFFu) { visible[tb] = BLOCK_MIXED; return; }   // the block spans draws: K1 asks per triangle whether its draw is visible
     if (drawVisible[d] == 0u) { visible[tb] = 0u; return; }
     const float mn[3] = {lo.x, lo.y, lo.z}, mx[3] = {hi.x, hi.y, hi.z};
     float T[16];

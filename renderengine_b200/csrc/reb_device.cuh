@@ -210,6 +210,7 @@ __device__ __forceinline__ uint32_t find_draw(const DrawDev* __restrict__ draws,
 // Bit 31 of a table entry (BLOCK_ONE_DRAW, set by the host for the cache-slot table): the whole 256-element block lies inside that
 // draw, so the walk — a dependent load of the next draw's key, 24 % of the vertex kernel's stall samples — is skipped.
 constexpr uint32_t BLOCK_ONE_DRAW = 0x80000000u;
+constexpr uint32_t BLOCK_MIXED = 2u;   // blockVisible value of a 256-triangle block that spans two or more draws (sort-first culling)
 template <bool BY_CACHE>
 __device__ __forceinline__ uint32_t find_draw_block(const DrawDev* __restrict__ draws, uint32_t nDraws, const uint32_t* __restrict__ blockDraw, uint32_t v) {
     const uint32_t e = __ldg(blockDraw + (v >> 8));
