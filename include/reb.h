@@ -167,6 +167,23 @@ int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);
  * counterpart (single GPU; it renders the map once, RenderScene.cpp:171-175, and samples it every frame). */
 int reb_shadow_wait_event(reb_ctx* ctx, uint32_t shadowId, void* cudaEvent);
 
+/* Shadow depth pass of ONE draw that ALLOCATES NOTHING (no cudaMalloc / cudaFree, no context): for callers under CUDA graph
+ * capture, tight serving loops or harnesses that forbid allocation.  No counterpart in the reference.
+ * Same raster contract as reb_render_shadow (bit-exact on the same input): the map is cleared to 1.0, then
+ * every triangle (dIndices[3t..3t+2] into dVertices; position = the first three floats of each vertexStride-byte record, so the
+ * reference's 32-B Vertex buffer fits as is) goes through model16 -> shadowProj16 * shadowView16 -> viewport -> raster.
+ * dVertices / dIndices / dDepthOut (size * size floats) are DEVICE pointers on the current device; the three matrices are host
+ * pointers (column-major); cudaStream is a cudaStream_t (NULL = default stream); the work is asynchronous on it.
+ * Its scratch (post-transform vertex cache + large-triangle queue) is one static device array of 6 MiB + 256 B that every GPU
+ * loading this library holds until exit; inputs beyond REB_STATIC_MAX_VERTICES / REB_STATIC_MAX_TRIANGLES are rejected with
+ * REB_E_OVERFLOW.  All calls on a device share that array: calls that overlap on the GPU race — keep them on one stream.
+ * errOut (may be NULL) receives a static string describing a failure. */
+#define REB_STATIC_MAX_VERTICES  262144u
+#define REB_STATIC_MAX_TRIANGLES 524288u
+int reb_shadow_depth_static(const void* dVertices, uint32_t vertexStride, uint32_t nVertices, const uint32_t* dIndices, uint32_t nIndices,
+                            const float* model16, const float* shadowView16, const float* shadowProj16, uint32_t size, float* dDepthOut,
+                            void* cudaStream, const char** errOut);
+
 /* diagnostics: counters[0] clip children that could not be set up (non-finite input) + translucent fragments dropped by a
  * capacity limit — 0 for every finite scene within the limits above (triangles crossing the eye plane are CLIPPED, not dropped),
  * [1] triangles sent to the binned tile path by the passes of the last frame, [2] their tile-list entries, [3] queue regrow count */

@@ -17,8 +17,9 @@ SYMBOLS = [
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
     "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition", "reb_render_forward2",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_shadow_wait_event", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
-    "reb_get_kernel_times",
+    "reb_get_kernel_times", "reb_shadow_depth_static",
 ]
+REB_STATIC_MAX_VERTICES, REB_STATIC_MAX_TRIANGLES = 262144, 524288
 
 
 class RebParams(C.Structure):
@@ -79,12 +80,27 @@ def load():
     lib.reb_get_launch_count.argtypes = [vp, C.POINTER(u64)]
     lib.reb_set_profiling.argtypes = [vp, C.c_int]
     lib.reb_get_kernel_times.argtypes = [vp, C.c_int, vp]
+    lib.reb_shadow_depth_static.argtypes = [vp, u32, u32, vp, u32, vp, vp, vp, u32, vp, vp, C.POINTER(C.c_char_p)]
     _lib = lib
     return lib
 
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def shadow_depth_static(d_vertices, vertex_stride, n_vertices, d_indices, n_indices, model16, view16, proj16, size, d_depth_out, stream=None):
+    """reb_shadow_depth_static (include/reb.h): the allocation-free shadow depth pass of one draw.  d_* are DEVICE addresses (ints)
+    the caller owns; the matrices are 16 column-major floats each.  Asynchronous on `stream` (a cudaStream_t as int, None = default)."""
+    lib = load()
+    m = [np.ascontiguousarray(np.asarray(x, dtype=np.float32).reshape(16)) for x in (model16, view16, proj16)]
+    err = C.c_char_p()
+    rc = lib.reb_shadow_depth_static(C.c_void_p(d_vertices), vertex_stride, n_vertices, C.c_void_p(d_indices), n_indices,
+                                     _ptr(m[0]), _ptr(m[1]), _ptr(m[2]), size, C.c_void_p(d_depth_out), C.c_void_p(stream), C.byref(err))
+    if rc != 0:
+        e = RebError(f"libreb error {rc}: {(err.value or b'').decode()}")
+        e.code = rc
+        raise e
 
 
 _KIND_INFO = {REB_COLOR_SRGB8: (np.uint8, 4), REB_COLOR_F32: (np.float32, 4), REB_DEPTH_F32: (np.float32, 1),
