@@ -65,10 +65,27 @@ def build_host(force=False):
     hdir = os.path.join(HERE, "host")
     out = os.path.join(hdir, "reb_host_demo")
     srcs = [os.path.join(hdir, f) for f in ("RenderEngine.cpp", "demo_main.cpp")]
-    deps = srcs + [os.path.join(hdir, f) for f in ("RenderEngine.h", "reb_math.h")] + [os.path.join(os.path.dirname(HERE), "include", "reb.h"), OUT]
+    deps = srcs + [os.path.join(hdir, f) for f in ("RenderEngine.h", "reb_math.h", "demo_scene.h")] + [os.path.join(os.path.dirname(HERE), "include", "reb.h"), OUT]
     if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
         return out
     cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-o", out] + srcs + ["-L" + HERE, "-lreb", "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/.."]
+    subprocess.check_call(cmd)
+    build_mgpu_demo(force)
+    return out
+
+
+def build_mgpu_demo(force=False):
+    """host/reb_mgpu_demo: the C++ multi-GPU caller (one context per GPU + NCCL called directly), g++ against libreb.so, libcudart, libnccl."""
+    hdir = os.path.join(HERE, "host")
+    out = os.path.join(hdir, "reb_mgpu_demo")
+    srcs = [os.path.join(hdir, f) for f in ("RenderEngine.cpp", "demo_mgpu.cpp")]
+    deps = srcs + [os.path.join(hdir, f) for f in ("RenderEngine.h", "reb_math.h", "demo_scene.h")] + [os.path.join(os.path.dirname(HERE), "include", "reb.h"), OUT]
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(cuda, "include"), "-o", out] + srcs + \
+          ["-L" + HERE, "-lreb", "-L" + os.path.join(cuda, "lib64"), "-lcudart", "-lnccl", "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/..",
+           "-Wl,-rpath," + os.path.join(cuda, "lib64")]
     subprocess.check_call(cmd)
     return out
 

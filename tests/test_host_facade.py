@@ -113,3 +113,18 @@ def test_host_facade_reports_errors_as_exceptions(tmp_path):
     exe = build.build_host()
     r = subprocess.run([exe, "1", "1", "1", "0", "0", "0", "1"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 1 and "reb_create failed" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_multi_gpu_caller_reproduces_the_single_gpu_frames():
+    """host/demo_mgpu.cpp: one context per visible GPU, NCCL called directly from C++ on the pointers reb_get_output returns
+    (in-place ncclAllGather of shadow slabs for the sort-first split, ncclBroadcast + reb_shadow_wait_event for the view batch);
+    both schemes must reproduce GPU 0's own frames byte for byte.  With one GPU the collectives run on a 1-rank communicator."""
+    import torch
+    from renderengine_b200 import build
+    build.build_host()
+    exe = build.build_mgpu_demo()
+    n = max(1, min(torch.cuda.device_count(), 8))
+    r = subprocess.run([exe, str(n), "5", "4", "3", "640", "368", "512", "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "PASS" in r.stdout and r.stdout.count(" 0 differing bytes") == 2, r.stdout
