@@ -1055,9 +1055,12 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
     const int W = (int)sc->width, H = (int)sc->height;
     const size_t plane = (size_t)W * H;
     // translucent draws blend over the opaque frame in linear float and are drawn BEFORE the skybox (RenderScene.cpp:226-228)
-    const bool haveTranslucent = nSamples == 1 && sc->translucentDraws && sc->nTranslucentDraws;
+    const bool haveTranslucent = sc->translucentDraws && sc->nTranslucentDraws;
     std::vector<float> hdrTmp;
     if (haveTranslucent && !colorF32) { hdrTmp.resize(plane * 4); colorF32 = hdrTmp.data(); }
+    // Appendix B.15 + B.16 together: the multisampled target keeps one colour per SAMPLE until the resolve at the end of the pass
+    std::vector<float> colS;
+    if (haveTranslucent && nSamples == 4) colS.resize(4 * plane * 4);
     const bool skyNow = haveSky && !haveTranslucent;
     parallel_for(nT, [&](unsigned t) {
         int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
@@ -1076,16 +1079,17 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
                     V4 col[4];
                     for (int k = 0; k < 4; ++k) {
                         const uint32_t tri = triId[k * plane + p];
-                        const bool skyHere = haveSky && depth[k * plane + p] == 1.0f;
+                        const bool skyHere = skyNow && depth[k * plane + p] == 1.0f;
                         int same = -1;
                         for (int j = 0; j < k && same < 0; ++j) {
-                            const bool skyJ = haveSky && depth[j * plane + p] == 1.0f;
+                            const bool skyJ = skyNow && depth[j * plane + p] == 1.0f;
                             if (skyJ == skyHere && (skyHere || triId[j * plane + p] == tri)) same = j;
                         }
                         if (same >= 0) col[k] = col[same];
                         else if (skyHere) col[k] = sky_pixel(sky, x, y);
                         else if (tri != TRI_NONE) col[k] = shadeTri(x, y, tri);
                         else col[k] = clearColour;
+                        if (!colS.empty()) { float* c = &colS[(k * plane + p) * 4]; c[0] = col[k].x; c[1] = col[k].y; c[2] = col[k].z; c[3] = col[k].w; }
                     }
                     // pairwise sum: a pixel whose four samples agree resolves to exactly the 1-sample colour
                     out = {((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f, ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f,
@@ -1102,46 +1106,71 @@ int render_forward_impl(const orc_scene* sc, const float* shadowMap, float* dept
     // passes LessOrEqual against the current depth is shaded (at its pixel centre, attributes in the triangle's own vertex
     // order), blended  C = Cs * As + Cd * (1 - As),  A = As * (1 - As)  (GraphicsPipelineCache.cpp:305-315) in linear float —
     // the target is encoded once at the end — and writes its depth and ID.  The skybox comes after (depth still 1.0).
-    PassParams pt = pp; pt.twoSided = true;
-    Frontend ft;
+    // With 4 samples (B.15) coverage and the depth test run per sample and a primitive's one colour per pixel (shaded at the
+    // pixel centre) is blended into every sample it passes at: the samples are independent targets, so each one is replayed
+    // over its own colour / depth / ID plane; sky per sample, then the average resolve.
     const uint64_t idBase = fe.triPrefix.back();
-    run_frontend(sc, pt, ft, sc->translucentDraws, sc->nTranslucentDraws, idBase);
     curDraws = reinterpret_cast<const DrawRec*>(sc->translucentDraws);
-    curPrefix = &ft.triPrefix;
-    parallel_for(nT, [&](unsigned t) {
-        int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
-        for (const Setup& s : ft.setups) {
-            int ya = std::max(s.y0, r0), yb = std::min(s.y1, r1 - 1);
-            if (ya > yb) continue;
-            Edges e = make_edges(s);
-            for (int y = ya; y <= yb; ++y) {
-                if (!row_owned(sc, y)) continue;
-                int64_t Py = 256 * (int64_t)y + 128;
-                for (int x = s.x0; x <= s.x1; ++x) {
-                    int64_t Px = 256 * (int64_t)x + 128;
-                    int64_t F0 = e.A[0] * Px + e.B[0] * Py + e.C[0];
-                    int64_t F1 = e.A[1] * Px + e.B[1] * Py + e.C[1];
-                    int64_t F2 = e.A[2] * Px + e.B[2] * Py + e.C[2];
-                    if (F0 - e.bias[0] < 0 || F1 - e.bias[1] < 0 || F2 - e.bias[2] < 0) continue;
-                    float z = depth_at(s, F1, F2);
-                    if (!(z >= 0.0f && z <= 1.0f)) continue;
-                    size_t p = (size_t)y * W + x;
-                    if (!(z <= depth[p])) continue;
-                    const V4 src = shadeTri(x, y, (uint32_t)(s.triId - idBase));
-                    float* dst = colorF32 + 4 * p;
-                    const float a = src.w, ia = 1.0f - a;
-                    dst[0] = src.x * a + dst[0] * ia; dst[1] = src.y * a + dst[1] * ia; dst[2] = src.z * a + dst[2] * ia;
-                    dst[3] = a * ia;
-                    depth[p] = z; triId[p] = s.triId;
+    for (int k = 0; k < nSamples; ++k) {
+        PassParams pt = pp; pt.twoSided = true;
+        if (nSamples == 4) { pt.shiftX = MSAA4_SHIFT[k][0]; pt.shiftY = MSAA4_SHIFT[k][1]; }
+        Frontend ft;
+        run_frontend(sc, pt, ft, sc->translucentDraws, sc->nTranslucentDraws, idBase);
+        curPrefix = &ft.triPrefix;
+        float* colK = nSamples == 4 ? &colS[(size_t)k * plane * 4] : colorF32;
+        float* depthK = depth + (size_t)k * plane;
+        uint32_t* triK = triId + (size_t)k * plane;
+        parallel_for(nT, [&](unsigned t) {
+            int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
+            for (const Setup& s : ft.setups) {
+                int ya = std::max(s.y0, r0), yb = std::min(s.y1, r1 - 1);
+                if (ya > yb) continue;
+                Edges e = make_edges(s);
+                for (int y = ya; y <= yb; ++y) {
+                    if (!row_owned(sc, y)) continue;
+                    int64_t Py = 256 * (int64_t)y + 128;
+                    for (int x = s.x0; x <= s.x1; ++x) {
+                        int64_t Px = 256 * (int64_t)x + 128;
+                        int64_t F0 = e.A[0] * Px + e.B[0] * Py + e.C[0];
+                        int64_t F1 = e.A[1] * Px + e.B[1] * Py + e.C[1];
+                        int64_t F2 = e.A[2] * Px + e.B[2] * Py + e.C[2];
+                        if (F0 - e.bias[0] < 0 || F1 - e.bias[1] < 0 || F2 - e.bias[2] < 0) continue;
+                        float z = depth_at(s, F1, F2);
+                        if (!(z >= 0.0f && z <= 1.0f)) continue;
+                        size_t p = (size_t)y * W + x;
+                        if (!(z <= depthK[p])) continue;
+                        const V4 src = shadeTri(x, y, (uint32_t)(s.triId - idBase));
+                        float* dst = colK + 4 * p;
+                        const float a = src.w, ia = 1.0f - a;
+                        dst[0] = src.x * a + dst[0] * ia; dst[1] = src.y * a + dst[1] * ia; dst[2] = src.z * a + dst[2] * ia;
+                        dst[3] = a * ia;
+                        depthK[p] = z; triK[p] = s.triId;
+                    }
                 }
             }
-        }
+        });
+    }
+    parallel_for(nT, [&](unsigned t) {
+        int r0 = (int)((int64_t)H * t / nT), r1 = (int)((int64_t)H * (t + 1) / nT);
         for (int y = r0; y < r1; ++y)
             for (int x = 0; x < W; ++x) {
                 size_t p = (size_t)y * W + x;
-                if (haveSky && depth[p] == 1.0f && row_owned(sc, y)) {
-                    const V4 c = sky_pixel(sky, x, y);
-                    colorF32[4 * p + 0] = c.x; colorF32[4 * p + 1] = c.y; colorF32[4 * p + 2] = c.z; colorF32[4 * p + 3] = c.w;
+                if (nSamples == 1) {
+                    if (haveSky && depth[p] == 1.0f && row_owned(sc, y)) {
+                        const V4 c = sky_pixel(sky, x, y);
+                        colorF32[4 * p + 0] = c.x; colorF32[4 * p + 1] = c.y; colorF32[4 * p + 2] = c.z; colorF32[4 * p + 3] = c.w;
+                    }
+                } else {
+                    float c4[4][4];
+                    bool skyDone = false; V4 skyC{};
+                    for (int k = 0; k < 4; ++k) {
+                        const float* c = &colS[((size_t)k * plane + p) * 4];
+                        if (haveSky && depth[(size_t)k * plane + p] == 1.0f) {
+                            if (!skyDone) { skyC = sky_pixel(sky, x, y); skyDone = true; }
+                            c4[k][0] = skyC.x; c4[k][1] = skyC.y; c4[k][2] = skyC.z; c4[k][3] = skyC.w;
+                        } else { c4[k][0] = c[0]; c4[k][1] = c[1]; c4[k][2] = c[2]; c4[k][3] = c[3]; }
+                    }
+                    for (int ch = 0; ch < 4; ++ch) colorF32[4 * p + ch] = ((c4[0][ch] + c4[1][ch]) + (c4[2][ch] + c4[3][ch])) * 0.25f;
                 }
                 if (colorSRGB8) orc_srgb8(colorF32 + 4 * p, colorSRGB8 + 4 * p);
             }

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libreb.so")
-SOURCES = ["k_vertex.cu", "k_setup.cu", "k_tile.cu", "k_translucent.cu", "reb_capi.cu", "reb_noalloc.cu"]
+SOURCES = ["k_vertex.cu", "k_setup.cu", "k_tile.cu", "k_translucent.cu", "reb_capi.cu", "reb_noalloc.cu", "k_reorder.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "--fmad=false",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

@@ -146,21 +146,25 @@ __device__ __forceinline__ void k1_store_small(K1Warp& ws, const K1Tri& t, uint3
 // and are gathered as an all-zero (degenerate, hence culled) triangle; K0 skipped the vertices of wholly invisible draws, so in a
 // block that spans draws the triangle's own draw is looked up.
 constexpr uint32_t SLOT_CULLED = 0xFFFFFFFFu;
+// `tri` is the position in K1's stream; .w of the result is the triangle's SUBMISSION-order ID (Appendix B.9) — the same number
+// unless the draw list was re-ordered (k_reorder.cu), in which case one 16-B record holds the slots and the ID.
 template <bool CULL>
-__device__ __forceinline__ uint3 k1_load_slots(const PassConst& pc, uint32_t tri) {
-    if (tri >= pc.nTris) return make_uint3(0u, 0u, 0u);
+__device__ __forceinline__ uint4 k1_load_slots(const PassConst& pc, uint32_t tri) {
+    if (tri >= pc.nTris) return make_uint4(0u, 0u, 0u, tri);
     if (CULL) {
         const uint32_t vis = __ldg(pc.blockVisible + (tri >> 8));
-        if (vis == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
+        if (vis == 0u) return make_uint4(SLOT_CULLED, 0u, 0u, tri);
         // a block that spans draws: K0 did not run the vertices of a culled draw, so its triangles must not be gathered
-        if (vis == BLOCK_MIXED && __ldg(pc.drawVisible + find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri)) == 0u) return make_uint3(SLOT_CULLED, 0u, 0u);
+        // (a re-ordered list keeps every triangle inside its draw's range of positions, so the lookup by position holds)
+        if (vis == BLOCK_MIXED && __ldg(pc.drawVisible + find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri)) == 0u) return make_uint4(SLOT_CULLED, 0u, 0u, tri);
     }
-    if (pc.deindexed) return make_uint3(3u * tri, 3u * tri + 1u, 3u * tri + 2u);
+    if (pc.triStream) return __ldg(pc.triStream + tri);
+    if (pc.deindexed) return make_uint4(3u * tri, 3u * tri + 1u, 3u * tri + 2u, tri);
     const uint32_t* f = pc.flatSlots + 3ull * tri;
-    return make_uint3(__ldg(f), __ldg(f + 1), __ldg(f + 2));
+    return make_uint4(__ldg(f), __ldg(f + 1), __ldg(f + 2), tri);
 }
 template <bool CULL>
-__device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uint3 s, uint4 q[3]) {
+__device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uint4 s, uint4 q[3]) {
     if (tri >= pc.nTris || (CULL && s.x == SLOT_CULLED)) { q[0] = q[1] = q[2] = make_uint4(0, 0, 0, 0); return; }
     const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
     q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
@@ -279,43 +283,45 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     uint32_t batch = blockIdx.x * K1_WARPS + warp;
     uint4 q[3];
     bool curCulled = false;   // CULL: every triangle of the current batch belongs to a culled draw (warp-uniform)
+    uint32_t curId;           // submission-order ID of this lane's triangle of the current batch
     {
         const uint32_t tri = K1_TRI(batch);
-        const uint3 s0 = k1_load_slots<CULL>(pc, tri);
+        const uint4 s0 = k1_load_slots<CULL>(pc, tri);
         if (CULL) curCulled = __all_sync(0xFFFFFFFFu, s0.x == SLOT_CULLED || tri >= pc.nTris);
         k1_gather<CULL>(pc, tri, s0, q);
+        curId = s0.w;
     }
-    uint3 ns = k1_load_slots<CULL>(pc, K1_TRI(batch + totalWarps));   // slot stream runs two batches ahead of the raster stages
+    uint4 ns = k1_load_slots<CULL>(pc, K1_TRI(batch + totalWarps));   // slot stream runs two batches ahead of the raster stages
     uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;   // warp-uniform
     while (batch < nBatches) {
         const uint32_t nbatch = batch + totalWarps;
         const uint32_t tri = K1_TRI(batch), ntri = K1_TRI(nbatch);
-        const uint3 nns = k1_load_slots<CULL>(pc, K1_TRI(nbatch + totalWarps));   // in flight for a whole iteration
+        const uint4 nns = k1_load_slots<CULL>(pc, K1_TRI(nbatch + totalWarps));   // in flight for a whole iteration
         if (CULL && curCulled) {   // nothing of this batch is ours: only advance the software pipeline
             curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
             k1_gather<CULL>(pc, ntri, ns, q);
-            ns = nns; batch = nbatch;
+            curId = ns.w; ns = nns; batch = nbatch;
             continue;
         }
 
         // ---- 1. classify, emit large, append small records + rows ----------------------------------------
         K1Tri t;
         k1_classify<SHIFT>(pc, tri < pc.nTris, q, t);
-        k1_emit_large(pc, t, tri, lane);
+        k1_emit_large(pc, t, curId, lane);
         if (t.needsClip) {   // Appendix B.3, rare: queued for the tile stage's bin_phase (keeps the clipper out of this kernel's register budget)
             const uint32_t qi = atomicAdd(&pc.status[6], 1u);
-            if (qi < pc.clipCap) pc.clipQueue[qi] = tri; else atomicOr(&pc.status[2], OVF_LARGE);
+            if (qi < pc.clipCap) pc.clipQueue[qi] = curId; else atomicOr(&pc.status[2], OVF_LARGE);
         }
         const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
         const uint32_t mySlot = (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1);
         // row entries of this lane's triangle: one per bbox row, two (half rows) when the bbox is wider than K1_SPLIT
         const bool isTiny = t.isSmall && k1_is_tiny((uint32_t)(t.x1 - t.x0 + 1), (uint32_t)(t.y1 - t.y0 + 1));   // one entry for the whole bbox
         const uint32_t nEnt = !t.isSmall ? 0u : (isTiny ? 1u : (uint32_t)(t.y1 - t.y0 + 1) << ((t.x1 - t.x0 + 1) > (int32_t)K1_SPLIT ? 1 : 0));
-        if (t.isSmall) k1_store_small(ws, t, tri, mySlot);
+        if (t.isSmall) k1_store_small(ws, t, curId, mySlot);
         ringPos += __popc(smallMask);
         if (CULL) curCulled = __all_sync(0xFFFFFFFFu, ns.x == SLOT_CULLED || ntri >= pc.nTris);
         k1_gather<CULL>(pc, ntri, ns, q);                            // in flight during the raster stages
-        ns = nns;
+        curId = ns.w; ns = nns;
 
         // ---- 2./3. rows -> samples -> resolve; <= K1_SPLIT row entries per lane and round keep the rings within capacity ----
         uint32_t done = 0;

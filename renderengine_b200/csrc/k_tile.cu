@@ -472,7 +472,7 @@ struct ResolveStage {                 // per warp: the block's shading tasks, co
 #endif
 template <bool TEXTURED, bool PBR, bool AFFINE>
 __global__ void __launch_bounds__(KT_THREADS, KR_MIN_BLOCKS) k_msaa_resolve(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh,
-                                                                const float* __restrict__ msDepth, const uint32_t* __restrict__ msTriId) {
+                                                                const float* __restrict__ msDepth, const uint32_t* __restrict__ msTriId, float4* __restrict__ msColour) {
     __shared__ ResolveStage stage[KT_WARPS];
     pdl_enter();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -529,6 +529,11 @@ __global__ void __launch_bounds__(KT_THREADS, KR_MIN_BLOCKS) k_msaa_resolve(cons
         const bool shaded = sky[src[k]] || tri[src[k]] != TRI_NONE;
         col[k] = shaded ? rs.colour[lane][src[k]] : make_float4(0.0f, 0.0f, 0.0f, 1.0f);   // colour clear (RenderScene.cpp:218)
     }
+    if (msColour) {   // a translucent list follows inside this multisampled pass (Appendix B.16): every sample stays its own blend target
+#pragma unroll
+        for (int k = 0; k < 4; ++k) msColour[k * plane + p] = col[k];
+        return;       // k_tl_resolve_ms resolves, draws the sky and encodes
+    }
     float4 out;
     out.x = ((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f;
     out.y = ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f;
@@ -540,13 +545,13 @@ __global__ void __launch_bounds__(KT_THREADS, KR_MIN_BLOCKS) k_msaa_resolve(cons
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = out;
 }
 
-void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st) {
+void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, float4* msColour, cudaStream_t st) {
     const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
     const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
-    using Kern = void (*)(PassConst, ShadeConst, const float*, const uint32_t*);
+    using Kern = void (*)(PassConst, ShadeConst, const float*, const uint32_t*, float4*);
     static const Kern kern[8] = {k_msaa_resolve<false, false, false>, k_msaa_resolve<true, false, false>, k_msaa_resolve<false, true, false>, k_msaa_resolve<true, true, false>,
                                  k_msaa_resolve<false, false, true>,  k_msaa_resolve<true, false, true>,  k_msaa_resolve<false, true, true>,  k_msaa_resolve<true, true, true>};
-    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(pc.tilesX * pc.tilesY), dim3(KT_THREADS), st, true, pc, sh, msDepth, msTriId);
+    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(pc.tilesX * pc.tilesY), dim3(KT_THREADS), st, true, pc, sh, msDepth, msTriId, msColour);
 }
 
 void launch_tile_binned(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st) {

@@ -11,8 +11,10 @@
 //                 depth, shade at the pixel centre with the ordinary shade_pixel* code, C = Cs*As + Cd*(1-As),
 //                 A = As*(1-As) in linear float on the colour the opaque pass left, depth / ID write — then the skybox
 //                 (drawn after the translucent list, RenderScene.cpp:228) where the depth is still 1.0, then the encode.
-// Same individually rounded operations as oracle/oracle.cpp.  Limits of this first version: a pixel keeps at most
-// TL_MAX_FRAGS fragments and the frame at most `cap` list nodes (the excess is dropped and counted).
+// Same individually rounded operations as oracle/oracle.cpp.  A pixel's list has no length limit (up to TL_MAX_FRAGS fragments are
+// sorted in registers / local memory, longer lists are replayed by selection from the list itself); the frame holds at most `cap`
+// list nodes (the excess is dropped and counted).  Inside a 4x multisampled pass (Appendix B.15) the raster kernels run once per
+// sample with the sample's shift and list-head plane, and k_tl_resolve_ms merges the four lists of a pixel.
 #include "reb_shade.cuh"
 #include "reb_shade_pbr.cuh"
 #include "reb_sky.cuh"
@@ -39,7 +41,7 @@ __device__ __forceinline__ void tl_load(const PassConst& pc, uint32_t tri, VtxA 
     for (int k = 0; k < 3; ++k) {
         const uint32_t slot = s3[k];
         const uint4 q = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
-        a[k] = {(int32_t)q.x, (int32_t)q.y, __uint_as_float(q.z), q.w};
+        a[k] = {(int32_t)q.x + pc.shiftX, (int32_t)q.y + pc.shiftY, __uint_as_float(q.z), q.w};   // + the B.15 sample shift (0 in a 1-sample pass)
     }
 }
 
@@ -244,6 +246,8 @@ __global__ void __launch_bounds__(256) k_tl_raster_large(const __grid_constant__
         const int n = clip_parent<false>(pc, tri, c);
         for (int i = 1; i + 1 < n; ++i) {
             VtxA ch[3] = {viewport_snap(c[0], pc.W, pc.H), viewport_snap(c[i], pc.W, pc.H), viewport_snap(c[i + 1], pc.W, pc.H)};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { ch[k].X += pc.shiftX; ch[k].Y += pc.shiftY; }
             if (((ch[0].flags | ch[1].flags | ch[2].flags) & VF_NEEDS_CLIP) != 0u) {   // cannot happen for finite inputs: counted, dropped
                 if (threadIdx.x == 0 && local == 0) atomicAdd(&counters[2], 1u);
                 continue;
@@ -252,6 +256,21 @@ __global__ void __launch_bounds__(256) k_tl_raster_large(const __grid_constant__
         }
     }
 }
+
+// Ordered walk over a pixel's (unsorted) list without storing it: the fragment with the smallest submission-order ID above `prev`
+// (one list traversal per step; only lists longer than TL_MAX_FRAGS and the per-sample lists of a multisampled pass use it).
+struct TlCursor { uint32_t id; float z; };
+__device__ __forceinline__ TlCursor tl_scan(const uint4* __restrict__ nodes, uint32_t cap, uint32_t h, bool any, uint32_t prev) {
+    TlCursor c = {TL_NONE, 0.0f};
+    for (uint32_t q = h; q != TL_NONE && q < cap;) {
+        const uint4 nd = nodes[q];
+        if ((any || nd.y > prev) && nd.y < c.id) { c.id = nd.y; c.z = __uint_as_float(nd.z); }
+        q = nd.x;
+    }
+    return c;
+}
+__device__ __forceinline__ TlCursor tl_first(const uint4* __restrict__ nodes, uint32_t cap, uint32_t h) { return tl_scan(nodes, cap, h, true, 0u); }
+__device__ __forceinline__ TlCursor tl_next(const uint4* __restrict__ nodes, uint32_t cap, uint32_t h, uint32_t prev) { return tl_scan(nodes, cap, h, false, prev); }
 
 template <bool TEXTURED, bool PBR, bool AFFINE>
 __global__ void __launch_bounds__(256, 2) k_tl_resolve(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh, uint32_t* __restrict__ head,
@@ -272,24 +291,40 @@ __global__ void __launch_bounds__(256, 2) k_tl_resolve(const __grid_constant__ P
         head[p] = TL_NONE;                       // re-armed for the next frame
         uint32_t id[TL_MAX_FRAGS]; float z[TL_MAX_FRAGS];
         int n = 0;
-        while (h != TL_NONE && h < cap) {
-            const uint4 nd = nodes[h];
+        bool longList = false;                   // more than TL_MAX_FRAGS fragments: replayed by selection straight from the list
+        for (uint32_t q = h; q != TL_NONE && q < cap;) {
+            const uint4 nd = nodes[q];
             if (n < TL_MAX_FRAGS) {              // insertion by submission-order ID
                 int i = n++;
                 while (i > 0 && id[i - 1] > nd.y) { id[i] = id[i - 1]; z[i] = z[i - 1]; --i; }
                 id[i] = nd.y; z[i] = __uint_as_float(nd.z);
             } else {
-                atomicAdd(&counters[1], 1u);
+                longList = true;
+                break;
             }
-            h = nd.x;
+            q = nd.x;
         }
-        for (int i = 0; i < n; ++i) {
-            if (!(z[i] <= d)) continue;          // LessOrEqual against the running depth (depth write on)
-            const float4 src = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, id[i]) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, id[i]);
-            const float a = src.w, ia = 1.0f - a;
-            col.x = src.x * a + col.x * ia; col.y = src.y * a + col.y * ia; col.z = src.z * a + col.z * ia;
-            col.w = a * ia;
-            d = z[i]; lastId = id[i];
+        if (!longList) {
+            for (int i = 0; i < n; ++i) {
+                if (!(z[i] <= d)) continue;      // LessOrEqual against the running depth (depth write on)
+                const float4 src = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, id[i]) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, id[i]);
+                const float a = src.w, ia = 1.0f - a;
+                col.x = src.x * a + col.x * ia; col.y = src.y * a + col.y * ia; col.z = src.z * a + col.z * ia;
+                col.w = a * ia;
+                d = z[i]; lastId = id[i];
+            }
+        } else {
+            TlCursor c = tl_first(nodes, cap, h);
+            while (c.id != TL_NONE) {
+                if (c.z <= d) {
+                    const float4 src = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, c.id) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, c.id);
+                    const float a = src.w, ia = 1.0f - a;
+                    col.x = src.x * a + col.x * ia; col.y = src.y * a + col.y * ia; col.z = src.z * a + col.z * ia;
+                    col.w = a * ia;
+                    d = c.z; lastId = c.id;
+                }
+                c = tl_next(nodes, cap, h, c.id);
+            }
         }
     }
     if (sh.skyFaces && d == 1.0f) col = sky_pixel(sh, x, y);   // the skybox follows the translucent list (RenderScene.cpp:228)
@@ -301,6 +336,76 @@ __global__ void __launch_bounds__(256, 2) k_tl_resolve(const __grid_constant__ P
     if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(col);
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
     else reinterpret_cast<float4*>(hdr)[p] = col;
+}
+
+// Appendix B.15 + B.16: the translucent list inside the 4x multisampled base pass.  Every sample is its own blend target: the
+// opaque resolve left one linear colour per sample (msColour) and the four sample passes of the translucent raster one list per
+// sample.  Per pixel the four lists are merged in ID order; a primitive is shaded ONCE at the pixel centre when any of its
+// samples passes LessOrEqual against that sample's running depth, and blended into each passing sample; then the skybox per
+// sample (depth still 1.0), the average resolve ((s0 + s1) + (s2 + s3)) / 4 and the encode.  The per-sample depth / ID planes
+// are updated; the depth / ID targets take sample 0.
+template <bool TEXTURED, bool PBR, bool AFFINE>
+__global__ void __launch_bounds__(256, 2) k_tl_resolve_ms(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh, uint32_t* __restrict__ head,
+                                                          const uint4* __restrict__ nodes, uint32_t cap, uint32_t idBase, const float4* __restrict__ msColour,
+                                                          float* __restrict__ msDepth, uint32_t* __restrict__ msTriId) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * 8u, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * 32 + 8 * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * 8 + 4 * (int)(warp >> 2) + (int)(lane >> 3);
+    if (x >= (int)pc.W || y >= (int)pc.H) return;
+    const size_t p = (size_t)y * pc.W + x, plane = (size_t)pc.W * pc.H;
+    float4 col[4]; float d[4]; uint32_t h[4]; TlCursor c[4]; uint32_t lastId[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        col[k] = msColour[k * plane + p];
+        d[k] = msDepth[k * plane + p];
+        h[k] = head[k * plane + p];
+        lastId[k] = TL_NONE;
+        if (h[k] != TL_NONE) head[k * plane + p] = TL_NONE;   // re-armed for the next frame
+        c[k] = tl_first(nodes, cap, h[k]);
+    }
+    for (;;) {
+        const uint32_t id = min(min(c[0].id, c[1].id), min(c[2].id, c[3].id));
+        if (id == TL_NONE) break;
+        bool pass[4]; bool any = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { pass[k] = c[k].id == id && c[k].z <= d[k]; any = any || pass[k]; }
+        if (any) {
+            const float4 src = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, id) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, id);
+            const float a = src.w, ia = 1.0f - a;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (pass[k]) {
+                    col[k].x = src.x * a + col[k].x * ia; col[k].y = src.y * a + col[k].y * ia; col[k].z = src.z * a + col[k].z * ia;
+                    col[k].w = a * ia;
+                    d[k] = c[k].z; lastId[k] = id;
+                }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (c[k].id == id) c[k] = tl_next(nodes, cap, h[k], id);
+    }
+    bool anySky = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) anySky = anySky || (sh.skyFaces && d[k] == 1.0f);
+    if (anySky) {
+        const float4 s = sky_pixel(sh, x, y);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (d[k] == 1.0f) col[k] = s;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (lastId[k] != TL_NONE) { msDepth[k * plane + p] = d[k]; msTriId[k * plane + p] = lastId[k] + idBase; }
+    float4 out;
+    out.x = ((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f;
+    out.y = ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f;
+    out.z = ((col[0].z + col[1].z) + (col[2].z + col[3].z)) * 0.25f;
+    out.w = ((col[0].w + col[1].w) + (col[2].w + col[3].w)) * 0.25f;
+    if (sh.outDepth) sh.outDepth[p] = d[0];
+    if (sh.outTriId) sh.outTriId[p] = lastId[0] != TL_NONE ? lastId[0] + idBase : msTriId[p];   // (the opaque resolve left the 1-plane targets to this kernel)
+    if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(out);
+    if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = out;
 }
 
 void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, uint2* largeList, int numSMs,
@@ -321,6 +426,18 @@ void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head
     const uint32_t tilesX = (pc.W + 31u) / 32u, tilesY = (pc.H + 7u) / 8u;
     PassConst q = pc; q.tilesX = tilesX; q.tilesY = tilesY;
     launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(tilesX * tilesY), dim3(256), st, true, q, sh, head, nodes, cap, idBase, hdr, depth, counters);
+}
+
+void launch_tl_resolve_ms(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, const float4* msColour,
+                          float* msDepth, uint32_t* msTriId, cudaStream_t st) {
+    const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
+    const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
+    using Kern = void (*)(PassConst, ShadeConst, uint32_t*, const uint4*, uint32_t, uint32_t, const float4*, float*, uint32_t*);
+    static const Kern kern[8] = {k_tl_resolve_ms<false, false, false>, k_tl_resolve_ms<true, false, false>, k_tl_resolve_ms<false, true, false>, k_tl_resolve_ms<true, true, false>,
+                                 k_tl_resolve_ms<false, false, true>,  k_tl_resolve_ms<true, false, true>,  k_tl_resolve_ms<false, true, true>,  k_tl_resolve_ms<true, true, true>};
+    const uint32_t tilesX = (pc.W + 31u) / 32u, tilesY = (pc.H + 7u) / 8u;
+    PassConst q = pc; q.tilesX = tilesX; q.tilesY = tilesY;
+    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(tilesX * tilesY), dim3(256), st, true, q, sh, head, nodes, cap, idBase, msColour, msDepth, msTriId);
 }
 
 }  // namespace reb

@@ -32,19 +32,20 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     if (!in.valid) return in;
     // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
     const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, slot);
-    uint32_t v;
+    uint32_t v = slot;
     if (pc.deindexed) {
         const uint32_t tri = slot / 3u, k = slot - 3u * tri;
         v = __ldg(pc.indices + __ldg(&pc.draws[d].indexOffset) + 3u * (tri - __ldg(&pc.draws[d].firstTri)) + k);
-    } else {
+    } else if (!pc.posS) {
         v = (uint32_t)((int32_t)slot - __ldg(&pc.draws[d].cacheOffset));
     }
     // no row of this draw belongs to this rank: nothing is fetched, transformed or stored (K1 never gathers these slots: it skips
     // the draw's 256-triangle blocks, and resolves the draw per triangle in a block that spans two draws)
     if (CULL && __ldg(pc.drawVisible + d) == 0u) { in.valid = false; return in; }
     in.node = __ldg(&pc.draws[d].node);
-    in.p = __ldg(pc.pos4 + v);
-    if (!SHADOW) in.n = __ldg(pc.nrm4 + v);
+    // re-ordered draw list: the source streams were copied into slot order (k_reorder.cu), the read is as linear as the write
+    in.p = __ldg((pc.posS ? pc.posS : pc.pos4) + v);
+    if (!SHADOW) in.n = __ldg((pc.posS ? pc.nrmS : pc.nrm4) + v);
     return in;
 }
 
@@ -263,12 +264,14 @@ __global__ void __launch_bounds__(256) k_block_bounds(const __grid_constant__ Pa
     __shared__ uint32_t dFirst, dLast;
     const uint32_t tb = blockIdx.x, tri = tb * 256u + threadIdx.x;
     float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-    if (tri < pc.nTris) {
+    if (tri < pc.nTris) {   // (with a re-ordered list `tri` is a position in K1's stream: blocks are blocks of that stream)
         const uint32_t d = find_draw_block<false>(pc.draws, pc.nDraws, pc.triBlockDraw, tri);
         const uint32_t* ix = pc.indices + pc.draws[d].indexOffset + 3u * (tri - pc.draws[d].firstTri);
+        uint32_t sl[3] = {0u, 0u, 0u};
+        if (pc.triStream) { const uint4 r = __ldg(pc.triStream + tri); sl[0] = r.x; sl[1] = r.y; sl[2] = r.z; }
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            const float4 p = __ldg(pc.pos4 + __ldg(ix + k));
+            const float4 p = pc.triStream ? __ldg(pc.posS + sl[k]) : __ldg(pc.pos4 + __ldg(ix + k));
             lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
             hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
         }

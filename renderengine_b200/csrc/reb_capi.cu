@@ -29,6 +29,8 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaq
     uint32_t cacheSize = 0, deindexed = 0;
     uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;
     float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
+    // re-ordered list (k_reorder.cu): source streams in slot order, K1's {slots, submission ID} stream
+    float4* posS = nullptr; float4* nrmS = nullptr; size_t streamCap = 0; uint4* triStream = nullptr; size_t triStreamCap = 0; bool reordered = false;
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
     bool pending = false;        // enqueued since the last overflow check
 };
@@ -68,7 +70,8 @@ struct reb_ctx {
     // translucent list (Appendix B.16, k_translucent.cu): per-pixel list heads, node pool, device counters {nodes, dropped, needs-clip};
     // internal linear-colour / depth targets when the caller did not enable those outputs
     uint32_t* tlHead = nullptr; uint4* tlNodes = nullptr; uint32_t tlCap = 0; uint32_t* tlCounters = nullptr; uint2* tlLarge = nullptr; uint32_t tlLargeCap = 0;
-    float* tlHdr = nullptr; float* tlDepth = nullptr; size_t tlPx = 0;
+    float* tlHdr = nullptr; float* tlDepth = nullptr; size_t tlPx = 0;   // tlPx = pixels x samples the lists are sized for
+    float4* msColour = nullptr;   // 4 sample planes of linear colour: a translucent list inside a multisampled pass blends per sample
     bool tlFollows = false, tlPending = false; ShadeConst tlShade; uint32_t tlIdBase = 0; uint64_t tlDropped = 0;
     // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
     uint32_t samples = 1; float* msDepth = nullptr; uint32_t* msTriId = nullptr;
@@ -305,10 +308,8 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
             if ((rc = dev_alloc(ctx, &ps.blockBox, (size_t)ps.triBlocks * 2)) || (rc = dev_alloc(ctx, &ps.blockVisible, (size_t)ps.triBlocks))) return rc;
             ps.blockCullCap = ps.triBlocks;
         }
-        PassConst pcb;
-        fill_pass(ctx, kind, pcb);
-        launch_block_bounds(pcb, ps.blockBox, ctx->stream); ctx->launches++;
     }
+    ps.reordered = false;
     if (!ps.deindexed && tri) {   // index stream re-based into cache-slot space
         if (tri > ps.flatCap) {
             int rc;
@@ -318,6 +319,31 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         PassConst pc;
         fill_pass(ctx, kind, pc);
         launch_flatten_slots(pc, ps.flatSlots, ps.triMaterial, ctx->stream); ctx->launches++;
+        CU(cudaStreamSynchronize(ctx->stream));
+        // long lists: triangles along a Morton curve per draw, slots in first-use order (k_reorder.cu).  Short lists stay in
+        // submission order: a list that fits the caches has no locality to win and K1's 16-B stream records cost more than
+        // 12 B of slots (C1, 64 k triangles: K1 12 -> 16 us).
+        static const bool noReorder = std::getenv("REB_NO_REORDER") != nullptr;
+        static const uint64_t minTris = std::getenv("REB_REORDER_MIN_TRIS") ? std::strtoull(std::getenv("REB_REORDER_MIN_TRIS"), nullptr, 10) : 262144ull;
+        if (!noReorder && tri >= minTris) {
+            int rc;
+            if (slots > ps.streamCap) {
+                if ((rc = dev_alloc(ctx, &ps.posS, (size_t)slots)) || (rc = dev_alloc(ctx, &ps.nrmS, (size_t)slots))) return rc;
+                ps.streamCap = (size_t)slots;
+            }
+            if (tri > ps.triStreamCap) {
+                if ((rc = dev_alloc(ctx, &ps.triStream, (size_t)tri))) return rc;
+                ps.triStreamCap = (size_t)tri;
+            }
+            CU(reorder_draw_list(pc, ps.drawBounds, ps.posS, ps.nrmS, ps.triStream, ps.flatSlots, ctx->stream));
+            ctx->launches += 9;
+            ps.reordered = true;
+        }
+    }
+    if (n) {   // per-block bounds for the sort-first culling: blocks of K1's stream, i.e. after a re-ordering
+        PassConst pcb;
+        fill_pass(ctx, kind, pcb);
+        launch_block_bounds(pcb, ps.blockBox, ctx->stream); ctx->launches++;
         CU(cudaStreamSynchronize(ctx->stream));
     }
     ps.draws.assign(draws, draws + n);
@@ -339,6 +365,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
     pc.tileHead = ctx->tileHead[kind == 2 ? 1 : kind]; pc.tileRecs = ctx->tileList; pc.listCap = ctx->listCap;
     pc.flatSlots = ps.flatSlots; pc.triMaterial = ps.triMaterial;
+    if (ps.reordered) { pc.posS = ps.posS; pc.nrmS = ps.nrmS; pc.triStream = ps.triStream; }
     pc.triBlockDraw = ps.blockDraw; pc.slotBlockDraw = ps.blockDraw ? ps.blockDraw + ps.triBlocks : nullptr;
     pc.status = ctx->dStatus + STATUS_WORDS * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
@@ -476,7 +503,7 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         }
         mark(3); mark(4);
         if (ctx->shadowReadyEvent) { CU(cudaStreamWaitEvent(ctx->stream, ctx->shadowReadyEvent, 0)); ctx->shadowReadyEvent = nullptr; }
-        launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
+        launch_msaa_resolve(pc, sh, ctx->msDepth, ctx->msTriId, ctx->tlFollows ? ctx->msColour : nullptr, ctx->stream); ctx->launches++;
     } else {
         if (ps.nTris) { launch_setup_raster(pc, kind == 0, ctx->numSMs, ctx->stream); ctx->launches++; }
         mark(3);
@@ -552,6 +579,25 @@ int run_translucent(reb_ctx* ctx) {
         ctx->tlLargeCap = pc.nTris;
     }
     CU(cudaMemsetAsync(ctx->tlCounters, 0, 32, ctx->stream));
+    if (ctx->samples == 4) {
+        // Appendix B.15 + B.16: one raster pass of the translucent list per sample (the sample's exact vertex shift, its own opaque depth
+        // plane and list-head plane; the node pool is shared), then the merge over the per-sample colours the opaque resolve left
+        static const int32_t shift[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};
+        const size_t px = (size_t)ctx->W * ctx->H;
+        if (pc.nTris) { launch_vertex(pc, false, /*pdl=*/false, ctx->stream); ctx->launches++; }
+        for (int k = 0; k < 4 && pc.nTris; ++k) {
+            PassConst pk = pc;
+            pk.shiftX = shift[k][0]; pk.shiftY = shift[k][1];
+            if (k) CU(cudaMemsetAsync(ctx->tlCounters + 4, 0, 8, ctx->stream));   // the large-triangle work list restarts; the node counter runs on
+            launch_tl_raster(pk, ctx->msDepth + (size_t)k * px, ctx->tlHead + (size_t)k * px, ctx->tlNodes, ctx->tlCap, ctx->tlCounters, ctx->tlLarge, ctx->numSMs, ctx->stream);
+            ctx->launches += 2;
+        }
+        pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
+        launch_tl_resolve_ms(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, ctx->msColour, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
+        CU(cudaGetLastError());
+        ctx->tlPending = true;
+        return REB_OK;
+    }
     if (pc.nTris) {
         launch_vertex(pc, false, /*pdl=*/false, ctx->stream);
         launch_tl_raster(pc, depth, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlCounters, ctx->tlLarge, ctx->numSMs, ctx->stream);

@@ -65,7 +65,9 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible,
                     ctx->pass[2].dDraws, ctx->pass[2].vtxA, ctx->pass[2].vtxBC, ctx->pass[2].blockDraw, ctx->pass[2].flatSlots, ctx->pass[2].drawBounds,
                     ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
-                    ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge};
+                    ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge, ctx->msColour,
+                    ctx->pass[0].posS, ctx->pass[1].posS, ctx->pass[2].posS, ctx->pass[0].nrmS, ctx->pass[1].nrmS, ctx->pass[2].nrmS,
+                    ctx->pass[0].triStream, ctx->pass[1].triStream, ctx->pass[2].triStream};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);
@@ -268,16 +270,16 @@ static int render_base_pass(reb_ctx* ctx, const reb_draw* draws, uint32_t n, con
     if (!ctx->tlFollows) return submit_forward(ctx);
     // Appendix B.16: the translucent list of the same base pass (RenderScene.cpp:226-227)
     if (!translucent) return fail(ctx, REB_E_INVALID, "reb_render_forward2: null translucent draws");
-    if (ctx->samples != 1) return fail(ctx, REB_E_UNSUPPORTED, "reb_render_forward2: translucent draws are not supported with 4x multisampling yet");
     if ((rc = set_draws(ctx, 2, translucent, nTranslucent))) return rc;
-    const size_t px = (size_t)ctx->W * ctx->H;
-    if (ctx->tlPx != px) {
+    const size_t px = (size_t)ctx->W * ctx->H, spx = px * ctx->samples;   // one list head per sample
+    if (ctx->tlPx != spx) {
         CU(cudaStreamSynchronize(ctx->stream));
-        const uint32_t cap = (uint32_t)std::min<size_t>(std::max<size_t>(4 * px, (size_t)1 << 20), (size_t)1 << 28);
-        if ((rc = dev_alloc(ctx, &ctx->tlHead, px)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)8)) ||
+        const uint32_t cap = (uint32_t)std::min<size_t>(std::max<size_t>(4 * spx, (size_t)1 << 20), (size_t)1 << 28);
+        if ((rc = dev_alloc(ctx, &ctx->msColour, ctx->samples == 4 ? spx : 0))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->tlHead, spx)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)8)) ||
             (rc = dev_alloc(ctx, &ctx->tlHdr, ctx->outF32 ? 0 : px * 4)) || (rc = dev_alloc(ctx, &ctx->tlDepth, ctx->outDepth ? 0 : px))) return rc;
-        launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, px, ctx->numSMs, ctx->stream); ctx->launches++;
-        ctx->tlCap = cap; ctx->tlPx = px;
+        launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, spx, ctx->numSMs, ctx->stream); ctx->launches++;
+        ctx->tlCap = cap; ctx->tlPx = spx;
     }
     uint64_t nOpaque = 0;
     for (uint32_t i = 0; i < n; ++i) nOpaque += draws[i].nbIndices / 3;

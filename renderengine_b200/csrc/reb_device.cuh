@@ -112,6 +112,9 @@ struct PassConst {
     // tile rows of this rank's bands, in order ("virtual" rows the forward tile stage iterates): bandRows = bandH / TILE_H,
     // vTilesY = how many tile rows the rank owns; without a split bandRows = vTilesY = tilesY
     uint32_t bandRows, vTilesY;
+    // draw list re-ordered along a Morton curve (k_reorder.cu; NULL = submission order): source vertex streams in cache-slot order
+    // for K0, and K1's stream of {slot0, slot1, slot2, submission-order ID} records
+    const float4* posS; const float4* nrmS; const uint4* triStream;
 };
 
 // status[2] bits

@@ -60,8 +60,13 @@ void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* h
                       cudaStream_t st);
 void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,
                        uint32_t* counters, cudaStream_t st);
+// the same inside a 4x multisampled pass: merges the four per-sample lists of a pixel over the per-sample colours / depths
+void launch_tl_resolve_ms(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, const float4* msColour,
+                          float* msDepth, uint32_t* msTriId, cudaStream_t st);
+// k_reorder.cu: Morton order of a draw list's triangles + first-use order of its cache slots, once per draw list (synchronises st)
+cudaError_t reorder_draw_list(const PassConst& pc, const uint32_t* drawBounds, float4* posS, float4* nrmS, uint4* triStream, uint32_t* flat, cudaStream_t st);
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st);   // between the sample passes of a multisampled frame
 // Appendix B.15 resolve: per pixel, shade every distinct primitive of the 4 sample planes once at the pixel centre, average
-void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, cudaStream_t st);
+void launch_msaa_resolve(const PassConst& pc, const ShadeConst& sh, const float* msDepth, const uint32_t* msTriId, float4* msColour, cudaStream_t st);   // msColour != NULL: leave per-sample colours for the translucent list
 
 }  // namespace reb

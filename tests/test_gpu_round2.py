@@ -261,3 +261,83 @@ def test_render_twice_is_bit_identical(variant):
                 h.update(np.ascontiguousarray(ctx.readback(kind)).tobytes())
             digests.append(h.hexdigest())
     assert len(set(digests)) == 1, digests
+
+
+# ---- VERDICT "missing" 6: the translucent list inside the multisampled base pass; no per-pixel layer limit ------------------------------
+@pytest.mark.parametrize("variant", ["phong", "pbr_sky", "quads", "inside"])
+def test_parity_translucent_list_inside_the_multisampled_pass(variant):
+    """The reference draws opaque + translucent + skybox in ONE multisampled render pass (RenderScene.cpp:217-228,
+    Swapchain.cpp:110-123,212).  Appendix B.15 + B.16 together: coverage / depth test / blend per sample, one shading per pixel and
+    primitive at the pixel centre, skybox per sample, average resolve.  All four depth / ID planes bit-exact after the translucent
+    list, resolved colour <= 1 LSB, HDR PSNR >= 50 dB.  `quads`: large overlapping translucent quads (the large-triangle work
+    list of every sample pass); `inside`: camera inside the scene, the translucent ground plane is clipped (Appendix B.3)."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    if variant == "quads":
+        base = _quads_scene(40)
+        s = sc.to_translucent(base, which=[1], alpha=0.4)
+    else:
+        base = sc.make_scene("small")
+        if variant == "pbr_sky":
+            base = sc.to_pbr(base)
+            base["skybox"] = sc.make_skybox(32)
+        if variant == "inside":
+            base["view"] = sc.view_from(base, (0.3, 1.2, 0.4), (6.0, 0.0, 5.0))
+            ground = int(np.asarray(base["draws"], np.uint32)[:, 2].max() >> 4)   # the ground plane's material is the last one
+            s = sc.to_translucent(base, which=[ground, 0], alpha=0.45)
+        else:
+            s = sc.to_translucent(base, every=2, alpha=0.45)
+    assert len(s["translucent_draws"]) > 0
+    all_draws = np.concatenate([s["draws"], s["translucent_draws"]])
+    ref_shadow = orc.Oracle(dict(base)).render_shadow()
+    o = orc.Oracle(s)
+    ref = o.render_forward_msaa4(ref_shadow)
+    n_opaque = int(sum(int(d[1]) // 3 for d in s["draws"]))
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.set_sample_count(4)
+    for frame in range(2):                               # the second frame runs over re-armed list heads
+        ctx.render_shadow(all_draws)
+        ctx.render_forward(s["draws"], s["translucent_draws"])
+        ctx.sync()
+        assert ctx.counters()[0] == 0
+        tri = ctx.readback(capi.REB_MS_TRIID_U32); dep = ctx.readback(capi.REB_MS_DEPTH_F32)
+        for k in range(4):
+            assert np.array_equal(tri[k], ref["tri_id"][k]), f"frame {frame} sample {k}: {np.count_nonzero(tri[k] != ref['tri_id'][k])} triangle IDs differ"
+            assert np.array_equal(dep[k].view(np.uint32), ref["depth"][k].view(np.uint32)), f"frame {frame} sample {k}: depth not bit-exact"
+        assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"][0])
+        assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), ref["depth"][0].view(np.uint32))
+        d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32))
+        assert d8.max() <= 1, f"frame {frame}: sRGB8 differs by {d8.max()} LSB at {np.count_nonzero(d8 > 1)} channel samples"
+        assert _psnr(ctx.readback(capi.REB_COLOR_F32), ref["color_f32"]) >= 50.0
+    t = ref["tri_id"]
+    assert ((t != 0xFFFFFFFF) & (t >= n_opaque)).any(axis=0).mean() > 0.03      # translucent fragments are on screen
+    # and back to the 1-sample contract with the same context
+    ctx.set_sample_count(1)
+    one = o.render_forward(ref_shadow)
+    ctx.render_shadow(all_draws); ctx.render_forward(s["draws"], s["translucent_draws"]); ctx.sync()
+    assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), one["tri_id"])
+    assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - one["color_srgb8"].astype(np.int32)).max() <= 1
+
+
+def test_parity_more_translucent_layers_than_the_sorted_fast_path_holds():
+    """100 large translucent quads stacked over the frame: many pixels carry 20-40 fragments — beyond the TL_MAX_FRAGS = 16 a thread
+    sorts in place, so the replay selects straight from the list.  Nothing is dropped (counters[0] == 0) and the frame equals the
+    oracle's, which has no limit."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    base = _quads_scene(150)
+    s = sc.to_translucent(base, which=[0, 1], alpha=0.3)      # 100 of the 150 quads
+    ref_shadow = orc.Oracle(dict(base)).render_shadow()
+    ref = orc.Oracle(s).render_forward(ref_shadow)
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.render_shadow(np.concatenate([s["draws"], s["translucent_draws"]]))
+    ctx.render_forward(s["draws"], s["translucent_draws"])
+    ctx.sync()
+    assert ctx.counters()[0] == 0
+    assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"])
+    assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), ref["depth"].view(np.uint32))
+    d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32))
+    assert d8.max() <= 1, f"{np.count_nonzero(d8 > 1)} channel samples beyond 1 LSB (max {d8.max()})"
+    assert _psnr(ctx.readback(capi.REB_COLOR_F32), ref["color_f32"]) >= 50.0
