@@ -273,10 +273,18 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     K1Warp& ws = sm.w[warp];
     const uint32_t bl = pc.batchLog2, tpb = 1u << bl;
-    const uint32_t nBatches = (pc.nTris + tpb - 1u) >> bl;
+    // CULL (sort-first split): batches are numbered over the compacted list of the 256-triangle blocks this rank has to look at
+    // (k_cull_blocks), 2^(8 - bl) batches per block, instead of over all triangles
+    const uint32_t nBatches = CULL ? (__ldcg(pc.cullCounts) << (8u - bl)) : ((pc.nTris + tpb - 1u) >> bl);
     const uint32_t totalWarps = gridDim.x * K1_WARPS;
     const uint32_t laneTri = lane < tpb ? lane : 0xFFFFFFFFu;   // lanes past the batch see triangle index >= nTris (nothing to do)
-#define K1_TRI(b) (laneTri == 0xFFFFFFFFu ? 0xFFFFFFFFu : ((b) << bl) + laneTri)
+    auto batch_tri = [&](uint32_t b) -> uint32_t {
+        if (laneTri == 0xFFFFFFFFu) return 0xFFFFFFFFu;
+        if (!CULL) return (b << bl) + laneTri;
+        if (b >= nBatches) return 0xFFFFFFFFu;
+        return (__ldg(pc.triBlockList + (b >> (8u - bl))) << 8) + ((b & ((1u << (8u - bl)) - 1u)) << bl) + laneTri;
+    };
+#define K1_TRI(b) batch_tri(b)
 
     // static schedule: warp g takes batches g, g + totalWarps, ... (a shared work counter would serialise on one
     // L2 atomic unit: ~10 cycles per same-address atomic-with-return chip-wide, measured as the top stall)

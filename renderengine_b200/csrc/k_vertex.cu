@@ -30,6 +30,8 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     in.valid = slot < pc.cacheSize;
     in.node = 0; in.p = in.n = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!in.valid) return in;
+    // sort-first split: no visible 256-triangle block of this rank references this 256-slot block
+    if (CULL && __ldg(pc.slotBlockVisible + (slot >> 8)) == 0u) { in.valid = false; return in; }
     // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
     const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, slot);
     uint32_t v = slot;
@@ -85,6 +87,23 @@ __device__ __forceinline__ void k0_prologue(const PassConst& pc) {
 }
 // Fused clear of the shadow map to depth 1.0 (ShadowSystem.cpp:111-127): every CTA streams one contiguous slice.
 __device__ __forceinline__ void k0_clear_shadow(const PassConst& pc) {
+    if (pc.nRanks > 1 && (pc.W & 3u) == 0u) {
+        // row slabs (reb_set_shadow_partition): only this rank's rows are rasterised, and the other rows are overwritten by the
+        // all-gather that completes the map — clearing them on every rank was 7/8 of a 16.8-MB store stream at N = 8
+        const uint32_t perBand = pc.bandH * (pc.W >> 2), period = pc.bandH * pc.nRanks;
+        const uint32_t nBands = (pc.H + period - 1u) / period;                  // bands of this rank (the last may be cut by H)
+        const size_t n4 = (size_t)nBands * perBand;
+        const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
+        const size_t lo = per * blockIdx.x, hi = lo + per < n4 ? lo + per : n4;
+        uint4* dst = reinterpret_cast<uint4*>(pc.depthBits);
+        const uint4 one = make_uint4(0x3F800000u, 0x3F800000u, 0x3F800000u, 0x3F800000u);
+        for (size_t i = lo + threadIdx.x; i < hi; i += 256u) {
+            const uint32_t vb = (uint32_t)(i / perBand), r = (uint32_t)(i - (size_t)vb * perBand);
+            const uint32_t y = (vb * pc.nRanks + pc.rank) * pc.bandH + r / (pc.W >> 2);
+            if (y < pc.H) dst[(size_t)y * (pc.W >> 2) + r % (pc.W >> 2)] = one;
+        }
+        return;
+    }
     const size_t nPix = (size_t)pc.W * pc.H, n4 = nPix / 4u;
     if (blockIdx.x == 0 && threadIdx.x < (nPix & 3u)) pc.depthBits[4u * n4 + threadIdx.x] = 0x3F800000u;
     const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
@@ -232,7 +251,11 @@ __device__ __forceinline__ void load_node_transform(const PassConst& pc, uint32_
 }
 // Once per pass and frame, ahead of K0: per-draw visibility (K0 skips the vertices of the other draws) ...
 template <bool SHADOW>
-__global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ visible) {
+__global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ visible,
+                                                    uint32_t* __restrict__ slotBlockVisible, uint32_t nSlotBlocks, uint32_t* __restrict__ cullCounts) {
+    // re-arm what k_cull_blocks fills: the slot-block marks and the length of the visible-block list
+    for (uint32_t i = blockIdx.x * 128u + threadIdx.x; i < nSlotBlocks; i += gridDim.x * 128u) slotBlockVisible[i] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) cullCounts[0] = 0u;
     const uint32_t d = blockIdx.x * 128u + threadIdx.x;
     if (d >= pc.nDraws) return;
     const uint32_t* b = bounds + 6 * (size_t)d;
@@ -244,19 +267,83 @@ __global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ Pass
 }
 // ... and per 256-triangle block (K1 skips the other blocks: meshes come out of subdivision / the importer in spatially coherent
 // index order, so a block is a small patch).  blockBox[8 tb]: min xyz, draw (0xFFFFFFFF: the block spans draws), max xyz, pad.
+// A block that stays is appended to the compacted list K1 walks (one atomicAdd per warp; list order varies from frame to frame,
+// which no result depends on: every resolve is a minimum) and marks the 256-slot blocks of the post-transform cache its
+// triangles reference (table built once per draw list by k_block_slot_refs) for K0.
 template <bool SHADOW>
 __global__ void __launch_bounds__(128) k_cull_blocks(const __grid_constant__ PassConst pc, const float4* __restrict__ blockBox, const uint32_t* __restrict__ drawVisible,
-                                                     uint32_t nBlocks, uint32_t* __restrict__ visible) {
+                                                     uint32_t nBlocks, uint32_t* __restrict__ visible, const uint32_t* __restrict__ refs,
+                                                     uint32_t* __restrict__ slotBlockVisible, uint32_t* __restrict__ list, uint32_t* __restrict__ cullCounts) {
     const uint32_t tb = blockIdx.x * 128u + threadIdx.x;
-    if (tb >= nBlocks) return;
-    const float4 lo = blockBox[2 * (size_t)tb], hi = blockBox[2 * (size_t)tb + 1];
-    const uint32_t d = __float_as_uint(lo.w);
-    if (d == 0xFFFFFFFFu) { visible[tb] = BLOCK_MIXED; return; }   // the block spans draws: K1 asks per triangle whether its draw is visible
-    if (drawVisible[d] == 0u) { visible[tb] = 0u; return; }
-    const float mn[3] = {lo.x, lo.y, lo.z}, mx[3] = {hi.x, hi.y, hi.z};
-    float T[16];
-    load_node_transform(pc, pc.draws[d].node, T);
-    visible[tb] = box_touches_rank<SHADOW>(pc, T, mn, mx);
+    uint32_t vis = 0u;
+    if (tb < nBlocks) {
+        const float4 lo = blockBox[2 * (size_t)tb], hi = blockBox[2 * (size_t)tb + 1];
+        const uint32_t d = __float_as_uint(lo.w);
+        if (d == 0xFFFFFFFFu) vis = BLOCK_MIXED;   // the block spans draws: K1 asks per triangle whether its draw is visible
+        else if (drawVisible[d] != 0u) {
+            const float mn[3] = {lo.x, lo.y, lo.z}, mx[3] = {hi.x, hi.y, hi.z};
+            float T[16];
+            load_node_transform(pc, pc.draws[d].node, T);
+            vis = box_touches_rank<SHADOW>(pc, T, mn, mx);
+        }
+        visible[tb] = vis;
+    }
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, vis != 0u);
+    if (!m) return;
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(cullCounts, (uint32_t)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+    if (vis == 0u) return;
+    list[base + __popc(m & ((1u << lane) - 1u))] = tb;
+    const uint32_t* r = refs + (size_t)tb * BLOCK_REFS;
+    const uint32_t n = r[0];
+    if (n == 0xFFFFFFFFu) { for (uint32_t b = r[1]; b <= r[2]; ++b) slotBlockVisible[b] = 1u; }
+    else for (uint32_t i = 0; i < n; ++i) slotBlockVisible[r[1 + i]] = 1u;
+}
+// Once per draw list: the distinct 256-slot blocks the triangles of every 256-triangle block reference (with slots in first-use
+// order of a Morton-ordered stream: its own run of new slots plus a few runs shared with neighbouring patches).  One CTA per
+// block, one triangle per thread, a 64-entry shared hash set; more than BLOCK_REFS - 1 distinct blocks: the [min, max] range.
+__global__ void __launch_bounds__(256) k_block_slot_refs(const __grid_constant__ PassConst pc, uint32_t* __restrict__ refs) {
+    __shared__ uint32_t tab[64];
+    __shared__ uint32_t cnt, lo, hi, full;
+    const uint32_t tb = blockIdx.x, tri = tb * 256u + threadIdx.x;
+    if (threadIdx.x < 64) tab[threadIdx.x] = 0xFFFFFFFFu;
+    if (threadIdx.x == 0) { cnt = 0u; lo = 0xFFFFFFFFu; hi = 0u; full = 0u; }
+    __syncthreads();
+    if (tri < pc.nTris) {
+        uint32_t sl[3];
+        if (pc.triStream) { const uint4 r = __ldg(pc.triStream + tri); sl[0] = r.x; sl[1] = r.y; sl[2] = r.z; }
+        else if (pc.deindexed) { sl[0] = 3u * tri; sl[1] = 3u * tri + 1u; sl[2] = 3u * tri + 2u; }
+        else { const uint32_t* f = pc.flatSlots + 3ull * tri; sl[0] = f[0]; sl[1] = f[1]; sl[2] = f[2]; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t v = sl[k] >> 8;
+            if (k > 0 && v == (sl[k - 1] >> 8)) continue;
+            atomicMin(&lo, v); atomicMax(&hi, v);
+            uint32_t h = (v * 2654435761u) >> 26;
+            for (int probe = 0; probe < 64; ++probe, h = (h + 1u) & 63u) {
+                const uint32_t old = atomicCAS(&tab[h], 0xFFFFFFFFu, v);
+                if (old == 0xFFFFFFFFu || old == v) break;
+                if (probe == 63) full = 1u;
+            }
+        }
+    }
+    __syncthreads();
+    uint32_t* r = refs + (size_t)tb * BLOCK_REFS;
+    if (threadIdx.x < 64 && tab[threadIdx.x] != 0xFFFFFFFFu) {
+        const uint32_t i = atomicAdd(&cnt, 1u);
+        if (i < (uint32_t)BLOCK_REFS - 1u) r[1 + i] = tab[threadIdx.x];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (full || cnt > (uint32_t)BLOCK_REFS - 1u) { r[0] = 0xFFFFFFFFu; r[1] = lo; r[2] = hi; }
+        else r[0] = cnt;
+    }
+}
+void launch_block_slot_refs(const PassConst& pc, uint32_t* refs, cudaStream_t st) {
+    if (pc.nTris == 0) return;
+    k_block_slot_refs<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, refs);
 }
 // Object-space box of every 256-triangle block, once per draw list: one CTA per block, one triangle per thread.
 __global__ void __launch_bounds__(256) k_block_bounds(const __grid_constant__ PassConst pc, float4* __restrict__ blockBox) {
@@ -296,15 +383,18 @@ void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st)
     if (pc.nTris == 0) return;
     k_block_bounds<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, blockBox);
 }
-void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, cudaStream_t st) {
+void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, const uint32_t* refs,
+                        uint32_t* slotBlockVisible, uint32_t* list, uint32_t* cullCounts, cudaStream_t st) {
     if (nBlocks == 0) return;
-    if (shadow) k_cull_blocks<true><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible);
-    else k_cull_blocks<false><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible);
+    if (shadow) k_cull_blocks<true><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible, refs, slotBlockVisible, list, cullCounts);
+    else k_cull_blocks<false><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible, refs, slotBlockVisible, list, cullCounts);
 }
-void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, cudaStream_t st) {
+void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, uint32_t* slotBlockVisible, uint32_t nSlotBlocks, uint32_t* cullCounts,
+                       cudaStream_t st) {
     if (pc.nDraws == 0) return;
-    if (shadow) k_cull_draws<true><<<(pc.nDraws + 127u) / 128u, 128, 0, st>>>(pc, bounds, visible);
-    else k_cull_draws<false><<<(pc.nDraws + 127u) / 128u, 128, 0, st>>>(pc, bounds, visible);
+    const uint32_t grid = std::max((pc.nDraws + 127u) / 128u, std::min((nSlotBlocks + 127u) / 128u, 64u));
+    if (shadow) k_cull_draws<true><<<grid, 128, 0, st>>>(pc, bounds, visible, slotBlockVisible, nSlotBlocks, cullCounts);
+    else k_cull_draws<false><<<grid, 128, 0, st>>>(pc, bounds, visible, slotBlockVisible, nSlotBlocks, cullCounts);
 }
 
 void launch_vertex_both(const PassConst& ps, const PassConst& pf, cudaStream_t st) {

@@ -28,7 +28,9 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaq
     uint32_t* flatSlots = nullptr; uint32_t* triMaterial = nullptr; size_t flatCap = 0;   // 3 cache slots + the material handle per triangle, submission order (indexed mode); flatCap in triangles
     uint32_t cacheSize = 0, deindexed = 0;
     uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;
-    float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
+    float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;
+    uint32_t* blockRefs = nullptr; uint32_t* triBlockList = nullptr; uint32_t* cullCounts = nullptr;   // [triBlocks * BLOCK_REFS], [triBlocks], [4]
+    uint32_t* slotBlockVisible = nullptr; uint32_t slotBlocks = 0, slotBlockCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
     // re-ordered list (k_reorder.cu): source streams in slot order, K1's {slots, submission ID} stream
     float4* posS = nullptr; float4* nrmS = nullptr; size_t streamCap = 0; uint4* triStream = nullptr; size_t triStreamCap = 0; bool reordered = false;
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
@@ -305,8 +307,16 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
         CU(cudaStreamSynchronize(ctx->stream));   // init is a stack-lifetime staging buffer
         if (ps.triBlocks > ps.blockCullCap) {
             int rc;
-            if ((rc = dev_alloc(ctx, &ps.blockBox, (size_t)ps.triBlocks * 2)) || (rc = dev_alloc(ctx, &ps.blockVisible, (size_t)ps.triBlocks))) return rc;
+            if ((rc = dev_alloc(ctx, &ps.blockBox, (size_t)ps.triBlocks * 2)) || (rc = dev_alloc(ctx, &ps.blockVisible, (size_t)ps.triBlocks)) ||
+                (rc = dev_alloc(ctx, &ps.blockRefs, (size_t)ps.triBlocks * BLOCK_REFS)) || (rc = dev_alloc(ctx, &ps.triBlockList, (size_t)ps.triBlocks)) ||
+                (rc = dev_alloc(ctx, &ps.cullCounts, (size_t)4))) return rc;
             ps.blockCullCap = ps.triBlocks;
+        }
+        ps.slotBlocks = (uint32_t)((slots + 255) / 256);
+        if (ps.slotBlocks > ps.slotBlockCap) {
+            int rc;
+            if ((rc = dev_alloc(ctx, &ps.slotBlockVisible, (size_t)ps.slotBlocks))) return rc;
+            ps.slotBlockCap = ps.slotBlocks;
         }
     }
     ps.reordered = false;
@@ -343,7 +353,8 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
     if (n) {   // per-block bounds for the sort-first culling: blocks of K1's stream, i.e. after a re-ordering
         PassConst pcb;
         fill_pass(ctx, kind, pcb);
-        launch_block_bounds(pcb, ps.blockBox, ctx->stream); ctx->launches++;
+        launch_block_bounds(pcb, ps.blockBox, ctx->stream);
+        launch_block_slot_refs(pcb, ps.blockRefs, ctx->stream); ctx->launches += 2;
         CU(cudaStreamSynchronize(ctx->stream));
     }
     ps.draws.assign(draws, draws + n);
@@ -379,6 +390,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
     pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
     pc.blockVisible = pc.drawVisible ? ps.blockVisible : nullptr;
+    if (pc.drawVisible) { pc.triBlockList = ps.triBlockList; pc.cullCounts = ps.cullCounts; pc.slotBlockVisible = ps.slotBlockVisible; }
 }
 
 // Everything a pass needs before its kernels can be enqueued: queue capacities, texture table, kernel parameters.
@@ -445,8 +457,9 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     }
     mark(1);
     if (ps.nTris && pc.drawVisible) {
-        launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ctx->stream);
-        launch_cull_blocks(pc, kind == 0, ps.blockBox, ps.drawVisible, ps.triBlocks, ps.blockVisible, ctx->stream); ctx->launches += 2;
+        launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ps.slotBlockVisible, ps.slotBlocks, ps.cullCounts, ctx->stream);
+        launch_cull_blocks(pc, kind == 0, ps.blockBox, ps.drawVisible, ps.triBlocks, ps.blockVisible, ps.blockRefs, ps.slotBlockVisible, ps.triBlockList, ps.cullCounts, ctx->stream);
+        ctx->launches += 2;
     }
     if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
     mark(2);
@@ -567,7 +580,7 @@ int run_translucent(reb_ctx* ctx) {
     int rc;
     if ((rc = prepare_pass(ctx, 2, pc))) return rc;
     pc.tilesX = pc.tilesY = 0;                       // K0's prologue has no tile counters to re-arm for this list
-    pc.drawVisible = nullptr; pc.blockVisible = nullptr;
+    pc.drawVisible = nullptr; pc.blockVisible = nullptr; pc.triBlockList = nullptr; pc.cullCounts = nullptr; pc.slotBlockVisible = nullptr;
     pc.status = ctx->dStatus + 2 * STATUS_WORDS;
     pc.hostStatus = nullptr;
     ShadeConst sh = ctx->tlShade;

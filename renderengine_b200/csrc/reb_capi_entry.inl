@@ -67,7 +67,9 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
                     ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge, ctx->msColour,
                     ctx->pass[0].posS, ctx->pass[1].posS, ctx->pass[2].posS, ctx->pass[0].nrmS, ctx->pass[1].nrmS, ctx->pass[2].nrmS,
-                    ctx->pass[0].triStream, ctx->pass[1].triStream, ctx->pass[2].triStream};
+                    ctx->pass[0].triStream, ctx->pass[1].triStream, ctx->pass[2].triStream,
+                    ctx->pass[0].blockRefs, ctx->pass[1].blockRefs, ctx->pass[2].blockRefs, ctx->pass[0].triBlockList, ctx->pass[1].triBlockList, ctx->pass[2].triBlockList,
+                    ctx->pass[0].cullCounts, ctx->pass[1].cullCounts, ctx->pass[2].cullCounts, ctx->pass[0].slotBlockVisible, ctx->pass[1].slotBlockVisible, ctx->pass[2].slotBlockVisible};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);
     if (ctx->dTextures) cudaFree(ctx->dTextures);

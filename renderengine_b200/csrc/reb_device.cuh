@@ -115,7 +115,12 @@ struct PassConst {
     // draw list re-ordered along a Morton curve (k_reorder.cu; NULL = submission order): source vertex streams in cache-slot order
     // for K0, and K1's stream of {slot0, slot1, slot2, submission-order ID} records
     const float4* posS; const float4* nrmS; const uint4* triStream;
+    // sort-first split, per pass and frame (k_cull_blocks): the 256-triangle blocks this rank has to look at, compacted (their
+    // number is cullCounts[0]; K1 walks this list instead of all blocks), and which 256-slot blocks of the post-transform cache
+    // those blocks reference (K0 skips the others).  NULL without culling.
+    const uint32_t* triBlockList; const uint32_t* cullCounts; const uint32_t* slotBlockVisible;
 };
+constexpr int BLOCK_REFS = 16;   // words per 256-triangle block in the slot-block reference table: [0] count (0xFFFFFFFF: a range [1]..[2]), then block ids
 
 // status[2] bits
 constexpr uint32_t OVF_LARGE = 1u, OVF_LIST = 2u;
