@@ -812,7 +812,7 @@ def main():
     ap.add_argument("--mode", default="auto", choices=["auto", "frame", "views", "tiles", "replicas"],
                     help="auto: N = 1 -> the C2 frame; N > 1 -> the C5 view batch as headline + the C4 sort-first record")
     ap.add_argument("--views-per-rank", type=int, default=64, help="C5: 512 views over 8 GPUs")
-    ap.add_argument("--bands-per-rank", type=int, default=2,
+    ap.add_argument("--bands-per-rank", type=int, default=3,
                     help="sort-first: row bands per rank, interleaved (1 = one contiguous band: least geometry per rank after culling but unbalanced; 0 = 64-row bands)")
     ap.add_argument("--sort-first-frames", type=int, default=10)
     ap.add_argument("--shading", default="phong", choices=["phong", "pbr"],
