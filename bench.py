@@ -467,16 +467,16 @@ def run_single(args, torch, dist, local_rank):
     counters = ctx.counters()
 
     # ---- end to end through the C ABI with host buffers (wall clock, includes D2H of the frame) -------
-    # every frame: host view / light blocks in, the finished sRGB8 frame out to pinned host memory.  The target is a two-image swapchain,
+    # every frame: host view / light blocks in, the finished sRGB8 frame out to pinned host memory.  The target is a three-image swapchain,
     # so frame i's device->host copy (copy stream) overlaps frame i+1's rendering; all inside the timed region.
-    pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(3)]
     for p in pinned:
         p.zero_()                                          # first touch on the GPU-local NUMA node
     view_host = np.array(scene["view"])
     n_e2e = max(10, min(args.steps, 100))
     with torch.cuda.stream(st):
         for i in range(4):
-            rig.frame(); ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i & 1].data_ptr())
+            rig.frame(); ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i % 3].data_ptr())
         ctx.sync()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -485,7 +485,7 @@ def run_single(args, torch, dist, local_rank):
             if S:
                 ctx.shadow_set_transform(scene["shadow_view"], scene["shadow_proj"])
             rig.frame()
-            ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i & 1].data_ptr())
+            ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i % 3].data_ptr())
         ctx.sync()
         torch.cuda.synchronize()
         e2e_ms = (time.perf_counter() - t0) * 1e3 / n_e2e
@@ -509,7 +509,7 @@ def run_single(args, torch, dist, local_rank):
                 "d2h_bytes_per_step": W * H * 4, "d2h_gbs_achieved": d2h_gbs,
                 "host_ceiling_gbs": ceiling["aggregate_gbs"], "host_ceiling": ceiling, "e2e_over_ceiling": d2h_gbs / ceiling["aggregate_gbs"], "numa": numa,
                 "bound": "host copy" if d2h_gbs > 0.8 * ceiling["aggregate_gbs"] else "render",
-                "note": "wall clock through reb_set_view/reb_render_*/reb_readback_async + final reb_sync with host buffers (pinned, 2-image swapchain: the copy of frame i overlaps frame i+1); geometry is static and resident as in the reference frame loop; host_ceiling_gbs = copy-only probe of the same 8.3-MB frames, nothing rendered"},
+                "note": "wall clock through reb_set_view/reb_render_*/reb_readback_async + final reb_sync with host buffers (pinned, 3-image swapchain: the copy of frame i overlaps the rendering of frames i+1 and i+2); geometry is static and resident as in the reference frame loop; host_ceiling_gbs = copy-only probe of the same 8.3-MB frames, nothing rendered"},
         "gpu_launches": int(launches), "clocks": clocks,
         "frame_us": {"median": 1e3 * float(np.median(per_frame)), "p95": 1e3 * float(np.percentile(per_frame, 95)), "rank": 0},
         "counters": {"needs_clip": int(counters[0]), "binned_triangles": int(counters[1]), "tile_list_entries": int(counters[2]), "regrows": int(counters[3])},
@@ -650,7 +650,7 @@ def run_views(args, torch, dist, rank, world, local_rank, flush, peak, peak_src)
 
     # ---- end to end: every view's finished frame to pinned host memory, host view blocks in -----------------------------------------
     numa = pin_to_gpu_numa(local_rank)
-    pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(3)]
     for p in pinned:
         p.zero_()
     n_e2e = max(2, min(args.steps, 10))
@@ -667,7 +667,7 @@ def run_views(args, torch, dist, rank, world, local_rank, flush, peak, peak_src)
         for i, v in enumerate(views):
             ctx.set_view(v)
             ctx.render_forward(rig.draws, rig.tl)
-            ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i & 1].data_ptr())
+            ctx.readback_async_into(capi.REB_COLOR_SRGB8, pinned[i % 3].data_ptr())
     with torch.cuda.stream(st):
         e2e_step(); ctx.sync(); barrier()
         t0 = time.perf_counter()
@@ -703,7 +703,7 @@ def run_views(args, torch, dist, rank, world, local_rank, flush, peak, peak_src)
         "e2e": {"value": world * nv * T / (e2e_ms * 1e3), "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": nv * 160 + 128 + 16 * len(rig.shadow_draws) + nv * 16 * len(rig.draws),
                 "d2h_bytes_per_step": nv * W * H * 4, "d2h_gbs_achieved": d2h_gbs, "host_ceiling_gbs": ceiling["aggregate_gbs"], "host_ceiling": ceiling,
                 "e2e_over_ceiling": d2h_gbs / ceiling["aggregate_gbs"], "numa": numa,
-                "note": "per rank and step: host view block in + finished sRGB8 frame out to pinned host memory for EVERY view (2-image swapchain, copy stream); bytes are per rank; host_ceiling_gbs = copy-only probe, all ranks at once, nothing rendered"},
+                "note": "per rank and step: host view block in + finished sRGB8 frame out to pinned host memory for EVERY view (3-image swapchain, copy stream); bytes are per rank; host_ceiling_gbs = copy-only probe, all ranks at once, nothing rendered"},
         "gpu_launches": int(launches), "clocks": clocks,
         "frame_us": {"median": 1e3 * float(np.median(per_step)) / nv, "p95": 1e3 * float(np.percentile(per_step, 95)) / nv, "rank": 0, "per": "view"},
     }

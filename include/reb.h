@@ -145,8 +145,8 @@ int reb_get_output(reb_ctx* ctx, reb_output_kind kind, void** devPtr, uint64_t* 
 int reb_readback(reb_ctx* ctx, reb_output_kind kind, void* host);
 int reb_sync(reb_ctx* ctx);
 /* Present-style readback: enqueue the device->host copy of an output and return at once; the data is valid after the
- * next reb_sync.  REB_COLOR_SRGB8 is a two-image swapchain (Swapchain.cpp:200-237): its copy runs on a copy stream
- * while the next frame renders into the other image.  host should be pinned memory for the copy to overlap. */
+ * next reb_sync.  REB_COLOR_SRGB8 is a three-image swapchain (Swapchain.cpp:55-59,200-237): its copy runs on a copy stream
+ * while the next frames render into the other images.  host should be pinned memory for the copy to overlap. */
 int reb_readback_async(reb_ctx* ctx, reb_output_kind kind, void* host);
 
 /* multi-GPU helpers */

@@ -16,6 +16,11 @@ using namespace reb;
 namespace {
 
 std::string g_createError;
+// Images of the sRGB8 "swapchain": the reference asks for minImageCount + 1 (Swapchain.cpp:55-59), three on common drivers, so a
+// finished frame is always waiting when the copy engine becomes free.  (Measured against two images on C2: end to end 163.3 vs
+// 164.9 us / frame, i.e. no difference — the copy itself runs at 0.90 of the copy-only ceiling while the kernels of the next frames
+// compete for HBM; the third image is kept for the reference's frames-in-flight behaviour, not for speed.)
+constexpr int SWAP_IMAGES = 3;
 
 struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaque), 2 = the translucent list of the base pass
     std::vector<reb_draw> draws; // last submitted list (host copy, for change detection and replay)
@@ -63,10 +68,10 @@ struct reb_ctx {
     uint32_t S = 0; float* shadowMap = nullptr; float sview[16], sproj[16], SPV[16]; bool haveShadowXf = false, shadowValid = false;
     // outputs + visibility buffer
     uint8_t* outSRGB8 = nullptr; float* outF32 = nullptr; float* outDepth = nullptr; uint32_t* outTriId = nullptr;
-    // two-image "swapchain" for the sRGB8 target (the reference presents from >= 2 swapchain images, Swapchain.cpp:200-237):
-    // reb_readback_async copies image i on a copy stream while the next frame renders into image i ^ 1
-    uint8_t* swap[2] = {nullptr, nullptr}; int swapCur = 0; bool copyInFlight[2] = {false, false};
-    cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[2] = {nullptr, nullptr};
+    // SWAP_IMAGES-image "swapchain" for the sRGB8 target (Swapchain.cpp:55-59,200-237):
+    // reb_readback_async copies image i on a copy stream while the next frames render into the other images
+    uint8_t* swap[SWAP_IMAGES] = {}; int swapCur = 0; bool copyInFlight[SWAP_IMAGES] = {};
+    cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr; cudaEvent_t evCopied[SWAP_IMAGES] = {};
     void* asyncHost = nullptr; bool asyncOutstanding = false;   // last reb_readback_async target (re-copied if the frame is replayed)
     unsigned long long* vis = nullptr;
     // translucent list (Appendix B.16, k_translucent.cu): per-pixel list heads, node pool, device counters {nodes, dropped, needs-clip};
@@ -154,7 +159,7 @@ int alloc_targets(reb_ctx* ctx) {
     if ((rc = dev_alloc(ctx, &ctx->msDepth, ctx->samples > 1 ? px * ctx->samples : 0))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->msTriId, ctx->samples > 1 ? px * ctx->samples : 0))) return rc;
     if (ctx->outputs & REB_OUT_COLOR_SRGB8) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < SWAP_IMAGES; ++i) {
             if ((rc = dev_alloc(ctx, &ctx->swap[i], px * 4))) return rc;
             launch_fill_u32(reinterpret_cast<uint32_t*>(ctx->swap[i]), 0xFF000000u, px, ctx->numSMs, ctx->stream); ctx->launches++;
         }
@@ -465,8 +470,8 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     mark(2);
     ShadeConst sh;
     if (kind == 1) {
-        if (ctx->swap[0]) {   // acquire the other swapchain image; wait for an async readback still draining it
-            ctx->swapCur ^= 1; ctx->outSRGB8 = ctx->swap[ctx->swapCur];
+        if (ctx->swap[0]) {   // acquire the next swapchain image; wait for an async readback still draining it
+            ctx->swapCur = (ctx->swapCur + 1) % SWAP_IMAGES; ctx->outSRGB8 = ctx->swap[ctx->swapCur];
             if (ctx->copyInFlight[ctx->swapCur]) { CU(cudaStreamWaitEvent(ctx->stream, ctx->evCopied[ctx->swapCur], 0)); ctx->copyInFlight[ctx->swapCur] = false; }
         }
         std::memset(&sh, 0, sizeof sh);

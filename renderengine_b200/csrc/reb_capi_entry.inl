@@ -57,7 +57,7 @@ int reb_destroy(reb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void* ptrs[] = {ctx->pos4, ctx->nrm4, ctx->indices, ctx->transforms, ctx->nmats, ctx->materials, ctx->lights, ctx->shadowMap,
-                    ctx->swap[0], ctx->swap[1], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileHead[0], ctx->tileHead[1],
+                    ctx->swap[0], ctx->swap[1], ctx->swap[2], ctx->outF32, ctx->outDepth, ctx->outTriId, ctx->vis, ctx->large, ctx->clipQueue, ctx->tileHead[0], ctx->tileHead[1],
                     ctx->tileList, ctx->dStatus, ctx->huge, ctx->pass[0].dDraws, ctx->pass[1].dDraws,
                     ctx->pass[0].vtxA, ctx->pass[1].vtxA, ctx->pass[0].vtxBC, ctx->pass[1].vtxBC,
                     ctx->pass[0].blockDraw, ctx->pass[1].blockDraw, ctx->pass[0].flatSlots, ctx->pass[1].flatSlots,
@@ -80,7 +80,7 @@ int reb_destroy(reb_ctx* ctx) {
     if (ctx->hStatus) cudaFreeHost(ctx->hStatus);
     if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
     if (ctx->evRendered) cudaEventDestroy(ctx->evRendered);
-    for (int i = 0; i < 2; ++i) if (ctx->evCopied[i]) cudaEventDestroy(ctx->evCopied[i]);
+    for (int i = 0; i < SWAP_IMAGES; ++i) if (ctx->evCopied[i]) cudaEventDestroy(ctx->evCopied[i]);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return REB_OK;
@@ -355,7 +355,7 @@ int reb_sync(reb_ctx* ctx) {
     { int rc = flush_deferred(ctx); if (rc) return rc; }
     CU(cudaStreamSynchronize(ctx->stream));
     if (ctx->copyStream) CU(cudaStreamSynchronize(ctx->copyStream));
-    ctx->copyInFlight[0] = ctx->copyInFlight[1] = false;
+    for (bool& f : ctx->copyInFlight) f = false;
     return check_and_recover(ctx);
 }
 
@@ -414,7 +414,7 @@ int reb_readback_async(reb_ctx* ctx, reb_output_kind kind, void* host) {
     if (!ctx->copyStream) {
         CU(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&ctx->evRendered, cudaEventDisableTiming));
-        for (int i = 0; i < 2; ++i) CU(cudaEventCreateWithFlags(&ctx->evCopied[i], cudaEventDisableTiming));
+        for (int i = 0; i < SWAP_IMAGES; ++i) CU(cudaEventCreateWithFlags(&ctx->evCopied[i], cudaEventDisableTiming));
     }
     CU(cudaEventRecord(ctx->evRendered, ctx->stream));
     CU(cudaStreamWaitEvent(ctx->copyStream, ctx->evRendered, 0));
@@ -432,7 +432,7 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
     { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     if (ctx->copyStream) CU(cudaStreamSynchronize(ctx->copyStream));   // an async readback may still be draining a swapchain image
-    ctx->copyInFlight[0] = ctx->copyInFlight[1] = false; ctx->asyncOutstanding = false;
+    for (bool& f : ctx->copyInFlight) f = false; ctx->asyncOutstanding = false;
     ctx->rank = rank; ctx->nRanks = nRanks; ctx->bandH = bandH;
     return alloc_targets(ctx);   // re-clear: pixels outside this rank's bands keep the clear values
 }

@@ -271,7 +271,7 @@ def test_fused_and_unfused_vertex_stage_agree(monkeypatch):
 
 
 def test_async_readback_swapchain_matches_blocking_readback():
-    """reb_readback_async: frame i's copy (copy stream, swapchain image i & 1) overlaps frame i + 1; every host image must
+    """reb_readback_async: frame i's copy (copy stream, swapchain image i % 3) overlaps the frames after it; every host image must
     equal the blocking readback of the same view."""
     import torch
     from renderengine_b200 import capi, scene as sc
