@@ -368,6 +368,221 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
 #undef K1_TRI
 }
 
+// ---------------------------------------------------------------------------------------------------------------------------------
+// K1 for the 4x multisampled base pass (Appendix B.15) in ONE pass over the triangles.  Sampling at (x + sx, y + sy) equals sampling
+// the pixel centre of the triangle moved by s = (128 - 256 sx, 128 - 256 sy) sub-pixel units, and an edge function of the moved
+// triangle is the unmoved one plus the constant -(A sx' + B sy'): so gather, clip flags, facing, edge equations, 1 / |A2| and the
+// ring record are computed once per triangle and the row stage tests every pixel centre of the UNION bbox against four sets of
+// constants; samples go to the visibility plane of their sample index.  Triangles beyond the small class are appended to the
+// queue set of every sample with that sample's moved vertices, so K2 / the tile stage of each sample pass run unchanged.
+// (The first version ran the whole K1 once per sample: 4 x 26 us on C2.)
+// ---------------------------------------------------------------------------------------------------------------------------------
+__constant__ int32_t c_msShift[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};   // Vulkan standard 4-sample locations as vertex shifts
+constexpr int32_t MS_PAD = 96;          // largest |shift|: the union bbox is the bbox of the unmoved triangle grown by this much
+constexpr int MS_PIXQ = 1024;           // sample ring (32-bit entries): < 32 pending + 32 * 16 new per sample
+// the union bbox of a 1-3 px triangle is 3 x 3 or 4 x 4 centres: the one-entry class takes the full 4 x 4 here
+__device__ __forceinline__ bool k1ms_is_tiny(uint32_t w, uint32_t h) { return w <= 4u && h <= 4u; }
+
+__device__ __forceinline__ void k1ms_classify(const PassConst& pc, bool valid, const uint4 q[3], K1Tri& t) {
+    t.isSmall = t.isLarge = t.needsClip = false;
+    t.A2 = 0; t.x0 = t.y0 = 0; t.x1 = t.y1 = -1;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) t.a[k] = {(int32_t)q[k].x, (int32_t)q[k].y, __uint_as_float(q[k].z), q[k].w};
+    if (!valid) return;
+    const uint32_t f0 = t.a[0].flags, f1 = t.a[1].flags, f2 = t.a[2].flags;
+    if ((f0 & f1 & f2 & VF_PLANES) != 0u) return;
+    if (((f0 | f1 | f2) & VF_NEEDS_CLIP) != 0u) { t.needsClip = true; return; }
+    const VtxA &a0 = t.a[0], &a1 = t.a[1], &a2 = t.a[2];
+    t.A2 = (long long)(a1.X - a0.X) * (long long)(a2.Y - a0.Y) - (long long)(a2.X - a0.X) * (long long)(a1.Y - a0.Y);   // translation-invariant
+    if (t.A2 >= 0) return;
+    const int32_t minX = min(a0.X, min(a1.X, a2.X)) - MS_PAD, maxX = max(a0.X, max(a1.X, a2.X)) + MS_PAD;
+    const int32_t minY = min(a0.Y, min(a1.Y, a2.Y)) - MS_PAD, maxY = max(a0.Y, max(a1.Y, a2.Y)) + MS_PAD;
+    t.x0 = max((minX + 127) >> 8, 0); t.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+    t.y0 = max((minY + 127) >> 8, 0); t.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+    if (t.x0 > t.x1 || t.y0 > t.y1) return;                     // no pixel centre under any sample's bbox
+    t.isSmall = (maxX - minX) <= SMALL_LIMIT * 256 && (maxY - minY) <= SMALL_LIMIT * 256;   // the grown spans: ring and 32-bit bounds as in K1
+    t.isLarge = !t.isSmall;
+}
+
+// the triangle as sample k's pass sees it: moved vertices, that pass's own bbox (k1_classify's), large by construction
+__device__ __forceinline__ bool k1ms_moved(const PassConst& pc, const K1Tri& t, int k, K1Tri& m) {
+    m = t;
+#pragma unroll
+    for (int v = 0; v < 3; ++v) { m.a[v].X += c_msShift[k][0]; m.a[v].Y += c_msShift[k][1]; }
+    const int32_t minX = min(m.a[0].X, min(m.a[1].X, m.a[2].X)), maxX = max(m.a[0].X, max(m.a[1].X, m.a[2].X));
+    const int32_t minY = min(m.a[0].Y, min(m.a[1].Y, m.a[2].Y)), maxY = max(m.a[0].Y, max(m.a[1].Y, m.a[2].Y));
+    m.x0 = max((minX + 127) >> 8, 0); m.x1 = min((maxX - 128) >> 8, (int32_t)pc.W - 1);
+    m.y0 = max((minY + 127) >> 8, 0); m.y1 = min((maxY - 128) >> 8, (int32_t)pc.H - 1);
+    m.isLarge = t.isLarge && m.x0 <= m.x1 && m.y0 <= m.y1;
+    m.isSmall = false;
+    return m.isLarge;
+}
+
+// Sample stage: entry = slot | i << 6 | j << 11 | sample << 16
+__device__ __forceinline__ void k1ms_pixels(const PassConst& pc, const MsTargets& ms, const K1Warp& ws, const uint32_t* pixq, uint32_t pixHead, uint32_t cnt, unsigned lane) {
+    if (lane >= cnt) return;
+    const uint32_t e = pixq[(pixHead + lane) & (MS_PIXQ - 1)];
+    const uint32_t slot = e & 0x3Fu, k = e >> 16;
+    const int32_t pi = (int32_t)((e >> 6) & 0x1Fu), pj = (int32_t)((e >> 11) & 0x1Fu);
+    const int32_t sx = c_msShift[k][0], sy = c_msShift[k][1];
+    const int32_t c1 = -((ws.Ax[1][slot] >> 8) * sx + (ws.By[1][slot] >> 8) * sy), c2 = -((ws.Ax[2][slot] >> 8) * sx + (ws.By[2][slot] >> 8) * sy);
+    const int32_t u1 = ws.C[1][slot] + pj * ws.By[1][slot] + pi * ws.Ax[1][slot] + c1;   // unbiased edge values of the moved triangle (Appendix B.8)
+    const int32_t u2 = ws.C[2][slot] + pj * ws.By[2][slot] + pi * ws.Ax[2][slot] + c2;
+    const float z = depth_from((float)u1, (float)u2, ws.inv[slot], ws.z0[slot], ws.dz1[slot], ws.dz2[slot]);
+    if (!(z >= 0.0f && z <= 1.0f)) return;
+    const uint32_t xy = ws.xy[slot];
+    const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
+    atomicMin(ms.vis[k] + px, ((unsigned long long)__float_as_uint(z) << 32) | ws.idKey[slot]);
+}
+
+// Row stage: as k1_rows, but every entry yields one coverage mask per sample; the sample queue is drained between samples, so it
+// needs no more room than the 1-sample kernel's.
+template <bool CULL>
+__device__ __forceinline__ void k1ms_rows(const PassConst& pc, const MsTargets& ms, K1Warp& ws, uint32_t* pixq, uint32_t rowHead, uint32_t cnt, uint32_t& pixHead,
+                                          uint32_t& pixTail, unsigned lane) {
+    bool active = lane < cnt;
+    uint32_t slot = 0, j = 0, whb = 0, xo = 0;
+    bool tiny = false;
+    if (active) {
+        const uint32_t e = ws.rowq[(rowHead + lane) & (K1_ROWQ - 1)];
+        slot = e & 0x3Fu;
+        whb = ws.whb[slot];
+        tiny = k1ms_is_tiny(whb & 0xFFu, (whb >> 8) & 0xFFu);
+        const uint32_t wide = (whb & 0xFFu) > K1_SPLIT ? 1u : 0u;
+        j = (e >> 6) >> wide; xo = ((e >> 6) & wide) * K1_SPLIT;
+        if (!tiny && !row_owned((ws.xy[slot] >> 16) + j, pc.rank, pc.nRanks, pc.bandH)) active = false;
+    }
+    const uint32_t w = active ? min((whb & 0xFFu) - xo, K1_SPLIT) : 0u;
+    const uint32_t h = active ? (tiny ? ((whb >> 8) & 0xFFu) : 1u) : 0u;
+    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, w);
+    const uint32_t hmax = __reduce_max_sync(0xFFFFFFFFu, h);
+    const int32_t s0 = ws.Ax[0][slot], s1 = ws.Ax[1][slot], s2 = ws.Ax[2][slot];
+    const int32_t b0 = ws.By[0][slot], b1 = ws.By[1][slot], b2 = ws.By[2][slot];
+    const int32_t E0 = ws.C[0][slot] + (int32_t)j * b0 + (int32_t)xo * s0 - (int32_t)((whb >> 16) & 1u);   // top-left bias folded in
+    const int32_t E1 = ws.C[1][slot] + (int32_t)j * b1 + (int32_t)xo * s1 - (int32_t)((whb >> 17) & 1u);
+    const int32_t E2 = ws.C[2][slot] + (int32_t)j * b2 + (int32_t)xo * s2 - (int32_t)((whb >> 18) & 1u);
+    uint32_t ownRows = 0xFu;   // tiny entries: rows of the bbox this rank owns
+    if (tiny && pc.nRanks > 1) {
+        const uint32_t y0 = ws.xy[slot] >> 16;
+        ownRows = 0u;
+#pragma unroll
+        for (uint32_t jj = 0; jj < 4u; ++jj) if (row_owned(y0 + jj, pc.rank, pc.nRanks, pc.bandH)) ownRows |= 1u << jj;
+    }
+    const uint32_t tag = slot | (xo << 6) | (j << 11);
+#pragma unroll 1
+    for (uint32_t k = 0; k < 4u; ++k) {
+        const int32_t sx = c_msShift[k][0], sy = c_msShift[k][1];
+        const int32_t F0 = E0 - ((s0 >> 8) * sx + (b0 >> 8) * sy), F1 = E1 - ((s1 >> 8) * sx + (b1 >> 8) * sy), F2 = E2 - ((s2 >> 8) * sx + (b2 >> 8) * sy);
+        uint32_t mask = 0;
+#pragma unroll 1
+        for (uint32_t jj = 0; jj < hmax; ++jj) {   // rows past the first exist for tiny entries only (<= 4 columns, bit i + 4 jj)
+            if (jj > 0 && !tiny) break;
+#pragma unroll 1
+            for (uint32_t i = 0; i < wmax; ++i) {
+                const int32_t v = (F0 + (int32_t)jj * b0 + (int32_t)i * s0) | (F1 + (int32_t)jj * b1 + (int32_t)i * s1) | (F2 + (int32_t)jj * b2 + (int32_t)i * s2);
+                if (i < w && jj < h) mask |= (v >= 0 ? 1u : 0u) << (tiny ? 4u * jj + i : i);
+            }
+        }
+        if (tiny) {
+#pragma unroll
+            for (uint32_t jj = 0; jj < 4u; ++jj) if (!((ownRows >> jj) & 1u)) mask &= ~(0xFu << (4u * jj));
+        }
+        const uint32_t n = __popc(mask);
+        const uint32_t incl = warp_incl_scan(n, lane);
+        uint32_t pos = pixTail + incl - n;
+        pixTail += __shfl_sync(0xFFFFFFFFu, incl, 31);
+        while (mask) {
+            const uint32_t bpos = (uint32_t)__ffs(mask) - 1u;
+            mask &= mask - 1u;
+            const uint32_t i = tiny ? (bpos & 3u) : bpos, jj = tiny ? (bpos >> 2) : 0u;
+            pixq[pos++ & (MS_PIXQ - 1)] = (tag + (i << 6) + (jj << 11)) | (k << 16);
+        }
+        __syncwarp();
+        while (pixTail - pixHead >= 32u) { k1ms_pixels(pc, ms, ws, pixq, pixHead, 32u, lane); pixHead += 32u; }
+        __syncwarp();
+    }
+}
+
+template <bool CULL>
+__global__ void __launch_bounds__(K1_THREADS, 5) k_setup_raster_ms(const __grid_constant__ PassConst pc, const __grid_constant__ MsTargets ms) {
+    __shared__ K1Shared sm;
+    __shared__ uint32_t pixq32[K1_WARPS][MS_PIXQ];
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    K1Warp& ws = sm.w[warp];
+    uint32_t* pixq = pixq32[warp];
+    const uint32_t bl = pc.batchLog2, tpb = 1u << bl;
+    const uint32_t nBatches = CULL ? (__ldcg(pc.cullCounts) << (8u - bl)) : ((pc.nTris + tpb - 1u) >> bl);
+    const uint32_t totalWarps = gridDim.x * K1_WARPS;
+    const uint32_t laneTri = lane < tpb ? lane : 0xFFFFFFFFu;
+    auto batch_tri = [&](uint32_t b) -> uint32_t {
+        if (laneTri == 0xFFFFFFFFu) return 0xFFFFFFFFu;
+        if (!CULL) return (b << bl) + laneTri;
+        if (b >= nBatches) return 0xFFFFFFFFu;
+        return (__ldg(pc.triBlockList + (b >> (8u - bl))) << 8) + ((b & ((1u << (8u - bl)) - 1u)) << bl) + laneTri;
+    };
+    uint32_t ringPos = 0, rowHead = 0, rowTail = 0, pixHead = 0, pixTail = 0;
+    // software pipeline as in K1: the slot stream runs two batches ahead, the cache gathers one batch ahead of the raster stages
+    uint32_t batch = blockIdx.x * K1_WARPS + warp;
+    uint4 q[3];
+    uint32_t id;
+    {
+        const uint32_t tri0 = batch_tri(batch);
+        const uint4 s0 = k1_load_slots<CULL>(pc, tri0);
+        k1_gather<CULL>(pc, tri0, s0, q);
+        id = s0.w;
+    }
+    uint4 ns = k1_load_slots<CULL>(pc, batch_tri(batch + totalWarps));
+    for (; batch < nBatches; batch += totalWarps) {
+        const uint32_t tri = batch_tri(batch), ntri = batch_tri(batch + totalWarps);
+        const uint4 nns = k1_load_slots<CULL>(pc, batch_tri(batch + 2u * totalWarps));
+        K1Tri t;
+        k1ms_classify(pc, tri < pc.nTris, q, t);
+        // ---- beyond the small class (rare in the dense meshes this kernel is for): every sample's queue set gets its own record
+        if (__any_sync(0xFFFFFFFFu, t.isLarge || t.needsClip)) {
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) {
+                PassConst pk = pc;
+                pk.status = ms.status[k]; pk.large = ms.large[k]; pk.huge = ms.huge[k]; pk.tileHead = ms.tileHead[k]; pk.clipQueue = ms.clipQueue[k];
+                K1Tri m;
+                k1ms_moved(pc, t, k, m);
+                k1_emit_large(pk, m, id, lane);
+                if (t.needsClip) {
+                    const uint32_t qi = atomicAdd(&pk.status[6], 1u);
+                    if (qi < pc.clipCap) pk.clipQueue[qi] = id; else atomicOr(&pk.status[2], OVF_LARGE);
+                }
+            }
+        }
+        // ---- small: one ring record, row entries over the union bbox
+        const unsigned smallMask = __ballot_sync(0xFFFFFFFFu, t.isSmall);
+        const uint32_t mySlot = (ringPos + __popc(smallMask & ((1u << lane) - 1u))) & (K1_RING - 1);
+        const bool isTiny = t.isSmall && k1ms_is_tiny((uint32_t)(t.x1 - t.x0 + 1), (uint32_t)(t.y1 - t.y0 + 1));
+        const uint32_t nEnt = !t.isSmall ? 0u : (isTiny ? 1u : (uint32_t)(t.y1 - t.y0 + 1) << ((t.x1 - t.x0 + 1) > (int32_t)K1_SPLIT ? 1 : 0));
+        if (t.isSmall) k1_store_small(ws, t, id, mySlot);
+        ringPos += __popc(smallMask);
+        k1_gather<CULL>(pc, ntri, ns, q);                            // in flight during the raster stages
+        id = ns.w; ns = nns;
+        uint32_t done = 0;
+        do {
+            const uint32_t c = min(nEnt - done, K1_SPLIT);
+            const uint32_t cIncl = warp_incl_scan(c, lane);
+            const uint32_t rowPos = rowTail + cIncl - c;
+            for (uint32_t r = 0; r < c; ++r) ws.rowq[(rowPos + r) & (K1_ROWQ - 1)] = (uint16_t)(mySlot | ((done + r) << 6));
+            rowTail += __shfl_sync(0xFFFFFFFFu, cIncl, 31);
+            done += c;
+            __syncwarp();
+            while (rowTail - rowHead >= 32u) { k1ms_rows<CULL>(pc, ms, ws, pixq, rowHead, 32u, pixHead, pixTail, lane); rowHead += 32u; }
+        } while (__any_sync(0xFFFFFFFFu, done < nEnt));
+        // queued samples reference ring slots of this batch or the one before: drain them before the ring advances
+        if (pixTail != pixHead) { k1ms_pixels(pc, ms, ws, pixq, pixHead, pixTail - pixHead, lane); pixHead = pixTail; }
+        __syncwarp();
+    }
+    if (rowTail != rowHead) {
+        k1ms_rows<CULL>(pc, ms, ws, pixq, rowHead, rowTail - rowHead, pixHead, pixTail, lane);
+        while (pixTail != pixHead) { const uint32_t c = min(32u, pixTail - pixHead); k1ms_pixels(pc, ms, ws, pixq, pixHead, c, lane); pixHead += c; }
+    }
+}
+
 // Re-bases a draw list's index stream into cache-slot space, in submission order (runs when the list changes).
 __global__ void __launch_bounds__(256) k_flatten_slots(const __grid_constant__ PassConst pc, uint32_t* __restrict__ flat, uint32_t* __restrict__ triMaterial) {
     const uint32_t tri = blockIdx.x * 256u + threadIdx.x;
@@ -444,6 +659,36 @@ __global__ void __launch_bounds__(256) k_pass_reset(const __grid_constant__ Pass
 }
 void launch_pass_reset(const PassConst& pc, int numSMs, cudaStream_t st) {
     launch_k(k_pass_reset, dim3((unsigned)numSMs), dim3(256), st, true, pc);
+}
+
+// Before the one-pass multisampled K1: arm the queue sets of samples 1-3 (K0's prologue armed sample 0's, the pass's own)
+__global__ void __launch_bounds__(256) k_ms_reset(const __grid_constant__ MsTargets ms, uint32_t nTiles) {
+    pdl_enter();
+    for (int k = 1; k < 4; ++k) {
+        if (blockIdx.x == 0 && threadIdx.x < STATUS_WORDS) ms.status[k][threadIdx.x] = 0u;
+        uint4* th = reinterpret_cast<uint4*>(ms.tileHead[k]);
+        for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < nTiles; i += gridDim.x * 256u) th[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+void launch_setup_raster_ms(const PassConst& pc, const MsTargets& ms, int numSMs, cudaStream_t st) {
+    if (pc.nTris == 0) return;
+    launch_k(k_ms_reset, dim3((unsigned)numSMs), dim3(256), st, true, ms, pc.tilesX * pc.tilesY);
+    using Kern = void (*)(PassConst, MsTargets);
+    static const Kern kern[2] = {k_setup_raster_ms<false>, k_setup_raster_ms<true>};
+    const int v = pc.drawVisible ? 1 : 0;
+    static int perSM[2] = {0, 0};
+    if (!perSM[v]) {
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern[v], K1_THREADS, 0);
+        perSM[v] = n > 0 ? n : 1;
+    }
+    const uint32_t maxWarps = (uint32_t)(numSMs * perSM[v]) * K1_WARPS;
+    PassConst pk = pc;
+    pk.batchLog2 = 5u;
+    while (pk.batchLog2 > 0u && ((pc.nTris + (1u << pk.batchLog2) - 1u) >> pk.batchLog2) < maxWarps / 2u) --pk.batchLog2;
+    const uint32_t nBatches = (pc.nTris + (1u << pk.batchLog2) - 1u) >> pk.batchLog2;
+    const uint32_t grid = std::min<uint32_t>((nBatches + K1_WARPS - 1u) / K1_WARPS, (uint32_t)(numSMs * perSM[v]));
+    launch_k(kern[v], dim3(grid), dim3(K1_THREADS), st, true, pk, ms);
 }
 
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st) {

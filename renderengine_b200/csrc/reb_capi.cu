@@ -82,6 +82,9 @@ struct reb_ctx {
     bool tlFollows = false, tlPending = false; ShadeConst tlShade; uint32_t tlIdBase = 0; uint64_t tlDropped = 0;
     // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
     uint32_t samples = 1; float* msDepth = nullptr; uint32_t* msTriId = nullptr;
+    // queue sets of samples 1-3 for the one-pass multisampled K1 (sample 0 uses the forward pass's own): large-triangle queue, clip queue,
+    // broadcast list, per-tile heads; their status words are sets 3-5 of dStatus, their host mirrors sets 2-4 of hStatus
+    LargeRec* msLarge[3] = {}; uint32_t* msClip[3] = {}; LargeRec* msHuge = nullptr; TileHead* msTileHead[3] = {}; uint32_t msLargeAlloc = 0, msClipCap = 0, msTileCap = 0;
     // queues
     LargeRec* large = nullptr; uint32_t largeCap = 0;
     uint32_t* clipQueue = nullptr;   // largeCap entries
@@ -91,7 +94,7 @@ struct reb_ctx {
     cudaEvent_t shadowReadyEvent = nullptr;   // reb_shadow_wait_event: waited for right before the next forward tile stage (one-shot)
     bool shadowDeferred = false; float recordedSPV[16];   // reb_render_shadow recorded, not yet submitted
     LargeRec* tileList = nullptr; uint32_t listCap = 0;   // per-tile lists of 48-B records (listCap records)
-    uint32_t* dStatus = nullptr;     // 3 x STATUS_WORDS words
+    uint32_t* dStatus = nullptr;     // 6 x STATUS_WORDS words: shadow, forward, translucent, samples 1-3 of a multisampled forward pass
     uint32_t* hStatus = nullptr;     // pinned + mapped mirror, written by the tile stage kernels
     uint32_t* hStatusDev = nullptr;  // device-side address of hStatus
     PassState pass[3];
@@ -188,6 +191,12 @@ int ensure_tiles(reb_ctx* ctx, int kind, uint32_t nTiles) {
         CU(cudaMemsetAsync(ctx->tileHead[kind], 0, ((size_t)nTiles + 1) * sizeof(TileHead), ctx->stream));   // K0's prologue zeroes them every pass
         ctx->tileCap[kind] = nTiles + 1;
     }
+    if (kind == 1 && ctx->samples == 4 && nTiles + 1 > ctx->msTileCap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        for (int k = 0; k < 3; ++k) if ((rc = dev_alloc(ctx, &ctx->msTileHead[k], (size_t)nTiles + 1))) return rc;
+        if (!ctx->msHuge && (rc = dev_alloc(ctx, &ctx->msHuge, (size_t)3 * HUGE_CAP))) return rc;
+        ctx->msTileCap = nTiles + 1;
+    }
     return REB_OK;
 }
 
@@ -206,6 +215,12 @@ int ensure_large(reb_ctx* ctx, uint32_t nTris) {
         CU(cudaStreamSynchronize(ctx->stream));
         if ((rc = dev_alloc(ctx, &ctx->clipQueue, (size_t)nTris))) return rc;
         ctx->largeCap = nTris;
+    }
+    if (ctx->samples == 4 && (ctx->msLargeAlloc < ctx->largeAlloc || ctx->msClipCap < ctx->largeCap)) {   // the same for samples 1-3
+        CU(cudaStreamSynchronize(ctx->stream));
+        for (int k = 0; k < 3; ++k)
+            if ((rc = dev_alloc(ctx, &ctx->msLarge[k], (size_t)ctx->largeAlloc)) || (rc = dev_alloc(ctx, &ctx->msClip[k], (size_t)ctx->largeCap))) return rc;
+        ctx->msLargeAlloc = ctx->largeAlloc; ctx->msClipCap = ctx->largeCap;
     }
     return REB_OK;
 }
@@ -509,15 +524,29 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
         // (128 - 256 s) sub-pixel units; every pass leaves its depth / triangle-ID plane, the resolve kernel shades.
         static const int32_t shift[4][2] = {{32, 96}, {-96, 32}, {96, -32}, {-32, -96}};
         const size_t px = (size_t)ctx->W * ctx->H;
+        // ONE K1 pass tests every triangle against the four sample positions and fills the four visibility planes and the four
+        // queue sets; K2 and the (visibility-only) tile stage then run per sample on that sample's set
+        MsTargets ms;
+        for (int k = 0; k < 4; ++k) {
+            ms.vis[k] = ctx->vis + (size_t)k * px;
+            ms.status[k] = k ? ctx->dStatus + (size_t)(2 + k) * STATUS_WORDS : pc.status;
+            ms.large[k] = k ? ctx->msLarge[k - 1] : pc.large;
+            ms.clipQueue[k] = k ? ctx->msClip[k - 1] : pc.clipQueue;
+            ms.huge[k] = k ? ctx->msHuge + (size_t)(k - 1) * HUGE_CAP : pc.huge;
+            ms.tileHead[k] = k ? ctx->msTileHead[k - 1] : pc.tileHead;
+        }
+        if (ps.nTris) { launch_setup_raster_ms(pc, ms, ctx->numSMs, ctx->stream); ctx->launches += 2; }
+        else CU(cudaMemsetAsync(ctx->dStatus + 3 * STATUS_WORDS, 0, 3 * STATUS_WORDS * 4, ctx->stream));   // no K1 to arm the sets of samples 1-3: their tile stages read the list lengths
         for (int k = 0; k < 4; ++k) {
             PassConst pk = pc;
-            pk.vis = ctx->vis + (size_t)k * px; pk.shiftX = shift[k][0]; pk.shiftY = shift[k][1];
+            pk.vis = ms.vis[k]; pk.shiftX = shift[k][0]; pk.shiftY = shift[k][1];   // (the shift still applies to the children K2 clips)
+            pk.status = ms.status[k]; pk.large = ms.large[k]; pk.clipQueue = ms.clipQueue[k]; pk.huge = ms.huge[k]; pk.tileHead = ms.tileHead[k];
+            if (k && ctx->hStatusDev) pk.hostStatus = ctx->hStatusDev + 8 * (1 + k);
             ShadeConst sk = sh;
             sk.outSRGB8 = nullptr; sk.outF32 = nullptr; sk.skyFaces = nullptr;   // visibility only
             sk.outDepth = ctx->msDepth + (size_t)k * px; sk.outTriId = ctx->msTriId + (size_t)k * px;
-            if (k > 0 && ps.nTris) { launch_pass_reset(pk, ctx->numSMs, ctx->stream); ctx->launches++; }
-            if (ps.nTris) { launch_setup_raster(pk, false, ctx->numSMs, ctx->stream); launch_tile_binned(pk, false, ctx->numSMs, ctx->stream); ctx->launches += 2; }
-            launch_tile_forward(pk, sk, ctx->numSMs, ctx->stream); ctx->launches++;
+            if (ps.nTris) { launch_tile_binned(pk, false, ctx->numSMs, ctx->stream); ctx->launches++; }
+            launch_tile_forward(pk, sk, ctx->numSMs, ctx->stream); ctx->launches++;   // (folding these four passes into the resolve was measured: 4 x 21 + 118 us became 207 us)
         }
         mark(3); mark(4);
         if (ctx->shadowReadyEvent) { CU(cudaStreamWaitEvent(ctx->stream, ctx->shadowReadyEvent, 0)); ctx->shadowReadyEvent = nullptr; }
@@ -635,13 +664,16 @@ int check_and_recover(reb_ctx* ctx) {
         bool first = true;                           // counters[0] = drops of the passes checked now (not carried over from earlier frames)
         for (int k = 0; k < 2; ++k) {
             if (!ctx->pass[k].pending) continue;
-            const uint32_t* st = ctx->hStatus + 8 * k;
-            ctx->counters[0] = (first ? 0 : ctx->counters[0]) + st[1];
-            ctx->counters[1] = (first ? 0 : ctx->counters[1]) + st[0];    // binned triangles / tile-list entries: summed over the passes of the frame
-            ctx->counters[2] = (first ? 0 : ctx->counters[2]) + st[3];
-            first = false;
-            if (st[2] & OVF_LARGE) { overflow = true; ctx->largeWorstCase = true; }   // clip children outgrew the slack: size for the worst case
-            if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
+            const int nSets = (k == 1 && ctx->samples == 4) ? 4 : 1;   // a multisampled forward pass has one status set per sample
+            for (int q = 0; q < nSets; ++q) {
+                const uint32_t* st = ctx->hStatus + 8 * (q ? 1 + q : k);
+                ctx->counters[0] = (first ? 0 : ctx->counters[0]) + st[1];
+                ctx->counters[1] = (first ? 0 : ctx->counters[1]) + st[0];    // binned triangles / tile-list entries: summed over the passes of the frame
+                ctx->counters[2] = (first ? 0 : ctx->counters[2]) + st[3];
+                first = false;
+                if (st[2] & OVF_LARGE) { overflow = true; ctx->largeWorstCase = true; }   // clip children outgrew the slack: size for the worst case
+                if (st[2] & OVF_LIST) { overflow = true; need = std::max(need, st[3] + st[3] / 4 + 1024u); }
+            }
         }
         if (!overflow) {
             ctx->pass[0].pending = ctx->pass[1].pending = false;

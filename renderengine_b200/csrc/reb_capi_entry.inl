@@ -38,12 +38,12 @@ int reb_create(const reb_params* params, reb_ctx** out) {
     if (ctx->rank >= ctx->nRanks || ctx->bandH % TILE_H) return bail(fail(ctx, REB_E_INVALID, "reb_create: bad partition (rank < n_ranks, band_h multiple of 8)"));
     int rc;
     if ((rc = alloc_targets(ctx))) return bail(rc);
-    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 3 * STATUS_WORDS * 4) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 3 * STATUS_WORDS * 4) != cudaSuccess ||
+    if (cudaMalloc(reinterpret_cast<void**>(&ctx->dStatus), 6 * STATUS_WORDS * 4) != cudaSuccess || cudaMemset(ctx->dStatus, 0, 6 * STATUS_WORDS * 4) != cudaSuccess ||
         cudaMalloc(reinterpret_cast<void**>(&ctx->huge), 2 * HUGE_CAP * sizeof(LargeRec)) != cudaSuccess ||
-        cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 64, cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostAlloc(reinterpret_cast<void**>(&ctx->hStatus), 256, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->hStatusDev), ctx->hStatus, 0) != cudaSuccess)
         return bail(fail(ctx, REB_E_CUDA, "status buffers allocation failed"));
-    std::memset(ctx->hStatus, 0, 64);
+    std::memset(ctx->hStatus, 0, 256);
     ctx->listCap = 1u << 20;   // records of 48 B; grown on overflow (check_and_recover)
     if (const char* e = std::getenv("REB_TILE_LIST_CAP")) ctx->listCap = std::max(1024u, (uint32_t)std::strtoul(e, nullptr, 10));   // tests: force the regrow + replay path
     if (cudaMalloc(reinterpret_cast<void**>(&ctx->tileList), (size_t)ctx->listCap * sizeof(LargeRec)) != cudaSuccess) return bail(fail(ctx, REB_E_CUDA, "tile list allocation failed"));
@@ -69,6 +69,7 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].posS, ctx->pass[1].posS, ctx->pass[2].posS, ctx->pass[0].nrmS, ctx->pass[1].nrmS, ctx->pass[2].nrmS,
                     ctx->pass[0].triStream, ctx->pass[1].triStream, ctx->pass[2].triStream,
                     ctx->pass[0].blockRefs, ctx->pass[1].blockRefs, ctx->pass[2].blockRefs, ctx->pass[0].triBlockList, ctx->pass[1].triBlockList, ctx->pass[2].triBlockList,
+                    ctx->msLarge[0], ctx->msLarge[1], ctx->msLarge[2], ctx->msClip[0], ctx->msClip[1], ctx->msClip[2], ctx->msHuge, ctx->msTileHead[0], ctx->msTileHead[1], ctx->msTileHead[2],
                     ctx->pass[0].cullCounts, ctx->pass[1].cullCounts, ctx->pass[2].cullCounts, ctx->pass[0].slotBlockVisible, ctx->pass[1].slotBlockVisible, ctx->pass[2].slotBlockVisible};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : ctx->texAllocs) cudaFree(p);

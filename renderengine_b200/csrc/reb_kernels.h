@@ -39,6 +39,13 @@ inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream
     cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// one-pass K1 of the 4x multisampled base pass (k_setup.cu): per sample, where K1 puts what that sample's K2 / tile stage consume
+struct MsTargets {
+    unsigned long long* vis[4];
+    uint32_t* status[4]; LargeRec* large[4]; LargeRec* huge[4]; TileHead* tileHead[4]; uint32_t* clipQueue[4];
+};
+void launch_setup_raster_ms(const PassConst& pc, const MsTargets& ms, int numSMs, cudaStream_t st);
+
 void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st);
 void launch_vertex_both(const PassConst& shadowPass, const PassConst& forwardPass, cudaStream_t st);   // identical cache layouts
 void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st);

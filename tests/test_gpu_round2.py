@@ -341,3 +341,35 @@ def test_parity_more_translucent_layers_than_the_sorted_fast_path_holds():
     d8 = np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32))
     assert d8.max() <= 1, f"{np.count_nonzero(d8 > 1)} channel samples beyond 1 LSB (max {d8.max()})"
     assert _psnr(ctx.readback(capi.REB_COLOR_F32), ref["color_f32"]) >= 50.0
+
+
+def test_multisampled_pass_on_a_split_context():
+    """Sort-first row bands + 4x multisampling: the one-pass multisampled K1 walks the compacted block list of the rank (CULL
+    instantiation) and filters rows per sample; every rank's own rows of all four sample planes equal the unsplit oracle frame."""
+    from oracle import orc
+    from renderengine_b200 import capi, parallel, scene as sc
+    s = sc.make_scene("small", level=2)
+    world = 2
+    band = parallel.contiguous_band(s["height"], 2 * world)      # two interleaved bands per rank
+    o = orc.Oracle(s)
+    ref_shadow = o.render_shadow()
+    for v in (np.asarray(s["view"]), sc.view_from(s, (0.3, 1.2, 0.4), (6.0, 0.0, 5.0))):
+        o.set_view(v)
+        ref = o.render_forward_msaa4(ref_shadow)
+        got_t = np.full_like(ref["tri_id"], 0xFFFFFFFF); got_z = np.ones_like(ref["depth"]); got_c = np.zeros_like(ref["color_srgb8"])
+        for r in range(world):
+            ctx = capi.Context(s["width"], s["height"], rank=r, n_ranks=world, band_h=band)
+            ctx.upload_scene(s)
+            ctx.set_sample_count(4)
+            ctx.set_view(v)
+            for _ in range(2):
+                ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"]); ctx.sync()
+            own = ((np.arange(s["height"]) // band) % world == r)
+            got_t[:, own] = ctx.readback(capi.REB_MS_TRIID_U32)[:, own]
+            got_z[:, own] = ctx.readback(capi.REB_MS_DEPTH_F32)[:, own]
+            got_c[own] = ctx.readback(capi.REB_COLOR_SRGB8)[own]
+            assert ctx.counters()[0] == 0
+            ctx.close()
+        assert np.array_equal(got_t, ref["tri_id"]), f"{np.count_nonzero(got_t != ref['tri_id'])} sample IDs differ"
+        assert np.array_equal(got_z.view(np.uint32), ref["depth"].view(np.uint32))
+        assert np.abs(got_c.astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
