@@ -91,6 +91,9 @@ def build_mgpu_demo(force=False):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "checked":   # device-side asserts on computed indices: REB_LIB=<printed path> python -m pytest tests -m gpu
+        print("built", build_variant("checked", ["REB_CHECKED"]))
+        sys.exit(0)
     build(force=True, verbose=True)
     print("built", OUT)
     print("built", build_host(force=True))

@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) k_fill_ff(uint32_t* __restrict__ p, size_
 __global__ void __launch_bounds__(256) k_first_use(uint32_t nTris, const uint32_t* __restrict__ sortedTri, const uint32_t* __restrict__ flat, uint32_t* __restrict__ firstUse) {
     const uint32_t pos = blockIdx.x * 256u + threadIdx.x;
     if (pos >= nTris) return;
+    REB_ASSERT(sortedTri[pos] < nTris);
     const uint32_t* f = flat + 3ull * sortedTri[pos];
     atomicMin(firstUse + f[0], pos); atomicMin(firstUse + f[1], pos); atomicMin(firstUse + f[2], pos);
 }
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(256) k_slot_streams(const __grid_constant__ Pa
     const uint32_t slot = blockIdx.x * 256u + threadIdx.x;
     if (slot >= pc.cacheSize) return;
     const uint32_t old = newToOld[slot];
+    REB_ASSERT(old < pc.cacheSize);
     remap[old] = slot;
     const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, old);
     const uint32_t v = (uint32_t)((int32_t)old - pc.draws[d].cacheOffset);

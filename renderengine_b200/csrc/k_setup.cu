@@ -167,6 +167,7 @@ template <bool CULL>
 __device__ __forceinline__ void k1_gather(const PassConst& pc, uint32_t tri, uint4 s, uint4 q[3]) {
     if (tri >= pc.nTris || (CULL && s.x == SLOT_CULLED)) { q[0] = q[1] = q[2] = make_uint4(0, 0, 0, 0); return; }
     const uint4* va = reinterpret_cast<const uint4*>(pc.vtxA);
+    REB_ASSERT(s.x < pc.cacheSize && s.y < pc.cacheSize && s.z < pc.cacheSize && s.w < pc.nTris);
     q[0] = __ldg(va + s.x); q[1] = __ldg(va + s.y); q[2] = __ldg(va + s.z);
 }
 
@@ -259,6 +260,7 @@ __device__ __forceinline__ void k1_pixels(const PassConst& pc, const K1Warp& ws,
     if (!(z >= 0.0f && z <= 1.0f)) return;
     const uint32_t xy = ws.xy[slot];
     const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
+    REB_ASSERT((xy >> 16) + (uint32_t)pj < pc.H && (xy & 0xFFFFu) + (uint32_t)pi < pc.W && slot < (uint32_t)K1_RING);
     if (SHADOW) atomicMin(pc.depthBits + px, __float_as_uint(z));
     else atomicMin(pc.vis + px, ((unsigned long long)__float_as_uint(z) << 32) | ws.idKey[slot]);
 }
@@ -282,6 +284,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
         if (laneTri == 0xFFFFFFFFu) return 0xFFFFFFFFu;
         if (!CULL) return (b << bl) + laneTri;
         if (b >= nBatches) return 0xFFFFFFFFu;
+        REB_ASSERT(__ldg(pc.triBlockList + (b >> (8u - bl))) < (pc.nTris + 255u) / 256u);
         return (__ldg(pc.triBlockList + (b >> (8u - bl))) << 8) + ((b & ((1u << (8u - bl)) - 1u)) << bl) + laneTri;
     };
 #define K1_TRI(b) batch_tri(b)
@@ -347,6 +350,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_BLOCKS) k_setup_raster(cons
                 rowTail += __shfl_sync(0xFFFFFFFFu, cIncl, 31);
             }
             done += c;
+            REB_ASSERT(rowTail - rowHead <= (uint32_t)K1_ROWQ && pixTail - pixHead <= (uint32_t)K1_PIXQ);
             __syncwarp();
             while (rowTail - rowHead >= 32u) {
                 k1_rows<SHADOW, CULL>(pc, ws, rowHead, 32u, pixTail, lane);
@@ -432,6 +436,7 @@ __device__ __forceinline__ void k1ms_pixels(const PassConst& pc, const MsTargets
     if (!(z >= 0.0f && z <= 1.0f)) return;
     const uint32_t xy = ws.xy[slot];
     const size_t px = (size_t)((xy >> 16) + (uint32_t)pj) * pc.W + (xy & 0xFFFFu) + (uint32_t)pi;
+    REB_ASSERT((xy >> 16) + (uint32_t)pj < pc.H && (xy & 0xFFFFu) + (uint32_t)pi < pc.W && k < 4u);
     atomicMin(ms.vis[k] + px, ((unsigned long long)__float_as_uint(z) << 32) | ws.idKey[slot]);
 }
 

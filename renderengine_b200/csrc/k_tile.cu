@@ -244,6 +244,7 @@ __device__ __forceinline__ uint32_t k2_next_tile(const PassConst& pc, uint32_t t
         const uint2 h = __ldcg(reinterpret_cast<const uint2*>(pc.tileHead + t));   // {count, start}
         if (!h.x || h.y >= pc.listCap) continue;            // empty, or an overflowed list (the host regrows and replays the frame)
         start = h.y; cnt = min(h.x, pc.listCap - h.y);
+        REB_ASSERT((unsigned long long)start + cnt <= pc.listCap);
         break;
     }
     return t;
@@ -381,6 +382,7 @@ __device__ __forceinline__ void kt_block(const PassConst& pc, const ShadeConst& 
     const int x = bx0 + lx, y = by0 + ly;
     const bool inb = x < (int)pc.W && y < (int)pc.H;
     const size_t p = (size_t)y * pc.W + x;
+    REB_ASSERT(!inb || p < (size_t)pc.W * pc.H);
     if (inb && key[0] != VIS_CLEAR) pc.vis[p] = VIS_CLEAR;   // leave the buffer cleared for the next frame
     if (nHuge) merge_huge<false, 1>(hs, nHuge, bx0, by0, x, y, key, lane);
     if (!inb) return;

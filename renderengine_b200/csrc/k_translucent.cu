@@ -40,6 +40,7 @@ __device__ __forceinline__ void tl_load(const PassConst& pc, uint32_t tri, VtxA 
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const uint32_t slot = s3[k];
+        REB_ASSERT(tri < pc.nTris && slot < pc.cacheSize);
         const uint4 q = __ldg(reinterpret_cast<const uint4*>(pc.vtxA) + slot);
         a[k] = {(int32_t)q.x + pc.shiftX, (int32_t)q.y + pc.shiftY, __uint_as_float(q.z), q.w};   // + the B.15 sample shift (0 in a 1-sample pass)
     }
@@ -128,6 +129,7 @@ __global__ void __launch_bounds__(256) k_tl_raster(const __grid_constant__ PassC
         }
         if (cls == 3) {   // one 64-bit atomic hands out the list slot (high word) and the first work item (low word) consistently
             const unsigned long long t = atomicAdd(reinterpret_cast<unsigned long long*>(counters + 4), (1ull << 32) | nTiles);
+            REB_ASSERT((uint32_t)(t >> 32) < pc.nTris);
             largeList[(uint32_t)(t >> 32)] = make_uint2(tri, (uint32_t)t);
         }
         // ---- small: coverage mask, one allocation per warp, emit

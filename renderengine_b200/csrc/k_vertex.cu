@@ -61,6 +61,7 @@ __device__ __forceinline__ void k0_transform_store(const PassConst& pc, uint32_t
     V3 world;
     const float4 c = vertex_stage<!SHADOW>(pc.PV, T, in.p.x, in.p.y, in.p.z, &world);
     const VtxA a = viewport_snap(c, pc.W, pc.H);
+    REB_ASSERT(slot < pc.cacheSize && in.node * 16u + 15u < 0xFFFFFFF0u);
     reinterpret_cast<uint4*>(pc.vtxA)[slot] = make_uint4((uint32_t)a.X, (uint32_t)a.Y, __float_as_uint(a.z), a.flags);
     if (!SHADOW) {
         const float4 n = in.n;
@@ -298,6 +299,7 @@ __global__ void __launch_bounds__(128) k_cull_blocks(const __grid_constant__ Pas
     list[base + __popc(m & ((1u << lane) - 1u))] = tb;
     const uint32_t* r = refs + (size_t)tb * BLOCK_REFS;
     const uint32_t n = r[0];
+    REB_ASSERT(n == 0xFFFFFFFFu ? (r[1] <= r[2] && r[2] < (pc.cacheSize + 255u) / 256u) : n < (uint32_t)BLOCK_REFS);
     if (n == 0xFFFFFFFFu) { for (uint32_t b = r[1]; b <= r[2]; ++b) slotBlockVisible[b] = 1u; }
     else for (uint32_t i = 0; i < n; ++i) slotBlockVisible[r[1 + i]] = 1u;
 }

@@ -83,6 +83,7 @@ __device__ __noinline__ void tile_walk(const PassConst& pc, const LargeRec r, un
             outside = outside || (Fmax < 0);
         }
         if (outside) continue;
+        REB_ASSERT(tx >= 0 && ty >= 0 && (uint32_t)tx < pc.tilesX && (uint32_t)ty < pc.tilesY);
         TileHead* th = pc.tileHead + ((uint32_t)ty * pc.tilesX + (uint32_t)tx);
         if (!SCATTER) {
             atomicAdd(&th->count, 1u);

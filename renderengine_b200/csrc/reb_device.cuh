@@ -7,6 +7,16 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Checked build (-DREB_CHECKED, `python -m renderengine_b200.build checked` -> variants/libreb_checked.so, loaded with REB_LIB=...):
+// device-side asserts on every index this code computes into a buffer it does not own the bounds of by construction — the GPU
+// suite run against that library is this repo's stand-in for compute-sanitizer memcheck, which is closed on this pool.
+#ifdef REB_CHECKED
+#include <cassert>
+#define REB_ASSERT(c) assert(c)
+#else
+#define REB_ASSERT(c) ((void)0)
+#endif
+
 namespace reb {
 
 constexpr uint32_t TRI_NONE = 0xFFFFFFFFu;
@@ -244,6 +254,7 @@ __device__ __forceinline__ TriRef tri_ref(const PassConst& pc, uint32_t tri) {
         const uint32_t* f = pc.flatSlots + 3ull * tri;
         r.s[0] = __ldg(f); r.s[1] = __ldg(f + 1); r.s[2] = __ldg(f + 2); r.materialRaw = __ldg(pc.triMaterial + tri);
     }
+    REB_ASSERT(tri < pc.nTris && r.s[0] < pc.cacheSize && r.s[1] < pc.cacheSize && r.s[2] < pc.cacheSize);
     return r;
 }
 
