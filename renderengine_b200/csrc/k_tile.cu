@@ -85,6 +85,22 @@ __device__ __forceinline__ void test_samples(long long F0, long long F1, long lo
     }
 }
 
+// The same for a block that lies entirely inside the triangle (every edge function is >= 0 at the block's extreme centres, hence at
+// all of them): no coverage test, only the two edge values the depth needs.
+template <bool SHADOW, int SUB>
+__device__ __forceinline__ void test_samples_inside(long long F1, long long F2, long long s1, long long s2, uint32_t bias12,
+                                                    float inv, float z0, float dz1, float dz2, uint32_t idKey, typename KeyOf<SHADOW>::type (&key)[SUB]) {
+    F1 += (long long)(bias12 & 1u); F2 += (long long)(bias12 >> 1);   // unbiased
+#pragma unroll
+    for (int r = 0; r < SUB; ++r, F1 += s1, F2 += s2) {
+        const float z = depth_from((float)F1, (float)F2, inv, z0, dz1, dz2);
+        if (!(z >= 0.0f && z <= 1.0f)) continue;
+        const typename KeyOf<SHADOW>::type k = SHADOW ? (typename KeyOf<SHADOW>::type)__float_as_uint(z)
+                                                      : (typename KeyOf<SHADOW>::type)(((unsigned long long)__float_as_uint(z) << 32) | idKey);
+        if (k < key[r]) key[r] = k;
+    }
+}
+
 // ---- 1-D bulk asynchronous copy (TMA engine, no tensor map) global -> shared, completion on an mbarrier --------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -172,13 +188,45 @@ __device__ __forceinline__ void merge_huge(const HugeStage& hs, uint32_t nHuge, 
     const int32_t cx0 = 256 * bx0 + 128, cy0 = 256 * by0 + 128;
     const int32_t spanX = 256 * (BLK_W - 1), spanY = 256 * (BLK_ROWS * SUB - 1);
     if (nHuge <= (uint32_t)HUGE_DIRECT) {
-        // short list (a ground plane is two triangles): a warp-uniform bbox reject, then every lane tests its samples
-        // (cheaper than one lane per record deciding liveness with 64-bit edge evaluations)
+        // short list (a ground plane is two triangles)
+        if (!SHADOW) {
+            // forward tile stage (one sample per lane): a warp-uniform bbox reject, then every lane tests its sample.  (The block
+            // classification below costs this kernel registers it does not have: 80 + spills, tile stage 50 -> 60 us on C2.)
+            for (uint32_t s = 0; s < nHuge; ++s) {
+                if (hs.maxX[s] < cx0 || hs.minX[s] > cx0 + spanX || hs.maxY[s] < cy0 || hs.minY[s] > cy0 + spanY) continue;
+                const long long F0 = hs.E[0][s] + mulw(hs.A[0][s], 256 * x) + mulw(hs.B[0][s], 256 * y);
+                const long long F1 = hs.E[1][s] + mulw(hs.A[1][s], 256 * x) + mulw(hs.B[1][s], 256 * y);
+                const long long F2 = hs.E[2][s] + mulw(hs.A[2][s], 256 * x) + mulw(hs.B[2][s], 256 * y);
+                test_samples<SHADOW, SUB>(F0, F1, F2, mulw(hs.B[0][s], 256 * BLK_ROWS), mulw(hs.B[1][s], 256 * BLK_ROWS), mulw(hs.B[2][s], 256 * BLK_ROWS),
+                                          hs.bias12[s], hs.inv[s], hs.z0[s], hs.dz1[s], hs.dz2[s], hs.idKey[s], key);
+            }
+            return;
+        }
+        // the block against every (triangle, edge) pair, one pair per lane (<= 3 * HUGE_DIRECT = 18 pairs): an edge function is
+        // linear, so its extremes over the block's pixel centres are at the corners.  Outside one edge everywhere -> the triangle
+        // is skipped (a screen-filling ground quad is two triangles: every block but the diagonal's is outside one of them);
+        // inside all three everywhere -> no per-sample coverage test.  (Replaces a per-triangle bbox reject, which this subsumes.)
+        bool edgeOut = false, edgeCut = false;
+        if (lane < 3u * nHuge) {
+            const uint32_t s = lane / 3u, k = lane - 3u * s;
+            const int32_t A = hs.A[k][s], B = hs.B[k][s];
+            const long long E0 = hs.E[k][s] + mulw(A, 256 * bx0) + mulw(B, 256 * by0);
+            const long long dA = mulw(A, spanX), dB = mulw(B, spanY);
+            edgeOut = E0 + (dA > 0 ? dA : 0ll) + (dB > 0 ? dB : 0ll) < 0;
+            edgeCut = E0 + (dA < 0 ? dA : 0ll) + (dB < 0 ? dB : 0ll) < 0;
+        }
+        const unsigned mOut = __ballot_sync(0xFFFFFFFFu, edgeOut), mCut = __ballot_sync(0xFFFFFFFFu, edgeCut);
         for (uint32_t s = 0; s < nHuge; ++s) {
-            if (hs.maxX[s] < cx0 || hs.minX[s] > cx0 + spanX || hs.maxY[s] < cy0 || hs.minY[s] > cy0 + spanY) continue;
-            const long long F0 = hs.E[0][s] + mulw(hs.A[0][s], 256 * x) + mulw(hs.B[0][s], 256 * y);
+            const bool outside = ((mOut >> (3u * s)) & 7u) != 0u, inside = ((mCut >> (3u * s)) & 7u) == 0u;
+            if (outside) continue;
             const long long F1 = hs.E[1][s] + mulw(hs.A[1][s], 256 * x) + mulw(hs.B[1][s], 256 * y);
             const long long F2 = hs.E[2][s] + mulw(hs.A[2][s], 256 * x) + mulw(hs.B[2][s], 256 * y);
+            if (inside) {
+                test_samples_inside<SHADOW, SUB>(F1, F2, mulw(hs.B[1][s], 256 * BLK_ROWS), mulw(hs.B[2][s], 256 * BLK_ROWS),
+                                                 hs.bias12[s], hs.inv[s], hs.z0[s], hs.dz1[s], hs.dz2[s], hs.idKey[s], key);
+                continue;
+            }
+            const long long F0 = hs.E[0][s] + mulw(hs.A[0][s], 256 * x) + mulw(hs.B[0][s], 256 * y);
             test_samples<SHADOW, SUB>(F0, F1, F2, mulw(hs.B[0][s], 256 * BLK_ROWS), mulw(hs.B[1][s], 256 * BLK_ROWS), mulw(hs.B[2][s], 256 * BLK_ROWS),
                                       hs.bias12[s], hs.inv[s], hs.z0[s], hs.dz1[s], hs.dz2[s], hs.idKey[s], key);
         }
