@@ -31,7 +31,7 @@ __device__ __forceinline__ K0In k0_load(const PassConst& pc, uint32_t slot) {
     in.node = 0; in.p = in.n = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!in.valid) return in;
     // sort-first split: no visible 256-triangle block of this rank references this 256-slot block
-    if (CULL && __ldg(pc.slotBlockVisible + (slot >> 8)) == 0u) { in.valid = false; return in; }
+    if (CULL && __ldg(pc.slotBlockVisible + (slot >> 8)) != pc.cullStamp) { in.valid = false; return in; }
     // cacheBase is 3 * firstTri in de-indexed mode, so one table serves both layouts
     const uint32_t d = find_draw_block<true>(pc.draws, pc.nDraws, pc.slotBlockDraw, slot);
     uint32_t v = slot;
@@ -135,10 +135,19 @@ __global__ void __launch_bounds__(256) k_vertex_both(const __grid_constant__ Pas
 
 template <bool SHADOW, bool CULL>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
-    pdl_enter();
     const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
-    k0_prologue(pc);
-    if (SHADOW) k0_clear_shadow(pc);
+    if (CULL) {
+        // launched with PDL behind k_cull (an ordinary launch, so everything older has completed): the prologue and the map clear
+        // touch nothing k_cull does and run while it does; only the vertex loop needs its marks
+        asm volatile("griddepcontrol.launch_dependents;");
+        k0_prologue(pc);
+        if (SHADOW) k0_clear_shadow(pc);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    } else {
+        pdl_enter();
+        k0_prologue(pc);
+        if (SHADOW) k0_clear_shadow(pc);
+    }
     K0In in[K0_PER_THREAD];
 #pragma unroll
     for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW, CULL>(pc, base + 256u * k);
@@ -250,58 +259,55 @@ __device__ __forceinline__ void load_node_transform(const PassConst& pc, uint32_
 #pragma unroll
     for (int k = 0; k < 4; ++k) { const float4 q = Tq[k]; T[4 * k] = q.x; T[4 * k + 1] = q.y; T[4 * k + 2] = q.z; T[4 * k + 3] = q.w; }
 }
-// Once per pass and frame, ahead of K0: per-draw visibility (K0 skips the vertices of the other draws) ...
-template <bool SHADOW>
-__global__ void __launch_bounds__(128) k_cull_draws(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ visible,
-                                                    uint32_t* __restrict__ slotBlockVisible, uint32_t nSlotBlocks, uint32_t* __restrict__ cullCounts) {
-    // re-arm what k_cull_blocks fills: the slot-block marks and the length of the visible-block list
-    for (uint32_t i = blockIdx.x * 128u + threadIdx.x; i < nSlotBlocks; i += gridDim.x * 128u) slotBlockVisible[i] = 0u;
-    if (blockIdx.x == 0 && threadIdx.x == 0) cullCounts[0] = 0u;
-    const uint32_t d = blockIdx.x * 128u + threadIdx.x;
-    if (d >= pc.nDraws) return;
-    const uint32_t* b = bounds + 6 * (size_t)d;
-    if (b[0] > b[3]) { visible[d] = 0u; return; }   // draw without primitives
-    const float mn[3] = {dec_ordered(b[0]), dec_ordered(b[1]), dec_ordered(b[2])}, mx[3] = {dec_ordered(b[3]), dec_ordered(b[4]), dec_ordered(b[5])};
-    float T[16];
-    load_node_transform(pc, pc.draws[d].node, T);
-    visible[d] = box_touches_rank<SHADOW>(pc, T, mn, mx);
-}
-// ... and per 256-triangle block (K1 skips the other blocks: meshes come out of subdivision / the importer in spatially coherent
-// index order, so a block is a small patch).  blockBox[8 tb]: min xyz, draw (0xFFFFFFFF: the block spans draws), max xyz, pad.
+// Once per pass and frame, ahead of K0, ONE launch: per-draw visibility (K0 skips the vertices of the other draws; K1 asks it per
+// triangle in blocks that span draws) and per 256-triangle block (meshes come out of the re-ordering / the importer in spatially
+// coherent order, so a block is a small patch).  blockBox[2 tb]: min xyz, draw (0xFFFFFFFF: the block spans draws); [2 tb + 1]: max xyz.
 // A block that stays is appended to the compacted list K1 walks (one atomicAdd per warp; list order varies from frame to frame,
-// which no result depends on: every resolve is a minimum) and marks the 256-slot blocks of the post-transform cache its
-// triangles reference (table built once per draw list by k_block_slot_refs) for K0.
+// which no result depends on: every resolve is a minimum) and stamps the 256-slot blocks of the post-transform cache its triangles
+// reference (table built once per draw list by k_block_slot_refs) for K0.  Nothing is cleared per frame: the marks are a frame
+// stamp, and the list length alternates between two words (this launch zeroes the other one for the next frame).  A block thread
+// derives its draw's visibility itself instead of waiting for the per-draw pass (two launches, each ~6 us of latency, became one).
 template <bool SHADOW>
-__global__ void __launch_bounds__(128) k_cull_blocks(const __grid_constant__ PassConst pc, const float4* __restrict__ blockBox, const uint32_t* __restrict__ drawVisible,
-                                                     uint32_t nBlocks, uint32_t* __restrict__ visible, const uint32_t* __restrict__ refs,
-                                                     uint32_t* __restrict__ slotBlockVisible, uint32_t* __restrict__ list, uint32_t* __restrict__ cullCounts) {
-    const uint32_t tb = blockIdx.x * 128u + threadIdx.x;
+__global__ void __launch_bounds__(128) k_cull(const __grid_constant__ PassConst pc, const uint32_t* __restrict__ bounds, uint32_t* __restrict__ drawVisible,
+                                              const float4* __restrict__ blockBox, uint32_t nBlocks, uint32_t* __restrict__ visible, const uint32_t* __restrict__ refs,
+                                              uint32_t* __restrict__ slotBlockVisible, uint32_t* __restrict__ list, uint32_t* __restrict__ count, uint32_t* __restrict__ nextCount) {
+    const uint32_t i = blockIdx.x * 128u + threadIdx.x;
+    if (i == 0) *nextCount = 0u;
+    auto draw_visible = [&](uint32_t d) -> uint32_t {
+        const uint32_t* b = bounds + 6 * (size_t)d;
+        if (b[0] > b[3]) return 0u;   // draw without primitives
+        const float mn[3] = {dec_ordered(b[0]), dec_ordered(b[1]), dec_ordered(b[2])}, mx[3] = {dec_ordered(b[3]), dec_ordered(b[4]), dec_ordered(b[5])};
+        float T[16];
+        load_node_transform(pc, pc.draws[d].node, T);
+        return box_touches_rank<SHADOW>(pc, T, mn, mx);
+    };
+    if (i < pc.nDraws) drawVisible[i] = draw_visible(i);
     uint32_t vis = 0u;
-    if (tb < nBlocks) {
-        const float4 lo = blockBox[2 * (size_t)tb], hi = blockBox[2 * (size_t)tb + 1];
+    if (i < nBlocks) {
+        const float4 lo = blockBox[2 * (size_t)i], hi = blockBox[2 * (size_t)i + 1];
         const uint32_t d = __float_as_uint(lo.w);
         if (d == 0xFFFFFFFFu) vis = BLOCK_MIXED;   // the block spans draws: K1 asks per triangle whether its draw is visible
-        else if (drawVisible[d] != 0u) {
+        else if (draw_visible(d) != 0u) {
             const float mn[3] = {lo.x, lo.y, lo.z}, mx[3] = {hi.x, hi.y, hi.z};
             float T[16];
             load_node_transform(pc, pc.draws[d].node, T);
             vis = box_touches_rank<SHADOW>(pc, T, mn, mx);
         }
-        visible[tb] = vis;
+        visible[i] = vis;
     }
     const unsigned m = __ballot_sync(0xFFFFFFFFu, vis != 0u);
     if (!m) return;
     const unsigned lane = threadIdx.x & 31u;
     uint32_t base = 0;
-    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(cullCounts, (uint32_t)__popc(m));
+    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(count, (uint32_t)__popc(m));
     base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
     if (vis == 0u) return;
-    list[base + __popc(m & ((1u << lane) - 1u))] = tb;
-    const uint32_t* r = refs + (size_t)tb * BLOCK_REFS;
+    list[base + __popc(m & ((1u << lane) - 1u))] = i;
+    const uint32_t* r = refs + (size_t)i * BLOCK_REFS;
     const uint32_t n = r[0];
     REB_ASSERT(n == 0xFFFFFFFFu ? (r[1] <= r[2] && r[2] < (pc.cacheSize + 255u) / 256u) : n < (uint32_t)BLOCK_REFS);
-    if (n == 0xFFFFFFFFu) { for (uint32_t b = r[1]; b <= r[2]; ++b) slotBlockVisible[b] = 1u; }
-    else for (uint32_t i = 0; i < n; ++i) slotBlockVisible[r[1 + i]] = 1u;
+    if (n == 0xFFFFFFFFu) { for (uint32_t b = r[1]; b <= r[2]; ++b) slotBlockVisible[b] = pc.cullStamp; }
+    else for (uint32_t k = 0; k < n; ++k) slotBlockVisible[r[1 + k]] = pc.cullStamp;
 }
 // Once per draw list: the distinct 256-slot blocks the triangles of every 256-triangle block reference (with slots in first-use
 // order of a Morton-ordered stream: its own run of new slots plus a few runs shared with neighbouring patches).  One CTA per
@@ -385,18 +391,12 @@ void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st)
     if (pc.nTris == 0) return;
     k_block_bounds<<<(pc.nTris + 255u) / 256u, 256, 0, st>>>(pc, blockBox);
 }
-void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, const uint32_t* refs,
-                        uint32_t* slotBlockVisible, uint32_t* list, uint32_t* cullCounts, cudaStream_t st) {
-    if (nBlocks == 0) return;
-    if (shadow) k_cull_blocks<true><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible, refs, slotBlockVisible, list, cullCounts);
-    else k_cull_blocks<false><<<(nBlocks + 127u) / 128u, 128, 0, st>>>(pc, blockBox, drawVisible, nBlocks, visible, refs, slotBlockVisible, list, cullCounts);
-}
-void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, uint32_t* slotBlockVisible, uint32_t nSlotBlocks, uint32_t* cullCounts,
-                       cudaStream_t st) {
-    if (pc.nDraws == 0) return;
-    const uint32_t grid = std::max((pc.nDraws + 127u) / 128u, std::min((nSlotBlocks + 127u) / 128u, 64u));
-    if (shadow) k_cull_draws<true><<<grid, 128, 0, st>>>(pc, bounds, visible, slotBlockVisible, nSlotBlocks, cullCounts);
-    else k_cull_draws<false><<<grid, 128, 0, st>>>(pc, bounds, visible, slotBlockVisible, nSlotBlocks, cullCounts);
+void launch_cull(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* drawVisible, const float4* blockBox, uint32_t nBlocks, uint32_t* visible,
+                 const uint32_t* refs, uint32_t* slotBlockVisible, uint32_t* list, uint32_t* count, uint32_t* nextCount, cudaStream_t st) {
+    const uint32_t n = std::max(nBlocks, pc.nDraws);
+    if (n == 0) return;
+    if (shadow) k_cull<true><<<(n + 127u) / 128u, 128, 0, st>>>(pc, bounds, drawVisible, blockBox, nBlocks, visible, refs, slotBlockVisible, list, count, nextCount);
+    else k_cull<false><<<(n + 127u) / 128u, 128, 0, st>>>(pc, bounds, drawVisible, blockBox, nBlocks, visible, refs, slotBlockVisible, list, count, nextCount);
 }
 
 void launch_vertex_both(const PassConst& ps, const PassConst& pf, cudaStream_t st) {

@@ -35,7 +35,7 @@ struct PassState {               // per pass kind: 0 = shadow, 1 = forward (opaq
     uint32_t* drawBounds = nullptr; uint32_t* drawVisible = nullptr; uint32_t cullCap = 0;
     float4* blockBox = nullptr; uint32_t* blockVisible = nullptr; uint32_t blockCullCap = 0;
     uint32_t* blockRefs = nullptr; uint32_t* triBlockList = nullptr; uint32_t* cullCounts = nullptr;   // [triBlocks * BLOCK_REFS], [triBlocks], [4]
-    uint32_t* slotBlockVisible = nullptr; uint32_t slotBlocks = 0, slotBlockCap = 0;   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
+    uint32_t* slotBlockVisible = nullptr; uint32_t slotBlocks = 0, slotBlockCap = 0; uint32_t cullStamp = 0;   // marks of frame f carry stamp f; cullCounts[f & 1] is its list length   // the same per 256-triangle block   // sort-first split: per-draw object-space bounds (encoded), per-frame visibility
     // re-ordered list (k_reorder.cu): source streams in slot order, K1's {slots, submission ID} stream
     float4* posS = nullptr; float4* nrmS = nullptr; size_t streamCap = 0; uint4* triStream = nullptr; size_t triStreamCap = 0; bool reordered = false;
     bool valid = false;          // dDraws / cache layout match `draws` and the current geometry
@@ -330,12 +330,14 @@ int set_draws(reb_ctx* ctx, int kind, const reb_draw* draws, uint32_t n) {
             if ((rc = dev_alloc(ctx, &ps.blockBox, (size_t)ps.triBlocks * 2)) || (rc = dev_alloc(ctx, &ps.blockVisible, (size_t)ps.triBlocks)) ||
                 (rc = dev_alloc(ctx, &ps.blockRefs, (size_t)ps.triBlocks * BLOCK_REFS)) || (rc = dev_alloc(ctx, &ps.triBlockList, (size_t)ps.triBlocks)) ||
                 (rc = dev_alloc(ctx, &ps.cullCounts, (size_t)4))) return rc;
+            CU(cudaMemsetAsync(ps.cullCounts, 0, 16, ctx->stream));
             ps.blockCullCap = ps.triBlocks;
         }
         ps.slotBlocks = (uint32_t)((slots + 255) / 256);
         if (ps.slotBlocks > ps.slotBlockCap) {
             int rc;
             if ((rc = dev_alloc(ctx, &ps.slotBlockVisible, (size_t)ps.slotBlocks))) return rc;
+            CU(cudaMemsetAsync(ps.slotBlockVisible, 0, (size_t)ps.slotBlocks * 4, ctx->stream));   // no stamp yet
             ps.slotBlockCap = ps.slotBlocks;
         }
     }
@@ -410,7 +412,7 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
     pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
     pc.blockVisible = pc.drawVisible ? ps.blockVisible : nullptr;
-    if (pc.drawVisible) { pc.triBlockList = ps.triBlockList; pc.cullCounts = ps.cullCounts; pc.slotBlockVisible = ps.slotBlockVisible; }
+    if (pc.drawVisible) { pc.triBlockList = ps.triBlockList; pc.cullCounts = ps.cullCounts; pc.slotBlockVisible = ps.slotBlockVisible; }   // (run_pass picks the stamp and the length word)
 }
 
 // Everything a pass needs before its kernels can be enqueued: queue capacities, texture table, kernel parameters.
@@ -465,8 +467,14 @@ static void sky_ray_matrix(const float* view, const float* proj, float* out9) {
         for (int c = 0; c < 3; ++c) out9[3 * c + r] = (float)(adj[r][c] / det);
 }
 
-int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
+int run_pass(reb_ctx* ctx, int kind, const PassConst& pcIn, bool vertexDone) {
     PassState& ps = ctx->pass[kind];
+    PassConst pcFrame = pcIn;
+    if (pcFrame.drawVisible) {   // one k_cull launch per run: its stamp, and which of the two list-length words it counts in
+        ++ps.cullStamp;
+        pcFrame.cullStamp = ps.cullStamp; pcFrame.cullCounts = ps.cullCounts + (ps.cullStamp & 1u);
+    }
+    const PassConst& pc = pcFrame;
     // slots: 0 clear, 1 vertex stage, 2 setup + small raster (+ tile counts/layout), 3 bin scatter, 4 tile stage
     const bool fusedShadow = vertexDone && kind == 0;   // slots 0-1 were stamped before the fused two-pass vertex kernel
     auto mark = [&](int i) { if (ctx->profiling && !(fusedShadow && i < 2)) cudaEventRecord(ctx->ev[kind][i], ctx->stream); };
@@ -477,11 +485,11 @@ int run_pass(reb_ctx* ctx, int kind, const PassConst& pc, bool vertexDone) {
     }
     mark(1);
     if (ps.nTris && pc.drawVisible) {
-        launch_cull_draws(pc, kind == 0, ps.drawBounds, ps.drawVisible, ps.slotBlockVisible, ps.slotBlocks, ps.cullCounts, ctx->stream);
-        launch_cull_blocks(pc, kind == 0, ps.blockBox, ps.drawVisible, ps.triBlocks, ps.blockVisible, ps.blockRefs, ps.slotBlockVisible, ps.triBlockList, ps.cullCounts, ctx->stream);
-        ctx->launches += 2;
+        launch_cull(pc, kind == 0, ps.drawBounds, ps.drawVisible, ps.blockBox, ps.triBlocks, ps.blockVisible, ps.blockRefs, ps.slotBlockVisible, ps.triBlockList,
+                    ps.cullCounts + (pc.cullStamp & 1u), ps.cullCounts + ((pc.cullStamp + 1u) & 1u), ctx->stream);
+        ctx->launches++;
     }
-    if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/false, ctx->stream); ctx->launches++; }
+    if (ps.nTris && !vertexDone) { launch_vertex(pc, kind == 0, /*pdl=*/pc.drawVisible != nullptr, ctx->stream); ctx->launches++; }   // (PDL behind k_cull: K0's prologue and clear overlap it)
     mark(2);
     ShadeConst sh;
     if (kind == 1) {

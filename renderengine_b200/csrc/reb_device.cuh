@@ -129,6 +129,7 @@ struct PassConst {
     // number is cullCounts[0]; K1 walks this list instead of all blocks), and which 256-slot blocks of the post-transform cache
     // those blocks reference (K0 skips the others).  NULL without culling.
     const uint32_t* triBlockList; const uint32_t* cullCounts; const uint32_t* slotBlockVisible;
+    uint32_t cullStamp;           // slotBlockVisible[b] == cullStamp: marked this frame (a stamp instead of a clear; cullCounts alternates between two words)
 };
 constexpr int BLOCK_REFS = 16;   // words per 256-triangle block in the slot-block reference table: [0] count (0xFFFFFFFF: a range [1]..[2]), then block ids
 

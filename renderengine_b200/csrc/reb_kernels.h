@@ -51,11 +51,11 @@ void launch_vertex_both(const PassConst& shadowPass, const PassConst& forwardPas
 void launch_mip_down(const void* src, void* dst, uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh, cudaStream_t st);
 void launch_draw_ranges(const uint32_t* indices, const DrawDev* draws, uint32_t nDraws, uint32_t* ranges, cudaStream_t st);
 void launch_draw_bounds(const uint32_t* indices, const float4* pos4, const DrawDev* draws, uint32_t nDraws, uint32_t* bounds, cudaStream_t st);
-void launch_cull_draws(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* visible, uint32_t* slotBlockVisible, uint32_t nSlotBlocks, uint32_t* cullCounts,
-                       cudaStream_t st);   // sort-first split: per-draw row-band culling
+// sort-first split, one launch per pass and frame: per-draw + per-256-triangle-block row-band culling, the compacted list of visible
+// blocks for K1 (its length in *count; *nextCount is zeroed for the next frame) and the frame-stamped slot-block marks for K0
+void launch_cull(const PassConst& pc, bool shadow, const uint32_t* bounds, uint32_t* drawVisible, const float4* blockBox, uint32_t nBlocks, uint32_t* visible,
+                 const uint32_t* refs, uint32_t* slotBlockVisible, uint32_t* list, uint32_t* count, uint32_t* nextCount, cudaStream_t st);
 void launch_block_bounds(const PassConst& pc, float4* blockBox, cudaStream_t st);   // per 256-triangle block, once per draw list
-void launch_cull_blocks(const PassConst& pc, bool shadow, const float4* blockBox, const uint32_t* drawVisible, uint32_t nBlocks, uint32_t* visible, const uint32_t* refs,
-                        uint32_t* slotBlockVisible, uint32_t* list, uint32_t* cullCounts, cudaStream_t st);
 void launch_block_slot_refs(const PassConst& pc, uint32_t* refs, cudaStream_t st);   // once per draw list: slot blocks referenced by every 256-triangle block
 void launch_setup_raster(const PassConst& pc, bool shadow, int numSMs, cudaStream_t st);
 void launch_flatten_slots(const PassConst& pc, uint32_t* flat, uint32_t* triMaterial, cudaStream_t st);
