@@ -14,7 +14,7 @@ N > 1 (torchrun, one rank per GPU): the two splits BASELINE.json names, in one i
                 and triangle setup overlap the transfer.  Weak scaling (views per rank fixed).  `view_batch` repeats the figure next
                 to the same rank-local workload WITHOUT any exchange, measured in the same run (the single-GPU rate).
     sort_first = config 4: ONE 7680x4320 frame of the 10.5 M-triangle scene split into row bands (per-draw / per-block culling, the
-                shadow pass split into row slabs + one NCCL all-gather, overlapped the same way) — ms / frame at N next to the
+                shadow pass split between the ranks + one NCCL all-reduce MIN / all-gather, overlapped the same way) — ms / frame at N next to the
                 unsplit frame on one GPU in the same run.
     comm      = bytes and CUDA-event time of the collectives; parity_n = same-run bit comparisons of the exchanged / composed buffers.
 
@@ -154,7 +154,7 @@ def workload_string(args, world, scene, mode):
     if mode == "views":
         return (f"C5 view batch: {T} tris / {V} verts, {W}x{H} per view, {args.views_per_rank} views per GPU and step, shadow {S}^2 3x3 PCF rendered once per step" + tail)
     if mode == "tiles":
-        return f"C4 sort-first: {T} tris / {V} verts, ONE {W}x{H} frame split into row bands, shadow {S}^2 3x3 PCF rendered once (row slabs)" + tail
+        return f"C4 sort-first: {T} tris / {V} verts, ONE {W}x{H} frame split into row bands, shadow {S}^2 3x3 PCF rendered once (shared between the ranks)" + tail
     return f"{scene['config']}: {T} tris / {V} verts, {W}x{H}, shadow {S}^2 3x3 PCF, full frame (shadow + forward) per step" + tail
 
 
@@ -729,18 +729,21 @@ def run_sort_first(args, torch, dist, rank, world, local_rank, flush, peak):
     want = rig.hashes(rows=own)
     want_map = hashlib.sha256(ctx.readback(capi.REB_SHADOW_F32).tobytes()).hexdigest()
     # ---- (b) the split frame ----------------------------------------------------------------------------------------------------
-    slab = parallel.slab_rows(S, world)
+    slab = parallel.slab_rows(S, world) if args.shadow_split == "rows" else None
+    by_tris = args.shadow_split == "triangles"
     ctx.set_partition(rank, world, band_h)
     if slab:
         ctx.set_shadow_partition(rank, world, slab)
+    elif by_tris:
+        ctx.set_shadow_split(rank, world)          # sort-last: an equal share of the triangle stream into a whole map on every rank
     shadow_t = rig.shadow_tensor()
     comm = torch.cuda.Stream()
     ready = torch.cuda.Event()
     comm_ev = []
 
     def step(record_comm=False):
-        if slab or rank == 0:
-            ctx.render_shadow(rig.shadow_draws)            # this rank's row slab of the map (or the whole map on rank 0)
+        if slab or by_tris or rank == 0:
+            ctx.render_shadow(rig.shadow_draws)            # this rank's row slab / triangle share of the map (or the whole map on rank 0)
             ctx.flush()
         comm.wait_stream(st)
         with torch.cuda.stream(comm):
@@ -748,6 +751,8 @@ def run_sort_first(args, torch, dist, rank, world, local_rank, flush, peak):
                 a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True); a.record(comm)
             if slab:
                 parallel.allgather_shadow_slabs(shadow_t)  # NCCL all-gather in place: 4 S^2 / N bytes sent per rank
+            elif by_tris:
+                parallel.allreduce_shadow_min(shadow_t)    # NCCL all-reduce (MIN) in place: the minimum of the ranks' whole maps
             else:
                 parallel.broadcast_shadow(shadow_t, src=0)
             if record_comm:
@@ -778,8 +783,11 @@ def run_sort_first(args, torch, dist, rank, world, local_rank, flush, peak):
            "single_gpu_same_run": {"ms_per_frame": single_ms, "ms_per_frame_slowest_rank": single_max, "value": T / (single_ms * 1e3)},
            "speedup_vs_single_gpu_same_run": single_ms / ms,
            "parallelism": f"sort-first row bands x{world} (band_h {band_h}, {args.bands_per_rank} bands per rank, per-draw + per-block culling); shadow map: " +
-                          (f"{slab}-row slabs + in-place NCCL all-gather" if slab else "rank 0 + NCCL broadcast") + ", on its own stream; the forward tile stage waits for it",
-           "comm": {"collective": "ncclAllGather" if slab else "ncclBroadcast", "bytes_sent_per_rank": 4 * S * S // world if slab else 4 * S * S,
+                          (f"{slab}-row slabs + in-place NCCL all-gather" if slab else
+                           "split by triangles (equal shares of the stream into whole maps) + in-place NCCL all-reduce MIN" if by_tris else "rank 0 + NCCL broadcast") +
+                          ", on its own stream; the forward tile stage waits for it",
+           "comm": {"collective": "ncclAllGather" if slab else "ncclAllReduce(min)" if by_tris else "ncclBroadcast",
+                    "bytes_sent_per_rank": 4 * S * S // world if slab else 4 * S * S, "payload_bytes": 4 * S * S,
                     "event_ms_per_frame": comm_ms},
            "parity_n": {"own_bands_equal_unsplit_frame": all_true(torch, dist, got == want),
                         "gathered_map_equals_local_render": all_true(torch, dist, got_map == want_map)},
@@ -812,6 +820,9 @@ def main():
     ap.add_argument("--mode", default="auto", choices=["auto", "frame", "views", "tiles", "replicas"],
                     help="auto: N = 1 -> the C2 frame; N > 1 -> the C5 view batch as headline + the C4 sort-first record")
     ap.add_argument("--views-per-rank", type=int, default=64, help="C5: 512 views over 8 GPUs")
+    ap.add_argument("--shadow-split", choices=["triangles", "rows", "broadcast"], default="triangles",
+                    help="sort-first: how the shadow pass is shared: triangles = every rank rasterises an equal share of the triangle stream into a whole map, "
+                         "all-reduce MIN (reb_set_shadow_split); rows = row slabs + all-gather (reb_set_shadow_partition); broadcast = rank 0 renders it")
     ap.add_argument("--bands-per-rank", type=int, default=3,
                     help="sort-first: row bands per rank, interleaved (1 = one contiguous band: least geometry per rank after culling but unbalanced; 0 = 64-row bands)")
     ap.add_argument("--sort-first-frames", type=int, default=10)

@@ -157,6 +157,14 @@ int reb_set_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t ban
  * and calls reb_shadow_mark_valid.  With reb_set_partition (or reb_params.rank / n_ranks) the forward pass likewise skips
  * draws whose projected bounds touch none of this rank's rows. */
 int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint32_t bandH);
+/* Sort-LAST split of the shadow pass, the alternative to the row slabs above: this context rasterises the rank-th of nRanks
+ * contiguous ranges of the draw list's triangle stream — equal shares of the work whatever the light sees where, nothing
+ * culled and nothing rasterised twice at slab borders — into the WHOLE map (cleared to 1.0 first).  The complete map is the
+ * element-wise minimum of the ranks' maps: after reb_flush, ncclAllReduce(ncclMin, ncclFloat) in place on the buffer
+ * reb_get_output(REB_SHADOW_F32) returns (depths are non-negative floats), then reb_shadow_mark_valid / reb_shadow_wait_event.
+ * 4 S^2 bytes are reduced per frame instead of 4 S^2 / n gathered.  Replaces a reb_set_shadow_partition; (0, 1) turns the split off.  No counterpart in the reference. */
+int reb_set_shadow_split(reb_ctx* ctx, uint32_t rank, uint32_t nRanks);
+
 /* marks the shadow map as valid after its storage (reb_get_output REB_SHADOW_F32) was filled externally,
  * e.g. by an NCCL broadcast from the rank that rendered it */
 int reb_shadow_mark_valid(reb_ctx* ctx, uint32_t shadowId);

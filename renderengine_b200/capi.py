@@ -17,7 +17,7 @@ SYMBOLS = [
     "reb_upload_materials", "reb_upload_lights", "reb_register_texture", "reb_shadow_create", "reb_shadow_set_transform",
     "reb_set_view", "reb_render_shadow", "reb_render_forward", "reb_get_output", "reb_readback", "reb_sync", "reb_flush", "reb_readback_async", "reb_set_shading_model", "reb_set_skybox", "reb_set_sample_count", "reb_set_shadow_partition", "reb_render_forward2",
     "reb_set_partition", "reb_shadow_mark_valid", "reb_shadow_wait_event", "reb_get_counters", "reb_get_launch_count", "reb_set_profiling",
-    "reb_get_kernel_times", "reb_shadow_depth_static",
+    "reb_get_kernel_times", "reb_shadow_depth_static", "reb_set_shadow_split",
 ]
 REB_STATIC_MAX_VERTICES, REB_STATIC_MAX_TRIANGLES = 262144, 524288
 
@@ -72,6 +72,7 @@ def load():
     lib.reb_set_skybox.argtypes = [vp, vp, u32, u32]
     lib.reb_set_sample_count.argtypes = [vp, u32]
     lib.reb_set_shadow_partition.argtypes = [vp, u32, u32, u32]
+    lib.reb_set_shadow_split.argtypes = [vp, u32, u32]
     lib.reb_readback_async.argtypes = [vp, C.c_int, vp]
     lib.reb_set_partition.argtypes = [vp, u32, u32, u32]
     lib.reb_shadow_mark_valid.argtypes = [vp, u32]
@@ -266,6 +267,11 @@ class Context:
     def set_shadow_partition(self, rank, n_ranks, band_h):
         """Row split of the shadow pass (slabs of band_h rows, band_h % 32 == 0); fill the other rows, then shadow_mark_valid()."""
         self._ck(self.lib.reb_set_shadow_partition(self.h, rank, n_ranks, band_h))
+
+    def set_shadow_split(self, rank, n_ranks):
+        """Sort-last split of the shadow pass: this context rasterises its share of the triangle stream into the whole map; combine the
+        ranks' maps with an element-wise minimum (parallel.allreduce_shadow_min)."""
+        self._ck(self.lib.reb_set_shadow_split(self.h, rank, n_ranks))
 
     def shadow_mark_valid(self):
         self._ck(self.lib.reb_shadow_mark_valid(self.h, self.shadow_id))

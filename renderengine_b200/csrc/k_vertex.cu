@@ -281,9 +281,15 @@ __global__ void __launch_bounds__(128) k_cull(const __grid_constant__ PassConst 
         load_node_transform(pc, pc.draws[d].node, T);
         return box_touches_rank<SHADOW>(pc, T, mn, mx);
     };
-    if (i < pc.nDraws) drawVisible[i] = draw_visible(i);
+    if (SHADOW && pc.splitN > 1u) {   // sort-last split: a contiguous range of the block stream, every draw "visible"
+        if (i < pc.nDraws) drawVisible[i] = 1u;
+    } else if (i < pc.nDraws) drawVisible[i] = draw_visible(i);
     uint32_t vis = 0u;
-    if (i < nBlocks) {
+    if (SHADOW && pc.splitN > 1u) {
+        const uint32_t lo = (uint32_t)((unsigned long long)nBlocks * pc.splitRank / pc.splitN), hi = (uint32_t)((unsigned long long)nBlocks * (pc.splitRank + 1u) / pc.splitN);
+        vis = (i >= lo && i < hi) ? 1u : 0u;
+        if (i < nBlocks) visible[i] = vis;
+    } else if (i < nBlocks) {
         const float4 lo = blockBox[2 * (size_t)i], hi = blockBox[2 * (size_t)i + 1];
         const uint32_t d = __float_as_uint(lo.w);
         if (d == 0xFFFFFFFFu) vis = BLOCK_MIXED;   // the block spans draws: K1 asks per triangle whether its draw is visible

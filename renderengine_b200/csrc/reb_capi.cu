@@ -51,6 +51,7 @@ struct reb_ctx {
     uint32_t W = 0, H = 0, outputs = 0, maxDesc = 8192;
     uint32_t rank = 0, nRanks = 1, bandH = 64;
     uint32_t sRank = 0, sNRanks = 1, sBandH = 64;   // row split of the shadow map (reb_set_shadow_partition)
+    uint32_t sSplitRank = 0, sSplitN = 1;           // sort-last split of the shadow pass (reb_set_shadow_split)
     // geometry (SoA streams)
     float4* pos4 = nullptr; float4* nrm4 = nullptr; uint32_t* indices = nullptr; uint64_t nVerts = 0, nIdx = 0;
     float* transforms = nullptr; float* nmats = nullptr; uint32_t nNodes = 0;
@@ -403,14 +404,15 @@ void fill_pass(reb_ctx* ctx, int kind, PassConst& pc) {
     pc.status = ctx->dStatus + STATUS_WORDS * kind;
     pc.hostStatus = ctx->hStatusDev ? ctx->hStatusDev + 8 * kind : nullptr;
     if (kind >= 1) { pc.rank = ctx->rank; pc.nRanks = ctx->nRanks; pc.bandH = ctx->bandH; }
-    else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; }
+    else { pc.rank = ctx->sRank; pc.nRanks = ctx->sNRanks; pc.bandH = ctx->sBandH; pc.splitRank = ctx->sSplitRank; pc.splitN = ctx->sSplitN; }
     pc.bandRows = pc.tilesY; pc.vTilesY = pc.tilesY;
     if (pc.nRanks > 1) {
         pc.bandRows = pc.bandH / TILE_H; pc.vTilesY = 0;
         for (uint32_t b = pc.rank; b * pc.bandRows < pc.tilesY; b += pc.nRanks) pc.vTilesY += std::min(pc.bandRows, pc.tilesY - b * pc.bandRows);
     }
     static const bool noCull = std::getenv("REB_NO_DRAW_CULL") != nullptr;
-    pc.drawVisible = (pc.nRanks > 1 && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
+    pc.drawVisible = ((pc.nRanks > 1 || pc.splitN > 1) && !noCull && ps.nDraws) ? ps.drawVisible : nullptr;
+    if (!pc.drawVisible) pc.splitN = 0;   // (REB_NO_DRAW_CULL: every rank rasterises everything; the minimum is the same)
     pc.blockVisible = pc.drawVisible ? ps.blockVisible : nullptr;
     if (pc.drawVisible) { pc.triBlockList = ps.triBlockList; pc.cullCounts = ps.cullCounts; pc.slotBlockVisible = ps.slotBlockVisible; }   // (run_pass picks the stamp and the length word)
 }
@@ -597,7 +599,7 @@ int submit_forward(reb_ctx* ctx) {
     const PassState &s0 = ctx->pass[0], &s1 = ctx->pass[1];
     const bool fuse = ctx->shadowDeferred && s0.nTris && s1.nTris && s0.deindexed == s1.deindexed && s0.cacheSize == s1.cacheSize &&
                       s0.draws.size() == s1.draws.size() && std::memcmp(s0.draws.data(), s1.draws.data(), s0.draws.size() * sizeof(reb_draw)) == 0 &&
-                      ctx->nRanks <= 1 && ctx->sNRanks <= 1 &&   // a split pass culls draws per rank: its K0 is not the other pass's
+                      ctx->nRanks <= 1 && ctx->sNRanks <= 1 && ctx->sSplitN <= 1 &&   // a split pass culls per rank: its K0 is not the other pass's
                       !std::getenv("REB_NO_FUSED_VERTEX");
     if (!fuse) {
         if ((rc = flush_deferred(ctx))) return rc;

@@ -444,6 +444,17 @@ int reb_set_shadow_partition(reb_ctx* ctx, uint32_t rank, uint32_t nRanks, uint3
     CU(cudaSetDevice(ctx->device));
     { int frc = flush_deferred(ctx); if (frc) return frc; }
     ctx->sRank = rank; ctx->sNRanks = nRanks; ctx->sBandH = bandH;
+    ctx->sSplitRank = 0; ctx->sSplitN = 1;   // one split of the shadow pass at a time
+    return REB_OK;
+}
+
+int reb_set_shadow_split(reb_ctx* ctx, uint32_t rank, uint32_t nRanks) {
+    CHECK_CTX();
+    if (nRanks == 0 || rank >= nRanks) return fail(ctx, REB_E_INVALID, "reb_set_shadow_split: need rank < nRanks");
+    CU(cudaSetDevice(ctx->device));
+    { int frc = flush_deferred(ctx); if (frc) return frc; }
+    ctx->sSplitRank = rank; ctx->sSplitN = nRanks;
+    ctx->sRank = 0; ctx->sNRanks = 1;
     return REB_OK;
 }
 

@@ -129,6 +129,10 @@ struct PassConst {
     // number is cullCounts[0]; K1 walks this list instead of all blocks), and which 256-slot blocks of the post-transform cache
     // those blocks reference (K0 skips the others).  NULL without culling.
     const uint32_t* triBlockList; const uint32_t* cullCounts; const uint32_t* slotBlockVisible;
+    // sort-LAST split of the shadow pass (reb_set_shadow_split): this rank rasterises the splitRank-th of splitN contiguous ranges of
+    // K1's block stream into the WHOLE map (no row filter: nRanks stays 1) and the ranks' maps are combined with an element-wise
+    // minimum.  (A triangle of the broadcast list is seen by the one rank whose range holds it, which rasterises all of it.)  0 / 1 = off.
+    uint32_t splitRank, splitN;
     uint32_t cullStamp;           // slotBlockVisible[b] == cullStamp: marked this frame (a stamp instead of a clear; cullCounts alternates between two words)
 };
 constexpr int BLOCK_REFS = 16;   // words per 256-triangle block in the slot-block reference table: [0] count (0xFFFFFFFF: a range [1]..[2]), then block ids

@@ -5,7 +5,8 @@ plumbing.  Backend-agnostic (nccl on the GPU box, gloo in the CPU tests).
     rank 0 and broadcast (NCCL over NVLink on the box).
   * sort-first row bands (config C4): rank r owns pixel rows y with (y // band_h) % world == r; geometry is replicated;
     the optional final exchange all-gathers every rank's frame and keeps the owned rows.
-No data-path collective exists besides those two.
+    Its shadow pass is split either into row slabs (all-gather) or by triangles into whole maps (all-reduce MIN).
+No data-path collective exists besides those.
 """
 import numpy as np
 
@@ -50,6 +51,16 @@ def allgather_shadow_slabs(shadow_tensor):
     if rows is None:
         raise ValueError("shadow map rows must divide into equal slabs of a multiple of 32 rows")
     dist.all_gather_into_tensor(shadow_tensor, shadow_tensor[rank * rows:(rank + 1) * rows])
+    return shadow_tensor
+
+
+def allreduce_shadow_min(shadow_tensor):
+    """Shadow pass split by TRIANGLES (reb_set_shadow_split): every rank rasterised its share of the triangle stream into a whole
+    map; the element-wise minimum over the ranks (one in-place all-reduce of 4*S*S bytes; depths are non-negative floats) is the
+    map a single GPU renders, bit for bit."""
+    import torch.distributed as dist
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(shadow_tensor, op=dist.ReduceOp.MIN)
     return shadow_tensor
 
 

@@ -400,3 +400,42 @@ def test_parity_full_size_c2_multisampled_with_translucent_list():
     assert d8.max() <= 1, f"sRGB8 differs by {d8.max()} LSB at {np.count_nonzero(d8 > 1)} channel samples"
     n_opaque = int(sum(int(d[1]) // 3 for d in s["draws"]))
     assert ((ref["tri_id"] != 0xFFFFFFFF) & (ref["tri_id"] >= n_opaque)).any(axis=0).mean() > 0.05
+
+
+@pytest.mark.parametrize("config,world", [("small", 3), ("quads", 2), ("C2", 8)])
+def test_shadow_pass_split_by_triangles_min_of_the_ranks_maps(config, world):
+    """reb_set_shadow_split: every rank rasterises its contiguous share of the triangle stream into a whole map; the element-wise
+    minimum of the ranks' maps must be the oracle's map bit for bit.  `quads`: everything is large / huge (binned path + the row
+    split of the broadcast list); `C2`: full size, re-ordered list, eight ranks; light moved between frames on the same contexts."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = _quads_scene(40) if config == "quads" else sc.make_scene(config)
+    ctxs = []
+    for r in range(world):
+        c = capi.Context(64, 64)
+        c.upload_geometry(s["verts"], s["indices"]); c.upload_transforms(s["transforms"])
+        c.shadow_create(s["shadow_size"])
+        c.set_shadow_split(r, world)
+        ctxs.append(c)
+    lights = [(-0.3, -1.0, -0.2), (0.6, -1.0, 0.1)] if config != "C2" else [None]
+    for ld in lights:
+        s2 = dict(s)
+        if ld is not None:
+            ldn = np.asarray(ld, np.float32); ldn = ldn / np.linalg.norm(ldn)
+            s2["shadow_view"] = sc.to_flat(sc.light_view_matrix(ldn))
+        ref = orc.Oracle(s2).render_shadow()
+        got = np.ones_like(ref)
+        share = []
+        for c in ctxs:
+            c.shadow_set_transform(s2["shadow_view"], s2["shadow_proj"])
+            c.render_shadow(s["draws"]); c.flush(); c.sync()
+            m = c.readback(capi.REB_SHADOW_F32)
+            share.append(float((m < 1.0).mean()))
+            got = np.minimum(got, m)
+            assert c.counters()[0] == 0
+        assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), f"{np.count_nonzero(got.view(np.uint32) != ref.view(np.uint32))} texels differ"
+        assert min(share) < 0.9 * float((ref < 1.0).mean())                      # the work was split: some rank's map is visibly partial
+    # back to an unsplit pass on the same context
+    ctxs[0].set_shadow_split(0, 1)
+    ctxs[0].render_shadow(s["draws"]); ctxs[0].flush(); ctxs[0].sync()
+    assert np.array_equal(ctxs[0].readback(capi.REB_SHADOW_F32).view(np.uint32), ref.view(np.uint32))

@@ -112,3 +112,34 @@ def test_two_rank_shadow_slab_allgather():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def _min_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # every rank holds a whole map with its share of the "triangles" rasterised into it (here: every world-th texel) over 1.0
+        S = 64
+        g = torch.Generator().manual_seed(7)
+        full = torch.rand((S, S), generator=g, dtype=torch.float32)
+        mine = torch.ones((S, S), dtype=torch.float32)
+        sel = (torch.arange(S * S).reshape(S, S) % world) == rank
+        mine[sel] = full[sel]
+        parallel.allreduce_shadow_min(mine)
+        q.put((rank, bool(torch.equal(mine, full))))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_shadow_split_by_triangles_allreduce_min():
+    """Shadow pass split by triangles (reb_set_shadow_split): the element-wise minimum of the ranks' whole maps is the map."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_min_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]
