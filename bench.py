@@ -820,7 +820,7 @@ def main():
     ap.add_argument("--mode", default="auto", choices=["auto", "frame", "views", "tiles", "replicas"],
                     help="auto: N = 1 -> the C2 frame; N > 1 -> the C5 view batch as headline + the C4 sort-first record")
     ap.add_argument("--views-per-rank", type=int, default=64, help="C5: 512 views over 8 GPUs")
-    ap.add_argument("--shadow-split", choices=["triangles", "rows", "broadcast"], default="triangles",
+    ap.add_argument("--shadow-split", choices=["rows", "triangles", "broadcast"], default="rows",
                     help="sort-first: how the shadow pass is shared: triangles = every rank rasterises an equal share of the triangle stream into a whole map, "
                          "all-reduce MIN (reb_set_shadow_split); rows = row slabs + all-gather (reb_set_shadow_partition); broadcast = rank 0 renders it")
     ap.add_argument("--bands-per-rank", type=int, default=3,
