@@ -472,7 +472,7 @@ static void sky_ray_matrix(const float* view, const float* proj, float* out9) {
 int run_pass(reb_ctx* ctx, int kind, const PassConst& pcIn, bool vertexDone) {
     PassState& ps = ctx->pass[kind];
     PassConst pcFrame = pcIn;
-    if (pcFrame.drawVisible) {   // one k_cull launch per run: its stamp, and which of the two list-length words it counts in
+    if (pcFrame.drawVisible && ps.nTris) {   // exactly one k_cull launch per increment: its stamp, and which of the two list-length words it counts in
         ++ps.cullStamp;
         pcFrame.cullStamp = ps.cullStamp; pcFrame.cullCounts = ps.cullCounts + (ps.cullStamp & 1u);
     }
