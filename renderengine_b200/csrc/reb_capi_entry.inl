@@ -122,10 +122,14 @@ int reb_upload_transforms(reb_ctx* ctx, const float* m, uint32_t nNodes) {
     { int frc = flush_deferred(ctx); if (frc) return frc; }
     CU(cudaStreamSynchronize(ctx->stream));
     int rc;
-    if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
-    if ((rc = dev_alloc(ctx, &ctx->nmats, (size_t)nNodes * 12))) return rc;
+    if (nNodes != ctx->nNodes || !ctx->transforms) {
+        if ((rc = dev_alloc(ctx, &ctx->transforms, (size_t)nNodes * 16))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->nmats, (size_t)nNodes * 12))) return rc;
+    }
+    // draws are validated against the node count: a re-upload of the same number of nodes (moving objects) keeps the draw lists'
+    // preprocessing — cache layout, tables, the re-ordering — which depends on geometry and draws only
+    if (nNodes != ctx->nNodes) ctx->pass[0].valid = ctx->pass[1].valid = ctx->pass[2].valid = false;
     ctx->nNodes = nNodes;
-    ctx->pass[0].valid = ctx->pass[1].valid = ctx->pass[2].valid = false;   // draws are validated against the node count
     if (!nNodes) return REB_OK;
     std::vector<float> nm((size_t)nNodes * 12);
     for (uint32_t n = 0; n < nNodes; ++n) normal_matrix12(m + 16 * (size_t)n, &nm[12 * (size_t)n]);

@@ -439,3 +439,33 @@ def test_shadow_pass_split_by_triangles_min_of_the_ranks_maps(config, world):
     ctxs[0].set_shadow_split(0, 1)
     ctxs[0].render_shadow(s["draws"]); ctxs[0].flush(); ctxs[0].sync()
     assert np.array_equal(ctxs[0].readback(capi.REB_SHADOW_F32).view(np.uint32), ref.view(np.uint32))
+
+
+def test_moving_nodes_keep_the_draw_list_preprocessing():
+    """Re-uploading the same number of node transforms (objects moving between frames, SceneTree::UploadToGPU again) must not redo
+    the draw-list preprocessing, and the frames must follow the new transforms: parity against the oracle for three placements."""
+    from oracle import orc
+    from renderengine_b200 import capi, scene as sc
+    s = sc.make_scene("small")
+    ctx = capi.Context(s["width"], s["height"])
+    ctx.upload_scene(s)
+    ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"]); ctx.sync()
+    launches0 = None
+    rng = np.random.default_rng(3)
+    for k in range(3):
+        t = np.array(s["transforms"], np.float32).reshape(-1, 16).copy()
+        t[:-1, 12] += rng.uniform(-0.4, 0.4, t.shape[0] - 1).astype(np.float32)      # spheres slide in x and y; the ground stays
+        t[:-1, 13] += rng.uniform(0.0, 0.5, t.shape[0] - 1).astype(np.float32)
+        s2 = dict(s); s2["transforms"] = t
+        o = orc.Oracle(s2)
+        ref_shadow = o.render_shadow(); ref = o.render_forward(ref_shadow)
+        before = ctx.launch_count()
+        ctx.upload_transforms(t)
+        ctx.render_shadow(s["draws"]); ctx.render_forward(s["draws"]); ctx.sync()
+        n = ctx.launch_count() - before
+        launches0 = n if launches0 is None else launches0
+        assert n == launches0 and n <= 8, f"frame {k}: {n} launches (draw-list preprocessing re-run?)"
+        assert np.array_equal(ctx.readback(capi.REB_SHADOW_F32).view(np.uint32), ref_shadow.view(np.uint32))
+        assert np.array_equal(ctx.readback(capi.REB_TRIID_U32), ref["tri_id"])
+        assert np.array_equal(ctx.readback(capi.REB_DEPTH_F32).view(np.uint32), ref["depth"].view(np.uint32))
+        assert np.abs(ctx.readback(capi.REB_COLOR_SRGB8).astype(np.int32) - ref["color_srgb8"].astype(np.int32)).max() <= 1
