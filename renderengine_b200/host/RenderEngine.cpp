@@ -96,6 +96,16 @@ void Skybox::Remove() {
 }
 void Renderer::Submit() const { Check(reb_flush(m_ctx), "reb_flush"); }
 void Renderer::Readback(reb_output_kind kind, void* host) const { Check(reb_readback(m_ctx, kind, host), "reb_readback"); }
+void Renderer::SetPartition(uint32_t rank, uint32_t nRanks, uint32_t bandH) const { Check(reb_set_partition(m_ctx, rank, nRanks, bandH), "reb_set_partition"); }
+void Renderer::SetShadowPartition(uint32_t rank, uint32_t nRanks, uint32_t rows) const { Check(reb_set_shadow_partition(m_ctx, rank, nRanks, rows), "reb_set_shadow_partition"); }
+void Renderer::SetShadowSplit(uint32_t rank, uint32_t nRanks) const { Check(reb_set_shadow_split(m_ctx, rank, nRanks), "reb_set_shadow_split"); }
+float* Renderer::GetShadowMapDevicePointer() const {
+    void* p = nullptr; uint64_t bytes = 0;
+    Check(reb_get_output(m_ctx, REB_SHADOW_F32, &p, &bytes), "reb_get_output(REB_SHADOW_F32)");
+    return static_cast<float*>(p);
+}
+void Renderer::ShadowMapFilled() const { Check(reb_shadow_mark_valid(m_ctx, 0), "reb_shadow_mark_valid"); }
+void Renderer::ShadowMapArrivesWith(void* cudaEvent) const { Check(reb_shadow_wait_event(m_ctx, 0, cudaEvent), "reb_shadow_wait_event"); }
 std::vector<reb_draw> Renderer::ToDraws(const std::vector<MeshDrawInfo>& drawCalls) {
     std::vector<reb_draw> d(drawCalls.size());
     for (size_t i = 0; i < drawCalls.size(); ++i)

@@ -317,6 +317,13 @@ public:
     void SetSampleCount(uint32_t samples) const;           // 1 (default) or 4: PhysicalDevice::GetMsaaSamples analogue (PhysicalDevice.cpp:172-186), Swapchain.cpp:110-123
     void Submit() const;                                   // reb_flush (CommandRingBuffer submit analogue, RenderLoop.cpp:124-132)
     void Readback(reb_output_kind kind, void* host) const; // swapchain image -> host (headless present)
+    // multi-GPU (no counterpart in the reference: one vk::Device, Device.h:12-13); see host/demo_mgpu.cpp for a complete caller
+    void SetPartition(uint32_t rank, uint32_t nRanks, uint32_t bandH) const;        // sort-first row bands of the frame
+    void SetShadowPartition(uint32_t rank, uint32_t nRanks, uint32_t rows) const;   // shadow pass: row slabs, completed by an all-gather
+    void SetShadowSplit(uint32_t rank, uint32_t nRanks) const;                      // shadow pass: shares of the triangle stream, completed by an all-reduce (min)
+    float* GetShadowMapDevicePointer() const;                                       // the buffer those collectives run on
+    void ShadowMapFilled() const;                                                   // reb_shadow_mark_valid
+    void ShadowMapArrivesWith(void* cudaEvent) const;                               // reb_shadow_wait_event
     static std::vector<reb_draw> ToDraws(const std::vector<MeshDrawInfo>& drawCalls);
 private:
     reb_ctx* m_ctx = nullptr;
