@@ -124,7 +124,7 @@ def test_cpp_multi_gpu_caller_reproduces_the_single_gpu_frames():
     from renderengine_b200 import build
     build.build_host()
     exe = build.build_mgpu_demo()
-    n = max(1, min(torch.cuda.device_count(), 8))
+    n = max(1, min(torch.cuda.device_count(), 2))   # (measured at 1 and 2 GPUs; the binary itself takes any count)
     r = subprocess.run([exe, str(n), "5", "4", "3", "640", "368", "512", "3"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "PASS" in r.stdout and r.stdout.count(" 0 differing bytes") == 3, r.stdout   # two sort-first variants + the view batch
