@@ -340,6 +340,122 @@ __global__ void __launch_bounds__(256, 2) k_tl_resolve(const __grid_constant__ P
     else reinterpret_cast<float4*>(hdr)[p] = col;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------------------
+// The 1-sample resolve as three kernels (k_tl_resolve above does the same in one: 117-128 registers because the list replay and
+// the whole fragment shader are live together, 20 % occupancy, and a warp shades as many rounds as its longest list):
+//   k_tl_gather  per pixel: pull the list, order it by ID, replay ONLY the depth test (LessOrEqual + write) — which fragments pass is
+//                known without shading — and emit the passing ones, in order, as {pixel, id} records into a compact array (one
+//                atomicAdd per warp); leaves the final depth / ID and the pixel's span {first record, count}; light, full occupancy;
+//   k_tl_shade   one thread per PASSING FRAGMENT of the whole frame: the ordinary shade_pixel* at the fragment's pixel centre, colour
+//                stored; every lane busy, the shader's registers only;
+//   k_tl_blend   per pixel: blend the span's colours in order over the opaque colour (same three individually rounded operations per
+//                channel), then the skybox where the depth is still 1.0, then the encode.
+// ---------------------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_tl_gather(const __grid_constant__ PassConst pc, uint32_t* __restrict__ head, const uint4* __restrict__ nodes, uint32_t cap,
+                                                   uint32_t idBase, float* __restrict__ depth, uint32_t* __restrict__ outTriId, float* __restrict__ outDepth,
+                                                   uint2* __restrict__ span, uint2* __restrict__ frags, uint32_t* __restrict__ counters) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * 8u, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * 32 + 8 * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * 8 + 4 * (int)(warp >> 2) + (int)(lane >> 3);
+    const bool inb = x < (int)pc.W && y < (int)pc.H;
+    const size_t p = inb ? (size_t)y * pc.W + x : 0;
+    float d = inb ? depth[p] : 0.0f;
+    uint32_t lastId = TL_NONE;
+    uint32_t h = inb ? head[p] : TL_NONE;
+    uint32_t pass[TL_MAX_FRAGS];                 // IDs of the passing fragments, in order (fast path)
+    int nPass = 0;
+    bool longList = false;
+    if (h != TL_NONE) {
+        head[p] = TL_NONE;                       // re-armed for the next frame
+        uint32_t id[TL_MAX_FRAGS]; float z[TL_MAX_FRAGS];
+        int n = 0;
+        for (uint32_t q = h; q != TL_NONE && q < cap;) {
+            const uint4 nd = nodes[q];
+            if (n < TL_MAX_FRAGS) {
+                int i = n++;
+                while (i > 0 && id[i - 1] > nd.y) { id[i] = id[i - 1]; z[i] = z[i - 1]; --i; }
+                id[i] = nd.y; z[i] = __uint_as_float(nd.z);
+            } else { longList = true; break; }
+            q = nd.x;
+        }
+        if (!longList) {
+            for (int i = 0; i < n; ++i)
+                if (z[i] <= d) { pass[nPass++] = id[i]; d = z[i]; lastId = id[i]; }
+        } else {                                 // count first (selection walk), emit below with the same walk
+            float dd = d;
+            for (TlCursor c = tl_first(nodes, cap, h); c.id != TL_NONE; c = tl_next(nodes, cap, h, c.id))
+                if (c.z <= dd) { ++nPass; dd = c.z; }
+        }
+    }
+    // one allocation per warp
+    uint32_t incl = (uint32_t)nPass;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o); if ((int)lane >= o) incl += v; }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    uint32_t wbase = 0;
+    if (total) {
+        if (lane == 0) wbase = atomicAdd(&counters[6], total);
+        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 0);
+    }
+    if (!inb) return;
+    const uint32_t base = wbase + incl - (uint32_t)nPass;
+    if (nPass) {
+        if (!longList) {
+            for (int i = 0; i < nPass; ++i) if (base + i < cap) frags[base + i] = make_uint2((uint32_t)p, pass[i]);
+        } else {
+            uint32_t k = 0;
+            for (TlCursor c = tl_first(nodes, cap, h); c.id != TL_NONE; c = tl_next(nodes, cap, h, c.id))
+                if (c.z <= d) { if (base + k < cap) frags[base + k] = make_uint2((uint32_t)p, c.id); ++k; d = c.z; lastId = c.id; }
+        }
+        span[p] = make_uint2(base, (uint32_t)nPass);
+    }
+    if (lastId != TL_NONE) {
+        depth[p] = d;
+        if (outTriId) outTriId[p] = lastId + idBase;
+    }
+    if (outDepth && outDepth != depth) outDepth[p] = d;
+}
+
+template <bool TEXTURED, bool PBR, bool AFFINE>
+__global__ void __launch_bounds__(256, 3) k_tl_shade(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh, const uint2* __restrict__ frags,
+                                                     float4* __restrict__ cols, uint32_t cap, const uint32_t* __restrict__ counters) {
+    pdl_enter();
+    const uint32_t n = min(__ldcg(&counters[6]), cap);
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) {
+        const uint2 f = __ldg(frags + i);
+        const int y = (int)(f.x / pc.W), x = (int)(f.x - (uint32_t)y * pc.W);
+        cols[i] = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, f.y) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, f.y);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_tl_blend(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh, uint2* __restrict__ span,
+                                                  const float4* __restrict__ cols, uint32_t cap, float* __restrict__ hdr, const float* __restrict__ depth) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * 8u, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * 32 + 8 * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * 8 + 4 * (int)(warp >> 2) + (int)(lane >> 3);
+    if (x >= (int)pc.W || y >= (int)pc.H) return;
+    const size_t p = (size_t)y * pc.W + x;
+    float4 col = reinterpret_cast<const float4*>(hdr)[p];
+    const uint2 sp = span[p];
+    if (sp.y) {
+        span[p] = make_uint2(0u, 0u);            // re-armed for the next frame
+        for (uint32_t i = 0; i < sp.y && sp.x + i < cap; ++i) {
+            const float4 src = __ldg(cols + sp.x + i);
+            const float a = src.w, ia = 1.0f - a;
+            col.x = src.x * a + col.x * ia; col.y = src.y * a + col.y * ia; col.z = src.z * a + col.z * ia;
+            col.w = a * ia;
+        }
+    }
+    if (sh.skyFaces && depth[p] == 1.0f) col = sky_pixel(sh, x, y);   // the skybox follows the translucent list (RenderScene.cpp:228)
+    if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(col);
+    if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = col;
+    else reinterpret_cast<float4*>(hdr)[p] = col;
+}
+
 // Appendix B.15 + B.16: the translucent list inside the 4x multisampled base pass.  Every sample is its own blend target: the
 // opaque resolve left one linear colour per sample (msColour) and the four sample passes of the translucent raster one list per
 // sample.  Per pixel the four lists are merged in ID order; a primitive is shaded ONCE at the pixel centre when any of its
@@ -440,6 +556,20 @@ void launch_tl_resolve_ms(const PassConst& pc, const ShadeConst& sh, uint32_t* h
     const uint32_t tilesX = (pc.W + 31u) / 32u, tilesY = (pc.H + 7u) / 8u;
     PassConst q = pc; q.tilesX = tilesX; q.tilesY = tilesY;
     launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3(tilesX * tilesY), dim3(256), st, true, q, sh, head, nodes, cap, idBase, msColour, msDepth, msTriId);
+}
+
+void launch_tl_resolve_split(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,
+                             uint32_t* counters, uint2* span, uint2* frags, float4* cols, int numSMs, cudaStream_t st) {
+    const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
+    const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
+    const uint32_t tilesX = (pc.W + 31u) / 32u, tilesY = (pc.H + 7u) / 8u;
+    PassConst q = pc; q.tilesX = tilesX; q.tilesY = tilesY;
+    launch_k(k_tl_gather, dim3(tilesX * tilesY), dim3(256), st, true, q, head, nodes, cap, idBase, depth, sh.outTriId, sh.outDepth, span, frags, counters);
+    using Kern = void (*)(PassConst, ShadeConst, const uint2*, float4*, uint32_t, const uint32_t*);
+    static const Kern kern[8] = {k_tl_shade<false, false, false>, k_tl_shade<true, false, false>, k_tl_shade<false, true, false>, k_tl_shade<true, true, false>,
+                                 k_tl_shade<false, false, true>,  k_tl_shade<true, false, true>,  k_tl_shade<false, true, true>,  k_tl_shade<true, true, true>};
+    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3((unsigned)numSMs * 6u), dim3(256), st, true, q, sh, (const uint2*)frags, cols, cap, (const uint32_t*)counters);
+    launch_k(k_tl_blend, dim3(tilesX * tilesY), dim3(256), st, true, q, sh, span, (const float4*)cols, cap, hdr, (const float*)depth);
 }
 
 }  // namespace reb

@@ -79,6 +79,7 @@ struct reb_ctx {
     // internal linear-colour / depth targets when the caller did not enable those outputs
     uint32_t* tlHead = nullptr; uint4* tlNodes = nullptr; uint32_t tlCap = 0; uint32_t* tlCounters = nullptr; uint2* tlLarge = nullptr; uint32_t tlLargeCap = 0;
     float* tlHdr = nullptr; float* tlDepth = nullptr; size_t tlPx = 0;   // tlPx = pixels x samples the lists are sized for
+    uint2* tlSpan = nullptr; uint2* tlFrags = nullptr; float4* tlCols = nullptr;   // split resolve (1 sample): per-pixel span, passing fragments {pixel, id}, their colours
     float4* msColour = nullptr;   // 4 sample planes of linear colour: a translucent list inside a multisampled pass blends per sample
     bool tlFollows = false, tlPending = false; ShadeConst tlShade; uint32_t tlIdBase = 0; uint64_t tlDropped = 0;
     // multisampling (Appendix B.15): 1 or 4 samples; with 4, `vis` holds four planes and each sample pass leaves its depth / triangle ID plane here
@@ -661,7 +662,12 @@ int run_translucent(reb_ctx* ctx) {
         ctx->launches += 3;
     }
     pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
-    launch_tl_resolve(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, hdr, depth, ctx->tlCounters, ctx->stream); ctx->launches++;
+    static const bool fusedResolve = std::getenv("REB_TL_FUSED_RESOLVE") != nullptr;   // A/B: the one-kernel resolve
+    if (fusedResolve || !ctx->tlFrags) { launch_tl_resolve(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, hdr, depth, ctx->tlCounters, ctx->stream); ctx->launches++; }
+    else {
+        launch_tl_resolve_split(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, hdr, depth, ctx->tlCounters, ctx->tlSpan, ctx->tlFrags, ctx->tlCols, ctx->numSMs, ctx->stream);
+        ctx->launches += 3;
+    }
     CU(cudaGetLastError());
     ctx->tlPending = true;
     return REB_OK;

@@ -65,7 +65,7 @@ int reb_destroy(reb_ctx* ctx) {
                     ctx->pass[0].blockBox, ctx->pass[1].blockBox, ctx->pass[0].blockVisible, ctx->pass[1].blockVisible,
                     ctx->pass[2].dDraws, ctx->pass[2].vtxA, ctx->pass[2].vtxBC, ctx->pass[2].blockDraw, ctx->pass[2].flatSlots, ctx->pass[2].drawBounds,
                     ctx->pass[2].drawVisible, ctx->pass[2].blockBox, ctx->pass[2].blockVisible, ctx->pass[2].vtxUV,
-                    ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge, ctx->msColour,
+                    ctx->pass[0].triMaterial, ctx->pass[1].triMaterial, ctx->pass[2].triMaterial, ctx->tlHead, ctx->tlNodes, ctx->tlCounters, ctx->tlHdr, ctx->tlDepth, ctx->tlLarge, ctx->msColour, ctx->tlSpan, ctx->tlFrags, ctx->tlCols,
                     ctx->pass[0].posS, ctx->pass[1].posS, ctx->pass[2].posS, ctx->pass[0].nrmS, ctx->pass[1].nrmS, ctx->pass[2].nrmS,
                     ctx->pass[0].triStream, ctx->pass[1].triStream, ctx->pass[2].triStream,
                     ctx->pass[0].blockRefs, ctx->pass[1].blockRefs, ctx->pass[2].blockRefs, ctx->pass[0].triBlockList, ctx->pass[1].triBlockList, ctx->pass[2].triBlockList,
@@ -286,6 +286,10 @@ static int render_base_pass(reb_ctx* ctx, const reb_draw* draws, uint32_t n, con
         if ((rc = dev_alloc(ctx, &ctx->tlHead, spx)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)8)) ||
             (rc = dev_alloc(ctx, &ctx->tlHdr, ctx->outF32 ? 0 : px * 4)) || (rc = dev_alloc(ctx, &ctx->tlDepth, ctx->outDepth ? 0 : px))) return rc;
         launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, spx, ctx->numSMs, ctx->stream); ctx->launches++;
+        // split resolve of the 1-sample pass: span per pixel (zero = nothing), one record + one colour per passing fragment
+        if ((rc = dev_alloc(ctx, &ctx->tlSpan, ctx->samples == 1 ? px : 0)) || (rc = dev_alloc(ctx, &ctx->tlFrags, ctx->samples == 1 ? (size_t)cap : 0)) ||
+            (rc = dev_alloc(ctx, &ctx->tlCols, ctx->samples == 1 ? (size_t)cap : 0))) return rc;
+        if (ctx->tlSpan) CU(cudaMemsetAsync(ctx->tlSpan, 0, px * sizeof(uint2), ctx->stream));
         ctx->tlCap = cap; ctx->tlPx = spx;
     }
     uint64_t nOpaque = 0;
