@@ -425,7 +425,8 @@ __global__ void __launch_bounds__(256, 3) k_tl_shade(const __grid_constant__ Pas
     const uint32_t n = min(__ldcg(&counters[6]), cap);
     for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) {
         const uint2 f = __ldg(frags + i);
-        const int y = (int)(f.x / pc.W), x = (int)(f.x - (uint32_t)y * pc.W);
+        const uint32_t pix = f.x & 0x0FFFFFFFu;   // (bits 28-31: the sample mask of a multisampled pass; extents are <= 16384, so a pixel index fits 28 bits)
+        const int y = (int)(pix / pc.W), x = (int)(pix - (uint32_t)y * pc.W);
         cols[i] = PBR ? shade_pixel_pbr<TEXTURED, AFFINE>(pc, sh, x, y, f.y) : shade_pixel<TEXTURED, AFFINE>(pc, sh, x, y, f.y);
     }
 }
@@ -526,6 +527,121 @@ __global__ void __launch_bounds__(256, 2) k_tl_resolve_ms(const __grid_constant_
     if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = out;
 }
 
+// The multisampled resolve (k_tl_resolve_ms) as the same three kernels: the gather merges the pixel's four per-sample lists in ID order
+// (four selection cursors, walked twice: count, then emit), replays the per-sample depth tests and emits one record per primitive
+// that passes at any sample, {pixel | sample mask << 28, id}; k_tl_shade shades the records; the blend applies each colour to the
+// samples of its mask, draws the sky per sample, resolves and encodes.
+__global__ void __launch_bounds__(256) k_tl_gather_ms(const __grid_constant__ PassConst pc, uint32_t* __restrict__ head, const uint4* __restrict__ nodes, uint32_t cap,
+                                                      uint32_t idBase, float* __restrict__ msDepth, uint32_t* __restrict__ msTriId, uint2* __restrict__ span,
+                                                      uint2* __restrict__ frags, uint32_t* __restrict__ counters) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * 8u, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * 32 + 8 * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * 8 + 4 * (int)(warp >> 2) + (int)(lane >> 3);
+    const bool inb = x < (int)pc.W && y < (int)pc.H;
+    const size_t p = inb ? (size_t)y * pc.W + x : 0, plane = (size_t)pc.W * pc.H;
+    float d0[4]; uint32_t h[4];
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        d0[k] = inb ? msDepth[k * plane + p] : 0.0f;
+        h[k] = inb ? head[k * plane + p] : TL_NONE;
+        if (h[k] != TL_NONE) { head[k * plane + p] = TL_NONE; any = true; }   // re-armed for the next frame
+    }
+    // the merge, run twice: emit == false counts the records, emit == true writes them (and the planes)
+    auto merge = [&](bool emit, uint32_t base) -> uint32_t {
+        float d[4] = {d0[0], d0[1], d0[2], d0[3]};
+        uint32_t lastId[4] = {TL_NONE, TL_NONE, TL_NONE, TL_NONE};
+        TlCursor c[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c[k] = tl_first(nodes, cap, h[k]);
+        uint32_t n = 0;
+        for (;;) {
+            const uint32_t id = min(min(c[0].id, c[1].id), min(c[2].id, c[3].id));
+            if (id == TL_NONE) break;
+            uint32_t mask = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (c[k].id == id && c[k].z <= d[k]) { mask |= 1u << k; d[k] = c[k].z; lastId[k] = id; }
+            if (mask) {
+                if (emit && base + n < cap) frags[base + n] = make_uint2((uint32_t)p | (mask << 28), id);
+                ++n;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (c[k].id == id) c[k] = tl_next(nodes, cap, h[k], id);
+        }
+        if (emit) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (lastId[k] != TL_NONE) { msDepth[k * plane + p] = d[k]; msTriId[k * plane + p] = lastId[k] + idBase; }
+        }
+        return n;
+    };
+    const uint32_t nRec = any ? merge(false, 0u) : 0u;
+    uint32_t incl = nRec;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o); if ((int)lane >= o) incl += v; }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    uint32_t wbase = 0;
+    if (total) {
+        if (lane == 0) wbase = atomicAdd(&counters[6], total);
+        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 0);
+    }
+    if (!inb || !nRec) return;
+    const uint32_t base = wbase + incl - nRec;
+    merge(true, base);
+    span[p] = make_uint2(base, nRec);
+}
+
+__global__ void __launch_bounds__(256) k_tl_blend_ms(const __grid_constant__ PassConst pc, const __grid_constant__ ShadeConst sh, uint2* __restrict__ span,
+                                                     const uint2* __restrict__ frags, const float4* __restrict__ cols, uint32_t cap, const float4* __restrict__ msColour,
+                                                     const float* __restrict__ msDepth, const uint32_t* __restrict__ msTriId) {
+    pdl_enter();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t ty = blockIdx.x / pc.tilesX, tx = blockIdx.x - ty * pc.tilesX;
+    if (!row_owned(ty * 8u, pc.rank, pc.nRanks, pc.bandH)) return;
+    const int x = (int)tx * 32 + 8 * (int)(warp & 3u) + (int)(lane & 7u), y = (int)ty * 8 + 4 * (int)(warp >> 2) + (int)(lane >> 3);
+    if (x >= (int)pc.W || y >= (int)pc.H) return;
+    const size_t p = (size_t)y * pc.W + x, plane = (size_t)pc.W * pc.H;
+    float4 col[4]; float d[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { col[k] = msColour[k * plane + p]; d[k] = msDepth[k * plane + p]; }
+    const uint2 sp = span[p];
+    if (sp.y) {
+        span[p] = make_uint2(0u, 0u);
+        for (uint32_t i = 0; i < sp.y && sp.x + i < cap; ++i) {
+            const uint32_t mask = __ldg(&frags[sp.x + i].x) >> 28;
+            const float4 src = __ldg(cols + sp.x + i);
+            const float a = src.w, ia = 1.0f - a;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if ((mask >> k) & 1u) {
+                    col[k].x = src.x * a + col[k].x * ia; col[k].y = src.y * a + col[k].y * ia; col[k].z = src.z * a + col[k].z * ia;
+                    col[k].w = a * ia;
+                }
+        }
+    }
+    bool anySky = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) anySky = anySky || (sh.skyFaces && d[k] == 1.0f);
+    if (anySky) {
+        const float4 s = sky_pixel(sh, x, y);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (d[k] == 1.0f) col[k] = s;
+    }
+    float4 out;
+    out.x = ((col[0].x + col[1].x) + (col[2].x + col[3].x)) * 0.25f;
+    out.y = ((col[0].y + col[1].y) + (col[2].y + col[3].y)) * 0.25f;
+    out.z = ((col[0].z + col[1].z) + (col[2].z + col[3].z)) * 0.25f;
+    out.w = ((col[0].w + col[1].w) + (col[2].w + col[3].w)) * 0.25f;
+    if (sh.outDepth) sh.outDepth[p] = d[0];
+    if (sh.outTriId) sh.outTriId[p] = msTriId[p];
+    if (sh.outSRGB8) reinterpret_cast<uint32_t*>(sh.outSRGB8)[p] = pack_srgb8(out);
+    if (sh.outF32) reinterpret_cast<float4*>(sh.outF32)[p] = out;
+}
+
 void launch_tl_raster(const PassConst& pc, const float* opaqueDepth, uint32_t* head, uint4* nodes, uint32_t cap, uint32_t* counters, uint2* largeList, int numSMs,
                       cudaStream_t st) {
     if (pc.nTris == 0) return;
@@ -570,6 +686,20 @@ void launch_tl_resolve_split(const PassConst& pc, const ShadeConst& sh, uint32_t
                                  k_tl_shade<false, false, true>,  k_tl_shade<true, false, true>,  k_tl_shade<false, true, true>,  k_tl_shade<true, true, true>};
     launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3((unsigned)numSMs * 6u), dim3(256), st, true, q, sh, (const uint2*)frags, cols, cap, (const uint32_t*)counters);
     launch_k(k_tl_blend, dim3(tilesX * tilesY), dim3(256), st, true, q, sh, span, (const float4*)cols, cap, hdr, (const float*)depth);
+}
+
+void launch_tl_resolve_ms_split(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, const float4* msColour,
+                                float* msDepth, uint32_t* msTriId, uint32_t* counters, uint2* span, uint2* frags, float4* cols, int numSMs, cudaStream_t st) {
+    const bool tex = sh.nTextures && pc.vtxUV, pbr = sh.shadingModel == 1u;
+    const bool affine = sh.STR[3] == 0.0f && sh.STR[7] == 0.0f && sh.STR[11] == 0.0f && sh.STR[15] == 1.0f;
+    const uint32_t tilesX = (pc.W + 31u) / 32u, tilesY = (pc.H + 7u) / 8u;
+    PassConst q = pc; q.tilesX = tilesX; q.tilesY = tilesY;
+    launch_k(k_tl_gather_ms, dim3(tilesX * tilesY), dim3(256), st, true, q, head, nodes, cap, idBase, msDepth, msTriId, span, frags, counters);
+    using Kern = void (*)(PassConst, ShadeConst, const uint2*, float4*, uint32_t, const uint32_t*);
+    static const Kern kern[8] = {k_tl_shade<false, false, false>, k_tl_shade<true, false, false>, k_tl_shade<false, true, false>, k_tl_shade<true, true, false>,
+                                 k_tl_shade<false, false, true>,  k_tl_shade<true, false, true>,  k_tl_shade<false, true, true>,  k_tl_shade<true, true, true>};
+    launch_k(kern[(tex ? 1 : 0) | (pbr ? 2 : 0) | (affine ? 4 : 0)], dim3((unsigned)numSMs * 6u), dim3(256), st, true, q, sh, (const uint2*)frags, cols, cap, (const uint32_t*)counters);
+    launch_k(k_tl_blend_ms, dim3(tilesX * tilesY), dim3(256), st, true, q, sh, span, (const uint2*)frags, (const float4*)cols, cap, msColour, (const float*)msDepth, (const uint32_t*)msTriId);
 }
 
 }  // namespace reb

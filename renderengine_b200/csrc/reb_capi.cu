@@ -651,7 +651,13 @@ int run_translucent(reb_ctx* ctx) {
             ctx->launches += 2;
         }
         pc.tilesX = (pc.W + TILE_W - 1) / TILE_W; pc.tilesY = (pc.H + TILE_H - 1) / TILE_H;
-        launch_tl_resolve_ms(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, ctx->msColour, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++;
+        static const bool fusedMs = std::getenv("REB_TL_FUSED_RESOLVE") != nullptr;
+        if (fusedMs || !ctx->tlFrags) { launch_tl_resolve_ms(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, ctx->msColour, ctx->msDepth, ctx->msTriId, ctx->stream); ctx->launches++; }
+        else {
+            launch_tl_resolve_ms_split(pc, sh, ctx->tlHead, ctx->tlNodes, ctx->tlCap, ctx->tlIdBase, ctx->msColour, ctx->msDepth, ctx->msTriId, ctx->tlCounters, ctx->tlSpan, ctx->tlFrags,
+                                       ctx->tlCols, ctx->numSMs, ctx->stream);
+            ctx->launches += 3;
+        }
         CU(cudaGetLastError());
         ctx->tlPending = true;
         return REB_OK;

@@ -286,9 +286,8 @@ static int render_base_pass(reb_ctx* ctx, const reb_draw* draws, uint32_t n, con
         if ((rc = dev_alloc(ctx, &ctx->tlHead, spx)) || (rc = dev_alloc(ctx, &ctx->tlNodes, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCounters, (size_t)8)) ||
             (rc = dev_alloc(ctx, &ctx->tlHdr, ctx->outF32 ? 0 : px * 4)) || (rc = dev_alloc(ctx, &ctx->tlDepth, ctx->outDepth ? 0 : px))) return rc;
         launch_fill_u32(ctx->tlHead, 0xFFFFFFFFu, spx, ctx->numSMs, ctx->stream); ctx->launches++;
-        // split resolve of the 1-sample pass: span per pixel (zero = nothing), one record + one colour per passing fragment
-        if ((rc = dev_alloc(ctx, &ctx->tlSpan, ctx->samples == 1 ? px : 0)) || (rc = dev_alloc(ctx, &ctx->tlFrags, ctx->samples == 1 ? (size_t)cap : 0)) ||
-            (rc = dev_alloc(ctx, &ctx->tlCols, ctx->samples == 1 ? (size_t)cap : 0))) return rc;
+        // split resolve: span per pixel (zero = nothing), one record + one colour per passing fragment (per primitive and pixel with 4 samples)
+        if ((rc = dev_alloc(ctx, &ctx->tlSpan, px)) || (rc = dev_alloc(ctx, &ctx->tlFrags, (size_t)cap)) || (rc = dev_alloc(ctx, &ctx->tlCols, (size_t)cap))) return rc;
         if (ctx->tlSpan) CU(cudaMemsetAsync(ctx->tlSpan, 0, px * sizeof(uint2), ctx->stream));
         ctx->tlCap = cap; ctx->tlPx = spx;
     }

@@ -73,6 +73,8 @@ void launch_tl_resolve(const PassConst& pc, const ShadeConst& sh, uint32_t* head
 // the 1-sample resolve as three kernels: gather (order + depth replay -> passing fragments), shade (one thread per fragment), blend
 void launch_tl_resolve_split(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, float* hdr, float* depth,
                              uint32_t* counters, uint2* span, uint2* frags, float4* cols, int numSMs, cudaStream_t st);
+void launch_tl_resolve_ms_split(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, const float4* msColour,
+                                float* msDepth, uint32_t* msTriId, uint32_t* counters, uint2* span, uint2* frags, float4* cols, int numSMs, cudaStream_t st);
 // the same inside a 4x multisampled pass: merges the four per-sample lists of a pixel over the per-sample colours / depths
 void launch_tl_resolve_ms(const PassConst& pc, const ShadeConst& sh, uint32_t* head, const uint4* nodes, uint32_t cap, uint32_t idBase, const float4* msColour,
                           float* msDepth, uint32_t* msTriId, cudaStream_t st);
