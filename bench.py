@@ -532,6 +532,15 @@ def run_single(args, torch, dist, local_rank):
         # ---- the other single-GPU configurations of BASELINE.json, same invocation ("1080p/4K") -------------------------------
         line["c1"] = sub_record(args, "C1", local_rank, flush, peak, 50, 3)
         line["c3"] = sub_record(args, "C3", local_rank, flush, peak, 30, 1)
+        # C3 with the reference's default 4096^2 map as well (RenderScene.cpp:26); device time only
+        c3big = sc.make_scene("C3", shadow_size=4096)
+        rb = Rig(c3big, local_rank)
+        perb = rb.timed(rb.frame, 20, 3, flush)
+        mb = float(np.median(perb))
+        bsh, bfw = sc.algorithmic_bytes(c3big)
+        line["c3"]["shadow_4096"] = {"workload": workload_string(args, 1, c3big, "frame"), "ms_per_frame": mb, "value": c3big["n_triangles"] / (mb * 1e3), "unit": UNIT,
+                                     "algorithmic_bytes": bsh + bfw, "frac_of_peak": (bsh + bfw) / (mb * 1e-3) / 1e9 / peak}
+        rb.close()
         # ---- the binned tile path on the record: the C2 grid at subdivision level 2 (16 k triangles of ~16 / 52 px) with the
         # reference's default 4096^2 shadow map (RenderScene.cpp:26) ------------------------------------------------------------
         low = sc.make_scene("C2", level=2, shadow_size=4096)
