@@ -17,9 +17,12 @@
 namespace reb {
 
 #ifndef K0_PER_THREAD_D
-#define K0_PER_THREAD_D 4
+#define K0_PER_THREAD_D 1
 #endif
-constexpr int K0_PER_THREAD = K0_PER_THREAD_D;   // cache slots per thread: four independent load chains in flight
+// cache slots per thread.  Four (independent load chains in flight) was the round-1 optimum; since the source streams are read in slot
+// order (k_reorder.cu) more, lighter threads win: C2 136.2 / 134.5 / 136.2 / 132.1 us per frame at 4 / 2 / 3 / 1, C1 48.2 -> 43.0 us
+constexpr int K0_PER_THREAD = K0_PER_THREAD_D;
+constexpr int K0_PER_THREAD_CULL = 4;            // sort-first split: most CTAs find nothing to do, fewer and fatter ones cost less (slowest rank of C4 at N = 8: 307 vs 316 us)
 
 constexpr uint32_t K0_MIN_GRID = 296u;           // two CTAs per SM
 struct K0In { float4 p, n; uint32_t node; bool valid; };
@@ -135,7 +138,8 @@ __global__ void __launch_bounds__(256) k_vertex_both(const __grid_constant__ Pas
 
 template <bool SHADOW, bool CULL>
 __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassConst pc) {
-    const uint32_t base = blockIdx.x * (256u * K0_PER_THREAD) + threadIdx.x;
+    constexpr int PER = CULL ? K0_PER_THREAD_CULL : K0_PER_THREAD;
+    const uint32_t base = blockIdx.x * (256u * PER) + threadIdx.x;
     if (CULL) {
         // launched with PDL behind k_cull (an ordinary launch, so everything older has completed): the prologue and the map clear
         // touch nothing k_cull does and run while it does; only the vertex loop needs its marks
@@ -148,11 +152,11 @@ __global__ void __launch_bounds__(256) k_vertex(const __grid_constant__ PassCons
         k0_prologue(pc);
         if (SHADOW) k0_clear_shadow(pc);
     }
-    K0In in[K0_PER_THREAD];
+    K0In in[PER];
 #pragma unroll
-    for (int k = 0; k < K0_PER_THREAD; ++k) in[k] = k0_load<SHADOW, CULL>(pc, base + 256u * k);
+    for (int k = 0; k < PER; ++k) in[k] = k0_load<SHADOW, CULL>(pc, base + 256u * k);
 #pragma unroll
-    for (int k = 0; k < K0_PER_THREAD; ++k) k0_transform_store<SHADOW>(pc, base + 256u * k, in[k]);
+    for (int k = 0; k < PER; ++k) k0_transform_store<SHADOW>(pc, base + 256u * k, in[k]);
 }
 
 // Per-draw referenced vertex range (min, max index), computed when a draw list changes (not per frame).
@@ -197,7 +201,8 @@ void launch_vertex(const PassConst& pc, bool shadow, bool pdl, cudaStream_t st) 
     if (pc.cacheSize == 0) return;
     // at least K0_MIN_GRID CTAs: the pass prologue and the shadow-map clear are sliced over the grid (a 2 k-vertex scene
     // otherwise streams the 16-MB clear through three CTAs: 107 us); CTAs past the cache only do their slice
-    const uint32_t grid = std::max((pc.cacheSize + 256u * K0_PER_THREAD - 1u) / (256u * K0_PER_THREAD), K0_MIN_GRID);
+    const uint32_t per = 256u * (uint32_t)(pc.drawVisible ? K0_PER_THREAD_CULL : K0_PER_THREAD);
+    const uint32_t grid = std::max((pc.cacheSize + per - 1u) / per, K0_MIN_GRID);
     using Kern = void (*)(PassConst);
     static const Kern kern[4] = {k_vertex<false, false>, k_vertex<true, false>, k_vertex<false, true>, k_vertex<true, true>};
     launch_k(kern[(shadow ? 1 : 0) | (pc.drawVisible ? 2 : 0)], dim3(grid), dim3(256), st, pdl, pc);
